@@ -1,0 +1,220 @@
+"""Generate tests/golden/*.npz by running the REAL reference (``/root/reference``) on CPU.
+
+Run only in the build container (the reference does not travel to the GPU box):
+
+    python oracle/gen_golden.py
+
+The reference module needs matplotlib at import time (U:21-22) which is not installed; three
+stub modules are injected before ``import utils``.  The stored fixtures hold the
+*outputs of the reference's own functions* on seeded synthetic inputs (inputs are regenerated
+from the seeds by ``gaussian_processes_b200.synth``; only what cannot be regenerated is stored).
+
+The body of ``closure_hyperparams`` (U:2030-2099) is a nested function and cannot be imported;
+``ref_closure`` below re-states its *sequencing* around calls into the reference's own
+localker / acosker / mean_f / compute_loglikelihood / compute_KL_div.
+"""
+from __future__ import annotations
+
+import io
+import contextlib
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+REF = "/root/reference/Spatial_GP_repo"
+
+
+def import_reference():
+    for name in ("matplotlib", "matplotlib.pyplot", "matplotlib.ticker"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.modules["matplotlib.ticker"].FuncFormatter = object
+    sys.modules["matplotlib.ticker"].MaxNLocator = object
+    sys.path.insert(0, REF)
+    with contextlib.redirect_stdout(io.StringIO()):
+        import utils as ref  # noqa
+    torch.set_default_device("cpu")
+    return ref
+
+
+from gaussian_processes_b200 import synth  # noqa: E402
+
+
+def ref_closure(ref, theta, X, r, xtilde, n_px, B, m_b, V_b, f_params):
+    """Sequencing of U:2030-2099 around the reference's own functions."""
+    lo, hi = synth.THETA_LIMS_LO, synth.THETA_LIMS_HI
+    nt, ntilde = X.shape[0], xtilde.shape[0]
+    C, mask, dC = ref.localker(theta=theta, theta_higher_lims=hi, theta_lower_lims=lo, n_px_side=n_px, grad=True)
+    K_tilde, dK_tilde = ref.acosker(theta, xtilde[:, mask], xtilde[:, mask], C=C, dC=dC, diag=False)
+    K, dK = ref.acosker(theta, X[:, mask], xtilde[:, mask], C=C, dC=dC, diag=False) if ntilde != nt else (K_tilde, dK_tilde)
+    Kvec, dKvec = ref.acosker(theta, X[:, mask], x2=None, C=C, dC=dC, diag=True)
+    K_tilde_b = B.T @ K_tilde @ B
+    K_tilde_b = (K_tilde_b + K_tilde_b.T) * 0.5
+    K_b = K @ B
+    dK_tilde_b = {k: B.T @ dK_tilde[k] @ B for k in dK_tilde}
+    dK_b = {k: dK[k] @ B for k in dK}
+    K_tilde_inv_b = torch.linalg.solve(K_tilde_b, torch.eye(K_tilde_b.shape[0]))
+    KKtilde_inv_b = K_b @ K_tilde_inv_b if ntilde != nt else B
+    f_mean, lambda_m, lambda_var, dlambda_m, dlambda_var = ref.mean_f(
+        f_params=f_params, calculate_moments=True, x=X[:, mask], K_tilde=K_tilde_b, KKtilde_inv=KKtilde_inv_b,
+        Kvec=Kvec, K=K_b, C=C, m=m_b, V=V_b, theta=theta, kernfun=ref.acosker, lambda_m=None, lambda_var=None,
+        dK=dK_b, dK_tilde=dK_tilde_b, dK_vec=dKvec, K_tilde_inv=K_tilde_inv_b)
+    loglik, dloglik = ref.compute_loglikelihood(X.new_tensor(r) if not torch.is_tensor(r) else r, f_mean, lambda_m,
+                                                lambda_var, f_params, dlambda_m=dlambda_m, dlambda_var=dlambda_var)
+    KL, dKL = ref.compute_KL_div(m_b, V_b, K_tilde_b, K_tilde_inv=K_tilde_inv_b, dK_tilde=dK_tilde_b)
+    keys = list(theta.keys())
+    return dict(C=C, mask=mask, K_tilde=K_tilde, K=K, Kvec=Kvec, K_tilde_b=K_tilde_b, K_tilde_inv_b=K_tilde_inv_b,
+                a=KKtilde_inv_b, K_b=K_b, lam_m=lambda_m, lam_var=lambda_var, f=f_mean, loglik=loglik, KL=KL,
+                dloglik=torch.stack([dloglik[k] for k in keys]), dKL=torch.stack([dKL[k] for k in keys]),
+                dC=dC, dK_tilde=dK_tilde, dK=dK, dKvec=dKvec)
+
+
+def setup_case(ref, N, n, m, cfg, theta_dict):
+    prob = synth.make_problem(N, n, m, cfg=cfg, theta=theta_dict)
+    theta = synth.theta_tensors(prob.theta)
+    lo, hi = synth.THETA_LIMS_LO, synth.THETA_LIMS_HI
+    C, mask = ref.localker(theta=theta, theta_higher_lims=hi, theta_lower_lims=lo, n_px_side=n, grad=False)
+    Kt = ref.acosker(theta, prob.xtilde[:, mask], prob.xtilde[:, mask], C=C, dC=None, diag=False)
+    ev, evec = torch.linalg.eigh(Kt, UPLO="L")
+    keep = ev > max(ev.max() * ref.EIGVAL_TOL, ref.EIGVAL_TOL)
+    B = evec[:, keep]
+    Kt_b = torch.diag(ev[keep])
+    m_b, V_b = synth.make_variational_state(Kt_b, cfg)
+    return prob, theta, B, m_b, V_b, ev
+
+
+def gen_closure_case(ref, name, N, n, m, cfg, theta_dict, store_big=False, perturb=None):
+    prob, theta, B, m_b, V_b, ev = setup_case(ref, N, n, m, cfg, theta_dict)
+    if perturb:  # evaluate the closure at a theta different from the one B was built at (frozen B, U:2036-2049)
+        theta = synth.theta_tensors({k: prob.theta[k] + perturb.get(k, 0.0) for k in prob.theta})
+    f_params = {"logA": torch.tensor(prob.logA), "lambda0": torch.tensor(prob.lambda0)}
+    out = ref_closure(ref, theta, prob.X, prob.r, prob.xtilde, n, B, m_b, V_b, f_params)
+    # E-step pieces at the same state (a10, a8, a7 f-param mode), with the *closure's* a / K_b
+    a, K_b = out["a"], out["K_b"]
+    m_new, V_new = ref.Estep(r=prob.r, KKtilde_inv=a, m=m_b, f_params=f_params, f_mean=out["f"],
+                             K_tilde=out["K_tilde_b"], K_tilde_inv=out["K_tilde_inv_b"], update_V_inv=False, alpha=1)
+    A = torch.exp(f_params["logA"])
+    g = A * a.T @ (prob.r - out["f"])
+    G = A * A * a.T @ (a * out["f"][:, None])
+    lam0 = ref.lambda0_given_logA(f_params["logA"], prob.r, out["lam_m"], out["lam_var"])
+    ll_f, dll_f = ref.compute_loglikelihood(prob.r, out["f"], out["lam_m"], out["lam_var"], f_params,
+                                            compute_grad_for_f_params=True)
+    lam_m2, lam_var2 = ref.lambda_moments(None, out["K_tilde_b"], a, out["Kvec"], K_b, None, m_new, V_new, theta)
+    keys = list(theta.keys())
+    fx = dict(
+        N=N, n=n, m=m, cfg=cfg, theta=np.array([float(theta[k]) for k in keys]), theta_keys=np.array(keys),
+        theta_B=np.array([prob.theta[k] for k in keys]),
+        q=B.shape[1], p=int(out["mask"].sum()), mask=out["mask"].numpy(),
+        B=B.numpy(), m_b=m_b.numpy(), V_b=V_b.numpy(), logA=prob.logA, lambda0=prob.lambda0,
+        loglik=float(out["loglik"]), KL=float(out["KL"]), dloglik=out["dloglik"].numpy(), dKL=out["dKL"].numpy(),
+        lam_m=out["lam_m"].numpy(), lam_var=out["lam_var"].numpy(), f=out["f"].numpy(), Kvec=out["Kvec"].numpy(),
+        K_tilde_b=out["K_tilde_b"].numpy(), K_tilde_inv_b=out["K_tilde_inv_b"].numpy(),
+        estep_g=g.numpy(), estep_G=G.numpy(), estep_m=m_new.numpy(), estep_V=V_new.numpy(),
+        lam_m_after=lam_m2.numpy(), lam_var_after=lam_var2.numpy(),
+        lambda0_closed=float(lam0), fpar_loglik=float(ll_f), fpar_dlogA=float(dll_f["logA"]),
+        fpar_dlambda0=float(dll_f["lambda0"]), eigvals=ev.numpy(),
+    )
+    if store_big:
+        dkeys = list(out["dC"].keys())
+        fx.update(C=out["C"].numpy(), K_tilde=out["K_tilde"].numpy(), K=out["K"].numpy(),
+                  dC_keys=np.array(dkeys), dC=np.stack([out["dC"][k].numpy() for k in dkeys]),
+                  dK_keys=np.array(list(out["dK"].keys())),
+                  dK=np.stack([out["dK"][k].numpy() for k in out["dK"]]),
+                  dK_tilde=np.stack([out["dK_tilde"][k].numpy() for k in out["dK_tilde"]]),
+                  dKvec=np.stack([out["dKvec"][k].numpy() for k in out["dKvec"]]))
+    path = os.path.join(ROOT, "tests", "golden", f"{name}.npz")
+    np.savez_compressed(path, **fx)
+    print(f"{name}: N={N} n={n} m={m} p={fx['p']} q={fx['q']} loglik={fx['loglik']:.6f} KL={fx['KL']:.6f} "
+          f"-> {os.path.getsize(path)/1024:.0f} KiB")
+
+
+def gen_kat(ref):
+    """The toy known-answer vectors of moments_gradients.ipynb cells 1-3, recomputed with the
+    reference's own lambda_moments / compute_loglikelihood / log_det and compared with the
+    numbers stored in the notebook output."""
+    a_mat = torch.tensor([[1.0, 2.0, 3.0, 4], [5.0, 6.0, 7.0, 8], [9.0, 10.0, 11.0, 12]])
+    Sigma = torch.tensor([[1.0, 2.0, 3.0], [5.0, 6.0, 7.0], [8.0, 7.0, 6.0]]); Sigma = Sigma + Sigma.T
+    dSigma = torch.tensor([[4.0, 5.0, 6.0], [5.0, 6.0, 7.0], [6.0, 7.0, 8.0]]); dSigma = dSigma + dSigma.T
+    m = torch.tensor([1.0, 2.0, 3.0])
+    dki = torch.tensor([[6.0, 7.0, 8.0, 9.0], [2.0, 3.0, 4.0, 5.0], [9.0, 8.0, 7.0, 6]])
+    dkstar = torch.tensor([3.0, 4, 5, 6])
+    invV = Sigma * 3
+    a, K, dK = a_mat.T, dki.T, dki.T
+    K_tilde_inv = torch.linalg.pinv(Sigma)
+    V = torch.linalg.inv(invV)
+    lam_m, lam_var, dlm, dlv = ref.lambda_moments(None, Sigma, a, dkstar, K, None, m, V, None, dK={"k": dK},
+                                                  dK_tilde={"k": dSigma}, dK_vec={"k": dkstar}, K_tilde_inv=K_tilde_inv)
+    f = torch.tensor([55.0, 4.0, 22.0, 5.0]); r = torch.tensor([23.0, 47.0, 2.0, 1.0])
+    lam_m_toy = torch.tensor([1.0, 2.0, 3.0, 4.0])
+    fp = {"logA": torch.tensor(0.0), "lambda0": torch.tensor(0.0)}
+    ll, dll = ref.compute_loglikelihood(r, f, lam_m_toy, None, fp, dlambda_m=dlm, dlambda_var=dlv)
+    c = V @ K_tilde_inv; b = K_tilde_inv @ m; Bm = dSigma @ K_tilde_inv
+    I10 = 10 * torch.eye(3)
+    KLD = -0.5 * (ref.log_det(V + I10) - ref.log_det(Sigma + I10)) + 0.5 * (m @ b) + 0.5 * torch.trace(c)
+    dKL = 0.5 * torch.trace(Bm) - 0.5 * torch.trace(c @ Bm) - 0.5 * b @ (Bm @ m)
+    got = dict(dlam_m=dlm["k"].numpy(), dlam_var=dlv["k"].numpy(), logLK=float(ll), dlogLK=float(dll["k"]),
+               KLD=float(KLD), dKL=float(dKL))
+    # numbers printed in the notebook's stored output
+    assert np.allclose(got["dlam_m"], [13.75, 19.9167, 26.0833, 32.25], atol=1e-4)
+    assert np.allclose(got["dlam_var"], [-2199.1944, -3161.6944, -4291.75, -5589.3611], atol=1e-4)
+    assert got["logLK"] == 41.0 and abs(got["dlogLK"] - 127749.63888888987) < 1e-6
+    assert abs(got["KLD"] - 34.91913283450331) < 1e-10 and abs(got["dKL"] - 110.47222222222383) < 1e-9
+    print("KAT (moments_gradients.ipynb) reproduced by the reference:", {k: v for k, v in got.items() if np.isscalar(v)})
+
+
+def gen_fit_case(ref, name, N, n, m, cfg, theta_dict, maxiter, nE, nM, nF):
+    """Loop-level fixture: the reference's own varGP on a small synthetic problem."""
+    prob = synth.make_problem(N, n, m, cfg=cfg, theta=theta_dict)
+    theta = synth.theta_tensors(prob.theta, requires_grad=True)
+    args = dict(
+        fit_parameters=dict(ntilde=m, maxiter=maxiter, nEstep=nE, nMstep=nM, nFparamstep=nF, kernfun="acosker",
+                            cellid=0, n_px_side=n, display_hyper=False),
+        xtilde=prob.xtilde, hyperparams_tuple=(theta, dict(synth.THETA_LIMS_LO), dict(synth.THETA_LIMS_HI)),
+        f_params={"logA": torch.tensor(prob.logA), "lambda0": torch.tensor(prob.lambda0)},
+    )
+    with contextlib.redirect_stdout(io.StringIO()):
+        fit, err = ref.varGP(prob.X, prob.r, **args)
+    assert not err["is_error"], err
+    vt = fit["values_track"]
+    keys = list(fit["hyperparams_tuple"][0].keys())
+    fx = dict(N=N, n=n, m=m, cfg=cfg, maxiter=maxiter, nEstep=nE, nMstep=nM, nFparamstep=nF,
+              theta0=np.array([prob.theta[k] for k in keys]), theta_keys=np.array(keys),
+              logA0=prob.logA, lambda00=prob.lambda0,
+              logmarginal=vt["loss_track"]["logmarginal"].numpy(), loglikelihood=vt["loss_track"]["loglikelihood"].numpy(),
+              KL=vt["loss_track"]["KL"].numpy(),
+              theta_track=np.stack([vt["theta_track"][k].numpy() for k in keys]),
+              logA_track=vt["f_par_track"]["logA"].numpy(), lambda0_track=vt["f_par_track"]["lambda0"].numpy(),
+              q=fit["B"].shape[1], m_b=fit["m_b"].numpy(), V_b=fit["V_b"].numpy())
+    path = os.path.join(ROOT, "tests", "golden", f"{name}.npz")
+    np.savez_compressed(path, **fx)
+    print(f"{name}: logmarginal track {fx['logmarginal']}")
+
+
+def main():
+    ref = import_reference()
+    assert torch.pi == 3.1415927410125732  # U:25
+    gen_kat(ref)
+    # small closure cases, every intermediate stored
+    gen_closure_case(ref, "closure_dense_n8", N=150, n=8, m=24, cfg=11, theta_dict=synth.THETA_DENSE, store_big=True)
+    gen_closure_case(ref, "closure_local_n12", N=260, n=12, m=40, cfg=12, theta_dict=synth.theta_localised(12),
+                     store_big=True, perturb={"eps_0x": 0.03, "-2log2beta": -0.05, "sigma_0": 0.1, "Amp": 0.2})
+    # m > p: K_tilde is rank deficient, q < m (eigen-truncation active)
+    gen_closure_case(ref, "closure_rankdef_n10", N=300, n=10, m=90, cfg=13,
+                     theta_dict={**synth.THETA_NOTEBOOK, "-2log2beta": 3.0, "-log2rho2": 3.5}, store_big=False,
+                     perturb={"eps_0y": -0.02, "-log2rho2": 0.1})
+    # ntilde == nt (active-learning configuration: K = K_tilde, a = B)
+    gen_closure_case(ref, "closure_square_n8", N=48, n=8, m=48, cfg=14, theta_dict=synth.THETA_DENSE, store_big=False)
+    # BASELINE config 1 (20x20, N=2000, m=100), dense and localised theta
+    gen_closure_case(ref, "closure_c1_dense", N=2000, n=20, m=100, cfg=1, theta_dict=synth.THETA_DENSE)
+    gen_closure_case(ref, "closure_c1_local", N=2000, n=20, m=100, cfg=1, theta_dict=synth.theta_localised(20),
+                     perturb={"eps_0x": 0.01, "eps_0y": -0.01})
+    gen_fit_case(ref, "fit_small_n10", N=400, n=10, m=40, cfg=21, theta_dict=synth.theta_localised(10),
+                 maxiter=4, nE=3, nM=3, nF=3)
+
+
+if __name__ == "__main__":
+    main()
