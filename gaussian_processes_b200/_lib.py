@@ -1,0 +1,114 @@
+"""ctypes binding of libsgp_b200.so (C ABI: include/sgp_b200.h).
+
+The shared object is built in-tree by ``__graft_entry__.build()`` (or ``make -C gaussian_processes_b200/csrc``).
+Importing this module without it raises: the product path has no CPU / PyTorch fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsgp_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build the sm_100a extension first "
+        "(python -c 'import __graft_entry__ as g; g.build()'). There is no CPU fallback.")
+
+lib = C.CDLL(LIB_PATH)
+
+SGP_OK, SGP_E_CUDA, SGP_E_ARG, SGP_E_BOUNDS, SGP_E_UNSUPPORTED, SGP_E_NOMEM = range(6)
+FLAG_KT_NOT_PD, FLAG_KT_SMALL_PIVOT, FLAG_V_NOT_PD, FLAG_V_SMALL_PIVOT, FLAG_NAN = 1, 2, 4, 8, 16
+
+_p = C.c_void_p
+_d = C.c_double
+_i = C.c_int
+_l = C.c_long
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+
+# name -> (restype, argtypes); must list every symbol include/sgp_b200.h declares (checked by tests)
+SIGNATURES = {
+    "sgp_version": (_i, []),
+    "sgp_create": (_i, [_i, C.POINTER(_p)]),
+    "sgp_destroy": (_i, [_p]),
+    "sgp_last_error": (C.c_char_p, [_p]),
+    "sgp_set_slab_rows": (_i, [_p, _l]),
+    "sgp_invalidate_cache": (_i, [_p]),
+    "sgp_launch_count": (_l, [_p, _i]),
+    "sgp_mask_host": (_i, [_dp, _i, C.POINTER(C.c_uint8), _ip]),
+    "sgp_localker": (_i, [_p, _dp, _i, _p, _l, _p, _l, _p]),
+    "sgp_acosker": (_i, [_p, _p, _l, _l, _p, _l, _l, _i, _p, _l, _d, _p, _l, _i, _p]),
+    "sgp_acosker_diag": (_i, [_p, _p, _l, _l, _i, _p, _l, _d, _p, _p]),
+    "sgp_lambda_moments": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _p, _p, _l, _p, _p, _p]),
+    "sgp_fparam_eval": (_i, [_p, _p, _p, _p, _l, _d, _d, _p, _dp, _p]),
+    "sgp_estep_terms": (_i, [_p, _p, _l, _p, _p, _l, _i, _d, _p, _p, _l, _p]),
+    "sgp_cholesky": (_i, [_p, _p, _l, _i, _ip, _p]),
+    "sgp_spd_inverse": (_i, [_p, _p, _l, _i, _p, _l, _dp, _ip, _p]),
+    "sgp_gemm_f64": (_i, [_p, _i, _i, _p, _l, _p, _l, _p, _l, _i, _i, _i, _d, _i, _i, _p]),
+    "sgp_elbo_grad": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i, _dp, _dp, _dp, _p, _l, _i, _p, _p, _l, _d, _d,
+                           _dp, _p, _p, _p, _dp, _p]),
+    "sgp_elbo_grad_host": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i, _dp, _p, _l, _i, _p, _p, _l, _d, _d, _dp]),
+    "sgp_debug_get": (_i, [_p, C.c_char_p, _p, _l, C.POINTER(_l), C.POINTER(_l), C.POINTER(_l)]),
+}
+
+for _name, (_res, _args) in SIGNATURES.items():
+    _fn = getattr(lib, _name)          # AttributeError here == symbol missing from the .so
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+
+class SgpError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libsgp_b200 error {code}: {msg}")
+        self.code = code
+
+
+class Handle:
+    """Owns one sgp_handle (scratch workspace + cached masked image copies) for one CUDA device."""
+
+    def __init__(self, device: int = 0):
+        self._h = _p()
+        rc = lib.sgp_create(int(device), C.byref(self._h))
+        if rc != SGP_OK:
+            raise SgpError(rc, "sgp_create failed")
+        self.device = int(device)
+
+    def check(self, rc: int):
+        if rc != SGP_OK:
+            msg = lib.sgp_last_error(self._h)
+            raise SgpError(rc, msg.decode() if msg else "")
+
+    @property
+    def ptr(self):
+        return self._h
+
+    def launch_count(self, reset: bool = False) -> int:
+        return int(lib.sgp_launch_count(self._h, 1 if reset else 0))
+
+    def close(self):
+        if self._h:
+            lib.sgp_destroy(self._h)
+            self._h = _p()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_handles = {}
+_lock = threading.Lock()
+
+
+def handle_for(device: int) -> Handle:
+    """Per-(thread, device) handle: entry points are re-entrant per handle (SURVEY 8b threading row)."""
+    key = (threading.get_ident(), int(device))
+    with _lock:
+        h = _handles.get(key)
+        if h is None:
+            h = _handles[key] = Handle(device)
+        return h

@@ -1,0 +1,918 @@
+// C ABI of the Spatial_GP hot path (include/sgp_b200.h): handle, workspace, and the orchestration of the
+// fused M-step closure.  Host C++ only launches kernels; there is no CPU compute path.
+#include "../../include/sgp_b200.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "gemm_f64.cuh"
+#include "sgp_kernels.cuh"
+
+using namespace sgp;
+
+namespace {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  cudaError_t reserve(size_t need) {
+    if (need <= bytes) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+    cudaError_t e = cudaMalloc(&p, need);
+    if (e == cudaSuccess) bytes = need;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+};
+
+struct DebugEntry { const double* ptr; long rows, cols, ld; };
+
+inline long rup(long x, long a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+struct sgp_handle {
+  int device = 0;
+  std::string err;
+  long slab_rows = 65536;
+  long launches_base = 0;
+  bool gemm_ready = false;
+  // scratch arena (re-carved every call) + persistent caches
+  DevBuf arena, xg, ug, gcpart, s2part;
+  // cache key of the gathered copies
+  const double* cache_X = nullptr; long cache_N = 0, cache_ldx = 0;
+  const double* cache_U = nullptr; long cache_m = 0, cache_ldu = 0;
+  std::vector<uint8_t> cache_mask;
+  bool cache_valid = false;
+  int* d_flags = nullptr;
+  double* d_scal = nullptr;
+  double* d_out = nullptr;
+  double* h_out = nullptr;  // pinned
+  std::map<std::string, DebugEntry> dbg;
+  // second stream + events for the host-streaming variant
+  cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
+  DevBuf hx[2], hr, small;
+  cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr};
+};
+
+namespace {
+
+int fail(sgp_handle* h, int code, const std::string& msg) {
+  if (h) h->err = msg;
+  return code;
+}
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e__ = (call);                                                             \
+    if (e__ != cudaSuccess)                                                               \
+      return fail(h, SGP_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));    \
+  } while (0)
+
+// torch.linspace(-1, 1, n) in fp64 (ATen: start + step*i below the midpoint, end - step*(n-1-i) above)
+inline double lin_coord(int i, int n) {
+  if (n == 1) return -1.0;
+  const double step = 2.0 / (double)(n - 1);
+  return (i < n / 2) ? (-1.0 + step * i) : (1.0 - step * (n - 1 - i));
+}
+
+ThetaDev make_theta(const double* t) {
+  ThetaDev th;
+  th.s0 = t[0]; th.s02 = t[0] * t[0];
+  th.ex = t[1]; th.ey = t[2];
+  th.eb = std::exp(t[3]); th.er = std::exp(t[4]);
+  th.amp = t[5];
+  return th;
+}
+
+// RF mask of localker (U:880-883), pixel k = iy*n + ix has x = lin[ix], y = lin[iy] (U:876-879)
+int compute_mask(const double* theta, int n, std::vector<uint8_t>& mask, std::vector<int>& idx,
+                 std::vector<double>& gx, std::vector<double>& gy) {
+  const ThetaDev th = make_theta(theta);
+  mask.assign((size_t)n * n, 0);
+  idx.clear(); gx.clear(); gy.clear();
+  for (int iy = 0; iy < n; ++iy)
+    for (int ix = 0; ix < n; ++ix) {
+      const double x = lin_coord(ix, n), y = lin_coord(iy, n);
+      const double la = -th.eb * ((x - th.ex) * (x - th.ex) + (y - th.ey) * (y - th.ey));
+      if (std::exp(la) >= kMaskThr) {
+        mask[(size_t)iy * n + ix] = 1;
+        idx.push_back(iy * n + ix);
+        gx.push_back(x); gy.push_back(y);
+      }
+    }
+  return (int)idx.size();
+}
+
+struct Arena {
+  char* base; size_t off = 0, cap;
+  Arena(void* b, size_t c) : base((char*)b), cap(c) {}
+  template <class T> T* take(size_t n) {
+    off = (off + 255) & ~size_t(255);
+    T* p = (T*)(base + off);
+    off += n * sizeof(T);
+    return p;
+  }
+};
+
+cudaError_t gemm(cudaStream_t st, int al, int bl, int mode, bool small, int nsplit, GemmArgs g) {
+  if (g.k_chunk == 0) g.k_chunk = (int)rup(g.K, 16);
+  if (g.alpha == 0.0) g.alpha = 1.0;
+  return gemm_f64_launch(g, GemmLaunch{al, bl, mode, small, nsplit}, st);
+}
+// plain C = alpha * op(A) op(B) helper
+cudaError_t mm(cudaStream_t st, int al, int bl, const double* A, long lda, const double* B, long ldb, double* C,
+               long ldc, int M, int N, int K, double alpha = 1.0, bool small = true) {
+  GemmArgs g{};
+  g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K; g.alpha = alpha;
+  return gemm(st, al, bl, kStore, small, 1, g);
+}
+
+int ensure_ready(sgp_handle* h) {
+  CU(cudaSetDevice(h->device));
+  if (!h->gemm_ready) {
+    CU(gemm_f64_init());
+    CU(cudaMalloc(&h->d_flags, sizeof(int) * 4));
+    CU(cudaMalloc(&h->d_scal, sizeof(double) * kNumSlots));
+    CU(cudaMalloc(&h->d_out, sizeof(double) * 16));
+    CU(cudaMallocHost(&h->h_out, sizeof(double) * 16));
+    h->gemm_ready = true;
+  }
+  return SGP_OK;
+}
+
+// pick a split-K factor so tiles*nz fills the 148 SMs in (nearly) whole waves
+int pick_split(int tiles, long K) {
+  int best = 1; double best_score = -1.0;
+  for (int nz = 1; nz <= 64; ++nz) {
+    if (nz > 1 && K / nz < 256) break;
+    const double ctas = (double)tiles * nz;
+    const double waves = ctas / 148.0;
+    const double eff = waves / std::ceil(waves);
+    const double score = eff - 0.002 * nz;
+    if (score > best_score) { best_score = score; best = nz; }
+  }
+  return best;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sgp_version(void) { return 100; }
+
+int sgp_create(int device, sgp_handle** out) {
+  if (!out) return SGP_E_ARG;
+  sgp_handle* h = new sgp_handle();
+  h->device = device;
+  h->launches_base = launch_counter();
+  *out = h;
+  return SGP_OK;
+}
+
+int sgp_destroy(sgp_handle* h) {
+  if (!h) return SGP_OK;
+  if (h->gemm_ready) {
+    cudaSetDevice(h->device);
+    h->arena.release(); h->xg.release(); h->ug.release(); h->gcpart.release(); h->s2part.release();
+    h->hx[0].release(); h->hx[1].release(); h->hr.release(); h->small.release();
+    if (h->d_flags) cudaFree(h->d_flags);
+    if (h->d_scal) cudaFree(h->d_scal);
+    if (h->d_out) cudaFree(h->d_out);
+    if (h->h_out) cudaFreeHost(h->h_out);
+    for (int i = 0; i < 2; ++i) {
+      if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]);
+      if (h->ev_used[i]) cudaEventDestroy(h->ev_used[i]);
+    }
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    if (h->compute_stream) cudaStreamDestroy(h->compute_stream);
+  }
+  delete h;
+  return SGP_OK;
+}
+
+const char* sgp_last_error(const sgp_handle* h) { return h ? h->err.c_str() : "null handle"; }
+
+int sgp_set_slab_rows(sgp_handle* h, long rows) {
+  if (!h) return SGP_E_ARG;
+  h->slab_rows = rows > 0 ? rup(rows, 128) : 65536;
+  return SGP_OK;
+}
+
+int sgp_invalidate_cache(sgp_handle* h) {
+  if (!h) return SGP_E_ARG;
+  h->cache_valid = false;
+  return SGP_OK;
+}
+
+long sgp_launch_count(const sgp_handle* h, int reset) {
+  if (!h) return 0;
+  const long now = launch_counter();
+  const long n = now - h->launches_base;
+  if (reset) const_cast<sgp_handle*>(h)->launches_base = now;
+  return n;
+}
+
+int sgp_mask_host(const double* theta, int n_px, uint8_t* mask_host, int* p_out) {
+  if (!theta || n_px <= 0) return SGP_E_ARG;
+  std::vector<uint8_t> mask; std::vector<int> idx; std::vector<double> gx, gy;
+  const int p = compute_mask(theta, n_px, mask, idx, gx, gy);
+  if (mask_host) std::memcpy(mask_host, mask.data(), mask.size());
+  if (p_out) *p_out = p;
+  return SGP_OK;
+}
+
+int sgp_localker(sgp_handle* h, const double* theta, int n_px, double* C, long ldc, double* dC, long dc_stride,
+                 void* stream) {
+  if (!h || !theta || !C) return fail(h, SGP_E_ARG, "sgp_localker: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  std::vector<uint8_t> mask; std::vector<int> idx; std::vector<double> gx, gy;
+  const int p = compute_mask(theta, n_px, mask, idx, gx, gy);
+  if (ldc < p) return fail(h, SGP_E_ARG, "sgp_localker: ldc < p");
+  CU(h->arena.reserve((size_t)(2 * p + 64) * sizeof(double)));
+  double* dgx = (double*)h->arena.p; double* dgy = dgx + p;
+  CU(cudaMemcpyAsync(dgx, gx.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(dgy, gy.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
+  // build_C writes an ldc x ldc square; the caller's buffer is p rows x ldc -> clamp rows via p-sized launch
+  const ThetaDev th = make_theta(theta);
+  if (ldc == p) {
+    build_C(C, ldc, p, dgx, dgy, th, dC, dc_stride, st);
+  } else {
+    return fail(h, SGP_E_ARG, "sgp_localker: ldc must equal p");
+  }
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(st));  // gx/gy host vectors go out of scope
+  return SGP_OK;
+}
+
+int sgp_gemm_f64(sgp_handle* h, int al, int bl, const double* A, long lda, const double* B, long ldb, double* C,
+                 long ldc, int M, int N, int K, double alpha, int accumulate, int small_tile, void* stream) {
+  if (!h || !A || !B || !C) return fail(h, SGP_E_ARG, "sgp_gemm_f64: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  GemmArgs g{};
+  g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K;
+  g.alpha = alpha; g.accumulate = accumulate; g.k_chunk = (int)rup(K, 16);
+  CU(gemm_f64_launch(g, GemmLaunch{al, bl, kStore, small_tile != 0, 1}, (cudaStream_t)stream));
+  return SGP_OK;
+}
+
+int sgp_cholesky(sgp_handle* h, double* A, long ld, int n, int* flags_host, void* stream) {
+  if (!h || !A) return fail(h, SGP_E_ARG, "sgp_cholesky: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
+  CU(cholesky_lower(A, ld, n, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, st));
+  if (flags_host) {
+    CU(cudaMemcpyAsync(flags_host, h->d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return SGP_OK;
+}
+
+int sgp_spd_inverse(sgp_handle* h, const double* A, long lda, int n, double* Ainv, long ldi, double* logdet_host,
+                    int* flags_host, void* stream) {
+  if (!h || !A || !Ainv) return fail(h, SGP_E_ARG, "sgp_spd_inverse: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long ld = rup(n, 16);
+  CU(h->arena.reserve((size_t)(3 * ld * ld + 64 * ld + 1024) * sizeof(double)));
+  Arena ar(h->arena.p, h->arena.bytes);
+  double* L = ar.take<double>(ld * ld);
+  double* X = ar.take<double>(ld * ld);
+  double* R = ar.take<double>(ld * ld);
+  double* tmp = ar.take<double>(64 * ld);
+  CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
+  copy_mat(A, lda, n, n, L, ld, st);
+  CU(cholesky_lower(L, ld, n, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, st));
+  logdet_from_chol(L, ld, n, h->d_scal, kSlotLogdetK, st);
+  CU(tri_inverse_lower(L, ld, n, X, tmp, st));
+  CU(mm(st, 1, 1, X, ld, X, ld, R, ld, n, n, n));
+  symmetrize(R, ld, n, Ainv, ldi, st);
+  CU(cudaGetLastError());
+  if (logdet_host) CU(cudaMemcpyAsync(logdet_host, h->d_scal + kSlotLogdetK, sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (flags_host) CU(cudaMemcpyAsync(flags_host, h->d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return SGP_OK;
+}
+
+int sgp_debug_get(sgp_handle* h, const char* name, double* dst, long capacity, long* rows, long* cols, long* ld) {
+  if (!h || !name) return SGP_E_ARG;
+  auto it = h->dbg.find(name);
+  if (it == h->dbg.end()) return fail(h, SGP_E_ARG, std::string("sgp_debug_get: unknown name ") + name);
+  const DebugEntry& e = it->second;
+  if (rows) *rows = e.rows;
+  if (cols) *cols = e.cols;
+  if (ld) *ld = e.ld;
+  if (dst) {
+    const long need = e.rows * e.ld;
+    if (capacity < need) return fail(h, SGP_E_ARG, "sgp_debug_get: capacity too small");
+    CU(cudaMemcpy(dst, e.ptr, sizeof(double) * need, cudaMemcpyDeviceToDevice));
+  }
+  return SGP_OK;
+}
+
+}  // extern "C"
+
+// =====================================================================================================
+// the fused closure
+// =====================================================================================================
+namespace {
+
+struct ClosureIn {
+  const double* X; long ldx; const double* r; long N;        // device (or per-slab device staging when streaming)
+  const double* U; long ldu; int m; int n_px;
+  const double* theta; const double* B; long ldb; int q; const double* m_b; const double* V; long ldv;
+  double logA, lambda0; const double* logdetV_host;
+  double* lam_m; double* lam_var; double* f;
+  // host streaming (X_host != nullptr): X / r above are ignored
+  const double* X_host = nullptr; const double* r_host = nullptr;
+};
+
+int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream_t st) {
+  int rc = ensure_ready(h); if (rc) return rc;
+  const bool streaming = in.X_host != nullptr;
+  const long N = in.N; const int m = in.m, q = in.q, n = in.n_px; const long P = (long)n * n;
+  if (N <= 0 || m <= 0 || q <= 0 || q > m) return fail(h, SGP_E_ARG, "sgp_elbo_grad: bad sizes");
+  if (m > kBwdMaxCols) return fail(h, SGP_E_UNSUPPORTED, "sgp_elbo_grad: m > 2048 not supported");
+  if (N == m) return fail(h, SGP_E_UNSUPPORTED, "sgp_elbo_grad: ntilde == nt (a = B) path not implemented");
+
+  // ---- host: mask / coordinates (U:880-887) ------------------------------------------------------
+  std::vector<uint8_t> mask; std::vector<int> idx; std::vector<double> gx, gy;
+  const int p = compute_mask(in.theta, n, mask, idx, gx, gy);
+  if (p == 0) return fail(h, SGP_E_ARG, "sgp_elbo_grad: empty receptive-field mask");
+  const ThetaDev th = make_theta(in.theta);
+  const double A = std::exp(in.logA);
+  const long ldp = rup(p, 16), ldm = rup(m, 16), ldq = rup(q, 16);
+  const long slab = std::min<long>(h->slab_rows, rup(N, 128));
+  const long ldpartN = rup(slab, 16), ldpartU = ldm;
+  const int ntp = (int)((p + 127) / 128), ntm = (int)((m + 127) / 128);
+  const int ntp_s = (int)((p + 63) / 64);
+  const bool full_mask = (p == P);
+
+  // ---- gathered / aligned copies of the images (cached across calls while the mask is unchanged) --
+  const bool direct_X = !streaming && full_mask && (in.ldx % 2 == 0) && ((uintptr_t)in.X % 16 == 0);
+  const bool direct_U = full_mask && (in.ldu % 2 == 0) && ((uintptr_t)in.U % 16 == 0);
+  bool regather = !h->cache_valid || h->cache_mask != mask || h->cache_X != in.X || h->cache_N != N ||
+                  h->cache_ldx != in.ldx || h->cache_U != in.U || h->cache_m != m || h->cache_ldu != in.ldu;
+  if (streaming) regather = true;
+  const double* Xg = in.X; long ldxg = in.ldx;
+  const double* Ug = in.U; long ldug = in.ldu;
+  if (!direct_X && !streaming) { CU(h->xg.reserve((size_t)N * ldp * sizeof(double))); Xg = (double*)h->xg.p; ldxg = ldp; }
+  if (!direct_U) { CU(h->ug.reserve((size_t)m * ldp * sizeof(double))); Ug = (double*)h->ug.p; ldug = ldp; }
+
+  // ---- arena ---------------------------------------------------------------------------------------
+  const int nblk_bwd = acos_backward_blocks(slab), nblk_bwdU = acos_backward_blocks(m);
+  const int nblk_mom = moments_rows_blocks(slab);
+  size_t need = 0;
+  auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
+  acc(p); acc(p); acc((size_t)(p + 1) / 2 + 8);                       // gx, gy, idx
+  acc((size_t)p * ldp);                                               // C
+  acc((size_t)m * ldq); acc((size_t)q * ldq);                         // Bw, Vw
+  acc((size_t)m * ldp); acc((size_t)ntp_s * ldpartU); acc(m); acc(m); // ZU/YU, partU, tU, X2
+  for (int i = 0; i < 6; ++i) acc((size_t)m * ldm);                   // Kraw, Kt, cosU, Mfull, Sig2, GKt
+  for (int i = 0; i < 3; ++i) acc((size_t)m * ldq);                   // tmp_mq x3
+  for (int i = 0; i < 14; ++i) acc((size_t)q * ldq);                  // q x q scratch
+  acc(64 * ldq);                                                      // tri-inverse tmp
+  for (int i = 0; i < 12; ++i) acc(ldm);                              // small vectors
+  acc((size_t)slab * ldp);                                            // Z / Y
+  for (int i = 0; i < 3; ++i) acc((size_t)slab * ldm);                // K, cos, T/R
+  for (int i = 0; i < 6; ++i) acc(slab);                              // s, X1, u, v, w (+1)
+  for (int i = 0; i < 3; ++i) acc(N);                                 // lam_m, lam_var, f (when not supplied)
+  acc((size_t)std::max(ntp, ntm) * ldpartN * 3);                      // partN, pm1, pm2
+  acc((size_t)nblk_mom * 4); acc((size_t)nblk_bwd * ldm * 2); acc(nblk_bwd);
+  acc((size_t)nblk_bwdU * ldm); acc(nblk_bwdU);
+  acc((size_t)p * ldp);                                               // GCU
+  acc((size_t)p * 5);                                                 // gpart
+  if (streaming) { acc((size_t)slab * ldp); }                         // gathered slab when streaming from host
+  need += 4096;
+  CU(h->arena.reserve(need));
+  Arena ar(h->arena.p, h->arena.bytes);
+
+  double* d_gx = ar.take<double>(p); double* d_gy = ar.take<double>(p);
+  int* d_idx = (int*)ar.take<double>((size_t)(p + 1) / 2 + 8);
+  double* C = ar.take<double>((size_t)p * ldp);
+  double* Bw = ar.take<double>((size_t)m * ldq); double* Vw = ar.take<double>((size_t)q * ldq);
+  double* ZU = ar.take<double>((size_t)m * ldp);
+  double* partU = ar.take<double>((size_t)ntp_s * ldpartU);
+  double* tU = ar.take<double>(m); double* X2 = ar.take<double>(m);
+  double* Kraw = ar.take<double>((size_t)m * ldm); double* Kt = ar.take<double>((size_t)m * ldm);
+  double* cosU = ar.take<double>((size_t)m * ldm); double* Mfull = ar.take<double>((size_t)m * ldm);
+  double* Sig2 = ar.take<double>((size_t)m * ldm); double* GKt = ar.take<double>((size_t)m * ldm);
+  double* tmq1 = ar.take<double>((size_t)m * ldq); double* tmq2 = ar.take<double>((size_t)m * ldq);
+  double* tmq3 = ar.take<double>((size_t)m * ldq);
+  double* qq[14]; for (int i = 0; i < 14; ++i) qq[i] = ar.take<double>((size_t)q * ldq);
+  double* tri_tmp = ar.take<double>(64 * ldq);
+  double* vecs[12]; for (int i = 0; i < 12; ++i) vecs[i] = ar.take<double>(ldm);
+  double* Zs = ar.take<double>((size_t)slab * ldp);
+  double* Ks = ar.take<double>((size_t)slab * ldm); double* cos_s = ar.take<double>((size_t)slab * ldm);
+  double* Ts = ar.take<double>((size_t)slab * ldm);
+  double* s_s = ar.take<double>(slab); double* X1 = ar.take<double>(slab); double* u_s = ar.take<double>(slab);
+  double* v_s = ar.take<double>(slab); double* w_s = ar.take<double>(slab); (void)ar.take<double>(slab);
+  double* lam_m = in.lam_m ? in.lam_m : ar.take<double>(N);
+  double* lam_var = in.lam_var ? in.lam_var : ar.take<double>(N);
+  double* fvec = in.f ? in.f : ar.take<double>(N);
+  const int ntmax = std::max(ntp, ntm);
+  double* partN = ar.take<double>((size_t)ntmax * ldpartN); double* pm1 = ar.take<double>((size_t)ntmax * ldpartN);
+  double* pm2 = ar.take<double>((size_t)ntmax * ldpartN);
+  double* blockpart = ar.take<double>((size_t)nblk_mom * 4);
+  double* colk = ar.take<double>((size_t)nblk_bwd * ldm); double* coly = ar.take<double>((size_t)nblk_bwd * ldm);
+  double* sumpartR = ar.take<double>(nblk_bwd);
+  double* colkU = ar.take<double>((size_t)nblk_bwdU * ldm); double* sumpartU = ar.take<double>(nblk_bwdU);
+  double* GCU = ar.take<double>((size_t)p * ldp);
+  double* gpart = ar.take<double>((size_t)p * 5);
+  double* Xslab_stream = streaming ? ar.take<double>((size_t)slab * ldp) : nullptr;
+
+  double* Ktb_raw = qq[0]; double* Ktb = qq[1]; double* Lk = qq[2]; double* Linv = qq[3]; double* Kinv_raw = qq[4];
+  double* Kinv = qq[5]; double* KV = qq[6]; double* KVK = qq[7]; double* Mg = qq[8]; double* Lv = qq[9];
+  double* S2b = qq[10]; double* W2 = qq[11]; double* inner = qq[12]; double* Sq = qq[13];
+  double* GKtb = Ktb_raw;  // reused after the forward pass
+  double* bq = vecs[0]; double* bb = vecs[1]; double* kappa = vecs[2]; double* yv = vecs[3]; double* beta = vecs[4];
+  double* y_b = vecs[5]; double* wr = vecs[6]; double* kappaU = vecs[7]; double* wc = vecs[8]; double* wU = vecs[9];
+
+  // ---- uploads -------------------------------------------------------------------------------------
+  CU(cudaMemcpyAsync(d_gx, gx.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_gy, gy.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_idx, idx.data(), sizeof(int) * p, cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
+  CU(cudaMemsetAsync(h->d_scal, 0, sizeof(double) * kNumSlots, st));
+  if (regather) {
+    if (!direct_X && !streaming) gather_cols(in.X, in.ldx, N, d_idx, p, (double*)Xg, ldp, st);
+    if (!direct_U) gather_cols(in.U, in.ldu, m, d_idx, p, (double*)Ug, ldp, st);
+    h->cache_mask = mask; h->cache_X = in.X; h->cache_N = N; h->cache_ldx = in.ldx;
+    h->cache_U = in.U; h->cache_m = m; h->cache_ldu = in.ldu; h->cache_valid = !streaming;
+  }
+  copy_mat(in.B, in.ldb, m, q, Bw, ldq, st);
+  copy_mat(in.V, in.ldv, q, q, Vw, ldq, st);
+
+  // ---- a1: C(theta) ---------------------------------------------------------------------------------
+  build_C(C, ldp, p, d_gx, d_gy, th, nullptr, 0, st);
+
+  const bool smallU = true;  // inducing-point GEMMs are small: 64x64 tiles
+  // ---- inducing-point path: K_tilde, K_tilde_b, its inverse, and the moment matrices ------------------
+  {
+    GemmArgs g{};  // ZU = Ug C ; partial row dots for t_j = u_j^T C u_j
+    g.A = Ug; g.lda = ldug; g.B = C; g.ldb = ldp; g.C = ZU; g.ldc = ldp; g.M = m; g.N = p; g.K = p;
+    g.aux = Ug; g.ldaux = ldug; g.part1 = partU; g.ldpart = ldpartU;
+    CU(gemm(st, 0, 1, kRowdot, smallU, 1, g));
+    norms_finalize(partU, ldpartU, ntp_s, m, th.s02, tU, X2, st);
+    GemmArgs a{};  // K_tilde (raw) = acos-kernel(ZU Ug^T)
+    a.A = ZU; a.lda = ldp; a.B = Ug; a.ldb = ldug; a.C = Kraw; a.ldc = ldm; a.M = m; a.N = m; a.K = p;
+    a.rowvec = X2; a.colvec = X2; a.C2 = cosU; a.s02 = th.s02;
+    CU(gemm(st, 0, 0, kAcos, smallU, 1, a));
+    symmetrize(Kraw, ldm, m, Kt, ldm, st);                                              // U:1024-1025
+    CU(mm(st, 0, 1, Kt, ldm, Bw, ldq, tmq1, ldq, m, q, m));                              // Kt B
+    CU(mm(st, 1, 1, Bw, ldq, tmq1, ldq, Ktb_raw, ldq, q, q, m));                         // B^T Kt B   U:2047
+    symmetrize(Ktb_raw, ldq, q, Ktb, ldq, st);                                          // U:2048
+    copy_mat(Ktb, ldq, q, q, Lk, ldq, st);
+    CU(cholesky_lower(Lk, ldq, q, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, st));
+    logdet_from_chol(Lk, ldq, q, h->d_scal, kSlotLogdetK, st);
+    CU(tri_inverse_lower(Lk, ldq, q, Linv, tri_tmp, st));
+    CU(mm(st, 1, 1, Linv, ldq, Linv, ldq, Kinv_raw, ldq, q, q, q));                      // K_tilde_b^-1  (U:2067)
+    symmetrize(Kinv_raw, ldq, q, Kinv, ldq, st);
+    gemv(Kinv, ldq, q, q, 0, in.m_b, bq, st);                                           // b = Kinv m_b
+    gemv(Bw, ldq, m, q, 0, bq, bb, st);                                                 // bb = B b
+    CU(mm(st, 0, 1, Kinv, ldq, Vw, ldq, KV, ldq, q, q, q));                              // Kinv V
+    CU(mm(st, 0, 1, KV, ldq, Kinv, ldq, KVK, ldq, q, q, q));                             // Kinv V Kinv
+    lincomb(Mg, ldq, q, q, 2.0, KVK, ldq, -2.0, Kinv, ldq, 0.0, st);                    // Mg = 2 KVK - 2 Kinv
+    CU(mm(st, 0, 1, Bw, ldq, Mg, ldq, tmq2, ldq, m, q, q));                              // B Mg
+    CU(mm(st, 0, 0, tmq2, ldq, Bw, ldq, Mfull, ldm, m, m, q));                           // Mfull = B Mg B^T
+    if (!in.logdetV_host) {
+      copy_mat(Vw, ldq, q, q, Lv, ldq, st);
+      CU(cholesky_lower(Lv, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, st));
+      logdet_from_chol(Lv, ldq, q, h->d_scal, kSlotLogdetV, st);
+    }
+    kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, st);
+  }
+
+  // ---- split-K plans for the two reductions over images ----------------------------------------------
+  const int tilesGC = ntp * ntp, tilesS2 = ntm * ntm;
+  const int nzGC = pick_split(tilesGC, slab), nzS2 = pick_split(tilesS2, slab);
+  const long zGC = (long)p * ldp, zS2 = (long)m * ldm;
+  CU(h->gcpart.reserve((size_t)nzGC * zGC * sizeof(double)));
+  CU(h->s2part.reserve((size_t)nzS2 * zS2 * sizeof(double)));
+  double* GCpart = (double*)h->gcpart.p; double* S2part = (double*)h->s2part.p;
+
+  // ---- host streaming resources ------------------------------------------------------------------------
+  if (streaming) {
+    if (!h->copy_stream) {
+      CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+      for (int i = 0; i < 2; ++i) {
+        CU(cudaEventCreateWithFlags(&h->ev_copied[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&h->ev_used[i], cudaEventDisableTiming));
+      }
+    }
+    for (int i = 0; i < 2; ++i) CU(h->hx[i].reserve((size_t)slab * P * sizeof(double)));
+    CU(h->hr.reserve((size_t)N * sizeof(double)));
+    CU(cudaMemcpyAsync(h->hr.p, in.r_host, sizeof(double) * N, cudaMemcpyHostToDevice, st));
+  }
+  const double* rdev = streaming ? (const double*)h->hr.p : in.r;
+
+  // ---- image pass, slab by slab ---------------------------------------------------------------------------
+  int slab_i = 0;
+  auto issue_copy = [&](int si) -> cudaError_t {  // H2D of slab si into staging buffer si%2
+    const long i0 = (long)si * slab;
+    const long ns = std::min(slab, N - i0);
+    const int bsel = si & 1;
+    cudaError_t e;
+    if (si >= 2 && (e = cudaStreamWaitEvent(h->copy_stream, h->ev_used[bsel], 0)) != cudaSuccess) return e;
+    if ((e = cudaMemcpy2DAsync(h->hx[bsel].p, P * sizeof(double), in.X_host + i0 * in.ldx, in.ldx * sizeof(double),
+                               P * sizeof(double), ns, cudaMemcpyHostToDevice, h->copy_stream)) != cudaSuccess)
+      return e;
+    return cudaEventRecord(h->ev_copied[bsel], h->copy_stream);
+  };
+  const int nslabs = (int)((N + slab - 1) / slab);
+  if (streaming) CU(issue_copy(0));
+
+  for (long i0 = 0; i0 < N; i0 += slab, ++slab_i) {
+    const long ns = std::min(slab, N - i0);
+    const int acc_flag = slab_i > 0 ? 1 : 0;
+    const double* Xs; long ldxs;
+    if (streaming) {
+      if (slab_i + 1 < nslabs) CU(issue_copy(slab_i + 1));
+      const int bsel = slab_i & 1;
+      CU(cudaStreamWaitEvent(st, h->ev_copied[bsel], 0));
+      if (full_mask && P % 2 == 0) { Xs = (const double*)h->hx[bsel].p; ldxs = P; }
+      else { gather_cols((const double*)h->hx[bsel].p, P, ns, d_idx, p, Xslab_stream, ldp, st); Xs = Xslab_stream; ldxs = ldp; }
+    } else {
+      Xs = Xg + i0 * ldxg; ldxs = ldxg;
+    }
+    // G1: Z = X C, partial s_i = x_i^T C x_i                                  (U:978, U:1029)
+    GemmArgs g1{};
+    g1.A = Xs; g1.lda = ldxs; g1.B = C; g1.ldb = ldp; g1.C = Zs; g1.ldc = ldp; g1.M = (int)ns; g1.N = p; g1.K = p;
+    g1.aux = Xs; g1.ldaux = ldxs; g1.part1 = partN; g1.ldpart = ldpartN;
+    CU(gemm(st, 0, 1, kRowdot, false, 1, g1));
+    norms_finalize(partN, ldpartN, ntp, ns, th.s02, s_s, X1, st);
+    // G2: K = acos-kernel(Z Ug^T)                                             (U:982-990)
+    GemmArgs g2{};
+    g2.A = Zs; g2.lda = ldp; g2.B = Ug; g2.ldb = ldug; g2.C = Ks; g2.ldc = ldm; g2.M = (int)ns; g2.N = m; g2.K = p;
+    g2.rowvec = X1; g2.colvec = X2; g2.C2 = cos_s; g2.s02 = th.s02;
+    CU(gemm(st, 0, 0, kAcos, false, 1, g2));
+    // G3: T = K Mfull^T ; partial lam_var / lam_m row sums                    (U:1090-1101)
+    GemmArgs g3{};
+    g3.A = Ks; g3.lda = ldm; g3.B = Mfull; g3.ldb = ldm; g3.C = Ts; g3.ldc = ldm; g3.M = (int)ns; g3.N = m; g3.K = m;
+    g3.aux = Ks; g3.ldaux = ldm; g3.colvec = bb; g3.part1 = pm1; g3.part2 = pm2; g3.ldpart = ldpartN;
+    CU(gemm(st, 0, 0, kMoments, false, 1, g3));
+    moments_rows(s_s, pm1, pm2, ldpartN, ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
+                 v_s, blockpart, st);
+    const int nbm = moments_rows_blocks(ns);
+    sum_to_slot(blockpart + 0, nbm, 4, 1.0, h->d_scal, kSlotRLam, acc_flag, st);
+    sum_to_slot(blockpart + 1, nbm, 4, 1.0, h->d_scal, kSlotSumF, acc_flag, st);
+    sum_to_slot(blockpart + 2, nbm, 4, 1.0, h->d_scal, kSlotSumR, acc_flag, st);
+    sum_to_slot(blockpart + 3, nbm, 4, 1.0, h->d_scal, kSlotNaN, acc_flag, st);
+    // adjoint of the arc-cosine map: R (in place over T), row weights w, column sums kappa / y
+    acos_backward(0, Ts, cos_s, Ks, ldm, ns, m, u_s, v_s, bb, X1, X2, w_s, colk, coly, ldm, sumpartR, st);
+    const int nbb = acos_backward_blocks(ns);
+    col_reduce(colk, nbb, m, ldm, kappa, acc_flag, st);
+    col_reduce(coly, nbb, m, ldm, yv, acc_flag, st);
+    sum_to_slot(sumpartR, nbb, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+    sum_to_slot(w_s, ns, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+    // G4: Y = R Ug + diag(w) X   (into the Z buffer)
+    GemmArgs g4{};
+    g4.A = Ts; g4.lda = ldm; g4.B = Ug; g4.ldb = ldug; g4.C = Zs; g4.ldc = ldp; g4.M = (int)ns; g4.N = p; g4.K = m;
+    g4.rowvec = w_s; g4.aux = Xs; g4.ldaux = ldxs;
+    CU(gemm(st, 0, 1, kAxpyRow, false, 1, g4));
+    // G5: GC += X^T Y   (split-K over the images of the slab)
+    GemmArgs g5{};
+    g5.A = Xs; g5.lda = ldxs; g5.B = Zs; g5.ldb = ldp; g5.C = GCpart; g5.ldc = ldp; g5.M = p; g5.N = p; g5.K = (int)ns;
+    g5.k_chunk = (int)rup((ns + nzGC - 1) / nzGC, 16); g5.zstride = zGC; g5.accumulate = acc_flag;
+    CU(gemm(st, 1, 1, kStore, false, nzGC, g5));
+    // G6: Sig2 += K^T diag(v) K
+    GemmArgs g6{};
+    g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
+    g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
+    CU(gemm(st, 1, 1, kStore, false, nzS2, g6));
+    if (streaming) CU(cudaEventRecord(h->ev_used[slab_i & 1], st));
+  }
+
+  // ---- adjoint of K_tilde_b (q x q algebra) ---------------------------------------------------------------
+  slice_reduce(S2part, nzS2, zS2, zS2, Sig2, 0, st);
+  col_weights(kappa, nullptr, nullptr, X2, m, beta, st);                                 // beta_j = kappa_j / (2 X2_j)
+  sum_to_slot(beta, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+  gemv(Bw, ldq, m, q, 1, yv, y_b, st);                                                  // y_b = B^T y
+  CU(mm(st, 0, 1, Sig2, ldm, Bw, ldq, tmq1, ldq, m, q, m));
+  CU(mm(st, 1, 1, Bw, ldq, tmq1, ldq, S2b, ldq, q, q, m));                               // B^T Sig2 B
+  CU(mm(st, 0, 0, Kinv, ldq, Vw, ldq, KV, ldq, q, q, q));                                // Kinv V^T
+  lincomb(W2, ldq, q, q, 2.0, KV, ldq, 0.0, nullptr, 0, -1.0, st);                      // 2 Kinv V^T - I
+  CU(mm(st, 0, 1, S2b, ldq, W2, ldq, inner, ldq, q, q, q));
+  rank1_add(inner, ldq, q, q, 1.0, y_b, in.m_b, st);                                    // + y_b m_b^T
+  CU(mm(st, 0, 1, Kinv, ldq, inner, ldq, Sq, ldq, q, q, q));                             // S = Kinv (...)
+  CU(mm(st, 0, 1, Sq, ldq, Kinv, ldq, GKtb, ldq, q, q, q, -1.0));                        // -S Kinv
+  gkt_assemble(GKtb, ldq, q, Kinv, KVK, bq, st);                                        // KL part (U:1333)
+  CU(mm(st, 0, 1, Bw, ldq, GKtb, ldq, tmq3, ldq, m, q, q));
+  CU(mm(st, 0, 0, tmq3, ldq, Bw, ldq, GKt, ldm, m, m, q));                               // GKt = B GKtb B^T
+
+  // ---- inducing-point path, backward -----------------------------------------------------------------------
+  acos_backward(1, GKt, cosU, nullptr, ldm, m, m, nullptr, nullptr, nullptr, X2, X2, wr, colkU, nullptr, ldm,
+                sumpartU, st);
+  col_reduce(colkU, nblk_bwdU, m, ldm, kappaU, 0, st);
+  col_weights(kappaU, nullptr, nullptr, X2, m, wc, st);
+  sum_to_slot(sumpartU, nblk_bwdU, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+  sum_to_slot(wr, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+  sum_to_slot(wc, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+  col_weights(nullptr, nullptr, wr, X2, m, wU, st);                                      // wU = wr
+  lincomb(wU, ldm, 1, m, 1.0, wU, ldm, 1.0, wc, ldm, 0.0, st);                          // + wc
+  lincomb(wU, ldm, 1, m, 1.0, wU, ldm, 1.0, beta, ldm, 0.0, st);                        // + beta
+  {
+    GemmArgs g{};  // YU = RU Ug + diag(wU) Ug
+    g.A = GKt; g.lda = ldm; g.B = Ug; g.ldb = ldug; g.C = ZU; g.ldc = ldp; g.M = m; g.N = p; g.K = m;
+    g.rowvec = wU; g.aux = Ug; g.ldaux = ldug;
+    CU(gemm(st, 0, 1, kAxpyRow, smallU, 1, g));
+    CU(mm(st, 1, 1, Ug, ldug, ZU, ldp, GCU, ldp, p, p, m));                              // Ug^T YU
+  }
+
+  // ---- <dC_k, GC> and result assembly -----------------------------------------------------------------------
+  contract_dC(GCpart, nzGC, zGC, GCU, C, ldp, p, d_gx, d_gy, th, gpart, st);
+  for (int k = 0; k < 5; ++k) sum_to_slot(gpart + k, p, 5, 1.0, h->d_scal, kSlotG + k, 0, st);
+  finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p, in.logdetV_host ? *in.logdetV_host : 0.0,
+           in.logdetV_host ? 1 : 0, h->d_out, st);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(double) * 16, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (out_host) std::memcpy(out_host, h->h_out, sizeof(double) * 16);
+
+  h->dbg.clear();
+  h->dbg["C"] = {C, p, p, ldp};   h->dbg["Kt"] = {Kt, m, m, ldm};     h->dbg["Ktb"] = {Ktb, q, q, ldq};
+  h->dbg["Kinv"] = {Kinv, q, q, ldq}; h->dbg["Mfull"] = {Mfull, m, m, ldm}; h->dbg["GKt"] = {GKt, m, m, ldm};
+  h->dbg["GCU"] = {GCU, p, p, ldp};   h->dbg["Sig2"] = {Sig2, m, m, ldm};   h->dbg["bb"] = {bb, 1, m, ldm};
+  h->dbg["y"] = {yv, 1, m, ldm};      h->dbg["beta"] = {beta, 1, m, ldm};   h->dbg["X2"] = {X2, 1, m, ldm};
+  h->dbg["GCpart"] = {GCpart, (long)nzGC * p, p, ldp}; h->dbg["scal"] = {h->d_scal, 1, kNumSlots, kNumSlots};
+  h->dbg["K_last"] = {Ks, std::min(slab, N - (long)(nslabs - 1) * slab), m, ldm};
+  h->dbg["Y_last"] = {Zs, std::min(slab, N - (long)(nslabs - 1) * slab), p, ldp};
+  h->dbg["R_last"] = {Ts, std::min(slab, N - (long)(nslabs - 1) * slab), m, ldm};
+  h->dbg["w_last"] = {w_s, 1, std::min(slab, N - (long)(nslabs - 1) * slab), slab};
+  h->dbg["KtRaw"] = {Kraw, m, m, ldm}; h->dbg["Linv"] = {Linv, q, q, ldq}; h->dbg["GKtb"] = {GKtb, q, q, ldq};
+  return SGP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sgp_elbo_grad(sgp_handle* h, const double* X, long ldx, const double* r, long N, const double* xtilde, long ldu,
+                  int m, int n_px, const double* theta, const double* lo, const double* hi, const double* B, long ldb,
+                  int q, const double* m_b, const double* V_b, long ldv, double logA, double lambda0,
+                  const double* logdetV_host, double* lam_m, double* lam_var, double* f, double* out_host,
+                  void* stream) {
+  if (!h || !X || !r || !xtilde || !theta || !B || !m_b || !V_b)
+    return fail(h, SGP_E_ARG, "sgp_elbo_grad: null argument");
+  if (lo && hi)
+    for (int k = 0; k < 6; ++k)
+      if (!(lo[k] <= theta[k] && theta[k] <= hi[k]))
+        return fail(h, SGP_E_BOUNDS, "sgp_elbo_grad: theta[" + std::to_string(k) + "] outside its limits");
+  ClosureIn in{};
+  in.X = X; in.ldx = ldx; in.r = r; in.N = N; in.U = xtilde; in.ldu = ldu; in.m = m; in.n_px = n_px;
+  in.theta = theta; in.B = B; in.ldb = ldb; in.q = q; in.m_b = m_b; in.V = V_b; in.ldv = ldv;
+  in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = logdetV_host;
+  in.lam_m = lam_m; in.lam_var = lam_var; in.f = f;
+  return run_closure(h, in, out_host, (cudaStream_t)stream);
+}
+
+int sgp_elbo_grad_host(sgp_handle* h, const double* X_host, long ldx, const double* r_host, long N,
+                       const double* xtilde_host, long ldu, int m, int n_px, const double* theta,
+                       const double* B_host, long ldb, int q, const double* m_b_host, const double* V_b_host,
+                       long ldv, double logA, double lambda0, double* out_host) {
+  if (!h || !X_host || !r_host || !xtilde_host || !theta || !B_host || !m_b_host || !V_b_host)
+    return fail(h, SGP_E_ARG, "sgp_elbo_grad_host: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  if (!h->compute_stream) CU(cudaStreamCreateWithFlags(&h->compute_stream, cudaStreamNonBlocking));
+  cudaStream_t st = h->compute_stream;
+  const long P = (long)n_px * n_px;
+  // small operands: plain synchronous uploads into a dedicated buffer (a few MB)
+  DevBuf& small = h->small;
+  const size_t nU = (size_t)m * P, nB = (size_t)m * q, nV = (size_t)q * q;
+  CU(small.reserve((nU + nB + nV + q + 64) * sizeof(double)));
+  double* dU = (double*)small.p; double* dB = dU + ((nU + 1) & ~size_t(1)); double* dV = dB + ((nB + 1) & ~size_t(1));
+  double* dm = dV + ((nV + 1) & ~size_t(1));
+  CU(cudaMemcpy2DAsync(dU, P * sizeof(double), xtilde_host, ldu * sizeof(double), P * sizeof(double), m,
+                       cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpy2DAsync(dB, q * sizeof(double), B_host, ldb * sizeof(double), q * sizeof(double), m,
+                       cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpy2DAsync(dV, q * sizeof(double), V_b_host, ldv * sizeof(double), q * sizeof(double), q,
+                       cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(dm, m_b_host, q * sizeof(double), cudaMemcpyHostToDevice, st));
+  ClosureIn in{};
+  in.X = nullptr; in.ldx = ldx; in.r = nullptr; in.N = N; in.U = dU; in.ldu = P; in.m = m; in.n_px = n_px;
+  in.theta = theta; in.B = dB; in.ldb = q; in.q = q; in.m_b = dm; in.V = dV; in.ldv = q;
+  in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = nullptr;
+  in.X_host = X_host; in.r_host = r_host;
+  return run_closure(h, in, out_host, st);
+}
+
+}  // extern "C"
+
+// =====================================================================================================
+// function-level entry points of the reference call surface (a2, a3, a5, a6-a8, a10)
+// =====================================================================================================
+namespace {
+
+bool aligned2(const void* p, long ld) { return ((uintptr_t)p % 16 == 0) && (ld % 2 == 0); }
+
+}  // namespace
+
+extern "C" {
+
+int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double* x2, long n2, long ld2, int p,
+                const double* C, long ldc, double sigma_0, double* K, long ldk, int symm, void* stream) {
+  if (!h || !x1 || !x2 || !C || !K) return fail(h, SGP_E_ARG, "sgp_acosker: null argument");
+  if (symm && n1 != n2) return fail(h, SGP_E_ARG, "sgp_acosker: symmetrize needs n1 == n2");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long ldp = rup(p, 16), ldn2 = rup(n2, 16);
+  const long slab = std::min<long>(h->slab_rows, rup(n1, 128));
+  const int ntp_s = (p + 63) / 64, ntp = (p + 127) / 128;
+  const long ldpart = rup(std::max<long>(slab, n2), 16);
+  const double s02 = sigma_0 * sigma_0;
+  size_t need = 0;
+  auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
+  acc((size_t)p * ldp); acc((size_t)n2 * ldp); acc((size_t)n2 * ldp); acc((size_t)slab * ldp); acc((size_t)slab * ldp);
+  acc((size_t)ntp_s * ldpart); acc(n2); acc(n2); acc(slab); acc(slab); acc((size_t)slab * ldn2); acc((size_t)slab * ldn2);
+  acc(symm ? (size_t)n1 * ldn2 : 1);
+  need += 4096;
+  CU(h->arena.reserve(need));
+  Arena ar(h->arena.p, h->arena.bytes);
+  double* Cw = ar.take<double>((size_t)p * ldp);
+  double* x2w = ar.take<double>((size_t)n2 * ldp);
+  double* Z2 = ar.take<double>((size_t)n2 * ldp);
+  double* x1w = ar.take<double>((size_t)slab * ldp);
+  double* Z1 = ar.take<double>((size_t)slab * ldp);
+  double* part = ar.take<double>((size_t)ntp_s * ldpart);
+  double* t2 = ar.take<double>(n2); double* X2 = ar.take<double>(n2);
+  double* s1 = ar.take<double>(slab); double* X1 = ar.take<double>(slab);
+  double* Kw = ar.take<double>((size_t)slab * ldn2); double* cosw = ar.take<double>((size_t)slab * ldn2);
+  double* Kfull = symm ? ar.take<double>((size_t)n1 * ldn2) : nullptr;
+
+  const double* Cc = C; long ldcc = ldc;
+  if (!aligned2(C, ldc)) { copy_mat(C, ldc, p, p, Cw, ldp, st); Cc = Cw; ldcc = ldp; }
+  const double* x2c = x2; long ld2c = ld2;
+  if (!aligned2(x2, ld2)) { copy_mat(x2, ld2, (int)n2, p, x2w, ldp, st); x2c = x2w; ld2c = ldp; }
+  {
+    GemmArgs g{};
+    g.A = x2c; g.lda = ld2c; g.B = Cc; g.ldb = ldcc; g.C = Z2; g.ldc = ldp; g.M = (int)n2; g.N = p; g.K = p;
+    g.aux = x2c; g.ldaux = ld2c; g.part1 = part; g.ldpart = ldpart;
+    CU(gemm(st, 0, 1, kRowdot, true, 1, g));
+    norms_finalize(part, ldpart, ntp_s, n2, s02, t2, X2, st);
+  }
+  for (long i0 = 0; i0 < n1; i0 += slab) {
+    const long ns = std::min(slab, n1 - i0);
+    const double* xs = x1 + i0 * ld1; long lds = ld1;
+    if (!aligned2(xs, ld1)) { copy_mat(xs, ld1, (int)ns, p, x1w, ldp, st); xs = x1w; lds = ldp; }
+    GemmArgs g{};
+    g.A = xs; g.lda = lds; g.B = Cc; g.ldb = ldcc; g.C = Z1; g.ldc = ldp; g.M = (int)ns; g.N = p; g.K = p;
+    g.aux = xs; g.ldaux = lds; g.part1 = part; g.ldpart = ldpart;
+    CU(gemm(st, 0, 1, kRowdot, false, 1, g));
+    norms_finalize(part, ldpart, ntp, ns, s02, s1, X1, st);
+    GemmArgs a{};  // K slab into scratch (ld = ldn2, shared with the cosine scratch), then out
+    a.A = Z1; a.lda = ldp; a.B = x2c; a.ldb = ld2c; a.C = Kw; a.ldc = ldn2; a.M = (int)ns; a.N = (int)n2; a.K = p;
+    a.rowvec = X1; a.colvec = X2; a.C2 = cosw; a.s02 = s02;
+    CU(gemm(st, 0, 0, kAcos, false, 1, a));
+    if (symm) copy_mat(Kw, ldn2, (int)ns, (int)n2, Kfull + i0 * ldn2, ldn2, st);
+    else copy_mat(Kw, ldn2, (int)ns, (int)n2, K + i0 * ldk, ldk, st);
+  }
+  if (symm) symmetrize(Kfull, ldn2, (int)n1, K, ldk, st);   // U:1024-1025
+  CU(cudaGetLastError());
+  return SGP_OK;
+}
+
+int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, const double* C, long ldc,
+                     double sigma_0, double* Kvec, void* stream) {
+  if (!h || !x1 || !C || !Kvec) return fail(h, SGP_E_ARG, "sgp_acosker_diag: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long ldp = rup(p, 16);
+  const long slab = std::min<long>(h->slab_rows, rup(n1, 128));
+  const int ntp = (p + 127) / 128;
+  const long ldpart = rup(slab, 16);
+  size_t need = 0;
+  auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
+  acc((size_t)p * ldp); acc((size_t)slab * ldp); acc((size_t)slab * ldp); acc((size_t)ntp * ldpart); acc(slab);
+  need += 4096;
+  CU(h->arena.reserve(need));
+  Arena ar(h->arena.p, h->arena.bytes);
+  double* Cw = ar.take<double>((size_t)p * ldp);
+  double* x1w = ar.take<double>((size_t)slab * ldp);
+  double* Z1 = ar.take<double>((size_t)slab * ldp);
+  double* part = ar.take<double>((size_t)ntp * ldpart);
+  double* nrm = ar.take<double>(slab);
+  const double* Cc = C; long ldcc = ldc;
+  if (!aligned2(C, ldc)) { copy_mat(C, ldc, p, p, Cw, ldp, st); Cc = Cw; ldcc = ldp; }
+  for (long i0 = 0; i0 < n1; i0 += slab) {
+    const long ns = std::min(slab, n1 - i0);
+    const double* xs = x1 + i0 * ld1; long lds = ld1;
+    if (!aligned2(xs, ld1)) { copy_mat(xs, ld1, (int)ns, p, x1w, ldp, st); xs = x1w; lds = ldp; }
+    GemmArgs g{};
+    g.A = xs; g.lda = lds; g.B = Cc; g.ldb = ldcc; g.C = Z1; g.ldc = ldp; g.M = (int)ns; g.N = p; g.K = p;
+    g.aux = xs; g.ldaux = lds; g.part1 = part; g.ldpart = ldpart;
+    CU(gemm(st, 0, 1, kRowdot, false, 1, g));
+    norms_finalize(part, ldpart, ntp, ns, sigma_0 * sigma_0, Kvec + i0, nrm, st);
+  }
+  CU(cudaGetLastError());
+  return SGP_OK;
+}
+
+int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K_b, long ldk, const double* Kvec,
+                       long N, int q, const double* m_b, const double* V_b, long ldv, double* lam_m, double* lam_var,
+                       void* stream) {
+  if (!h || !a || !K_b || !Kvec || !m_b || !V_b || !lam_m || !lam_var)
+    return fail(h, SGP_E_ARG, "sgp_lambda_moments: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long ldq = rup(q, 16);
+  const long slab = std::min<long>(h->slab_rows, rup(N, 128));
+  const int ntq = (q + 127) / 128;
+  const long ldpart = rup(slab, 16);
+  size_t need = 0;
+  auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
+  acc((size_t)q * ldq); acc((size_t)slab * ldq); acc((size_t)slab * ldq); acc((size_t)ntq * ldpart * 2);
+  need += 4096;
+  CU(h->arena.reserve(need));
+  Arena ar(h->arena.p, h->arena.bytes);
+  double* Vw = ar.take<double>((size_t)q * ldq);
+  double* aw = ar.take<double>((size_t)slab * ldq);
+  double* T = ar.take<double>((size_t)slab * ldq);
+  double* p1 = ar.take<double>((size_t)ntq * ldpart); double* p2 = ar.take<double>((size_t)ntq * ldpart);
+  copy_mat(V_b, ldv, q, q, Vw, ldq, st);
+  for (long i0 = 0; i0 < N; i0 += slab) {
+    const long ns = std::min(slab, N - i0);
+    const double* as = a + i0 * lda; long ldas = lda;
+    if (!aligned2(as, lda)) { copy_mat(as, lda, (int)ns, q, aw, ldq, st); as = aw; ldas = ldq; }
+    GemmArgs g{};  // T = a V^T ; part1 = rowdot(T, a) ; part2 = a m_b
+    g.A = as; g.lda = ldas; g.B = Vw; g.ldb = ldq; g.C = T; g.ldc = ldq; g.M = (int)ns; g.N = q; g.K = q;
+    g.aux = as; g.ldaux = ldas; g.colvec = m_b; g.part1 = p1; g.part2 = p2; g.ldpart = ldpart;
+    CU(gemm(st, 0, 0, kMoments, false, 1, g));
+    moments_combine(Kvec + i0, p1, p2, ldpart, ntq, a + i0 * lda, lda, K_b + i0 * ldk, ldk, ns, q, lam_m + i0,
+                    lam_var + i0, st);
+  }
+  CU(cudaGetLastError());
+  return SGP_OK;
+}
+
+int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, const double* r, long N, double logA,
+                    double lambda0, double* f, double* out_host, void* stream) {
+  if (!h || !lam_m || !lam_var || !r || !out_host) return fail(h, SGP_E_ARG, "sgp_fparam_eval: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nb = fparam_blocks(N);
+  CU(h->arena.reserve((size_t)nb * 8 * sizeof(double) + 4096));
+  double* bp = (double*)h->arena.p;
+  const double A = std::exp(logA);
+  fparam_pass(lam_m, lam_var, r, N, A, lambda0, f, bp, st);
+  for (int k = 0; k < 6; ++k) sum_to_slot(bp + k, nb, 8, 1.0, h->d_scal, kSlotAux0 + k, 0, st);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(h->h_out, h->d_scal + kSlotAux0, sizeof(double) * 6, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  const double rl = h->h_out[0], sf = h->h_out[1], sdf = h->h_out[2], sr = h->h_out[3], se = h->h_out[4];
+  out_host[0] = A * rl + lambda0 * sr - sf;          // loglik            U:1243
+  out_host[1] = A * (rl - sdf);                      // dloglik/dlogA     U:1253
+  out_host[2] = sr - sf;                             // dloglik/dlambda0  U:1255
+  out_host[3] = std::log(sr) - std::log(se);         // lambda0 closed form U:1227
+  out_host[4] = sr; out_host[5] = sf; out_host[6] = rl; out_host[7] = h->h_out[5];
+  return SGP_OK;
+}
+
+int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, const double* f, long N, int q,
+                    double logA, double* g, double* G, long ldg, void* stream) {
+  if (!h || !a || !r || !f || !g || !G) return fail(h, SGP_E_ARG, "sgp_estep_terms: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const double A = std::exp(logA);
+  const long ldq = rup(q, 16);
+  const long slab = std::min<long>(h->slab_rows, rup(N, 128));
+  const int ntq = (q + 127) / 128;
+  const int nz = pick_split(ntq * ntq, slab);
+  const long zs = (long)q * ldq;
+  const int ncb = colsum_blocks(slab);
+  size_t need = 0;
+  auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
+  acc((size_t)slab * ldq); acc((size_t)nz * zs); acc((size_t)ncb * ldq); acc((size_t)q * ldq);
+  need += 4096;
+  CU(h->arena.reserve(need));
+  Arena ar(h->arena.p, h->arena.bytes);
+  double* aw = ar.take<double>((size_t)slab * ldq);
+  double* Gpart = ar.take<double>((size_t)nz * zs);
+  double* colpart = ar.take<double>((size_t)ncb * ldq);
+  double* Gw = ar.take<double>((size_t)q * ldq);
+  int si = 0;
+  for (long i0 = 0; i0 < N; i0 += slab, ++si) {
+    const long ns = std::min(slab, N - i0);
+    const double* as = a + i0 * lda; long ldas = lda;
+    if (!aligned2(as, lda)) { copy_mat(as, lda, (int)ns, q, aw, ldq, st); as = aw; ldas = ldq; }
+    GemmArgs gg{};  // G += a^T diag(f) a   (U:1422)
+    gg.A = as; gg.lda = ldas; gg.B = as; gg.ldb = ldas; gg.C = Gpart; gg.ldc = ldq; gg.M = q; gg.N = q; gg.K = (int)ns;
+    gg.k_chunk = (int)rup((ns + nz - 1) / nz, 16); gg.zstride = zs; gg.accumulate = si > 0; gg.kscale = f + i0;
+    CU(gemm(st, 1, 1, kStore, false, nz, gg));
+    colsum_weighted(as, ldas, ns, q, r + i0, f + i0, colpart, ldq, st);   // g += a^T (r - f)   (U:1421)
+    col_reduce(colpart, colsum_blocks(ns), q, ldq, g, si > 0, st);
+  }
+  slice_reduce(Gpart, nz, zs, zs, Gw, 0, st);
+  lincomb(G, ldg, q, q, A * A, Gw, ldq, 0.0, nullptr, 0, 0.0, st);
+  scale_vec(g, q, A, st);
+  CU(cudaGetLastError());
+  return SGP_OK;
+}
+
+}  // extern "C"

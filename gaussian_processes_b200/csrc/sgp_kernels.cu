@@ -1,0 +1,762 @@
+// Non-GEMM kernels of the Spatial_GP ELBO+gradient pass (sm_100a).  See sgp_kernels.cuh.
+#include "sgp_kernels.cuh"
+
+#include <atomic>
+
+#include "gemm_f64.cuh"
+#include "sgp_common.cuh"
+
+namespace sgp {
+
+static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
+
+static std::atomic<long> g_launches{0};
+void note_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+long launch_counter() { return g_launches.load(std::memory_order_relaxed); }
+
+// =====================================================================================================
+// a1: localker (reference utils.py:880-910)
+// =====================================================================================================
+__global__ void build_C_kernel(double* __restrict__ C, long ldc, int p, const double* __restrict__ gx,
+                               const double* __restrict__ gy, ThetaDev th, double* __restrict__ dC, long dcs) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y;
+  if (j >= ldc) return;
+  double c = 0.0;
+  double d[5] = {0, 0, 0, 0, 0};
+  if (i < p && j < p) {
+    const double xi = gx[i], yi = gy[i], xj = gx[j], yj = gy[j];
+    const double lai = -th.eb * ((xi - th.ex) * (xi - th.ex) + (yi - th.ey) * (yi - th.ey));
+    const double laj = -th.eb * ((xj - th.ex) * (xj - th.ex) + (yj - th.ey) * (yj - th.ey));
+    const double ai = exp(lai), aj = exp(laj);
+    const double ls = -th.er * ((xj - xi) * (xj - xi) + (yj - yi) * (yj - yi));
+    const double e = exp(ls);
+    const double cij = ((th.amp * ai) * e) * aj;   // U:895 evaluation order
+    const double cji = ((th.amp * aj) * e) * ai;
+    c = (cij + cji) / 2;                            // U:898
+    if (dC) {
+      d[0] = c / th.amp;                                   // Amp        U:902
+      d[1] = c * (lai + laj);                              // -2log2beta U:907
+      d[2] = c * ls;                                       // -log2rho2  U:909
+      d[3] = 2.0 * th.eb * c * (xi + xj - 2 * th.ex);      // eps_0x     U:904
+      d[4] = 2.0 * th.eb * c * (yi + yj - 2 * th.ey);      // eps_0y     U:905
+    }
+  }
+  if (i < ldc) {
+    C[(long)i * ldc + j] = c;
+    if (dC) {
+#pragma unroll
+      for (int k = 0; k < 5; ++k) dC[k * dcs + (long)i * ldc + j] = d[k];
+    }
+  }
+}
+
+void build_C(double* C, long ldc, int p, const double* gx, const double* gy, const ThetaDev& th, double* dC,
+             long dcs, cudaStream_t st) {
+  dim3 grid(cdiv(ldc, 128), (unsigned)ldc);
+  note_launch(); build_C_kernel<<<grid, 128, 0, st>>>(C, ldc, p, gx, gy, th, dC, dcs);
+}
+
+__global__ void gather_cols_kernel(const double* __restrict__ X, long ldx, long nrows, const int* __restrict__ idx,
+                                   int p, double* __restrict__ out, long ldo) {
+  const long row = blockIdx.y;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < ldo; c += gridDim.x * blockDim.x)
+    out[row * ldo + c] = (c < p) ? X[row * ldx + idx[c]] : 0.0;
+}
+
+void gather_cols(const double* X, long ldx, long nrows, const int* idx, int p, double* out, long ldo,
+                 cudaStream_t st) {
+  if (nrows <= 0) return;
+  const long maxy = 65535;
+  for (long r0 = 0; r0 < nrows; r0 += maxy) {
+    const long nr = (nrows - r0) < maxy ? (nrows - r0) : maxy;
+    dim3 grid(cdiv(ldo, 256) > 8 ? 8 : cdiv(ldo, 256), (unsigned)nr);
+    note_launch(); gather_cols_kernel<<<grid, 256, 0, st>>>(X + r0 * ldx, ldx, nr, idx, p, out + r0 * ldo, ldo);
+  }
+}
+
+__global__ void norms_finalize_kernel(const double* __restrict__ part, long ldpart, int nparts, long n, double s02,
+                                      double* __restrict__ s, double* __restrict__ nrm) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double a = 0.0;
+  for (int t = 0; t < nparts; ++t) a += part[t * ldpart + i];
+  a += s02;
+  s[i] = a;
+  nrm[i] = sqrt(a);
+}
+
+void norms_finalize(const double* part, long ldpart, int nparts, long n, double s02, double* s, double* nrm,
+                    cudaStream_t st) {
+  if (n <= 0) return;
+  note_launch(); norms_finalize_kernel<<<cdiv(n, 256), 256, 0, st>>>(part, ldpart, nparts, n, s02, s, nrm);
+}
+
+// =====================================================================================================
+// a5-a7: moments / rate / adjoint weights per image (reference utils.py:1090-1101, 1138, 1243, 1266)
+// =====================================================================================================
+__global__ void moments_rows_kernel(const double* __restrict__ s, const double* __restrict__ part1,
+                                    const double* __restrict__ part2, long ldpart, int nparts,
+                                    const double* __restrict__ r, long n, double A, double lambda0,
+                                    double* __restrict__ lam_m, double* __restrict__ lam_var, double* __restrict__ f,
+                                    double* __restrict__ u, double* __restrict__ v, double* __restrict__ blockpart) {
+  __shared__ double red[32];
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  double rl = 0.0, fs = 0.0, rs = 0.0, nn = 0.0;
+  if (i < n) {
+    double q1 = 0.0, q2 = 0.0;
+    for (int t = 0; t < nparts; ++t) {
+      q1 += part1[t * ldpart + i];
+      q2 += part2[t * ldpart + i];
+    }
+    const double lv = s[i] + 0.5 * q1;
+    const double lm = q2;
+    const double fi = exp(A * lm + 0.5 * A * A * lv + lambda0);   // U:1138
+    const double ri = r[i];
+    lam_m[i] = lm;
+    lam_var[i] = lv;
+    f[i] = fi;
+    u[i] = A * (ri - fi);          // d loglik / d lam_m   (U:1266)
+    v[i] = -0.5 * A * A * fi;      // d loglik / d lam_var
+    rl = ri * lm; fs = fi; rs = ri; nn = (fi != fi) ? 1.0 : 0.0;
+  }
+  rl = block_sum(rl, red);
+  fs = block_sum(fs, red);
+  rs = block_sum(rs, red);
+  nn = block_sum(nn, red);
+  if (threadIdx.x == 0) {
+    blockpart[blockIdx.x * 4 + 0] = rl;
+    blockpart[blockIdx.x * 4 + 1] = fs;
+    blockpart[blockIdx.x * 4 + 2] = rs;
+    blockpart[blockIdx.x * 4 + 3] = nn;
+  }
+}
+
+int moments_rows_blocks(long n) { return cdiv(n, 256); }
+
+void moments_rows(const double* s, const double* part1, const double* part2, long ldpart, int nparts,
+                  const double* r, long n, double A, double lambda0, double* lam_m, double* lam_var, double* f,
+                  double* u, double* v, double* blockpart, cudaStream_t st) {
+  if (n <= 0) return;
+  note_launch(); moments_rows_kernel<<<moments_rows_blocks(n), 256, 0, st>>>(s, part1, part2, ldpart, nparts, r, n, A, lambda0,
+                                                              lam_m, lam_var, f, u, v, blockpart);
+}
+
+// =====================================================================================================
+// adjoint of the arc-cosine nonlinearity (reference local partials utils.py:996-1021)
+// =====================================================================================================
+template <int MODE>
+__global__ void __launch_bounds__(256) acos_backward_kernel(double* __restrict__ G, const double* __restrict__ cosm,
+                                                            const double* __restrict__ Kmat, long ld, long n, int m,
+                                                            const double* __restrict__ u, const double* __restrict__ v,
+                                                            const double* __restrict__ bb,
+                                                            const double* __restrict__ na,
+                                                            const double* __restrict__ nb, double* __restrict__ rowout,
+                                                            double* __restrict__ colpart_k,
+                                                            double* __restrict__ colpart_y, long ldcol,
+                                                            double* __restrict__ sumpart) {
+  constexpr int CM = kBwdMaxCols / 256;
+  __shared__ double rowred[8][kBwdRows];
+  __shared__ double red[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long r0 = (long)blockIdx.x * kBwdRows;
+  double ck[CM], cy[CM], bbj[CM], nbj[CM];
+#pragma unroll
+  for (int c = 0; c < CM; ++c) {
+    ck[c] = cy[c] = 0.0;
+    const int j = tid + c * 256;
+    bbj[c] = (MODE == 0 && j < m) ? bb[j] : 0.0;
+    nbj[c] = (j < m) ? nb[j] : 0.0;
+  }
+  double sumR = 0.0;
+  for (int rr = 0; rr < kBwdRows; ++rr) {
+    const long i = r0 + rr;
+    double rho = 0.0;
+    if (i < n) {
+      const double ui = (MODE == 0) ? u[i] : 0.0;
+      const double vi = (MODE == 0) ? v[i] : 0.0;
+      const double nai = na[i];
+#pragma unroll
+      for (int c = 0; c < CM; ++c) {
+        const int j = tid + c * 256;
+        if (j < m) {
+          const long o = i * ld + j;
+          const double gij = G[o];
+          const double gk = (MODE == 0) ? (ui * bbj[c] + vi * gij) : gij;
+          double P, Q;
+          acos_partials(cosm[o], P, Q);
+          const double Rv = gk * P;
+          const double rq = gk * Q;
+          G[o] = Rv;
+          sumR += Rv;
+          rho += rq * nbj[c];
+          ck[c] += rq * nai;
+          if (MODE == 0) cy[c] += Kmat[o] * ui;
+        }
+      }
+    }
+    rho = warp_sum(rho);
+    if (lane == 0) rowred[warp][rr] = rho;
+  }
+  __syncthreads();
+  if (tid < kBwdRows) {
+    const long i = r0 + tid;
+    if (i < n) {
+      double rho = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) rho += rowred[w][tid];
+      rowout[i] = ((MODE == 0) ? v[i] : 0.0) + 0.5 * rho / na[i];
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < CM; ++c) {
+    const int j = tid + c * 256;
+    if (j < m) {
+      colpart_k[(long)blockIdx.x * ldcol + j] = ck[c];
+      if (MODE == 0) colpart_y[(long)blockIdx.x * ldcol + j] = cy[c];
+    }
+  }
+  sumR = block_sum(sumR, red);
+  if (tid == 0) sumpart[blockIdx.x] = sumR;
+}
+
+int acos_backward_blocks(long n) { return cdiv(n, kBwdRows); }
+
+void acos_backward(int mode, double* G, const double* cosm, const double* Kmat, long ld, long n, int m,
+                   const double* u, const double* v, const double* bb, const double* na, const double* nb,
+                   double* rowout, double* colpart_k, double* colpart_y, long ldcol, double* sumpart,
+                   cudaStream_t st) {
+  if (n <= 0) return;
+  const int nblk = acos_backward_blocks(n);
+  if (mode == 0) {
+    note_launch(); acos_backward_kernel<0><<<nblk, 256, 0, st>>>(G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout, colpart_k,
+                                                  colpart_y, ldcol, sumpart);
+  } else {
+    note_launch(); acos_backward_kernel<1><<<nblk, 256, 0, st>>>(G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout, colpart_k,
+                                                  colpart_y, ldcol, sumpart);
+  }
+}
+
+// =====================================================================================================
+// deterministic reductions
+// =====================================================================================================
+__global__ void col_reduce_kernel(const double* __restrict__ part, int nblk, int m, long ld, double* __restrict__ out,
+                                  int accumulate) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= m) return;
+  double a = 0.0;
+  for (int b = 0; b < nblk; ++b) a += part[(long)b * ld + j];
+  out[j] = accumulate ? out[j] + a : a;
+}
+void col_reduce(const double* part, int nblk, int m, long ld, double* out, int accumulate, cudaStream_t st) {
+  if (m <= 0) return;
+  note_launch(); col_reduce_kernel<<<cdiv(m, 64), 64, 0, st>>>(part, nblk, m, ld, out, accumulate);
+}
+
+__global__ void slice_reduce_kernel(const double* __restrict__ part, int nz, long zstride, long n,
+                                    double* __restrict__ out, int accumulate) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    double a = 0.0;
+    for (int z = 0; z < nz; ++z) a += part[z * zstride + i];
+    out[i] = accumulate ? out[i] + a : a;
+  }
+}
+void slice_reduce(const double* part, int nz, long zstride, long n, double* out, int accumulate, cudaStream_t st) {
+  if (n <= 0) return;
+  int nb = cdiv(n, 256);
+  if (nb > 148 * 8) nb = 148 * 8;
+  note_launch(); slice_reduce_kernel<<<nb, 256, 0, st>>>(part, nz, zstride, n, out, accumulate);
+}
+
+__global__ void sum_to_slot_kernel(const double* __restrict__ x, long n, long stride, double scale,
+                                   double* __restrict__ scal, int slot, int accumulate) {
+  __shared__ double red[32];
+  double a = 0.0;
+  for (long i = threadIdx.x; i < n; i += blockDim.x) a += x[i * stride];
+  a = block_sum(a, red);
+  if (threadIdx.x == 0) scal[slot] = (accumulate ? scal[slot] : 0.0) + scale * a;
+}
+void sum_to_slot(const double* x, long n, long stride, double scale, double* scal, int slot, int accumulate,
+                 cudaStream_t st) {
+  note_launch(); sum_to_slot_kernel<<<1, 1024, 0, st>>>(x, n < 0 ? 0 : n, stride, scale, scal, slot, accumulate);
+}
+
+// =====================================================================================================
+// small dense helpers
+// =====================================================================================================
+__global__ void symmetrize_kernel(const double* __restrict__ A, long lda, int n, double* __restrict__ out, long ldo) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i < n && j < n) out[(long)i * ldo + j] = (A[(long)i * lda + j] + A[(long)j * lda + i]) * 0.5;
+}
+void symmetrize(const double* A, long lda, int n, double* out, long ldo, cudaStream_t st) {
+  if (n <= 0) return;
+  note_launch(); symmetrize_kernel<<<dim3(cdiv(n, 128), n), 128, 0, st>>>(A, lda, n, out, ldo);
+}
+
+__global__ void lincomb_kernel(double* __restrict__ out, long ldo, int rows, int cols, double a,
+                               const double* __restrict__ A, long lda, double b, const double* __restrict__ B, long ldb,
+                               double diag) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i >= rows || j >= cols) return;
+  double v = a * A[(long)i * lda + j];
+  if (B) v += b * B[(long)i * ldb + j];
+  if (i == j) v += diag;
+  out[(long)i * ldo + j] = v;
+}
+void lincomb(double* out, long ldo, int rows, int cols, double a, const double* A, long lda, double b,
+             const double* B, long ldb, double diag, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return;
+  note_launch(); lincomb_kernel<<<dim3(cdiv(cols, 128), rows), 128, 0, st>>>(out, ldo, rows, cols, a, A, lda, b, B, ldb, diag);
+}
+
+__global__ void rank1_add_kernel(double* __restrict__ out, long ldo, int rows, int cols, double alpha,
+                                 const double* __restrict__ x, const double* __restrict__ y) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i < rows && j < cols) out[(long)i * ldo + j] += alpha * x[i] * y[j];
+}
+void rank1_add(double* out, long ldo, int rows, int cols, double alpha, const double* x, const double* y,
+               cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return;
+  note_launch(); rank1_add_kernel<<<dim3(cdiv(cols, 128), rows), 128, 0, st>>>(out, ldo, rows, cols, alpha, x, y);
+}
+
+// y = A x (trans = 0, one warp per row) or y = A^T x (trans = 1, one thread per column)
+__global__ void gemv_n_kernel(const double* __restrict__ A, long lda, int rows, int cols,
+                              const double* __restrict__ x, double* __restrict__ y) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  double a = 0.0;
+  for (int j = lane; j < cols; j += 32) a += A[(long)row * lda + j] * x[j];
+  a = warp_sum(a);
+  if (lane == 0) y[row] = a;
+}
+__global__ void gemv_t_kernel(const double* __restrict__ A, long lda, int rows, int cols,
+                              const double* __restrict__ x, double* __restrict__ y) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= cols) return;
+  double a = 0.0;
+  for (int i = 0; i < rows; ++i) a += A[(long)i * lda + j] * x[i];
+  y[j] = a;
+}
+void gemv(const double* A, long lda, int rows, int cols, int trans, const double* x, double* y, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return;
+  if (!trans) {
+    note_launch(); gemv_n_kernel<<<cdiv(rows, 8), 256, 0, st>>>(A, lda, rows, cols, x, y);
+  } else {
+    note_launch(); gemv_t_kernel<<<cdiv(cols, 64), 64, 0, st>>>(A, lda, rows, cols, x, y);
+  }
+}
+
+__global__ void copy_mat_kernel(const double* __restrict__ A, long lda, int rows, int cols, double* __restrict__ out,
+                                long ldo) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i < rows && j < ldo) out[(long)i * ldo + j] = (j < cols) ? A[(long)i * lda + j] : 0.0;
+}
+void copy_mat(const double* A, long lda, int rows, int cols, double* out, long ldo, cudaStream_t st) {
+  if (rows <= 0) return;
+  note_launch(); copy_mat_kernel<<<dim3(cdiv(ldo, 128), rows), 128, 0, st>>>(A, lda, rows, cols, out, ldo);
+}
+
+__global__ void gkt_assemble_kernel(double* __restrict__ G, long ld, int q, const double* __restrict__ Kinv,
+                                    const double* __restrict__ KVK, const double* __restrict__ b) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i < q && j < q)
+    G[(long)i * ld + j] += -0.5 * Kinv[(long)i * ld + j] + 0.5 * KVK[(long)j * ld + i] + 0.5 * b[i] * b[j];
+}
+void gkt_assemble(double* G, long ld, int q, const double* Kinv, const double* KVK, const double* b, cudaStream_t st) {
+  note_launch(); gkt_assemble_kernel<<<dim3(cdiv(q, 128), q), 128, 0, st>>>(G, ld, q, Kinv, KVK, b);
+}
+
+__global__ void col_weights_kernel(const double* __restrict__ ka, const double* __restrict__ kb,
+                                   const double* __restrict__ extra, const double* __restrict__ nrm, int m,
+                                   double* __restrict__ out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= m) return;
+  double k = ka ? ka[j] : 0.0;
+  if (kb) k += kb[j];
+  out[j] = 0.5 * k / nrm[j] + (extra ? extra[j] : 0.0);
+}
+void col_weights(const double* ka, const double* kb, const double* extra, const double* nrm, int m, double* out,
+                 cudaStream_t st) {
+  if (m <= 0) return;
+  note_launch(); col_weights_kernel<<<cdiv(m, 128), 128, 0, st>>>(ka, kb, extra, nrm, m, out);
+}
+
+// =====================================================================================================
+// blocked Cholesky (panel 64): [factor 64x64 diagonal block + TRSM of the rows below] ; DMMA trailing update
+// =====================================================================================================
+constexpr int kNB = 64;
+
+// Block 0 factors the diagonal block and writes it back; blocks >= 1 redo the tiny factorisation in shared
+// memory (cheaper than a second launch) and solve 64 rows of the panel:  X * L11^T = A21.
+__global__ void __launch_bounds__(kNB) chol_panel_kernel(double* __restrict__ A, long ld, int n, int j0, int nb,
+                                                         int* __restrict__ flags, int bit_notpd, int bit_small) {
+  __shared__ double D[kNB][kNB + 1];
+  const int tid = threadIdx.x;
+  // load the diagonal block (lower triangle), identity-padded to 64x64
+  for (int r = 0; r < kNB; ++r) {
+    double v = (r == tid) ? 1.0 : 0.0;
+    if (r < nb && tid < nb) v = (tid <= r) ? A[(long)(j0 + r) * ld + j0 + tid] : 0.0;
+    D[r][tid] = v;
+  }
+  int bad = 0;
+  for (int k = 0; k < kNB; ++k) {
+    __syncthreads();
+    const double d = D[k][k];
+    if (k < nb) {
+      if (!(d > 0.0)) bad |= bit_notpd;
+      else if (sqrt(d) < 1e-10) bad |= bit_small;
+    }
+    const double lkk = sqrt(d > 0.0 ? d : 1.0);   // keep going with a harmless pivot; the flag tells the host
+    __syncthreads();
+    if (tid == k) D[k][k] = lkk;
+    if (tid > k) D[tid][k] /= lkk;
+    __syncthreads();
+    if (tid > k) {
+      const double lik = D[tid][k];
+      for (int l = k + 1; l <= tid; ++l) D[tid][l] -= lik * D[l][k];
+    }
+  }
+  __syncthreads();
+  if (blockIdx.x == 0) {
+    if (tid == 0 && bad) atomicOr(flags, bad);
+    for (int r = 0; r < nb; ++r)
+      if (tid < nb) A[(long)(j0 + r) * ld + j0 + tid] = (tid <= r) ? D[r][tid] : 0.0;
+    return;
+  }
+  // ---- TRSM: rows r0 .. r0+63 of the panel below the diagonal block (one row per thread)
+  const int row = j0 + nb + (blockIdx.x - 1) * kNB + tid;
+  if (row < n) {
+    double* ap = A + (long)row * ld + j0;
+    double x[kNB];
+#pragma unroll
+    for (int k = 0; k < kNB; ++k) x[k] = (k < nb) ? ap[k] : 0.0;
+#pragma unroll
+    for (int k = 0; k < kNB; ++k) {
+      double sacc = x[k];
+#pragma unroll
+      for (int l = 0; l < k; ++l) sacc -= x[l] * D[k][l];
+      x[k] = sacc / D[k][k];
+    }
+#pragma unroll
+    for (int k = 0; k < kNB; ++k)
+      if (k < nb) ap[k] = x[k];
+  }
+}
+
+cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, cudaStream_t st) {
+  for (int j0 = 0; j0 < n; j0 += kNB) {
+    const int nb = (n - j0) < kNB ? (n - j0) : kNB;
+    const int rem = n - j0 - nb;
+    note_launch(); chol_panel_kernel<<<1 + cdiv(rem, kNB), kNB, 0, st>>>(A, ld, n, j0, nb, flags, bit_notpd, bit_small);
+    if (rem > 0) {
+      GemmArgs g{};
+      const int j1 = j0 + nb;
+      g.A = A + (long)j1 * ld + j0; g.lda = ld;
+      g.B = g.A; g.ldb = ld;
+      g.C = A + (long)j1 * ld + j1; g.ldc = ld;
+      g.M = rem; g.N = rem; g.K = nb; g.k_chunk = kNB; g.alpha = -1.0; g.accumulate = 1;
+      cudaError_t e = gemm_f64_launch(g, GemmLaunch{0, 0, kStore, true, 1}, st);
+      if (e != cudaSuccess) return e;
+    }
+  }
+  return cudaGetLastError();
+}
+
+// inverse of each 64x64 diagonal block of L, written into the diagonal blocks of X (rest of X zeroed by caller)
+__global__ void __launch_bounds__(kNB) tri_diag_inv_kernel(const double* __restrict__ L, long ld, int n,
+                                                           double* __restrict__ X) {
+  __shared__ double D[kNB][kNB + 1];
+  const int tid = threadIdx.x;
+  const int j0 = blockIdx.x * kNB;
+  const int nb = (n - j0) < kNB ? (n - j0) : kNB;
+  for (int r = 0; r < kNB; ++r) {
+    double v = (r == tid) ? 1.0 : 0.0;
+    if (r < nb && tid < nb) v = (tid <= r) ? L[(long)(j0 + r) * ld + j0 + tid] : 0.0;
+    D[r][tid] = v;
+  }
+  __syncthreads();
+  double x[kNB];
+#pragma unroll
+  for (int k = 0; k < kNB; ++k) {
+    double sacc = (k == tid) ? 1.0 : 0.0;
+#pragma unroll
+    for (int l = 0; l < k; ++l) sacc -= D[k][l] * x[l];
+    x[k] = sacc / D[k][k];
+  }
+  // thread tid owns column tid of the inverse
+#pragma unroll
+  for (int k = 0; k < kNB; ++k)
+    if (k < nb && tid < nb) X[(long)(j0 + k) * ld + j0 + tid] = x[k];
+}
+
+__global__ void zero_mat_kernel(double* __restrict__ X, long ld, int rows) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i < rows && j < ld) X[(long)i * ld + j] = 0.0;
+}
+
+cudaError_t tri_inverse_lower(const double* L, long ld, int n, double* X, double* tmp, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  note_launch(); zero_mat_kernel<<<dim3(cdiv(ld, 128), n), 128, 0, st>>>(X, ld, n);
+  const int nblk = cdiv(n, kNB);
+  note_launch(); tri_diag_inv_kernel<<<nblk, kNB, 0, st>>>(L, ld, n, X);
+  for (int I = 1; I < nblk; ++I) {
+    const int i0 = I * kNB;
+    const int nb = (n - i0) < kNB ? (n - i0) : kNB;
+    // tmp[nb x i0] = L[i0:i0+nb, 0:i0] * X[0:i0, 0:i0]
+    GemmArgs g{};
+    g.A = L + (long)i0 * ld; g.lda = ld;
+    g.B = X; g.ldb = ld;
+    g.C = tmp; g.ldc = ld;
+    g.M = nb; g.N = i0; g.K = i0; g.k_chunk = (i0 + 15) / 16 * 16; g.alpha = 1.0;
+    cudaError_t e = gemm_f64_launch(g, GemmLaunch{0, 1, kStore, true, 1}, st);
+    if (e != cudaSuccess) return e;
+    // X[i0:i0+nb, 0:i0] = -Dinv_I * tmp
+    GemmArgs h{};
+    h.A = X + (long)i0 * ld + i0; h.lda = ld;
+    h.B = tmp; h.ldb = ld;
+    h.C = X + (long)i0 * ld; h.ldc = ld;
+    h.M = nb; h.N = i0; h.K = nb; h.k_chunk = kNB; h.alpha = -1.0;
+    e = gemm_f64_launch(h, GemmLaunch{0, 1, kStore, true, 1}, st);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaGetLastError();
+}
+
+__global__ void logdet_kernel(const double* __restrict__ L, long ld, int n, double* __restrict__ scal, int slot) {
+  __shared__ double red[32];
+  double a = 0.0;
+  for (int k = threadIdx.x; k < n; k += blockDim.x) a += log(L[(long)k * ld + k]);
+  a = block_sum(a, red);
+  if (threadIdx.x == 0) scal[slot] = 2.0 * a;
+}
+void logdet_from_chol(const double* L, long ld, int n, double* scal, int slot, cudaStream_t st) {
+  note_launch(); logdet_kernel<<<1, 256, 0, st>>>(L, ld, n, scal, slot);
+}
+
+__global__ void kl_scalars_kernel(const double* __restrict__ m_b, const double* __restrict__ b,
+                                  const double* __restrict__ V, long ldv, const double* __restrict__ Kinv, long ldk,
+                                  int q, double* __restrict__ scal, int slot_mb, int slot_tr) {
+  __shared__ double red[32];
+  double a = 0.0, tr = 0.0;
+  for (int i = threadIdx.x; i < q; i += blockDim.x) a += m_b[i] * b[i];
+  for (long e = threadIdx.x; e < (long)q * q; e += blockDim.x) {
+    const int i = (int)(e / q), j = (int)(e % q);
+    tr += V[(long)i * ldv + j] * Kinv[(long)j * ldk + i];
+  }
+  a = block_sum(a, red);
+  tr = block_sum(tr, red);
+  if (threadIdx.x == 0) {
+    scal[slot_mb] = a;
+    scal[slot_tr] = tr;
+  }
+}
+void kl_scalars(const double* m_b, const double* b, const double* V, long ldv, const double* Kinv, long ldk, int q,
+                double* scal, int slot_mb, int slot_tr, cudaStream_t st) {
+  note_launch(); kl_scalars_kernel<<<1, 1024, 0, st>>>(m_b, b, V, ldv, Kinv, ldk, q, scal, slot_mb, slot_tr);
+}
+
+// =====================================================================================================
+// <dC_k, GC> for the 5 localker hyper-parameters; dC_k is regenerated from C and the pixel coordinates
+// (reference utils.py:902-909), it is never stored.
+// =====================================================================================================
+__global__ void __launch_bounds__(256) contract_dC_kernel(const double* __restrict__ GCpart, int nz, long zstride,
+                                                          const double* __restrict__ GCextra,
+                                                          const double* __restrict__ C, long ld, int p,
+                                                          const double* __restrict__ gx,
+                                                          const double* __restrict__ gy, ThetaDev th,
+                                                          double* __restrict__ gpart) {
+  __shared__ double red[32];
+  const int i = blockIdx.x;
+  double acc[5] = {0, 0, 0, 0, 0};
+  if (i < p) {
+    const double xi = gx[i], yi = gy[i];
+    const double lai = -th.eb * ((xi - th.ex) * (xi - th.ex) + (yi - th.ey) * (yi - th.ey));
+    for (int j = threadIdx.x; j < p; j += blockDim.x) {
+      const long o = (long)i * ld + j;
+      double gsum = GCextra ? GCextra[o] : 0.0;
+      for (int z = 0; z < nz; ++z) gsum += GCpart[z * zstride + o];
+      const double xj = gx[j], yj = gy[j];
+      const double laj = -th.eb * ((xj - th.ex) * (xj - th.ex) + (yj - th.ey) * (yj - th.ey));
+      const double ls = -th.er * ((xj - xi) * (xj - xi) + (yj - yi) * (yj - yi));
+      const double gc = gsum * C[o];
+      acc[0] += gc;
+      acc[1] += gc * (lai + laj);
+      acc[2] += gc * ls;
+      acc[3] += gc * (xi + xj - 2 * th.ex);
+      acc[4] += gc * (yi + yj - 2 * th.ey);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const double sres = block_sum(acc[k], red);
+    if (threadIdx.x == 0) gpart[(long)blockIdx.x * 5 + k] = sres;
+  }
+}
+int contract_blocks(int p) { return p; }
+void contract_dC(const double* GCpart, int nz, long zstride, const double* GCextra, const double* C, long ld, int p,
+                 const double* gx, const double* gy, const ThetaDev& th, double* gpart, cudaStream_t st) {
+  if (p <= 0) return;
+  note_launch(); contract_dC_kernel<<<p, 256, 0, st>>>(GCpart, nz, zstride, GCextra, C, ld, p, gx, gy, th, gpart);
+}
+
+__global__ void finalize_kernel(const double* __restrict__ scal, const int* __restrict__ flags, double A,
+                                double lambda0, ThetaDev th, int p, double logdetV_override, int use_override,
+                                double* __restrict__ out) {
+  const double s0 = th.s0, amp = th.amp, eb = th.eb;
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const double logdetV = use_override ? logdetV_override : scal[kSlotLogdetV];
+  const double loglik = A * scal[kSlotRLam] + lambda0 * scal[kSlotSumR] - scal[kSlotSumF];      // U:1243
+  const double KL = -0.5 * logdetV + 0.5 * scal[kSlotLogdetK] + 0.5 * scal[kSlotMb] + 0.5 * scal[kSlotTrVK];  // U:1326
+  int fl = flags[0];
+  if (scal[kSlotNaN] > 0.0) fl |= kFlagNaN;
+  out[0] = loglik;
+  out[1] = KL;
+  out[2] = 2.0 * s0 * scal[kSlotSig];          // sigma_0
+  out[3] = 2.0 * eb * scal[kSlotG + 3];        // eps_0x
+  out[4] = 2.0 * eb * scal[kSlotG + 4];        // eps_0y
+  out[5] = scal[kSlotG + 1];                   // -2log2beta
+  out[6] = scal[kSlotG + 2];                   // -log2rho2
+  out[7] = scal[kSlotG + 0] / amp;             // Amp
+  out[8] = (double)fl;
+  out[9] = (double)p;
+  out[10] = scal[kSlotSumR];
+  out[11] = scal[kSlotSumF];
+  out[12] = scal[kSlotRLam];
+  out[13] = scal[kSlotLogdetK];
+  out[14] = logdetV;
+  out[15] = 0.0;
+}
+
+void finalize(const double* scal, const int* flags, double A, double lambda0, const ThetaDev& th, int p,
+              double logdetV_override, int use_override, double* out, cudaStream_t st) {
+  note_launch(); finalize_kernel<<<1, 32, 0, st>>>(scal, flags, A, lambda0, th, p, logdetV_override, use_override, out);
+}
+
+
+// =====================================================================================================
+// E-step / f-param helpers
+// =====================================================================================================
+__global__ void moments_combine_kernel(const double* __restrict__ Kvec, const double* __restrict__ part1,
+                                       const double* __restrict__ part2, long ldpart, int nparts,
+                                       const double* __restrict__ a, long lda, const double* __restrict__ K_b,
+                                       long ldk, long n, int q, double* __restrict__ lam_m,
+                                       double* __restrict__ lam_var) {
+  // one warp per image
+  const long i = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= n) return;
+  double d = 0.0;
+  for (int j = lane; j < q; j += 32) d += K_b[i * ldk + j] * a[i * lda + j];
+  d = warp_sum(d);
+  if (lane == 0) {
+    double q1 = 0.0, q2 = 0.0;
+    for (int t = 0; t < nparts; ++t) {
+      q1 += part1[t * ldpart + i];
+      q2 += part2[t * ldpart + i];
+    }
+    lam_m[i] = q2;
+    lam_var[i] = Kvec[i] + (q1 - d);
+  }
+}
+void moments_combine(const double* Kvec, const double* part1, const double* part2, long ldpart, int nparts,
+                     const double* a, long lda, const double* K_b, long ldk, long n, int q, double* lam_m,
+                     double* lam_var, cudaStream_t st) {
+  if (n <= 0) return;
+  note_launch(); moments_combine_kernel<<<cdiv(n, 8), 256, 0, st>>>(Kvec, part1, part2, ldpart, nparts, a, lda, K_b,
+                                                                    ldk, n, q, lam_m, lam_var);
+}
+
+constexpr int kFparamBlocks = 148 * 4;
+__global__ void __launch_bounds__(256) fparam_kernel(const double* __restrict__ lam_m,
+                                                     const double* __restrict__ lam_var,
+                                                     const double* __restrict__ r, long n, double A, double lambda0,
+                                                     double* __restrict__ f, double* __restrict__ blockpart) {
+  __shared__ double red[32];
+  double acc[6] = {0, 0, 0, 0, 0, 0};
+  const double hA2 = 0.5 * A * A;
+  auto body = [&](double lm, double lv, double ri, double& fout) {
+    const double e = exp(A * lm + hA2 * lv);            // U:1224
+    const double fi = exp(A * lm + hA2 * lv + lambda0);  // U:1138
+    fout = fi;
+    acc[0] += ri * lm;
+    acc[1] += fi;
+    acc[2] += (lm + A * lv) * fi;                        // U:1253
+    acc[3] += ri;
+    acc[4] += e;
+    acc[5] += (fi != fi) ? 1.0 : 0.0;
+  };
+  const long n2 = n >> 1;
+  const double2* lm2 = reinterpret_cast<const double2*>(lam_m);
+  const double2* lv2 = reinterpret_cast<const double2*>(lam_var);
+  const double2* r2 = reinterpret_cast<const double2*>(r);
+  const bool vec_ok = ((reinterpret_cast<uintptr_t>(lam_m) | reinterpret_cast<uintptr_t>(lam_var) |
+                        reinterpret_cast<uintptr_t>(r) | reinterpret_cast<uintptr_t>(f)) & 15) == 0;
+  if (vec_ok) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (long)gridDim.x * blockDim.x) {
+      const double2 a = lm2[i], b = lv2[i], c = r2[i];
+      double f0, f1;
+      body(a.x, b.x, c.x, f0);
+      body(a.y, b.y, c.y, f1);
+      if (f) reinterpret_cast<double2*>(f)[i] = make_double2(f0, f1);
+    }
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+      double f0;
+      body(lam_m[n - 1], lam_var[n - 1], r[n - 1], f0);
+      if (f) f[n - 1] = f0;
+    }
+  } else {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+      double f0;
+      body(lam_m[i], lam_var[i], r[i], f0);
+      if (f) f[i] = f0;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    const double sres = block_sum(acc[k], red);
+    if (threadIdx.x == 0) blockpart[(long)blockIdx.x * 8 + k] = sres;
+  }
+}
+int fparam_blocks(long n) {
+  const int nb = cdiv(n, 512);
+  return nb < kFparamBlocks ? (nb < 1 ? 1 : nb) : kFparamBlocks;
+}
+void fparam_pass(const double* lam_m, const double* lam_var, const double* r, long n, double A, double lambda0,
+                 double* f, double* blockpart, cudaStream_t st) {
+  note_launch(); fparam_kernel<<<fparam_blocks(n), 256, 0, st>>>(lam_m, lam_var, r, n, A, lambda0, f, blockpart);
+}
+
+constexpr int kColsumRows = 128;
+__global__ void __launch_bounds__(256) colsum_weighted_kernel(const double* __restrict__ a, long lda, long n, int q,
+                                                              const double* __restrict__ r,
+                                                              const double* __restrict__ f,
+                                                              double* __restrict__ colpart, long ldcol) {
+  const long r0 = (long)blockIdx.x * kColsumRows;
+  for (int j = threadIdx.x; j < q; j += blockDim.x) {
+    double acc = 0.0;
+    for (int rr = 0; rr < kColsumRows; ++rr) {
+      const long i = r0 + rr;
+      if (i < n) acc += a[i * lda + j] * (r[i] - f[i]);
+    }
+    colpart[(long)blockIdx.x * ldcol + j] = acc;
+  }
+}
+int colsum_blocks(long n) { return cdiv(n, kColsumRows); }
+void colsum_weighted(const double* a, long lda, long n, int q, const double* r, const double* f, double* colpart,
+                     long ldcol, cudaStream_t st) {
+  if (n <= 0) return;
+  note_launch(); colsum_weighted_kernel<<<colsum_blocks(n), 256, 0, st>>>(a, lda, n, q, r, f, colpart, ldcol);
+}
+
+__global__ void scale_vec_kernel(double* __restrict__ x, long n, double alpha) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) x[i] *= alpha;
+}
+void scale_vec(double* x, long n, double alpha, cudaStream_t st) {
+  if (n <= 0) return;
+  note_launch(); scale_vec_kernel<<<cdiv(n, 256), 256, 0, st>>>(x, n, alpha);
+}
+
+}  // namespace sgp

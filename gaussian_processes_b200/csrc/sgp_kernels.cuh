@@ -1,0 +1,133 @@
+// Host-callable wrappers of the non-GEMM kernels of the Spatial_GP pass (definitions: sgp_kernels.cu).
+// All pointers are device pointers unless stated otherwise; every launch goes to `st`.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace sgp {
+
+// status bits reported in out[8] of the fused closure (and by the factorisation helpers)
+enum StatusBits : int {
+  kFlagKtNotPD = 1,        // Cholesky of K_tilde_b hit a pivot <= 0 (reference: log_det falls back to eigh, U:1279)
+  kFlagKtSmallPivot = 2,   // pivot < 1e-10 (reference safe_log raises, U:670)
+  kFlagVNotPD = 4,         // same for V_b
+  kFlagVSmallPivot = 8,
+  kFlagNaN = 16,           // NaN in f (reference raises in the f-param closure, U:1923)
+};
+
+// slots of the small device scalar buffer the closure accumulates into
+enum ScalSlot : int {
+  kSlotLogdetK = 0, kSlotLogdetV = 1, kSlotMb = 2, kSlotTrVK = 3,
+  kSlotRLam = 4, kSlotSumF = 5, kSlotSumR = 6, kSlotNaN = 7,
+  kSlotSig = 8,            // sum R + sum w + sum beta + sum R~ + sum w~   (sigma_0 gradient / (2 sigma_0))
+  kSlotG = 9,              // 5 slots: <dC_k, GC> for Amp, -2log2beta, -log2rho2, eps_0x, eps_0y
+  kSlotAux0 = 14, kSlotAux1 = 15, kSlotAux2 = 16, kSlotAux3 = 17,
+  kNumSlots = 32
+};
+
+// every kernel launch of the library is counted (bench.py reports it as gpu_launches)
+void note_launch(int n = 1);
+long launch_counter();
+
+struct ThetaDev {  // hyper-parameters in the form the kernels need
+  double s0, s02, ex, ey, eb, er, amp;
+};
+
+// ---- a1: localker --------------------------------------------------------------------------
+// C (p x p, ld = ldc, padding zeroed) from masked pixel coordinates gx/gy (device, length p).
+// dC (optional): 5 matrices, stride dc_stride, order Amp, -2log2beta, -log2rho2, eps_0x, eps_0y (U:910).
+void build_C(double* C, long ldc, int p, const double* gx, const double* gy, const ThetaDev& th, double* dC,
+             long dc_stride, cudaStream_t st);
+
+// out[i][c] = X[i][idx[c]] (c < p), 0 for p <= c < ldo
+void gather_cols(const double* X, long ldx, long nrows, const int* idx, int p, double* out, long ldo,
+                 cudaStream_t st);
+
+// s[i] = s02 + sum_t part[t*ldpart + i] ; nrm[i] = sqrt(s[i])
+void norms_finalize(const double* part, long ldpart, int nparts, long n, double s02, double* s, double* nrm,
+                    cudaStream_t st);
+
+// ---- a5-a7: per-image moments, rate, adjoint weights ---------------------------------------
+// lam_var = s + 0.5*sum_t part1 ; lam_m = sum_t part2 ; f = exp(A lam_m + A^2 lam_var/2 + lambda0)
+// u = A (r - f) ; v = -A^2 f / 2 ; blockpart[blk*4 + {0,1,2,3}] = sum r*lam_m, sum f, sum r, nan-count
+int moments_rows_blocks(long n);
+void moments_rows(const double* s, const double* part1, const double* part2, long ldpart, int nparts,
+                  const double* r, long n, double A, double lambda0, double* lam_m, double* lam_var, double* f,
+                  double* u, double* v, double* blockpart, cudaStream_t st);
+
+// ---- adjoint of the arc-cosine nonlinearity (N x m elementwise + row/column reductions) ----
+// mode 0: GK_ij = u_i*bb_j + v_i*G_ij ; mode 1: GK_ij = G_ij.
+// G is overwritten with R = GK*P.  rowout_i = (mode0 ? v_i : 0) + 0.5*rho_i/na_i,
+// colpart_k[blk][j] = sum_{i in blk} GK_ij Q_ij na_i ; colpart_y[blk][j] = sum_i Kmat_ij u_i (mode 0)
+// sumpart[blk] = sum R.   Requires m <= kBwdMaxCols.
+constexpr int kBwdRows = 64;
+constexpr int kBwdMaxCols = 2048;
+int acos_backward_blocks(long n);
+void acos_backward(int mode, double* G, const double* cosm, const double* Kmat, long ld, long n, int m,
+                   const double* u, const double* v, const double* bb, const double* na, const double* nb,
+                   double* rowout, double* colpart_k, double* colpart_y, long ldcol, double* sumpart,
+                   cudaStream_t st);
+
+// out[j] (+)= sum_b part[b*ld + j]   (fixed order -> deterministic)
+void col_reduce(const double* part, int nblk, int m, long ld, double* out, int accumulate, cudaStream_t st);
+// out[i] (+)= sum_z part[z*zstride + i], i < n
+void slice_reduce(const double* part, int nz, long zstride, long n, double* out, int accumulate, cudaStream_t st);
+// scal[slot] (+)= scale * sum_i x[i*stride], single CTA, fixed order
+void sum_to_slot(const double* x, long n, long stride, double scale, double* scal, int slot, int accumulate,
+                 cudaStream_t st);
+
+// ---- small dense helpers (q x q / m x m) -----------------------------------------------------
+void symmetrize(const double* A, long lda, int n, double* out, long ldo, cudaStream_t st);   // out = (A + A^T)/2
+void lincomb(double* out, long ldo, int rows, int cols, double a, const double* A, long lda, double b,
+             const double* B, long ldb, double diag, cudaStream_t st);                        // out = a*A + b*B + diag*I
+void rank1_add(double* out, long ldo, int rows, int cols, double alpha, const double* x, const double* y,
+               cudaStream_t st);                                                             // out += alpha x y^T
+void gemv(const double* A, long lda, int rows, int cols, int trans, const double* x, double* y, cudaStream_t st);
+void copy_mat(const double* A, long lda, int rows, int cols, double* out, long ldo, cudaStream_t st);
+// G = G - 0.5*Kinv + 0.5*KVK^T + 0.5*b b^T     (adjoint of K_tilde_b: loglik part already in G)
+void gkt_assemble(double* G, long ld, int q, const double* Kinv, const double* KVK, const double* b, cudaStream_t st);
+// out = 0.5*(kap_a + kap_b)/nrm + extra   (null pointers count as 0)
+void col_weights(const double* kap_a, const double* kap_b, const double* extra, const double* nrm, int m,
+                 double* out, cudaStream_t st);
+
+// ---- Cholesky / triangular inverse (blocked, panel 64) --------------------------------------
+// In-place lower Cholesky of A (n x n, lower triangle referenced; the strict upper triangle is
+// clobbered). flags |= notpd/small bits.  The trailing update uses the DMMA GEMM.
+cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, cudaStream_t st);
+// X = L^{-1} (lower, strict upper zero). X must not alias L. tmp: scratch >= 64*ld doubles.
+cudaError_t tri_inverse_lower(const double* L, long ld, int n, double* X, double* tmp, cudaStream_t st);
+// scal[slot] = 2*sum log L_kk
+void logdet_from_chol(const double* L, long ld, int n, double* scal, int slot, cudaStream_t st);
+// scal[slot_mb] = m.b ; scal[slot_tr] = sum_ij V_ij Kinv_ji
+void kl_scalars(const double* m_b, const double* b, const double* V, long ldv, const double* Kinv, long ldk, int q,
+                double* scal, int slot_mb, int slot_tr, cudaStream_t st);
+
+// ---- final contraction with dC_k and result assembly -----------------------------------------
+// GC = sum_z GCpart[z] + GCextra ; gpart[blk*5 + k] = sum_ab GC_ab * dC_k,ab  (k: Amp, beta, rho, ex, ey)
+int contract_blocks(int p);
+void contract_dC(const double* GCpart, int nz, long zstride, const double* GCextra, const double* C, long ld, int p,
+                 const double* gx, const double* gy, const ThetaDev& th, double* gpart, cudaStream_t st);
+
+// out[0] loglik, [1] KL, [2..7] d(loglik-KL)/d(sigma_0, eps_0x, eps_0y, -2log2beta, -log2rho2, Amp),
+// [8] flags, [9] p, [10] sum r, [11] sum f, [12] sum r*lam_m, [13] logdet K_tilde_b, [14] logdet V_b, [15] 0
+void finalize(const double* scal, const int* flags, double A, double lambda0, const ThetaDev& th, int p,
+              double logdetV_override, int use_override, double* out, cudaStream_t st);
+
+
+// ---- E-step / f-param helpers -------------------------------------------------------------------
+// lam_m = sum_t part2 ; lam_var = Kvec + sum_t part1 - rowdot(K_b, a)        (utils.py:1090-1101)
+void moments_combine(const double* Kvec, const double* part1, const double* part2, long ldpart, int nparts,
+                     const double* a, long lda, const double* K_b, long ldk, long n, int q, double* lam_m,
+                     double* lam_var, cudaStream_t st);
+// one streaming pass over (lam_m, lam_var, r): blockpart[blk*8 + {0..5}] =
+//   sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, sum exp(A lam_m + A^2 lam_var/2), nan-count
+int fparam_blocks(long n);
+void fparam_pass(const double* lam_m, const double* lam_var, const double* r, long n, double A, double lambda0,
+                 double* f, double* blockpart, cudaStream_t st);
+// colpart[blk][j] = sum_{i in blk} a_ij (r_i - f_i)
+int colsum_blocks(long n);
+void colsum_weighted(const double* a, long lda, long n, int q, const double* r, const double* f, double* colpart,
+                     long ldcol, cudaStream_t st);
+void scale_vec(double* x, long n, double alpha, cudaStream_t st);
+
+}  // namespace sgp

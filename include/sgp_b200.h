@@ -1,0 +1,143 @@
+/* sgp_b200.h -- C ABI of the B200-native Spatial_GP ELBO+gradient hot path.
+ *
+ * The reference (retinal-information-processing-lab/gaussian_processes, Spatial_GP_repo/utils.py) has no
+ * FFI of its own: its boundary is the set of module-level Python callables the notebooks use (SURVEY.md
+ * 8b).  This header is what a `utils`-compatible Python module binds through ctypes
+ * (gaussian_processes_b200/utils.py does exactly that; INTEGRATION.md shows the stub).  Each entry point
+ * cites the reference callable (utils.py line range) whose tensor work it replaces.
+ *
+ * Conventions
+ *   - every function returns an int status (SGP_OK == 0); sgp_last_error(h) gives the message;
+ *   - all matrices are fp64, row-major, caller-allocated DEVICE memory unless the name ends in _host;
+ *   - `ld*` are leading dimensions in elements; `stream` is a cudaStream_t passed as void*;
+ *   - the library never owns user-visible memory; the handle owns scratch workspace only;
+ *   - theta is 6 doubles in the reference's dict order (utils.py:824):
+ *        [sigma_0, eps_0x, eps_0y, -2log2beta, -log2rho2, Amp];
+ *   - there is no CPU fallback: without a CUDA device every compute call returns SGP_E_CUDA.
+ */
+#ifndef SGP_B200_H_
+#define SGP_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define SGP_API __attribute__((visibility("default")))
+#else
+#define SGP_API
+#endif
+
+typedef struct sgp_handle sgp_handle;
+
+enum {
+  SGP_OK = 0,
+  SGP_E_CUDA = 1,        /* CUDA runtime error (message has the cudaError string) */
+  SGP_E_ARG = 2,         /* bad argument (null pointer, odd leading dimension, m too large, ...) */
+  SGP_E_BOUNDS = 3,      /* theta outside [lo, hi]: reference raises ValueError (utils.py:865-867) */
+  SGP_E_UNSUPPORTED = 4, /* configuration not implemented on the device path */
+  SGP_E_NOMEM = 5
+};
+
+/* status bits returned in out[8] of sgp_elbo_grad and by the factorisation helpers */
+enum {
+  SGP_FLAG_KT_NOT_PD = 1,      /* K_tilde_b not positive definite (log_det takes the eigh fallback, utils.py:1279) */
+  SGP_FLAG_KT_SMALL_PIVOT = 2, /* Cholesky pivot < 1e-10 (safe_log raises, utils.py:670) */
+  SGP_FLAG_V_NOT_PD = 4,
+  SGP_FLAG_V_SMALL_PIVOT = 8,
+  SGP_FLAG_NAN = 16            /* NaN in the mean rate f (utils.py:1923) */
+};
+
+SGP_API int sgp_version(void);
+SGP_API int sgp_create(int device, sgp_handle** out);
+SGP_API int sgp_destroy(sgp_handle* h);
+SGP_API const char* sgp_last_error(const sgp_handle* h);
+/* rows of the image pass processed per slab (bounds the scratch memory); 0 = default (65536) */
+SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
+/* forget the cached masked copies of X / xtilde (call if their contents changed in place) */
+SGP_API int sgp_invalidate_cache(sgp_handle* h);
+/* number of kernels this library has launched through `h` since creation / last reset */
+SGP_API long sgp_launch_count(const sgp_handle* h, int reset);
+
+/* ---- a1: localker(theta, hi, lo, n_px_side, grad)  utils.py:861-914 ---------------------------------------
+ * sgp_mask_host: RF mask alpha >= 1e-3 on the n_px x n_px grid (HOST output, n_px^2 bytes) and p = mask.sum().
+ * sgp_localker : C (p x p, ld = ldc >= p) and optionally dC (5 matrices, consecutive, each ldc*p.. see dc_stride)
+ *                in the reference's dict order Amp, -2log2beta, -log2rho2, eps_0x, eps_0y (utils.py:910).     */
+SGP_API int sgp_mask_host(const double* theta_host, int n_px, uint8_t* mask_host, int* p_out);
+SGP_API int sgp_localker(sgp_handle* h, const double* theta_host, int n_px, double* C, long ldc, double* dC, long dc_stride,
+                 void* stream);
+
+/* ---- a2: acosker(theta, x1, x2, C, dC=None, diag=False)  utils.py:975-1025 ---------------------------------
+ * x1 (n1 x p, ld1), x2 (n2 x p, ld2) are the MASKED images; K (n1 x n2, ldk).  symmetrize != 0 applies
+ * K = (K + K^T)/2 (the reference does so whenever n1 == n2).                                                   */
+SGP_API int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double* x2, long n2, long ld2, int p,
+                const double* C, long ldc, double sigma_0, double* K, long ldk, int symmetrize, void* stream);
+/* ---- a3: acosker(theta, x1, x2=None, C, diag=True)  utils.py:1027-1030 : Kvec_i = x_i^T C x_i + sigma_0^2     */
+SGP_API int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, const double* C, long ldc,
+                     double sigma_0, double* Kvec, void* stream);
+
+/* ---- a5: lambda_moments(x, K_tilde, KKtilde_inv, Kvec, K, C, m, V, theta)  utils.py:1089-1101 -----------------
+ * lam_m = a m ; lam_var = Kvec + rowsum(a o (a V^T) - K_b o a).  a, K_b: N x q (lda, ldk).                      */
+SGP_API int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K_b, long ldk, const double* Kvec,
+                       long N, int q, const double* m_b, const double* V_b, long ldv, double* lam_m,
+                       double* lam_var, void* stream);
+
+/* ---- a6-a8: mean_f_given_lambda_moments / compute_loglikelihood(f-param mode) / lambda0_given_logA -------------
+ * One streaming pass over (lam_m, lam_var, r)  (utils.py:1138, 1243, 1253-1255, 1220-1227).
+ * out_host[8] = { loglik, dloglik/dlogA, dloglik/dlambda0, lambda0_closed_form, sum r, sum f, sum r*lam_m,
+ *                 nan_count };  f (N, nullable) receives the mean rate.                                         */
+SGP_API int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, const double* r, long N, double logA,
+                    double lambda0, double* f, double* out_host, void* stream);
+
+/* ---- a10: Estep(r, KKtilde_inv, m, f_params, f_mean, K_tilde, ...)  utils.py:1420-1422 ------------------------
+ * g = A a^T (r - f) (q) ; G = A^2 a^T diag(f) a (q x q, ldg).                                                   */
+SGP_API int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, const double* f, long N, int q,
+                    double logA, double* g, double* G, long ldg, void* stream);
+
+/* ---- small dense algebra on the q x q state (north_star item 2) -----------------------------------------------
+ * In-place lower Cholesky (strict upper triangle clobbered) ; X = L^{-1} ; flags_host receives SGP_FLAG_KT_* bits. */
+SGP_API int sgp_cholesky(sgp_handle* h, double* A, long ld, int n, int* flags_host, void* stream);
+SGP_API int sgp_spd_inverse(sgp_handle* h, const double* A, long lda, int n, double* Ainv, long ldi, double* logdet_host,
+                    int* flags_host, void* stream);
+
+/* ---- generic fp64 tensor-core GEMM (exposed for tests and for the roofline measurement) -----------------------
+ * C[M x N] = alpha * A * B^T-style contraction with selectable operand layouts:
+ *   a_layout / b_layout = 0 : element (row, k) at ptr[row*ld + k] ; = 1 : at ptr[k*ld + row].                  */
+SGP_API int sgp_gemm_f64(sgp_handle* h, int a_layout, int b_layout, const double* A, long lda, const double* B, long ldb,
+                 double* C, long ldc, int M, int N, int K, double alpha, int accumulate, int small_tile,
+                 void* stream);
+
+/* ---- a11: the M-step closure body of varGP (utils.py:2030-2099) as ONE call -----------------------------------
+ * theta -> loglik, KL and d(loglik - KL)/dtheta, with X, xtilde, r, B, m_b, V_b, f_params fixed.
+ *   X (N x n_px^2, ldx), r (N), xtilde (m x n_px^2, ldu), B (m x q, ldb), m_b (q), V_b (q x q, ldv).
+ *   lo_host / hi_host: theta limits (6 each, may be NULL = no check) -> SGP_E_BOUNDS (closure returns +inf, U:2021-2028).
+ *   logdetV_host: pointer to a precomputed log det V_b, or NULL to compute it here.
+ *   lam_m / lam_var / f: optional device outputs (N each).
+ *   out_host[16] = { loglik, KL, g_sigma_0, g_eps_0x, g_eps_0y, g_-2log2beta, g_-log2rho2, g_Amp,
+ *                    flags, p, sum r, sum f, sum r*lam_m, logdet K_tilde_b, logdet V_b, 0 }
+ *   with g_k = d(loglik - KL)/dtheta_k (the closure hands -g_k to LBFGS, U:2099).
+ * The call synchronises `stream` before returning (the caller needs the loss as a host float).                  */
+SGP_API int sgp_elbo_grad(sgp_handle* h, const double* X, long ldx, const double* r, long N, const double* xtilde, long ldu,
+                  int m, int n_px, const double* theta_host, const double* lo_host, const double* hi_host,
+                  const double* B, long ldb, int q, const double* m_b, const double* V_b, long ldv, double logA,
+                  double lambda0, const double* logdetV_host, double* lam_m, double* lam_var, double* f,
+                  double* out_host, void* stream);
+
+/* Same evaluation with X / r in HOST memory (pinned or pageable): the images are streamed to the device slab by
+ * slab on a copy stream that overlaps the compute stream.  Used for the end-to-end measurement.                  */
+SGP_API int sgp_elbo_grad_host(sgp_handle* h, const double* X_host, long ldx, const double* r_host, long N,
+                       const double* xtilde_host, long ldu, int m, int n_px, const double* theta_host,
+                       const double* B_host, long ldb, int q, const double* m_b_host, const double* V_b_host,
+                       long ldv, double logA, double lambda0, double* out_host);
+
+/* ---- debugging aid for parity tests: copy a named intermediate of the last sgp_elbo_grad call ---------------
+ * names: C Kt Ktb Kinv Mfull GKt GCU Sig2 bb y beta X2 ...   dst: device, capacity in elements.                */
+SGP_API int sgp_debug_get(sgp_handle* h, const char* name, double* dst, long capacity, long* rows, long* cols, long* ld);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SGP_B200_H_ */
