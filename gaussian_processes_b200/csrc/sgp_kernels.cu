@@ -42,7 +42,7 @@ __global__ void build_C_kernel(double* __restrict__ C, long ldc, int p, const do
       d[4] = 2.0 * th.eb * c * (yi + yj - 2 * th.ey);      // eps_0y     U:905
     }
   }
-  if (i < ldc) {
+  if (i < p) {
     C[(long)i * ldc + j] = c;
     if (dC) {
 #pragma unroll
@@ -53,7 +53,7 @@ __global__ void build_C_kernel(double* __restrict__ C, long ldc, int p, const do
 
 void build_C(double* C, long ldc, int p, const double* gx, const double* gy, const ThetaDev& th, double* dC,
              long dcs, cudaStream_t st) {
-  dim3 grid(cdiv(ldc, 128), (unsigned)ldc);
+  dim3 grid(cdiv(ldc, 128), (unsigned)p);   // p rows x ldc columns (column padding zeroed)
   note_launch(); build_C_kernel<<<grid, 128, 0, st>>>(C, ldc, p, gx, gy, th, dC, dcs);
 }
 

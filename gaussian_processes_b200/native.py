@@ -1,0 +1,258 @@
+"""Thin torch-tensor front end of the C ABI (include/sgp_b200.h).
+
+Every function takes CUDA fp64 tensors, passes ``data_ptr()`` + the current CUDA stream to
+libsgp_b200.so and returns fresh torch tensors.  CPU tensors raise: there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import lib
+
+THETA_KEYS = ("sigma_0", "eps_0x", "eps_0y", "-2log2beta", "-log2rho2", "Amp")   # utils.py:824
+DC_KEYS = ("Amp", "-2log2beta", "-log2rho2", "eps_0x", "eps_0y")                  # utils.py:910
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("gaussian_processes_b200: CUDA tensors required (no CPU fallback on this path)")
+        if t.dtype != torch.float64:
+            raise TypeError("gaussian_processes_b200: fp64 tensors required")
+
+
+def _c(t: torch.Tensor) -> torch.Tensor:
+    """row-major view with unit inner stride (copy only if needed)"""
+    if t.dim() == 2 and t.stride(1) == 1 and t.stride(0) >= t.shape[1]:
+        return t
+    return t.contiguous()
+
+
+def _ld(t: torch.Tensor) -> int:
+    return t.stride(0) if t.dim() == 2 else t.shape[-1]
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _stream(dev) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def _h(t: torch.Tensor) -> _lib.Handle:
+    return _lib.handle_for(t.device.index if t.device.index is not None else torch.cuda.current_device())
+
+
+def theta_array(theta) -> "C.Array":
+    vals = [float(theta[k]) for k in THETA_KEYS] if isinstance(theta, dict) else [float(v) for v in theta]
+    return (C.c_double * 6)(*vals)
+
+
+def mask_host(theta, n_px: int) -> torch.Tensor:
+    """RF mask of localker (utils.py:880-883) as a CPU bool tensor; pure host arithmetic."""
+    buf = (C.c_uint8 * (n_px * n_px))()
+    p = C.c_int(0)
+    rc = lib.sgp_mask_host(theta_array(theta), int(n_px), buf, C.byref(p))
+    if rc != _lib.SGP_OK:
+        raise _lib.SgpError(rc, "sgp_mask_host")
+    return torch.frombuffer(bytearray(buf), dtype=torch.uint8).bool()
+
+
+def localker(theta, n_px: int, device, grad: bool = False):
+    mask = mask_host(theta, n_px)
+    p = int(mask.sum())
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError("gaussian_processes_b200: CUDA device required (no CPU fallback on this path)")
+    Cm = torch.empty((p, p), dtype=torch.float64, device=dev)
+    dC = torch.empty((5, p, p), dtype=torch.float64, device=dev) if grad else None
+    h = _h(Cm)
+    h.check(lib.sgp_localker(h.ptr, theta_array(theta), int(n_px), _ptr(Cm), p, _ptr(dC), p * p, _stream(dev)))
+    return (Cm, mask.to(dev), dC) if grad else (Cm, mask.to(dev))
+
+
+def acosker(sigma_0: float, x1: torch.Tensor, x2: torch.Tensor, Cm: torch.Tensor, symmetrize: bool) -> torch.Tensor:
+    _need_cuda(x1, x2, Cm)
+    x1, x2, Cm = _c(x1), _c(x2), _c(Cm)
+    n1, p = x1.shape
+    n2 = x2.shape[0]
+    K = torch.empty((n1, n2), dtype=torch.float64, device=x1.device)
+    h = _h(x1)
+    h.check(lib.sgp_acosker(h.ptr, _ptr(x1), n1, _ld(x1), _ptr(x2), n2, _ld(x2), int(p), _ptr(Cm), _ld(Cm),
+                            float(sigma_0), _ptr(K), n2, 1 if symmetrize else 0, _stream(x1.device)))
+    return K
+
+
+def acosker_diag(sigma_0: float, x1: torch.Tensor, Cm: torch.Tensor) -> torch.Tensor:
+    _need_cuda(x1, Cm)
+    x1, Cm = _c(x1), _c(Cm)
+    n1, p = x1.shape
+    Kvec = torch.empty((n1,), dtype=torch.float64, device=x1.device)
+    h = _h(x1)
+    h.check(lib.sgp_acosker_diag(h.ptr, _ptr(x1), n1, _ld(x1), int(p), _ptr(Cm), _ld(Cm), float(sigma_0),
+                                 _ptr(Kvec), _stream(x1.device)))
+    return Kvec
+
+
+def lambda_moments(a: torch.Tensor, K_b: torch.Tensor, Kvec: torch.Tensor, m_b: torch.Tensor, V_b: torch.Tensor):
+    _need_cuda(a, K_b, Kvec, m_b, V_b)
+    a, K_b, V_b = _c(a), _c(K_b), _c(V_b)
+    Kvec, m_b = Kvec.contiguous(), m_b.contiguous()
+    N, q = a.shape
+    lam_m = torch.empty((N,), dtype=torch.float64, device=a.device)
+    lam_var = torch.empty_like(lam_m)
+    h = _h(a)
+    h.check(lib.sgp_lambda_moments(h.ptr, _ptr(a), _ld(a), _ptr(K_b), _ld(K_b), _ptr(Kvec), N, int(q), _ptr(m_b),
+                                   _ptr(V_b), _ld(V_b), _ptr(lam_m), _ptr(lam_var), _stream(a.device)))
+    return lam_m, lam_var
+
+
+def fparam_eval(lam_m: torch.Tensor, lam_var: torch.Tensor, r: torch.Tensor, logA: float, lambda0: float,
+                want_f: bool = True):
+    """One streaming pass: dict(loglik, dlogA, dlambda0, lambda0_closed, sum_r, sum_f, r_lam, nan) and f."""
+    _need_cuda(lam_m, lam_var, r)
+    lam_m, lam_var, r = lam_m.contiguous(), lam_var.contiguous(), r.contiguous()
+    N = lam_m.shape[0]
+    f = torch.empty_like(lam_m) if want_f else None
+    out = (C.c_double * 8)()
+    h = _h(lam_m)
+    h.check(lib.sgp_fparam_eval(h.ptr, _ptr(lam_m), _ptr(lam_var), _ptr(r), N, float(logA), float(lambda0), _ptr(f),
+                                out, _stream(lam_m.device)))
+    keys = ("loglik", "dlogA", "dlambda0", "lambda0_closed", "sum_r", "sum_f", "r_lam", "nan")
+    return dict(zip(keys, list(out))), f
+
+
+def estep_terms(a: torch.Tensor, r: torch.Tensor, f: torch.Tensor, logA: float):
+    _need_cuda(a, r, f)
+    a, r, f = _c(a), r.contiguous(), f.contiguous()
+    N, q = a.shape
+    g = torch.empty((q,), dtype=torch.float64, device=a.device)
+    G = torch.empty((q, q), dtype=torch.float64, device=a.device)
+    h = _h(a)
+    h.check(lib.sgp_estep_terms(h.ptr, _ptr(a), _ld(a), _ptr(r), _ptr(f), N, int(q), float(logA), _ptr(g), _ptr(G),
+                                q, _stream(a.device)))
+    return g, G
+
+
+def cholesky(A: torch.Tensor):
+    """Lower Cholesky factor (new tensor) and status flags."""
+    _need_cuda(A)
+    n = A.shape[0]
+    ld = (n + 1) // 2 * 2
+    W = torch.zeros((n, ld), dtype=torch.float64, device=A.device)
+    W[:, :n] = A
+    fl = C.c_int(0)
+    h = _h(A)
+    h.check(lib.sgp_cholesky(h.ptr, _ptr(W), ld, int(n), C.byref(fl), _stream(A.device)))
+    return torch.tril(W[:, :n]), int(fl.value)
+
+
+def spd_inverse(A: torch.Tensor):
+    """(A^-1, logdet A, flags) through the blocked Cholesky + triangular inverse kernels."""
+    _need_cuda(A)
+    A = _c(A)
+    n = A.shape[0]
+    Ainv = torch.empty((n, n), dtype=torch.float64, device=A.device)
+    ld_, fl = C.c_double(0.0), C.c_int(0)
+    h = _h(A)
+    h.check(lib.sgp_spd_inverse(h.ptr, _ptr(A), _ld(A), int(n), _ptr(Ainv), n, C.byref(ld_), C.byref(fl),
+                                _stream(A.device)))
+    return Ainv, float(ld_.value), int(fl.value)
+
+
+def gemm_f64(A: torch.Tensor, B: torch.Tensor, a_layout: int = 0, b_layout: int = 0, alpha: float = 1.0,
+             out: Optional[torch.Tensor] = None, accumulate: bool = False, small_tile: bool = False):
+    """C[M,N] = alpha * sum_k A(m,k) B(n,k); layout 0: tensor is [rows, K]; layout 1: tensor is [K, rows]."""
+    _need_cuda(A, B)
+    A, B = _c(A), _c(B)
+    M, K = (A.shape if a_layout == 0 else (A.shape[1], A.shape[0]))
+    N = B.shape[0] if b_layout == 0 else B.shape[1]
+    ldc = (N + 1) // 2 * 2
+    if out is None:
+        out = torch.zeros((M, ldc), dtype=torch.float64, device=A.device)
+    h = _h(A)
+    h.check(lib.sgp_gemm_f64(h.ptr, int(a_layout), int(b_layout), _ptr(A), _ld(A), _ptr(B), _ld(B), _ptr(out),
+                             _ld(out), int(M), int(N), int(K), float(alpha), 1 if accumulate else 0,
+                             1 if small_tile else 0, _stream(A.device)))
+    return out[:, :N]
+
+
+OUT_KEYS = ("loglik", "KL", "g_sigma_0", "g_eps_0x", "g_eps_0y", "g_-2log2beta", "g_-log2rho2", "g_Amp",
+            "flags", "p", "sum_r", "sum_f", "r_lam", "logdetK", "logdetV", "_")
+
+
+def elbo_grad(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
+              m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float, lims=None,
+              logdetV: Optional[float] = None, want_moments: bool = False) -> Dict:
+    """Fused M-step closure body (utils.py:2030-2099): one C call, one 16-double read-back."""
+    _need_cuda(X, r, xtilde, B, m_b, V_b)
+    X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
+    r, m_b = r.contiguous(), m_b.contiguous()
+    N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]
+    lam_m = lam_var = f = None
+    if want_moments:
+        lam_m = torch.empty((N,), dtype=torch.float64, device=X.device)
+        lam_var, f = torch.empty_like(lam_m), torch.empty_like(lam_m)
+    lo = hi = None
+    if lims is not None:
+        lo = (C.c_double * 6)(*[float(lims[0][k]) for k in THETA_KEYS])
+        hi = (C.c_double * 6)(*[float(lims[1][k]) for k in THETA_KEYS])
+    ldv_val = C.c_double(logdetV if logdetV is not None else 0.0)
+    out = (C.c_double * 16)()
+    h = _h(X)
+    h.check(lib.sgp_elbo_grad(h.ptr, _ptr(X), _ld(X), _ptr(r), N, _ptr(xtilde), _ld(xtilde), int(m), int(n_px),
+                              theta_array(theta), lo, hi, _ptr(B), _ld(B), int(q), _ptr(m_b), _ptr(V_b), _ld(V_b),
+                              float(logA), float(lambda0), C.byref(ldv_val) if logdetV is not None else None,
+                              _ptr(lam_m), _ptr(lam_var), _ptr(f), out, _stream(X.device)))
+    res = dict(zip(OUT_KEYS, list(out)))
+    res["grad"] = {k: res["g_" + k] for k in THETA_KEYS}
+    res["flags"] = int(res["flags"])
+    res["p"] = int(res["p"])
+    if want_moments:
+        res.update(lam_m=lam_m, lam_var=lam_var, f=f)
+    return res
+
+
+def elbo_grad_host(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
+                   m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float, device: int = 0) -> Dict:
+    """Same evaluation with every operand in HOST memory (pinned preferred); H2D streamed slab by slab."""
+    for t in (X, r, xtilde, B, m_b, V_b):
+        if t.is_cuda or t.dtype != torch.float64:
+            raise TypeError("elbo_grad_host expects CPU fp64 tensors")
+    X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
+    r, m_b = r.contiguous(), m_b.contiguous()
+    N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]
+    out = (C.c_double * 16)()
+    h = _lib.handle_for(device)
+    h.check(lib.sgp_elbo_grad_host(h.ptr, _ptr(X), _ld(X), _ptr(r), N, _ptr(xtilde), _ld(xtilde), int(m), int(n_px),
+                                   theta_array(theta), _ptr(B), _ld(B), int(q), _ptr(m_b), _ptr(V_b), _ld(V_b),
+                                   float(logA), float(lambda0), out))
+    res = dict(zip(OUT_KEYS, list(out)))
+    res["grad"] = {k: res["g_" + k] for k in THETA_KEYS}
+    res["flags"] = int(res["flags"])
+    return res
+
+
+def debug_get(device, name: str) -> torch.Tensor:
+    h = _lib.handle_for(device.index if isinstance(device, torch.device) else int(device))
+    rows, cols, ld = C.c_long(0), C.c_long(0), C.c_long(0)
+    h.check(lib.sgp_debug_get(h.ptr, name.encode(), None, 0, C.byref(rows), C.byref(cols), C.byref(ld)))
+    buf = torch.empty((rows.value, ld.value), dtype=torch.float64, device=f"cuda:{h.device}")
+    h.check(lib.sgp_debug_get(h.ptr, name.encode(), _ptr(buf), buf.numel(), None, None, None))
+    return buf[:, :cols.value]
+
+
+def set_slab_rows(device: int, rows: int):
+    h = _lib.handle_for(device)
+    h.check(lib.sgp_set_slab_rows(h.ptr, int(rows)))
+
+
+def launch_count(device: int = 0, reset: bool = False) -> int:
+    return _lib.handle_for(device).launch_count(reset)

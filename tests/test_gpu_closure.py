@@ -1,0 +1,86 @@
+"""GPU: the fused M-step closure (sgp_elbo_grad) against fixtures produced by the real reference."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import case_inputs, load
+
+pytestmark = pytest.mark.gpu
+CASES = ["closure_dense_n8", "closure_local_n12", "closure_rankdef_n10", "closure_c1_dense", "closure_c1_local"]
+RTOL = 1e-9   # north_star: 1e-9 relative in fp64
+
+
+def run_case(name, slab=None):
+    from gaussian_processes_b200 import native
+    fx = load(name)
+    prob, st = case_inputs(fx)
+    d = torch.device("cuda:0")
+    native.set_slab_rows(0, slab if slab else 0)
+    out = native.elbo_grad(prob.X.to(d), prob.r.to(d), prob.xtilde.to(d), prob.n_px_side, prob.theta,
+                           st["B"].to(d), st["m_b"].to(d), st["V_b"].to(d), st["logA"], st["lambda0"],
+                           want_moments=True)
+    native.set_slab_rows(0, 0)
+    return fx, out
+
+
+def check(fx, out):
+    assert out["flags"] == 0
+    assert out["p"] == int(fx["p"])
+    assert abs(out["loglik"] - float(fx["loglik"])) <= RTOL * abs(float(fx["loglik"]))
+    assert abs(out["KL"] - float(fx["KL"])) <= RTOL * abs(float(fx["KL"]))
+    keys = [str(k) for k in fx["theta_keys"]]
+    ref = fx["dloglik"] - fx["dKL"]
+    got = np.array([out["grad"][k] for k in keys])
+    scale = max(np.abs(fx["dloglik"]).max(), np.abs(fx["dKL"]).max())
+    assert np.abs(got - ref).max() <= RTOL * scale, (got, ref)
+    assert np.allclose(out["lam_m"].cpu().numpy(), fx["lam_m"], rtol=RTOL, atol=1e-12)
+    assert np.allclose(out["lam_var"].cpu().numpy(), fx["lam_var"], rtol=RTOL, atol=1e-10)
+    assert np.allclose(out["f"].cpu().numpy(), fx["f"], rtol=RTOL, atol=0)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_closure_against_reference(name):
+    fx, out = run_case(name)
+    check(fx, out)
+
+
+@pytest.mark.parametrize("name", ["closure_c1_dense", "closure_local_n12"])
+def test_closure_multi_slab(name):
+    # ragged slabs: N is not a multiple of the slab
+    fx, out = run_case(name, slab=128)
+    check(fx, out)
+
+
+def test_closure_repeatable_and_cached():
+    fx, a = run_case("closure_c1_local")
+    _, b = run_case("closure_c1_local")
+    assert a["loglik"] == b["loglik"] and a["grad"] == b["grad"]   # deterministic reductions
+
+
+def test_closure_bounds_error():
+    from gaussian_processes_b200 import native, synth, _lib
+    fx = load("closure_dense_n8")
+    prob, st = case_inputs(fx)
+    d = torch.device("cuda:0")
+    th = dict(prob.theta)
+    th["eps_0x"] = 1.5
+    with pytest.raises(_lib.SgpError) as e:
+        native.elbo_grad(prob.X.to(d), prob.r.to(d), prob.xtilde.to(d), prob.n_px_side, th, st["B"].to(d),
+                         st["m_b"].to(d), st["V_b"].to(d), st["logA"], st["lambda0"],
+                         lims=(synth.THETA_LIMS_LO, synth.THETA_LIMS_HI))
+    assert e.value.code == _lib.SGP_E_BOUNDS
+
+
+def test_closure_host_streaming_matches_device():
+    from gaussian_processes_b200 import native
+    fx = load("closure_c1_dense")
+    prob, st = case_inputs(fx)
+    native.set_slab_rows(0, 512)
+    out = native.elbo_grad_host(prob.X.pin_memory(), prob.r, prob.xtilde, prob.n_px_side, prob.theta, st["B"],
+                                st["m_b"], st["V_b"], st["logA"], st["lambda0"])
+    native.set_slab_rows(0, 0)
+    assert abs(out["loglik"] - float(fx["loglik"])) <= RTOL * abs(float(fx["loglik"]))
+    keys = [str(k) for k in fx["theta_keys"]]
+    ref = fx["dloglik"] - fx["dKL"]
+    got = np.array([out["grad"][k] for k in keys])
+    assert np.abs(got - ref).max() <= RTOL * np.abs(ref).max()

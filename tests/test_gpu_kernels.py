@@ -1,0 +1,133 @@
+"""GPU: the DMMA GEMM family, the blocked Cholesky / inverse and the function-level entry points,
+each against a plain torch fp64 computation of the same op (kernel-level numerics) and against
+fixtures produced by the real reference (function-level parity).  All calls go through the C ABI."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import case_inputs, load, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from gaussian_processes_b200 import native
+    return native
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+@pytest.mark.parametrize("small", [False, True])
+@pytest.mark.parametrize("al,bl", [(0, 0), (0, 1), (1, 0), (1, 1)])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 16), (130, 70, 37), (257, 129, 200), (64, 400, 1000), (1, 1, 1),
+                                   (300, 300, 3)])
+def test_gemm_layouts(nat, small, al, bl, M, N, K):
+    g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K)
+    A = torch.randn(M, K, generator=g, dtype=torch.float64)
+    B = torch.randn(N, K, generator=g, dtype=torch.float64)
+    ref = A @ B.T
+
+    def pad(t):  # even leading dimension, as the ABI requires
+        r, c = t.shape
+        w = torch.zeros(r, c + (c & 1), dtype=torch.float64)
+        w[:, :c] = t
+        return w.to(dev())[:, :c]
+    Ad = pad(A if al == 0 else A.T.contiguous())
+    Bd = pad(B if bl == 0 else B.T.contiguous())
+    out = nat.gemm_f64(Ad, Bd, al, bl, alpha=1.0, small_tile=small)
+    torch.cuda.synchronize()
+    err = (out.cpu() - ref).abs().max().item()
+    assert err < 1e-11 * max(1.0, K ** 0.5) * 10, err
+
+
+def test_gemm_alpha_accumulate(nat):
+    g = torch.Generator(device="cpu").manual_seed(5)
+    A = torch.randn(200, 64, generator=g, dtype=torch.float64).to(dev())
+    B = torch.randn(150, 64, generator=g, dtype=torch.float64).to(dev())
+    C0 = torch.randn(200, 150, generator=g, dtype=torch.float64).to(dev())
+    out = C0.clone()
+    nat.gemm_f64(A, B, 0, 0, alpha=-1.0, out=out, accumulate=True, small_tile=True)
+    assert (out - (C0 - A @ B.T)).abs().max().item() < 1e-11
+
+
+@pytest.mark.parametrize("n", [1, 5, 64, 65, 100, 257, 500])
+def test_cholesky_and_spd_inverse(nat, n):
+    g = torch.Generator(device="cpu").manual_seed(n)
+    W = torch.randn(n, n + 3, generator=g, dtype=torch.float64)
+    A = (W @ W.T + 0.5 * torch.eye(n, dtype=torch.float64))
+    Ad = A.to(dev())
+    L, fl = nat.cholesky(Ad)
+    assert fl == 0
+    Lref = torch.linalg.cholesky(A)
+    assert (L.cpu() - Lref).abs().max().item() < 1e-10 * Lref.abs().max().item()
+    Ainv, logdet, fl = nat.spd_inverse(Ad)
+    assert fl == 0
+    ref = torch.linalg.inv(A)
+    assert (Ainv.cpu() - ref).abs().max().item() < 1e-9 * ref.abs().max().item()
+    assert abs(logdet - torch.logdet(A).item()) < 1e-10 * max(1.0, abs(torch.logdet(A).item()))
+
+
+def test_cholesky_flags_indefinite(nat):
+    A = torch.eye(70, dtype=torch.float64)
+    A[40, 40] = -1.0
+    _, fl = nat.cholesky(A.to(dev()))
+    assert fl & 1
+
+
+@pytest.mark.parametrize("name", ["closure_dense_n8", "closure_local_n12"])
+def test_localker_acosker_against_reference(nat, name):
+    fx = load(name)
+    prob, st = case_inputs(fx)
+    n = prob.n_px_side
+    C, mask, dC = nat.localker(prob.theta, n, dev(), grad=True)
+    assert np.array_equal(mask.cpu().numpy(), fx["mask"])
+    assert rel_err(C.cpu().numpy(), fx["C"]) < 1e-13
+    for i, k in enumerate([str(s) for s in fx["dC_keys"]]):
+        j = nat.DC_KEYS.index(k)
+        assert rel_err(dC[j].cpu().numpy(), fx["dC"][i]) < 1e-12, k
+    mk = mask.cpu()
+    xm = prob.X[:, mk].to(dev())
+    um = prob.xtilde[:, mk].to(dev())
+    s0 = prob.theta["sigma_0"]
+    K = nat.acosker(s0, xm, um, C, False)
+    Kt = nat.acosker(s0, um, um, C, True)
+    Kvec = nat.acosker_diag(s0, xm, C)
+    assert rel_err(K.cpu().numpy(), fx["K"]) < 1e-11
+    assert rel_err(Kt.cpu().numpy(), fx["K_tilde"]) < 1e-11
+    assert rel_err(Kvec.cpu().numpy(), fx["Kvec"]) < 1e-12
+
+
+@pytest.mark.parametrize("name", ["closure_dense_n8", "closure_local_n12", "closure_rankdef_n10", "closure_c1_dense"])
+def test_moments_estep_fparams_against_reference(nat, name):
+    import oracle.spatial_gp_oracle as orc
+    fx = load(name)
+    prob, st = case_inputs(fx)
+    # rebuild a / K_b on the CPU with the oracle (inputs of the functions under test)
+    C, mask = orc.build_C(prob.theta, prob.n_px_side)
+    xm, um = prob.X[:, mask], prob.xtilde[:, mask]
+    Kt = orc.arccos_kernel(prob.theta, um, um, C)
+    K = orc.arccos_kernel(prob.theta, xm, um, C)
+    B = st["B"]
+    Kt_b = B.T @ Kt @ B
+    Kt_b = 0.5 * (Kt_b + Kt_b.T)
+    Kinv = torch.linalg.solve(Kt_b, torch.eye(Kt_b.shape[0], dtype=torch.float64))
+    K_b = K @ B
+    a = K_b @ Kinv
+    Kvec = orc.arccos_kernel_diag(prob.theta, xm, C)
+    d = dev()
+    lam_m, lam_var = nat.lambda_moments(a.to(d), K_b.to(d), Kvec.to(d), st["m_b"].to(d), st["V_b"].to(d))
+    assert np.allclose(lam_m.cpu().numpy(), fx["lam_m"], rtol=1e-9, atol=1e-12)
+    assert np.allclose(lam_var.cpu().numpy(), fx["lam_var"], rtol=1e-9, atol=1e-10)
+    res, f = nat.fparam_eval(torch.from_numpy(fx["lam_m"]).to(d), torch.from_numpy(fx["lam_var"]).to(d),
+                             prob.r.to(d), st["logA"], st["lambda0"])
+    assert np.allclose(f.cpu().numpy(), fx["f"], rtol=1e-12)
+    assert abs(res["loglik"] - float(fx["fpar_loglik"])) <= 1e-11 * abs(float(fx["fpar_loglik"]))
+    assert abs(res["dlogA"] - float(fx["fpar_dlogA"])) <= 1e-10 * abs(float(fx["fpar_dlogA"]))
+    assert abs(res["dlambda0"] - float(fx["fpar_dlambda0"])) <= 1e-10 * max(1.0, abs(float(fx["fpar_dlambda0"])))
+    assert abs(res["lambda0_closed"] - float(fx["lambda0_closed"])) < 1e-12
+    g, G = nat.estep_terms(a.to(d), prob.r.to(d), torch.from_numpy(fx["f"]).to(d), st["logA"])
+    assert rel_err(g.cpu().numpy(), fx["estep_g"]) < 1e-9
+    assert rel_err(G.cpu().numpy(), fx["estep_G"]) < 1e-9
