@@ -1,0 +1,330 @@
+"""Benchmark of the Spatial_GP ELBO+gradient hot path (BASELINE.json metric: ELBO+grad evals/sec).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step = ONE evaluation of the M-step closure body (utils.py:2030-2099: theta -> loglik, KL, 6 gradients) over
+the whole image set.  Workload at N=1: BASELINE config 2 (40x40 images, N=100,000, m=500 inducing, dense theta,
+p=1600, q=m) -- override with SGP_BENCH_N / SGP_BENCH_NPX / SGP_BENCH_M.  With N>1 GPUs the images are sharded
+(100,000 per rank, weak scaling) and the 8 ELBO/gradient scalars are all-reduced over NCCL once per step.
+Prints ONE JSON line (see the keys at the bottom).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+from gaussian_processes_b200 import synth  # noqa: E402
+
+CFG = 2
+KEYS = synth.THETA_KEYS
+
+
+def workload():
+    return dict(N=int(os.environ.get("SGP_BENCH_N", 100000)), n=int(os.environ.get("SGP_BENCH_NPX", 40)),
+                m=int(os.environ.get("SGP_BENCH_M", 500)))
+
+
+def config_dict(w, world, extra=None):
+    c = {"workload": f"config2: single cell, {w['n']}x{w['n']} px, N={w['N']} images per GPU, m={w['m']} inducing, "
+                     f"dense theta (p={w['n'] ** 2}), fp64, one ELBO+grad closure evaluation per step",
+         "images_per_gpu": w["N"], "n_px_side": w["n"], "m": w["m"], "gpus": world,
+         "sharding": "images" if world > 1 else "none",
+         "l2": "inputs (1.28 GB of images per GPU) are larger than the 126 MB L2; no flush needed"}
+    if extra:
+        c.update(extra)
+    return c
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU every 200 ms while the timed region runs."""
+
+    def __init__(self, index=0):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40,
+                     "sw_thermal_slowdown": 0x20, "hw_power_brake": 0x80}
+            while not self._stop_evt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    for k, b in names.items():
+                        if bits & b:
+                            self.reasons.add(k)
+                except Exception:
+                    pass
+                self._stop_evt.wait(0.2)
+        except Exception as e:  # pragma: no cover
+            self.reasons.add(f"sampler_error:{type(e).__name__}")
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        med = statistics.median(self.samples) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------ problem
+def build_state_cpu(prob, orc):
+    """B / m_b / V_b from the oracle on CPU (used by the reference arm and for the CPU baseline sample)."""
+    C, mask = orc.build_C(prob.theta, prob.n_px_side)
+    um = prob.xtilde[:, mask]
+    Kt = orc.arccos_kernel(prob.theta, um, um, C)
+    B, Kt_b, _ = orc.eig_projection(Kt)
+    m_b, V_b = synth.make_variational_state(Kt_b, CFG)
+    return B, m_b, V_b
+
+
+def cpu_eval_time(orc, prob, B, m_b, V_b, chunk, reps, warm=1):
+    """Seconds per oracle closure evaluation on the first `chunk` images (all host threads)."""
+    Xc, rc = prob.X[:chunk], prob.r[:chunk]
+    ts = []
+    for i in range(warm + reps):
+        t0 = time.perf_counter()
+        orc.elbo_and_grad(prob.theta, Xc, rc, prob.xtilde, prob.n_px_side, B, m_b, V_b, prob.logA, prob.lambda0)
+        if i >= warm:
+            ts.append(time.perf_counter() - t0)
+    return ts
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    """The reference's own algorithm on the host cores (oracle port: the Python reference cannot travel to the
+    GPU box).  Each step evaluates the closure on a bounded sample of the workload; the rate is scaled to N."""
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if rank != 0:
+        return
+    import oracle.spatial_gp_oracle as orc
+    w = workload()
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    chunk = int(os.environ.get("SGP_BENCH_CPU_CHUNK", min(2000, w["N"])))
+    prob = synth.make_problem(max(chunk, w["m"]), w["n"], w["m"], cfg=CFG, theta=synth.THETA_DENSE)
+    B, m_b, V_b = build_state_cpu(prob, orc)
+    ts = cpu_eval_time(orc, prob, B, m_b, V_b, chunk, reps=args.steps, warm=args.warmup)
+    t_step = sum(ts) / len(ts)
+    n_total = w["N"] * world
+    value = 1.0 / (t_step * n_total / chunk)
+    sample = (f"oracle port (torch CPU fp64, forward-mode as the reference) on the first {chunk} of {n_total} images, "
+              f"time scaled linearly to N (extrapolated)")
+    line = {"impl": "reference", "metric": "elbo_grad_evals_per_sec", "value": value, "unit": "evals/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / value,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config_dict(w, world),
+            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def measure_fp64_peak(dev):
+    """cuBLAS DGEMM 8192^3, best of 5 (the fp64 tensor-pipe denominator; MEASURED_PEAKS.json has none)."""
+    n = 8192
+    a = torch.randn(n, n, dtype=torch.float64, device=dev)
+    b = torch.randn(n, n, dtype=torch.float64, device=dev)
+    best = float("inf")
+    for i in range(7):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 2:
+            best = min(best, e0.elapsed_time(e1) * 1e-3)
+    del a, b
+    torch.cuda.empty_cache()
+    return 2 * n ** 3 / best / 1e12
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from gaussian_processes_b200 import native
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    w = workload()
+    N, n, m = w["N"], w["n"], w["m"]
+
+    # ---- synthetic inputs: rank k draws its own image shard; xtilde / state come from rank 0
+    prob = synth.make_problem(N, n, m, cfg=CFG + 100 * rank, theta=synth.THETA_DENSE)
+    Xh = prob.X.pin_memory()
+    rh = prob.r.pin_memory()
+    X, r = Xh.to(dev), rh.to(dev)
+    xt = prob.xtilde.to(dev)
+    if world > 1:
+        dist.broadcast(xt, 0)
+    theta = prob.theta
+    Cm, mask = native.localker(theta, n, dev)
+    Kt = native.acosker(theta["sigma_0"], xt, xt, Cm, True)
+    ev, evec = torch.linalg.eigh(Kt, UPLO="L")                       # library call
+    keep = ev > max(float(ev.max()) * 1e-4, 1e-4)
+    B = evec[:, keep].contiguous()
+    m_b, V_b = synth.make_variational_state(torch.diag(ev[keep]).cpu(), CFG)
+    m_b, V_b = m_b.to(dev), V_b.to(dev)
+    if world > 1:
+        for t in (B, m_b, V_b):
+            dist.broadcast(t, 0)
+    q = B.shape[1]
+    native.set_option(local, "kl_weight", 1.0 if rank == 0 else 0.0)
+    peak_f64 = measure_fp64_peak(dev) if rank == 0 else None
+
+    def step():
+        out = native.elbo_grad(X, r, xt, n, theta, B, m_b, V_b, prob.logA, prob.lambda0)
+        vec = torch.tensor([out["loglik"]] + [out["grad"][k] for k in KEYS] + [out["sum_r"]], dtype=torch.float64,
+                           device=dev)
+        if world > 1:
+            dist.all_reduce(vec)          # the one exchange step of the sharded evaluation (8 doubles)
+        return out, vec
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    native.set_option(local, "profile", 1.0)
+    native.get_profile(local, reset=True)
+    native.launch_count(local, reset=True)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out, vec = step()
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = native.launch_count(local)
+    stage_ms, calls = native.get_profile(local, reset=True)
+    native.set_option(local, "profile", 0.0)
+    t = torch.tensor([e0.elapsed_time(e1) * 1e-3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed = float(t.item())
+    value = args.steps / elapsed                                  # whole-job evaluations per second
+
+    # ---- end to end through the host-buffer entry point: H2D of the images inside the timed region
+    native.set_option(local, "kl_weight", 1.0 if rank == 0 else 0.0)
+    Bh, mh, Vh, xth = B.cpu(), m_b.cpu(), V_b.cpu(), xt.cpu()
+    for _ in range(1):
+        native.elbo_grad_host(Xh, rh, xth, n, theta, Bh, mh, Vh, prob.logA, prob.lambda0, device=local)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 3))
+    for _ in range(e2e_steps):
+        oh = native.elbo_grad_host(Xh, rh, xth, n, theta, Bh, mh, Vh, prob.logA, prob.lambda0, device=local)
+        if world > 1:
+            dist.all_reduce(torch.tensor([oh["loglik"]] + [oh["grad"][k] for k in KEYS], dtype=torch.float64,
+                                         device=dev))
+    barrier()
+    te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = e2e_steps / float(te.item())
+    h2d = Xh.numel() * 8 + rh.numel() * 8 + (xth.numel() + Bh.numel() + Vh.numel() + mh.numel()) * 8
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel: Z = X C (2*N*p^2 flop per launch, one launch per slab)
+    p = out["p"]
+    flops_xc = 2.0 * N * p * p * calls
+    ach = flops_xc / (stage_ms["gemm_XC"] * 1e-3) / 1e12 if stage_ms["gemm_XC"] > 0 else None
+    traffic = None
+    tf = os.path.join(ROOT, "profiles", "r1_gemm_xc_traffic.json")
+    if os.path.exists(tf):
+        traffic = json.load(open(tf)).get("dram_bytes_per_launch")
+    contract_flops = 4.0 * N * p * p + 4.0 * N * p * m + 4.0 * N * q * q + 4.0 * N * m * q
+    executed_flops = 4.0 * N * p * p + 4.0 * N * p * m + 4.0 * N * m * m
+    roof = {"bound": "tensor", "kernel": "gemm_f64_kernel<128,128,K-major,MN-major,kRowdot> (Z = X*C)",
+            "achieved": ach, "peak": peak_f64, "unit": "TFLOP/s", "frac": (ach / peak_f64) if ach else None,
+            "traffic": traffic,
+            "peak_source": "cuBLAS fp64 torch.matmul 8192^3 best-of-5 measured in this run "
+                           "(MEASURED_PEAKS.json has no fp64 entry)",
+            "stage_ms_per_eval": {k: v / max(calls, 1) for k, v in stage_ms.items()},
+            "whole_eval": {"contract_flops": contract_flops, "executed_flops": executed_flops,
+                           "contract_tflops": contract_flops * value / world / 1e12,
+                           "executed_tflops": executed_flops * value / world / 1e12}}
+    try:
+        mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        roof["hbm_peak_gbs_measured"] = mp.get("hbm_gbs")
+    except Exception:
+        pass
+
+    # ---- CPU baseline beside it (rank 0, N=1 only): oracle port on a bounded sample
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        import oracle.spatial_gp_oracle as orc
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        chunk = int(os.environ.get("SGP_BENCH_CPU_CHUNK", min(2000, N)))
+        Bc, mc, Vc = B.cpu(), m_b.cpu(), V_b.cpu()
+        ts = cpu_eval_time(orc, prob, Bc, mc, Vc, chunk, reps=3, warm=1)
+        tmed = statistics.median(ts)
+        cpu = {"value": 1.0 / (tmed * N / chunk), "unit": "evals/s", "cores": cores, "kind": "port",
+               "sample": f"oracle port on the first {chunk} of {N} images, median of 3, scaled linearly to N "
+                         f"(extrapolated); {tmed:.3f} s per {chunk}-image evaluation"}
+
+    line = {"metric": "elbo_grad_evals_per_sec", "value": value, "unit": "evals/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config_dict(w, world, {"p": p, "q": q, "images_total": N * world,
+                                             "images_per_sec": value * N * world}),
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 128,
+                    "steps": e2e_steps, "api": "sgp_elbo_grad_host (pinned host images streamed slab by slab)"},
+            "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+            "result": {"loglik": float(vec[0]), "KL": out["KL"], "grad": [float(v) for v in vec[1:7]]}}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -37,6 +37,8 @@ SIGNATURES = {
     "sgp_last_error": (C.c_char_p, [_p]),
     "sgp_set_slab_rows": (_i, [_p, _l]),
     "sgp_invalidate_cache": (_i, [_p]),
+    "sgp_set_option": (_i, [_p, C.c_char_p, _d]),
+    "sgp_get_profile": (_i, [_p, _dp, _i, C.POINTER(_l), _i]),
     "sgp_launch_count": (_l, [_p, _i]),
     "sgp_mask_host": (_i, [_dp, _i, C.POINTER(C.c_uint8), _ip]),
     "sgp_localker": (_i, [_p, _dp, _i, _p, _l, _p, _l, _p]),

@@ -58,6 +58,11 @@ struct sgp_handle {
   cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
   DevBuf hx[2], hr, small;
   cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr};
+  // options
+  double kl_weight = 1.0;   // weight of the KL adjoint in the gradient (image-sharded ranks > 0 use 0)
+  bool profile = false;     // record CUDA events at stage boundaries of the closure
+  std::vector<cudaEvent_t> prof_ev; std::vector<int> prof_stage; size_t prof_used = 0;
+  double stage_ms[16] = {0}; long stage_calls = 0;
 };
 
 namespace {
@@ -203,6 +208,24 @@ int sgp_set_slab_rows(sgp_handle* h, long rows) {
   return SGP_OK;
 }
 
+int sgp_set_option(sgp_handle* h, const char* name, double value) {
+  if (!h || !name) return SGP_E_ARG;
+  const std::string n(name);
+  if (n == "kl_weight") h->kl_weight = value;
+  else if (n == "profile") h->profile = value != 0.0;
+  else if (n == "slab_rows") return sgp_set_slab_rows(h, (long)value);
+  else return fail(h, SGP_E_ARG, "sgp_set_option: unknown option " + n);
+  return SGP_OK;
+}
+
+int sgp_get_profile(sgp_handle* h, double* stage_ms_out, int n, long* calls_out, int reset) {
+  if (!h) return SGP_E_ARG;
+  for (int i = 0; i < n && i < 16; ++i) stage_ms_out[i] = h->stage_ms[i];
+  if (calls_out) *calls_out = h->stage_calls;
+  if (reset) { for (double& v : h->stage_ms) v = 0.0; h->stage_calls = 0; }
+  return SGP_OK;
+}
+
 int sgp_invalidate_cache(sgp_handle* h) {
   if (!h) return SGP_E_ARG;
   h->cache_valid = false;
@@ -335,6 +358,16 @@ struct ClosureIn {
 
 int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream_t st) {
   int rc = ensure_ready(h); if (rc) return rc;
+  h->prof_used = 0;
+  auto mark = [&](int stage) {   // "stage begins now" (only when profiling)
+    if (!h->profile) return;
+    if (h->prof_used == h->prof_ev.size()) {
+      cudaEvent_t e; cudaEventCreate(&e); h->prof_ev.push_back(e); h->prof_stage.push_back(0);
+    }
+    h->prof_stage[h->prof_used] = stage;
+    cudaEventRecord(h->prof_ev[h->prof_used++], st);
+  };
+  mark(0);
   const bool streaming = in.X_host != nullptr;
   const long N = in.N; const int m = in.m, q = in.q, n = in.n_px; const long P = (long)n * n;
   if (N <= 0 || m <= 0 || q <= 0 || q > m) return fail(h, SGP_E_ARG, "sgp_elbo_grad: bad sizes");
@@ -541,22 +574,26 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     } else {
       Xs = Xg + i0 * ldxg; ldxs = ldxg;
     }
+    mark(1);
     // G1: Z = X C, partial s_i = x_i^T C x_i                                  (U:978, U:1029)
     GemmArgs g1{};
     g1.A = Xs; g1.lda = ldxs; g1.B = C; g1.ldb = ldp; g1.C = Zs; g1.ldc = ldp; g1.M = (int)ns; g1.N = p; g1.K = p;
     g1.aux = Xs; g1.ldaux = ldxs; g1.part1 = partN; g1.ldpart = ldpartN;
     CU(gemm(st, 0, 1, kRowdot, false, 1, g1));
+    mark(2);
     norms_finalize(partN, ldpartN, ntp, ns, th.s02, s_s, X1, st);
     // G2: K = acos-kernel(Z Ug^T)                                             (U:982-990)
     GemmArgs g2{};
     g2.A = Zs; g2.lda = ldp; g2.B = Ug; g2.ldb = ldug; g2.C = Ks; g2.ldc = ldm; g2.M = (int)ns; g2.N = m; g2.K = p;
     g2.rowvec = X1; g2.colvec = X2; g2.C2 = cos_s; g2.s02 = th.s02;
     CU(gemm(st, 0, 0, kAcos, false, 1, g2));
+    mark(3);
     // G3: T = K Mfull^T ; partial lam_var / lam_m row sums                    (U:1090-1101)
     GemmArgs g3{};
     g3.A = Ks; g3.lda = ldm; g3.B = Mfull; g3.ldb = ldm; g3.C = Ts; g3.ldc = ldm; g3.M = (int)ns; g3.N = m; g3.K = m;
     g3.aux = Ks; g3.ldaux = ldm; g3.colvec = bb; g3.part1 = pm1; g3.part2 = pm2; g3.ldpart = ldpartN;
     CU(gemm(st, 0, 0, kMoments, false, 1, g3));
+    mark(4);
     moments_rows(s_s, pm1, pm2, ldpartN, ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
                  v_s, blockpart, st);
     const int nbm = moments_rows_blocks(ns);
@@ -571,21 +608,25 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     col_reduce(coly, nbb, m, ldm, yv, acc_flag, st);
     sum_to_slot(sumpartR, nbb, 1, 1.0, h->d_scal, kSlotSig, 1, st);
     sum_to_slot(w_s, ns, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+    mark(5);
     // G4: Y = R Ug + diag(w) X   (into the Z buffer)
     GemmArgs g4{};
     g4.A = Ts; g4.lda = ldm; g4.B = Ug; g4.ldb = ldug; g4.C = Zs; g4.ldc = ldp; g4.M = (int)ns; g4.N = p; g4.K = m;
     g4.rowvec = w_s; g4.aux = Xs; g4.ldaux = ldxs;
     CU(gemm(st, 0, 1, kAxpyRow, false, 1, g4));
+    mark(6);
     // G5: GC += X^T Y   (split-K over the images of the slab)
     GemmArgs g5{};
     g5.A = Xs; g5.lda = ldxs; g5.B = Zs; g5.ldb = ldp; g5.C = GCpart; g5.ldc = ldp; g5.M = p; g5.N = p; g5.K = (int)ns;
     g5.k_chunk = (int)rup((ns + nzGC - 1) / nzGC, 16); g5.zstride = zGC; g5.accumulate = acc_flag;
     CU(gemm(st, 1, 1, kStore, false, nzGC, g5));
+    mark(7);
     // G6: Sig2 += K^T diag(v) K
     GemmArgs g6{};
     g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
     g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
     CU(gemm(st, 1, 1, kStore, false, nzS2, g6));
+    mark(8);
     if (streaming) CU(cudaEventRecord(h->ev_used[slab_i & 1], st));
   }
 
@@ -602,7 +643,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   rank1_add(inner, ldq, q, q, 1.0, y_b, in.m_b, st);                                    // + y_b m_b^T
   CU(mm(st, 0, 1, Kinv, ldq, inner, ldq, Sq, ldq, q, q, q));                             // S = Kinv (...)
   CU(mm(st, 0, 1, Sq, ldq, Kinv, ldq, GKtb, ldq, q, q, q, -1.0));                        // -S Kinv
-  gkt_assemble(GKtb, ldq, q, Kinv, KVK, bq, st);                                        // KL part (U:1333)
+  gkt_assemble(GKtb, ldq, q, Kinv, KVK, bq, h->kl_weight, st);                                        // KL part (U:1333)
   CU(mm(st, 0, 1, Bw, ldq, GKtb, ldq, tmq3, ldq, m, q, q));
   CU(mm(st, 0, 0, tmq3, ldq, Bw, ldq, GKt, ldm, m, m, q));                               // GKt = B GKtb B^T
 
@@ -632,8 +673,18 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
            in.logdetV_host ? 1 : 0, h->d_out, st);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(double) * 16, cudaMemcpyDeviceToHost, st));
+  mark(-1);
   CU(cudaStreamSynchronize(st));
   if (out_host) std::memcpy(out_host, h->h_out, sizeof(double) * 16);
+  if (h->profile) {
+    for (size_t i = 0; i + 1 < h->prof_used; ++i) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, h->prof_ev[i], h->prof_ev[i + 1]);
+      const int sg = h->prof_stage[i];
+      if (sg >= 0 && sg < 16) h->stage_ms[sg] += ms;
+    }
+    h->stage_calls++;
+  }
 
   h->dbg.clear();
   h->dbg["C"] = {C, p, p, ldp};   h->dbg["Kt"] = {Kt, m, m, ldm};     h->dbg["Ktb"] = {Ktb, q, q, ldq};

@@ -359,13 +359,14 @@ void copy_mat(const double* A, long lda, int rows, int cols, double* out, long l
 }
 
 __global__ void gkt_assemble_kernel(double* __restrict__ G, long ld, int q, const double* __restrict__ Kinv,
-                                    const double* __restrict__ KVK, const double* __restrict__ b) {
+                                    const double* __restrict__ KVK, const double* __restrict__ b, double klw) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
   if (i < q && j < q)
-    G[(long)i * ld + j] += -0.5 * Kinv[(long)i * ld + j] + 0.5 * KVK[(long)j * ld + i] + 0.5 * b[i] * b[j];
+    G[(long)i * ld + j] += klw * (-0.5 * Kinv[(long)i * ld + j] + 0.5 * KVK[(long)j * ld + i] + 0.5 * b[i] * b[j]);
 }
-void gkt_assemble(double* G, long ld, int q, const double* Kinv, const double* KVK, const double* b, cudaStream_t st) {
-  note_launch(); gkt_assemble_kernel<<<dim3(cdiv(q, 128), q), 128, 0, st>>>(G, ld, q, Kinv, KVK, b);
+void gkt_assemble(double* G, long ld, int q, const double* Kinv, const double* KVK, const double* b, double klw,
+                  cudaStream_t st) {
+  note_launch(); gkt_assemble_kernel<<<dim3(cdiv(q, 128), q), 128, 0, st>>>(G, ld, q, Kinv, KVK, b, klw);
 }
 
 __global__ void col_weights_kernel(const double* __restrict__ ka, const double* __restrict__ kb,

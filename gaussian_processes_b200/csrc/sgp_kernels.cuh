@@ -84,8 +84,9 @@ void rank1_add(double* out, long ldo, int rows, int cols, double alpha, const do
                cudaStream_t st);                                                             // out += alpha x y^T
 void gemv(const double* A, long lda, int rows, int cols, int trans, const double* x, double* y, cudaStream_t st);
 void copy_mat(const double* A, long lda, int rows, int cols, double* out, long ldo, cudaStream_t st);
-// G = G - 0.5*Kinv + 0.5*KVK^T + 0.5*b b^T     (adjoint of K_tilde_b: loglik part already in G)
-void gkt_assemble(double* G, long ld, int q, const double* Kinv, const double* KVK, const double* b, cudaStream_t st);
+// G = G + klw*(-0.5*Kinv + 0.5*KVK^T + 0.5*b b^T)     (adjoint of K_tilde_b: loglik part already in G)
+void gkt_assemble(double* G, long ld, int q, const double* Kinv, const double* KVK, const double* b, double klw,
+                  cudaStream_t st);
 // out = 0.5*(kap_a + kap_b)/nrm + extra   (null pointers count as 0)
 void col_weights(const double* kap_a, const double* kap_b, const double* extra, const double* nrm, int m,
                  double* out, cudaStream_t st);

@@ -256,3 +256,21 @@ def set_slab_rows(device: int, rows: int):
 
 def launch_count(device: int = 0, reset: bool = False) -> int:
     return _lib.handle_for(device).launch_count(reset)
+
+
+STAGES = ("setup+inducing_fwd", "gemm_XC", "gemm_acos", "gemm_moments", "rows+acos_adjoint", "gemm_RU", "gemm_XtY",
+          "gemm_KtvK", "tail_qxq+inducing_bwd+contract")
+
+
+def set_option(device: int, name: str, value: float):
+    h = _lib.handle_for(device)
+    h.check(lib.sgp_set_option(h.ptr, name.encode(), float(value)))
+
+
+def get_profile(device: int = 0, reset: bool = True):
+    """Per-stage device milliseconds accumulated by sgp_elbo_grad while option "profile" is on."""
+    h = _lib.handle_for(device)
+    ms = (C.c_double * 16)()
+    calls = C.c_long(0)
+    h.check(lib.sgp_get_profile(h.ptr, ms, 16, C.byref(calls), 1 if reset else 0))
+    return dict(zip(STAGES, list(ms)[:len(STAGES)])), int(calls.value)

@@ -57,6 +57,15 @@ SGP_API int sgp_destroy(sgp_handle* h);
 SGP_API const char* sgp_last_error(const sgp_handle* h);
 /* rows of the image pass processed per slab (bounds the scratch memory); 0 = default (65536) */
 SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
+/* options: "kl_weight" (weight of the KL adjoint in the returned gradient; ranks > 0 of an image-sharded
+ * evaluation use 0 so that the all-reduced sum counts the N-independent KL term once), "profile" (1 = record
+ * CUDA events at the stage boundaries of sgp_elbo_grad), "slab_rows".                                          */
+SGP_API int sgp_set_option(sgp_handle* h, const char* name, double value);
+/* accumulated per-stage device milliseconds of sgp_elbo_grad since the last reset:
+ * [0] setup + inducing-point forward, [1] X*C GEMM, [2] acos-kernel GEMM, [3] moments GEMM, [4] per-image
+ * moments + adjoint of the acos map, [5] R*U GEMM, [6] X^T*Y GEMM, [7] K^T diag(v) K GEMM, [8] q x q adjoint,
+ * inducing-point backward, <dC,GC> contraction.                                                                */
+SGP_API int sgp_get_profile(sgp_handle* h, double* stage_ms_out, int n, long* calls_out, int reset);
 /* forget the cached masked copies of X / xtilde (call if their contents changed in place) */
 SGP_API int sgp_invalidate_cache(sgp_handle* h);
 /* number of kernels this library has launched through `h` since creation / last reset */
