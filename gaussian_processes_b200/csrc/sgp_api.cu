@@ -925,6 +925,23 @@ int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, c
   return SGP_OK;
 }
 
+int sgp_loglik_sums(sgp_handle* h, const double* r, const double* f, const double* lam_m, const double* lam_var, long N,
+                    double logA, double* out_host, void* stream) {
+  if (!h || !r || !f || !lam_m || !out_host) return fail(h, SGP_E_ARG, "sgp_loglik_sums: null argument");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nb = fparam_blocks(N);
+  CU(h->arena.reserve((size_t)nb * 8 * sizeof(double) + 4096));
+  double* bp = (double*)h->arena.p;
+  loglik_sums_pass(r, f, lam_m, lam_var, N, std::exp(logA), bp, st);
+  for (int k = 0; k < 5; ++k) sum_to_slot(bp + k, nb, 8, 1.0, h->d_scal, kSlotAux0 + k, 0, st);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(h->h_out, h->d_scal + kSlotAux0, sizeof(double) * 5, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  for (int k = 0; k < 5; ++k) out_host[k] = h->h_out[k];
+  return SGP_OK;
+}
+
 int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, const double* f, long N, int q,
                     double logA, double* g, double* G, long ldg, void* stream) {
   if (!h || !a || !r || !f || !g || !G) return fail(h, SGP_E_ARG, "sgp_estep_terms: null argument");

@@ -729,6 +729,35 @@ void fparam_pass(const double* lam_m, const double* lam_var, const double* r, lo
   note_launch(); fparam_kernel<<<fparam_blocks(n), 256, 0, st>>>(lam_m, lam_var, r, n, A, lambda0, f, blockpart);
 }
 
+
+// sums for compute_loglikelihood with a caller-supplied f (utils.py:1240-1255):
+// blockpart[blk*8 + {0..4}] = sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, nan-count(f)
+__global__ void __launch_bounds__(256) loglik_sums_kernel(const double* __restrict__ r, const double* __restrict__ f,
+                                                          const double* __restrict__ lam_m,
+                                                          const double* __restrict__ lam_var, long n, double A,
+                                                          double* __restrict__ blockpart) {
+  __shared__ double red[32];
+  double acc[5] = {0, 0, 0, 0, 0};
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const double ri = r[i], fi = f[i], lm = lam_m[i];
+    const double lv = lam_var ? lam_var[i] : 0.0;
+    acc[0] += ri * lm;
+    acc[1] += fi;
+    acc[2] += (lm + A * lv) * fi;
+    acc[3] += ri;
+    acc[4] += (fi != fi) ? 1.0 : 0.0;
+  }
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const double sres = block_sum(acc[k], red);
+    if (threadIdx.x == 0) blockpart[(long)blockIdx.x * 8 + k] = sres;
+  }
+}
+void loglik_sums_pass(const double* r, const double* f, const double* lam_m, const double* lam_var, long n, double A,
+                      double* blockpart, cudaStream_t st) {
+  note_launch(); loglik_sums_kernel<<<fparam_blocks(n), 256, 0, st>>>(r, f, lam_m, lam_var, n, A, blockpart);
+}
+
 constexpr int kColsumRows = 128;
 __global__ void __launch_bounds__(256) colsum_weighted_kernel(const double* __restrict__ a, long lda, long n, int q,
                                                               const double* __restrict__ r,

@@ -125,6 +125,9 @@ void moments_combine(const double* Kvec, const double* part1, const double* part
 int fparam_blocks(long n);
 void fparam_pass(const double* lam_m, const double* lam_var, const double* r, long n, double A, double lambda0,
                  double* f, double* blockpart, cudaStream_t st);
+// same block layout as fparam_pass, for a caller-supplied f: {sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, nan}
+void loglik_sums_pass(const double* r, const double* f, const double* lam_m, const double* lam_var, long n, double A,
+                      double* blockpart, cudaStream_t st);
 // colpart[blk][j] = sum_{i in blk} a_ij (r_i - f_i)
 int colsum_blocks(long n);
 void colsum_weighted(const double* a, long lda, long n, int q, const double* r, const double* f, double* colpart,

@@ -34,6 +34,16 @@ def _c(t: torch.Tensor) -> torch.Tensor:
     return t.contiguous()
 
 
+def _even(t: torch.Tensor) -> torch.Tensor:
+    """row-major view whose leading dimension is even and whose base is 16-byte aligned (GEMM operand rule)"""
+    t = _c(t)
+    if t.stride(0) % 2 == 0 and t.data_ptr() % 16 == 0:
+        return t
+    w = torch.zeros((t.shape[0], t.shape[1] + (t.shape[1] & 1)), dtype=t.dtype, device=t.device)
+    w[:, :t.shape[1]] = t
+    return w[:, :t.shape[1]]
+
+
 def _ld(t: torch.Tensor) -> int:
     return t.stride(0) if t.dim() == 2 else t.shape[-1]
 
@@ -129,6 +139,19 @@ def fparam_eval(lam_m: torch.Tensor, lam_var: torch.Tensor, r: torch.Tensor, log
     return dict(zip(keys, list(out))), f
 
 
+def loglik_sums(r: torch.Tensor, f: torch.Tensor, lam_m: torch.Tensor, lam_var: Optional[torch.Tensor], logA: float):
+    """dict(r_lam, sum_f, lamf, sum_r, nan): the N-sized reductions of compute_loglikelihood (utils.py:1240-1255)
+    for a caller-supplied f; lamf = sum (lam_m + A lam_var) f."""
+    _need_cuda(r, f, lam_m, lam_var)
+    r, f, lam_m = r.contiguous(), f.contiguous(), lam_m.contiguous()
+    lam_var = lam_var.contiguous() if lam_var is not None else None
+    out = (C.c_double * 8)()
+    h = _h(r)
+    h.check(lib.sgp_loglik_sums(h.ptr, _ptr(r), _ptr(f), _ptr(lam_m), _ptr(lam_var), r.shape[0], float(logA), out,
+                                _stream(r.device)))
+    return dict(zip(("r_lam", "sum_f", "lamf", "sum_r", "nan"), list(out)[:5]))
+
+
 def estep_terms(a: torch.Tensor, r: torch.Tensor, f: torch.Tensor, logA: float):
     _need_cuda(a, r, f)
     a, r, f = _c(a), r.contiguous(), f.contiguous()
@@ -171,7 +194,7 @@ def gemm_f64(A: torch.Tensor, B: torch.Tensor, a_layout: int = 0, b_layout: int 
              out: Optional[torch.Tensor] = None, accumulate: bool = False, small_tile: bool = False):
     """C[M,N] = alpha * sum_k A(m,k) B(n,k); layout 0: tensor is [rows, K]; layout 1: tensor is [K, rows]."""
     _need_cuda(A, B)
-    A, B = _c(A), _c(B)
+    A, B = _even(A), _even(B)
     M, K = (A.shape if a_layout == 0 else (A.shape[1], A.shape[0]))
     N = B.shape[0] if b_layout == 0 else B.shape[1]
     ldc = (N + 1) // 2 * 2
@@ -182,6 +205,30 @@ def gemm_f64(A: torch.Tensor, B: torch.Tensor, a_layout: int = 0, b_layout: int 
                              _ld(out), int(M), int(N), int(K), float(alpha), 1 if accumulate else 0,
                              1 if small_tile else 0, _stream(A.device)))
     return out[:, :N]
+
+
+def matmul(A: torch.Tensor, B: torch.Tensor) -> torch.Tensor:
+    """A @ B on the DMMA GEMM (A: [M,K], B: [K,N]); contiguous result."""
+    small = max(A.shape[0], B.shape[1]) <= 1024
+    return gemm_f64(A, B, 0, 1, small_tile=small).contiguous()
+
+
+def matmul_nt(A: torch.Tensor, Bt: torch.Tensor) -> torch.Tensor:
+    """A @ Bt.T on the DMMA GEMM (A: [M,K], Bt: [N,K])."""
+    small = max(A.shape[0], Bt.shape[0]) <= 1024
+    return gemm_f64(A, Bt, 0, 0, small_tile=small).contiguous()
+
+
+def matmul_tn(At: torch.Tensor, B: torch.Tensor) -> torch.Tensor:
+    """At.T @ B on the DMMA GEMM (At: [K,M], B: [K,N])."""
+    small = max(At.shape[1], B.shape[1]) <= 1024
+    return gemm_f64(At, B, 1, 1, small_tile=small).contiguous()
+
+
+def rate(lam_m: torch.Tensor, lam_var: torch.Tensor, logA: float, lambda0: float) -> torch.Tensor:
+    """f = exp(A lam_m + A^2 lam_var / 2 + lambda0)  (utils.py:1138), one streaming pass."""
+    _, f = fparam_eval(lam_m, lam_var, lam_m, logA, lambda0, want_f=True)
+    return f
 
 
 OUT_KEYS = ("loglik", "KL", "g_sigma_0", "g_eps_0x", "g_eps_0y", "g_-2log2beta", "g_-log2rho2", "g_Amp",

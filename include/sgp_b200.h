@@ -101,6 +101,12 @@ SGP_API int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const d
 SGP_API int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, const double* r, long N, double logA,
                     double lambda0, double* f, double* out_host, void* stream);
 
+/* ---- a7: compute_loglikelihood with a caller-supplied f_mean  utils.py:1240-1255 / 1269 -----------------------
+ * out_host[5] = { sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, nan-count(f) } ; lam_var may be NULL.
+ * loglik = A*out[0] + lambda0*out[3] - out[1] ; dloglik/dlogA = A*(out[0] - out[2]) ; dloglik/dlambda0 = out[3]-out[1] */
+SGP_API int sgp_loglik_sums(sgp_handle* h, const double* r, const double* f, const double* lam_m, const double* lam_var,
+                    long N, double logA, double* out_host, void* stream);
+
 /* ---- a10: Estep(r, KKtilde_inv, m, f_params, f_mean, K_tilde, ...)  utils.py:1420-1422 ------------------------
  * g = A a^T (r - f) (q) ; G = A^2 a^T diag(f) a (q x q, ldg).                                                   */
 SGP_API int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, const double* f, long N, int q,

@@ -1,0 +1,188 @@
+"""CPU: host-side logic of the `utils`-compatible call surface (varGP's EM loop, closures, result layout,
+error semantics) with the CUDA library replaced by the oracle-backed stand-in tests/fake_native.py.
+Reference values: fixtures produced by the real reference (oracle/gen_golden.py)."""
+import contextlib
+import io
+import math
+
+import numpy as np
+import pytest
+import torch
+
+import fake_native
+from gaussian_processes_b200 import synth
+from helpers import case_inputs, load
+
+
+@pytest.fixture()
+def U(monkeypatch):
+    with contextlib.redirect_stdout(io.StringIO()):
+        from gaussian_processes_b200 import utils
+    monkeypatch.setattr(utils, "native", fake_native)
+    return utils
+
+
+def fit_args(fx, prob):
+    n, m = int(fx["n"]), int(fx["m"])
+    theta = synth.theta_tensors(prob.theta, requires_grad=True)
+    return dict(
+        fit_parameters=dict(ntilde=m, maxiter=int(fx["maxiter"]), nEstep=int(fx["nEstep"]), nMstep=int(fx["nMstep"]),
+                            nFparamstep=int(fx["nFparamstep"]), kernfun="acosker", cellid=0, n_px_side=n,
+                            display_hyper=False),
+        xtilde=prob.xtilde, hyperparams_tuple=(theta, dict(synth.THETA_LIMS_LO), dict(synth.THETA_LIMS_HI)),
+        f_params={"logA": torch.tensor(prob.logA), "lambda0": torch.tensor(prob.lambda0)})
+
+
+def run_fit(U, name="fit_small_n10", **over):
+    fx = load(name)
+    keys = [str(k) for k in fx["theta_keys"]]
+    prob = synth.make_problem(int(fx["N"]), int(fx["n"]), int(fx["m"]), cfg=int(fx["cfg"]),
+                              theta=dict(zip(keys, fx["theta0"].tolist())))
+    args = fit_args(fx, prob)
+    args.update(over)
+    with contextlib.redirect_stdout(io.StringIO()):
+        fit, err = U.varGP(prob.X, prob.r, **args)
+    return fx, keys, prob, args, fit, err
+
+
+def test_vargp_tracks_match_reference(U):
+    """Loop-level parity: loss / theta / f-param tracks of the reference's own varGP."""
+    fx, keys, prob, args, fit, err = run_fit(U)
+    assert not err["is_error"], err
+    vt = fit["values_track"]
+    tol = 1e-6   # LBFGS line searches amplify round-off differences of the adjoint vs forward-mode gradients
+    assert np.allclose(vt["loss_track"]["logmarginal"].numpy(), fx["logmarginal"], rtol=tol)
+    assert np.allclose(vt["loss_track"]["loglikelihood"].numpy(), fx["loglikelihood"], rtol=tol)
+    assert np.allclose(vt["loss_track"]["KL"].numpy(), fx["KL"], rtol=tol, atol=1e-8)
+    got = np.stack([vt["theta_track"][k].numpy() for k in keys])
+    assert np.allclose(got, fx["theta_track"], rtol=tol, atol=1e-8)
+    assert np.allclose(vt["f_par_track"]["logA"].numpy(), fx["logA_track"], rtol=tol)
+    assert np.allclose(vt["f_par_track"]["lambda0"].numpy(), fx["lambda0_track"], rtol=tol)
+    assert fit["B"].shape[1] == int(fx["q"])
+    assert np.allclose(fit["V_b"].numpy(), fx["V_b"], rtol=1e-5, atol=1e-8)
+
+
+def test_vargp_result_layout_and_no_mutation(U):
+    fx, keys, prob, args, fit, err = run_fit(U)
+    assert set(fit) == {"fit_parameters", "final_kernel", "err_dict", "xtilde", "hyperparams_tuple", "f_params", "m_b",
+                        "V_b", "C", "mask", "K_tilde_b", "K_tilde_inv_b", "K_b", "Kvec", "B", "values_track"}
+    assert set(fit["final_kernel"]) == {"C", "mask", "K_tilde", "K", "Kvec", "eigvecs"}
+    vt = fit["values_track"]
+    assert set(vt) == {"loss_track", "theta_track", "f_par_track", "variation_par_track"}
+    assert len(vt["variation_par_track"]["V_b"]) == int(fx["maxiter"])
+    assert fit["fit_parameters"]["min_tolerance"] == 1e-11 and fit["fit_parameters"]["eigval_tol"] == 1e-4
+    # caller's dicts are not mutated (U:1632, U:1653-1660)
+    th0 = args["hyperparams_tuple"][0]
+    assert all(float(th0[k]) == fx["theta0"][i] for i, k in enumerate(keys))
+    assert float(args["f_params"]["logA"]) == float(fx["logA0"])
+    assert "min_tolerance" not in args["fit_parameters"]
+    # one fused call per M-step closure, none elsewhere
+    assert fake_native.calls["elbo_grad"] > 0
+
+
+def test_vargp_warm_start_tolerates_extra_keys(U):
+    """The active loop feeds the previous fit_model back as kwargs (cell 17): extra keys must be ignored."""
+    fx, keys, prob, args, fit, err = run_fit(U)
+    again = dict(fit)
+    again["fit_parameters"] = dict(fit["fit_parameters"], maxiter=2)
+    with contextlib.redirect_stdout(io.StringIO()):
+        fit2, err2 = U.varGP(prob.X, prob.r, **again)
+    assert not err2["is_error"]
+    assert fit2["values_track"]["loss_track"]["logmarginal"].shape[0] == 2
+
+
+def test_vargp_error_rollback(U, monkeypatch):
+    """An exception inside the loop rolls back to the last tracked iteration and is reported via err_dict."""
+    real = fake_native.estep_terms
+    n = {"c": 0}
+
+    def flaky(*a, **k):
+        n["c"] += 1
+        if n["c"] > 7:      # fails inside iteration 3 (3 E-steps per iteration)
+            raise RuntimeError("injected")
+        return real(*a, **k)
+    monkeypatch.setattr(fake_native, "estep_terms", flaky)
+    fx, keys, prob, args, fit, err = run_fit(U)
+    assert err["is_error"] and isinstance(err["error"], RuntimeError)
+    assert fit["fit_parameters"]["maxiter"] == 3
+    vt = fit["values_track"]
+    assert vt["loss_track"]["logmarginal"].shape[0] == 3
+    for i, k in enumerate(keys):     # theta restored to the value tracked at iteration maxiter-1
+        assert float(fit["hyperparams_tuple"][0][k]) == float(vt["theta_track"][k][2])
+
+
+def test_closure_out_of_bounds_returns_inf(U):
+    fx = load("closure_dense_n8")
+    prob, st = case_inputs(fx)
+    th = synth.theta_tensors(prob.theta)
+    th["eps_0x"] = torch.tensor(1.5)
+    with pytest.raises(ValueError):
+        U.localker(th, synth.THETA_LIMS_HI, synth.THETA_LIMS_LO, prob.n_px_side)
+    with pytest.raises(ValueError):
+        U.elbo_and_grad(th, synth.THETA_LIMS_LO, synth.THETA_LIMS_HI, prob.n_px_side, prob.X, prob.xtilde, prob.r,
+                        st["B"], st["m_b"], st["V_b"], {"logA": torch.tensor(st["logA"]),
+                                                        "lambda0": torch.tensor(st["lambda0"])})
+
+
+@pytest.mark.parametrize("name", ["closure_square_n8", "closure_local_n12"])
+def test_forward_mode_closure_matches_reference(U, name):
+    """ntilde == nt (a = B) and the fallback path: the reference-sequenced closure on the function-level surface."""
+    fx = load(name)
+    prob, st = case_inputs(fx)
+    th = synth.theta_tensors(prob.theta)
+    fp = {"logA": torch.tensor(st["logA"]), "lambda0": torch.tensor(st["lambda0"])}
+    same = prob.X.shape[0] == prob.xtilde.shape[0]
+    ll, kl, g = U._closure_forward_mode(th, synth.THETA_LIMS_LO, synth.THETA_LIMS_HI, prob.n_px_side, prob.X,
+                                        prob.xtilde, prob.r, U.acosker, same, st["B"], st["m_b"], st["V_b"], fp)
+    assert abs(ll - float(fx["loglik"])) <= 1e-10 * abs(float(fx["loglik"]))
+    assert abs(kl - float(fx["KL"])) <= 1e-10 * abs(float(fx["KL"]))
+    keys = [str(k) for k in fx["theta_keys"]]
+    ref = fx["dloglik"] - fx["dKL"]
+    scale = max(np.abs(fx["dloglik"]).max(), np.abs(fx["dKL"]).max())
+    assert np.abs(np.array([g[k] for k in keys]) - ref).max() <= 1e-9 * scale
+
+
+def test_function_level_surface_against_reference(U):
+    fx = load("closure_local_n12")
+    prob, st = case_inputs(fx)
+    th = synth.theta_tensors(prob.theta)
+    C, mask, dC = U.localker(th, synth.THETA_LIMS_HI, synth.THETA_LIMS_LO, prob.n_px_side, grad=True)
+    assert list(dC.keys()) == ["Amp", "-2log2beta", "-log2rho2", "eps_0x", "eps_0y"]
+    xm, um = prob.X[:, mask], prob.xtilde[:, mask]
+    K, dK = U.acosker(th, xm, um, C=C, dC=dC)
+    assert list(dK.keys())[0] == "sigma_0"
+    for i, k in enumerate([str(s) for s in fx["dK_keys"]]):
+        assert np.allclose(dK[k].numpy(), fx["dK"][i], rtol=1e-9, atol=1e-12), k
+    Kvec, dKvec = U.acosker(th, xm, C=C, dC=dC, diag=True)
+    assert np.allclose(Kvec.numpy(), fx["Kvec"], rtol=1e-12)
+    fp = {"logA": torch.tensor(st["logA"]), "lambda0": torch.tensor(st["lambda0"])}
+    lam_m, lam_var = torch.from_numpy(fx["lam_m"]), torch.from_numpy(fx["lam_var"])
+    f = U.mean_f_given_lambda_moments(fp, lam_m, lam_var)
+    assert np.allclose(f.numpy(), fx["f"], rtol=1e-12)
+    ll, d = U.compute_loglikelihood(prob.r, f, lam_m, lam_var, fp, compute_grad_for_f_params=True)
+    assert abs(float(ll) - float(fx["fpar_loglik"])) <= 1e-11 * abs(float(fx["fpar_loglik"]))
+    assert abs(float(d["logA"]) - float(fx["fpar_dlogA"])) <= 1e-10 * abs(float(fx["fpar_dlogA"]))
+    ll3 = U.compute_loglikelihood(prob.r, f, lam_m, lam_var, fp)
+    assert len(ll3) == 3 and float(ll3[2]) == float(prob.r.sum())
+    assert abs(float(U.lambda0_given_logA(fp["logA"], prob.r, lam_m, lam_var)) - float(fx["lambda0_closed"])) < 1e-12
+    # E-step against the reference's Estep output
+    Kt_b, Kinv = torch.from_numpy(fx["K_tilde_b"]), torch.from_numpy(fx["K_tilde_inv_b"])
+    Cm, mk = C, mask
+    a = (U.acosker(th, xm, um, C=Cm) @ st["B"]) @ Kinv
+    m_new, V_new = U.Estep(r=prob.r, KKtilde_inv=a, m=st["m_b"], f_params=fp, f_mean=torch.from_numpy(fx["f"]),
+                           K_tilde=Kt_b, K_tilde_inv=Kinv)
+    assert np.allclose(m_new.numpy(), fx["estep_m"], rtol=1e-8, atol=1e-11)
+    assert np.allclose(V_new.numpy(), fx["estep_V"], rtol=1e-8, atol=1e-11)
+    KL = U.compute_KL_div(st["m_b"], st["V_b"], Kt_b, Kinv)
+    assert abs(float(KL) - float(fx["KL"])) <= 1e-10 * abs(float(fx["KL"]))
+
+
+def test_log_det_fallback_semantics(U):
+    M = torch.diag(torch.tensor([2.0, 1.0, -1.0]))
+    with pytest.warns(UserWarning):
+        v = U.log_det(M, name="M")
+    assert abs(float(v) - math.log(2.0)) < 1e-12          # only eigenvalues > max(2e-4, 1e-4): {2, 1}
+    assert U.log_det(M, ignore_warning=True) is not None
+    A = torch.tensor([[1.0, 2.0], [0.0, 1.0]])
+    with pytest.warns(UserWarning):
+        assert U.log_det(A) == 0                           # not symmetric -> 0 with a warning (U:1302-1304)
