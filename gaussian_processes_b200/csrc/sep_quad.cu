@@ -1,0 +1,198 @@
+// Per-image quadratic forms x_i^T C x_i and x_i^T dC_k x_i through the SEPARABLE structure of localker's C.
+//
+// localker (utils.py:880-898) builds  C = Amp * D_a (G (x) G) D_a  on the pixel grid, with
+//   a_k = exp(-e^{theta_beta} |xi_k - eps_0|^2) (zero outside the receptive-field mask) and
+//   G_ab = exp(-e^{theta_rho} (lin_a - lin_b)^2), lin = linspace(-1, 1, n)  -- a Kronecker product of two n x n
+// Gaussian matrices, because exp(-rho((dx)^2 + (dy)^2)) factorises.  With M = (x o a) reshaped to n x n [iy][ix]:
+//   Sy = M G M^T, Sx = M^T G M, Ey = Sy o G, Ex = Sx o G, rsx/rsy = row sums of Ex/Ey, D2_ab = (lin_a - lin_b)^2
+//   x^T C x                    = Amp * sum(Ey)
+//   x^T dC_{-log2rho2} x       = -e^{theta_rho} Amp (sum(Ex o D2) + sum(Ey o D2))                  (utils.py:909)
+//   x^T dC_{eps_0x} x          = 4 e^{theta_beta} Amp sum_ix (lin_ix - eps_0x) rsx[ix]             (utils.py:904)
+//   x^T dC_{eps_0y} x          = 4 e^{theta_beta} Amp sum_iy (lin_iy - eps_0y) rsy[iy]             (utils.py:905)
+//   x^T dC_{-2log2beta} x      = -2 e^{theta_beta} Amp (sum (lin_ix-eps_0x)^2 rsx + sum (lin_iy-eps_0y)^2 rsy)  (U:907)
+// i.e. 8 n^3 flops per image instead of the 2 p^2 (value) + 2 p^2 (adjoint) of the dense products.
+//
+// One warp per image; the four n x n x n products run on the fp64 tensor pipe (DMMA m8n8k4).  The first product
+// of each chain stays in registers: its C fragments are turned into A fragments with quad shuffles.
+#include "sgp_common.cuh"
+#include "sgp_kernels.cuh"
+
+namespace sgp {
+
+namespace {
+
+constexpr int kSepWarps = 8;
+
+__device__ __forceinline__ double lin_coord_dev(int i, int n) {   // torch.linspace(-1, 1, n), as on the host
+  if (n == 1) return -1.0;
+  const double step = 2.0 / (double)(n - 1);
+  return (i < n / 2) ? (-1.0 + step * i) : (1.0 - step * (n - 1 - i));
+}
+
+// One chain for all row tiles.  TR = false: rows are iy (Sy = M G M^T); TR = true: rows are ix (Sx = M^T G M).
+// Returns per-lane partial sums: rs_tot = sum E, d2 = sum E o D2, a1 = sum phi*rs, a2 = sum phi^2*rs.
+template <int NT, bool TR>
+__device__ __forceinline__ void chain(const double* __restrict__ M, const double* __restrict__ G,
+                                      const double* __restrict__ lin, double center, int lane, double& rs_tot,
+                                      double& d2, double& a1, double& a2) {
+  constexpr int LD = 8 * NT + 4;
+  const int g = lane >> 2, t = lane & 3;
+#pragma unroll 1
+  for (int i = 0; i < NT; ++i) {
+    double P[NT][2];
+#pragma unroll
+    for (int j = 0; j < NT; ++j) P[j][0] = P[j][1] = 0.0;
+#pragma unroll
+    for (int kk = 0; kk < 2 * NT; ++kk) {
+      const int k = 4 * kk + t;
+      const double af = TR ? M[k * LD + 8 * i + g] : M[(8 * i + g) * LD + k];
+#pragma unroll
+      for (int j = 0; j < NT; ++j) dmma884(P[j][0], P[j][1], af, G[k * LD + 8 * j + g]);
+    }
+    double S[NT][2];
+#pragma unroll
+    for (int j = 0; j < NT; ++j) S[j][0] = S[j][1] = 0.0;
+#pragma unroll
+    for (int jk = 0; jk < NT; ++jk) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        // A fragment (row g, column 4h+t of tile jk) out of the C fragments (row g, columns 2t', 2t'+1)
+        const int src = (lane & ~3) | (2 * h + (t >> 1));
+        const double v0 = __shfl_sync(0xffffffffu, P[jk][0], src);
+        const double v1 = __shfl_sync(0xffffffffu, P[jk][1], src);
+        const double af = (t & 1) ? v1 : v0;
+        const int k = 8 * jk + 4 * h + t;
+#pragma unroll
+        for (int jn = 0; jn < NT; ++jn)
+          dmma884(S[jn][0], S[jn][1], af, TR ? M[k * LD + 8 * jn + g] : M[(8 * jn + g) * LD + k]);
+      }
+    }
+    const int a = 8 * i + g;
+    const double la = lin[a];
+    double rs = 0.0;
+#pragma unroll
+    for (int jn = 0; jn < NT; ++jn) {
+      const int b = 8 * jn + 2 * t;
+      const double2 gg = *reinterpret_cast<const double2*>(G + a * LD + b);
+      const double e0 = S[jn][0] * gg.x, e1 = S[jn][1] * gg.y;
+      const double d0 = la - lin[b], d1 = la - lin[b + 1];
+      rs += e0 + e1;
+      d2 += e0 * (d0 * d0) + e1 * (d1 * d1);
+    }
+    const double phi = la - center;
+    rs_tot += rs;
+    a1 += phi * rs;
+    a2 += (phi * phi) * rs;
+  }
+}
+
+template <int NT>
+__global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQuadArgs a) {
+  constexpr int NP = 8 * NT, LD = NP + 4;
+  extern __shared__ __align__(16) double sm[];
+  double* sG = sm;                 // NP x LD
+  double* sLin = sG + NP * LD;     // NP
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* sM = sLin + NP + (size_t)warp * NP * LD;
+
+  for (int e = tid; e < NP; e += blockDim.x) sLin[e] = (e < a.n) ? lin_coord_dev(e, a.n) : 0.0;
+  for (int e = tid; e < NP * LD; e += blockDim.x) {
+    const int r = e / LD, c = e % LD;
+    double v = 0.0;
+    if (r < a.n && c < a.n) {
+      const double d = lin_coord_dev(c, a.n) - lin_coord_dev(r, a.n);
+      v = exp(-a.er * (d * d));
+    }
+    sG[e] = v;
+  }
+  for (int e = lane; e < NP * LD; e += 32) sM[e] = 0.0;   // pixels outside the mask / padding stay zero
+  __syncthreads();
+
+  for (long img = (long)blockIdx.x * kSepWarps + warp; img < a.nrows; img += (long)gridDim.x * kSepWarps) {
+    const double* xr = a.X + img * a.ldx;
+    for (int c = lane; c < a.p; c += 32) sM[a.off[c]] = xr[c] * a.alpha[c];
+    __syncwarp();
+    double base = 0.0, dy = 0.0, ay1 = 0.0, ay2 = 0.0, bx = 0.0, dx = 0.0, ax1 = 0.0, ax2 = 0.0;
+    chain<NT, false>(sM, sG, sLin, a.ey, lane, base, dy, ay1, ay2);
+    chain<NT, true>(sM, sG, sLin, a.ex, lane, bx, dx, ax1, ax2);
+    __syncwarp();
+    base = warp_sum(base);
+    const double dd = warp_sum(dx + dy);
+    ax1 = warp_sum(ax1);
+    ay1 = warp_sum(ay1);
+    const double a2 = warp_sum(ax2 + ay2);
+    if (lane == 0) {
+      const double sq = a.amp * base;          // x^T C x
+      const double s = sq + a.s02;
+      a.s[img] = s;
+      a.nrm[img] = sqrt(s);
+      if (a.Q) {
+        double* q = a.Q + img * 5;             // units of the closure's gradient slots (see finalize_kernel)
+        q[0] = sq;                             // Amp        : <C, x x^T>
+        q[1] = -2.0 * a.eb * a.amp * a2;       // -2log2beta
+        q[2] = -a.er * a.amp * dd;             // -log2rho2
+        q[3] = 2.0 * a.amp * ax1;              // eps_0x / (2 e^{theta_beta})
+        q[4] = 2.0 * a.amp * ay1;              // eps_0y / (2 e^{theta_beta})
+      }
+    }
+  }
+}
+
+template <int NT>
+cudaError_t launch_sep(const SepQuadArgs& a, cudaStream_t st) {
+  constexpr int NP = 8 * NT, LD = NP + 4;
+  const size_t smem = (size_t)(NP * LD + NP + kSepWarps * NP * LD) * sizeof(double);
+  cudaError_t e = cudaFuncSetAttribute(sep_quad_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  long nb = (a.nrows + kSepWarps - 1) / kSepWarps;
+  if (nb > 148) nb = 148;
+  note_launch();
+  sep_quad_kernel<NT><<<(unsigned)nb, kSepWarps * 32, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+int sep_quad_tiles(int n_px) { return (n_px + 7) / 8; }
+bool sep_quad_supported(int n_px) { return n_px >= 1 && n_px <= 8 * kSepMaxTiles; }
+int sep_quad_ld(int n_px) { return 8 * sep_quad_tiles(n_px) + 4; }
+
+cudaError_t sep_quad(const SepQuadArgs& a, cudaStream_t st) {
+  if (a.nrows <= 0) return cudaSuccess;
+  switch (sep_quad_tiles(a.n)) {
+    case 1: return launch_sep<1>(a, st);
+    case 2: return launch_sep<2>(a, st);
+    case 3: return launch_sep<3>(a, st);
+    case 4: return launch_sep<4>(a, st);
+    case 5: return launch_sep<5>(a, st);
+    case 6: return launch_sep<6>(a, st);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+// blockpart[blk*5 + k] = sum_{i in blk} w_i Q[i][k]
+__global__ void __launch_bounds__(256) wq_reduce_kernel(const double* __restrict__ w, const double* __restrict__ Q,
+                                                        long n, double* __restrict__ blockpart) {
+  __shared__ double red[32];
+  double acc[5] = {0, 0, 0, 0, 0};
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const double wi = w[i];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) acc[k] += wi * Q[i * 5 + k];
+  }
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const double sres = block_sum(acc[k], red);
+    if (threadIdx.x == 0) blockpart[(long)blockIdx.x * 5 + k] = sres;
+  }
+}
+int wq_reduce_blocks(long n) {
+  long nb = (n + 1023) / 1024;
+  return (int)(nb < 1 ? 1 : (nb > 296 ? 296 : nb));
+}
+void wq_reduce(const double* w, const double* Q, long n, double* blockpart, cudaStream_t st) {
+  note_launch();
+  wq_reduce_kernel<<<wq_reduce_blocks(n), 256, 0, st>>>(w, Q, n, blockpart);
+}
+
+}  // namespace sgp

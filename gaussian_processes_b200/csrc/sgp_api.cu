@@ -43,7 +43,8 @@ struct sgp_handle {
   long launches_base = 0;
   bool gemm_ready = false;
   // scratch arena (re-carved every call) + persistent caches
-  DevBuf arena, xg, ug, gcpart, s2part;
+  DevBuf arena, xg, ug, gcpart, s2part, dpart;
+  int path = 0;             // 0 = choose per (n, p); 1 = dense C products; 2 = separable quadratic forms
   // cache key of the gathered copies
   const double* cache_X = nullptr; long cache_N = 0, cache_ldx = 0;
   const double* cache_U = nullptr; long cache_m = 0, cache_ldu = 0;
@@ -183,7 +184,7 @@ int sgp_destroy(sgp_handle* h) {
   if (!h) return SGP_OK;
   if (h->gemm_ready) {
     cudaSetDevice(h->device);
-    h->arena.release(); h->xg.release(); h->ug.release(); h->gcpart.release(); h->s2part.release();
+    h->arena.release(); h->xg.release(); h->ug.release(); h->gcpart.release(); h->s2part.release(); h->dpart.release();
     h->hx[0].release(); h->hx[1].release(); h->hr.release(); h->small.release();
     if (h->d_flags) cudaFree(h->d_flags);
     if (h->d_scal) cudaFree(h->d_scal);
@@ -213,6 +214,7 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
   const std::string n(name);
   if (n == "kl_weight") h->kl_weight = value;
   else if (n == "profile") h->profile = value != 0.0;
+  else if (n == "path") h->path = (int)value;
   else if (n == "slab_rows") return sgp_set_slab_rows(h, (long)value);
   else return fail(h, SGP_E_ARG, "sgp_set_option: unknown option " + n);
   return SGP_OK;
@@ -386,6 +388,20 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const int ntp = (int)((p + 127) / 128), ntm = (int)((m + 127) / 128);
   const int ntp_s = (int)((p + 63) / 64);
   const bool full_mask = (p == P);
+  // separable path (sep_quad.cu): 8 n^3 flops per image for the quadratic forms instead of 4 p^2 dense ones
+  bool use_sep = sep_quad_supported(n) && (12.0 * n * n * n < 4.0 * (double)p * p);
+  if (h->path == 1) use_sep = false;
+  if (h->path == 2) use_sep = sep_quad_supported(n);
+  std::vector<int> off; std::vector<double> alpha;
+  if (use_sep) {
+    const int ldq_sep = sep_quad_ld(n);
+    off.resize(p); alpha.resize(p);
+    for (int c = 0; c < p; ++c) {
+      const int iy = idx[c] / n, ix = idx[c] % n;
+      off[c] = iy * ldq_sep + ix;
+      alpha[c] = std::exp(-th.eb * ((gx[c] - th.ex) * (gx[c] - th.ex) + (gy[c] - th.ey) * (gy[c] - th.ey)));
+    }
+  }
 
   // ---- gathered / aligned copies of the images (cached across calls while the mask is unchanged) --
   const bool direct_X = !streaming && full_mask && (in.ldx % 2 == 0) && ((uintptr_t)in.X % 16 == 0);
@@ -412,7 +428,11 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   for (int i = 0; i < 14; ++i) acc((size_t)q * ldq);                  // q x q scratch
   acc(64 * ldq);                                                      // tri-inverse tmp
   for (int i = 0; i < 12; ++i) acc(ldm);                              // small vectors
-  acc((size_t)slab * ldp);                                            // Z / Y
+  acc(use_sep ? 1 : (size_t)slab * ldp);                              // Z / Y (dense path only)
+  if (use_sep) {
+    acc((size_t)(p + 1) / 2 + 8); acc(p); acc((size_t)slab * 5); acc((size_t)wq_reduce_blocks(slab) * 5);
+    acc((size_t)p * ldm);                                             // D = X^T R
+  }
   for (int i = 0; i < 3; ++i) acc((size_t)slab * ldm);                // K, cos, T/R
   for (int i = 0; i < 6; ++i) acc(slab);                              // s, X1, u, v, w (+1)
   for (int i = 0; i < 3; ++i) acc(N);                                 // lam_m, lam_var, f (when not supplied)
@@ -441,7 +461,15 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* qq[14]; for (int i = 0; i < 14; ++i) qq[i] = ar.take<double>((size_t)q * ldq);
   double* tri_tmp = ar.take<double>(64 * ldq);
   double* vecs[12]; for (int i = 0; i < 12; ++i) vecs[i] = ar.take<double>(ldm);
-  double* Zs = ar.take<double>((size_t)slab * ldp);
+  double* Zs = ar.take<double>(use_sep ? 1 : (size_t)slab * ldp);
+  int* d_off = nullptr; double* d_alpha = nullptr; double* Qs = nullptr; double* wqpart = nullptr; double* Dm = nullptr;
+  if (use_sep) {
+    d_off = (int*)ar.take<double>((size_t)(p + 1) / 2 + 8);
+    d_alpha = ar.take<double>(p);
+    Qs = ar.take<double>((size_t)slab * 5);
+    wqpart = ar.take<double>((size_t)wq_reduce_blocks(slab) * 5);
+    Dm = ar.take<double>((size_t)p * ldm);
+  }
   double* Ks = ar.take<double>((size_t)slab * ldm); double* cos_s = ar.take<double>((size_t)slab * ldm);
   double* Ts = ar.take<double>((size_t)slab * ldm);
   double* s_s = ar.take<double>(slab); double* X1 = ar.take<double>(slab); double* u_s = ar.take<double>(slab);
@@ -473,6 +501,10 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   CU(cudaMemcpyAsync(d_idx, idx.data(), sizeof(int) * p, cudaMemcpyHostToDevice, st));
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
   CU(cudaMemsetAsync(h->d_scal, 0, sizeof(double) * kNumSlots, st));
+  if (use_sep) {
+    CU(cudaMemcpyAsync(d_off, off.data(), sizeof(int) * p, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_alpha, alpha.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
+  }
   if (regather) {
     if (!direct_X && !streaming) gather_cols(in.X, in.ldx, N, d_idx, p, (double*)Xg, ldp, st);
     if (!direct_U) gather_cols(in.U, in.ldu, m, d_idx, p, (double*)Ug, ldp, st);
@@ -524,8 +556,11 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
 
   // ---- split-K plans for the two reductions over images ----------------------------------------------
   const int tilesGC = ntp * ntp, tilesS2 = ntm * ntm;
-  const int nzGC = pick_split(tilesGC, slab), nzS2 = pick_split(tilesS2, slab);
-  const long zGC = (long)p * ldp, zS2 = (long)m * ldm;
+  const int nzGC = use_sep ? 1 : pick_split(tilesGC, slab), nzS2 = pick_split(tilesS2, slab);
+  const int nzD = pick_split(ntp * ntm, slab);
+  const long zGC = (long)p * ldp, zS2 = (long)m * ldm, zD = (long)p * ldm;
+  if (use_sep) CU(h->dpart.reserve((size_t)nzD * zD * sizeof(double)));
+  double* Dpart = (double*)h->dpart.p;
   CU(h->gcpart.reserve((size_t)nzGC * zGC * sizeof(double)));
   CU(h->s2part.reserve((size_t)nzS2 * zS2 * sizeof(double)));
   double* GCpart = (double*)h->gcpart.p; double* S2part = (double*)h->s2part.p;
@@ -575,16 +610,29 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       Xs = Xg + i0 * ldxg; ldxs = ldxg;
     }
     mark(1);
-    // G1: Z = X C, partial s_i = x_i^T C x_i                                  (U:978, U:1029)
-    GemmArgs g1{};
-    g1.A = Xs; g1.lda = ldxs; g1.B = C; g1.ldb = ldp; g1.C = Zs; g1.ldc = ldp; g1.M = (int)ns; g1.N = p; g1.K = p;
-    g1.aux = Xs; g1.ldaux = ldxs; g1.part1 = partN; g1.ldpart = ldpartN;
-    CU(gemm(st, 0, 1, kRowdot, false, 1, g1));
-    mark(2);
-    norms_finalize(partN, ldpartN, ntp, ns, th.s02, s_s, X1, st);
-    // G2: K = acos-kernel(Z Ug^T)                                             (U:982-990)
     GemmArgs g2{};
-    g2.A = Zs; g2.lda = ldp; g2.B = Ug; g2.ldb = ldug; g2.C = Ks; g2.ldc = ldm; g2.M = (int)ns; g2.N = m; g2.K = p;
+    if (use_sep) {
+      // s_i = x_i^T C x_i + sigma_0^2 and the five x_i^T dC_k x_i from the Kronecker structure of C (sep_quad.cu)
+      SepQuadArgs sq{};
+      sq.X = Xs; sq.ldx = ldxs; sq.nrows = ns; sq.p = p; sq.off = d_off; sq.alpha = d_alpha; sq.n = n;
+      sq.er = th.er; sq.eb = th.eb; sq.ex = th.ex; sq.ey = th.ey; sq.amp = th.amp; sq.s02 = th.s02;
+      sq.s = s_s; sq.nrm = X1; sq.Q = Qs;
+      CU(sep_quad(sq, st));
+      mark(2);
+      // G2: K = acos-kernel(X (U C)^T)   -- x_i^T C u_j with the m x p matrix ZU = U C
+      g2.A = Xs; g2.lda = ldxs; g2.B = ZU; g2.ldb = ldp;
+    } else {
+      // G1: Z = X C, partial s_i = x_i^T C x_i                                  (U:978, U:1029)
+      GemmArgs g1{};
+      g1.A = Xs; g1.lda = ldxs; g1.B = C; g1.ldb = ldp; g1.C = Zs; g1.ldc = ldp; g1.M = (int)ns; g1.N = p; g1.K = p;
+      g1.aux = Xs; g1.ldaux = ldxs; g1.part1 = partN; g1.ldpart = ldpartN;
+      CU(gemm(st, 0, 1, kRowdot, false, 1, g1));
+      mark(2);
+      norms_finalize(partN, ldpartN, ntp, ns, th.s02, s_s, X1, st);
+      // G2: K = acos-kernel(Z Ug^T)                                             (U:982-990)
+      g2.A = Zs; g2.lda = ldp; g2.B = Ug; g2.ldb = ldug;
+    }
+    g2.C = Ks; g2.ldc = ldm; g2.M = (int)ns; g2.N = m; g2.K = p;
     g2.rowvec = X1; g2.colvec = X2; g2.C2 = cos_s; g2.s02 = th.s02;
     CU(gemm(st, 0, 0, kAcos, false, 1, g2));
     mark(3);
@@ -609,17 +657,29 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     sum_to_slot(sumpartR, nbb, 1, 1.0, h->d_scal, kSlotSig, 1, st);
     sum_to_slot(w_s, ns, 1, 1.0, h->d_scal, kSlotSig, 1, st);
     mark(5);
-    // G4: Y = R Ug + diag(w) X   (into the Z buffer)
-    GemmArgs g4{};
-    g4.A = Ts; g4.lda = ldm; g4.B = Ug; g4.ldb = ldug; g4.C = Zs; g4.ldc = ldp; g4.M = (int)ns; g4.N = p; g4.K = m;
-    g4.rowvec = w_s; g4.aux = Xs; g4.ldaux = ldxs;
-    CU(gemm(st, 0, 1, kAxpyRow, false, 1, g4));
-    mark(6);
-    // G5: GC += X^T Y   (split-K over the images of the slab)
-    GemmArgs g5{};
-    g5.A = Xs; g5.lda = ldxs; g5.B = Zs; g5.ldb = ldp; g5.C = GCpart; g5.ldc = ldp; g5.M = p; g5.N = p; g5.K = (int)ns;
-    g5.k_chunk = (int)rup((ns + nzGC - 1) / nzGC, 16); g5.zstride = zGC; g5.accumulate = acc_flag;
-    CU(gemm(st, 1, 1, kStore, false, nzGC, g5));
+    if (use_sep) {
+      // sum_i w_i x_i^T dC_k x_i from the stored quadratic forms; D += X^T R (split-K over the images of the slab)
+      wq_reduce(w_s, Qs, ns, wqpart, st);
+      for (int k = 0; k < 5; ++k)
+        sum_to_slot(wqpart + k, wq_reduce_blocks(ns), 5, 1.0, h->d_scal, kSlotGW + k, acc_flag, st);
+      mark(6);
+      GemmArgs g5{};
+      g5.A = Xs; g5.lda = ldxs; g5.B = Ts; g5.ldb = ldm; g5.C = Dpart; g5.ldc = ldm; g5.M = p; g5.N = m; g5.K = (int)ns;
+      g5.k_chunk = (int)rup((ns + nzD - 1) / nzD, 16); g5.zstride = zD; g5.accumulate = acc_flag;
+      CU(gemm(st, 1, 1, kStore, false, nzD, g5));
+    } else {
+      // G4: Y = R Ug + diag(w) X   (into the Z buffer)
+      GemmArgs g4{};
+      g4.A = Ts; g4.lda = ldm; g4.B = Ug; g4.ldb = ldug; g4.C = Zs; g4.ldc = ldp; g4.M = (int)ns; g4.N = p; g4.K = m;
+      g4.rowvec = w_s; g4.aux = Xs; g4.ldaux = ldxs;
+      CU(gemm(st, 0, 1, kAxpyRow, false, 1, g4));
+      mark(6);
+      // G5: GC += X^T Y   (split-K over the images of the slab)
+      GemmArgs g5{};
+      g5.A = Xs; g5.lda = ldxs; g5.B = Zs; g5.ldb = ldp; g5.C = GCpart; g5.ldc = ldp; g5.M = p; g5.N = p; g5.K = (int)ns;
+      g5.k_chunk = (int)rup((ns + nzGC - 1) / nzGC, 16); g5.zstride = zGC; g5.accumulate = acc_flag;
+      CU(gemm(st, 1, 1, kStore, false, nzGC, g5));
+    }
     mark(7);
     // G6: Sig2 += K^T diag(v) K
     GemmArgs g6{};
@@ -667,8 +727,14 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   }
 
   // ---- <dC_k, GC> and result assembly -----------------------------------------------------------------------
+  if (use_sep) {
+    slice_reduce(Dpart, nzD, zD, zD, Dm, 0, st);
+    CU(mm(st, 0, 1, Dm, ldm, Ug, ldug, GCpart, ldp, p, p, m));                           // (X^T R) U
+  }
   contract_dC(GCpart, nzGC, zGC, GCU, C, ldp, p, d_gx, d_gy, th, gpart, st);
   for (int k = 0; k < 5; ++k) sum_to_slot(gpart + k, p, 5, 1.0, h->d_scal, kSlotG + k, 0, st);
+  if (use_sep)
+    for (int k = 0; k < 5; ++k) sum_to_slot(h->d_scal + kSlotGW + k, 1, 1, 1.0, h->d_scal, kSlotG + k, 1, st);
   finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p, in.logdetV_host ? *in.logdetV_host : 0.0,
            in.logdetV_host ? 1 : 0, h->d_out, st);
   CU(cudaGetLastError());

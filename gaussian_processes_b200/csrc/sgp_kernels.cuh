@@ -22,6 +22,7 @@ enum ScalSlot : int {
   kSlotSig = 8,            // sum R + sum w + sum beta + sum R~ + sum w~   (sigma_0 gradient / (2 sigma_0))
   kSlotG = 9,              // 5 slots: <dC_k, GC> for Amp, -2log2beta, -log2rho2, eps_0x, eps_0y
   kSlotAux0 = 14, kSlotAux1 = 15, kSlotAux2 = 16, kSlotAux3 = 17,
+  kSlotGW = 22,            // 5 slots: sum_i w_i x_i^T dC_k x_i (separable path), added to kSlotG at the end
   kNumSlots = 32
 };
 
@@ -133,5 +134,23 @@ int colsum_blocks(long n);
 void colsum_weighted(const double* a, long lda, long n, int q, const double* r, const double* f, double* colpart,
                      long ldcol, cudaStream_t st);
 void scale_vec(double* x, long n, double alpha, cudaStream_t st);
+
+// ---- separable evaluation of the per-image quadratic forms (sep_quad.cu) ------------------------------
+// s_i = x_i^T C x_i + sigma_0^2, nrm_i = sqrt(s_i) and Q[i][5] = x_i^T dC_k x_i in the units of the closure's
+// gradient slots (Amp, -2log2beta, -log2rho2, eps_0x, eps_0y), from the Kronecker structure of localker's C.
+// X: gathered images (nrows x p, ld = ldx); off[c] = iy*sep_quad_ld(n) + ix of masked pixel c; alpha[c] = RF envelope.
+constexpr int kSepMaxTiles = 6;   // n_px_side <= 48
+struct SepQuadArgs {
+  const double* X; long ldx; long nrows; int p;
+  const int* off; const double* alpha;
+  int n;
+  double er, eb, ex, ey, amp, s02;
+  double* s; double* nrm; double* Q;   // Q may be null (value only)
+};
+bool sep_quad_supported(int n_px);
+int sep_quad_ld(int n_px);
+cudaError_t sep_quad(const SepQuadArgs& a, cudaStream_t st);
+int wq_reduce_blocks(long n);
+void wq_reduce(const double* w, const double* Q, long n, double* blockpart, cudaStream_t st);
 
 }  // namespace sgp

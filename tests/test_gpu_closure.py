@@ -10,16 +10,19 @@ CASES = ["closure_dense_n8", "closure_local_n12", "closure_rankdef_n10", "closur
 RTOL = 1e-9   # north_star: 1e-9 relative in fp64
 
 
-def run_case(name, slab=None):
+def run_case(name, slab=None, path=0):
+    """path: 0 = library's choice, 1 = dense C products, 2 = separable quadratic forms (sep_quad.cu)"""
     from gaussian_processes_b200 import native
     fx = load(name)
     prob, st = case_inputs(fx)
     d = torch.device("cuda:0")
     native.set_slab_rows(0, slab if slab else 0)
+    native.set_option(0, "path", path)
     out = native.elbo_grad(prob.X.to(d), prob.r.to(d), prob.xtilde.to(d), prob.n_px_side, prob.theta,
                            st["B"].to(d), st["m_b"].to(d), st["V_b"].to(d), st["logA"], st["lambda0"],
                            want_moments=True)
     native.set_slab_rows(0, 0)
+    native.set_option(0, "path", 0)
     return fx, out
 
 
@@ -38,16 +41,18 @@ def check(fx, out):
     assert np.allclose(out["f"].cpu().numpy(), fx["f"], rtol=RTOL, atol=0)
 
 
+@pytest.mark.parametrize("path", [0, 1, 2])
 @pytest.mark.parametrize("name", CASES)
-def test_closure_against_reference(name):
-    fx, out = run_case(name)
+def test_closure_against_reference(name, path):
+    fx, out = run_case(name, path=path)
     check(fx, out)
 
 
 @pytest.mark.parametrize("name", ["closure_c1_dense", "closure_local_n12"])
-def test_closure_multi_slab(name):
+@pytest.mark.parametrize("path", [1, 2])
+def test_closure_multi_slab(name, path):
     # ragged slabs: N is not a multiple of the slab
-    fx, out = run_case(name, slab=128)
+    fx, out = run_case(name, slab=128, path=path)
     check(fx, out)
 
 
