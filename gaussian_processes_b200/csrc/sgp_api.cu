@@ -40,6 +40,7 @@ struct sgp_handle {
   int device = 0;
   std::string err;
   long slab_rows = 65536;
+  long stream_slab_rows = 16384;   // host-streaming variant: smaller slabs so H2D copies overlap the compute earlier
   long launches_base = 0;
   bool gemm_ready = false;
   // scratch arena (re-carved every call) + persistent caches
@@ -206,6 +207,7 @@ const char* sgp_last_error(const sgp_handle* h) { return h ? h->err.c_str() : "n
 int sgp_set_slab_rows(sgp_handle* h, long rows) {
   if (!h) return SGP_E_ARG;
   h->slab_rows = rows > 0 ? rup(rows, 128) : 65536;
+  h->stream_slab_rows = rows > 0 ? std::min<long>(rup(rows, 128), 16384) : 16384;
   return SGP_OK;
 }
 
@@ -383,7 +385,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const ThetaDev th = make_theta(in.theta);
   const double A = std::exp(in.logA);
   const long ldp = rup(p, 16), ldm = rup(m, 16), ldq = rup(q, 16);
-  const long slab = std::min<long>(h->slab_rows, rup(N, 128));
+  const long slab = std::min<long>(streaming ? h->stream_slab_rows : h->slab_rows, rup(N, 128));
   const long ldpartN = rup(slab, 16), ldpartU = ldm;
   const int ntp = (int)((p + 127) / 128), ntm = (int)((m + 127) / 128);
   const int ntp_s = (int)((p + 63) / 64);
@@ -588,9 +590,13 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     const int bsel = si & 1;
     cudaError_t e;
     if (si >= 2 && (e = cudaStreamWaitEvent(h->copy_stream, h->ev_used[bsel], 0)) != cudaSuccess) return e;
-    if ((e = cudaMemcpy2DAsync(h->hx[bsel].p, P * sizeof(double), in.X_host + i0 * in.ldx, in.ldx * sizeof(double),
-                               P * sizeof(double), ns, cudaMemcpyHostToDevice, h->copy_stream)) != cudaSuccess)
-      return e;
+    if (in.ldx == P)
+      e = cudaMemcpyAsync(h->hx[bsel].p, in.X_host + i0 * in.ldx, (size_t)ns * P * sizeof(double),
+                          cudaMemcpyHostToDevice, h->copy_stream);
+    else
+      e = cudaMemcpy2DAsync(h->hx[bsel].p, P * sizeof(double), in.X_host + i0 * in.ldx, in.ldx * sizeof(double),
+                            P * sizeof(double), ns, cudaMemcpyHostToDevice, h->copy_stream);
+    if (e != cudaSuccess) return e;
     return cudaEventRecord(h->ev_copied[bsel], h->copy_stream);
   };
   const int nslabs = (int)((N + slab - 1) / slab);
@@ -633,8 +639,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       g2.A = Zs; g2.lda = ldp; g2.B = Ug; g2.ldb = ldug;
     }
     g2.C = Ks; g2.ldc = ldm; g2.M = (int)ns; g2.N = m; g2.K = p;
-    g2.rowvec = X1; g2.colvec = X2; g2.C2 = cos_s; g2.s02 = th.s02;
-    CU(gemm(st, 0, 0, kAcos, false, 1, g2));
+    CU(gemm(st, 0, 0, kStore, false, 1, g2));
+    mark(9);
+    acos_forward(Ks, cos_s, ldm, ns, m, X1, X2, th.s02, st);
     mark(3);
     // G3: T = K Mfull^T ; partial lam_var / lam_m row sums                    (U:1090-1101)
     GemmArgs g3{};

@@ -143,6 +143,38 @@ void moments_rows(const double* s, const double* part1, const double* part2, lon
 }
 
 // =====================================================================================================
+// arc-cosine map as its own streaming pass (utils.py:982-990): K <- X1X2 * J(cos), cos stored beside it.
+// Run at full occupancy so the long fp64 acos/sqrt/div dependency chains overlap across many warps
+// (as a GEMM epilogue they ran on 8 warps per SM with nothing to hide their latency).
+// =====================================================================================================
+__global__ void __launch_bounds__(256) acos_forward_kernel(double* __restrict__ K, double* __restrict__ cosm, long ld,
+                                                           long n, int m, const double* __restrict__ na,
+                                                           const double* __restrict__ nb, double s02) {
+  const int m2 = (m + 1) >> 1;
+  const long total = n * m2;
+  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
+    const long i = e / m2;
+    const int j = (int)(e - i * m2) * 2;
+    const long o = i * ld + j;
+    const double nai = __ldg(na + i);
+    const double2 lin = *reinterpret_cast<const double2*>(K + o);   // ld is even, padding columns are in bounds
+    double c0, c1 = 0.0;
+    const double k0 = acos_kernel_value(lin.x + s02, nai * __ldg(nb + j), &c0);
+    const double k1 = (j + 1 < m) ? acos_kernel_value(lin.y + s02, nai * __ldg(nb + j + 1), &c1) : 0.0;
+    *reinterpret_cast<double2*>(K + o) = make_double2(k0, k1);
+    *reinterpret_cast<double2*>(cosm + o) = make_double2(c0, c1);
+  }
+}
+void acos_forward(double* K, double* cosm, long ld, long n, int m, const double* na, const double* nb, double s02,
+                  cudaStream_t st) {
+  if (n <= 0 || m <= 0) return;
+  const long total = n * ((m + 1) >> 1);
+  long nb_ = (total + 255) / 256;
+  if (nb_ > 148L * 32) nb_ = 148L * 32;
+  note_launch(); acos_forward_kernel<<<(unsigned)nb_, 256, 0, st>>>(K, cosm, ld, n, m, na, nb, s02);
+}
+
+// =====================================================================================================
 // adjoint of the arc-cosine nonlinearity (reference local partials utils.py:996-1021)
 // =====================================================================================================
 template <int MODE>
@@ -389,47 +421,54 @@ void col_weights(const double* ka, const double* kb, const double* extra, const 
 // =====================================================================================================
 constexpr int kNB = 64;
 
-// Block 0 factors the diagonal block and writes it back; blocks >= 1 redo the tiny factorisation in shared
-// memory (cheaper than a second launch) and solve 64 rows of the panel:  X * L11^T = A21.
-__global__ void __launch_bounds__(kNB) chol_panel_kernel(double* __restrict__ A, long ld, int n, int j0, int nb,
-                                                         int* __restrict__ flags, int bit_notpd, int bit_small) {
+// Every block factors the 64x64 diagonal block in shared memory (right-looking, all 256 threads share each
+// rank-1 update; redoing the tiny factorisation is cheaper than a second launch).  Block 0 writes it back;
+// blocks >= 1 solve 256 rows of the panel below it, one row per thread:  X * L11^T = A21.
+constexpr int kCholThreads = 256;
+__global__ void __launch_bounds__(kCholThreads) chol_panel_kernel(double* __restrict__ A, long ld, int n, int j0,
+                                                                  int nb, int* __restrict__ flags, int bit_notpd,
+                                                                  int bit_small) {
   __shared__ double D[kNB][kNB + 1];
   const int tid = threadIdx.x;
   // load the diagonal block (lower triangle), identity-padded to 64x64
-  for (int r = 0; r < kNB; ++r) {
-    double v = (r == tid) ? 1.0 : 0.0;
-    if (r < nb && tid < nb) v = (tid <= r) ? A[(long)(j0 + r) * ld + j0 + tid] : 0.0;
-    D[r][tid] = v;
+  for (int e = tid; e < kNB * kNB; e += kCholThreads) {
+    const int r = e >> 6, c = e & 63;
+    double v = (r == c) ? 1.0 : 0.0;
+    if (r < nb && c < nb) v = (c <= r) ? A[(long)(j0 + r) * ld + j0 + c] : 0.0;
+    D[r][c] = v;
   }
+  __syncthreads();
   int bad = 0;
+  const int row = tid & 63, cg = tid >> 6;
   for (int k = 0; k < kNB; ++k) {
-    __syncthreads();
     const double d = D[k][k];
     if (k < nb) {
       if (!(d > 0.0)) bad |= bit_notpd;
       else if (sqrt(d) < 1e-10) bad |= bit_small;
     }
     const double lkk = sqrt(d > 0.0 ? d : 1.0);   // keep going with a harmless pivot; the flag tells the host
-    __syncthreads();
+    __syncthreads();                              // everyone has read D[k][k]
     if (tid == k) D[k][k] = lkk;
-    if (tid > k) D[tid][k] /= lkk;
+    if (tid > k && tid < kNB) D[tid][k] /= lkk;
     __syncthreads();
-    if (tid > k) {
-      const double lik = D[tid][k];
-      for (int l = k + 1; l <= tid; ++l) D[tid][l] -= lik * D[l][k];
+    if (row > k) {
+      const double lik = D[row][k];
+      for (int l = k + 1 + cg; l <= row; l += 4) D[row][l] -= lik * D[l][k];
     }
+    __syncthreads();
   }
-  __syncthreads();
   if (blockIdx.x == 0) {
     if (tid == 0 && bad) atomicOr(flags, bad);
-    for (int r = 0; r < nb; ++r)
-      if (tid < nb) A[(long)(j0 + r) * ld + j0 + tid] = (tid <= r) ? D[r][tid] : 0.0;
+    for (int e = tid; e < nb * nb; e += kCholThreads) {
+      const int r = e / nb, c = e % nb;
+      A[(long)(j0 + r) * ld + j0 + c] = (c <= r) ? D[r][c] : 0.0;
+    }
     return;
   }
-  // ---- TRSM: rows r0 .. r0+63 of the panel below the diagonal block (one row per thread)
-  const int row = j0 + nb + (blockIdx.x - 1) * kNB + tid;
-  if (row < n) {
-    double* ap = A + (long)row * ld + j0;
+  // ---- TRSM: 256 rows of the panel below the diagonal block (one row per thread)
+  const int arow = j0 + nb + (blockIdx.x - 1) * kCholThreads + tid;
+  if (arow < n) {
+    double* ap = A + (long)arow * ld + j0;
     double x[kNB];
 #pragma unroll
     for (int k = 0; k < kNB; ++k) x[k] = (k < nb) ? ap[k] : 0.0;
@@ -450,7 +489,7 @@ cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd,
   for (int j0 = 0; j0 < n; j0 += kNB) {
     const int nb = (n - j0) < kNB ? (n - j0) : kNB;
     const int rem = n - j0 - nb;
-    note_launch(); chol_panel_kernel<<<1 + cdiv(rem, kNB), kNB, 0, st>>>(A, ld, n, j0, nb, flags, bit_notpd, bit_small);
+    note_launch(); chol_panel_kernel<<<1 + cdiv(rem, kCholThreads), kCholThreads, 0, st>>>(A, ld, n, j0, nb, flags, bit_notpd, bit_small);
     if (rem > 0) {
       GemmArgs g{};
       const int j1 = j0 + nb;

@@ -56,6 +56,10 @@ void moments_rows(const double* s, const double* part1, const double* part2, lon
                   const double* r, long n, double A, double lambda0, double* lam_m, double* lam_var, double* f,
                   double* u, double* v, double* blockpart, cudaStream_t st);
 
+// ---- arc-cosine map, in place: K holds x1^T C x2 on entry (n x m, ld even), K = X1X2*J and cos on exit ----
+void acos_forward(double* K, double* cosm, long ld, long n, int m, const double* na, const double* nb, double s02,
+                  cudaStream_t st);
+
 // ---- adjoint of the arc-cosine nonlinearity (N x m elementwise + row/column reductions) ----
 // mode 0: GK_ij = u_i*bb_j + v_i*G_ij ; mode 1: GK_ij = G_ij.
 // G is overwritten with R = GK*P.  rowout_i = (mode0 ? v_i : 0) + 0.5*rho_i/na_i,

@@ -305,8 +305,8 @@ def launch_count(device: int = 0, reset: bool = False) -> int:
     return _lib.handle_for(device).launch_count(reset)
 
 
-STAGES = ("setup+inducing_fwd", "gemm_XC", "gemm_acos", "gemm_moments", "rows+acos_adjoint", "gemm_RU", "gemm_XtY",
-          "gemm_KtvK", "tail_qxq+inducing_bwd+contract")
+STAGES = ("setup+inducing_fwd", "quad_forms", "gemm_X_UC", "gemm_moments", "rows+acos_adjoint", "wq_reduce", "gemm_XtR",
+          "gemm_KtvK", "tail_qxq+inducing_bwd+contract", "acos_map")
 
 
 def set_option(device: int, name: str, value: float):

@@ -62,9 +62,10 @@ SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
  * CUDA events at the stage boundaries of sgp_elbo_grad), "slab_rows".                                          */
 SGP_API int sgp_set_option(sgp_handle* h, const char* name, double value);
 /* accumulated per-stage device milliseconds of sgp_elbo_grad since the last reset:
- * [0] setup + inducing-point forward, [1] X*C GEMM, [2] acos-kernel GEMM, [3] moments GEMM, [4] per-image
- * moments + adjoint of the acos map, [5] R*U GEMM, [6] X^T*Y GEMM, [7] K^T diag(v) K GEMM, [8] q x q adjoint,
- * inducing-point backward, <dC,GC> contraction.                                                                */
+ * [0] setup + inducing-point forward, [1] per-image quadratic forms (separable kernel, or the dense X*C GEMM),
+ * [2] GEMM X (U C)^T (dense path: Z U^T), [3] moments GEMM, [4] per-image moments + adjoint of the acos map,
+ * [5] sum w_i x_i^T dC_k x_i (dense path: R*U GEMM), [6] GEMM X^T R (dense path: X^T Y), [7] K^T diag(v) K GEMM,
+ * [8] q x q adjoint, inducing-point backward, <dC,GC> contraction, [9] arc-cosine map (streaming pass).          */
 SGP_API int sgp_get_profile(sgp_handle* h, double* stage_ms_out, int n, long* calls_out, int reset);
 /* forget the cached masked copies of X / xtilde (call if their contents changed in place) */
 SGP_API int sgp_invalidate_cache(sgp_handle* h);
