@@ -7,11 +7,12 @@
 //   AL/BL = 1 : "MN-major" -- element (row, k) at ptr[k*ld + row]   (row contiguous)
 // so X*C, Z*U^T, X^T*Y (reduction over images), K^T diag(v) K ... are all this one kernel.
 //
-// Tiling: CTA tile BM x BN x 16, 8 warps as 2(m) x 4(n); each warp owns (BM/2) x (BN/4) as
-// (BM/16) x (BN/32) DMMA 8x8 accumulators.  4-stage cp.async pipeline; shared-memory rows are
-// padded (+4 doubles) so every fragment LDS.64 is bank-conflict free:
-//   K-major  tile [rows][16+4] : addr = row*20 + k   -> (g*4 + t) mod 16 distinct per half-warp
-//   MN-major tile [16][rows+4] : addr = k*(BM+4)+row -> (t*4 + g) mod 16 distinct per half-warp
+// Tiling: CTA tile BM x BN x kBK (32), 8 warps as 2(m) x 4(n); each warp owns (BM/2) x (BN/4) as
+// (BM/16) x (BN/32) DMMA 8x8 accumulators.  3-stage cp.async pipeline (216 KB of shared memory for the
+// 128 x 128 tile; measured +3 % over 4 stages of k-depth 16: half as many block barriers); shared-memory rows
+// are padded (+4 doubles) so every fragment LDS.64 is bank-conflict free:
+//   K-major  tile [rows][kBK+4] : addr = row*36 + k   -> (g*4 + t) mod 16 distinct per half-warp
+//   MN-major tile [kBK][rows+4] : addr = k*(BM+4)+row -> (t*4 + g) mod 16 distinct per half-warp
 // Fused epilogues (MODE) implement the per-image reductions of the Spatial_GP pass, see below.
 #pragma once
 #include "sgp_common.cuh"
@@ -39,10 +40,17 @@ struct GemmArgs {
   const double* rowvec; const double* colvec;
   double* part1; double* part2; long ldpart;
   double* C2; double s02;
+  int lower_only;         // kStore with M == N: skip CTA tiles strictly above the diagonal (symmetric product)
 };
 
-constexpr int kBK = 16;
-constexpr int kStages = 4;
+#ifndef SGP_BK
+#define SGP_BK 32
+#endif
+#ifndef SGP_STAGES
+#define SGP_STAGES 3
+#endif
+constexpr int kBK = SGP_BK;          // k-depth of one pipeline stage (multiple of 16)
+constexpr int kStages = SGP_STAGES;
 constexpr int kGemmThreads = 256;
 
 template <int BM, int BN>
@@ -56,8 +64,9 @@ constexpr int gemm_smem_bytes() {
 template <int ROWS, int LAYOUT>
 __device__ __forceinline__ void load_tile(double* smem, const double* __restrict__ base, long ld, int row0,
                                           int nrows, int k0, int kend, int tid) {
-  // ROWS x 16 doubles = ROWS*8 chunks of 16 bytes
-  constexpr int kChunks = ROWS * 8;
+  // ROWS x kBK doubles = ROWS*kBK/2 chunks of 16 bytes
+  constexpr int kCpk = kBK / 2;       // chunks per row of a K-major tile
+  constexpr int kChunks = ROWS * kCpk;
 #pragma unroll
   for (int c0 = 0; c0 < kChunks; c0 += kGemmThreads) {
     const int c = c0 + tid;
@@ -66,7 +75,7 @@ __device__ __forceinline__ void load_tile(double* smem, const double* __restrict
     const double* src;
     double* dst;
     if (LAYOUT == 0) {
-      const int r = c >> 3, ch = c & 7;
+      const int r = c / kCpk, ch = c % kCpk;
       const int row = row0 + r, k = k0 + ch * 2;
       int nv = kend - k;
       nv = nv < 0 ? 0 : (nv > 2 ? 2 : nv);
@@ -101,6 +110,7 @@ __global__ void __launch_bounds__(kGemmThreads, (BM == 128 ? 1 : 2)) gemm_f64_ke
   const int gq = lane >> 2, t = lane & 3;
   const int wm = warp >> 2, wn = warp & 3;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  if (MODE == kStore && g.lower_only && n0 > m0 + BM - 1) return;
   const int kbeg = blockIdx.z * g.k_chunk;
   const int kend = min(g.K, kbeg + g.k_chunk);
   const int KT = (kend - kbeg + kBK - 1) / kBK;

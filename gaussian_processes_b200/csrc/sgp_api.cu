@@ -558,7 +558,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
 
   // ---- split-K plans for the two reductions over images ----------------------------------------------
   const int tilesGC = ntp * ntp, tilesS2 = ntm * ntm;
-  const int nzGC = use_sep ? 1 : pick_split(tilesGC, slab), nzS2 = pick_split(tilesS2, slab);
+  const int nzGC = use_sep ? 1 : pick_split(tilesGC, slab), nzS2 = pick_split(ntm * (ntm + 1) / 2, slab);
+  (void)tilesS2;
   const int nzD = pick_split(ntp * ntm, slab);
   const long zGC = (long)p * ldp, zS2 = (long)m * ldm, zD = (long)p * ldm;
   if (use_sep) CU(h->dpart.reserve((size_t)nzD * zD * sizeof(double)));
@@ -692,6 +693,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     GemmArgs g6{};
     g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
     g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
+    g6.lower_only = 1;   // K^T diag(v) K is symmetric: only the CTA tiles on and below the diagonal are computed
     CU(gemm(st, 1, 1, kStore, false, nzS2, g6));
     mark(8);
     if (streaming) CU(cudaEventRecord(h->ev_used[slab_i & 1], st));
@@ -699,6 +701,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
 
   // ---- adjoint of K_tilde_b (q x q algebra) ---------------------------------------------------------------
   slice_reduce(S2part, nzS2, zS2, zS2, Sig2, 0, st);
+  mirror_lower(Sig2, ldm, m, st);
   col_weights(kappa, nullptr, nullptr, X2, m, beta, st);                                 // beta_j = kappa_j / (2 X2_j)
   sum_to_slot(beta, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);
   gemv(Bw, ldq, m, q, 1, yv, y_b, st);                                                  // y_b = B^T y
@@ -1024,7 +1027,7 @@ int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, c
   const long ldq = rup(q, 16);
   const long slab = std::min<long>(h->slab_rows, rup(N, 128));
   const int ntq = (q + 127) / 128;
-  const int nz = pick_split(ntq * ntq, slab);
+  const int nz = pick_split(ntq * (ntq + 1) / 2, slab);
   const long zs = (long)q * ldq;
   const int ncb = colsum_blocks(slab);
   size_t need = 0;
@@ -1045,11 +1048,13 @@ int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, c
     GemmArgs gg{};  // G += a^T diag(f) a   (U:1422)
     gg.A = as; gg.lda = ldas; gg.B = as; gg.ldb = ldas; gg.C = Gpart; gg.ldc = ldq; gg.M = q; gg.N = q; gg.K = (int)ns;
     gg.k_chunk = (int)rup((ns + nz - 1) / nz, 16); gg.zstride = zs; gg.accumulate = si > 0; gg.kscale = f + i0;
+    gg.lower_only = 1;
     CU(gemm(st, 1, 1, kStore, false, nz, gg));
     colsum_weighted(as, ldas, ns, q, r + i0, f + i0, colpart, ldq, st);   // g += a^T (r - f)   (U:1421)
     col_reduce(colpart, colsum_blocks(ns), q, ldq, g, si > 0, st);
   }
   slice_reduce(Gpart, nz, zs, zs, Gw, 0, st);
+  mirror_lower(Gw, ldq, q, st);
   lincomb(G, ldg, q, q, A * A, Gw, ldq, 0.0, nullptr, 0, 0.0, st);
   scale_vec(g, q, A, st);
   CU(cudaGetLastError());

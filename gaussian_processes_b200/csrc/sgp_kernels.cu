@@ -177,7 +177,9 @@ void acos_forward(double* K, double* cosm, long ld, long n, int m, const double*
 // =====================================================================================================
 // adjoint of the arc-cosine nonlinearity (reference local partials utils.py:996-1021)
 // =====================================================================================================
-template <int MODE>
+// CM = column slots per thread (m <= 256*CM); rows are processed RU at a time with all their loads issued first,
+// so enough memory requests are in flight per SM to approach the HBM rate (the pass reads T, cos, K and writes R).
+template <int MODE, int CM>
 __global__ void __launch_bounds__(256) acos_backward_kernel(double* __restrict__ G, const double* __restrict__ cosm,
                                                             const double* __restrict__ Kmat, long ld, long n, int m,
                                                             const double* __restrict__ u, const double* __restrict__ v,
@@ -187,7 +189,7 @@ __global__ void __launch_bounds__(256) acos_backward_kernel(double* __restrict__
                                                             double* __restrict__ colpart_k,
                                                             double* __restrict__ colpart_y, long ldcol,
                                                             double* __restrict__ sumpart) {
-  constexpr int CM = kBwdMaxCols / 256;
+  constexpr int RU = (CM <= 2) ? 4 : (CM == 4 ? 2 : 1);
   __shared__ double rowred[8][kBwdRows];
   __shared__ double red[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -201,34 +203,47 @@ __global__ void __launch_bounds__(256) acos_backward_kernel(double* __restrict__
     nbj[c] = (j < m) ? nb[j] : 0.0;
   }
   double sumR = 0.0;
-  for (int rr = 0; rr < kBwdRows; ++rr) {
-    const long i = r0 + rr;
-    double rho = 0.0;
-    if (i < n) {
-      const double ui = (MODE == 0) ? u[i] : 0.0;
-      const double vi = (MODE == 0) ? v[i] : 0.0;
-      const double nai = na[i];
+  for (int rr0 = 0; rr0 < kBwdRows; rr0 += RU) {
+    if (r0 + rr0 >= n) break;
+    double gv[RU][CM], cv[RU][CM], kv[RU][CM], ui[RU], vi[RU], nai[RU];
+#pragma unroll
+    for (int q = 0; q < RU; ++q) {
+      const long i = r0 + rr0 + q;
+      const bool rv = i < n;
+      ui[q] = (MODE == 0 && rv) ? u[i] : 0.0;
+      vi[q] = (MODE == 0 && rv) ? v[i] : 0.0;
+      nai[q] = rv ? na[i] : 1.0;
 #pragma unroll
       for (int c = 0; c < CM; ++c) {
         const int j = tid + c * 256;
-        if (j < m) {
-          const long o = i * ld + j;
-          const double gij = G[o];
-          const double gk = (MODE == 0) ? (ui * bbj[c] + vi * gij) : gij;
-          double P, Q;
-          acos_partials(cosm[o], P, Q);
-          const double Rv = gk * P;
-          const double rq = gk * Q;
-          G[o] = Rv;
-          sumR += Rv;
-          rho += rq * nbj[c];
-          ck[c] += rq * nai;
-          if (MODE == 0) cy[c] += Kmat[o] * ui;
-        }
+        const bool ok = rv && j < m;
+        const long o = i * ld + j;
+        gv[q][c] = ok ? G[o] : 0.0;
+        cv[q][c] = ok ? cosm[o] : 0.0;
+        kv[q][c] = (MODE == 0 && ok) ? Kmat[o] : 0.0;
       }
     }
-    rho = warp_sum(rho);
-    if (lane == 0) rowred[warp][rr] = rho;
+#pragma unroll
+    for (int q = 0; q < RU; ++q) {
+      const long i = r0 + rr0 + q;
+      double rho = 0.0;
+#pragma unroll
+      for (int c = 0; c < CM; ++c) {
+        const int j = tid + c * 256;
+        const double gk = (MODE == 0) ? (ui[q] * bbj[c] + vi[q] * gv[q][c]) : gv[q][c];
+        double P, Q;
+        acos_partials(cv[q][c], P, Q);
+        const double Rv = gk * P;
+        const double rq = gk * Q;
+        if (i < n && j < m) G[i * ld + j] = Rv;
+        sumR += Rv;
+        rho += rq * nbj[c];
+        ck[c] += rq * nai[q];
+        if (MODE == 0) cy[c] += kv[q][c] * ui[q];
+      }
+      rho = warp_sum(rho);
+      if (lane == 0) rowred[warp][rr0 + q] = rho;
+    }
   }
   __syncthreads();
   if (tid < kBwdRows) {
@@ -254,35 +269,63 @@ __global__ void __launch_bounds__(256) acos_backward_kernel(double* __restrict__
 
 int acos_backward_blocks(long n) { return cdiv(n, kBwdRows); }
 
+template <int MODE>
+static void acos_backward_launch(int nblk, double* G, const double* cosm, const double* Kmat, long ld, long n, int m,
+                                 const double* u, const double* v, const double* bb, const double* na,
+                                 const double* nb, double* rowout, double* colpart_k, double* colpart_y, long ldcol,
+                                 double* sumpart, cudaStream_t st) {
+#define SGP_BWD(CM_)                                                                                              \
+  acos_backward_kernel<MODE, CM_><<<nblk, 256, 0, st>>>(G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout,        \
+                                                        colpart_k, colpart_y, ldcol, sumpart)
+  note_launch();
+  if (m <= 256) SGP_BWD(1);
+  else if (m <= 512) SGP_BWD(2);
+  else if (m <= 1024) SGP_BWD(4);
+  else SGP_BWD(8);
+#undef SGP_BWD
+}
+
 void acos_backward(int mode, double* G, const double* cosm, const double* Kmat, long ld, long n, int m,
                    const double* u, const double* v, const double* bb, const double* na, const double* nb,
                    double* rowout, double* colpart_k, double* colpart_y, long ldcol, double* sumpart,
                    cudaStream_t st) {
   if (n <= 0) return;
   const int nblk = acos_backward_blocks(n);
-  if (mode == 0) {
-    note_launch(); acos_backward_kernel<0><<<nblk, 256, 0, st>>>(G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout, colpart_k,
-                                                  colpart_y, ldcol, sumpart);
-  } else {
-    note_launch(); acos_backward_kernel<1><<<nblk, 256, 0, st>>>(G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout, colpart_k,
-                                                  colpart_y, ldcol, sumpart);
-  }
+  if (mode == 0)
+    acos_backward_launch<0>(nblk, G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout, colpart_k, colpart_y, ldcol,
+                            sumpart, st);
+  else
+    acos_backward_launch<1>(nblk, G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout, colpart_k, colpart_y, ldcol,
+                            sumpart, st);
 }
 
 // =====================================================================================================
 // deterministic reductions
 // =====================================================================================================
-__global__ void col_reduce_kernel(const double* __restrict__ part, int nblk, int m, long ld, double* __restrict__ out,
-                                  int accumulate) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= m) return;
+// block = 32 columns x 8 row groups; each thread sums rows rg, rg+8, ... then the 8 groups are added in fixed order
+__global__ void __launch_bounds__(256) col_reduce_kernel(const double* __restrict__ part, int nblk, int m, long ld,
+                                                         const double* __restrict__ w, double* __restrict__ out,
+                                                         int accumulate) {
+  __shared__ double red[8][33];
+  const int lane = threadIdx.x & 31, rg = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + lane;
   double a = 0.0;
-  for (int b = 0; b < nblk; ++b) a += part[(long)b * ld + j];
-  out[j] = accumulate ? out[j] + a : a;
+  if (j < m) {
+    if (w) for (int b = rg; b < nblk; b += 8) a += part[(long)b * ld + j] * w[b];
+    else   for (int b = rg; b < nblk; b += 8) a += part[(long)b * ld + j];
+  }
+  red[rg][lane] = a;
+  __syncthreads();
+  if (rg == 0 && j < m) {
+    double t = 0.0;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) t += red[g][lane];
+    out[j] = accumulate ? out[j] + t : t;
+  }
 }
 void col_reduce(const double* part, int nblk, int m, long ld, double* out, int accumulate, cudaStream_t st) {
   if (m <= 0) return;
-  note_launch(); col_reduce_kernel<<<cdiv(m, 64), 64, 0, st>>>(part, nblk, m, ld, out, accumulate);
+  note_launch(); col_reduce_kernel<<<cdiv(m, 32), 256, 0, st>>>(part, nblk, m, ld, nullptr, out, accumulate);
 }
 
 __global__ void slice_reduce_kernel(const double* __restrict__ part, int nz, long zstride, long n,
@@ -325,6 +368,16 @@ void symmetrize(const double* A, long lda, int n, double* out, long ldo, cudaStr
   note_launch(); symmetrize_kernel<<<dim3(cdiv(n, 128), n), 128, 0, st>>>(A, lda, n, out, ldo);
 }
 
+// A[i][j] = A[j][i] for j > i (completes a product whose upper CTA tiles were skipped)
+__global__ void mirror_lower_kernel(double* __restrict__ A, long ld, int n) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i < n && j < n && j > i) A[(long)i * ld + j] = A[(long)j * ld + i];
+}
+void mirror_lower(double* A, long ld, int n, cudaStream_t st) {
+  if (n <= 0) return;
+  note_launch(); mirror_lower_kernel<<<dim3(cdiv(n, 128), n), 128, 0, st>>>(A, ld, n);
+}
+
 __global__ void lincomb_kernel(double* __restrict__ out, long ldo, int rows, int cols, double a,
                                const double* __restrict__ A, long lda, double b, const double* __restrict__ B, long ldb,
                                double diag) {
@@ -363,20 +416,12 @@ __global__ void gemv_n_kernel(const double* __restrict__ A, long lda, int rows, 
   a = warp_sum(a);
   if (lane == 0) y[row] = a;
 }
-__global__ void gemv_t_kernel(const double* __restrict__ A, long lda, int rows, int cols,
-                              const double* __restrict__ x, double* __restrict__ y) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= cols) return;
-  double a = 0.0;
-  for (int i = 0; i < rows; ++i) a += A[(long)i * lda + j] * x[i];
-  y[j] = a;
-}
 void gemv(const double* A, long lda, int rows, int cols, int trans, const double* x, double* y, cudaStream_t st) {
   if (rows <= 0 || cols <= 0) return;
   if (!trans) {
     note_launch(); gemv_n_kernel<<<cdiv(rows, 8), 256, 0, st>>>(A, lda, rows, cols, x, y);
   } else {
-    note_launch(); gemv_t_kernel<<<cdiv(cols, 64), 64, 0, st>>>(A, lda, rows, cols, x, y);
+    note_launch(); col_reduce_kernel<<<cdiv(cols, 32), 256, 0, st>>>(A, rows, cols, lda, x, y, 0);
   }
 }
 
@@ -583,7 +628,7 @@ __global__ void kl_scalars_kernel(const double* __restrict__ m_b, const double* 
   for (int i = threadIdx.x; i < q; i += blockDim.x) a += m_b[i] * b[i];
   for (long e = threadIdx.x; e < (long)q * q; e += blockDim.x) {
     const int i = (int)(e / q), j = (int)(e % q);
-    tr += V[(long)i * ldv + j] * Kinv[(long)j * ldk + i];
+    tr += V[(long)i * ldv + j] * Kinv[(long)i * ldk + j];   // Kinv is exactly symmetric (symmetrised by the caller)
   }
   a = block_sum(a, red);
   tr = block_sum(tr, red);

@@ -83,6 +83,7 @@ void sum_to_slot(const double* x, long n, long stride, double scale, double* sca
 
 // ---- small dense helpers (q x q / m x m) -----------------------------------------------------
 void symmetrize(const double* A, long lda, int n, double* out, long ldo, cudaStream_t st);   // out = (A + A^T)/2
+void mirror_lower(double* A, long ld, int n, cudaStream_t st);                                // A[i][j] = A[j][i], j > i
 void lincomb(double* out, long ldo, int rows, int cols, double a, const double* A, long lda, double b,
              const double* B, long ldb, double diag, cudaStream_t st);                        // out = a*A + b*B + diag*I
 void rank1_add(double* out, long ldo, int rows, int cols, double alpha, const double* x, const double* y,
