@@ -161,7 +161,7 @@ def measure_fp64_peak(dev):
 
 def run_ours(args):
     import torch.distributed as dist
-    from gaussian_processes_b200 import native
+    from gaussian_processes_b200 import native, sharded
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -193,15 +193,13 @@ def run_ours(args):
         for t in (B, m_b, V_b):
             dist.broadcast(t, 0)
     q = B.shape[1]
-    native.set_option(local, "kl_weight", 1.0 if rank == 0 else 0.0)
     peak_f64 = measure_fp64_peak(dev) if rank == 0 else None
+    sg = sharded.ShardGroup(device=dev) if world > 1 else None
 
     def step():
-        out = native.elbo_grad(X, r, xt, n, theta, B, m_b, V_b, prob.logA, prob.lambda0)
-        vec = torch.tensor([out["loglik"]] + [out["grad"][k] for k in KEYS] + [out["sum_r"]], dtype=torch.float64,
-                           device=dev)
-        if world > 1:
-            dist.all_reduce(vec)          # the one exchange step of the sharded evaluation (8 doubles)
+        # fused closure on the local block of images + (N > 1) the one exchange step: all-reduce of 8 doubles
+        out = sharded.elbo_grad(X, r, xt, n, theta, B, m_b, V_b, prob.logA, prob.lambda0, sg=sg)
+        vec = [out["loglik"]] + [out["grad"][k] for k in KEYS]
         return out, vec
 
     def barrier():

@@ -998,6 +998,7 @@ int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, c
   out_host[2] = sr - sf;                             // dloglik/dlambda0  U:1255
   out_host[3] = std::log(sr) - std::log(se);         // lambda0 closed form U:1227
   out_host[4] = sr; out_host[5] = sf; out_host[6] = rl; out_host[7] = h->h_out[5];
+  out_host[8] = sdf; out_host[9] = se;               // raw sums, for image-sharded callers (all-reduce, then combine)
   return SGP_OK;
 }
 

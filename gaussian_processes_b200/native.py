@@ -131,11 +131,11 @@ def fparam_eval(lam_m: torch.Tensor, lam_var: torch.Tensor, r: torch.Tensor, log
     lam_m, lam_var, r = lam_m.contiguous(), lam_var.contiguous(), r.contiguous()
     N = lam_m.shape[0]
     f = torch.empty_like(lam_m) if want_f else None
-    out = (C.c_double * 8)()
+    out = (C.c_double * 10)()
     h = _h(lam_m)
     h.check(lib.sgp_fparam_eval(h.ptr, _ptr(lam_m), _ptr(lam_var), _ptr(r), N, float(logA), float(lambda0), _ptr(f),
                                 out, _stream(lam_m.device)))
-    keys = ("loglik", "dlogA", "dlambda0", "lambda0_closed", "sum_r", "sum_f", "r_lam", "nan")
+    keys = ("loglik", "dlogA", "dlambda0", "lambda0_closed", "sum_r", "sum_f", "r_lam", "nan", "lamf", "sum_exp")
     return dict(zip(keys, list(out))), f
 
 
@@ -237,9 +237,11 @@ OUT_KEYS = ("loglik", "KL", "g_sigma_0", "g_eps_0x", "g_eps_0y", "g_-2log2beta",
 
 def elbo_grad(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
               m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float, lims=None,
-              logdetV: Optional[float] = None, want_moments: bool = False) -> Dict:
-    """Fused M-step closure body (utils.py:2030-2099): one C call, one 16-double read-back."""
+              logdetV: Optional[float] = None, want_moments: bool = False, kl_weight: float = 1.0) -> Dict:
+    """Fused M-step closure body (utils.py:2030-2099): one C call, one 16-double read-back.
+    kl_weight scales the KL part of the returned gradient (image shards other than the first pass 0)."""
     _need_cuda(X, r, xtilde, B, m_b, V_b)
+    set_option(X.device.index if X.device.index is not None else torch.cuda.current_device(), "kl_weight", kl_weight)
     X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
     r, m_b = r.contiguous(), m_b.contiguous()
     N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]

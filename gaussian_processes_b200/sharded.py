@@ -1,0 +1,86 @@
+"""Image sharding of the Spatial_GP hot path across GPUs (north_star item 4).
+
+One process per GPU (``torchrun``); rank k holds a contiguous block of the training images ``x`` / spike counts
+``r``; the small state (theta, xtilde, B, m_b, V_b, f_params) is replicated and recomputed bit-identically on
+every rank.  Every place the path contracts over images is a plain sum, so the exchange step is ONE all-reduce
+of a few doubles per evaluation:
+
+* M-step closure (``elbo_grad``): ``[loglik, 6 gradients, K_tilde_b-not-PD flag]``; the N-independent KL term and
+  its gradient are computed on every rank and counted once (``kl_weight`` = 1 on rank 0, 0 elsewhere);
+* E-step (``utils.Estep``): ``g`` (q) and ``G`` (q x q);
+* logA closure / lambda0 / loss tracking: 4-6 scalar sums.
+
+``enable()`` installs the reducer into ``gaussian_processes_b200.utils`` so that ``utils.varGP`` runs SPMD: all
+ranks execute the same host loop on their shard and see identical reduced numbers, hence identical LBFGS
+trajectories.  Backend: NCCL over NVLink on GPUs; ``gloo`` is used by the CPU tests of this host logic.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+class ShardGroup:
+    """Sum-reducer over a torch.distributed process group."""
+
+    def __init__(self, group=None, device: Optional[torch.device] = None):
+        if not dist.is_initialized():
+            raise RuntimeError("sharded.enable(): torch.distributed is not initialised")
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        backend = dist.get_backend(group)
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+        self.device = torch.device(device)
+        self.calls = 0
+
+    def sum_floats(self, vals: Sequence[float]):
+        t = torch.tensor([float(v) for v in vals], dtype=torch.float64, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        self.calls += 1
+        return t.tolist()
+
+    def sum_tensor_(self, t: torch.Tensor) -> torch.Tensor:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        self.calls += 1
+        return t
+
+
+def enable(group=None, device=None) -> ShardGroup:
+    """Make ``utils`` treat its ``x`` / ``r`` arguments as this rank's block of the images."""
+    from . import utils
+    sg = ShardGroup(group, device)
+    utils._SHARD = sg
+    return sg
+
+
+def disable() -> None:
+    from . import utils
+    utils._SHARD = None
+
+
+def shard_rows(N: int, rank: int, world: int) -> slice:
+    """Contiguous block of rank `rank` out of N images (the first N % world ranks hold one image more)."""
+    base, extra = divmod(N, world)
+    lo = rank * base + min(rank, extra)
+    return slice(lo, lo + base + (1 if rank < extra else 0))
+
+
+def elbo_grad(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0, sg: Optional[ShardGroup] = None,
+              native_mod=None, logdetV=None):
+    """One image-sharded ELBO+gradient evaluation: the fused call on the local block, then ONE all-reduce.
+    Returns dict(loglik, KL, grad{key}, flags) identical on every rank."""
+    if native_mod is None:
+        from . import native as native_mod
+    keys = native_mod.THETA_KEYS
+    rank = sg.rank if sg is not None else 0
+    out = native_mod.elbo_grad(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0, logdetV=logdetV,
+                               kl_weight=1.0 if rank == 0 else 0.0)
+    vec = [out["loglik"]] + [out["grad"][k] for k in keys] + [float(out["flags"] != 0)]
+    if sg is not None and sg.world > 1:
+        vec = sg.sum_floats(vec)
+    return {"loglik": vec[0], "KL": out["KL"], "grad": dict(zip(keys, vec[1:7])), "flags": out["flags"],
+            "any_flag": vec[7] > 0, "p": out.get("p")}

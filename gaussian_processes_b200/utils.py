@@ -177,6 +177,25 @@ def _link_params(f_params):
     return logA, lambda0
 
 
+# ---- image sharding hook (gaussian_processes_b200/sharded.py installs a reducer here) ---------------------
+_SHARD = None
+
+
+def _shard_rank() -> int:
+    return 0 if _SHARD is None else _SHARD.rank
+
+
+def _shard_sum(vals):
+    """Sum a short list of floats over the image shards (identity when not sharded)."""
+    return list(vals) if _SHARD is None or _SHARD.world == 1 else _SHARD.sum_floats(vals)
+
+
+def _shard_sum_tensor_(t):
+    if _SHARD is not None and _SHARD.world > 1:
+        _SHARD.sum_tensor_(t)
+    return t
+
+
 def _out_of_bounds(theta, lo, hi):
     return [k for k, v in theta.items() if not (_fl(lo[k]) <= _fl(v) <= _fl(hi[k]))]
 
@@ -276,7 +295,8 @@ def mean_f_given_lambda_moments(f_params, lambda_m, lambda_var):
 def lambda0_given_logA(logA, r, lambda_m, lambda_var):
     """Closed-form lambda0 = log sum r - log sum exp(A lambda_m + A^2 lambda_var / 2)  (U:1215-1229)."""
     res, _ = native.fparam_eval(lambda_m, lambda_var, r, _fl(logA), 0.0, want_f=False)
-    return _scalar(res["lambda0_closed"], like=r)
+    sum_r, sum_exp = _shard_sum([res["sum_r"], res["sum_exp"]])
+    return _scalar(math.log(sum_r) - math.log(sum_exp), like=r)                                 # U:1227
 
 
 def mean_f(f_params, calculate_moments, lambda_m=None, lambda_var=None, x=None, K_tilde=None, KKtilde_inv=None,
@@ -310,6 +330,7 @@ def compute_loglikelihood(r, f_mean, lambda_m, lambda_var, f_params, compute_gra
     logA, lambda0 = _link_params(f_params)
     A = math.exp(logA)
     s = native.loglik_sums(r, f_mean, lambda_m, lambda_var, logA)
+    s = dict(zip(s.keys(), _shard_sum(s.values())))
     loglikelihood = _scalar(A * s["r_lam"] + lambda0 * s["sum_r"] - s["sum_f"], like=r)        # U:1243
     if compute_grad_for_f_params:
         d = {'logA': _scalar(A * (s["r_lam"] - s["lamf"]), like=r)}                            # U:1253
@@ -322,6 +343,7 @@ def compute_loglikelihood(r, f_mean, lambda_m, lambda_var, f_params, compute_gra
         d = {}
         for key in dlambda_m.keys():                                                           # U:1266
             d[key] = A * (r @ dlambda_m[key]) - A * (f_mean @ dlambda_m[key]) - 0.5 * A * A * (f_mean @ dlambda_var[key])
+            _shard_sum_tensor_(d[key])
         return loglikelihood, d
     return loglikelihood, _scalar(s["r_lam"], like=r), _scalar(s["sum_r"], like=r)             # U:1269
 
@@ -372,6 +394,8 @@ def Estep(r, KKtilde_inv, m, f_params, f_mean, K_tilde=None, K_tilde_inv=None, V
     if update_V_inv or alpha != 1 or K_tilde is None:
         raise NotImplementedError('Estep: only update_V_inv=False, alpha=1 is provided (the branch varGP uses)')
     g, G = native.estep_terms(KKtilde_inv, r, f_mean, _fl(f_params['logA']))
+    _shard_sum_tensor_(g)
+    _shard_sum_tensor_(G)
     V_new = None
     if K_tilde_inv is not None:
         # (I + K G)^-1 K == (K^-1 + G)^-1 : symmetric positive definite -> blocked Cholesky inverse on the device
@@ -521,9 +545,11 @@ def elbo_and_grad(theta, lo, hi, n_px_side, x, xtilde, r, B, m_b, V_b, f_params,
     if not same:
         logA, lambda0 = _link_params(f_params)
         out = native.elbo_grad(x, r, xtilde, int(n_px_side), _theta_floats(theta), B, m_b, V_b, logA, lambda0,
-                               logdetV=logdetV)
-        if not (out["flags"] & (FLAG_KT_NOT_PD | FLAG_KT_SMALL_PIVOT)):
-            return out["loglik"], out["KL"], dict(out["grad"])
+                               logdetV=logdetV, kl_weight=1.0 if _shard_rank() == 0 else 0.0)
+        bad = float(bool(out["flags"] & (FLAG_KT_NOT_PD | FLAG_KT_SMALL_PIVOT)))
+        vec = _shard_sum([out["loglik"]] + [out["grad"][k] for k in THETA_KEYS] + [bad])   # the one exchange step
+        if vec[7] == 0:
+            return vec[0], out["KL"], dict(zip(THETA_KEYS, vec[1:7]))
     return _closure_forward_mode(theta, lo, hi, n_px_side, x, xtilde, r, kernfun, same, B, m_b, V_b, f_params)
 
 
@@ -552,6 +578,8 @@ def varGP(x, r, **kwargs):
     else:
         raise Exception('Kernel function not recognized')
 
+    if _SHARD is not None and 'xtilde' not in kwargs:
+        raise Exception('image-sharded varGP needs xtilde passed explicitly (it must be identical on every rank)')
     xtilde = kwargs['xtilde'] if 'xtilde' in kwargs else generate_xtilde(ntilde, x)
     if ntilde != xtilde.shape[0]:
         raise Exception('Number of inducing points does not match ntilde')
@@ -670,13 +698,20 @@ def varGP(x, r, **kwargs):
                         optimizer_f_params.zero_grad()
                         logA_now, lambda0_now = _link_params(f_params)
                         res, f_mean = native.fparam_eval(lambda_m, lambda_var, r, logA_now, lambda0_now, want_f=True)
+                        if _SHARD is not None and _SHARD.world > 1:
+                            A_now = math.exp(logA_now)
+                            names = ("r_lam", "sum_f", "lamf", "sum_r", "sum_exp", "nan")
+                            res.update(zip(names, _shard_sum([res[k] for k in names])))
+                            res["loglik"] = A_now * res["r_lam"] + lambda0_now * res["sum_r"] - res["sum_f"]
+                            res["dlogA"] = A_now * (res["r_lam"] - res["lamf"])
+                            res["lambda0_closed"] = math.log(res["sum_r"]) - math.log(res["sum_exp"])
                         f_params['logA'].grad = _scalar(-res["dlogA"], like=f_params['logA'])
                         f_params['lambda0'] = _scalar(res["lambda0_closed"], like=r)
                         if res["nan"] > 0:
                             raise ValueError(f'Nan in f_mean during f param update in Estep, closure has been called '
                                              f'{calls[0]} times in estep {i_estep} iteration. Try substituting them '
                                              f'with inf.')
-                        if res["sum_f"] / lambda_m.shape[0] > 100:
+                        if _SHARD is None and res["sum_f"] / lambda_m.shape[0] > 100:
                             print(f'f_mean mean is {res["sum_f"] / lambda_m.shape[0]} at i_step {i_estep} iteration '
                                   f'{iteration} at closure call {calls[0]}')
                         return _scalar(-res["loglik"], like=r)

@@ -97,8 +97,10 @@ SGP_API int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const d
 
 /* ---- a6-a8: mean_f_given_lambda_moments / compute_loglikelihood(f-param mode) / lambda0_given_logA -------------
  * One streaming pass over (lam_m, lam_var, r)  (utils.py:1138, 1243, 1253-1255, 1220-1227).
- * out_host[8] = { loglik, dloglik/dlogA, dloglik/dlambda0, lambda0_closed_form, sum r, sum f, sum r*lam_m,
- *                 nan_count };  f (N, nullable) receives the mean rate.                                         */
+ * out_host[10] = { loglik, dloglik/dlogA, dloglik/dlambda0, lambda0_closed_form, sum r, sum f, sum r*lam_m,
+ *                  nan_count, sum (lam_m + A lam_var) f, sum exp(A lam_m + A^2 lam_var/2) };
+ * f (N, nullable) receives the mean rate.  An image-sharded caller all-reduces entries 4,5,6,8,9 and recombines:
+ * loglik = A*[6] + lambda0*[4] - [5], dlogA = A*([6] - [8]), dlambda0 = [4] - [5], lambda0_closed = log[4] - log[9]. */
 SGP_API int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, const double* r, long N, double logA,
                     double lambda0, double* f, double* out_host, void* stream);
 

@@ -61,7 +61,7 @@ def acos_backward(GK, P, Q, na, nb):
     return R, 0.5 * rho / na, 0.5 * kap / nb
 
 
-def elbo_and_grad(theta, X, r, xtilde, n, B, m_b, V_b, logA, lambda0):
+def elbo_and_grad(theta, X, r, xtilde, n, B, m_b, V_b, logA, lambda0, kl_weight=1.0):
     """Returns dict(loglik, KL, grad[key], lam_m, lam_var, f, inter=dict of intermediates)."""
     th = {k: float(v) for k, v in theta.items()}
     s0 = th["sigma_0"]
@@ -111,7 +111,9 @@ def elbo_and_grad(theta, X, r, xtilde, n, B, m_b, V_b, logA, lambda0):
     y_b = B.T @ y
     Sig2_b = B.T @ Sig2 @ B
     S = Kinv.T @ (torch.outer(y_b, m_b) + Sig2_b @ (2 * Kinv @ V_b.T - torch.eye(q, dtype=torch.float64)))
-    GKt_b = -S @ Kinv.T - 0.5 * Kinv.T + 0.5 * (Kinv @ V_b @ Kinv).T + 0.5 * torch.outer(b, b)
+    # kl_weight: image shards other than the first leave the (N-independent) KL adjoint out, so that the
+    # all-reduced gradient counts it once
+    GKt_b = -S @ Kinv.T + kl_weight * (-0.5 * Kinv.T + 0.5 * (Kinv @ V_b @ Kinv).T + 0.5 * torch.outer(b, b))
     GKt = B @ GKt_b @ B.T
 
     # ---- inducing-point path, backward ------------------------------------------------------

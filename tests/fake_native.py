@@ -56,7 +56,9 @@ def fparam_eval(lam_m, lam_var, r, logA, lambda0, want_f=True):
     dlogA, dl0 = orc.expected_loglik_fparam_grad(r, f, lam_m, lam_var, logA)
     res = dict(loglik=orc.expected_loglik(r, f, lam_m, logA, lambda0), dlogA=dlogA, dlambda0=dl0,
                lambda0_closed=orc.lambda0_closed_form(logA, r, lam_m, lam_var), sum_r=float(r.sum()),
-               sum_f=float(f.sum()), r_lam=float(r @ lam_m), nan=float(torch.isnan(f).sum()))
+               sum_f=float(f.sum()), r_lam=float(r @ lam_m), nan=float(torch.isnan(f).sum()),
+               lamf=float((lam_m + math.exp(logA) * lam_var) @ f),
+               sum_exp=float(torch.exp(math.exp(logA) * lam_m + 0.5 * math.exp(logA) ** 2 * lam_var).sum()))
     return res, (f if want_f else None)
 
 
@@ -106,9 +108,10 @@ def matmul_tn(At, B):
     return At.T @ B
 
 
-def elbo_grad(X, r, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0, lims=None, logdetV=None, want_moments=False):
+def elbo_grad(X, r, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0, lims=None, logdetV=None, want_moments=False,
+              kl_weight=1.0):
     calls["elbo_grad"] += 1
-    out = adjoint_model.elbo_and_grad(_th(theta), X, r, xtilde, n_px, B, m_b, V_b, logA, lambda0)
+    out = adjoint_model.elbo_and_grad(_th(theta), X, r, xtilde, n_px, B, m_b, V_b, logA, lambda0, kl_weight=kl_weight)
     KL = out["KL"]
     if logdetV is not None:   # caller-supplied log det V_b replaces the internally computed one
         L = torch.linalg.cholesky(V_b)
