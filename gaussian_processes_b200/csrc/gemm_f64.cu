@@ -37,7 +37,7 @@ cudaError_t optin_one() {
 cudaError_t gemm_f64_init() {
   cudaError_t e;
 #define X(AL_, BL_, MODE_, KS_)                                                       \
-  if ((e = optin_one<128, 128, AL_, BL_, MODE_, KS_>()) != cudaSuccess) return e;     \
+  if ((e = optin_one<64, 128, AL_, BL_, MODE_, KS_>()) != cudaSuccess) return e;      \
   if ((e = optin_one<64, 64, AL_, BL_, MODE_, KS_>()) != cudaSuccess) return e;
   SGP_FOR_EACH_GEMM(X)
 #undef X
@@ -55,7 +55,7 @@ cudaError_t gemm_f64_launch(const GemmArgs& a, const GemmLaunch& cfg, cudaStream
 #define X(AL_, BL_, MODE_, KS_)                                                          \
   if (cfg.al == AL_ && cfg.bl == BL_ && cfg.mode == MODE_ && ks == KS_) {                \
     return cfg.small_tile ? launch_one<64, 64, AL_, BL_, MODE_, KS_>(a, nsplit, st)      \
-                          : launch_one<128, 128, AL_, BL_, MODE_, KS_>(a, nsplit, st);   \
+                          : launch_one<64, 128, AL_, BL_, MODE_, KS_>(a, nsplit, st);    \
   }
   SGP_FOR_EACH_GEMM(X)
 #undef X

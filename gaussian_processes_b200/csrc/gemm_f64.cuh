@@ -7,11 +7,13 @@
 //   AL/BL = 1 : "MN-major" -- element (row, k) at ptr[k*ld + row]   (row contiguous)
 // so X*C, Z*U^T, X^T*Y (reduction over images), K^T diag(v) K ... are all this one kernel.
 //
-// Tiling: CTA tile BM x BN x kBK (32), 8 warps as 2(m) x 4(n); each warp owns (BM/2) x (BN/4) as
-// (BM/16) x (BN/32) DMMA 8x8 accumulators.  3-stage cp.async pipeline (216 KB of shared memory for the
-// 128 x 128 tile; measured +3 % over 4 stages of k-depth 16: half as many block barriers); shared-memory rows
-// are padded (+4 doubles) so every fragment LDS.64 is bank-conflict free:
-//   K-major  tile [rows][kBK+4] : addr = row*36 + k   -> (g*4 + t) mod 16 distinct per half-warp
+// Tiling: CTA tile BM x BN x kBK (64 x 128 x 16 for the large products, 64 x 64 x 16 for the small ones), 4 warps
+// as 2(m) x 2(n); each warp owns (BM/2) x (BN/2) as (BM/16) x (BN/16) DMMA 8x8 accumulators (32 x 64 -> 32 DMMAs
+// per 12 fragment loads).  3-stage cp.async pipeline, 90 KB of shared memory -> TWO independent CTAs per SM: while
+// one CTA sits at its per-k-tile barrier or in its epilogue the other keeps the fp64 tensor pipe busy (one
+// 8-warp CTA per SM measured 82 % DMMA-pipe activity; the library's own d884 kernels use this same shape).
+// Shared-memory rows are padded (+4 doubles) so every fragment LDS.64 is bank-conflict free:
+//   K-major  tile [rows][kBK+4] : addr = row*20 + k   -> (g*4 + t) mod 16 distinct per half-warp
 //   MN-major tile [kBK][rows+4] : addr = k*(BM+4)+row -> (t*4 + g) mod 16 distinct per half-warp
 // Fused epilogues (MODE) implement the per-image reductions of the Spatial_GP pass, see below.
 #pragma once
@@ -44,14 +46,14 @@ struct GemmArgs {
 };
 
 #ifndef SGP_BK
-#define SGP_BK 32
+#define SGP_BK 16
 #endif
 #ifndef SGP_STAGES
 #define SGP_STAGES 3
 #endif
 constexpr int kBK = SGP_BK;          // k-depth of one pipeline stage (multiple of 16)
 constexpr int kStages = SGP_STAGES;
-constexpr int kGemmThreads = 256;
+constexpr int kGemmThreads = 128;
 
 template <int BM, int BN>
 constexpr int gemm_smem_bytes() {
@@ -97,9 +99,9 @@ __device__ __forceinline__ void load_tile(double* smem, const double* __restrict
 }
 
 template <int BM, int BN, int AL, int BL, int MODE, bool KSCALE>
-__global__ void __launch_bounds__(kGemmThreads, (BM == 128 ? 1 : 2)) gemm_f64_kernel(const GemmArgs g) {
+__global__ void __launch_bounds__(kGemmThreads, (BN == 128 ? 2 : 3)) gemm_f64_kernel(const GemmArgs g) {
   constexpr int WMI = BM / 16;  // 8x8 accumulator tiles per warp along m
-  constexpr int WNI = BN / 32;  // ... along n
+  constexpr int WNI = BN / 16;  // ... along n
   constexpr int A_STAGE = (BM * (kBK + 4) > kBK * (BM + 4)) ? BM * (kBK + 4) : kBK * (BM + 4);
   constexpr int B_STAGE = (BN * (kBK + 4) > kBK * (BN + 4)) ? BN * (kBK + 4) : kBK * (BN + 4);
   extern __shared__ __align__(16) double smem[];
@@ -108,7 +110,7 @@ __global__ void __launch_bounds__(kGemmThreads, (BM == 128 ? 1 : 2)) gemm_f64_ke
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int gq = lane >> 2, t = lane & 3;
-  const int wm = warp >> 2, wn = warp & 3;
+  const int wm = warp >> 1, wn = warp & 1;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
   if (MODE == kStore && g.lower_only && n0 > m0 + BM - 1) return;
   const int kbeg = blockIdx.z * g.k_chunk;
@@ -162,7 +164,7 @@ __global__ void __launch_bounds__(kGemmThreads, (BM == 128 ? 1 : 2)) gemm_f64_ke
       }
 #pragma unroll
       for (int j = 0; j < WNI; ++j) {
-        const int c = wn * (BN / 4) + j * 8 + gq;
+        const int c = wn * (BN / 2) + j * 8 + gq;
         bf[j] = (BL == 0) ? b_s[c * (kBK + 4) + k] : b_s[k * (BN + 4) + c];
       }
 #pragma unroll
@@ -174,7 +176,7 @@ __global__ void __launch_bounds__(kGemmThreads, (BM == 128 ? 1 : 2)) gemm_f64_ke
   cp_async_wait<0>();
 
   // ---------------------------------------------------------------- epilogue
-  // accumulator (i, j, e): row = m0 + wm*BM/2 + i*8 + g ; col = n0 + wn*BN/4 + j*8 + 2t + e
+  // accumulator (i, j, e): row = m0 + wm*BM/2 + i*8 + g ; col = n0 + wn*BN/2 + j*8 + 2t + e
   double rs1[WMI], rs2[WMI];
   if (MODE == kRowdot || MODE == kMoments) {
 #pragma unroll
@@ -190,7 +192,7 @@ __global__ void __launch_bounds__(kGemmThreads, (BM == 128 ? 1 : 2)) gemm_f64_ke
     if (MODE == kAcos || MODE == kAxpyRow) rv = __ldg(g.rowvec + row);
 #pragma unroll
     for (int j = 0; j < WNI; ++j) {
-      const int col = n0 + wn * (BN / 4) + j * 8 + 2 * t;
+      const int col = n0 + wn * (BN / 2) + j * 8 + 2 * t;
       if (col >= g.N) continue;
       const bool two = (col + 1 < g.N);
       double v0 = acc[i][j][0], v1 = acc[i][j][1];
@@ -229,10 +231,10 @@ __global__ void __launch_bounds__(kGemmThreads, (BM == 128 ? 1 : 2)) gemm_f64_ke
   }
 
   if (MODE == kRowdot || MODE == kMoments) {
-    // deterministic row reduction: quad shuffle -> 4 n-warps through smem -> one partial per (n-tile,row)
+    // deterministic row reduction: quad shuffle -> 2 n-warps through smem -> one partial per (n-tile,row)
     __syncthreads();  // pipeline smem is free now
-    double* red1 = smem;            // [4][BM]
-    double* red2 = smem + 4 * BM;   // [4][BM]
+    double* red1 = smem;            // [2][BM]
+    double* red2 = smem + 2 * BM;   // [2][BM]
 #pragma unroll
     for (int i = 0; i < WMI; ++i) {
       double a = rs1[i], b = rs2[i];
@@ -251,8 +253,8 @@ __global__ void __launch_bounds__(kGemmThreads, (BM == 128 ? 1 : 2)) gemm_f64_ke
     __syncthreads();
     if (tid < BM && m0 + tid < g.M) {
       const long o = (long)blockIdx.x * g.ldpart + m0 + tid;
-      g.part1[o] = red1[tid] + red1[BM + tid] + red1[2 * BM + tid] + red1[3 * BM + tid];
-      if (MODE == kMoments) g.part2[o] = red2[tid] + red2[BM + tid] + red2[2 * BM + tid] + red2[3 * BM + tid];
+      g.part1[o] = red1[tid] + red1[BM + tid];
+      if (MODE == kMoments) g.part2[o] = red2[tid] + red2[BM + tid];
     }
   }
 }
@@ -260,7 +262,7 @@ __global__ void __launch_bounds__(kGemmThreads, (BM == 128 ? 1 : 2)) gemm_f64_ke
 // ---- host-side launcher (defined in gemm_f64.cu)
 struct GemmLaunch {
   int al, bl, mode;
-  bool small_tile;   // 64x64 CTA tile instead of 128x128
+  bool small_tile;   // 64x64 CTA tile instead of 64x128
   int nsplit;        // grid.z (split-K); requires mode == kStore
 };
 cudaError_t gemm_f64_launch(const GemmArgs& args, const GemmLaunch& cfg, cudaStream_t stream);

@@ -152,13 +152,24 @@ int ensure_ready(sgp_handle* h) {
   return SGP_OK;
 }
 
-// pick a split-K factor so tiles*nz fills the 148 SMs in (nearly) whole waves
+// CTA tiles of a large (64 x 128) product; `lower` counts only the tiles a symmetric product computes
+int gemm_tiles(int M, int N, bool lower = false) {
+  const int tm = (M + 63) / 64, tn = (N + 127) / 128;
+  if (!lower) return tm * tn;
+  int c = 0;
+  for (int a = 0; a < tm; ++a)
+    for (int b = 0; b < tn; ++b)
+      if (b * 128 <= a * 64 + 63) ++c;
+  return c;
+}
+
+// pick a split-K factor so tiles*nz fills the 148 SMs x 2 resident CTAs in (nearly) whole waves
 int pick_split(int tiles, long K) {
   int best = 1; double best_score = -1.0;
   for (int nz = 1; nz <= 64; ++nz) {
     if (nz > 1 && K / nz < 256) break;
     const double ctas = (double)tiles * nz;
-    const double waves = ctas / 148.0;
+    const double waves = ctas / 296.0;
     const double eff = waves / std::ceil(waves);
     const double score = eff - 0.002 * nz;
     if (score > best_score) { best_score = score; best = nz; }
@@ -557,10 +568,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   }
 
   // ---- split-K plans for the two reductions over images ----------------------------------------------
-  const int tilesGC = ntp * ntp, tilesS2 = ntm * ntm;
-  const int nzGC = use_sep ? 1 : pick_split(tilesGC, slab), nzS2 = pick_split(ntm * (ntm + 1) / 2, slab);
-  (void)tilesS2;
-  const int nzD = pick_split(ntp * ntm, slab);
+  const int nzGC = use_sep ? 1 : pick_split(gemm_tiles(p, p), slab), nzS2 = pick_split(gemm_tiles(m, m, true), slab);
+  const int nzD = pick_split(gemm_tiles(p, m), slab);
   const long zGC = (long)p * ldp, zS2 = (long)m * ldm, zD = (long)p * ldm;
   if (use_sep) CU(h->dpart.reserve((size_t)nzD * zD * sizeof(double)));
   double* Dpart = (double*)h->dpart.p;
@@ -1028,7 +1037,7 @@ int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, c
   const long ldq = rup(q, 16);
   const long slab = std::min<long>(h->slab_rows, rup(N, 128));
   const int ntq = (q + 127) / 128;
-  const int nz = pick_split(ntq * (ntq + 1) / 2, slab);
+  const int nz = pick_split(gemm_tiles(q, q, true), slab);
   const long zs = (long)q * ldq;
   const int ncb = colsum_blocks(slab);
   size_t need = 0;
