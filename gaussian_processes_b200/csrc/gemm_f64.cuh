@@ -147,30 +147,35 @@ __global__ void __launch_bounds__(kGemmThreads, (BN == 128 ? 2 : 3)) gemm_f64_ke
     }
     const double* a_s = sA + (kt % kStages) * A_STAGE;
     const double* b_s = sB + (kt % kStages) * B_STAGE;
-#pragma unroll
-    for (int kk = 0; kk < kBK / 4; ++kk) {
-      double af[WMI], bf[WNI];
+    // fragments are double-buffered in registers: the loads of k-step kk+1 are issued before the DMMAs of kk
+    double af[2][WMI], bf[2][WNI];
+    auto load_frags = [&](int buf, int kk) {
       const int k = kk * 4 + t;
 #pragma unroll
       for (int i = 0; i < WMI; ++i) {
         const int r = wm * (BM / 2) + i * 8 + gq;
-        af[i] = (AL == 0) ? a_s[r * (kBK + 4) + k] : a_s[k * (BM + 4) + r];
+        af[buf][i] = (AL == 0) ? a_s[r * (kBK + 4) + k] : a_s[k * (BM + 4) + r];
       }
       if (KSCALE) {
         const int kg = kbeg + kt * kBK + k;
         const double sc = (kg < kend) ? __ldg(g.kscale + kg) : 0.0;
 #pragma unroll
-        for (int i = 0; i < WMI; ++i) af[i] *= sc;
+        for (int i = 0; i < WMI; ++i) af[buf][i] *= sc;
       }
 #pragma unroll
       for (int j = 0; j < WNI; ++j) {
         const int c = wn * (BN / 2) + j * 8 + gq;
-        bf[j] = (BL == 0) ? b_s[c * (kBK + 4) + k] : b_s[k * (BN + 4) + c];
+        bf[buf][j] = (BL == 0) ? b_s[c * (kBK + 4) + k] : b_s[k * (BN + 4) + c];
       }
+    };
+    load_frags(0, 0);
+#pragma unroll
+    for (int kk = 0; kk < kBK / 4; ++kk) {
+      if (kk + 1 < kBK / 4) load_frags((kk + 1) & 1, kk + 1);
 #pragma unroll
       for (int i = 0; i < WMI; ++i)
 #pragma unroll
-        for (int j = 0; j < WNI; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+        for (int j = 0; j < WNI; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[kk & 1][i], bf[kk & 1][j]);
     }
   }
   cp_async_wait<0>();
