@@ -304,7 +304,8 @@ int sgp_cholesky(sgp_handle* h, double* A, long ld, int n, int* flags_host, void
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
-  CU(cholesky_lower(A, ld, n, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, st));
+  CU(h->arena.reserve((size_t)chol_winv_elems(n) * sizeof(double) + 4096));
+  CU(cholesky_lower(A, ld, n, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, (double*)h->arena.p, st));
   if (flags_host) {
     CU(cudaMemcpyAsync(flags_host, h->d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -318,17 +319,18 @@ int sgp_spd_inverse(sgp_handle* h, const double* A, long lda, int n, double* Ain
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const long ld = rup(n, 16);
-  CU(h->arena.reserve((size_t)(3 * ld * ld + 64 * ld + 1024) * sizeof(double)));
+  CU(h->arena.reserve((size_t)(3 * ld * ld + 64 * ld + chol_winv_elems(n) + 1024) * sizeof(double)));
   Arena ar(h->arena.p, h->arena.bytes);
   double* L = ar.take<double>(ld * ld);
   double* X = ar.take<double>(ld * ld);
   double* R = ar.take<double>(ld * ld);
   double* tmp = ar.take<double>(64 * ld);
+  double* winv = ar.take<double>(chol_winv_elems(n));
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
   copy_mat(A, lda, n, n, L, ld, st);
-  CU(cholesky_lower(L, ld, n, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, st));
+  CU(cholesky_lower(L, ld, n, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, winv, st));
   logdet_from_chol(L, ld, n, h->d_scal, kSlotLogdetK, st);
-  CU(tri_inverse_lower(L, ld, n, X, tmp, st));
+  CU(tri_inverse_lower(L, ld, n, X, tmp, winv, st));
   CU(mm(st, 1, 1, X, ld, X, ld, R, ld, n, n, n));
   symmetrize(R, ld, n, Ainv, ldi, st);
   CU(cudaGetLastError());
@@ -439,7 +441,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   for (int i = 0; i < 6; ++i) acc((size_t)m * ldm);                   // Kraw, Kt, cosU, Mfull, Sig2, GKt
   for (int i = 0; i < 3; ++i) acc((size_t)m * ldq);                   // tmp_mq x3
   for (int i = 0; i < 14; ++i) acc((size_t)q * ldq);                  // q x q scratch
-  acc(64 * ldq);                                                      // tri-inverse tmp
+  acc(64 * ldq); acc(chol_winv_elems(q));                             // tri-inverse tmp, inverses of L's diagonal blocks
   for (int i = 0; i < 12; ++i) acc(ldm);                              // small vectors
   acc(use_sep ? 1 : (size_t)slab * ldp);                              // Z / Y (dense path only)
   if (use_sep) {
@@ -473,6 +475,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* tmq3 = ar.take<double>((size_t)m * ldq);
   double* qq[14]; for (int i = 0; i < 14; ++i) qq[i] = ar.take<double>((size_t)q * ldq);
   double* tri_tmp = ar.take<double>(64 * ldq);
+  double* winv = ar.take<double>(chol_winv_elems(q));
   double* vecs[12]; for (int i = 0; i < 12; ++i) vecs[i] = ar.take<double>(ldm);
   double* Zs = ar.take<double>(use_sep ? 1 : (size_t)slab * ldp);
   int* d_off = nullptr; double* d_alpha = nullptr; double* Qs = nullptr; double* wqpart = nullptr; double* Dm = nullptr;
@@ -547,9 +550,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     CU(mm(st, 1, 1, Bw, ldq, tmq1, ldq, Ktb_raw, ldq, q, q, m));                         // B^T Kt B   U:2047
     symmetrize(Ktb_raw, ldq, q, Ktb, ldq, st);                                          // U:2048
     copy_mat(Ktb, ldq, q, q, Lk, ldq, st);
-    CU(cholesky_lower(Lk, ldq, q, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, st));
+    CU(cholesky_lower(Lk, ldq, q, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, winv, st));
     logdet_from_chol(Lk, ldq, q, h->d_scal, kSlotLogdetK, st);
-    CU(tri_inverse_lower(Lk, ldq, q, Linv, tri_tmp, st));
+    CU(tri_inverse_lower(Lk, ldq, q, Linv, tri_tmp, winv, st));
     CU(mm(st, 1, 1, Linv, ldq, Linv, ldq, Kinv_raw, ldq, q, q, q));                      // K_tilde_b^-1  (U:2067)
     symmetrize(Kinv_raw, ldq, q, Kinv, ldq, st);
     gemv(Kinv, ldq, q, q, 0, in.m_b, bq, st);                                           // b = Kinv m_b
@@ -561,7 +564,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     CU(mm(st, 0, 0, tmq2, ldq, Bw, ldq, Mfull, ldm, m, m, q));                           // Mfull = B Mg B^T
     if (!in.logdetV_host) {
       copy_mat(Vw, ldq, q, q, Lv, ldq, st);
-      CU(cholesky_lower(Lv, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, st));
+      CU(cholesky_lower(Lv, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, winv, st));
       logdet_from_chol(Lv, ldq, q, h->d_scal, kSlotLogdetV, st);
     }
     kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, st);

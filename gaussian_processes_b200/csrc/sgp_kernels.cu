@@ -466,114 +466,129 @@ void col_weights(const double* ka, const double* kb, const double* extra, const 
 // =====================================================================================================
 constexpr int kNB = 64;
 
-// Every block factors the 64x64 diagonal block in shared memory (right-looking, all 256 threads share each
-// rank-1 update; redoing the tiny factorisation is cheaper than a second launch).  Block 0 writes it back;
-// blocks >= 1 solve 256 rows of the panel below it, one row per thread:  X * L11^T = A21.
+// One CTA factors a 64 x 64 diagonal block D = L L^T and inverts the factor, W = L^-1, in the same sweep.
+// 256 threads as a 16 x 16 grid, each holding a 4 x 4 sub-block of D (-> L) and of W in registers.  Step k: the
+// owners publish column k of D and row k of the running W through double-buffered shared memory, ONE barrier,
+// then every thread scales by 1/sqrt(d_kk) and applies the rank-1 updates to its registers (right-looking):
+//   D_ij -= l_ik l_jk (k < j <= i),   W_ij -= l_ik w_kj (i > k),   w_k. = (e_k - sum_{l<k} l_kl w_l.) / l_kk.
+// W turns the panel solve below the block and the triangular inverse into plain DMMA GEMMs.
 constexpr int kCholThreads = 256;
-__global__ void __launch_bounds__(kCholThreads) chol_panel_kernel(double* __restrict__ A, long ld, int n, int j0,
-                                                                  int nb, int* __restrict__ flags, int bit_notpd,
-                                                                  int bit_small) {
-  __shared__ double D[kNB][kNB + 1];
-  const int tid = threadIdx.x;
-  // load the diagonal block (lower triangle), identity-padded to 64x64
-  for (int e = tid; e < kNB * kNB; e += kCholThreads) {
-    const int r = e >> 6, c = e & 63;
-    double v = (r == c) ? 1.0 : 0.0;
-    if (r < nb && c < nb) v = (c <= r) ? A[(long)(j0 + r) * ld + j0 + c] : 0.0;
-    D[r][c] = v;
-  }
-  __syncthreads();
+__global__ void __launch_bounds__(kCholThreads) chol_diag_kernel(double* __restrict__ A, long ld, int nb,
+                                                                 double* __restrict__ Wout, int* __restrict__ flags,
+                                                                 int bit_notpd, int bit_small) {
+  __shared__ double colL[2][kNB], rowW[2][kNB];
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  double a[4][4], w[4][4];
+#pragma unroll
+  for (int ri = 0; ri < 4; ++ri)
+#pragma unroll
+    for (int cj = 0; cj < 4; ++cj) {
+      const int r = 4 * ty + ri, c = 4 * tx + cj;
+      double v = (r == c) ? 1.0 : 0.0;                      // identity padding beyond nb
+      if (r < nb && c < nb) v = (c <= r) ? A[(long)r * ld + c] : 0.0;
+      a[ri][cj] = v;
+      w[ri][cj] = (r == c) ? 1.0 : 0.0;
+    }
   int bad = 0;
-  const int row = tid & 63, cg = tid >> 6;
+#pragma unroll
   for (int k = 0; k < kNB; ++k) {
-    const double d = D[k][k];
+    const int kb = k >> 2, kc = k & 3, buf = k & 1;
+    if (tx == kb) {
+#pragma unroll
+      for (int ri = 0; ri < 4; ++ri) colL[buf][4 * ty + ri] = a[ri][kc];
+    }
+    if (ty == kb) {
+#pragma unroll
+      for (int cj = 0; cj < 4; ++cj) rowW[buf][4 * tx + cj] = w[kc][cj];
+    }
+    __syncthreads();
+    const double d = colL[buf][k];
     if (k < nb) {
       if (!(d > 0.0)) bad |= bit_notpd;
       else if (sqrt(d) < 1e-10) bad |= bit_small;
     }
     const double lkk = sqrt(d > 0.0 ? d : 1.0);   // keep going with a harmless pivot; the flag tells the host
-    __syncthreads();                              // everyone has read D[k][k]
-    if (tid == k) D[k][k] = lkk;
-    if (tid > k && tid < kNB) D[tid][k] /= lkk;
-    __syncthreads();
-    if (row > k) {
-      const double lik = D[row][k];
-      for (int l = k + 1 + cg; l <= row; l += 4) D[row][l] -= lik * D[l][k];
+    const double inv = 1.0 / lkk;
+    double lr[4], lc[4], wk[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      lr[q] = colL[buf][4 * ty + q] * inv;
+      lc[q] = colL[buf][4 * tx + q] * inv;
+      wk[q] = rowW[buf][4 * tx + q] * inv;
     }
-    __syncthreads();
-  }
-  if (blockIdx.x == 0) {
-    if (tid == 0 && bad) atomicOr(flags, bad);
-    for (int e = tid; e < nb * nb; e += kCholThreads) {
-      const int r = e / nb, c = e % nb;
-      A[(long)(j0 + r) * ld + j0 + c] = (c <= r) ? D[r][c] : 0.0;
+    if (tx == kb) {
+#pragma unroll
+      for (int ri = 0; ri < 4; ++ri) {
+        const int r = 4 * ty + ri;
+        if (r > k) a[ri][kc] = lr[ri];
+        else if (r == k) a[ri][kc] = lkk;
+      }
     }
-    return;
-  }
-  // ---- TRSM: 256 rows of the panel below the diagonal block (one row per thread)
-  const int arow = j0 + nb + (blockIdx.x - 1) * kCholThreads + tid;
-  if (arow < n) {
-    double* ap = A + (long)arow * ld + j0;
-    double x[kNB];
+    if (ty == kb) {
 #pragma unroll
-    for (int k = 0; k < kNB; ++k) x[k] = (k < nb) ? ap[k] : 0.0;
-#pragma unroll
-    for (int k = 0; k < kNB; ++k) {
-      double sacc = x[k];
-#pragma unroll
-      for (int l = 0; l < k; ++l) sacc -= x[l] * D[k][l];
-      x[k] = sacc / D[k][k];
+      for (int cj = 0; cj < 4; ++cj) w[kc][cj] = wk[cj];
     }
 #pragma unroll
-    for (int k = 0; k < kNB; ++k)
-      if (k < nb) ap[k] = x[k];
+    for (int ri = 0; ri < 4; ++ri) {
+      const int r = 4 * ty + ri;
+      if (r > k) {
+#pragma unroll
+        for (int cj = 0; cj < 4; ++cj) {
+          const int c = 4 * tx + cj;
+          if (c > k && c <= r) a[ri][cj] -= lr[ri] * lc[cj];
+          w[ri][cj] -= lr[ri] * wk[cj];
+        }
+      }
+    }
   }
+  if (tid == 0 && bad) atomicOr(flags, bad);
+#pragma unroll
+  for (int ri = 0; ri < 4; ++ri)
+#pragma unroll
+    for (int cj = 0; cj < 4; ++cj) {
+      const int r = 4 * ty + ri, c = 4 * tx + cj;
+      if (r < nb && c < nb) A[(long)r * ld + c] = (c <= r) ? a[ri][cj] : 0.0;
+      Wout[r * kNB + c] = (c <= r) ? w[ri][cj] : 0.0;
+    }
 }
 
-cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, cudaStream_t st) {
+// In-place blocked Cholesky; Winv (cdiv(n,64) blocks of 64 x 64) receives the inverses of the diagonal blocks of L.
+cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, double* Winv,
+                           cudaStream_t st) {
   for (int j0 = 0; j0 < n; j0 += kNB) {
     const int nb = (n - j0) < kNB ? (n - j0) : kNB;
     const int rem = n - j0 - nb;
-    note_launch(); chol_panel_kernel<<<1 + cdiv(rem, kCholThreads), kCholThreads, 0, st>>>(A, ld, n, j0, nb, flags, bit_notpd, bit_small);
+    double* W = Winv + (long)(j0 / kNB) * kNB * kNB;
+    note_launch();
+    chol_diag_kernel<<<1, kCholThreads, 0, st>>>(A + (long)j0 * ld + j0, ld, nb, W, flags, bit_notpd, bit_small);
     if (rem > 0) {
-      GemmArgs g{};
       const int j1 = j0 + nb;
+      GemmArgs t{};   // panel below the block, in place: L21 = A21 W^T   (one n-tile: a CTA reads only the rows it writes)
+      t.A = A + (long)j1 * ld + j0; t.lda = ld;
+      t.B = W; t.ldb = kNB;
+      t.C = A + (long)j1 * ld + j0; t.ldc = ld;
+      t.M = rem; t.N = nb; t.K = nb; t.k_chunk = kNB; t.alpha = 1.0;
+      cudaError_t e = gemm_f64_launch(t, GemmLaunch{0, 0, kStore, true, 1}, st);
+      if (e != cudaSuccess) return e;
+      GemmArgs g{};   // trailing update A22 -= L21 L21^T
       g.A = A + (long)j1 * ld + j0; g.lda = ld;
       g.B = g.A; g.ldb = ld;
       g.C = A + (long)j1 * ld + j1; g.ldc = ld;
       g.M = rem; g.N = rem; g.K = nb; g.k_chunk = kNB; g.alpha = -1.0; g.accumulate = 1;
-      cudaError_t e = gemm_f64_launch(g, GemmLaunch{0, 0, kStore, true, 1}, st);
+      e = gemm_f64_launch(g, GemmLaunch{0, 0, kStore, true, 1}, st);
       if (e != cudaSuccess) return e;
     }
   }
   return cudaGetLastError();
 }
 
-// inverse of each 64x64 diagonal block of L, written into the diagonal blocks of X (rest of X zeroed by caller)
-__global__ void __launch_bounds__(kNB) tri_diag_inv_kernel(const double* __restrict__ L, long ld, int n,
-                                                           double* __restrict__ X) {
-  __shared__ double D[kNB][kNB + 1];
-  const int tid = threadIdx.x;
+// X (zeroed) <- the diagonal blocks of L^-1 from the Cholesky sweep
+__global__ void place_diag_blocks_kernel(const double* __restrict__ Winv, double* __restrict__ X, long ld, int n) {
   const int j0 = blockIdx.x * kNB;
-  const int nb = (n - j0) < kNB ? (n - j0) : kNB;
-  for (int r = 0; r < kNB; ++r) {
-    double v = (r == tid) ? 1.0 : 0.0;
-    if (r < nb && tid < nb) v = (tid <= r) ? L[(long)(j0 + r) * ld + j0 + tid] : 0.0;
-    D[r][tid] = v;
+  for (int e = threadIdx.x; e < kNB * kNB; e += blockDim.x) {
+    const int r = e >> 6, c = e & 63;
+    if (j0 + r < n && j0 + c < n) X[(long)(j0 + r) * ld + j0 + c] = Winv[(long)blockIdx.x * kNB * kNB + e];
   }
-  __syncthreads();
-  double x[kNB];
-#pragma unroll
-  for (int k = 0; k < kNB; ++k) {
-    double sacc = (k == tid) ? 1.0 : 0.0;
-#pragma unroll
-    for (int l = 0; l < k; ++l) sacc -= D[k][l] * x[l];
-    x[k] = sacc / D[k][k];
-  }
-  // thread tid owns column tid of the inverse
-#pragma unroll
-  for (int k = 0; k < kNB; ++k)
-    if (k < nb && tid < nb) X[(long)(j0 + k) * ld + j0 + tid] = x[k];
 }
 
 __global__ void zero_mat_kernel(double* __restrict__ X, long ld, int rows) {
@@ -581,11 +596,12 @@ __global__ void zero_mat_kernel(double* __restrict__ X, long ld, int rows) {
   if (i < rows && j < ld) X[(long)i * ld + j] = 0.0;
 }
 
-cudaError_t tri_inverse_lower(const double* L, long ld, int n, double* X, double* tmp, cudaStream_t st) {
+cudaError_t tri_inverse_lower(const double* L, long ld, int n, double* X, double* tmp, const double* Winv,
+                              cudaStream_t st) {
   if (n <= 0) return cudaSuccess;
   note_launch(); zero_mat_kernel<<<dim3(cdiv(ld, 128), n), 128, 0, st>>>(X, ld, n);
   const int nblk = cdiv(n, kNB);
-  note_launch(); tri_diag_inv_kernel<<<nblk, kNB, 0, st>>>(L, ld, n, X);
+  note_launch(); place_diag_blocks_kernel<<<nblk, 256, 0, st>>>(Winv, X, ld, n);
   for (int I = 1; I < nblk; ++I) {
     const int i0 = I * kNB;
     const int nb = (n - i0) < kNB ? (n - i0) : kNB;

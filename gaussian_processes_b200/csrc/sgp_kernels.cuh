@@ -98,11 +98,15 @@ void col_weights(const double* kap_a, const double* kap_b, const double* extra, 
                  double* out, cudaStream_t st);
 
 // ---- Cholesky / triangular inverse (blocked, panel 64) --------------------------------------
-// In-place lower Cholesky of A (n x n, lower triangle referenced; the strict upper triangle is
-// clobbered). flags |= notpd/small bits.  The trailing update uses the DMMA GEMM.
-cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, cudaStream_t st);
-// X = L^{-1} (lower, strict upper zero). X must not alias L. tmp: scratch >= 64*ld doubles.
-cudaError_t tri_inverse_lower(const double* L, long ld, int n, double* X, double* tmp, cudaStream_t st);
+// In-place lower Cholesky of A (n x n, lower triangle referenced; the strict upper triangle of the diagonal
+// blocks is zeroed). flags |= notpd/small bits.  Winv: workspace of chol_winv_elems(n) doubles, receives the
+// inverses of the 64 x 64 diagonal blocks of L.  Panel solve and trailing update run on the DMMA GEMM.
+inline long chol_winv_elems(int n) { return (long)((n + 63) / 64) * 64 * 64; }
+cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, double* Winv,
+                           cudaStream_t st);
+// X = L^{-1} (lower, strict upper zero). X must not alias L. tmp: scratch >= 64*ld doubles; Winv from cholesky_lower.
+cudaError_t tri_inverse_lower(const double* L, long ld, int n, double* X, double* tmp, const double* Winv,
+                              cudaStream_t st);
 // scal[slot] = 2*sum log L_kk
 void logdet_from_chol(const double* L, long ld, int n, double* scal, int slot, cudaStream_t st);
 // scal[slot_mb] = m.b ; scal[slot_tr] = sum_ij V_ij Kinv_ji
