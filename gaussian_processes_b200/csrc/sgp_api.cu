@@ -567,7 +567,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       CU(cholesky_lower(Lv, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, winv, st));
       logdet_from_chol(Lv, ldq, q, h->d_scal, kSlotLogdetV, st);
     }
-    kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, st);
+    kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, qq[12], st);   // qq[12]: free until the tail
   }
 
   // ---- split-K plans for the two reductions over images ----------------------------------------------

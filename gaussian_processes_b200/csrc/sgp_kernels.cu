@@ -490,9 +490,13 @@ __global__ void __launch_bounds__(kCholThreads) chol_diag_kernel(double* __restr
       w[ri][cj] = (r == c) ? 1.0 : 0.0;
     }
   int bad = 0;
+  // the 4 steps of one register column are unrolled (register indices must be compile-time); the 16 column groups
+  // loop, so the body stays resident in the instruction cache
+#pragma unroll 1
+  for (int kb = 0; kb < kNB / 4; ++kb)
 #pragma unroll
-  for (int k = 0; k < kNB; ++k) {
-    const int kb = k >> 2, kc = k & 3, buf = k & 1;
+  for (int kc = 0; kc < 4; ++kc) {
+    const int k = 4 * kb + kc, buf = kc & 1;
     if (tx == kb) {
 #pragma unroll
       for (int ri = 0; ri < 4; ++ri) colL[buf][4 * ty + ri] = a[ri][kc];
@@ -503,12 +507,13 @@ __global__ void __launch_bounds__(kCholThreads) chol_diag_kernel(double* __restr
     }
     __syncthreads();
     const double d = colL[buf][k];
+    const double ds = d > 0.0 ? d : 1.0;          // keep going with a harmless pivot; the flag tells the host
+    const double inv = rsqrt(ds);
+    const double lkk = ds * inv;
     if (k < nb) {
       if (!(d > 0.0)) bad |= bit_notpd;
-      else if (sqrt(d) < 1e-10) bad |= bit_small;
+      else if (lkk < 1e-10) bad |= bit_small;
     }
-    const double lkk = sqrt(d > 0.0 ? d : 1.0);   // keep going with a harmless pivot; the flag tells the host
-    const double inv = 1.0 / lkk;
     double lr[4], lc[4], wk[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -636,26 +641,26 @@ void logdet_from_chol(const double* L, long ld, int n, double* scal, int slot, c
   note_launch(); logdet_kernel<<<1, 256, 0, st>>>(L, ld, n, scal, slot);
 }
 
-__global__ void kl_scalars_kernel(const double* __restrict__ m_b, const double* __restrict__ b,
-                                  const double* __restrict__ V, long ldv, const double* __restrict__ Kinv, long ldk,
-                                  int q, double* __restrict__ scal, int slot_mb, int slot_tr) {
+// one block per row: part[i] = sum_j V_ij Kinv_ij (Kinv is exactly symmetric: symmetrised by the caller), part[q+i] = m_i b_i
+__global__ void __launch_bounds__(128) kl_rows_kernel(const double* __restrict__ m_b, const double* __restrict__ b,
+                                                      const double* __restrict__ V, long ldv,
+                                                      const double* __restrict__ Kinv, long ldk, int q,
+                                                      double* __restrict__ part) {
   __shared__ double red[32];
-  double a = 0.0, tr = 0.0;
-  for (int i = threadIdx.x; i < q; i += blockDim.x) a += m_b[i] * b[i];
-  for (long e = threadIdx.x; e < (long)q * q; e += blockDim.x) {
-    const int i = (int)(e / q), j = (int)(e % q);
-    tr += V[(long)i * ldv + j] * Kinv[(long)i * ldk + j];   // Kinv is exactly symmetric (symmetrised by the caller)
-  }
-  a = block_sum(a, red);
+  const int i = blockIdx.x;
+  double tr = 0.0;
+  for (int j = threadIdx.x; j < q; j += blockDim.x) tr += V[(long)i * ldv + j] * Kinv[(long)i * ldk + j];
   tr = block_sum(tr, red);
   if (threadIdx.x == 0) {
-    scal[slot_mb] = a;
-    scal[slot_tr] = tr;
+    part[i] = tr;
+    part[q + i] = m_b[i] * b[i];
   }
 }
 void kl_scalars(const double* m_b, const double* b, const double* V, long ldv, const double* Kinv, long ldk, int q,
-                double* scal, int slot_mb, int slot_tr, cudaStream_t st) {
-  note_launch(); kl_scalars_kernel<<<1, 1024, 0, st>>>(m_b, b, V, ldv, Kinv, ldk, q, scal, slot_mb, slot_tr);
+                double* scal, int slot_mb, int slot_tr, double* scratch, cudaStream_t st) {
+  note_launch(); kl_rows_kernel<<<q, 128, 0, st>>>(m_b, b, V, ldv, Kinv, ldk, q, scratch);
+  sum_to_slot(scratch, q, 1, 1.0, scal, slot_tr, 0, st);
+  sum_to_slot(scratch + q, q, 1, 1.0, scal, slot_mb, 0, st);
 }
 
 // =====================================================================================================

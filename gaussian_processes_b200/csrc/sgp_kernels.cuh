@@ -109,9 +109,9 @@ cudaError_t tri_inverse_lower(const double* L, long ld, int n, double* X, double
                               cudaStream_t st);
 // scal[slot] = 2*sum log L_kk
 void logdet_from_chol(const double* L, long ld, int n, double* scal, int slot, cudaStream_t st);
-// scal[slot_mb] = m.b ; scal[slot_tr] = sum_ij V_ij Kinv_ji
+// scal[slot_mb] = m.b ; scal[slot_tr] = sum_ij V_ij Kinv_ij (Kinv symmetric) ; scratch: 2*q doubles
 void kl_scalars(const double* m_b, const double* b, const double* V, long ldv, const double* Kinv, long ldk, int q,
-                double* scal, int slot_mb, int slot_tr, cudaStream_t st);
+                double* scal, int slot_mb, int slot_tr, double* scratch, cudaStream_t st);
 
 // ---- final contraction with dC_k and result assembly -----------------------------------------
 // GC = sum_z GCpart[z] + GCextra ; gpart[blk*5 + k] = sum_ab GC_ab * dC_k,ab  (k: Amp, beta, rho, ex, ey)
