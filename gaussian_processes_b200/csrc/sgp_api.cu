@@ -1039,7 +1039,6 @@ int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, c
   const double A = std::exp(logA);
   const long ldq = rup(q, 16);
   const long slab = std::min<long>(h->slab_rows, rup(N, 128));
-  const int ntq = (q + 127) / 128;
   const int nz = pick_split(gemm_tiles(q, q, true), slab);
   const long zs = (long)q * ldq;
   const int ncb = colsum_blocks(slab);

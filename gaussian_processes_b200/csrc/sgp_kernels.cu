@@ -427,12 +427,13 @@ void gemv(const double* A, long lda, int rows, int cols, int trans, const double
 
 __global__ void copy_mat_kernel(const double* __restrict__ A, long lda, int rows, int cols, double* __restrict__ out,
                                 long ldo) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
-  if (i < rows && j < ldo) out[(long)i * ldo + j] = (j < cols) ? A[(long)i * lda + j] : 0.0;
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= ldo) return;
+  for (int i = blockIdx.y; i < rows; i += gridDim.y) out[(long)i * ldo + j] = (j < cols) ? A[(long)i * lda + j] : 0.0;
 }
 void copy_mat(const double* A, long lda, int rows, int cols, double* out, long ldo, cudaStream_t st) {
   if (rows <= 0) return;
-  note_launch(); copy_mat_kernel<<<dim3(cdiv(ldo, 128), rows), 128, 0, st>>>(A, lda, rows, cols, out, ldo);
+  note_launch(); copy_mat_kernel<<<dim3(cdiv(ldo, 128), rows < 32768 ? rows : 32768), 128, 0, st>>>(A, lda, rows, cols, out, ldo);
 }
 
 __global__ void gkt_assemble_kernel(double* __restrict__ G, long ld, int q, const double* __restrict__ Kinv,

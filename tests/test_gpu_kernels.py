@@ -100,6 +100,22 @@ def test_localker_acosker_against_reference(nat, name):
     assert rel_err(Kvec.cpu().numpy(), fx["Kvec"]) < 1e-12
 
 
+def test_acosker_many_rows_odd_leading_dimension(nat):
+    """More rows than one slab (65536) and more than gridDim.y allows, with an odd p so the operands go through the
+    staging copies: standalone acosker / acosker_diag against the oracle (utils.py:986-1034)."""
+    import oracle.spatial_gp_oracle as orc
+    g = torch.Generator().manual_seed(11)
+    n1, n2, p = 70001, 9, 15
+    x1 = torch.randn(n1, p, generator=g, dtype=torch.float64)
+    x2 = torch.randn(n2, p, generator=g, dtype=torch.float64)
+    A = torch.randn(p, p, generator=g, dtype=torch.float64)
+    C = A @ A.T / p + 0.1 * torch.eye(p, dtype=torch.float64)
+    K = nat.acosker(0.7, x1.to(dev()), x2.to(dev()), C.to(dev()), False)
+    Kvec = nat.acosker_diag(0.7, x1.to(dev()), C.to(dev()))
+    assert rel_err(K.cpu().numpy(), orc.arccos_kernel({"sigma_0": 0.7}, x1, x2, C).numpy()) < 1e-11
+    assert rel_err(Kvec.cpu().numpy(), (((x1 @ C) * x1).sum(1) + 0.49).numpy()) < 1e-12
+
+
 @pytest.mark.parametrize("name", ["closure_dense_n8", "closure_local_n12", "closure_rankdef_n10", "closure_c1_dense"])
 def test_moments_estep_fparams_against_reference(nat, name):
     import oracle.spatial_gp_oracle as orc
