@@ -143,6 +143,7 @@ int ensure_ready(sgp_handle* h) {
   CU(cudaSetDevice(h->device));
   if (!h->gemm_ready) {
     CU(gemm_f64_init());
+    CU(oz_init());
     CU(cudaMalloc(&h->d_flags, sizeof(int) * 4));
     CU(cudaMalloc(&h->d_scal, sizeof(double) * kNumSlots));
     CU(cudaMalloc(&h->d_out, sizeof(double) * 16));
@@ -296,6 +297,29 @@ int sgp_gemm_f64(sgp_handle* h, int al, int bl, const double* A, long lda, const
   g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K;
   g.alpha = alpha; g.accumulate = accumulate; g.k_chunk = (int)rup(K, 16);
   CU(gemm_f64_launch(g, GemmLaunch{al, bl, kStore, small_tile != 0, 1}, (cudaStream_t)stream));
+  return SGP_OK;
+}
+
+int sgp_gemm_i8emu(sgp_handle* h, const double* A, long M, long lda, const double* B, int N, long ldb, int K,
+                   int slices, double* C, long ldc, void* stream) {
+  if (!h || !A || !B || !C) return fail(h, SGP_E_ARG, "sgp_gemm_i8emu: null argument");
+  if (slices < 2 || slices > 8) return fail(h, SGP_E_ARG, "sgp_gemm_i8emu: slices must be in 2..8");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int ldk = oz_ldk(K);
+  size_t need = 0;
+  auto acc = [&](size_t bytes) { need = ((need + 1023) & ~size_t(1023)) + bytes; };
+  acc((size_t)slices * M * ldk); acc((size_t)slices * N * ldk); acc((size_t)M * sizeof(int)); acc((size_t)N * sizeof(int));
+  need += 4096;
+  CU(h->arena.reserve(need));
+  Arena ar(h->arena.p, h->arena.bytes);
+  int8_t* qa = ar.take<int8_t>((size_t)slices * M * ldk);
+  int8_t* qb = ar.take<int8_t>((size_t)slices * N * ldk);
+  int* ea = ar.take<int>(M);
+  int* eb = ar.take<int>(N);
+  CU(oz_slice_rows(A, lda, M, K, slices, qa, ldk, ea, st));
+  CU(oz_slice_rows(B, ldb, N, K, slices, qb, ldk, eb, st));
+  CU(oz_gemm(qa, ea, M, qb, eb, N, K, ldk, slices, C, ldc, 0, st));
   return SGP_OK;
 }
 

@@ -162,4 +162,14 @@ cudaError_t sep_quad(const SepQuadArgs& a, cudaStream_t st);
 int wq_reduce_blocks(long n);
 void wq_reduce(const double* w, const double* Q, long n, double* blockpart, cudaStream_t st);
 
+// ---- fp64-accurate GEMM on tcgen05.mma.kind::i8 (int8 slices, exact int32 accumulation in TMEM): ozaki_i8.cu ----
+int oz_ldk(int K);                                   // row pitch (bytes) of a sliced operand with K columns
+cudaError_t oz_init();                               // opt-in shared memory of the kernel (once per process)
+// q: [S][rows][ldk] int8 digits, exps[rows]: power-of-two row scales
+cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
+                          cudaStream_t st);
+// C (M x N) = A * B^T from the slices of A (M rows) and B (N rows), K columns each
+cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,
+                    int S, double* C, long ldc, int sm_count, cudaStream_t st);
+
 }  // namespace sgp

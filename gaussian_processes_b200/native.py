@@ -207,6 +207,19 @@ def gemm_f64(A: torch.Tensor, B: torch.Tensor, a_layout: int = 0, b_layout: int 
     return out[:, :N]
 
 
+def gemm_i8emu(A: torch.Tensor, B: torch.Tensor, slices: int = 8) -> torch.Tensor:
+    """A @ B.T (A: [M,K], B: [N,K]) on tcgen05.mma.kind::i8 from int8 digit slices, recombined in fp64."""
+    _need_cuda(A, B)
+    A, B = _c(A), _c(B)
+    M, K = A.shape
+    N = B.shape[0]
+    out = torch.empty((M, N), dtype=torch.float64, device=A.device)
+    h = _h(A)
+    h.check(lib.sgp_gemm_i8emu(h.ptr, _ptr(A), int(M), _ld(A), _ptr(B), int(N), _ld(B), int(K), int(slices),
+                               _ptr(out), _ld(out), _stream(A.device)))
+    return out
+
+
 def matmul(A: torch.Tensor, B: torch.Tensor) -> torch.Tensor:
     """A @ B on the DMMA GEMM (A: [M,K], B: [K,N]); contiguous result."""
     small = max(A.shape[0], B.shape[1]) <= 1024

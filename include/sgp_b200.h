@@ -128,6 +128,15 @@ SGP_API int sgp_gemm_f64(sgp_handle* h, int a_layout, int b_layout, const double
                  double* C, long ldc, int M, int N, int K, double alpha, int accumulate, int small_tile,
                  void* stream);
 
+/* ---- fp64-accurate GEMM on the int8 tensor cores (tcgen05.mma.kind::i8, exposed for tests and measurement) -----
+ * C[M x N] (ldc) = A[M x K] (lda) * B[N x K]^T (ldb), both operands row-major with K contiguous.  The operands are
+ * split into `slices` (2..8) signed 7-bit digits per element relative to a power-of-two scale per row; the digit
+ * products are accumulated exactly in int32 in tensor memory and recombined in fp64 (csrc/ozaki_i8.cu).  With 8 slices
+ * the error is <= ~2^-53 * K * max|A_i.| * max|B_j.| per element, i.e. the class of a DGEMM; results are deterministic.
+ * Serves the same contractions of acosker (utils.py:969-973) / lambda_moments (utils.py:1090-1101) as sgp_gemm_f64. */
+SGP_API int sgp_gemm_i8emu(sgp_handle* h, const double* A, long M, long lda, const double* B, int N, long ldb, int K,
+                   int slices, double* C, long ldc, void* stream);
+
 /* ---- a11: the M-step closure body of varGP (utils.py:2030-2099) as ONE call -----------------------------------
  * theta -> loglik, KL and d(loglik - KL)/dtheta, with X, xtilde, r, B, m_b, V_b, f_params fixed.
  *   X (N x n_px^2, ldx), r (N), xtilde (m x n_px^2, ldu), B (m x q, ldb), m_b (q), V_b (q x q, ldv).
