@@ -13,10 +13,13 @@
 // Kernel shape (one CTA per SM, persistent over 128 x 64 output tiles):
 //   * TMEM holds ALL S diagonals of the tile at once: diagonal d lives in columns [64d, 64d+64) (S*64 <= 512), so
 //     there is a single epilogue per tile and no fp64 read-modify-write of the output;
-//   * one TMA box per operand and k-block brings the S slices of the tile ([S][rows][64 B], 64-byte swizzle);
-//   * the B slices are stacked along the MMA's N dimension: one tcgen05.mma with N = 64*c multiplies slice s of A
-//     with slices t0..t0+c-1 of B and lands in the c adjacent diagonals s+t0.. -- S(S+1)/2 slice pairs cost
-//     about S*3/2 instructions per 32-deep k-step, each at the full-width rate;
+//   * slices are stored PAIRWISE INTERLEAVED: for every row and every 64-byte k-block the bytes of slices 2j and
+//     2j+1 are adjacent, so a TMA box row is a full 128-byte line ([pair][rows][128 B], 128-byte swizzle) although
+//     a stage only advances K by 64; in shared memory slice 2j is k-steps 0,1 of that row and slice 2j+1 k-steps 2,3;
+//   * the B slices of one parity are stacked along the MMA's N dimension: one tcgen05.mma with N = 64*c multiplies
+//     slice s of A with slices t = pi, pi+2, .. of B and lands in the c diagonals s+t, which are adjacent because
+//     TMEM orders the diagonals even-first (0,2,4,6,1,3,5,7) -- S(S+1)/2 slice pairs cost about 2S instructions
+//     per 32-deep k-step, each at the full-width rate;
 //   * warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2-5 = epilogue (TMEM -> fp64 Horner sum over
 //     the diagonals -> scaled store), mbarrier pipelines between them.
 #include <cuda.h>
@@ -34,12 +37,15 @@ namespace {
 
 constexpr int kOzBM = 128;          // tile rows (TMEM lanes)
 constexpr int kOzBN = 64;           // tile columns per diagonal
-constexpr int kOzBK = 64;           // bytes of K per stage (one 64-byte swizzle row)
+constexpr int kOzBK = 64;           // K elements per stage; a shared-memory row is 128 B = this k-block of 2 slices
+constexpr int kOzRow = 2 * kOzBK;
 constexpr int kOzStages = 2;
 constexpr int kOzMaxS = 8;
 constexpr int kOzThreads = 192;
-constexpr int kOzStageA = kOzMaxS * kOzBM * kOzBK;   // 64 KB
-constexpr int kOzStageB = kOzMaxS * kOzBN * kOzBK;   // 32 KB
+constexpr int kOzPairA = kOzBM * kOzRow;              // 16 KB: one slice pair of the A tile
+constexpr int kOzPairB = kOzBN * kOzRow;              //  8 KB
+constexpr int kOzStageA = kOzMaxS / 2 * kOzPairA;     // 64 KB
+constexpr int kOzStageB = kOzMaxS / 2 * kOzPairB;     // 32 KB
 constexpr int kOzSmem = kOzStages * (kOzStageA + kOzStageB) + 1024 /*alignment*/ + 256 /*barriers*/;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -94,12 +100,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// K-major operand tile [rows][64 B] with the 64-byte swizzle TMA wrote: 8-row groups are 512 B apart.
-// (cute::UMMA::SmemDescriptor: start>>4 | LBO>>4 <<16 | SBO>>4 <<32 | version 1 <<46 | layout SWIZZLE_64B=4 <<61)
-__device__ __forceinline__ uint64_t kmajor_sw64_desc(uint32_t saddr) {
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) |
-         ((uint64_t)1 << 46) | ((uint64_t)4 << 61);
+// K-major operand tile [rows][128 B] with the 128-byte swizzle TMA wrote: 8-row groups are 1024 B apart; a k-step
+// inside the row is selected by advancing the start address (the swizzle is a function of the address bits).
+// (cute::UMMA::SmemDescriptor: start>>4 | LBO>>4 <<16 | SBO>>4 <<32 | version 1 <<46 | layout SWIZZLE_128B=2 <<61)
+__device__ __forceinline__ uint64_t kmajor_sw128_desc(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
+// TMEM column block of diagonal d (even diagonals first)
+__host__ __device__ constexpr int diag_pos(int d) { return (d & 1) * 4 + (d >> 1); }
 // cute::UMMA::InstrDescriptor for kind::i8: c = S32 (2<<4), a = b = signed int8 (1<<7, 1<<10), K-major both,
 // N>>3 at bit 17, M>>4 at bit 24.
 __host__ __device__ constexpr uint32_t i8_idesc(int n) {
@@ -150,7 +159,7 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      const uint32_t bytes = (uint32_t)S * (kOzBM + kOzBN) * kOzBK;
+      const uint32_t bytes = (uint32_t)((S + 1) / 2) * (kOzPairA + kOzPairB);
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m0 = (tile / num_nt) * kOzBM, n0 = (tile % num_nt) * kOzBN;
@@ -158,8 +167,8 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           mbar_wait(bar_empty + 8 * stage, phase ^ 1);
           const uint32_t sA = base + stage * (kOzStageA + kOzStageB), sB = sA + kOzStageA;
           mbar_expect_tx(bar_full + 8 * stage, bytes);
-          tma_load_3d(sA, &mapA, bar_full + 8 * stage, kb * kOzBK, m0, 0);
-          tma_load_3d(sB, &mapB, bar_full + 8 * stage, kb * kOzBK, n0, 0);
+          tma_load_3d(sA, &mapA, bar_full + 8 * stage, kb * kOzRow, m0, 0);
+          tma_load_3d(sB, &mapB, bar_full + 8 * stage, kb * kOzRow, n0, 0);
           if (++stage == kOzStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -178,12 +187,15 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #pragma unroll
           for (int ks = 0; ks < kOzBK / 32; ++ks) {
             for (int s = 0; s < S; ++s) {
-              const uint64_t adesc = kmajor_sw64_desc(sA + s * (kOzBM * kOzBK) + ks * 32);
+              const uint64_t adesc = kmajor_sw128_desc(sA + (s >> 1) * kOzPairA + (s & 1) * kOzBK + ks * 32);
               const uint32_t acc = (kb | ks | s) != 0;
-              for (int t0 = 0; t0 < S - s; t0 += 4) {
-                const int c = min(4, S - s - t0);
-                const uint64_t bdesc = kmajor_sw64_desc(sB + t0 * (kOzBN * kOzBK) + ks * 32);
-                mma_i8(tmem + (uint32_t)(kOzBN * (s + t0)), adesc, bdesc, i8_idesc(kOzBN * c), acc);
+#pragma unroll
+              for (int par = 0; par < 2; ++par) {          // B slices t = par, par+2, ..  with s + t <= S-1
+                const int last = S - 1 - s - par;
+                if (last < 0) continue;
+                const int c = (last >> 1) + 1;
+                const uint64_t bdesc = kmajor_sw128_desc(sB + par * kOzBK + ks * 32);
+                mma_i8(tmem + (uint32_t)(kOzBN * diag_pos(s + par)), adesc, bdesc, i8_idesc(kOzBN * c), acc);
               }
             }
           }
@@ -213,7 +225,7 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         for (int j = 0; j < 16; ++j) acc[j] = 0.0;
         for (int d = S - 1; d >= 0; --d) {
           uint32_t v[16];
-          tmem_ld16(tl + (uint32_t)(kOzBN * d + 16 * c), v);
+          tmem_ld16(tl + (uint32_t)(kOzBN * diag_pos(d) + 16 * c), v);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 16; ++j) acc[j] = fma(acc[j], 0.0078125, (double)(int)v[j]);
@@ -244,7 +256,7 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 // One warp per row: power-of-two row scale, then S round-to-nearest base-128 digits per element.
 __global__ void __launch_bounds__(256)
 oz_slice_rows_kernel(const double* __restrict__ X, long ldx, long rows, int cols, int S, int8_t* __restrict__ q,
-                     int ldk, long slice_stride, int* __restrict__ exps) {
+                     int ldk, long pair_stride, int* __restrict__ exps) {
   const int lane = threadIdx.x & 31;
   const long warp0 = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long nwarps = ((long)gridDim.x * blockDim.x) >> 5;
@@ -256,7 +268,7 @@ oz_slice_rows_kernel(const double* __restrict__ X, long ldx, long rows, int cols
     for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
     const int e = (m > 0.0 && m < 1.0e300) ? ilogb(m) + 1 : 0;
     if (lane == 0) exps[r] = e;
-    for (int g = lane; g < ldk / 4; g += 32) {
+    for (int g = lane; g < ldk / 8; g += 32) {
       double t[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -271,7 +283,9 @@ oz_slice_rows_kernel(const double* __restrict__ X, long ldx, long rows, int cols
           t[j] = (t[j] - d) * 128.0;
           w |= ((uint32_t)(__double2int_rn(d)) & 0xffu) << (8 * j);
         }
-        *reinterpret_cast<uint32_t*>(q + s * slice_stride + r * ldk + 4 * g) = w;
+        // pair s/2, row r, k-block (4g)/64: [slice 2j: 64 B][slice 2j+1: 64 B]
+        const int k = 4 * g;
+        *reinterpret_cast<uint32_t*>(q + (s >> 1) * pair_stride + r * ldk + (k >> 6) * 128 + (s & 1) * 64 + (k & 63)) = w;
       }
     }
   }
@@ -293,23 +307,24 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-// [S][rows][ldk] int8, box = 64 B of K x box_rows rows x S slices, 64-byte swizzle
-bool make_slice_map(CUtensorMap* map, const int8_t* q, long rows, int K, int ldk, long slice_stride, int S,
-                    int box_rows) {
+// [pairs][rows][ldk] int8 (ldk = 2 * K rounded up to 64), box = 128 B x box_rows rows x pairs, 128-byte swizzle
+bool make_slice_map(CUtensorMap* map, const int8_t* q, long rows, int ldk, int S, int box_rows) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return false;
-  const cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)rows, (cuuint64_t)S};
-  const cuuint64_t strides[2] = {(cuuint64_t)ldk, (cuuint64_t)slice_stride};
-  const cuuint32_t box[3] = {(cuuint32_t)kOzBK, (cuuint32_t)box_rows, (cuuint32_t)S};
+  const int pairs = (S + 1) / 2;
+  const cuuint64_t dims[3] = {(cuuint64_t)ldk, (cuuint64_t)rows, (cuuint64_t)pairs};
+  const cuuint64_t strides[2] = {(cuuint64_t)ldk, (cuuint64_t)rows * (cuuint64_t)ldk};
+  const cuuint32_t box[3] = {(cuuint32_t)kOzRow, (cuuint32_t)box_rows, (cuuint32_t)pairs};
   const cuuint32_t estr[3] = {1, 1, 1};
   return fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<int8_t*>(q), dims, strides, box, estr,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 }  // namespace
 
-int oz_ldk(int K) { return (K + 15) & ~15; }
+int oz_ldk(int K) { return 2 * ((K + 63) & ~63); }   // bytes per row of one slice PAIR
+size_t oz_slice_bytes(long rows, int K, int S) { return (size_t)((S + 1) / 2) * rows * oz_ldk(K); }
 
 cudaError_t oz_init() {
   return cudaFuncSetAttribute(oz_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kOzSmem);
@@ -318,7 +333,7 @@ cudaError_t oz_init() {
 cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
                           cudaStream_t st) {
   if (rows <= 0) return cudaSuccess;
-  if (S < 1 || S > kOzMaxS || (ldk & 15) || ldk < cols) return cudaErrorInvalidValue;
+  if (S < 1 || S > kOzMaxS || ldk != oz_ldk(cols)) return cudaErrorInvalidValue;
   const long blocks = std::min<long>((rows + 7) / 8, 148L * 8);
   note_launch();
   oz_slice_rows_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, ldx, rows, cols, S, q, ldk, rows * (long)ldk, exps);
@@ -331,8 +346,8 @@ cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, c
   if (M <= 0 || N <= 0) return cudaSuccess;
   if (S < 1 || S > kOzMaxS || (long)K * S * 4096 >= (1L << 31)) return cudaErrorInvalidValue;
   CUtensorMap mapA, mapB;
-  if (!make_slice_map(&mapA, qa, M, K, ldk, M * (long)ldk, S, kOzBM) ||
-      !make_slice_map(&mapB, qb, N, K, ldk, (long)N * ldk, S, kOzBN))
+  if (ldk != oz_ldk(K)) return cudaErrorInvalidValue;
+  if (!make_slice_map(&mapA, qa, M, ldk, S, kOzBM) || !make_slice_map(&mapB, qb, N, ldk, S, kOzBN))
     return cudaErrorNotSupported;
   OzArgs a{ea, eb, C, ldc, (int)M, N, K, S};
   const long tiles = ((M + kOzBM - 1) / kOzBM) * ((N + kOzBN - 1) / kOzBN);

@@ -309,12 +309,12 @@ int sgp_gemm_i8emu(sgp_handle* h, const double* A, long M, long lda, const doubl
   const int ldk = oz_ldk(K);
   size_t need = 0;
   auto acc = [&](size_t bytes) { need = ((need + 1023) & ~size_t(1023)) + bytes; };
-  acc((size_t)slices * M * ldk); acc((size_t)slices * N * ldk); acc((size_t)M * sizeof(int)); acc((size_t)N * sizeof(int));
+  acc(oz_slice_bytes(M, K, slices)); acc(oz_slice_bytes(N, K, slices)); acc((size_t)M * sizeof(int)); acc((size_t)N * sizeof(int));
   need += 4096;
   CU(h->arena.reserve(need));
   Arena ar(h->arena.p, h->arena.bytes);
-  int8_t* qa = ar.take<int8_t>((size_t)slices * M * ldk);
-  int8_t* qb = ar.take<int8_t>((size_t)slices * N * ldk);
+  int8_t* qa = ar.take<int8_t>(oz_slice_bytes(M, K, slices));
+  int8_t* qb = ar.take<int8_t>(oz_slice_bytes(N, K, slices));
   int* ea = ar.take<int>(M);
   int* eb = ar.take<int>(N);
   CU(oz_slice_rows(A, lda, M, K, slices, qa, ldk, ea, st));

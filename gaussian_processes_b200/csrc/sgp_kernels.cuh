@@ -163,9 +163,10 @@ int wq_reduce_blocks(long n);
 void wq_reduce(const double* w, const double* Q, long n, double* blockpart, cudaStream_t st);
 
 // ---- fp64-accurate GEMM on tcgen05.mma.kind::i8 (int8 slices, exact int32 accumulation in TMEM): ozaki_i8.cu ----
-int oz_ldk(int K);                                   // row pitch (bytes) of a sliced operand with K columns
+int oz_ldk(int K);                                   // row pitch (bytes) of one slice PAIR of an operand with K columns
+size_t oz_slice_bytes(long rows, int K, int S);      // bytes of the digit array of a rows x K operand
 cudaError_t oz_init();                               // opt-in shared memory of the kernel (once per process)
-// q: [S][rows][ldk] int8 digits, exps[rows]: power-of-two row scales
+// q: [ceil(S/2)][rows][ldk] int8 digits (slices 2j, 2j+1 interleaved per 64-byte k-block), exps[rows]: row scales
 cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
                           cudaStream_t st);
 // C (M x N) = A * B^T from the slices of A (M rows) and B (N rows), K columns each
