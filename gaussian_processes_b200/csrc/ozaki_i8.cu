@@ -20,13 +20,15 @@
 //     slice s of A with slices t = pi, pi+2, .. of B and lands in the c diagonals s+t, which are adjacent because
 //     TMEM orders the diagonals even-first (0,2,4,6,1,3,5,7) -- S(S+1)/2 slice pairs cost about 2S instructions
 //     per 32-deep k-step, each at the full-width rate;
-//   * warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2-5 = epilogue (TMEM -> fp64 Horner sum over
+//   * warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2-9 = epilogue (TMEM -> fp64 Horner sum over
 //     the diagonals -> scaled store), mbarrier pipelines between them.
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include <algorithm>
+#include <cmath>
+#include <cstdlib>
 
 #include "sgp_common.cuh"
 #include "sgp_kernels.cuh"
@@ -41,12 +43,13 @@ constexpr int kOzBK = 64;           // K elements per stage; a shared-memory row
 constexpr int kOzRow = 2 * kOzBK;
 constexpr int kOzStages = 2;
 constexpr int kOzMaxS = 8;
-constexpr int kOzThreads = 192;
+constexpr int kOzThreads = 320;         // TMA warp, MMA warp, 8 epilogue warps
 constexpr int kOzPairA = kOzBM * kOzRow;              // 16 KB: one slice pair of the A tile
 constexpr int kOzPairB = kOzBN * kOzRow;              //  8 KB
 constexpr int kOzStageA = kOzMaxS / 2 * kOzPairA;     // 64 KB
 constexpr int kOzStageB = kOzMaxS / 2 * kOzPairB;     // 32 KB
-constexpr int kOzSmem = kOzStages * (kOzStageA + kOzStageB) + 1024 /*alignment*/ + 256 /*barriers*/;
+constexpr int kOzSmem = kOzStages * (kOzStageA + kOzStageB) + 1024 /*alignment*/ + 64 /*barriers*/ +
+                        8 * 32 * 16 * 8 /*store staging of the 8 epilogue warps*/;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -115,10 +118,33 @@ __host__ __device__ constexpr uint32_t i8_idesc(int n) {
   return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kOzBM >> 4) << 24);
 }
 
+// All MMAs of one stage (two 32-deep k-steps): slice s of A against the B slices t = par, par+2, .. with s + t < S.
+// dA / dB: descriptors of the stage's A / B tiles; byte offsets inside the tile go into the 16-byte-unit address field.
+template <int S>
+__device__ __forceinline__ void issue_stage(uint64_t dA, uint64_t dB, uint32_t tmem, uint32_t first_acc) {
+#pragma unroll
+  for (int ks = 0; ks < kOzBK / 32; ++ks) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+#pragma unroll
+      for (int par = 0; par < 2; ++par) {
+        const int last = S - 1 - s - par;
+        if (last < 0) continue;
+        const int c = (last >> 1) + 1;
+        mma_i8(tmem + (uint32_t)(kOzBN * diag_pos(s + par)),
+               dA + (uint64_t)(((s >> 1) * kOzPairA + (s & 1) * kOzBK + ks * 32) >> 4),
+               dB + (uint64_t)((par * kOzBK + ks * 32) >> 4), i8_idesc(kOzBN * c), (ks | s) ? 1u : first_acc);
+      }
+    }
+  }
+}
+
 struct OzArgs {
   const int* ea; const int* eb;   // row exponents of A and of B
   double* C; long ldc;
   int M, N, K, S;
+  int nz, kb_per_z; long zstride; int accumulate;   // split-K: slice z covers k-blocks [z*kb_per_z, ..) -> C + z*zstride
+  int dbg;   // timing experiments only: 1 = skip A loads, 2 = skip B loads, 4 = every tile loads A rows 0..127
 };
 
 __device__ __forceinline__ double pow2d(int e) {   // 2^e for -1022 <= e <= 1023
@@ -139,12 +165,13 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   const int S = a.S;
   const int num_nt = (a.N + kOzBN - 1) / kOzBN;
   const int num_tiles = ((a.M + kOzBM - 1) / kOzBM) * num_nt;
-  const int nkb = (a.K + kOzBK - 1) / kOzBK;
+  const int num_items = num_tiles * a.nz;             // item = z * num_tiles + tile
+  const int nkb_all = (a.K + kOzBK - 1) / kOzBK;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kOzStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
     mbar_init(bar_tfull, 1);
-    mbar_init(bar_tempty, 128);
+    mbar_init(bar_tempty, 256);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -159,16 +186,18 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      const uint32_t bytes = (uint32_t)((S + 1) / 2) * (kOzPairA + kOzPairB);
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int tile = item % num_tiles, z = item / num_tiles;
         const int m0 = (tile / num_nt) * kOzBM, n0 = (tile % num_nt) * kOzBN;
-        for (int kb = 0; kb < nkb; ++kb) {
+        const int kb0 = z * a.kb_per_z, kb1 = min(nkb_all, kb0 + a.kb_per_z);
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(bar_empty + 8 * stage, phase ^ 1);
           const uint32_t sA = base + stage * (kOzStageA + kOzStageB), sB = sA + kOzStageA;
-          mbar_expect_tx(bar_full + 8 * stage, bytes);
-          tma_load_3d(sA, &mapA, bar_full + 8 * stage, kb * kOzRow, m0, 0);
-          tma_load_3d(sB, &mapB, bar_full + 8 * stage, kb * kOzRow, n0, 0);
+          const uint32_t pairs = (uint32_t)((S + 1) / 2);
+          mbar_expect_tx(bar_full + 8 * stage, ((a.dbg & 1) ? 0u : pairs * kOzPairA) + ((a.dbg & 2) ? 0u : pairs * kOzPairB));
+          if (!(a.dbg & 1)) tma_load_3d(sA, &mapA, bar_full + 8 * stage, kb * kOzRow, (a.dbg & 4) ? 0 : m0, 0);
+          if (!(a.dbg & 2)) tma_load_3d(sB, &mapB, bar_full + 8 * stage, kb * kOzRow, n0, 0);
           if (++stage == kOzStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -177,71 +206,103 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     // ===== MMA issuer (one thread) =====
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0, tphase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int z = item / num_tiles;
+        const int kb0 = z * a.kb_per_z, kb1 = min(nkb_all, kb0 + a.kb_per_z);
         mbar_wait(bar_tempty, tphase ^ 1);
         tc_fence_after();
-        for (int kb = 0; kb < nkb; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(bar_full + 8 * stage, phase);
           tc_fence_after();
           const uint32_t sA = base + stage * (kOzStageA + kOzStageB), sB = sA + kOzStageA;
-#pragma unroll
-          for (int ks = 0; ks < kOzBK / 32; ++ks) {
-            for (int s = 0; s < S; ++s) {
-              const uint64_t adesc = kmajor_sw128_desc(sA + (s >> 1) * kOzPairA + (s & 1) * kOzBK + ks * 32);
-              const uint32_t acc = (kb | ks | s) != 0;
-#pragma unroll
-              for (int par = 0; par < 2; ++par) {          // B slices t = par, par+2, ..  with s + t <= S-1
-                const int last = S - 1 - s - par;
-                if (last < 0) continue;
-                const int c = (last >> 1) + 1;
-                const uint64_t bdesc = kmajor_sw128_desc(sB + par * kOzBK + ks * 32);
-                mma_i8(tmem + (uint32_t)(kOzBN * diag_pos(s + par)), adesc, bdesc, i8_idesc(kOzBN * c), acc);
-              }
+          if (!(a.dbg & 16)) {
+            const uint64_t dA = kmajor_sw128_desc(sA), dB = kmajor_sw128_desc(sB);
+            const uint32_t first = kb != kb0;
+            switch (S) {     // fully unrolled per slice count: the issuing thread must not be the bottleneck
+              case 8: issue_stage<8>(dA, dB, tmem, first); break;
+              case 7: issue_stage<7>(dA, dB, tmem, first); break;
+              case 6: issue_stage<6>(dA, dB, tmem, first); break;
+              case 5: issue_stage<5>(dA, dB, tmem, first); break;
+              case 4: issue_stage<4>(dA, dB, tmem, first); break;
+              case 3: issue_stage<3>(dA, dB, tmem, first); break;
+              default: issue_stage<2>(dA, dB, tmem, first); break;
             }
           }
           tc_commit(bar_empty + 8 * stage);
-          if (kb == nkb - 1) tc_commit(bar_tfull);
+          if (kb == kb1 - 1) tc_commit(bar_tfull);
           if (++stage == kOzStages) { stage = 0; phase ^= 1; }
         }
         tphase ^= 1;
       }
     }
   } else {
-    // ===== epilogue: TMEM -> fp64 Horner sum over the diagonals -> scaled store =====
+    // ===== epilogue (8 warps): TMEM -> fp64 Horner sum over the diagonals in registers -> release TMEM ->
+    //       scale, transpose through shared memory, coalesced store (overlaps the next tile's MMAs) =====
     const int q = warp & 3;                       // TMEM lane quarter this warp may read
+    const int h = (warp - 2) >> 2;                // column half of the tile this warp owns
+    double* stg = reinterpret_cast<double*>(oz_smem_raw + (bars + 64 - raw)) + (warp - 2) * (32 * 16);
     uint32_t tphase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile / num_nt) * kOzBM, n0 = (tile % num_nt) * kOzBN;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int tile = item % num_tiles;
+      double* Cz = a.C + (long)(item / num_tiles) * a.zstride;
+      const int m0 = (tile / num_nt) * kOzBM, n0 = (tile % num_nt) * kOzBN + 32 * h;
       const long row = m0 + 32 * q + lane;
-      const bool row_ok = row < a.M;
-      const double sa = row_ok ? pow2d(a.ea[row] - 12) : 0.0;
+      const double sa = row < a.M ? pow2d(a.ea[row] - 12) : 0.0;
       mbar_wait(bar_tfull, tphase);
       tc_fence_after();
-      const uint32_t tl = tmem + ((uint32_t)(32 * q) << 16);
-#pragma unroll 1
-      for (int c = 0; c < kOzBN / 16; ++c) {
-        double acc[16];
+      const uint32_t tl = tmem + ((uint32_t)(32 * q) << 16) + 32 * h;
+      double acc[2][16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) acc[j] = 0.0;
-        for (int d = S - 1; d >= 0; --d) {
-          uint32_t v[16];
-          tmem_ld16(tl + (uint32_t)(kOzBN * diag_pos(d) + 16 * c), v);
+      for (int cg = 0; cg < 2; ++cg) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc[cg][j] = 0.0;
+        if (a.dbg & 8) continue;
+#pragma unroll
+        for (int dh = 4; dh >= 0; dh -= 4) {      // diagonals dh+3 .. dh, four TMEM loads in flight
+          uint32_t v[4][16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (dh + 3 - i < S) tmem_ld16(tl + (uint32_t)(kOzBN * diag_pos(dh + 3 - i) + 16 * cg), v[i]);
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 16; ++j) acc[j] = fma(acc[j], 0.0078125, (double)(int)v[j]);
-        }
-        if (row_ok) {
-          double* out = a.C + row * a.ldc + n0 + 16 * c;
+          for (int i = 0; i < 4; ++i)
+            if (dh + 3 - i < S) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int col = n0 + 16 * c + j;
-            if (col < a.N) out[j] = acc[j] * sa * pow2d(a.eb[col]);
-          }
+              for (int j = 0; j < 16; ++j) {
+                // int32 -> double through the 2^52 + 2^31 offset (exact; keeps the conversion off the I2F path)
+                const double dv = __hiloint2double(0x43300000, (int)(v[i][j] ^ 0x80000000u)) - 4503601774854144.0;
+                acc[cg][j] = fma(acc[cg][j], 0.0078125, dv);
+              }
+            }
         }
       }
       tc_fence_before();
-      mbar_arrive(bar_tempty);
+      mbar_arrive(bar_tempty);                    // TMEM is free: the next tile's MMAs may start
       tphase ^= 1;
+#pragma unroll
+      for (int cg = 0; cg < 2; ++cg) {
+        if (a.dbg & 32) break;
+        const int c0 = n0 + 16 * cg;
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int col = c0 + j;
+          const double sb = col < a.N ? pow2d(a.eb[col]) : 0.0;
+          stg[lane * 16 + (j ^ (lane & 15))] = acc[cg][j] * sa * sb;
+        }
+        __syncwarp();
+        const int cc = lane & 15;
+#pragma unroll 4
+        for (int r2 = 0; r2 < 16; ++r2) {
+          const int rr = 2 * r2 + (lane >> 4);
+          const long grow = m0 + 32 * q + rr;
+          if (grow < a.M && c0 + cc < a.N) {
+            double* dst = Cz + grow * a.ldc + c0 + cc;
+            const double val = stg[rr * 16 + (cc ^ (rr & 15))];
+            *dst = a.accumulate ? *dst + val : val;
+          }
+        }
+      }
     }
   }
 
@@ -288,6 +349,64 @@ oz_slice_rows_kernel(const double* __restrict__ X, long ldx, long rows, int cols
         *reinterpret_cast<uint32_t*>(q + (s >> 1) * pair_stride + r * ldk + (k >> 6) * 128 + (s & 1) * 64 + (k & 63)) = w;
       }
     }
+  }
+}
+
+// Column-wise |max| of a rows x cols matrix as monotone bit patterns (non-negative doubles order like their bits).
+__global__ void __launch_bounds__(256)
+oz_col_absmax_kernel(const double* __restrict__ X, long ldx, long rows, int cols, unsigned long long* __restrict__ mx) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int rl = threadIdx.x >> 5;
+  __shared__ double red[8][33];
+  double m = 0.0;
+  if (c < cols)
+    for (long r = (long)blockIdx.y * 8 + rl; r < rows; r += (long)gridDim.y * 8) m = fmax(m, fabs(X[r * ldx + c]));
+  red[rl][threadIdx.x & 31] = m;
+  __syncthreads();
+  if (rl == 0 && c < cols) {
+#pragma unroll
+    for (int i = 1; i < 8; ++i) m = fmax(m, red[i][threadIdx.x]);
+    atomicMax(mx + c, (unsigned long long)__double_as_longlong(m));
+  }
+}
+
+__global__ void oz_exps_from_max_kernel(const unsigned long long* __restrict__ mx, int n, int* __restrict__ exps) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double m = __longlong_as_double((long long)mx[i]);
+  exps[i] = (m > 0.0 && m < 1.0e300) ? ilogb(m) + 1 : 0;
+}
+
+// Slices of X^T: output row = column c of X (rows x cols), K runs over the rows of X.  One block transposes a
+// 64 (rows of X) x 64 (columns) tile through shared memory; thread (quarter, c) turns 16 consecutive k of column c
+// into one 16-byte store per slice.
+__global__ void __launch_bounds__(256)
+oz_slice_cols_kernel(const double* __restrict__ X, long ldx, long rows, int cols, int S, int8_t* __restrict__ q,
+                     int ldk, long pair_stride, const int* __restrict__ exps) {
+  __shared__ double tile[64][65];
+  const long r0 = (long)blockIdx.x * 64;
+  const int c0 = blockIdx.y * 64;
+  for (int e = threadIdx.x; e < 64 * 64; e += 256) {
+    const int i = e >> 6, c = e & 63;
+    tile[i][c] = (r0 + i < rows && c0 + c < cols) ? X[(r0 + i) * ldx + c0 + c] : 0.0;
+  }
+  __syncthreads();
+  const int c = threadIdx.x & 63, quarter = threadIdx.x >> 6;
+  if (c0 + c >= cols) return;
+  const int e = exps[c0 + c];
+  double t[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) t[j] = scalbn(tile[16 * quarter + j][c], 6 - e);
+  int8_t* orow = q + (long)(c0 + c) * ldk + (long)blockIdx.x * 128 + quarter * 16;
+  for (int s = 0; s < S; ++s) {
+    uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const double d = rint(t[j]);
+      t[j] = (t[j] - d) * 128.0;
+      w[j >> 2] |= ((uint32_t)(__double2int_rn(d)) & 0xffu) << (8 * (j & 3));
+    }
+    *reinterpret_cast<uint4*>(orow + (s >> 1) * pair_stride + (s & 1) * 64) = make_uint4(w[0], w[1], w[2], w[3]);
   }
 }
 
@@ -340,18 +459,56 @@ cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S,
   return cudaGetLastError();
 }
 
+// Slices of X^T for a contraction over the ROWS of X (rows x cols): q is [pairs][cols][oz_ldk(rows)], exps[cols].
+// mx: scratch of `cols` 8-byte words.
+cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
+                          unsigned long long* mx, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return cudaSuccess;
+  if (S < 1 || S > kOzMaxS || rows > (1L << 30) || ldk != oz_ldk((int)rows)) return cudaErrorInvalidValue;
+  cudaError_t e = cudaMemsetAsync(mx, 0, sizeof(unsigned long long) * cols, st);
+  if (e != cudaSuccess) return e;
+  const int gy = (int)std::min<long>((rows + 63) / 64, 148L * 4 / ((cols + 31) / 32) + 1);
+  note_launch(3);
+  oz_col_absmax_kernel<<<dim3((cols + 31) / 32, gy), 256, 0, st>>>(X, ldx, rows, cols, mx);
+  oz_exps_from_max_kernel<<<(cols + 255) / 256, 256, 0, st>>>(mx, cols, exps);
+  oz_slice_cols_kernel<<<dim3((unsigned)((rows + 63) / 64), (cols + 63) / 64), 256, 0, st>>>(
+      X, ldx, rows, cols, S, q, ldk, (long)cols * ldk, exps);
+  return cudaGetLastError();
+}
+
 // C (M x N, ld = ldc) = A * B^T from the int8 slices of A (M rows) and B (N rows); K bytes per row, pitch ldk.
+int oz_split(long M, int N, int K, int S) {
+  const long tiles = ((M + kOzBM - 1) / kOzBM) * ((N + kOzBN - 1) / kOzBN);
+  const int nkb = (K + kOzBK - 1) / kOzBK;
+  const int max_kb = (int)(((1L << 31) - 1) / ((long)S * 4096 * kOzBK));   // int32 exactness of one diagonal
+  int nz = (nkb + max_kb - 1) / max_kb;
+  // fill the SMs: prefer the split whose item count is closest to whole waves, never chunks under 16 k-blocks
+  double best = -1.0; int best_nz = nz;
+  for (int c = nz; c <= 64 && (c == nz || nkb / c >= 16); ++c) {
+    const double waves = (double)tiles * c / 148.0;
+    const double eff = waves / std::ceil(waves) - 0.003 * c;
+    if (eff > best) { best = eff; best_nz = c; }
+    if (tiles >= 4 * 148) break;   // plenty of tiles already: no split beyond what exactness needs
+  }
+  return best_nz;
+}
+
 cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,
-                    int S, double* C, long ldc, int sm_count, cudaStream_t st) {
+                    int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st) {
   if (M <= 0 || N <= 0) return cudaSuccess;
-  if (S < 1 || S > kOzMaxS || (long)K * S * 4096 >= (1L << 31)) return cudaErrorInvalidValue;
+  if (S < 1 || S > kOzMaxS || nz < 1) return cudaErrorInvalidValue;
+  const int nkb = (K + kOzBK - 1) / kOzBK;
+  const int kb_per_z = (nkb + nz - 1) / nz;
+  nz = (nkb + kb_per_z - 1) / kb_per_z;          // no empty slices
+  if ((long)kb_per_z * kOzBK * S * 4096 >= (1L << 31)) return cudaErrorInvalidValue;
   CUtensorMap mapA, mapB;
   if (ldk != oz_ldk(K)) return cudaErrorInvalidValue;
   if (!make_slice_map(&mapA, qa, M, ldk, S, kOzBM) || !make_slice_map(&mapB, qb, N, ldk, S, kOzBN))
     return cudaErrorNotSupported;
-  OzArgs a{ea, eb, C, ldc, (int)M, N, K, S};
+  static const int dbg = getenv("SGP_OZ_DEBUG") ? atoi(getenv("SGP_OZ_DEBUG")) : 0;
+  OzArgs a{ea, eb, C, ldc, (int)M, N, K, S, nz, kb_per_z, zstride, accumulate, dbg};
   const long tiles = ((M + kOzBM - 1) / kOzBM) * ((N + kOzBN - 1) / kOzBN);
-  const int grid = (int)std::min<long>(tiles, sm_count > 0 ? sm_count : 148);
+  const int grid = (int)std::min<long>(tiles * nz, 148);
   note_launch();
   oz_gemm_kernel<<<grid, kOzThreads, kOzSmem, st>>>(mapA, mapB, a);
   return cudaGetLastError();

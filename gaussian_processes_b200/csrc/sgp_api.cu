@@ -46,6 +46,11 @@ struct sgp_handle {
   // scratch arena (re-carved every call) + persistent caches
   DevBuf arena, xg, ug, gcpart, s2part, dpart;
   int path = 0;             // 0 = choose per (n, p); 1 = dense C products; 2 = separable quadratic forms
+  // the two N x p x m products on tcgen05.mma.kind::i8 (ozaki_i8.cu): -1 = when the slab is large, 0 = never
+  // (fp64 DMMA), 2..8 = always, with that many int8 slices
+  int i8_slices = -1;
+  DevBuf xq, xe, xtq, xte;  // int8 slices of the images (row-wise and transposed per slab) + their exponents
+  bool oz_valid = false; int oz_S = 0; long oz_slab = 0;
   // cache key of the gathered copies
   const double* cache_X = nullptr; long cache_N = 0, cache_ldx = 0;
   const double* cache_U = nullptr; long cache_m = 0, cache_ldu = 0;
@@ -229,6 +234,10 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
   if (n == "kl_weight") h->kl_weight = value;
   else if (n == "profile") h->profile = value != 0.0;
   else if (n == "path") h->path = (int)value;
+  else if (n == "i8_slices") {
+    if (value != -1 && value != 0 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices must be -1, 0 or 2..8");
+    h->i8_slices = (int)value;
+  }
   else if (n == "slab_rows") return sgp_set_slab_rows(h, (long)value);
   else return fail(h, SGP_E_ARG, "sgp_set_option: unknown option " + n);
   return SGP_OK;
@@ -245,6 +254,7 @@ int sgp_get_profile(sgp_handle* h, double* stage_ms_out, int n, long* calls_out,
 int sgp_invalidate_cache(sgp_handle* h) {
   if (!h) return SGP_E_ARG;
   h->cache_valid = false;
+  h->oz_valid = false;
   return SGP_OK;
 }
 
@@ -300,26 +310,45 @@ int sgp_gemm_f64(sgp_handle* h, int al, int bl, const double* A, long lda, const
   return SGP_OK;
 }
 
-int sgp_gemm_i8emu(sgp_handle* h, const double* A, long M, long lda, const double* B, int N, long ldb, int K,
-                   int slices, double* C, long ldc, void* stream) {
+int sgp_gemm_i8emu(sgp_handle* h, int layout, const double* A, long M, long lda, const double* B, int N, long ldb,
+                   long K, int slices, double* C, long ldc, void* stream) {
   if (!h || !A || !B || !C) return fail(h, SGP_E_ARG, "sgp_gemm_i8emu: null argument");
   if (slices < 2 || slices > 8) return fail(h, SGP_E_ARG, "sgp_gemm_i8emu: slices must be in 2..8");
+  if (M <= 0 || N <= 0 || K <= 0 || K > (1L << 30)) return fail(h, SGP_E_ARG, "sgp_gemm_i8emu: bad sizes");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  const int ldk = oz_ldk(K);
+  const int ldk = oz_ldk((int)K);
+  const int nz = oz_split(M, N, (int)K, slices);
+  const long zs = M * ldc;
   size_t need = 0;
   auto acc = [&](size_t bytes) { need = ((need + 1023) & ~size_t(1023)) + bytes; };
-  acc(oz_slice_bytes(M, K, slices)); acc(oz_slice_bytes(N, K, slices)); acc((size_t)M * sizeof(int)); acc((size_t)N * sizeof(int));
+  acc(oz_slice_bytes(M, (int)K, slices)); acc(oz_slice_bytes(N, (int)K, slices));
+  acc((size_t)M * sizeof(int)); acc((size_t)N * sizeof(int)); acc((size_t)std::max<long>(M, N) * 8);
+  acc(nz > 1 ? (size_t)nz * zs * sizeof(double) : 8);
   need += 4096;
   CU(h->arena.reserve(need));
   Arena ar(h->arena.p, h->arena.bytes);
-  int8_t* qa = ar.take<int8_t>(oz_slice_bytes(M, K, slices));
-  int8_t* qb = ar.take<int8_t>(oz_slice_bytes(N, K, slices));
+  int8_t* qa = ar.take<int8_t>(oz_slice_bytes(M, (int)K, slices));
+  int8_t* qb = ar.take<int8_t>(oz_slice_bytes(N, (int)K, slices));
   int* ea = ar.take<int>(M);
   int* eb = ar.take<int>(N);
-  CU(oz_slice_rows(A, lda, M, K, slices, qa, ldk, ea, st));
-  CU(oz_slice_rows(B, ldb, N, K, slices, qb, ldk, eb, st));
-  CU(oz_gemm(qa, ea, M, qb, eb, N, K, ldk, slices, C, ldc, 0, st));
+  unsigned long long* mx = ar.take<unsigned long long>(std::max<long>(M, N));
+  double* part = ar.take<double>(nz > 1 ? (size_t)nz * zs : 1);
+  if (layout == 0) {          // A: M x K, B: N x K (K contiguous)
+    CU(oz_slice_rows(A, lda, M, (int)K, slices, qa, ldk, ea, st));
+    CU(oz_slice_rows(B, ldb, N, (int)K, slices, qb, ldk, eb, st));
+  } else {                    // A: K x M, B: K x N (contraction over the rows)
+    CU(oz_slice_cols(A, lda, K, (int)M, slices, qa, ldk, ea, mx, st));
+    CU(oz_slice_cols(B, ldb, K, N, slices, qb, ldk, eb, mx, st));
+  }
+  if (nz > 1) {
+    CU(oz_gemm(qa, ea, M, qb, eb, N, (int)K, ldk, slices, part, ldc, nz, zs, 0, st));
+    const int kbz = (((int)K + 63) / 64 + nz - 1) / nz;
+    slice_reduce(part, (((int)K + 63) / 64 + kbz - 1) / kbz, zs, zs, C, 0, st);
+  } else {
+    CU(oz_gemm(qa, ea, M, qb, eb, N, (int)K, ldk, slices, C, ldc, 1, 0, 0, st));
+  }
+  CU(cudaGetLastError());
   return SGP_OK;
 }
 
@@ -431,6 +460,12 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   bool use_sep = sep_quad_supported(n) && (12.0 * n * n * n < 4.0 * (double)p * p);
   if (h->path == 1) use_sep = false;
   if (h->path == 2) use_sep = sep_quad_supported(n);
+  // int8-slice tensor-core products for K_lin = X (UC)^T and D = X^T R (separable path only)
+  int ozS = 0;
+  if (use_sep && h->i8_slices != 0) ozS = h->i8_slices > 0 ? h->i8_slices : (slab >= 4096 && m >= 64 ? 8 : 0);
+  const int ldkP = oz_ldk(p), ldkN = oz_ldk((int)slab);
+  const int oz_pairs = (ozS + 1) / 2;
+  const int nzO = ozS ? oz_split(p, m, (int)std::min(slab, N), ozS) : 1;
   std::vector<int> off; std::vector<double> alpha;
   if (use_sep) {
     const int ldq_sep = sep_quad_ld(n);
@@ -481,6 +516,10 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   acc((size_t)p * ldp);                                               // GCU
   acc((size_t)p * 5);                                                 // gpart
   if (streaming) { acc((size_t)slab * ldp); }                         // gathered slab when streaming from host
+  if (ozS) {                                                          // slices of UC and of R^T, exponents, col-max scratch
+    acc(oz_slice_bytes(m, p, ozS) / 8 + 16); acc((size_t)oz_pairs * m * ldkN / 8 + 16); acc(m); acc(m);
+    acc((size_t)std::max(p, m) + 8);
+  }
   need += 4096;
   CU(h->arena.reserve(need));
   Arena ar(h->arena.p, h->arena.bytes);
@@ -527,6 +566,13 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* GCU = ar.take<double>((size_t)p * ldp);
   double* gpart = ar.take<double>((size_t)p * 5);
   double* Xslab_stream = streaming ? ar.take<double>((size_t)slab * ldp) : nullptr;
+  int8_t* zuq = nullptr; int8_t* rtq = nullptr; int* zue = nullptr; int* rte = nullptr; unsigned long long* ozmx = nullptr;
+  if (ozS) {
+    zuq = (int8_t*)ar.take<double>(oz_slice_bytes(m, p, ozS) / 8 + 16);
+    rtq = (int8_t*)ar.take<double>((size_t)oz_pairs * m * ldkN / 8 + 16);
+    zue = (int*)ar.take<double>(m); rte = (int*)ar.take<double>(m);
+    ozmx = (unsigned long long*)ar.take<double>((size_t)std::max(p, m) + 8);
+  }
 
   double* Ktb_raw = qq[0]; double* Ktb = qq[1]; double* Lk = qq[2]; double* Linv = qq[3]; double* Kinv_raw = qq[4];
   double* Kinv = qq[5]; double* KV = qq[6]; double* KVK = qq[7]; double* Mg = qq[8]; double* Lv = qq[9];
@@ -598,7 +644,22 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const int nzGC = use_sep ? 1 : pick_split(gemm_tiles(p, p), slab), nzS2 = pick_split(gemm_tiles(m, m, true), slab);
   const int nzD = pick_split(gemm_tiles(p, m), slab);
   const long zGC = (long)p * ldp, zS2 = (long)m * ldm, zD = (long)p * ldm;
-  if (use_sep) CU(h->dpart.reserve((size_t)nzD * zD * sizeof(double)));
+  if (use_sep) CU(h->dpart.reserve((size_t)std::max(nzD, nzO) * zD * sizeof(double)));
+  // persistent int8 slices of the images: per slab, [pairs][rows][ldkP] for X and [pairs][p][ldkN] for X^T.
+  // Device-resident images are sliced once and reused while (X, N, ld, mask, slab, slice count) are unchanged --
+  // sgp_invalidate_cache() after modifying the images in place; host-streamed slabs are sliced every time.
+  const long nslabs_all = (N + slab - 1) / slab;
+  bool oz_reslice = true;
+  if (ozS) {
+    const long keep = streaming ? 1 : nslabs_all;
+    CU(h->xq.reserve(streaming ? oz_slice_bytes(slab, p, ozS) : oz_slice_bytes(N, p, ozS)));
+    CU(h->xe.reserve((size_t)(streaming ? slab : N) * sizeof(int)));
+    CU(h->xtq.reserve((size_t)keep * oz_pairs * p * ldkN));
+    CU(h->xte.reserve((size_t)keep * p * sizeof(int)));
+    oz_reslice = streaming || regather || !h->oz_valid || h->oz_S != ozS || h->oz_slab != slab;
+    h->oz_valid = !streaming; h->oz_S = ozS; h->oz_slab = slab;
+    CU(oz_slice_rows(ZU, ldp, m, p, ozS, zuq, ldkP, zue, st));      // slices of U C (this evaluation's theta)
+  }
   double* Dpart = (double*)h->dpart.p;
   CU(h->gcpart.reserve((size_t)nzGC * zGC * sizeof(double)));
   CU(h->s2part.reserve((size_t)nzS2 * zS2 * sizeof(double)));
@@ -676,7 +737,18 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       g2.A = Zs; g2.lda = ldp; g2.B = Ug; g2.ldb = ldug;
     }
     g2.C = Ks; g2.ldc = ldm; g2.M = (int)ns; g2.N = m; g2.K = p;
-    CU(gemm(st, 0, 0, kStore, false, 1, g2));
+    const long oz_si = streaming ? 0 : slab_i;                     // which persistent slice block this slab uses
+    int8_t* xq_s = nullptr; int* xe_s = nullptr; int8_t* xtq_s = nullptr; int* xte_s = nullptr;
+    if (ozS) {
+      xq_s = (int8_t*)h->xq.p + oz_slice_bytes(oz_si * slab, p, ozS);
+      xe_s = (int*)h->xe.p + oz_si * slab;
+      xtq_s = (int8_t*)h->xtq.p + (size_t)oz_si * oz_pairs * p * ldkN;
+      xte_s = (int*)h->xte.p + oz_si * p;
+      if (oz_reslice) CU(oz_slice_rows(Xs, ldxs, ns, p, ozS, xq_s, ldkP, xe_s, st));
+      CU(oz_gemm(xq_s, xe_s, ns, zuq, zue, m, p, ldkP, ozS, Ks, ldm, 1, 0, 0, st));
+    } else {
+      CU(gemm(st, 0, 0, kStore, false, 1, g2));
+    }
     mark(9);
     acos_forward(Ks, cos_s, ldm, ns, m, X1, X2, th.s02, st);
     mark(3);
@@ -707,10 +779,18 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       for (int k = 0; k < 5; ++k)
         sum_to_slot(wqpart + k, wq_reduce_blocks(ns), 5, 1.0, h->d_scal, kSlotGW + k, acc_flag, st);
       mark(6);
-      GemmArgs g5{};
-      g5.A = Xs; g5.lda = ldxs; g5.B = Ts; g5.ldb = ldm; g5.C = Dpart; g5.ldc = ldm; g5.M = p; g5.N = m; g5.K = (int)ns;
-      g5.k_chunk = (int)rup((ns + nzD - 1) / nzD, 16); g5.zstride = zD; g5.accumulate = acc_flag;
-      CU(gemm(st, 1, 1, kStore, false, nzD, g5));
+      if (ozS) {
+        // the contraction runs over the images: slices of X^T (persistent) and of R^T (this evaluation)
+        const int ldk_s = oz_ldk((int)ns);
+        if (oz_reslice) CU(oz_slice_cols(Xs, ldxs, ns, p, ozS, xtq_s, ldk_s, xte_s, ozmx, st));
+        CU(oz_slice_cols(Ts, ldm, ns, m, ozS, rtq, ldk_s, rte, ozmx, st));
+        CU(oz_gemm(xtq_s, xte_s, p, rtq, rte, m, (int)ns, ldk_s, ozS, Dpart, ldm, nzO, zD, acc_flag, st));
+      } else {
+        GemmArgs g5{};
+        g5.A = Xs; g5.lda = ldxs; g5.B = Ts; g5.ldb = ldm; g5.C = Dpart; g5.ldc = ldm; g5.M = p; g5.N = m; g5.K = (int)ns;
+        g5.k_chunk = (int)rup((ns + nzD - 1) / nzD, 16); g5.zstride = zD; g5.accumulate = acc_flag;
+        CU(gemm(st, 1, 1, kStore, false, nzD, g5));
+      }
     } else {
       // G4: Y = R Ug + diag(w) X   (into the Z buffer)
       GemmArgs g4{};
@@ -774,7 +854,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
 
   // ---- <dC_k, GC> and result assembly -----------------------------------------------------------------------
   if (use_sep) {
-    slice_reduce(Dpart, nzD, zD, zD, Dm, 0, st);
+    slice_reduce(Dpart, ozS ? oz_eff_split((int)std::min(slab, N), nzO) : nzD, zD, zD, Dm, 0, st);
     CU(mm(st, 0, 1, Dm, ldm, Ug, ldug, GCpart, ldp, p, p, m));                           // (X^T R) U
   }
   contract_dC(GCpart, nzGC, zGC, GCU, C, ldp, p, d_gx, d_gy, th, gpart, st);

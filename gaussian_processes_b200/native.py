@@ -207,16 +207,21 @@ def gemm_f64(A: torch.Tensor, B: torch.Tensor, a_layout: int = 0, b_layout: int 
     return out[:, :N]
 
 
-def gemm_i8emu(A: torch.Tensor, B: torch.Tensor, slices: int = 8) -> torch.Tensor:
-    """A @ B.T (A: [M,K], B: [N,K]) on tcgen05.mma.kind::i8 from int8 digit slices, recombined in fp64."""
+def gemm_i8emu(A: torch.Tensor, B: torch.Tensor, slices: int = 8, transposed: bool = False) -> torch.Tensor:
+    """A @ B.T (A: [M,K], B: [N,K]) -- or A.T @ B (A: [K,M], B: [K,N]) with ``transposed`` -- on
+    tcgen05.mma.kind::i8 from int8 digit slices, recombined in fp64."""
     _need_cuda(A, B)
     A, B = _c(A), _c(B)
-    M, K = A.shape
-    N = B.shape[0]
+    if transposed:
+        K, M = A.shape
+        N = B.shape[1]
+    else:
+        M, K = A.shape
+        N = B.shape[0]
     out = torch.empty((M, N), dtype=torch.float64, device=A.device)
     h = _h(A)
-    h.check(lib.sgp_gemm_i8emu(h.ptr, _ptr(A), int(M), _ld(A), _ptr(B), int(N), _ld(B), int(K), int(slices),
-                               _ptr(out), _ld(out), _stream(A.device)))
+    h.check(lib.sgp_gemm_i8emu(h.ptr, 1 if transposed else 0, _ptr(A), int(M), _ld(A), _ptr(B), int(N), _ld(B),
+                               int(K), int(slices), _ptr(out), _ld(out), _stream(A.device)))
     return out
 
 
@@ -327,6 +332,12 @@ STAGES = ("setup+inducing_fwd", "quad_forms", "gemm_X_UC", "gemm_moments", "rows
 def set_option(device: int, name: str, value: float):
     h = _lib.handle_for(device)
     h.check(lib.sgp_set_option(h.ptr, name.encode(), float(value)))
+
+
+def invalidate_cache(device: int = 0):
+    """Forget the cached gathered copies / int8 slices of the images (call after modifying X in place)."""
+    h = _lib.handle_for(device)
+    h.check(lib.sgp_invalidate_cache(h.ptr))
 
 
 def get_profile(device: int = 0, reset: bool = True):

@@ -59,7 +59,10 @@ SGP_API const char* sgp_last_error(const sgp_handle* h);
 SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
 /* options: "kl_weight" (weight of the KL adjoint in the returned gradient; ranks > 0 of an image-sharded
  * evaluation use 0 so that the all-reduced sum counts the N-independent KL term once), "profile" (1 = record
- * CUDA events at the stage boundaries of sgp_elbo_grad), "slab_rows".                                          */
+ * CUDA events at the stage boundaries of sgp_elbo_grad), "slab_rows", "path" (0 = choose, 1 = dense C products,
+ * 2 = separable quadratic forms), "i8_slices" (-1 = choose, 0 = the two N x p x m products of sgp_elbo_grad on the
+ * fp64 tensor pipe, 2..8 = on tcgen05.mma.kind::i8 with that many int8 slices per operand; see sgp_gemm_i8emu).
+ * With int8 slices the library keeps a sliced copy of device-resident images across calls (same bytes as X).     */
 SGP_API int sgp_set_option(sgp_handle* h, const char* name, double value);
 /* accumulated per-stage device milliseconds of sgp_elbo_grad since the last reset:
  * [0] setup + inducing-point forward, [1] per-image quadratic forms (separable kernel, or the dense X*C GEMM),
@@ -67,7 +70,7 @@ SGP_API int sgp_set_option(sgp_handle* h, const char* name, double value);
  * [5] sum w_i x_i^T dC_k x_i (dense path: R*U GEMM), [6] GEMM X^T R (dense path: X^T Y), [7] K^T diag(v) K GEMM,
  * [8] q x q adjoint, inducing-point backward, <dC,GC> contraction, [9] arc-cosine map (streaming pass).          */
 SGP_API int sgp_get_profile(sgp_handle* h, double* stage_ms_out, int n, long* calls_out, int reset);
-/* forget the cached masked copies of X / xtilde (call if their contents changed in place) */
+/* forget the cached masked copies and int8 slices of X / xtilde (call if their contents changed in place) */
 SGP_API int sgp_invalidate_cache(sgp_handle* h);
 /* number of kernels this library has launched through `h` since creation / last reset */
 SGP_API long sgp_launch_count(const sgp_handle* h, int reset);
@@ -129,13 +132,14 @@ SGP_API int sgp_gemm_f64(sgp_handle* h, int a_layout, int b_layout, const double
                  void* stream);
 
 /* ---- fp64-accurate GEMM on the int8 tensor cores (tcgen05.mma.kind::i8, exposed for tests and measurement) -----
- * C[M x N] (ldc) = A[M x K] (lda) * B[N x K]^T (ldb), both operands row-major with K contiguous.  The operands are
+ * layout 0: C[M x N] (ldc) = A[M x K] (lda) * B[N x K]^T (ldb), both operands row-major with K contiguous;
+ * layout 1: C = A^T B with A[K x M], B[K x N] (the contraction runs over the rows, e.g. over images).  The operands are
  * split into `slices` (2..8) signed 7-bit digits per element relative to a power-of-two scale per row; the digit
  * products are accumulated exactly in int32 in tensor memory and recombined in fp64 (csrc/ozaki_i8.cu).  With 8 slices
  * the error is <= ~2^-53 * K * max|A_i.| * max|B_j.| per element, i.e. the class of a DGEMM; results are deterministic.
  * Serves the same contractions of acosker (utils.py:969-973) / lambda_moments (utils.py:1090-1101) as sgp_gemm_f64. */
-SGP_API int sgp_gemm_i8emu(sgp_handle* h, const double* A, long M, long lda, const double* B, int N, long ldb, int K,
-                   int slices, double* C, long ldc, void* stream);
+SGP_API int sgp_gemm_i8emu(sgp_handle* h, int layout, const double* A, long M, long lda, const double* B, int N, long ldb,
+                   long K, int slices, double* C, long ldc, void* stream);
 
 /* ---- a11: the M-step closure body of varGP (utils.py:2030-2099) as ONE call -----------------------------------
  * theta -> loglik, KL and d(loglik - KL)/dtheta, with X, xtilde, r, B, m_b, V_b, f_params fixed.

@@ -32,7 +32,28 @@ def main():
     B = torch.randn(192, 256, generator=g, dtype=torch.float64, device=dev)
     C = native.gemm_i8emu(A, B, 8)
     print("rowscaled", err(C, A @ B.T, A, B), flush=True)
+    # contraction over rows (X^T R shape), split-K, ragged sizes
+    for (K, M, N) in [(300, 70, 50), (5000, 200, 130), (70000, 160, 100)]:
+        At = torch.randn(K, M, generator=g, dtype=torch.float64, device=dev)
+        Bt = torch.randn(K, N, generator=g, dtype=torch.float64, device=dev)
+        Bt *= torch.exp(3 * torch.randn(1, N, generator=g, dtype=torch.float64, device=dev))
+        C = native.gemm_i8emu(At, Bt, 8, transposed=True)
+        print("transposed", K, M, N, err(C, At.T @ Bt, At.T, Bt.T), flush=True)
     if len(sys.argv) > 1 and sys.argv[1] == "time":
+        Kt, Mt, Nt = 65536, 1600, 500
+        At = torch.randn(Kt, Mt, generator=g, dtype=torch.float64, device=dev)
+        Bt = torch.randn(Kt, Nt, generator=g, dtype=torch.float64, device=dev)
+        for _ in range(2):
+            native.gemm_i8emu(At, Bt, 8, transposed=True)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            native.gemm_i8emu(At, Bt, 8, transposed=True)
+        e1.record()
+        torch.cuda.synchronize()
+        print(f"X^T R shape S=8: {e0.elapsed_time(e1) / 5:.3f} ms per call incl. slicing both operands", flush=True)
+        del At, Bt
         M, N, K = 65536, 500, 1600
         A = torch.randn(M, K, generator=g, dtype=torch.float64, device=dev)
         B = torch.randn(N, K, generator=g, dtype=torch.float64, device=dev)

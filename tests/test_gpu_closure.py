@@ -10,19 +10,22 @@ CASES = ["closure_dense_n8", "closure_local_n12", "closure_rankdef_n10", "closur
 RTOL = 1e-9   # north_star: 1e-9 relative in fp64
 
 
-def run_case(name, slab=None, path=0):
-    """path: 0 = library's choice, 1 = dense C products, 2 = separable quadratic forms (sep_quad.cu)"""
+def run_case(name, slab=None, path=0, i8=-1):
+    """path: 0 = library's choice, 1 = dense C products, 2 = separable quadratic forms (sep_quad.cu);
+    i8: -1 = library's choice, 0 = fp64 DMMA products, 2..8 = int8-slice tcgen05 products (ozaki_i8.cu)"""
     from gaussian_processes_b200 import native
     fx = load(name)
     prob, st = case_inputs(fx)
     d = torch.device("cuda:0")
     native.set_slab_rows(0, slab if slab else 0)
     native.set_option(0, "path", path)
+    native.set_option(0, "i8_slices", i8)
     out = native.elbo_grad(prob.X.to(d), prob.r.to(d), prob.xtilde.to(d), prob.n_px_side, prob.theta,
                            st["B"].to(d), st["m_b"].to(d), st["V_b"].to(d), st["logA"], st["lambda0"],
                            want_moments=True)
     native.set_slab_rows(0, 0)
     native.set_option(0, "path", 0)
+    native.set_option(0, "i8_slices", -1)
     return fx, out
 
 
@@ -54,6 +57,27 @@ def test_closure_multi_slab(name, path):
     # ragged slabs: N is not a multiple of the slab
     fx, out = run_case(name, slab=128, path=path)
     check(fx, out)
+
+
+@pytest.mark.parametrize("slab", [None, 128])
+@pytest.mark.parametrize("name", CASES)
+def test_closure_int8_slices_against_reference(name, slab):
+    """K_lin = X (UC)^T and D = X^T R on tcgen05.mma.kind::i8 with 8 int8 slices: same 1e-9 bar as the DMMA path
+    (single slab and ragged multi-slab, which also exercises split-K accumulation across slabs)."""
+    fx, out = run_case(name, slab=slab, path=2, i8=8)
+    check(fx, out)
+
+
+def test_closure_int8_slices_cached_and_invalidate():
+    """The persistent slices of the images are reused across calls and rebuilt after sgp_invalidate_cache."""
+    from gaussian_processes_b200 import native
+    fx, a = run_case("closure_c1_local", path=2, i8=8)
+    _, b = run_case("closure_c1_local", path=2, i8=8)
+    assert a["loglik"] == b["loglik"] and a["grad"] == b["grad"]
+    native.invalidate_cache(0)
+    _, c = run_case("closure_c1_local", path=2, i8=8)
+    assert a["loglik"] == c["loglik"] and a["grad"] == c["grad"]
+    check(fx, c)
 
 
 def test_closure_repeatable_and_cached():

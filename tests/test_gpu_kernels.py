@@ -43,6 +43,33 @@ def test_gemm_layouts(nat, small, al, bl, M, N, K):
     assert err < 1e-11 * max(1.0, K ** 0.5) * 10, err
 
 
+@pytest.mark.parametrize("shape", [(128, 64, 64), (300, 70, 100), (1000, 500, 1600), (129, 65, 33)])
+@pytest.mark.parametrize("slices", [8, 7])
+def test_gemm_int8_slices(nat, shape, slices):
+    """fp64-accurate GEMM on tcgen05.mma.kind::i8 (ozaki_i8.cu): error relative to sum_k |a||b| (the DGEMM bound)."""
+    M, N, K = shape
+    g = torch.Generator().manual_seed(M + N + K)
+    A = torch.randn(M, K, generator=g, dtype=torch.float64)
+    A *= torch.exp(4 * torch.randn(M, 1, generator=g, dtype=torch.float64))       # rows of very different scale
+    B = torch.randn(N, K, generator=g, dtype=torch.float64)
+    C = nat.gemm_i8emu(A.to(dev()), B.to(dev()), slices).cpu()
+    bound = A.abs() @ B.abs().T
+    tol = 4e-15 if slices == 8 else 4e-13
+    assert float(((C - A @ B.T).abs() / bound).max()) < tol
+
+
+@pytest.mark.parametrize("shape", [(300, 70, 50), (5000, 200, 130), (70001, 160, 100)])
+def test_gemm_int8_slices_over_rows(nat, shape):
+    """A^T B with the contraction over the rows (the X^T R shape): transposed slicing, split-K, ragged K."""
+    K, M, N = shape
+    g = torch.Generator().manual_seed(K)
+    A = torch.randn(K, M, generator=g, dtype=torch.float64)
+    B = torch.randn(K, N, generator=g, dtype=torch.float64) * torch.exp(3 * torch.randn(1, N, generator=g, dtype=torch.float64))
+    C = nat.gemm_i8emu(A.to(dev()), B.to(dev()), 8, transposed=True).cpu()
+    bound = A.abs().T @ B.abs()
+    assert float(((C - A.T @ B).abs() / bound).max()) < 4e-15
+
+
 def test_gemm_alpha_accumulate(nat):
     g = torch.Generator(device="cpu").manual_seed(5)
     A = torch.randn(200, 64, generator=g, dtype=torch.float64).to(dev())
