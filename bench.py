@@ -159,6 +159,29 @@ def measure_fp64_peak(dev):
     return 2 * n ** 3 / best / 1e12
 
 
+def measure_int8_peak(dev):
+    """Library int8 tensor-core GEMM (torch._int_mm -> cuBLASLt) 8192^3, best of 5, in TOP/s; None if unavailable.
+    MEASURED_PEAKS.json has no int8 entry; the fallback denominator is 2 x its dense bf16 figure."""
+    try:
+        n = 8192
+        a = torch.randint(-64, 64, (n, n), dtype=torch.int8, device=dev)
+        b = torch.randint(-64, 64, (n, n), dtype=torch.int8, device=dev).t()
+        best = float("inf")
+        for i in range(7):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch._int_mm(a, b)
+            e1.record()
+            torch.cuda.synchronize()
+            if i >= 2:
+                best = min(best, e0.elapsed_time(e1) * 1e-3)
+        del a, b
+        torch.cuda.empty_cache()
+        return 2 * n ** 3 / best / 1e12
+    except Exception:
+        return None
+
+
 def secondary_metrics(native, dev, X, r, xt, Cm, mask, theta, B, ev_keep, m_b, V_b, logA, lambda0, hbm_peak):
     """SURVEY 8(d) secondary passes, each timed with CUDA events on the launching stream (rank 0, N = 1 only):
     * the logA closure (a6+a7+a8): ONE streaming kernel over (lambda_m, lambda_var, r) -> f and 6 sums; algorithmic
@@ -254,6 +277,8 @@ def run_ours(args):
             dist.broadcast(t, 0)
     q = B.shape[1]
     peak_f64 = measure_fp64_peak(dev) if rank == 0 else None
+    peak_i8_lib = measure_int8_peak(dev) if rank == 0 else None
+    native.set_option(local, "i8_slices", args.i8_slices)
     sg = sharded.ShardGroup(device=dev) if world > 1 else None
 
     def step():
@@ -322,36 +347,69 @@ def run_ours(args):
     #      slab; CUDA events on the launching stream).  Algorithmic flops per stage:
     p = out["p"]
     per = {k: v / max(calls, 1) for k, v in stage_ms.items()}
+    S = args.i8_slices if args.i8_slices > 0 else (8 if args.i8_slices < 0 else 0)
+    pairs = S * (S + 1) // 2
+    i8 = S > 0
     stage_flops = {"quad_forms": 8.0 * N * n ** 3, "gemm_X_UC": 2.0 * N * p * m, "gemm_moments": 2.0 * N * m * m,
-                   "gemm_XtR": 2.0 * N * p * m, "gemm_KtvK": 2.0 * N * m * m}
+                   "gemm_XtR_i8" if i8 else "gemm_XtR": 2.0 * N * p * m, "gemm_KtvK": 2.0 * N * m * m}
+    gemm_nm = ("oz_gemm_kernel (tcgen05.mma.kind::i8, %d int8 slices, TMA + TMEM)" % S) if i8 else \
+        "gemm_f64_kernel<64,128,...,kStore> (fp64 DMMA)"
     stage_kernel = {"quad_forms": "sep_quad_kernel<5> (per-image quadratic forms, Kronecker structure of C)",
-                    "gemm_X_UC": "gemm_f64_kernel<64,128,K-major,K-major,kStore> (K_lin = X (U C)^T)",
+                    "gemm_X_UC": gemm_nm + " (K_lin = X (U C)^T)",
                     "gemm_moments": "gemm_f64_kernel<64,128,kMoments> (T = K Mfull)",
-                    "gemm_XtR": "gemm_f64_kernel<64,128,MN-major,MN-major,kStore,split-K> (D = X^T R)",
+                    "gemm_XtR": gemm_nm + " (D = X^T R)", "gemm_XtR_i8": gemm_nm + " (D = X^T R)",
                     "gemm_KtvK": "gemm_f64_kernel<64,128,MN-major,MN-major,kscale,split-K> (K^T diag(v) K)"}
-    top = max(stage_flops, key=lambda k: per.get(k, 0.0))
-    ach = stage_flops[top] / (per[top] * 1e-3) / 1e12 if per.get(top, 0) > 0 else None
     traffic = None
     tf = os.path.join(ROOT, "profiles", "r1_top_kernel_traffic.json")
-    if os.path.exists(tf):
-        tj = json.load(open(tf))
+    tj = json.load(open(tf)) if os.path.exists(tf) else {}
+    if i8:
+        # dominant kernel: oz_gemm_kernel, launched for both N x p x m products of every slab.  Algorithmic work of a
+        # launch = 2 * (S(S+1)/2 slice pairs) * M*N*K int8 operations; duration = CUDA-event time of the two stages.
+        t_i8 = (per.get("gemm_X_UC", 0.0) + per.get("gemm_XtR_i8", 0.0)) * 1e-3
+        ops = 2.0 * pairs * (2.0 * N * p * m)
+        ach = ops / t_i8 / 1e12 if t_i8 > 0 else None
+        mp_bf16 = None
+        try:
+            mp_bf16 = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("bf16_tflops")
+        except Exception:
+            pass
+        peak = 2.0 * mp_bf16 if mp_bf16 else 4500.0
+        top = "gemm_X_UC + gemm_XtR_i8"
+        if tj.get("kernel", "").startswith("oz_gemm"):
+            traffic = tj.get("dram_bytes_per_eval")
+        roof = {"bound": "tensor", "kernel": gemm_nm + ": K_lin = X (U C)^T and D = X^T R", "stage": top,
+                "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": (ach / peak) if ach else None,
+                "traffic": traffic,
+                "ops": "int8 multiply-adds x 2, algorithmic (no tile padding): 2 * %d slice pairs * 2 * N*p*m per "
+                       "evaluation" % pairs,
+                "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops (burst); the file has no int8 entry, int8 dense "
+                                "issues at twice the bf16 rate on sm_100a" if mp_bf16 else
+                                "nominal 4.5 POP/s (MEASURED_PEAKS.json missing)"),
+                "library_int8_gemm_tops_measured": peak_i8_lib,
+                "fp64_equivalent_tflops": 2.0 * (2.0 * N * p * m) / t_i8 / 1e12 if t_i8 > 0 else None,
+                "fp64_dmma_peak_tflops_measured": peak_f64}
+    else:
+        top = max(stage_flops, key=lambda k: per.get(k, 0.0))
+        ach = stage_flops[top] / (per[top] * 1e-3) / 1e12 if per.get(top, 0) > 0 else None
         if tj.get("stage") == top:
             traffic = tj.get("dram_bytes_per_eval")
+        roof = {"bound": "tensor", "kernel": stage_kernel[top], "stage": top,
+                "achieved": ach, "peak": peak_f64, "unit": "TFLOP/s", "frac": (ach / peak_f64) if ach else None,
+                "traffic": traffic,
+                "peak_source": "cuBLAS fp64 torch.matmul 8192^3 best-of-5 measured in this run "
+                               "(MEASURED_PEAKS.json has no fp64 entry)"}
     contract_flops = 4.0 * N * p * p + 4.0 * N * p * m + 4.0 * N * q * q + 4.0 * N * m * q
     executed_flops = sum(stage_flops.values())
-    roof = {"bound": "tensor", "kernel": stage_kernel[top], "stage": top,
-            "achieved": ach, "peak": peak_f64, "unit": "TFLOP/s", "frac": (ach / peak_f64) if ach else None,
-            "traffic": traffic,
-            "peak_source": "cuBLAS fp64 torch.matmul 8192^3 best-of-5 measured in this run "
-                           "(MEASURED_PEAKS.json has no fp64 entry)",
-            "stage_ms_per_eval": per,
-            "stage_tflops": {k: stage_flops[k] / (per[k] * 1e-3) / 1e12 for k in stage_flops if per.get(k, 0) > 0},
-            "whole_eval": {"contract_flops": contract_flops, "executed_flops": executed_flops,
-                           "note": "the separable quadratic-form kernel does 8Nn^3 flops where the contract counts "
-                                   "4Np^2, so contract_tflops can exceed the pipe peak; executed_tflops cannot",
-                           "contract_tflops": contract_flops * sharded_evals_per_sec / 1e12,
-                           "executed_tflops": executed_flops * sharded_evals_per_sec / 1e12,
-                           "per": "GPU"}}
+    roof.update({
+        "stage_ms_per_eval": per,
+        "stage_tflops_fp64_equivalent": {k: stage_flops[k] / (per[k] * 1e-3) / 1e12 for k in stage_flops
+                                         if per.get(k, 0) > 0},
+        "whole_eval": {"contract_flops": contract_flops, "executed_flops": executed_flops,
+                       "note": "contract = the reference-shaped computation (4Np^2 + ...); executed counts the "
+                               "separable quadratic forms (8Nn^3) and fp64-equivalent flops of the int8-slice products",
+                       "contract_tflops": contract_flops * sharded_evals_per_sec / 1e12,
+                       "executed_tflops": executed_flops * sharded_evals_per_sec / 1e12,
+                       "per": "GPU"}})
     try:
         mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         roof["hbm_peak_gbs_measured"] = mp.get("hbm_gbs")
@@ -384,6 +442,11 @@ def run_ours(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": config_dict(w, world, {"p": p, "q": q, "images_total": N * world,
+                                             "products": ("K_lin = X(UC)^T and D = X^T R on tcgen05.mma.kind::i8 from "
+                                                          "%d int8 slices per fp64 operand (exact int32 accumulation "
+                                                          "in TMEM, fp64 recombination; error class of a DGEMM); the "
+                                                          "int8 slices of the resident images are made once, like "
+                                                          "the masked gather" % S) if i8 else "fp64 DMMA",
                                              "images_per_sec": sharded_evals_per_sec * N * world,
                                              "sharded_problem_evals_per_sec": sharded_evals_per_sec,
                                              "unit_of_work": "one ELBO+grad evaluation over N images x m inducing "
@@ -407,6 +470,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--i8-slices", type=int, default=-1,
+                    help="-1: library's choice (8 int8 slices on tcgen05 at this size), 0: fp64 DMMA products, 2..8")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     if args.impl == "reference":

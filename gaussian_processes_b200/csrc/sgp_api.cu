@@ -784,6 +784,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
         const int ldk_s = oz_ldk((int)ns);
         if (oz_reslice) CU(oz_slice_cols(Xs, ldxs, ns, p, ozS, xtq_s, ldk_s, xte_s, ozmx, st));
         CU(oz_slice_cols(Ts, ldm, ns, m, ozS, rtq, ldk_s, rte, ozmx, st));
+        mark(10);
         CU(oz_gemm(xtq_s, xte_s, p, rtq, rte, m, (int)ns, ldk_s, ozS, Dpart, ldm, nzO, zD, acc_flag, st));
       } else {
         GemmArgs g5{};

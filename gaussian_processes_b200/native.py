@@ -325,8 +325,9 @@ def launch_count(device: int = 0, reset: bool = False) -> int:
     return _lib.handle_for(device).launch_count(reset)
 
 
+# with int8 slices stage 6 is the transposed slicing of R (and of X when not cached) and stage 10 the product itself
 STAGES = ("setup+inducing_fwd", "quad_forms", "gemm_X_UC", "gemm_moments", "rows+acos_adjoint", "wq_reduce", "gemm_XtR",
-          "gemm_KtvK", "tail_qxq+inducing_bwd+contract", "acos_map")
+          "gemm_KtvK", "tail_qxq+inducing_bwd+contract", "acos_map", "gemm_XtR_i8")
 
 
 def set_option(device: int, name: str, value: float):

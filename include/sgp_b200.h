@@ -68,7 +68,8 @@ SGP_API int sgp_set_option(sgp_handle* h, const char* name, double value);
  * [0] setup + inducing-point forward, [1] per-image quadratic forms (separable kernel, or the dense X*C GEMM),
  * [2] GEMM X (U C)^T (dense path: Z U^T), [3] moments GEMM, [4] per-image moments + adjoint of the acos map,
  * [5] sum w_i x_i^T dC_k x_i (dense path: R*U GEMM), [6] GEMM X^T R (dense path: X^T Y), [7] K^T diag(v) K GEMM,
- * [8] q x q adjoint, inducing-point backward, <dC,GC> contraction, [9] arc-cosine map (streaming pass).          */
+ * [8] q x q adjoint, inducing-point backward, <dC,GC> contraction, [9] arc-cosine map (streaming pass),
+ * [10] with int8 slices: the X^T R product itself ([6] then holds the transposed slicing of R).                 */
 SGP_API int sgp_get_profile(sgp_handle* h, double* stage_ms_out, int n, long* calls_out, int reset);
 /* forget the cached masked copies and int8 slices of X / xtilde (call if their contents changed in place) */
 SGP_API int sgp_invalidate_cache(sgp_handle* h);
