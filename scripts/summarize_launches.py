@@ -2,7 +2,7 @@
 ELBO+grad evaluation (from the last build_C_kernel launch of the fused closure to the end of that evaluation),
 grouped by kernel, with each kernel's share of the evaluation.
 
-usage: python scripts/summarize_launches.py gpurun_out/launches.csv [launches_per_eval] > profiles/rN_launches_summary.txt
+usage: python scripts/summarize_launches.py gpurun_out/launches.csv [launches_per_eval [first_launch]] > profiles/rN_launches_summary.txt
 """
 import csv
 import re
@@ -34,7 +34,7 @@ def main():
     per_eval = int(sys.argv[2]) if len(sys.argv) > 2 else starts[-1] - starts[-2]
     # the last FULL evaluation of the device-resident timed loop: a window of per_eval launches from a build_C
     cand = [s for s in starts if s + per_eval <= len(rows)]
-    s0 = cand[-1]
+    s0 = int(sys.argv[3]) if len(sys.argv) > 3 else cand[-1]
     ev = rows[s0:s0 + per_eval]
     total = sum(t for _, t in ev)
     agg = OrderedDict()
