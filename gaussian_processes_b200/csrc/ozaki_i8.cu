@@ -144,6 +144,9 @@ struct OzArgs {
   double* C; long ldc;
   int M, N, K, S;
   int nz, kb_per_z; long zstride; int accumulate;   // split-K: slice z covers k-blocks [z*kb_per_z, ..) -> C + z*zstride
+  // optional moments epilogue (T = K Mfull^T, utils.py:1090-1101): per 16-column group g of the output,
+  //   part1[g*ldpart + row] = sum_col C*aux,  part2[g*ldpart + row] = sum_col aux*colvec
+  const double* aux; long ldaux; const double* colvec; double* part1; double* part2; long ldpart;
   int dbg;   // timing experiments only: 1 = skip A loads, 2 = skip B loads, 4 = every tile loads A rows 0..127
 };
 
@@ -284,11 +287,26 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         if (a.dbg & 32) break;
         const int c0 = n0 + 16 * cg;
         __syncwarp();
+        double t1 = 0.0, t2 = 0.0;               // moments epilogue: this row's sums over the 16-column group
+        const bool mom = a.part1 != nullptr && row < a.M;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int col = c0 + j;
-          const double sb = col < a.N ? pow2d(a.eb[col]) : 0.0;
-          stg[lane * 16 + (j ^ (lane & 15))] = acc[cg][j] * sa * sb;
+        for (int j = 0; j < 16; j += 2) {
+          const int col = c0 + j;                // N is padded to even leading dimensions: col, col+1 share validity
+          const double sb0 = col < a.N ? pow2d(a.eb[col]) : 0.0, sb1 = col + 1 < a.N ? pow2d(a.eb[col + 1]) : 0.0;
+          const double v0 = acc[cg][j] * sa * sb0, v1 = acc[cg][j + 1] * sa * sb1;
+          stg[lane * 16 + (j ^ (lane & 15))] = v0;
+          stg[lane * 16 + ((j + 1) ^ (lane & 15))] = v1;
+          if (mom && col < a.N) {
+            const double2 kv = *reinterpret_cast<const double2*>(a.aux + row * a.ldaux + col);
+            const double k1 = col + 1 < a.N ? kv.y : 0.0;
+            t1 = fma(v0, kv.x, fma(v1, k1, t1));
+            t2 = fma(kv.x, __ldg(a.colvec + col), t2);
+            if (col + 1 < a.N) t2 = fma(k1, __ldg(a.colvec + col + 1), t2);
+          }
+        }
+        if (mom && c0 < a.N) {
+          a.part1[(long)(c0 >> 4) * a.ldpart + row] = t1;
+          a.part2[(long)(c0 >> 4) * a.ldpart + row] = t2;
         }
         __syncwarp();
         const int cc = lane & 15;
@@ -494,7 +512,8 @@ int oz_split(long M, int N, int K, int S) {
 }
 
 cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,
-                    int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st) {
+                    int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st,
+                    const OzMoments* mom) {
   if (M <= 0 || N <= 0) return cudaSuccess;
   if (S < 1 || S > kOzMaxS || nz < 1) return cudaErrorInvalidValue;
   const int nkb = (K + kOzBK - 1) / kOzBK;
@@ -506,7 +525,10 @@ cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, c
   if (!make_slice_map(&mapA, qa, M, ldk, S, kOzBM) || !make_slice_map(&mapB, qb, N, ldk, S, kOzBN))
     return cudaErrorNotSupported;
   static const int dbg = getenv("SGP_OZ_DEBUG") ? atoi(getenv("SGP_OZ_DEBUG")) : 0;
-  OzArgs a{ea, eb, C, ldc, (int)M, N, K, S, nz, kb_per_z, zstride, accumulate, dbg};
+  OzArgs a{ea, eb, C, ldc, (int)M, N, K, S, nz, kb_per_z, zstride, accumulate,
+           mom ? mom->aux : nullptr, mom ? mom->ldaux : 0, mom ? mom->colvec : nullptr, mom ? mom->part1 : nullptr,
+           mom ? mom->part2 : nullptr, mom ? mom->ldpart : 0, dbg};
+  if (mom && (nz != 1 || accumulate)) return cudaErrorInvalidValue;
   const long tiles = ((M + kOzBM - 1) / kOzBM) * ((N + kOzBN - 1) / kOzBN);
   const int grid = (int)std::min<long>(tiles * nz, 148);
   note_launch();

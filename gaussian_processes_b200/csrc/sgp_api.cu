@@ -62,7 +62,8 @@ struct sgp_handle {
   double* h_out = nullptr;  // pinned
   std::map<std::string, DebugEntry> dbg;
   // second stream + events for the host-streaming variant
-  cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
+  cudaStream_t copy_stream = nullptr, compute_stream = nullptr, side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   DevBuf hx[2], hr, small;
   cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr};
   // options
@@ -500,7 +501,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   for (int i = 0; i < 6; ++i) acc((size_t)m * ldm);                   // Kraw, Kt, cosU, Mfull, Sig2, GKt
   for (int i = 0; i < 3; ++i) acc((size_t)m * ldq);                   // tmp_mq x3
   for (int i = 0; i < 14; ++i) acc((size_t)q * ldq);                  // q x q scratch
-  acc(64 * ldq); acc(chol_winv_elems(q));                             // tri-inverse tmp, inverses of L's diagonal blocks
+  acc(64 * ldq); acc(chol_winv_elems(q)); acc(chol_winv_elems(q));    // tri-inverse tmp, inverses of L's diagonal blocks (x2)
   for (int i = 0; i < 12; ++i) acc(ldm);                              // small vectors
   acc(use_sep ? 1 : (size_t)slab * ldp);                              // Z / Y (dense path only)
   if (use_sep) {
@@ -510,7 +511,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   for (int i = 0; i < 3; ++i) acc((size_t)slab * ldm);                // K, cos, T/R
   for (int i = 0; i < 6; ++i) acc(slab);                              // s, X1, u, v, w (+1)
   for (int i = 0; i < 3; ++i) acc(N);                                 // lam_m, lam_var, f (when not supplied)
-  acc((size_t)std::max(ntp, ntm) * ldpartN * 3);                      // partN, pm1, pm2
+  const int ng16 = (m + 15) / 16;                                     // 16-column groups of the int8 moments epilogue
+  acc((size_t)std::max(std::max(ntp, ntm), ozS ? ng16 : 0) * ldpartN * 3);   // partN, pm1, pm2
   acc((size_t)nblk_mom * 4); acc((size_t)nblk_bwd * ldm * 2); acc(nblk_bwd);
   acc((size_t)nblk_bwdU * ldm); acc(nblk_bwdU);
   acc((size_t)p * ldp);                                               // GCU
@@ -519,6 +521,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   if (ozS) {                                                          // slices of UC and of R^T, exponents, col-max scratch
     acc(oz_slice_bytes(m, p, ozS) / 8 + 16); acc((size_t)oz_pairs * m * ldkN / 8 + 16); acc(m); acc(m);
     acc((size_t)std::max(p, m) + 8);
+    acc(oz_slice_bytes(slab, m, ozS) / 8 + 16); acc(oz_slice_bytes(m, m, ozS) / 8 + 16); acc(slab / 2 + 8); acc(m);   // K, Mfull slices
   }
   need += 4096;
   CU(h->arena.reserve(need));
@@ -539,6 +542,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* qq[14]; for (int i = 0; i < 14; ++i) qq[i] = ar.take<double>((size_t)q * ldq);
   double* tri_tmp = ar.take<double>(64 * ldq);
   double* winv = ar.take<double>(chol_winv_elems(q));
+  double* winv2 = ar.take<double>(chol_winv_elems(q));
   double* vecs[12]; for (int i = 0; i < 12; ++i) vecs[i] = ar.take<double>(ldm);
   double* Zs = ar.take<double>(use_sep ? 1 : (size_t)slab * ldp);
   int* d_off = nullptr; double* d_alpha = nullptr; double* Qs = nullptr; double* wqpart = nullptr; double* Dm = nullptr;
@@ -556,7 +560,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* lam_m = in.lam_m ? in.lam_m : ar.take<double>(N);
   double* lam_var = in.lam_var ? in.lam_var : ar.take<double>(N);
   double* fvec = in.f ? in.f : ar.take<double>(N);
-  const int ntmax = std::max(ntp, ntm);
+  const int ntmax = std::max(std::max(ntp, ntm), ozS ? ng16 : 0);
   double* partN = ar.take<double>((size_t)ntmax * ldpartN); double* pm1 = ar.take<double>((size_t)ntmax * ldpartN);
   double* pm2 = ar.take<double>((size_t)ntmax * ldpartN);
   double* blockpart = ar.take<double>((size_t)nblk_mom * 4);
@@ -566,16 +570,20 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* GCU = ar.take<double>((size_t)p * ldp);
   double* gpart = ar.take<double>((size_t)p * 5);
   double* Xslab_stream = streaming ? ar.take<double>((size_t)slab * ldp) : nullptr;
+  int8_t* kq = nullptr; int8_t* mq = nullptr; int* ke = nullptr; int* me = nullptr;
   int8_t* zuq = nullptr; int8_t* rtq = nullptr; int* zue = nullptr; int* rte = nullptr; unsigned long long* ozmx = nullptr;
   if (ozS) {
     zuq = (int8_t*)ar.take<double>(oz_slice_bytes(m, p, ozS) / 8 + 16);
     rtq = (int8_t*)ar.take<double>((size_t)oz_pairs * m * ldkN / 8 + 16);
     zue = (int*)ar.take<double>(m); rte = (int*)ar.take<double>(m);
     ozmx = (unsigned long long*)ar.take<double>((size_t)std::max(p, m) + 8);
+    kq = (int8_t*)ar.take<double>(oz_slice_bytes(slab, m, ozS) / 8 + 16);
+    mq = (int8_t*)ar.take<double>(oz_slice_bytes(m, m, ozS) / 8 + 16);
+    ke = (int*)ar.take<double>(slab / 2 + 8); me = (int*)ar.take<double>(m);
   }
 
   double* Ktb_raw = qq[0]; double* Ktb = qq[1]; double* Lk = qq[2]; double* Linv = qq[3]; double* Kinv_raw = qq[4];
-  double* Kinv = qq[5]; double* KV = qq[6]; double* KVK = qq[7]; double* Mg = qq[8]; double* Lv = qq[9];
+  double* Kinv = qq[5]; double* KV = qq[6]; double* KVK = qq[7]; double* Mg = qq[8];   // qq[9]: Cholesky factor of V_b (side stream)
   double* S2b = qq[10]; double* W2 = qq[11]; double* inner = qq[12]; double* Sq = qq[13];
   double* GKtb = Ktb_raw;  // reused after the forward pass
   double* bq = vecs[0]; double* bb = vecs[1]; double* kappa = vecs[2]; double* yv = vecs[3]; double* beta = vecs[4];
@@ -599,6 +607,23 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   }
   copy_mat(in.B, in.ldb, m, q, Bw, ldq, st);
   copy_mat(in.V, in.ldv, q, q, Vw, ldq, st);
+  // log det V_b does not depend on theta: its Cholesky runs on a side stream next to the K_tilde_b chain
+  bool side_pending = false;
+  if (!in.logdetV_host) {
+    if (!h->side_stream) {
+      CU(cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking));
+      CU(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+    }
+    CU(cudaEventRecord(h->ev_fork, st));
+    CU(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
+    double* Lv_side = qq[9];
+    copy_mat(Vw, ldq, q, q, Lv_side, ldq, h->side_stream);
+    CU(cholesky_lower(Lv_side, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, winv2, h->side_stream));
+    logdet_from_chol(Lv_side, ldq, q, h->d_scal, kSlotLogdetV, h->side_stream);
+    CU(cudaEventRecord(h->ev_join, h->side_stream));
+    side_pending = true;
+  }
 
   // ---- a1: C(theta) ---------------------------------------------------------------------------------
   build_C(C, ldp, p, d_gx, d_gy, th, nullptr, 0, st);
@@ -632,11 +657,6 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     lincomb(Mg, ldq, q, q, 2.0, KVK, ldq, -2.0, Kinv, ldq, 0.0, st);                    // Mg = 2 KVK - 2 Kinv
     CU(mm(st, 0, 1, Bw, ldq, Mg, ldq, tmq2, ldq, m, q, q));                              // B Mg
     CU(mm(st, 0, 0, tmq2, ldq, Bw, ldq, Mfull, ldm, m, m, q));                           // Mfull = B Mg B^T
-    if (!in.logdetV_host) {
-      copy_mat(Vw, ldq, q, q, Lv, ldq, st);
-      CU(cholesky_lower(Lv, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, winv, st));
-      logdet_from_chol(Lv, ldq, q, h->d_scal, kSlotLogdetV, st);
-    }
     kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, qq[12], st);   // qq[12]: free until the tail
   }
 
@@ -659,6 +679,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     oz_reslice = streaming || regather || !h->oz_valid || h->oz_S != ozS || h->oz_slab != slab;
     h->oz_valid = !streaming; h->oz_S = ozS; h->oz_slab = slab;
     CU(oz_slice_rows(ZU, ldp, m, p, ozS, zuq, ldkP, zue, st));      // slices of U C (this evaluation's theta)
+    CU(oz_slice_rows(Mfull, ldm, m, m, ozS, mq, oz_ldk(m), me, st));
   }
   double* Dpart = (double*)h->dpart.p;
   CU(h->gcpart.reserve((size_t)nzGC * zGC * sizeof(double)));
@@ -756,9 +777,15 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     GemmArgs g3{};
     g3.A = Ks; g3.lda = ldm; g3.B = Mfull; g3.ldb = ldm; g3.C = Ts; g3.ldc = ldm; g3.M = (int)ns; g3.N = m; g3.K = m;
     g3.aux = Ks; g3.ldaux = ldm; g3.colvec = bb; g3.part1 = pm1; g3.part2 = pm2; g3.ldpart = ldpartN;
-    CU(gemm(st, 0, 0, kMoments, false, 1, g3));
+    if (ozS) {
+      CU(oz_slice_rows(Ks, ldm, ns, m, ozS, kq, oz_ldk(m), ke, st));
+      const OzMoments mom{Ks, ldm, bb, pm1, pm2, ldpartN};
+      CU(oz_gemm(kq, ke, ns, mq, me, m, m, oz_ldk(m), ozS, Ts, ldm, 1, 0, 0, st, &mom));
+    } else {
+      CU(gemm(st, 0, 0, kMoments, false, 1, g3));
+    }
     mark(4);
-    moments_rows(s_s, pm1, pm2, ldpartN, ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
+    moments_rows(s_s, pm1, pm2, ldpartN, ozS ? ng16 : ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
                  v_s, blockpart, st);
     const int nbm = moments_rows_blocks(ns);
     sum_to_slot(blockpart + 0, nbm, 4, 1.0, h->d_scal, kSlotRLam, acc_flag, st);
@@ -862,6 +889,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   for (int k = 0; k < 5; ++k) sum_to_slot(gpart + k, p, 5, 1.0, h->d_scal, kSlotG + k, 0, st);
   if (use_sep)
     for (int k = 0; k < 5; ++k) sum_to_slot(h->d_scal + kSlotGW + k, 1, 1, 1.0, h->d_scal, kSlotG + k, 1, st);
+  if (side_pending) CU(cudaStreamWaitEvent(st, h->ev_join, 0));
   finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p, in.logdetV_host ? *in.logdetV_host : 0.0,
            in.logdetV_host ? 1 : 0, h->d_out, st);
   CU(cudaGetLastError());

@@ -177,7 +177,10 @@ cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S,
 // oz_gemm never exceeds, is ceil(nkb / ceil(nkb / nz))); accumulate: C += instead of C =
 int oz_split(long M, int N, int K, int S);
 inline int oz_eff_split(int K, int nz) { const int nkb = (K + 63) / 64, kbz = (nkb + nz - 1) / nz; return (nkb + kbz - 1) / kbz; }
+// optional moments epilogue: per 16-column group g, part1[g*ldpart + row] = sum_col C*aux, part2 = sum_col aux*colvec
+struct OzMoments { const double* aux; long ldaux; const double* colvec; double* part1; double* part2; long ldpart; };
 cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,
-                    int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st);
+                    int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st,
+                    const OzMoments* mom = nullptr);
 
 }  // namespace sgp
