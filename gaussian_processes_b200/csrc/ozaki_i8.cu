@@ -513,7 +513,7 @@ int oz_split(long M, int N, int K, int S) {
 
 cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,
                     int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st,
-                    const OzMoments* mom) {
+                    const OzMoments* mom, int max_ctas) {
   if (M <= 0 || N <= 0) return cudaSuccess;
   if (S < 1 || S > kOzMaxS || nz < 1) return cudaErrorInvalidValue;
   const int nkb = (K + kOzBK - 1) / kOzBK;
@@ -530,7 +530,7 @@ cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, c
            mom ? mom->part2 : nullptr, mom ? mom->ldpart : 0, dbg};
   if (mom && (nz != 1 || accumulate)) return cudaErrorInvalidValue;
   const long tiles = ((M + kOzBM - 1) / kOzBM) * ((N + kOzBN - 1) / kOzBN);
-  const int grid = (int)std::min<long>(tiles * nz, 148);
+  const int grid = (int)std::min<long>(tiles * nz, max_ctas > 0 ? max_ctas : 148);   // fewer CTAs leave SMs to a concurrent stream
   note_launch();
   oz_gemm_kernel<<<grid, kOzThreads, kOzSmem, st>>>(mapA, mapB, a);
   return cudaGetLastError();

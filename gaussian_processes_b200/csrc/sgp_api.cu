@@ -64,6 +64,8 @@ struct sgp_handle {
   // second stream + events for the host-streaming variant
   cudaStream_t copy_stream = nullptr, compute_stream = nullptr, side_stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaStream_t chain_stream = nullptr; cudaEvent_t ev_chain_fork = nullptr, ev_chain_join = nullptr;
+  int overlap = 1;          // 1 = run the q x q inducing-point chain next to the first slab's quadratic forms
   DevBuf hx[2], hr, small;
   cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr};
   // options
@@ -235,6 +237,7 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
   if (n == "kl_weight") h->kl_weight = value;
   else if (n == "profile") h->profile = value != 0.0;
   else if (n == "path") h->path = (int)value;
+  else if (n == "overlap") h->overlap = value != 0.0;
   else if (n == "i8_slices") {
     if (value != -1 && value != 0 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices must be -1, 0 or 2..8");
     h->i8_slices = (int)value;
@@ -465,6 +468,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   int ozS = 0;
   if (use_sep && h->i8_slices != 0) ozS = h->i8_slices > 0 ? h->i8_slices : (slab >= 4096 && m >= 64 ? 8 : 0);
   const int ldkP = oz_ldk(p), ldkN = oz_ldk((int)slab);
+  const bool chain_overlap = use_sep && h->overlap != 0;
+  const bool tail_overlap = chain_overlap && ozS > 0;
   const int oz_pairs = (ozS + 1) / 2;
   const int nzO = ozS ? oz_split(p, m, (int)std::min(slab, N), ozS) : 1;
   std::vector<int> off; std::vector<double> alpha;
@@ -636,6 +641,20 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     g.aux = Ug; g.ldaux = ldug; g.part1 = partU; g.ldpart = ldpartU;
     CU(gemm(st, 0, 1, kRowdot, smallU, 1, g));
     norms_finalize(partU, ldpartU, ntp_s, m, th.s02, tU, X2, st);
+    // Everything below only feeds the moments (Mfull, bb) and the KL scalars: a chain of ~100 small launches that
+    // is latency-bound on a handful of SMs.  It runs on its own stream while the main stream starts the image pass
+    // (quadratic forms of the first slab on a slightly smaller grid); they join before the first moments product.
+    if (chain_overlap) {
+      if (!h->chain_stream) {
+        CU(cudaStreamCreateWithFlags(&h->chain_stream, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&h->ev_chain_fork, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&h->ev_chain_join, cudaEventDisableTiming));
+      }
+      CU(cudaEventRecord(h->ev_chain_fork, st));
+      CU(cudaStreamWaitEvent(h->chain_stream, h->ev_chain_fork, 0));
+    }
+    cudaStream_t st_main = st;
+    st = chain_overlap ? h->chain_stream : st;      // the rest of this block is issued on the chain stream
     GemmArgs a{};  // K_tilde (raw) = acos-kernel(ZU Ug^T)
     a.A = ZU; a.lda = ldp; a.B = Ug; a.ldb = ldug; a.C = Kraw; a.ldc = ldm; a.M = m; a.N = m; a.K = p;
     a.rowvec = X2; a.colvec = X2; a.C2 = cosU; a.s02 = th.s02;
@@ -658,6 +677,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     CU(mm(st, 0, 1, Bw, ldq, Mg, ldq, tmq2, ldq, m, q, q));                              // B Mg
     CU(mm(st, 0, 0, tmq2, ldq, Bw, ldq, Mfull, ldm, m, m, q));                           // Mfull = B Mg B^T
     kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, qq[12], st);   // qq[12]: free until the tail
+    if (ozS) CU(oz_slice_rows(Mfull, ldm, m, m, ozS, mq, oz_ldk(m), me, st));
+    if (chain_overlap) CU(cudaEventRecord(h->ev_chain_join, st));
+    st = st_main;
   }
 
   // ---- split-K plans for the two reductions over images ----------------------------------------------
@@ -679,7 +701,6 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     oz_reslice = streaming || regather || !h->oz_valid || h->oz_S != ozS || h->oz_slab != slab;
     h->oz_valid = !streaming; h->oz_S = ozS; h->oz_slab = slab;
     CU(oz_slice_rows(ZU, ldp, m, p, ozS, zuq, ldkP, zue, st));      // slices of U C (this evaluation's theta)
-    CU(oz_slice_rows(Mfull, ldm, m, m, ozS, mq, oz_ldk(m), me, st));
   }
   double* Dpart = (double*)h->dpart.p;
   CU(h->gcpart.reserve((size_t)nzGC * zGC * sizeof(double)));
@@ -742,6 +763,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       sq.X = Xs; sq.ldx = ldxs; sq.nrows = ns; sq.p = p; sq.off = d_off; sq.alpha = d_alpha; sq.n = n;
       sq.er = th.er; sq.eb = th.eb; sq.ex = th.ex; sq.ey = th.ey; sq.amp = th.amp; sq.s02 = th.s02;
       sq.s = s_s; sq.nrm = X1; sq.Q = Qs;
+      if (chain_overlap && slab_i == 0) sq.max_ctas = 148 - 20;   // leave SMs to the inducing-point chain
       CU(sep_quad(sq, st));
       mark(2);
       // G2: K = acos-kernel(X (U C)^T)   -- x_i^T C u_j with the m x p matrix ZU = U C
@@ -773,6 +795,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     mark(9);
     acos_forward(Ks, cos_s, ldm, ns, m, X1, X2, th.s02, st);
     mark(3);
+    if (chain_overlap && slab_i == 0) CU(cudaStreamWaitEvent(st, h->ev_chain_join, 0));
     // G3: T = K Mfull^T ; partial lam_var / lam_m row sums                    (U:1090-1101)
     GemmArgs g3{};
     g3.A = Ks; g3.lda = ldm; g3.B = Mfull; g3.ldb = ldm; g3.C = Ts; g3.ldc = ldm; g3.M = (int)ns; g3.N = m; g3.K = m;
@@ -805,6 +828,22 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       wq_reduce(w_s, Qs, ns, wqpart, st);
       for (int k = 0; k < 5; ++k)
         sum_to_slot(wqpart + k, wq_reduce_blocks(ns), 5, 1.0, h->d_scal, kSlotGW + k, acc_flag, st);
+      mark(7);
+      // G6: Sig2 += K^T diag(v) K (before X^T R: the q x q tail depends on it, not on D)
+      {
+        GemmArgs g6{};
+        g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
+        g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
+        g6.lower_only = 1;   // K^T diag(v) K is symmetric: only the CTA tiles on and below the diagonal are computed
+        CU(gemm(st, 1, 1, kStore, false, nzS2, g6));
+      }
+      const bool last = i0 + ns >= N;
+      if (tail_overlap && last) {
+        // the q x q tail and the inducing-point backward pass start now on the chain stream; this slab's X^T R
+        // (which they do not need) runs next to them on a slightly smaller grid
+        CU(cudaEventRecord(h->ev_chain_fork, st));
+        CU(cudaStreamWaitEvent(h->chain_stream, h->ev_chain_fork, 0));
+      }
       mark(6);
       if (ozS) {
         // the contraction runs over the images: slices of X^T (persistent) and of R^T (this evaluation)
@@ -812,7 +851,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
         if (oz_reslice) CU(oz_slice_cols(Xs, ldxs, ns, p, ozS, xtq_s, ldk_s, xte_s, ozmx, st));
         CU(oz_slice_cols(Ts, ldm, ns, m, ozS, rtq, ldk_s, rte, ozmx, st));
         mark(10);
-        CU(oz_gemm(xtq_s, xte_s, p, rtq, rte, m, (int)ns, ldk_s, ozS, Dpart, ldm, nzO, zD, acc_flag, st));
+        CU(oz_gemm(xtq_s, xte_s, p, rtq, rte, m, (int)ns, ldk_s, ozS, Dpart, ldm, nzO, zD, acc_flag, st, nullptr,
+                   (tail_overlap && last) ? 148 - 20 : 0));
       } else {
         GemmArgs g5{};
         g5.A = Xs; g5.lda = ldxs; g5.B = Ts; g5.ldb = ldm; g5.C = Dpart; g5.ldc = ldm; g5.M = p; g5.N = m; g5.K = (int)ns;
@@ -831,19 +871,21 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       g5.A = Xs; g5.lda = ldxs; g5.B = Zs; g5.ldb = ldp; g5.C = GCpart; g5.ldc = ldp; g5.M = p; g5.N = p; g5.K = (int)ns;
       g5.k_chunk = (int)rup((ns + nzGC - 1) / nzGC, 16); g5.zstride = zGC; g5.accumulate = acc_flag;
       CU(gemm(st, 1, 1, kStore, false, nzGC, g5));
+      mark(7);
+      // G6: Sig2 += K^T diag(v) K
+      GemmArgs g6{};
+      g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
+      g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
+      g6.lower_only = 1;
+      CU(gemm(st, 1, 1, kStore, false, nzS2, g6));
     }
-    mark(7);
-    // G6: Sig2 += K^T diag(v) K
-    GemmArgs g6{};
-    g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
-    g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
-    g6.lower_only = 1;   // K^T diag(v) K is symmetric: only the CTA tiles on and below the diagonal are computed
-    CU(gemm(st, 1, 1, kStore, false, nzS2, g6));
     mark(8);
     if (streaming) CU(cudaEventRecord(h->ev_used[slab_i & 1], st));
   }
 
   // ---- adjoint of K_tilde_b (q x q algebra) ---------------------------------------------------------------
+  cudaStream_t st_loop = st;
+  if (tail_overlap) st = h->chain_stream;     // issued after the fork above; joins before the final contraction
   slice_reduce(S2part, nzS2, zS2, zS2, Sig2, 0, st);
   mirror_lower(Sig2, ldm, m, st);
   col_weights(kappa, nullptr, nullptr, X2, m, beta, st);                                 // beta_j = kappa_j / (2 X2_j)
@@ -879,12 +921,17 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     CU(gemm(st, 0, 1, kAxpyRow, smallU, 1, g));
     CU(mm(st, 1, 1, Ug, ldug, ZU, ldp, GCU, ldp, p, p, m));                              // Ug^T YU
   }
+  if (tail_overlap) {
+    CU(cudaEventRecord(h->ev_chain_join, st));
+    st = st_loop;
+  }
 
   // ---- <dC_k, GC> and result assembly -----------------------------------------------------------------------
   if (use_sep) {
     slice_reduce(Dpart, ozS ? oz_eff_split((int)std::min(slab, N), nzO) : nzD, zD, zD, Dm, 0, st);
     CU(mm(st, 0, 1, Dm, ldm, Ug, ldug, GCpart, ldp, p, p, m));                           // (X^T R) U
   }
+  if (tail_overlap) CU(cudaStreamWaitEvent(st, h->ev_chain_join, 0));
   contract_dC(GCpart, nzGC, zGC, GCU, C, ldp, p, d_gx, d_gy, th, gpart, st);
   for (int k = 0; k < 5; ++k) sum_to_slot(gpart + k, p, 5, 1.0, h->d_scal, kSlotG + k, 0, st);
   if (use_sep)

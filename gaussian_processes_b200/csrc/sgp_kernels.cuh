@@ -155,6 +155,7 @@ struct SepQuadArgs {
   int n;
   double er, eb, ex, ey, amp, s02;
   double* s; double* nrm; double* Q;   // Q may be null (value only)
+  int max_ctas = 0;                    // 0 = one CTA per SM; smaller grids leave SMs to a concurrent stream
 };
 bool sep_quad_supported(int n_px);
 int sep_quad_ld(int n_px);
@@ -181,6 +182,6 @@ inline int oz_eff_split(int K, int nz) { const int nkb = (K + 63) / 64, kbz = (n
 struct OzMoments { const double* aux; long ldaux; const double* colvec; double* part1; double* part2; long ldpart; };
 cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,
                     int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st,
-                    const OzMoments* mom = nullptr);
+                    const OzMoments* mom = nullptr, int max_ctas = 0);
 
 }  // namespace sgp
