@@ -321,7 +321,7 @@ def run_ours(args):
 
     # ---- end to end through the host-buffer entry point: H2D of the images inside the timed region
     native.set_option(local, "kl_weight", 1.0 if rank == 0 else 0.0)
-    Bh, mh, Vh, xth = B.cpu(), m_b.cpu(), V_b.cpu(), xt.cpu()
+    Bh, mh, Vh, xth = B.cpu().pin_memory(), m_b.cpu().pin_memory(), V_b.cpu().pin_memory(), xt.cpu().pin_memory()
     for _ in range(1):
         native.elbo_grad_host(Xh, rh, xth, n, theta, Bh, mh, Vh, prob.logA, prob.lambda0, device=local)
     barrier()

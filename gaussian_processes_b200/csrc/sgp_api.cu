@@ -2,6 +2,7 @@
 // fused M-step closure.  Host C++ only launches kernels; there is no CPU compute path.
 #include "../../include/sgp_b200.h"
 
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -40,7 +41,7 @@ struct sgp_handle {
   int device = 0;
   std::string err;
   long slab_rows = 65536;
-  long stream_slab_rows = 16384;   // host-streaming variant: smaller slabs so H2D copies overlap the compute earlier
+  long stream_slab_rows = 8192;    // host-streaming variant: smaller slabs so H2D copies overlap the compute earlier
   long launches_base = 0;
   bool gemm_ready = false;
   // scratch arena (re-carved every call) + persistent caches
@@ -67,7 +68,7 @@ struct sgp_handle {
   cudaStream_t chain_stream = nullptr; cudaEvent_t ev_chain_fork = nullptr, ev_chain_join = nullptr;
   int overlap = 1;          // 1 = run the q x q inducing-point chain next to the first slab's quadratic forms
   DevBuf hx[2], hr, small;
-  cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr};
+  cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr}, ev_small = nullptr;
   // options
   double kl_weight = 1.0;   // weight of the KL adjoint in the gradient (image-sharded ranks > 0 use 0)
   bool profile = false;     // record CUDA events at stage boundaries of the closure
@@ -227,7 +228,7 @@ const char* sgp_last_error(const sgp_handle* h) { return h ? h->err.c_str() : "n
 int sgp_set_slab_rows(sgp_handle* h, long rows) {
   if (!h) return SGP_E_ARG;
   h->slab_rows = rows > 0 ? rup(rows, 128) : 65536;
-  h->stream_slab_rows = rows > 0 ? std::min<long>(rup(rows, 128), 16384) : 16384;
+  h->stream_slab_rows = rows > 0 ? std::min<long>(rup(rows, 128), 16384) : 8192;
   return SGP_OK;
 }
 
@@ -420,6 +421,17 @@ int sgp_debug_get(sgp_handle* h, const char* name, double* dst, long capacity, l
 // =====================================================================================================
 namespace {
 
+cudaError_t ensure_copy_stream(sgp_handle* h) {
+  if (h->copy_stream) return cudaSuccess;
+  cudaError_t e = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) return e;
+  for (int i = 0; i < 2; ++i) {
+    if ((e = cudaEventCreateWithFlags(&h->ev_copied[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+    if ((e = cudaEventCreateWithFlags(&h->ev_used[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+  }
+  return cudaEventCreateWithFlags(&h->ev_small, cudaEventDisableTiming);
+}
+
 struct ClosureIn {
   const double* X; long ldx; const double* r; long N;        // device (or per-slab device staging when streaming)
   const double* U; long ldu; int m; int n_px;
@@ -428,9 +440,11 @@ struct ClosureIn {
   double* lam_m; double* lam_var; double* f;
   // host streaming (X_host != nullptr): X / r above are ignored
   const double* X_host = nullptr; const double* r_host = nullptr;
+  bool first_copy_issued = false;   // the caller already started the H2D copy of slab 0 into hx[0]
 };
 
 int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream_t st) {
+  const double t_entry = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
   int rc = ensure_ready(h); if (rc) return rc;
   h->prof_used = 0;
   auto mark = [&](int stage) {   // "stage begins now" (only when profiling)
@@ -595,15 +609,49 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* y_b = vecs[5]; double* wr = vecs[6]; double* kappaU = vecs[7]; double* wc = vecs[8]; double* wU = vecs[9];
 
   // ---- uploads -------------------------------------------------------------------------------------
-  CU(cudaMemcpyAsync(d_gx, gx.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
-  CU(cudaMemcpyAsync(d_gy, gy.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
-  CU(cudaMemcpyAsync(d_idx, idx.data(), sizeof(int) * p, cudaMemcpyHostToDevice, st));
+  // Host-streaming calls send EVERY host->device copy through the copy stream, in the order they are needed: the
+  // DMA engine serves one copy at a time, and a small upload queued behind a 200 MB slab would stall the compute
+  // stream for the slab's whole duration.
+  if (streaming) CU(ensure_copy_stream(h));
+  cudaStream_t up = streaming ? h->copy_stream : st;
+  CU(cudaMemcpyAsync(d_gx, gx.data(), sizeof(double) * p, cudaMemcpyHostToDevice, up));
+  CU(cudaMemcpyAsync(d_gy, gy.data(), sizeof(double) * p, cudaMemcpyHostToDevice, up));
+  CU(cudaMemcpyAsync(d_idx, idx.data(), sizeof(int) * p, cudaMemcpyHostToDevice, up));
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
   CU(cudaMemsetAsync(h->d_scal, 0, sizeof(double) * kNumSlots, st));
   if (use_sep) {
-    CU(cudaMemcpyAsync(d_off, off.data(), sizeof(int) * p, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(d_alpha, alpha.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_off, off.data(), sizeof(int) * p, cudaMemcpyHostToDevice, up));
+    CU(cudaMemcpyAsync(d_alpha, alpha.data(), sizeof(double) * p, cudaMemcpyHostToDevice, up));
   }
+  // ---- host streaming resources ------------------------------------------------------------------------
+  if (streaming) {
+    for (int i = 0; i < 2; ++i) CU(h->hx[i].reserve((size_t)slab * P * sizeof(double)));
+    CU(h->hr.reserve((size_t)N * sizeof(double)));
+    CU(cudaMemcpyAsync(h->hr.p, in.r_host, sizeof(double) * N, cudaMemcpyHostToDevice, up));
+    CU(cudaEventRecord(h->ev_small, up));            // the compute stream starts once the small operands are in
+    CU(cudaStreamWaitEvent(st, h->ev_small, 0));
+  }
+  auto issue_copy = [&](int si) -> cudaError_t {  // H2D of slab si into staging buffer si%2
+    const long i0 = (long)si * slab;
+    const long ns = std::min(slab, N - i0);
+    const int bsel = si & 1;
+    cudaError_t e;
+    if (si >= 2 && (e = cudaStreamWaitEvent(h->copy_stream, h->ev_used[bsel], 0)) != cudaSuccess) return e;
+    if (in.ldx == P)
+      e = cudaMemcpyAsync(h->hx[bsel].p, in.X_host + i0 * in.ldx, (size_t)ns * P * sizeof(double),
+                          cudaMemcpyHostToDevice, h->copy_stream);
+    else
+      e = cudaMemcpy2DAsync(h->hx[bsel].p, P * sizeof(double), in.X_host + i0 * in.ldx, in.ldx * sizeof(double),
+                            P * sizeof(double), ns, cudaMemcpyHostToDevice, h->copy_stream);
+    if (e != cudaSuccess) return e;
+    return cudaEventRecord(h->ev_copied[bsel], h->copy_stream);
+  };
+  const int nslabs = (int)((N + slab - 1) / slab);
+  static const bool dbg_t = getenv("SGP_TIMING") != nullptr;
+  auto now_ms = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double t_issue = now_ms();
+  if (streaming && !in.first_copy_issued) CU(issue_copy(0));
+
   if (regather) {
     if (!direct_X && !streaming) gather_cols(in.X, in.ldx, N, d_idx, p, (double*)Xg, ldp, st);
     if (!direct_U) gather_cols(in.U, in.ldu, m, d_idx, p, (double*)Ug, ldp, st);
@@ -707,41 +755,10 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   CU(h->s2part.reserve((size_t)nzS2 * zS2 * sizeof(double)));
   double* GCpart = (double*)h->gcpart.p; double* S2part = (double*)h->s2part.p;
 
-  // ---- host streaming resources ------------------------------------------------------------------------
-  if (streaming) {
-    if (!h->copy_stream) {
-      CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
-      for (int i = 0; i < 2; ++i) {
-        CU(cudaEventCreateWithFlags(&h->ev_copied[i], cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&h->ev_used[i], cudaEventDisableTiming));
-      }
-    }
-    for (int i = 0; i < 2; ++i) CU(h->hx[i].reserve((size_t)slab * P * sizeof(double)));
-    CU(h->hr.reserve((size_t)N * sizeof(double)));
-    CU(cudaMemcpyAsync(h->hr.p, in.r_host, sizeof(double) * N, cudaMemcpyHostToDevice, st));
-  }
   const double* rdev = streaming ? (const double*)h->hr.p : in.r;
 
   // ---- image pass, slab by slab ---------------------------------------------------------------------------
   int slab_i = 0;
-  auto issue_copy = [&](int si) -> cudaError_t {  // H2D of slab si into staging buffer si%2
-    const long i0 = (long)si * slab;
-    const long ns = std::min(slab, N - i0);
-    const int bsel = si & 1;
-    cudaError_t e;
-    if (si >= 2 && (e = cudaStreamWaitEvent(h->copy_stream, h->ev_used[bsel], 0)) != cudaSuccess) return e;
-    if (in.ldx == P)
-      e = cudaMemcpyAsync(h->hx[bsel].p, in.X_host + i0 * in.ldx, (size_t)ns * P * sizeof(double),
-                          cudaMemcpyHostToDevice, h->copy_stream);
-    else
-      e = cudaMemcpy2DAsync(h->hx[bsel].p, P * sizeof(double), in.X_host + i0 * in.ldx, in.ldx * sizeof(double),
-                            P * sizeof(double), ns, cudaMemcpyHostToDevice, h->copy_stream);
-    if (e != cudaSuccess) return e;
-    return cudaEventRecord(h->ev_copied[bsel], h->copy_stream);
-  };
-  const int nslabs = (int)((N + slab - 1) / slab);
-  if (streaming) CU(issue_copy(0));
-
   for (long i0 = 0; i0 < N; i0 += slab, ++slab_i) {
     const long ns = std::min(slab, N - i0);
     const int acc_flag = slab_i > 0 ? 1 : 0;
@@ -942,7 +959,10 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(double) * 16, cudaMemcpyDeviceToHost, st));
   mark(-1);
+  const double t_enq = now_ms();
   CU(cudaStreamSynchronize(st));
+  if (dbg_t) fprintf(stderr, "[sgp timing] first copy issued %.3f ms after entry; all work enqueued at %.3f; done at %.3f\n",
+                     t_issue - t_entry, t_enq - t_entry, now_ms() - t_entry);
   if (out_host) std::memcpy(out_host, h->h_out, sizeof(double) * 16);
   if (h->profile) {
     for (size_t i = 0; i + 1 < h->prof_used; ++i) {
@@ -1007,13 +1027,15 @@ int sgp_elbo_grad_host(sgp_handle* h, const double* X_host, long ldx, const doub
   CU(small.reserve((nU + nB + nV + q + 64) * sizeof(double)));
   double* dU = (double*)small.p; double* dB = dU + ((nU + 1) & ~size_t(1)); double* dV = dB + ((nB + 1) & ~size_t(1));
   double* dm = dV + ((nV + 1) & ~size_t(1));
+  CU(ensure_copy_stream(h));
+  cudaStream_t up = h->copy_stream;   // run_closure makes the compute stream wait for these (ev_small)
   CU(cudaMemcpy2DAsync(dU, P * sizeof(double), xtilde_host, ldu * sizeof(double), P * sizeof(double), m,
-                       cudaMemcpyHostToDevice, st));
+                       cudaMemcpyHostToDevice, up));
   CU(cudaMemcpy2DAsync(dB, q * sizeof(double), B_host, ldb * sizeof(double), q * sizeof(double), m,
-                       cudaMemcpyHostToDevice, st));
+                       cudaMemcpyHostToDevice, up));
   CU(cudaMemcpy2DAsync(dV, q * sizeof(double), V_b_host, ldv * sizeof(double), q * sizeof(double), q,
-                       cudaMemcpyHostToDevice, st));
-  CU(cudaMemcpyAsync(dm, m_b_host, q * sizeof(double), cudaMemcpyHostToDevice, st));
+                       cudaMemcpyHostToDevice, up));
+  CU(cudaMemcpyAsync(dm, m_b_host, q * sizeof(double), cudaMemcpyHostToDevice, up));
   ClosureIn in{};
   in.X = nullptr; in.ldx = ldx; in.r = nullptr; in.N = N; in.U = dU; in.ldu = P; in.m = m; in.n_px = n_px;
   in.theta = theta; in.B = dB; in.ldb = q; in.q = q; in.m_b = dm; in.V = dV; in.ldv = q;
