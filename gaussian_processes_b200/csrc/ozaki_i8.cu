@@ -144,11 +144,26 @@ struct OzArgs {
   double* C; long ldc;
   int M, N, K, S;
   int nz, kb_per_z; long zstride; int accumulate;   // split-K: slice z covers k-blocks [z*kb_per_z, ..) -> C + z*zstride
+  double alpha; int lower_only;   // C = alpha * A B^T; lower_only (M == N): only tiles touching the lower triangle
+  int num_tiles;                  // tiles enumerated by tile_origin()
   // optional moments epilogue (T = K Mfull^T, utils.py:1090-1101): per 16-column group g of the output,
   //   part1[g*ldpart + row] = sum_col C*aux,  part2[g*ldpart + row] = sum_col aux*colvec
   const double* aux; long ldaux; const double* colvec; double* part1; double* part2; long ldpart;
   int dbg;   // timing experiments only: 1 = skip A loads, 2 = skip B loads, 4 = every tile loads A rows 0..127
 };
+
+// origin of tile t: row-major over (m-tile, n-tile); with lower_only row-tile mt keeps its first min(2mt+2, num_nt)
+// n-tiles (the ones that touch the lower triangle: 128-row tiles against 64-column tiles)
+__device__ __forceinline__ void tile_origin(int lower_only, int tile, int num_nt, int& m0, int& n0) {
+  if (!lower_only) { m0 = (tile / num_nt) * kOzBM; n0 = (tile % num_nt) * kOzBN; return; }
+  int mt = 0, base = 0;
+  for (;;) {
+    const int cnt = min(2 * mt + 2, num_nt);
+    if (tile < base + cnt) break;
+    base += cnt; ++mt;
+  }
+  m0 = mt * kOzBM; n0 = (tile - base) * kOzBN;
+}
 
 __device__ __forceinline__ double pow2d(int e) {   // 2^e for -1022 <= e <= 1023
   return __longlong_as_double((long long)(1023 + e) << 52);
@@ -167,7 +182,7 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int S = a.S;
   const int num_nt = (a.N + kOzBN - 1) / kOzBN;
-  const int num_tiles = ((a.M + kOzBM - 1) / kOzBM) * num_nt;
+  const int num_tiles = a.num_tiles;
   const int num_items = num_tiles * a.nz;             // item = z * num_tiles + tile
   const int nkb_all = (a.K + kOzBK - 1) / kOzBK;
 
@@ -192,7 +207,8 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       int stage = 0; uint32_t phase = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
         const int tile = item % num_tiles, z = item / num_tiles;
-        const int m0 = (tile / num_nt) * kOzBM, n0 = (tile % num_nt) * kOzBN;
+        int m0, n0;
+        tile_origin(a.lower_only, tile, num_nt, m0, n0);
         const int kb0 = z * a.kb_per_z, kb1 = min(nkb_all, kb0 + a.kb_per_z);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(bar_empty + 8 * stage, phase ^ 1);
@@ -248,9 +264,11 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
       const int tile = item % num_tiles;
       double* Cz = a.C + (long)(item / num_tiles) * a.zstride;
-      const int m0 = (tile / num_nt) * kOzBM, n0 = (tile % num_nt) * kOzBN + 32 * h;
+      int m0, n0;
+      tile_origin(a.lower_only, tile, num_nt, m0, n0);
+      n0 += 32 * h;
       const long row = m0 + 32 * q + lane;
-      const double sa = row < a.M ? pow2d(a.ea[row] - 12) : 0.0;
+      const double sa = row < a.M ? pow2d(a.ea[row] - 12) * a.alpha : 0.0;
       mbar_wait(bar_tfull, tphase);
       tc_fence_after();
       const uint32_t tl = tmem + ((uint32_t)(32 * q) << 16) + 32 * h;
@@ -372,13 +390,15 @@ oz_slice_rows_kernel(const double* __restrict__ X, long ldx, long rows, int cols
 
 // Column-wise |max| of a rows x cols matrix as monotone bit patterns (non-negative doubles order like their bits).
 __global__ void __launch_bounds__(256)
-oz_col_absmax_kernel(const double* __restrict__ X, long ldx, long rows, int cols, unsigned long long* __restrict__ mx) {
+oz_col_absmax_kernel(const double* __restrict__ X, long ldx, long rows, int cols, const double* __restrict__ negsq,
+                     unsigned long long* __restrict__ mx) {
   const int c = blockIdx.x * 32 + (threadIdx.x & 31);
   const int rl = threadIdx.x >> 5;
   __shared__ double red[8][33];
   double m = 0.0;
   if (c < cols)
-    for (long r = (long)blockIdx.y * 8 + rl; r < rows; r += (long)gridDim.y * 8) m = fmax(m, fabs(X[r * ldx + c]));
+    for (long r = (long)blockIdx.y * 8 + rl; r < rows; r += (long)gridDim.y * 8)
+      m = fmax(m, fabs(X[r * ldx + c]) * (negsq ? sqrt(-negsq[r]) : 1.0));
   red[rl][threadIdx.x & 31] = m;
   __syncthreads();
   if (rl == 0 && c < cols) {
@@ -400,13 +420,13 @@ __global__ void oz_exps_from_max_kernel(const unsigned long long* __restrict__ m
 // into one 16-byte store per slice.
 __global__ void __launch_bounds__(256)
 oz_slice_cols_kernel(const double* __restrict__ X, long ldx, long rows, int cols, int S, int8_t* __restrict__ q,
-                     int ldk, long pair_stride, const int* __restrict__ exps) {
+                     int ldk, long pair_stride, const int* __restrict__ exps, const double* __restrict__ negsq) {
   __shared__ double tile[64][65];
   const long r0 = (long)blockIdx.x * 64;
   const int c0 = blockIdx.y * 64;
   for (int e = threadIdx.x; e < 64 * 64; e += 256) {
     const int i = e >> 6, c = e & 63;
-    tile[i][c] = (r0 + i < rows && c0 + c < cols) ? X[(r0 + i) * ldx + c0 + c] : 0.0;
+    tile[i][c] = (r0 + i < rows && c0 + c < cols) ? X[(r0 + i) * ldx + c0 + c] * (negsq ? sqrt(-negsq[r0 + i]) : 1.0) : 0.0;
   }
   __syncthreads();
   const int c = threadIdx.x & 63, quarter = threadIdx.x >> 6;
@@ -480,23 +500,31 @@ cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S,
 // Slices of X^T for a contraction over the ROWS of X (rows x cols): q is [pairs][cols][oz_ldk(rows)], exps[cols].
 // mx: scratch of `cols` 8-byte words.
 cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
-                          unsigned long long* mx, cudaStream_t st) {
+                          unsigned long long* mx, cudaStream_t st, const double* negsq) {
   if (rows <= 0 || cols <= 0) return cudaSuccess;
   if (S < 1 || S > kOzMaxS || rows > (1L << 30) || ldk != oz_ldk((int)rows)) return cudaErrorInvalidValue;
   cudaError_t e = cudaMemsetAsync(mx, 0, sizeof(unsigned long long) * cols, st);
   if (e != cudaSuccess) return e;
   const int gy = (int)std::min<long>((rows + 63) / 64, 148L * 4 / ((cols + 31) / 32) + 1);
   note_launch(3);
-  oz_col_absmax_kernel<<<dim3((cols + 31) / 32, gy), 256, 0, st>>>(X, ldx, rows, cols, mx);
+  oz_col_absmax_kernel<<<dim3((cols + 31) / 32, gy), 256, 0, st>>>(X, ldx, rows, cols, negsq, mx);
   oz_exps_from_max_kernel<<<(cols + 255) / 256, 256, 0, st>>>(mx, cols, exps);
   oz_slice_cols_kernel<<<dim3((unsigned)((rows + 63) / 64), (cols + 63) / 64), 256, 0, st>>>(
-      X, ldx, rows, cols, S, q, ldk, (long)cols * ldk, exps);
+      X, ldx, rows, cols, S, q, ldk, (long)cols * ldk, exps, negsq);
   return cudaGetLastError();
 }
 
 // C (M x N, ld = ldc) = A * B^T from the int8 slices of A (M rows) and B (N rows); K bytes per row, pitch ldk.
-int oz_split(long M, int N, int K, int S) {
-  const long tiles = ((M + kOzBM - 1) / kOzBM) * ((N + kOzBN - 1) / kOzBN);
+static long oz_tiles(long M, int N, int lower_only) {
+  const long mt = (M + kOzBM - 1) / kOzBM; const int nt = (N + kOzBN - 1) / kOzBN;
+  if (!lower_only) return mt * nt;
+  long t = 0;
+  for (long i = 0; i < mt; ++i) t += std::min<long>(2 * i + 2, nt);
+  return t;
+}
+
+int oz_split(long M, int N, int K, int S, int lower_only) {
+  const long tiles = oz_tiles(M, N, lower_only);
   const int nkb = (K + kOzBK - 1) / kOzBK;
   const int max_kb = (int)(((1L << 31) - 1) / ((long)S * 4096 * kOzBK));   // int32 exactness of one diagonal
   int nz = (nkb + max_kb - 1) / max_kb;
@@ -513,7 +541,7 @@ int oz_split(long M, int N, int K, int S) {
 
 cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,
                     int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st,
-                    const OzMoments* mom, int max_ctas) {
+                    const OzMoments* mom, int max_ctas, double alpha, int lower_only) {
   if (M <= 0 || N <= 0) return cudaSuccess;
   if (S < 1 || S > kOzMaxS || nz < 1) return cudaErrorInvalidValue;
   const int nkb = (K + kOzBK - 1) / kOzBK;
@@ -525,11 +553,11 @@ cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, c
   if (!make_slice_map(&mapA, qa, M, ldk, S, kOzBM) || !make_slice_map(&mapB, qb, N, ldk, S, kOzBN))
     return cudaErrorNotSupported;
   static const int dbg = getenv("SGP_OZ_DEBUG") ? atoi(getenv("SGP_OZ_DEBUG")) : 0;
-  OzArgs a{ea, eb, C, ldc, (int)M, N, K, S, nz, kb_per_z, zstride, accumulate,
+  const long tiles = oz_tiles(M, N, lower_only);
+  OzArgs a{ea, eb, C, ldc, (int)M, N, K, S, nz, kb_per_z, zstride, accumulate, alpha, lower_only, (int)tiles,
            mom ? mom->aux : nullptr, mom ? mom->ldaux : 0, mom ? mom->colvec : nullptr, mom ? mom->part1 : nullptr,
            mom ? mom->part2 : nullptr, mom ? mom->ldpart : 0, dbg};
   if (mom && (nz != 1 || accumulate)) return cudaErrorInvalidValue;
-  const long tiles = ((M + kOzBM - 1) / kOzBM) * ((N + kOzBN - 1) / kOzBN);
   const int grid = (int)std::min<long>(tiles * nz, max_ctas > 0 ? max_ctas : 148);   // fewer CTAs leave SMs to a concurrent stream
   note_launch();
   oz_gemm_kernel<<<grid, kOzThreads, kOzSmem, st>>>(mapA, mapB, a);

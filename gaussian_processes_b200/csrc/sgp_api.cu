@@ -486,6 +486,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const bool tail_overlap = chain_overlap && ozS > 0;
   const int oz_pairs = (ozS + 1) / 2;
   const int nzO = ozS ? oz_split(p, m, (int)std::min(slab, N), ozS) : 1;
+  const int nzK = ozS ? oz_split(m, m, (int)std::min(slab, N), ozS, 1) : 1;
   std::vector<int> off; std::vector<double> alpha;
   if (use_sep) {
     const int ldq_sep = sep_quad_ld(n);
@@ -752,7 +753,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   }
   double* Dpart = (double*)h->dpart.p;
   CU(h->gcpart.reserve((size_t)nzGC * zGC * sizeof(double)));
-  CU(h->s2part.reserve((size_t)nzS2 * zS2 * sizeof(double)));
+  CU(h->s2part.reserve((size_t)std::max(nzS2, nzK) * zS2 * sizeof(double)));
   double* GCpart = (double*)h->gcpart.p; double* S2part = (double*)h->s2part.p;
 
   const double* rdev = streaming ? (const double*)h->hr.p : in.r;
@@ -847,7 +848,13 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
         sum_to_slot(wqpart + k, wq_reduce_blocks(ns), 5, 1.0, h->d_scal, kSlotGW + k, acc_flag, st);
       mark(7);
       // G6: Sig2 += K^T diag(v) K (before X^T R: the q x q tail depends on it, not on D)
-      {
+      if (ozS) {
+        // v_i = -A^2 f_i / 2 <= 0, so K^T diag(v) K = -W^T W with W = diag(sqrt(-v)) K: ONE transposed slicing serves
+        // both operands of the int8 product; only the tiles on and below the diagonal are computed
+        const int ldk_s = oz_ldk((int)ns);
+        CU(oz_slice_cols(Ks, ldm, ns, m, ozS, rtq, ldk_s, rte, ozmx, st, v_s));
+        CU(oz_gemm(rtq, rte, m, rtq, rte, m, (int)ns, ldk_s, ozS, S2part, ldm, nzK, zS2, acc_flag, st, nullptr, 0, -1.0, 1));
+      } else {
         GemmArgs g6{};
         g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
         g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
@@ -903,7 +910,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   // ---- adjoint of K_tilde_b (q x q algebra) ---------------------------------------------------------------
   cudaStream_t st_loop = st;
   if (tail_overlap) st = h->chain_stream;     // issued after the fork above; joins before the final contraction
-  slice_reduce(S2part, nzS2, zS2, zS2, Sig2, 0, st);
+  slice_reduce(S2part, ozS ? oz_eff_split((int)std::min(slab, N), nzK) : nzS2, zS2, zS2, Sig2, 0, st);
   mirror_lower(Sig2, ldm, m, st);
   col_weights(kappa, nullptr, nullptr, X2, m, beta, st);                                 // beta_j = kappa_j / (2 X2_j)
   sum_to_slot(beta, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);

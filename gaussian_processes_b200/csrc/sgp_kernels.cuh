@@ -172,16 +172,17 @@ cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S,
                           cudaStream_t st);
 // C (M x N) = A * B^T from the slices of A (M rows) and B (N rows), K columns each
 // slices of X^T (contraction over the rows of X): q is [ceil(S/2)][cols][oz_ldk(rows)], exps[cols]; mx: cols 8-byte words
+// negsq (optional, length rows, entries <= 0): row r is multiplied by sqrt(-negsq[r]) before slicing
 cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
-                          unsigned long long* mx, cudaStream_t st);
+                          unsigned long long* mx, cudaStream_t st, const double* negsq = nullptr);
 // nz > 1: split-K, slice z of the k-blocks goes to C + z * zstride (oz_split picks nz; the effective count, which
 // oz_gemm never exceeds, is ceil(nkb / ceil(nkb / nz))); accumulate: C += instead of C =
-int oz_split(long M, int N, int K, int S);
+int oz_split(long M, int N, int K, int S, int lower_only = 0);
 inline int oz_eff_split(int K, int nz) { const int nkb = (K + 63) / 64, kbz = (nkb + nz - 1) / nz; return (nkb + kbz - 1) / kbz; }
 // optional moments epilogue: per 16-column group g, part1[g*ldpart + row] = sum_col C*aux, part2 = sum_col aux*colvec
 struct OzMoments { const double* aux; long ldaux; const double* colvec; double* part1; double* part2; long ldpart; };
 cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,
                     int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st,
-                    const OzMoments* mom = nullptr, int max_ctas = 0);
+                    const OzMoments* mom = nullptr, int max_ctas = 0, double alpha = 1.0, int lower_only = 0);
 
 }  // namespace sgp
