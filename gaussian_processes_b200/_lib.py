@@ -51,6 +51,7 @@ SIGNATURES = {
     "sgp_cholesky": (_i, [_p, _p, _l, _i, _ip, _p]),
     "sgp_spd_inverse": (_i, [_p, _p, _l, _i, _p, _l, _dp, _ip, _p]),
     "sgp_gemm_f64": (_i, [_p, _i, _i, _p, _l, _p, _l, _p, _l, _i, _i, _i, _d, _i, _i, _p]),
+    "sgp_nd_utility": (_i, [_p, _p, _p, _l, _p, _i, _p, _p, _p, _p, _p, _p]),
     "sgp_gemm_i8emu": (_i, [_p, _i, _p, _l, _l, _p, _i, _l, _l, _i, _p, _l, _p]),
     "sgp_elbo_grad": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i, _dp, _dp, _dp, _p, _l, _i, _p, _p, _l, _d, _d,
                            _dp, _p, _p, _p, _dp, _p]),

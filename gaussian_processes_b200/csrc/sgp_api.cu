@@ -1162,6 +1162,16 @@ int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, 
   return SGP_OK;
 }
 
+int sgp_nd_utility(sgp_handle* h, const double* sigma2, const double* mu, long nstar, const double* r, int nr,
+                   double* U, double* lam, unsigned char* mask, double* p, double* logp, void* stream) {
+  if (!h || !sigma2 || !mu || !r) return fail(h, SGP_E_ARG, "sgp_nd_utility: null argument");
+  if (nstar < 0 || nr < 0) return fail(h, SGP_E_ARG, "sgp_nd_utility: bad sizes");
+  int rc = ensure_ready(h); if (rc) return rc;
+  nd_utility(sigma2, mu, r, nr, nstar, U, lam, mask, p, logp, (cudaStream_t)stream);
+  CU(cudaGetLastError());
+  return SGP_OK;
+}
+
 int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K_b, long ldk, const double* Kvec,
                        long N, int q, const double* m_b, const double* V_b, long ldv, double* lam_m, double* lam_var,
                        void* stream) {

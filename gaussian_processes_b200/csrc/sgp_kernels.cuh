@@ -185,4 +185,8 @@ cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, c
                     int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st,
                     const OzMoments* mom = nullptr, int max_ctas = 0, double alpha = 1.0, int lower_only = 0);
 
+// ---- active-learning utility (utils.py:416-525): U[nstar] and optional (r, nstar) arrays lam / mask / p / log p ----
+void nd_utility(const double* sigma2, const double* mu, const double* r, int nr, long nstar, double* U, double* lam,
+                unsigned char* mask, double* p, double* logp, cudaStream_t st);
+
 }  // namespace sgp

@@ -207,6 +207,24 @@ def gemm_f64(A: torch.Tensor, B: torch.Tensor, a_layout: int = 0, b_layout: int 
     return out[:, :N]
 
 
+def nd_utility(sigma2: torch.Tensor, mu: torch.Tensor, r: torch.Tensor, want_arrays: bool = False):
+    """utils.py:416-525 on the device: U[nstar]; with want_arrays also (lam, mask, p, log p), each (nr, nstar)."""
+    _need_cuda(sigma2, mu, r)
+    sigma2, mu, r = sigma2.contiguous(), mu.contiguous(), r.to(torch.float64).contiguous()
+    nstar, nr = sigma2.numel(), r.numel()
+    U = torch.empty(nstar, dtype=torch.float64, device=sigma2.device)
+    lam = mask = p = logp = None
+    if want_arrays:
+        lam, p, logp = (torch.empty((nr, nstar), dtype=torch.float64, device=sigma2.device) for _ in range(3))
+        mask = torch.empty((nr, nstar), dtype=torch.uint8, device=sigma2.device)
+    h = _h(sigma2)
+    h.check(lib.sgp_nd_utility(h.ptr, _ptr(sigma2), _ptr(mu), int(nstar), _ptr(r), int(nr), _ptr(U), _ptr(lam),
+                               _ptr(mask), _ptr(p), _ptr(logp), _stream(sigma2.device)))
+    if want_arrays:
+        return U, lam, mask.bool(), p, logp
+    return U
+
+
 def gemm_i8emu(A: torch.Tensor, B: torch.Tensor, slices: int = 8, transposed: bool = False) -> torch.Tensor:
     """A @ B.T (A: [M,K], B: [N,K]) -- or A.T @ B (A: [K,M], B: [K,N]) with ``transposed`` -- on
     tcgen05.mma.kind::i8 from int8 digit slices, recombined in fp64."""

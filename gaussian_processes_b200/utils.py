@@ -411,6 +411,77 @@ def Estep(r, KKtilde_inv, m, f_params, f_mean, K_tilde=None, K_tilde_inv=None, V
     return m_new, V_new
 
 
+# ---- active-learning utility (U:416-637): Lambert W on the device instead of the scipy round trip (U:464-466) ----
+def nd_mean_noise_entropy(p_response, log_r2d_fact, sigma2, mu):
+    """<H(r|f,x)>_p(f|D) for nstar candidates (U:416-436); p_response / log_r2d_fact are (r, nstar)."""
+    p_times_logr_sum = torch.sum(p_response * log_r2d_fact, dim=0)
+    return -torch.exp(mu + 0.5 * sigma2) * (mu + sigma2 - 1) + p_times_logr_sum
+
+
+def nd_lambda_r_mean(r, sigma2, mu):
+    """argmax of the Laplace-approximated log p(r|x,D) (U:438-471): (lambW (r, nstar), sum_mask (r, nstar))."""
+    _, lam, keep, _, _ = native.nd_utility(sigma2, mu, r, want_arrays=True)
+    return lam, keep
+
+
+def nd_p_r_given_xD(r, sigma2, mu):
+    """p(r|x,D) for every count and candidate (U:473-494): (p, log p, masked r (r, nstar), masked log r! (r, nstar))."""
+    _, _, keep, p, log_p = native.nd_utility(sigma2, mu, r, want_arrays=True)
+    zero = torch.zeros((), dtype=p.dtype, device=p.device)
+    r2d = torch.where(keep, r.to(p.dtype).unsqueeze(1).repeat(1, sigma2.shape[0]), zero)
+    log_r_fact = torch.where(keep, torch.lgamma(r.to(p.dtype) + 1).unsqueeze(1).repeat(1, sigma2.shape[0]), zero)
+    return p, log_p, r2d, log_r_fact
+
+
+@torch.no_grad()
+def nd_utility(sigma2, mu, r_masked):
+    """Utility U = H(r|x,D) - <H(r|f,x)> of nstar candidates (U:496-519) in one kernel launch."""
+    if sigma2.ndim == 0:
+        sigma2 = sigma2[None]
+        mu = mu[None]
+    return native.nd_utility(sigma2, mu, r_masked)
+
+
+def mean_noise_entropy(p_response, r, sigma2, mu):
+    """Single-candidate <H(r|f,x)> (U:521-538)."""
+    p_times_logr_sum = p_response @ torch.lgamma(r + 1)
+    return -torch.exp(mu + 0.5 * sigma2) * (mu + sigma2 - 1) + p_times_logr_sum
+
+
+def lambda_r_mean(r, sigma2, mu):
+    """Single-candidate variant (U:540-571): overflowing counts are REMOVED, not zeroed; returns (lamb, sum_mask)."""
+    _, lam, keep, _, _ = native.nd_utility(sigma2.reshape(1), mu.reshape(1), r, want_arrays=True)
+    keep = keep[:, 0]
+    return lam[:, 0][keep], keep
+
+
+def p_r_given_xD(r, sigma2, mu):
+    """Single-candidate p(r|x,D) over the kept counts (U:573-594): (p, log p, r[sum_mask])."""
+    _, _, keep, p, log_p = native.nd_utility(sigma2.reshape(1), mu.reshape(1), r, want_arrays=True)
+    keep = keep[:, 0]
+    return p[:, 0][keep], log_p[:, 0][keep], r[keep]
+
+
+@torch.no_grad()
+def utility(sigma2, mu, r_masked):
+    """Single-candidate utility (U:596-618)."""
+    p_response, log_p_response, r_masked2 = p_r_given_xD(r=r_masked, sigma2=sigma2, mu=mu)
+    H_r_xD = -torch.sum(p_response * log_p_response)
+    E_H_r_f = mean_noise_entropy(p_response, r_masked2, sigma2, mu)
+    return H_r_xD - E_H_r_f
+
+
+def get_utility(xstar, xtilde, C, mask, theta, m, V, K_tilde, K_tilde_inv, kernfun):
+    """U:620-631, kept call for call -- including the reference's own argument lists (its calls to
+    lambda_moments_star / utility omit arguments the current signatures require, so it raises TypeError there too)."""
+    if K_tilde_inv is None:
+        K_tilde_inv = torch.linalg.solve(K_tilde, torch.eye(K_tilde.shape[0], device=K_tilde.device))
+    xstar = xstar.unsqueeze(0)
+    mu_star, sigma2_star = lambda_moments_star(xstar[:, mask], xtilde[:, mask], C, theta, K_tilde_inv, m, V,
+                                               kernfun=kernfun)
+    return utility(sigma2=sigma2_star, mu=mu_star)
+
+
 # ---- inference (U:1476-1541, U:326-412) -------------------------------------------------------------------
 def lambda_moments_star(xstar, xtilde, C, theta, K_tilde, K_tilde_inv, m, V, B, kernfun):
     if kernfun == 'acosker':

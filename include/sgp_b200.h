@@ -119,6 +119,16 @@ SGP_API int sgp_loglik_sums(sgp_handle* h, const double* r, const double* f, con
 SGP_API int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, const double* f, long N, int q,
                     double logA, double* g, double* G, long ldg, void* stream);
 
+/* ---- nd_utility / nd_p_r_given_xD / nd_lambda_r_mean / nd_mean_noise_entropy  utils.py:416-525 --
+ * Active-learning utility of nstar candidate images from the mean `mu` and variance `sigma2` (device, length nstar)
+ * of log f at each candidate, summed over the counts r[0..nr) (device).  The Lambert-W step that the reference sends
+ * through scipy on the CPU (utils.py:464-466) runs on the device.  Outputs are device pointers, each may be null:
+ * U[nstar] (utils.py:516), and the (nr x nstar) row-major arrays lam (utils.py:466), mask (z != inf, utils.py:451),
+ * p and log p (utils.py:492-494).  Masked entries follow the reference: z, r*sigma2, r and log r! are zeroed and the
+ * entry stays in the sums. */
+SGP_API int sgp_nd_utility(sgp_handle* h, const double* sigma2, const double* mu, long nstar, const double* r, int nr,
+                   double* U, double* lam, unsigned char* mask, double* p, double* logp, void* stream);
+
 /* ---- small dense algebra on the q x q state (north_star item 2) -----------------------------------------------
  * In-place lower Cholesky (strict upper triangle clobbered) ; X = L^{-1} ; flags_host receives SGP_FLAG_KT_* bits. */
 SGP_API int sgp_cholesky(sgp_handle* h, double* A, long ld, int n, int* flags_host, void* stream);

@@ -194,10 +194,38 @@ def gen_fit_case(ref, name, N, n, m, cfg, theta_dict, maxiter, nE, nM, nF):
     print(f"{name}: logmarginal track {fx['logmarginal']}")
 
 
+def gen_utility(ref):
+    """nd_utility family (U:416-525) on seeded (mu, sigma2) pairs, including candidates whose z overflows for the
+    larger counts (the reference's masking quirk) and the 0-dim call of the single-candidate variants."""
+    g = torch.Generator().manual_seed(77)
+    nstar = 96
+    mu = -1.5 + 1.2 * torch.randn(nstar, generator=g, dtype=torch.float64)
+    sigma2 = torch.exp(-1.0 + 1.3 * torch.randn(nstar, generator=g, dtype=torch.float64))
+    sigma2[:6] = torch.tensor([8.0, 12.0, 20.0, 1e-6, 1e-3, 5.0], dtype=torch.float64)   # overflow / tiny variances
+    mu[:6] = torch.tensor([2.0, -3.0, 0.5, -2.0, 1.0, 4.0], dtype=torch.float64)
+    r = torch.arange(0, 100, dtype=torch.float64)
+    lam, keep = ref.nd_lambda_r_mean(r, sigma2, mu)
+    p, log_p, r2d, lrf = ref.nd_p_r_given_xD(r, sigma2, mu)
+    U = ref.nd_utility(sigma2, mu, r)
+    # single-candidate variants (U:540-611) for a candidate without overflow
+    j = 10
+    p1, log_p1, r1 = ref.p_r_given_xD(r, sigma2[j], mu[j])
+    U1 = ref.utility(sigma2[j], mu[j], r)
+    assert bool((~keep).any()), "fixture must contain masked entries"
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "utility_n96.npz"),
+                        mu=mu.numpy(), sigma2=sigma2.numpy(), r=r.numpy(), lam=lam.numpy(), keep=keep.numpy(),
+                        p=p.numpy(), log_p=log_p.numpy(), r2d=r2d.numpy(), lrf=lrf.numpy(), U=U.numpy(),
+                        single_index=j, p1=p1.numpy(), log_p1=log_p1.numpy(), r1=r1.numpy(), U1=float(U1))
+    print("utility_n96: masked entries", int((~keep).sum()), "U range", float(U.min()), float(U.max()))
+
+
 def main():
     ref = import_reference()
     assert torch.pi == 3.1415927410125732  # U:25
     gen_kat(ref)
+    gen_utility(ref)
+    if len(sys.argv) > 1 and sys.argv[1] == "utility":
+        return
     # small closure cases, every intermediate stored
     gen_closure_case(ref, "closure_dense_n8", N=150, n=8, m=24, cfg=11, theta_dict=synth.THETA_DENSE, store_big=True)
     gen_closure_case(ref, "closure_local_n12", N=260, n=12, m=40, cfg=12, theta_dict=synth.theta_localised(12),

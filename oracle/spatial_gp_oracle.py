@@ -305,3 +305,34 @@ def fparam_closure(logA: float, lambda0: float, r, lam_m, lam_var):
     ll = expected_loglik(r, f, lam_m, logA, lambda0)
     dlogA, _ = expected_loglik_fparam_grad(r, f, lam_m, lam_var, logA)
     return -ll, -dlogA, lambda0_closed_form(logA, r, lam_m, lam_var)
+
+
+# --------------------------------------------------------------------------- active-learning utility
+def utility_terms(sigma2, mu, r):
+    """nd_lambda_r_mean + nd_p_r_given_xD (U:438-494): returns (lam, keep, p, log_p, r2d, log_r_fact), each (nr, nstar).
+    Entries whose z = exp(r sigma2 + mu) sigma2 overflows are 'masked' the reference's way: z, r sigma2, r and log r!
+    are zeroed and the entry stays in every sum.  Lambert W: scipy, principal branch, tol 1e-8 (U:465)."""
+    import scipy.special
+    sigma2, mu, r = sigma2.to(F64), mu.to(F64), r.to(F64)
+    rs = torch.outer(r, sigma2)
+    z = torch.exp(rs + mu) * sigma2.unsqueeze(0)
+    keep = z != math.inf
+    z = torch.where(keep, z, torch.zeros((), dtype=F64))
+    rs = torch.where(keep, rs, torch.zeros((), dtype=F64))
+    w = torch.from_numpy(scipy.special.lambertw(z.numpy(), k=0, tol=1.0e-8).real)
+    lam = rs + mu - w
+    el = torch.exp(lam)
+    lrf = torch.lgamma(r + 1).unsqueeze(1).repeat(1, sigma2.shape[0])
+    r2d = r.unsqueeze(1).repeat(1, sigma2.shape[0])
+    lrf = torch.where(keep, lrf, torch.zeros((), dtype=F64))
+    r2d = torch.where(keep, r2d, torch.zeros((), dtype=F64))
+    log_p = lam * r2d - el - (lam - mu) ** 2 / (2 * sigma2.unsqueeze(0)) - 0.5 * torch.log(el * sigma2 + 1) - lrf
+    return lam, keep, torch.exp(log_p), log_p, r2d, lrf
+
+
+def utility(sigma2, mu, r):
+    """nd_utility (U:497-519) with nd_mean_noise_entropy (U:416-436): U[nstar] = H(r|x,D) - <H(r|f,x)>."""
+    _, _, p, log_p, _, lrf = utility_terms(sigma2, mu, r)
+    h_r = -torch.sum(p * log_p, dim=0)
+    h_mean = -torch.exp(mu + 0.5 * sigma2) * (mu + sigma2 - 1) + torch.sum(p * lrf, dim=0)
+    return h_r - h_mean

@@ -121,3 +121,12 @@ def elbo_grad(X, r, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0, lims=None, 
     if want_moments:
         res.update(lam_m=out["lam_m"], lam_var=out["lam_var"], f=out["f"])
     return res
+
+
+def nd_utility(sigma2, mu, r, want_arrays=False):
+    r = r.to(torch.float64)
+    U = orc.utility(sigma2, mu, r)
+    if not want_arrays:
+        return U
+    lam, keep, p, log_p, _, _ = orc.utility_terms(sigma2, mu, r)
+    return U, lam, keep, p, log_p

@@ -174,3 +174,28 @@ def test_moments_estep_fparams_against_reference(nat, name):
     g, G = nat.estep_terms(a.to(d), prob.r.to(d), torch.from_numpy(fx["f"]).to(d), st["logA"])
     assert rel_err(g.cpu().numpy(), fx["estep_g"]) < 1e-9
     assert rel_err(G.cpu().numpy(), fx["estep_G"]) < 1e-9
+
+
+def test_nd_utility_against_reference(nat):
+    """sgp_nd_utility (Lambert W on the device) against the reference's scipy-based nd_utility family, U:416-519."""
+    fx = load("utility_n96")
+    s2, mu, r = (torch.from_numpy(fx[k]).to(dev()) for k in ("sigma2", "mu", "r"))
+    U, lam, keep, p, log_p = nat.nd_utility(s2, mu, r, want_arrays=True)
+    assert np.array_equal(keep.cpu().numpy(), fx["keep"])
+    assert np.allclose(lam.cpu().numpy(), fx["lam"], rtol=1e-9, atol=1e-12)
+    assert np.allclose(log_p.cpu().numpy(), fx["log_p"], rtol=1e-9, atol=1e-11)
+    assert np.allclose(p.cpu().numpy(), fx["p"], rtol=1e-9, atol=1e-300)
+    assert np.allclose(U.cpu().numpy(), fx["U"], rtol=1e-9, atol=1e-12)
+    assert np.array_equal(nat.nd_utility(s2, mu, r).cpu().numpy(), U.cpu().numpy())
+
+
+def test_nd_utility_many_candidates(nat):
+    """Every candidate is independent: a large batch equals the small batches it is made of (bitwise)."""
+    g = torch.Generator().manual_seed(5)
+    n = 200_003
+    mu = (-1.0 + torch.randn(n, generator=g, dtype=torch.float64)).to(dev())
+    s2 = torch.exp(-1.0 + torch.randn(n, generator=g, dtype=torch.float64)).to(dev())
+    r = torch.arange(0, 100, dtype=torch.float64, device=dev())
+    U = nat.nd_utility(s2, mu, r)
+    assert torch.isfinite(U).all()
+    assert torch.equal(U[1000:1064], nat.nd_utility(s2[1000:1064].clone(), mu[1000:1064].clone(), r))

@@ -133,3 +133,15 @@ def test_cpu_tensors_raise(U):
     with pytest.raises((RuntimeError, TypeError)):
         U.elbo_and_grad(th, synth.THETA_LIMS_LO, synth.THETA_LIMS_HI, prob.n_px_side, prob.X, prob.xtilde, prob.r,
                         st["B"], st["m_b"], st["V_b"], fp)
+
+
+def test_utility_family_on_gpu(U):
+    fx = load("utility_n96")
+    s2, mu, r = (torch.from_numpy(fx[k]).to(D) for k in ("sigma2", "mu", "r"))
+    Uv = U.nd_utility(s2, mu, r)
+    assert Uv.is_cuda and np.allclose(Uv.cpu().numpy(), fx["U"], rtol=1e-9, atol=1e-12)
+    p, log_p, r2d, lrf = U.nd_p_r_given_xD(r, s2, mu)
+    assert np.allclose(log_p.cpu().numpy(), fx["log_p"], rtol=1e-9, atol=1e-11)
+    assert np.array_equal(r2d.cpu().numpy(), fx["r2d"])
+    j = int(fx["single_index"])
+    assert abs(float(U.utility(s2[j], mu[j], r)) - float(fx["U1"])) <= 1e-9 * abs(float(fx["U1"]))

@@ -131,3 +131,16 @@ def test_chunked_oracle_matches_full():
     assert abs(full["elbo"] - ch["elbo"]) < 1e-11 * abs(full["elbo"])
     for k in orc.KEYS:
         assert abs(full["grad"][k] - ch["grad"][k]) <= 1e-10 * max(abs(full["grad"][k]), 1e-3)
+
+
+def test_utility_family_against_reference():
+    """nd_lambda_r_mean / nd_p_r_given_xD / nd_utility (U:416-519), including the overflow-masked entries."""
+    fx = load("utility_n96")
+    s2, mu, r = (torch.from_numpy(fx[k]) for k in ("sigma2", "mu", "r"))
+    lam, keep, p, log_p, r2d, lrf = orc.utility_terms(s2, mu, r)
+    assert np.array_equal(keep.numpy(), fx["keep"]) and int((~keep).sum()) > 0
+    assert np.allclose(lam.numpy(), fx["lam"], rtol=1e-13, atol=1e-13)
+    assert np.allclose(log_p.numpy(), fx["log_p"], rtol=1e-12, atol=1e-12)
+    assert np.allclose(p.numpy(), fx["p"], rtol=1e-11, atol=1e-300)
+    assert np.array_equal(r2d.numpy(), fx["r2d"]) and np.allclose(lrf.numpy(), fx["lrf"], rtol=1e-15)
+    assert np.allclose(orc.utility(s2, mu, r).numpy(), fx["U"], rtol=1e-10, atol=1e-12)

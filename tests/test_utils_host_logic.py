@@ -186,3 +186,27 @@ def test_log_det_fallback_semantics(U):
     A = torch.tensor([[1.0, 2.0], [0.0, 1.0]])
     with pytest.warns(UserWarning):
         assert U.log_det(A) == 0                           # not symmetric -> 0 with a warning (U:1302-1304)
+
+
+def test_utility_family_surface(U):
+    """The nd_* and single-candidate utility functions (U:416-618): shapes, masking semantics, values."""
+    from helpers import load
+    fx = load("utility_n96")
+    s2, mu, r = (torch.from_numpy(fx[k]) for k in ("sigma2", "mu", "r"))
+    lam, keep = U.nd_lambda_r_mean(r, s2, mu)
+    assert lam.shape == (100, 96) and keep.dtype == torch.bool and np.array_equal(keep.numpy(), fx["keep"])
+    p, log_p, r2d, lrf = U.nd_p_r_given_xD(r, s2, mu)
+    assert np.allclose(log_p.numpy(), fx["log_p"], rtol=1e-12, atol=1e-12)
+    assert np.array_equal(r2d.numpy(), fx["r2d"]) and np.allclose(lrf.numpy(), fx["lrf"], rtol=1e-15)
+    Uv = U.nd_utility(s2, mu, r)
+    assert np.allclose(Uv.numpy(), fx["U"], rtol=1e-10, atol=1e-12)
+    assert np.allclose(U.nd_mean_noise_entropy(p, lrf, s2, mu).numpy(),
+                       (-torch.exp(mu + 0.5 * s2) * (mu + s2 - 1) + (p * lrf).sum(0)).numpy())
+    j = int(fx["single_index"])
+    assert U.nd_utility(s2[j], mu[j], r).shape == (1,)            # 0-dim inputs are promoted (U:508-510)
+    p1, log_p1, r1 = U.p_r_given_xD(r, s2[j], mu[j])
+    assert np.allclose(p1.numpy(), fx["p1"], rtol=1e-11) and np.array_equal(r1.numpy(), fx["r1"])
+    assert abs(float(U.utility(s2[j], mu[j], r)) - float(fx["U1"])) <= 1e-10 * abs(float(fx["U1"]))
+    # the single-candidate variants DROP overflowing counts instead of zeroing them (U:551-553)
+    lam0, keep0 = U.lambda_r_mean(r, s2[0], mu[0])
+    assert lam0.numel() == int(keep0.sum()) < 100
