@@ -236,6 +236,25 @@ def secondary_metrics(native, dev, X, r, xt, Cm, mask, theta, B, ev_keep, m_b, V
         native.fparam_eval(lm2, lv2, r, logA, 0.0, want_f=False)
     t = timed(estep_iter, reps=3, warm=1)
     flops = 2.0 * N * q * q * 2          # G = a^T diag(f) a (lower tiles only would be N q^2) + the a V product
+    # active-learning scoring: utility of 2^20 candidate images x 100 counts in one launch,
+    # beside the reference's formulation (torch + scipy Lambert W on the host cores) on 20 000 candidates
+    try:
+        ns = 1 << 20
+        mu_c = -1.0 + torch.randn(ns, generator=g, dtype=torch.float64, device=dev)
+        s2_c = torch.exp(-1.0 + torch.randn(ns, generator=g, dtype=torch.float64, device=dev))
+        rr_c = torch.arange(0, 100, dtype=torch.float64, device=dev)
+        tu = timed(lambda: native.nd_utility(s2_c, mu_c, rr_c))
+        import oracle.spatial_gp_oracle as orc_u
+        nc = 20000
+        t0 = time.perf_counter()
+        orc_u.utility(s2_c[:nc].cpu(), mu_c[:nc].cpu(), rr_c.cpu())
+        tc = time.perf_counter() - t0
+        out["nd_utility"] = {"kernel": "nd_utility_kernel (Lambert W on the device)", "candidates": ns, "counts": 100,
+                             "ms": tu * 1e3, "candidates_per_sec": ns / tu,
+                             "cpu_port_candidates_per_sec": nc / tc, "cpu_sample": "%d candidates, scipy lambertw" % nc}
+        del mu_c, s2_c
+    except Exception as e:  # pragma: no cover
+        out["nd_utility"] = {"error": repr(e)}
     out["estep_iteration"] = {"N": N, "q": q, "ms": t * 1e3, "iters_per_sec": 1.0 / t,
                               "contract_tflops": flops / t / 1e12,
                               "what": "rate, g/G (one pass over a), (K^-1+G)^-1 by blocked Cholesky, new moments, lambda0"}
