@@ -390,7 +390,7 @@ oz_slice_rows_kernel(const double* __restrict__ X, long ldx, long rows, int cols
 
 // Column-wise |max| of a rows x cols matrix as monotone bit patterns (non-negative doubles order like their bits).
 __global__ void __launch_bounds__(256)
-oz_col_absmax_kernel(const double* __restrict__ X, long ldx, long rows, int cols, const double* __restrict__ negsq,
+oz_col_absmax_kernel(const double* __restrict__ X, long ldx, long rows, int cols, const double* __restrict__ rowsq,
                      unsigned long long* __restrict__ mx) {
   const int c = blockIdx.x * 32 + (threadIdx.x & 31);
   const int rl = threadIdx.x >> 5;
@@ -398,7 +398,7 @@ oz_col_absmax_kernel(const double* __restrict__ X, long ldx, long rows, int cols
   double m = 0.0;
   if (c < cols)
     for (long r = (long)blockIdx.y * 8 + rl; r < rows; r += (long)gridDim.y * 8)
-      m = fmax(m, fabs(X[r * ldx + c]) * (negsq ? sqrt(-negsq[r]) : 1.0));
+      m = fmax(m, fabs(X[r * ldx + c]) * (rowsq ? sqrt(fabs(rowsq[r])) : 1.0));
   red[rl][threadIdx.x & 31] = m;
   __syncthreads();
   if (rl == 0 && c < cols) {
@@ -420,13 +420,13 @@ __global__ void oz_exps_from_max_kernel(const unsigned long long* __restrict__ m
 // into one 16-byte store per slice.
 __global__ void __launch_bounds__(256)
 oz_slice_cols_kernel(const double* __restrict__ X, long ldx, long rows, int cols, int S, int8_t* __restrict__ q,
-                     int ldk, long pair_stride, const int* __restrict__ exps, const double* __restrict__ negsq) {
+                     int ldk, long pair_stride, const int* __restrict__ exps, const double* __restrict__ rowsq) {
   __shared__ double tile[64][65];
   const long r0 = (long)blockIdx.x * 64;
   const int c0 = blockIdx.y * 64;
   for (int e = threadIdx.x; e < 64 * 64; e += 256) {
     const int i = e >> 6, c = e & 63;
-    tile[i][c] = (r0 + i < rows && c0 + c < cols) ? X[(r0 + i) * ldx + c0 + c] * (negsq ? sqrt(-negsq[r0 + i]) : 1.0) : 0.0;
+    tile[i][c] = (r0 + i < rows && c0 + c < cols) ? X[(r0 + i) * ldx + c0 + c] * (rowsq ? sqrt(fabs(rowsq[r0 + i])) : 1.0) : 0.0;
   }
   __syncthreads();
   const int c = threadIdx.x & 63, quarter = threadIdx.x >> 6;
@@ -500,17 +500,17 @@ cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S,
 // Slices of X^T for a contraction over the ROWS of X (rows x cols): q is [pairs][cols][oz_ldk(rows)], exps[cols].
 // mx: scratch of `cols` 8-byte words.
 cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
-                          unsigned long long* mx, cudaStream_t st, const double* negsq) {
+                          unsigned long long* mx, cudaStream_t st, const double* rowsq) {
   if (rows <= 0 || cols <= 0) return cudaSuccess;
   if (S < 1 || S > kOzMaxS || rows > (1L << 30) || ldk != oz_ldk((int)rows)) return cudaErrorInvalidValue;
   cudaError_t e = cudaMemsetAsync(mx, 0, sizeof(unsigned long long) * cols, st);
   if (e != cudaSuccess) return e;
   const int gy = (int)std::min<long>((rows + 63) / 64, 148L * 4 / ((cols + 31) / 32) + 1);
   note_launch(3);
-  oz_col_absmax_kernel<<<dim3((cols + 31) / 32, gy), 256, 0, st>>>(X, ldx, rows, cols, negsq, mx);
+  oz_col_absmax_kernel<<<dim3((cols + 31) / 32, gy), 256, 0, st>>>(X, ldx, rows, cols, rowsq, mx);
   oz_exps_from_max_kernel<<<(cols + 255) / 256, 256, 0, st>>>(mx, cols, exps);
   oz_slice_cols_kernel<<<dim3((unsigned)((rows + 63) / 64), (cols + 63) / 64), 256, 0, st>>>(
-      X, ldx, rows, cols, S, q, ldk, (long)cols * ldk, exps, negsq);
+      X, ldx, rows, cols, S, q, ldk, (long)cols * ldk, exps, rowsq);
   return cudaGetLastError();
 }
 

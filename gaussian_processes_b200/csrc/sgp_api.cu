@@ -59,6 +59,7 @@ struct sgp_handle {
   bool cache_valid = false;
   int* d_flags = nullptr;
   double* d_scal = nullptr;
+  unsigned* d_ticket = nullptr;        // last-block-done counter of the streaming reductions (zero between launches)
   double* d_out = nullptr;
   double* h_out = nullptr;  // pinned
   std::map<std::string, DebugEntry> dbg;
@@ -155,6 +156,8 @@ int ensure_ready(sgp_handle* h) {
     CU(oz_init());
     CU(cudaMalloc(&h->d_flags, sizeof(int) * 4));
     CU(cudaMalloc(&h->d_scal, sizeof(double) * kNumSlots));
+    CU(cudaMalloc(&h->d_ticket, 64));
+    CU(cudaMemset(h->d_ticket, 0, 64));
     CU(cudaMalloc(&h->d_out, sizeof(double) * 16));
     CU(cudaMallocHost(&h->h_out, sizeof(double) * 16));
     h->gemm_ready = true;
@@ -210,6 +213,7 @@ int sgp_destroy(sgp_handle* h) {
     h->hx[0].release(); h->hx[1].release(); h->hr.release(); h->small.release();
     if (h->d_flags) cudaFree(h->d_flags);
     if (h->d_scal) cudaFree(h->d_scal);
+    if (h->d_ticket) cudaFree(h->d_ticket);
     if (h->d_out) cudaFree(h->d_out);
     if (h->h_out) cudaFreeHost(h->h_out);
     for (int i = 0; i < 2; ++i) {
@@ -304,10 +308,49 @@ int sgp_localker(sgp_handle* h, const double* theta, int n_px, double* C, long l
   return SGP_OK;
 }
 
+// Slice count of the int8 tensor-core path for a product with `rows` long-side rows and inner sizes n, k:
+// 0 = use the DMMA GEMM.  Same policy as the fused closure (option "i8_slices": -1 auto, 0 off, 2..8 forced).
+static int oz_pick(const sgp_handle* h, long rows, long n, long k) {
+  if (h->i8_slices == 0 || n < 1 || k < 1) return 0;
+  if (h->i8_slices > 0) return h->i8_slices;
+  return (rows >= 4096 && n >= 64 && k >= 64) ? 8 : 0;
+}
+
+// C = alpha * op(A) op(B) (+ C) on the int8 slices; al/bl as in sgp_gemm_f64.  One pass over K (no split), so
+// K * S * 4096 must stay below 2^31.
+static int oz_mm(sgp_handle* h, cudaStream_t st, int al, int bl, const double* A, long lda, long M, const double* B,
+                 long ldb, int N, int K, int S, double* C, long ldc, double alpha, int accumulate) {
+  const int ldk = oz_ldk(K);
+  size_t need = 0;
+  auto acc = [&](size_t bytes) { need = ((need + 1023) & ~size_t(1023)) + bytes; };
+  acc(oz_slice_bytes(M, K, S)); acc(oz_slice_bytes(N, K, S));
+  acc((size_t)M * sizeof(int)); acc((size_t)N * sizeof(int)); acc((size_t)std::max<long>(M, N) * 8);
+  need += 4096;
+  CU(h->arena.reserve(need));
+  Arena ar(h->arena.p, h->arena.bytes);
+  int8_t* qa = ar.take<int8_t>(oz_slice_bytes(M, K, S));
+  int8_t* qb = ar.take<int8_t>(oz_slice_bytes(N, K, S));
+  int* ea = ar.take<int>(M);
+  int* eb = ar.take<int>(N);
+  unsigned long long* mx = ar.take<unsigned long long>(std::max<long>(M, N));
+  if (al == 0) CU(oz_slice_rows(A, lda, M, K, S, qa, ldk, ea, st));
+  else CU(oz_slice_cols(A, lda, K, (int)M, S, qa, ldk, ea, mx, st));
+  if (bl == 0) CU(oz_slice_rows(B, ldb, N, K, S, qb, ldk, eb, st));
+  else CU(oz_slice_cols(B, ldb, K, N, S, qb, ldk, eb, mx, st));
+  CU(oz_gemm(qa, ea, M, qb, eb, N, K, ldk, S, C, ldc, 1, 0, accumulate, st, nullptr, 0, alpha));
+  CU(cudaGetLastError());
+  return SGP_OK;
+}
+
 int sgp_gemm_f64(sgp_handle* h, int al, int bl, const double* A, long lda, const double* B, long ldb, double* C,
                  long ldc, int M, int N, int K, double alpha, int accumulate, int small_tile, void* stream) {
   if (!h || !A || !B || !C) return fail(h, SGP_E_ARG, "sgp_gemm_f64: null argument");
   int rc = ensure_ready(h); if (rc) return rc;
+  // image-sized products (K_b = K B, a = K_b K_tilde_b^-1: utils.py:1693-1694) go to the int8 tensor-core path
+  if (al == 0 && !small_tile && h->i8_slices != 0 && M >= 4096 && N >= 64 && K >= 64 &&
+      rup(K, 64) * 8L * 4096 < (1L << 31))
+    return oz_mm(h, (cudaStream_t)stream, al, bl, A, lda, M, B, ldb, N, K, h->i8_slices > 0 ? h->i8_slices : 8, C, ldc,
+                 alpha, accumulate);
   GemmArgs g{};
   g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K;
   g.alpha = alpha; g.accumulate = accumulate; g.k_chunk = (int)rup(K, 16);
@@ -1181,11 +1224,13 @@ int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K
   cudaStream_t st = (cudaStream_t)stream;
   const long ldq = rup(q, 16);
   const long slab = std::min<long>(h->slab_rows, rup(N, 128));
-  const int ntq = (q + 127) / 128;
+  const int ozS = oz_pick(h, N, q, q);        // T = a V^T on the int8 tensor-core path (csrc/ozaki_i8.cu)
+  const int ntq = ozS ? (q + 15) / 16 : (q + 127) / 128;   // partial row sums per 16- / 128-column group
   const long ldpart = rup(slab, 16);
   size_t need = 0;
   auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
   acc((size_t)q * ldq); acc((size_t)slab * ldq); acc((size_t)slab * ldq); acc((size_t)ntq * ldpart * 2);
+  if (ozS) { acc(oz_slice_bytes(slab, q, ozS) / 8 + 16); acc(oz_slice_bytes(q, q, ozS) / 8 + 16); acc(slab / 2 + 8); acc(q); }
   need += 4096;
   CU(h->arena.reserve(need));
   Arena ar(h->arena.p, h->arena.bytes);
@@ -1193,15 +1238,29 @@ int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K
   double* aw = ar.take<double>((size_t)slab * ldq);
   double* T = ar.take<double>((size_t)slab * ldq);
   double* p1 = ar.take<double>((size_t)ntq * ldpart); double* p2 = ar.take<double>((size_t)ntq * ldpart);
-  copy_mat(V_b, ldv, q, q, Vw, ldq, st);
+  int8_t* aq = nullptr; int8_t* vq = nullptr; int* ae = nullptr; int* ve = nullptr;
+  if (ozS) {
+    aq = (int8_t*)ar.take<double>(oz_slice_bytes(slab, q, ozS) / 8 + 16);
+    vq = (int8_t*)ar.take<double>(oz_slice_bytes(q, q, ozS) / 8 + 16);
+    ae = (int*)ar.take<double>(slab / 2 + 8); ve = (int*)ar.take<double>(q);
+    CU(oz_slice_rows(V_b, ldv, q, q, ozS, vq, oz_ldk(q), ve, st));
+  } else {
+    copy_mat(V_b, ldv, q, q, Vw, ldq, st);
+  }
   for (long i0 = 0; i0 < N; i0 += slab) {
     const long ns = std::min(slab, N - i0);
     const double* as = a + i0 * lda; long ldas = lda;
     if (!aligned2(as, lda)) { copy_mat(as, lda, (int)ns, q, aw, ldq, st); as = aw; ldas = ldq; }
-    GemmArgs g{};  // T = a V^T ; part1 = rowdot(T, a) ; part2 = a m_b
-    g.A = as; g.lda = ldas; g.B = Vw; g.ldb = ldq; g.C = T; g.ldc = ldq; g.M = (int)ns; g.N = q; g.K = q;
-    g.aux = as; g.ldaux = ldas; g.colvec = m_b; g.part1 = p1; g.part2 = p2; g.ldpart = ldpart;
-    CU(gemm(st, 0, 0, kMoments, false, 1, g));
+    if (ozS) {     // T = a V^T ; part1 = rowdot(T, a) ; part2 = a m_b
+      CU(oz_slice_rows(as, ldas, ns, q, ozS, aq, oz_ldk(q), ae, st));
+      const OzMoments mom{as, ldas, m_b, p1, p2, ldpart};
+      CU(oz_gemm(aq, ae, ns, vq, ve, q, q, oz_ldk(q), ozS, T, ldq, 1, 0, 0, st, &mom));
+    } else {
+      GemmArgs g{};
+      g.A = as; g.lda = ldas; g.B = Vw; g.ldb = ldq; g.C = T; g.ldc = ldq; g.M = (int)ns; g.N = q; g.K = q;
+      g.aux = as; g.ldaux = ldas; g.colvec = m_b; g.part1 = p1; g.part2 = p2; g.ldpart = ldpart;
+      CU(gemm(st, 0, 0, kMoments, false, 1, g));
+    }
     moments_combine(Kvec + i0, p1, p2, ldpart, ntq, a + i0 * lda, lda, K_b + i0 * ldk, ldk, ns, q, lam_m + i0,
                     lam_var + i0, st);
   }
@@ -1218,8 +1277,7 @@ int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, c
   CU(h->arena.reserve((size_t)nb * 8 * sizeof(double) + 4096));
   double* bp = (double*)h->arena.p;
   const double A = std::exp(logA);
-  fparam_pass(lam_m, lam_var, r, N, A, lambda0, f, bp, st);
-  for (int k = 0; k < 6; ++k) sum_to_slot(bp + k, nb, 8, 1.0, h->d_scal, kSlotAux0 + k, 0, st);
+  fparam_pass(lam_m, lam_var, r, N, A, lambda0, f, bp, h->d_ticket, h->d_scal + kSlotAux0, st);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(h->h_out, h->d_scal + kSlotAux0, sizeof(double) * 6, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
@@ -1241,8 +1299,7 @@ int sgp_loglik_sums(sgp_handle* h, const double* r, const double* f, const doubl
   const int nb = fparam_blocks(N);
   CU(h->arena.reserve((size_t)nb * 8 * sizeof(double) + 4096));
   double* bp = (double*)h->arena.p;
-  loglik_sums_pass(r, f, lam_m, lam_var, N, std::exp(logA), bp, st);
-  for (int k = 0; k < 5; ++k) sum_to_slot(bp + k, nb, 8, 1.0, h->d_scal, kSlotAux0 + k, 0, st);
+  loglik_sums_pass(r, f, lam_m, lam_var, N, std::exp(logA), bp, h->d_ticket, h->d_scal + kSlotAux0, st);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(h->h_out, h->d_scal + kSlotAux0, sizeof(double) * 5, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
@@ -1258,12 +1315,15 @@ int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, c
   const double A = std::exp(logA);
   const long ldq = rup(q, 16);
   const long slab = std::min<long>(h->slab_rows, rup(N, 128));
-  const int nz = pick_split(gemm_tiles(q, q, true), slab);
+  const int ozS = oz_pick(h, slab, q, q);   // G on the int8 tensor-core path: (sqrt(f) a)^T (sqrt(f) a), lower tiles
+  const int nz = ozS ? oz_split(q, q, (int)std::min(slab, N), ozS, 1) : pick_split(gemm_tiles(q, q, true), slab);
   const long zs = (long)q * ldq;
   const int ncb = colsum_blocks(slab);
+  const long ldkN = oz_ldk((int)slab);
   size_t need = 0;
   auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
   acc((size_t)slab * ldq); acc((size_t)nz * zs); acc((size_t)ncb * ldq); acc((size_t)q * ldq);
+  if (ozS) { acc((size_t)((ozS + 1) / 2) * q * ldkN / 8 + 16); acc(q); acc(q); }
   need += 4096;
   CU(h->arena.reserve(need));
   Arena ar(h->arena.p, h->arena.bytes);
@@ -1271,20 +1331,31 @@ int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, c
   double* Gpart = ar.take<double>((size_t)nz * zs);
   double* colpart = ar.take<double>((size_t)ncb * ldq);
   double* Gw = ar.take<double>((size_t)q * ldq);
+  int8_t* atq = nullptr; int* ate = nullptr; unsigned long long* amx = nullptr;
+  if (ozS) {
+    atq = (int8_t*)ar.take<double>((size_t)((ozS + 1) / 2) * q * ldkN / 8 + 16);
+    ate = (int*)ar.take<double>(q); amx = (unsigned long long*)ar.take<double>(q);
+  }
   int si = 0;
   for (long i0 = 0; i0 < N; i0 += slab, ++si) {
     const long ns = std::min(slab, N - i0);
     const double* as = a + i0 * lda; long ldas = lda;
     if (!aligned2(as, lda)) { copy_mat(as, lda, (int)ns, q, aw, ldq, st); as = aw; ldas = ldq; }
-    GemmArgs gg{};  // G += a^T diag(f) a   (U:1422)
-    gg.A = as; gg.lda = ldas; gg.B = as; gg.ldb = ldas; gg.C = Gpart; gg.ldc = ldq; gg.M = q; gg.N = q; gg.K = (int)ns;
-    gg.k_chunk = (int)rup((ns + nz - 1) / nz, 16); gg.zstride = zs; gg.accumulate = si > 0; gg.kscale = f + i0;
-    gg.lower_only = 1;
-    CU(gemm(st, 1, 1, kStore, false, nz, gg));
+    if (ozS) {      // G += a^T diag(f) a   (U:1422)
+      const int ldk_s = oz_ldk((int)ns);
+      CU(oz_slice_cols(as, ldas, ns, q, ozS, atq, ldk_s, ate, amx, st, f + i0));
+      CU(oz_gemm(atq, ate, q, atq, ate, q, (int)ns, ldk_s, ozS, Gpart, ldq, nz, zs, si > 0, st, nullptr, 0, 1.0, 1));
+    } else {
+      GemmArgs gg{};
+      gg.A = as; gg.lda = ldas; gg.B = as; gg.ldb = ldas; gg.C = Gpart; gg.ldc = ldq; gg.M = q; gg.N = q; gg.K = (int)ns;
+      gg.k_chunk = (int)rup((ns + nz - 1) / nz, 16); gg.zstride = zs; gg.accumulate = si > 0; gg.kscale = f + i0;
+      gg.lower_only = 1;
+      CU(gemm(st, 1, 1, kStore, false, nz, gg));
+    }
     colsum_weighted(as, ldas, ns, q, r + i0, f + i0, colpart, ldq, st);   // g += a^T (r - f)   (U:1421)
     col_reduce(colpart, colsum_blocks(ns), q, ldq, g, si > 0, st);
   }
-  slice_reduce(Gpart, nz, zs, zs, Gw, 0, st);
+  slice_reduce(Gpart, ozS ? oz_eff_split((int)std::min(slab, N), nz) : nz, zs, zs, Gw, 0, st);
   mirror_lower(Gw, ldq, q, st);
   lincomb(G, ldg, q, q, A * A, Gw, ldq, 0.0, nullptr, 0, 0.0, st);
   scale_vec(g, q, A, st);

@@ -776,16 +776,52 @@ void moments_combine(const double* Kvec, const double* part1, const double* part
 }
 
 constexpr int kFparamBlocks = 148 * 4;
+
+// Last-block-done finish of NS block-partial sums: every block stores its partials, takes a ticket, and the block that
+// draws the last ticket adds all partials in a fixed order (deterministic) into out[0..NS) and re-arms the ticket.
+template <int NS>
+__device__ __forceinline__ void finish_block_sums(const double (&acc)[NS], double* red, double* __restrict__ blockpart,
+                                                  unsigned* __restrict__ ticket, double* __restrict__ out) {
+  __shared__ bool is_last;
+#pragma unroll
+  for (int k = 0; k < NS; ++k) {
+    const double sres = block_sum(acc[k], red);
+    if (threadIdx.x == 0) blockpart[(long)blockIdx.x * 8 + k] = sres;
+  }
+  if (threadIdx.x == 0) {
+    __threadfence();
+    is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+#pragma unroll
+  for (int k = 0; k < NS; ++k) {
+    double v = 0.0;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) v += __ldcg(blockpart + (long)i * 8 + k);
+    const double sres = block_sum(v, red);
+    if (threadIdx.x == 0) out[k] = sres;
+  }
+  if (threadIdx.x == 0) *ticket = 0u;
+}
+
+// f and the sums of the logA closure in one pass (utils.py:1138, 1224, 1243, 1253-1255).  el0 = exp(lambda0) when
+// |lambda0| is moderate (el0_ok): then f = exp(x) * el0 shares the exponential with sum exp(x); otherwise, and for
+// elements whose exp(x) leaves the normal range, f = exp(x + lambda0) exactly as the reference writes it.
 __global__ void __launch_bounds__(256) fparam_kernel(const double* __restrict__ lam_m,
                                                      const double* __restrict__ lam_var,
                                                      const double* __restrict__ r, long n, double A, double lambda0,
-                                                     double* __restrict__ f, double* __restrict__ blockpart) {
+                                                     double el0, int el0_ok, double* __restrict__ f,
+                                                     double* __restrict__ blockpart, unsigned* __restrict__ ticket,
+                                                     double* __restrict__ out) {
   __shared__ double red[32];
   double acc[6] = {0, 0, 0, 0, 0, 0};
   const double hA2 = 0.5 * A * A;
   auto body = [&](double lm, double lv, double ri, double& fout) {
-    const double e = exp(A * lm + hA2 * lv);            // U:1224
-    const double fi = exp(A * lm + hA2 * lv + lambda0);  // U:1138
+    const double x = A * lm + hA2 * lv;
+    const double e = exp(x);                             // U:1224
+    double fi = e * el0;                                 // U:1138
+    if (!el0_ok || !(e > 1.0e-290 && e < 1.0e290)) fi = exp(x + lambda0);
     fout = fi;
     acc[0] += ri * lm;
     acc[1] += fi;
@@ -801,7 +837,22 @@ __global__ void __launch_bounds__(256) fparam_kernel(const double* __restrict__ 
   const bool vec_ok = ((reinterpret_cast<uintptr_t>(lam_m) | reinterpret_cast<uintptr_t>(lam_var) |
                         reinterpret_cast<uintptr_t>(r) | reinterpret_cast<uintptr_t>(f)) & 15) == 0;
   if (vec_ok) {
-    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (long)gridDim.x * blockDim.x) {
+    const long stride = (long)gridDim.x * blockDim.x;
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + stride < n2; i += 2 * stride) {           // two independent double2 triples in flight per thread
+      const double2 a0 = lm2[i], b0 = lv2[i], c0 = r2[i];
+      const double2 a1 = lm2[i + stride], b1 = lv2[i + stride], c1 = r2[i + stride];
+      double f0, f1, f2, f3;
+      body(a0.x, b0.x, c0.x, f0);
+      body(a0.y, b0.y, c0.y, f1);
+      body(a1.x, b1.x, c1.x, f2);
+      body(a1.y, b1.y, c1.y, f3);
+      if (f) {
+        reinterpret_cast<double2*>(f)[i] = make_double2(f0, f1);
+        reinterpret_cast<double2*>(f)[i + stride] = make_double2(f2, f3);
+      }
+    }
+    for (; i < n2; i += stride) {
       const double2 a = lm2[i], b = lv2[i], c = r2[i];
       double f0, f1;
       body(a.x, b.x, c.x, f0);
@@ -820,28 +871,28 @@ __global__ void __launch_bounds__(256) fparam_kernel(const double* __restrict__ 
       if (f) f[i] = f0;
     }
   }
-#pragma unroll
-  for (int k = 0; k < 6; ++k) {
-    const double sres = block_sum(acc[k], red);
-    if (threadIdx.x == 0) blockpart[(long)blockIdx.x * 8 + k] = sres;
-  }
+  finish_block_sums<6>(acc, red, blockpart, ticket, out);
 }
 int fparam_blocks(long n) {
   const int nb = cdiv(n, 512);
   return nb < kFparamBlocks ? (nb < 1 ? 1 : nb) : kFparamBlocks;
 }
 void fparam_pass(const double* lam_m, const double* lam_var, const double* r, long n, double A, double lambda0,
-                 double* f, double* blockpart, cudaStream_t st) {
-  note_launch(); fparam_kernel<<<fparam_blocks(n), 256, 0, st>>>(lam_m, lam_var, r, n, A, lambda0, f, blockpart);
+                 double* f, double* blockpart, unsigned* ticket, double* out, cudaStream_t st) {
+  const int ok = std::fabs(lambda0) < 300.0;
+  note_launch();
+  fparam_kernel<<<fparam_blocks(n), 256, 0, st>>>(lam_m, lam_var, r, n, A, lambda0, ok ? std::exp(lambda0) : 0.0, ok, f,
+                                                  blockpart, ticket, out);
 }
 
 
 // sums for compute_loglikelihood with a caller-supplied f (utils.py:1240-1255):
-// blockpart[blk*8 + {0..4}] = sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, nan-count(f)
+// out[0..5) = sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, nan-count(f)
 __global__ void __launch_bounds__(256) loglik_sums_kernel(const double* __restrict__ r, const double* __restrict__ f,
                                                           const double* __restrict__ lam_m,
                                                           const double* __restrict__ lam_var, long n, double A,
-                                                          double* __restrict__ blockpart) {
+                                                          double* __restrict__ blockpart,
+                                                          unsigned* __restrict__ ticket, double* __restrict__ out) {
   __shared__ double red[32];
   double acc[5] = {0, 0, 0, 0, 0};
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
@@ -853,15 +904,12 @@ __global__ void __launch_bounds__(256) loglik_sums_kernel(const double* __restri
     acc[3] += ri;
     acc[4] += (fi != fi) ? 1.0 : 0.0;
   }
-#pragma unroll
-  for (int k = 0; k < 5; ++k) {
-    const double sres = block_sum(acc[k], red);
-    if (threadIdx.x == 0) blockpart[(long)blockIdx.x * 8 + k] = sres;
-  }
+  finish_block_sums<5>(acc, red, blockpart, ticket, out);
 }
 void loglik_sums_pass(const double* r, const double* f, const double* lam_m, const double* lam_var, long n, double A,
-                      double* blockpart, cudaStream_t st) {
-  note_launch(); loglik_sums_kernel<<<fparam_blocks(n), 256, 0, st>>>(r, f, lam_m, lam_var, n, A, blockpart);
+                      double* blockpart, unsigned* ticket, double* out, cudaStream_t st) {
+  note_launch();
+  loglik_sums_kernel<<<fparam_blocks(n), 256, 0, st>>>(r, f, lam_m, lam_var, n, A, blockpart, ticket, out);
 }
 
 constexpr int kColsumRows = 128;

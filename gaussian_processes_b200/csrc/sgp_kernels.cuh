@@ -130,14 +130,15 @@ void finalize(const double* scal, const int* flags, double A, double lambda0, co
 void moments_combine(const double* Kvec, const double* part1, const double* part2, long ldpart, int nparts,
                      const double* a, long lda, const double* K_b, long ldk, long n, int q, double* lam_m,
                      double* lam_var, cudaStream_t st);
-// one streaming pass over (lam_m, lam_var, r): blockpart[blk*8 + {0..5}] =
-//   sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, sum exp(A lam_m + A^2 lam_var/2), nan-count
+// one streaming pass over (lam_m, lam_var, r): out[0..6) =
+//   sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, sum exp(A lam_m + A^2 lam_var/2), nan-count.
+// blockpart: fparam_blocks(n) * 8 doubles of scratch; ticket: one zero-initialised counter (re-armed by the kernel)
 int fparam_blocks(long n);
 void fparam_pass(const double* lam_m, const double* lam_var, const double* r, long n, double A, double lambda0,
-                 double* f, double* blockpart, cudaStream_t st);
-// same block layout as fparam_pass, for a caller-supplied f: {sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, nan}
+                 double* f, double* blockpart, unsigned* ticket, double* out, cudaStream_t st);
+// same, for a caller-supplied f: out[0..5) = {sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, nan}
 void loglik_sums_pass(const double* r, const double* f, const double* lam_m, const double* lam_var, long n, double A,
-                      double* blockpart, cudaStream_t st);
+                      double* blockpart, unsigned* ticket, double* out, cudaStream_t st);
 // colpart[blk][j] = sum_{i in blk} a_ij (r_i - f_i)
 int colsum_blocks(long n);
 void colsum_weighted(const double* a, long lda, long n, int q, const double* r, const double* f, double* colpart,
@@ -172,9 +173,9 @@ cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S,
                           cudaStream_t st);
 // C (M x N) = A * B^T from the slices of A (M rows) and B (N rows), K columns each
 // slices of X^T (contraction over the rows of X): q is [ceil(S/2)][cols][oz_ldk(rows)], exps[cols]; mx: cols 8-byte words
-// negsq (optional, length rows, entries <= 0): row r is multiplied by sqrt(-negsq[r]) before slicing
+// rowsq (optional, length rows): row r is multiplied by sqrt(|rowsq[r]|) before slicing (the sign goes into alpha)
 cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
-                          unsigned long long* mx, cudaStream_t st, const double* negsq = nullptr);
+                          unsigned long long* mx, cudaStream_t st, const double* rowsq = nullptr);
 // nz > 1: split-K, slice z of the k-blocks goes to C + z * zstride (oz_split picks nz; the effective count, which
 // oz_gemm never exceeds, is ceil(nkb / ceil(nkb / nz))); accumulate: C += instead of C =
 int oz_split(long M, int N, int K, int S, int lower_only = 0);

@@ -176,6 +176,52 @@ def test_moments_estep_fparams_against_reference(nat, name):
     assert rel_err(G.cpu().numpy(), fx["estep_G"]) < 1e-9
 
 
+@pytest.mark.parametrize("N,q", [(6000, 96), (9001, 131), (20000, 500)])
+def test_moments_and_estep_terms_many_images(nat, N, q):
+    """Image counts above the int8 threshold: lambda_moments (a V^T with the row-sum epilogue) and estep_terms
+    (a^T diag(f) a over lower tiles) on the tcgen05 int8-slice path, against torch fp64 (U:1090-1101, U:1421-1422)."""
+    g = torch.Generator().manual_seed(N + q)
+    a = torch.randn(N, q, generator=g, dtype=torch.float64) * torch.exp(torch.randn(N, 1, generator=g, dtype=torch.float64))
+    K_b = torch.randn(N, q, generator=g, dtype=torch.float64)
+    W = torch.randn(q, q, generator=g, dtype=torch.float64)
+    V = W @ W.T / q + 0.1 * torch.eye(q, dtype=torch.float64)
+    m_b = torch.randn(q, generator=g, dtype=torch.float64)
+    Kvec = torch.rand(N, generator=g, dtype=torch.float64) + 1.0
+    r = torch.poisson(torch.full((N,), 0.8, dtype=torch.float64), generator=g)
+    f = torch.exp(0.3 * torch.randn(N, generator=g, dtype=torch.float64))
+    d = dev()
+    lam_m, lam_var = nat.lambda_moments(a.to(d), K_b.to(d), Kvec.to(d), m_b.to(d), V.to(d))
+    ref_m = a @ m_b
+    ref_v = Kvec + (-K_b * a + a * (a @ V.T)).sum(1)
+    scale_v = Kvec + (K_b * a).abs().sum(1) + (a.abs() * (a.abs() @ V.abs().T)).sum(1)
+    assert float(((lam_m.cpu() - ref_m).abs() / (a.abs() @ m_b.abs())).max()) < 1e-14
+    assert float(((lam_var.cpu() - ref_v).abs() / scale_v).max()) < 1e-14
+    logA = -0.7
+    gv, G = nat.estep_terms(a.to(d), r.to(d), f.to(d), logA)
+    A = float(np.exp(logA))
+    G_ref = A * A * (a.T * f) @ a
+    g_ref = A * (a.T @ (r - f))
+    # the digit slices are relative to one scale per COLUMN of sqrt(f) a, so the error is bounded through the column
+    # maxima (include/sgp_b200.h, sgp_gemm_i8emu), not through sum |a||a| f; rows here span ~3 decades on purpose
+    cm = (a.abs() * f.sqrt()[:, None]).max(0).values
+    err = (G.cpu() - G_ref).abs()
+    assert float((err / (A * A * N * cm[:, None] * cm[None, :])).max()) < 2e-16
+    assert float((err / (A * A * (a.abs().T * f) @ a.abs())).max()) < 1e-12
+    assert float((G.cpu() - G.cpu().T).abs().max()) == 0.0
+    assert rel_err(gv.cpu().numpy(), g_ref.numpy()) < 1e-12
+
+
+def test_matmul_image_sized_goes_through_int8_slices(nat):
+    """native.matmul (K_b = K B, a = K_b K_tilde_b^-1: U:1693-1694) at image-sized row counts."""
+    g = torch.Generator().manual_seed(77)
+    K = torch.randn(5000, 130, generator=g, dtype=torch.float64)
+    B = torch.randn(130, 90, generator=g, dtype=torch.float64)
+    C = nat.matmul(K.to(dev()), B.to(dev())).cpu()
+    assert float(((C - K @ B).abs() / (K.abs() @ B.abs())).max()) < 4e-15
+    C2 = nat.matmul_nt(K.to(dev()), B.T.contiguous().to(dev())).cpu()
+    assert float(((C2 - K @ B).abs() / (K.abs() @ B.abs())).max()) < 4e-15
+
+
 def test_nd_utility_against_reference(nat):
     """sgp_nd_utility (Lambert W on the device) against the reference's scipy-based nd_utility family, U:416-519."""
     fx = load("utility_n96")
