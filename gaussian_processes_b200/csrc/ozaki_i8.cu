@@ -147,8 +147,8 @@ struct OzArgs {
   double alpha; int lower_only;   // C = alpha * A B^T; lower_only (M == N): only tiles touching the lower triangle
   int num_tiles;                  // tiles enumerated by tile_origin()
   // optional moments epilogue (T = K Mfull^T, utils.py:1090-1101): per 16-column group g of the output,
-  //   part1[g*ldpart + row] = sum_col C*aux,  part2[g*ldpart + row] = sum_col aux*colvec
-  const double* aux; long ldaux; const double* colvec; double* part1; double* part2; long ldpart;
+  //   part1[g*ldpart + row] = sum over the 16-column group g of C*aux
+  const double* aux; long ldaux; double* part1; long ldpart;
   int dbg;   // timing experiments only: 1 = skip A loads, 2 = skip B loads, 4 = every tile loads A rows 0..127
 };
 
@@ -300,43 +300,55 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       tc_fence_before();
       mbar_arrive(bar_tempty);                    // TMEM is free: the next tile's MMAs may start
       tphase ^= 1;
+      // Phase 1 (thread = row): row scale, staging store.  Phase 2 (lane & 15 = column, two rows per pass): column
+      // scale, coalesced store of C; with the moments epilogue the product with aux (read coalesced) goes back into
+      // the staging tile.  Phase 3 (thread = row): this row's sum over the 16-column group.
+      const bool mom = a.part1 != nullptr;
+      const int cc = lane & 15;
 #pragma unroll
       for (int cg = 0; cg < 2; ++cg) {
         if (a.dbg & 32) break;
         const int c0 = n0 + 16 * cg;
-        __syncwarp();
-        double t1 = 0.0, t2 = 0.0;               // moments epilogue: this row's sums over the 16-column group
-        const bool mom = a.part1 != nullptr && row < a.M;
+        const int colc = c0 + cc;
+        const double sbc = colc < a.N ? pow2d(a.eb[colc]) : 0.0;
+        // aux is read one 4-row batch ahead of its use (first batch before the staging stores)
+        auto load_aux = [&](double (&dst)[4], int rb) {
 #pragma unroll
-        for (int j = 0; j < 16; j += 2) {
-          const int col = c0 + j;                // N is padded to even leading dimensions: col, col+1 share validity
-          const double sb0 = col < a.N ? pow2d(a.eb[col]) : 0.0, sb1 = col + 1 < a.N ? pow2d(a.eb[col + 1]) : 0.0;
-          const double v0 = acc[cg][j] * sa * sb0, v1 = acc[cg][j + 1] * sa * sb1;
-          stg[lane * 16 + (j ^ (lane & 15))] = v0;
-          stg[lane * 16 + ((j + 1) ^ (lane & 15))] = v1;
-          if (mom && col < a.N) {
-            const double2 kv = *reinterpret_cast<const double2*>(a.aux + row * a.ldaux + col);
-            const double k1 = col + 1 < a.N ? kv.y : 0.0;
-            t1 = fma(v0, kv.x, fma(v1, k1, t1));
-            t2 = fma(kv.x, __ldg(a.colvec + col), t2);
-            if (col + 1 < a.N) t2 = fma(k1, __ldg(a.colvec + col + 1), t2);
+          for (int u = 0; u < 4; ++u) {
+            const long grow = m0 + 32 * q + 2 * (rb + u) + (lane >> 4);
+            dst[u] = (grow < a.M && colc < a.N) ? __ldg(a.aux + grow * a.ldaux + colc) : 0.0;
           }
-        }
-        if (mom && c0 < a.N) {
-          a.part1[(long)(c0 >> 4) * a.ldpart + row] = t1;
-          a.part2[(long)(c0 >> 4) * a.ldpart + row] = t2;
-        }
+        };
+        double ax[4] = {0.0, 0.0, 0.0, 0.0}, axn[4] = {0.0, 0.0, 0.0, 0.0};
+        if (mom) load_aux(ax, 0);
         __syncwarp();
-        const int cc = lane & 15;
-#pragma unroll 4
-        for (int r2 = 0; r2 < 16; ++r2) {
-          const int rr = 2 * r2 + (lane >> 4);
-          const long grow = m0 + 32 * q + rr;
-          if (grow < a.M && c0 + cc < a.N) {
-            double* dst = Cz + grow * a.ldc + c0 + cc;
-            const double val = stg[rr * 16 + (cc ^ (rr & 15))];
-            *dst = a.accumulate ? *dst + val : val;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) stg[lane * 16 + (j ^ cc)] = acc[cg][j] * sa;
+        __syncwarp();
+#pragma unroll 1
+        for (int rb = 0; rb < 16; rb += 4) {
+          if (mom && rb + 4 < 16) load_aux(axn, rb + 4);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int rr = 2 * (rb + u) + (lane >> 4);
+            const long grow = m0 + 32 * q + rr;
+            const int si = rr * 16 + (cc ^ (rr & 15));
+            const double val = stg[si] * sbc;
+            if (grow < a.M && colc < a.N) {
+              double* dst = Cz + grow * a.ldc + colc;
+              *dst = a.accumulate ? *dst + val : val;
+            }
+            if (mom) stg[si] = val * ax[u];
           }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) ax[u] = axn[u];
+        }
+        if (mom) {
+          __syncwarp();
+          double t1 = 0.0;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) t1 += stg[lane * 16 + (j ^ cc)];
+          if (row < a.M && c0 < a.N) a.part1[(long)(c0 >> 4) * a.ldpart + row] = t1;
         }
       }
     }
@@ -353,14 +365,21 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 // One warp per row: power-of-two row scale, then S round-to-nearest base-128 digits per element.
 __global__ void __launch_bounds__(256)
 oz_slice_rows_kernel(const double* __restrict__ X, long ldx, long rows, int cols, int S, int8_t* __restrict__ q,
-                     int ldk, long pair_stride, int* __restrict__ exps) {
+                     int ldk, long pair_stride, int* __restrict__ exps, const double* __restrict__ colvec,
+                     double* __restrict__ rowdot) {
   const int lane = threadIdx.x & 31;
   const long warp0 = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long nwarps = ((long)gridDim.x * blockDim.x) >> 5;
   for (long r = warp0; r < rows; r += nwarps) {
     const double* x = X + r * ldx;
-    double m = 0.0;
-    for (int c = lane; c < cols; c += 32) m = fmax(m, fabs(x[c]));
+    double m = 0.0, dot = 0.0;
+    if (colvec) {       // the row is in flight anyway: its product with colvec (lam_m = K bb, utils.py:1090)
+      for (int c = lane; c < cols; c += 32) { const double xv = x[c]; m = fmax(m, fabs(xv)); dot = fma(xv, __ldg(colvec + c), dot); }
+      dot = warp_sum(dot);
+      if (lane == 0) rowdot[r] = dot;
+    } else {
+      for (int c = lane; c < cols; c += 32) m = fmax(m, fabs(x[c]));
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
     const int e = (m > 0.0 && m < 1.0e300) ? ilogb(m) + 1 : 0;
@@ -488,12 +507,13 @@ cudaError_t oz_init() {
 }
 
 cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
-                          cudaStream_t st) {
+                          cudaStream_t st, const double* colvec, double* rowdot) {
   if (rows <= 0) return cudaSuccess;
   if (S < 1 || S > kOzMaxS || ldk != oz_ldk(cols)) return cudaErrorInvalidValue;
   const long blocks = std::min<long>((rows + 7) / 8, 148L * 8);
   note_launch();
-  oz_slice_rows_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, ldx, rows, cols, S, q, ldk, rows * (long)ldk, exps);
+  oz_slice_rows_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, ldx, rows, cols, S, q, ldk, rows * (long)ldk, exps,
+                                                           rowdot ? colvec : nullptr, rowdot);
   return cudaGetLastError();
 }
 
@@ -555,8 +575,7 @@ cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, c
   static const int dbg = getenv("SGP_OZ_DEBUG") ? atoi(getenv("SGP_OZ_DEBUG")) : 0;
   const long tiles = oz_tiles(M, N, lower_only);
   OzArgs a{ea, eb, C, ldc, (int)M, N, K, S, nz, kb_per_z, zstride, accumulate, alpha, lower_only, (int)tiles,
-           mom ? mom->aux : nullptr, mom ? mom->ldaux : 0, mom ? mom->colvec : nullptr, mom ? mom->part1 : nullptr,
-           mom ? mom->part2 : nullptr, mom ? mom->ldpart : 0, dbg};
+           mom ? mom->aux : nullptr, mom ? mom->ldaux : 0, mom ? mom->part1 : nullptr, mom ? mom->ldpart : 0, dbg};
   if (mom && (nz != 1 || accumulate)) return cudaErrorInvalidValue;
   const int grid = (int)std::min<long>(tiles * nz, max_ctas > 0 ? max_ctas : 148);   // fewer CTAs leave SMs to a concurrent stream
   note_launch();

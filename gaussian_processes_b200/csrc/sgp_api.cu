@@ -862,14 +862,14 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     g3.A = Ks; g3.lda = ldm; g3.B = Mfull; g3.ldb = ldm; g3.C = Ts; g3.ldc = ldm; g3.M = (int)ns; g3.N = m; g3.K = m;
     g3.aux = Ks; g3.ldaux = ldm; g3.colvec = bb; g3.part1 = pm1; g3.part2 = pm2; g3.ldpart = ldpartN;
     if (ozS) {
-      CU(oz_slice_rows(Ks, ldm, ns, m, ozS, kq, oz_ldk(m), ke, st));
-      const OzMoments mom{Ks, ldm, bb, pm1, pm2, ldpartN};
+      CU(oz_slice_rows(Ks, ldm, ns, m, ozS, kq, oz_ldk(m), ke, st, bb, pm2));   // pm2 = K bb on the way
+      const OzMoments mom{Ks, ldm, pm1, ldpartN};
       CU(oz_gemm(kq, ke, ns, mq, me, m, m, oz_ldk(m), ozS, Ts, ldm, 1, 0, 0, st, &mom));
     } else {
       CU(gemm(st, 0, 0, kMoments, false, 1, g3));
     }
     mark(4);
-    moments_rows(s_s, pm1, pm2, ldpartN, ozS ? ng16 : ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
+    moments_rows(s_s, pm1, pm2, ldpartN, ozS ? ng16 : ntm, ozS ? 1 : ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
                  v_s, blockpart, st);
     const int nbm = moments_rows_blocks(ns);
     sum_to_slot(blockpart + 0, nbm, 4, 1.0, h->d_scal, kSlotRLam, acc_flag, st);
@@ -1252,8 +1252,8 @@ int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K
     const double* as = a + i0 * lda; long ldas = lda;
     if (!aligned2(as, lda)) { copy_mat(as, lda, (int)ns, q, aw, ldq, st); as = aw; ldas = ldq; }
     if (ozS) {     // T = a V^T ; part1 = rowdot(T, a) ; part2 = a m_b
-      CU(oz_slice_rows(as, ldas, ns, q, ozS, aq, oz_ldk(q), ae, st));
-      const OzMoments mom{as, ldas, m_b, p1, p2, ldpart};
+      CU(oz_slice_rows(as, ldas, ns, q, ozS, aq, oz_ldk(q), ae, st, m_b, p2));   // p2 = a m_b on the way
+      const OzMoments mom{as, ldas, p1, ldpart};
       CU(oz_gemm(aq, ae, ns, vq, ve, q, q, oz_ldk(q), ozS, T, ldq, 1, 0, 0, st, &mom));
     } else {
       GemmArgs g{};
@@ -1261,7 +1261,7 @@ int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K
       g.aux = as; g.ldaux = ldas; g.colvec = m_b; g.part1 = p1; g.part2 = p2; g.ldpart = ldpart;
       CU(gemm(st, 0, 0, kMoments, false, 1, g));
     }
-    moments_combine(Kvec + i0, p1, p2, ldpart, ntq, a + i0 * lda, lda, K_b + i0 * ldk, ldk, ns, q, lam_m + i0,
+    moments_combine(Kvec + i0, p1, p2, ldpart, ntq, ozS ? 1 : ntq, a + i0 * lda, lda, K_b + i0 * ldk, ldk, ns, q, lam_m + i0,
                     lam_var + i0, st);
   }
   CU(cudaGetLastError());

@@ -96,7 +96,7 @@ void norms_finalize(const double* part, long ldpart, int nparts, long n, double 
 // a5-a7: moments / rate / adjoint weights per image (reference utils.py:1090-1101, 1138, 1243, 1266)
 // =====================================================================================================
 __global__ void moments_rows_kernel(const double* __restrict__ s, const double* __restrict__ part1,
-                                    const double* __restrict__ part2, long ldpart, int nparts,
+                                    const double* __restrict__ part2, long ldpart, int nparts, int nparts2,
                                     const double* __restrict__ r, long n, double A, double lambda0,
                                     double* __restrict__ lam_m, double* __restrict__ lam_var, double* __restrict__ f,
                                     double* __restrict__ u, double* __restrict__ v, double* __restrict__ blockpart) {
@@ -105,10 +105,8 @@ __global__ void moments_rows_kernel(const double* __restrict__ s, const double* 
   double rl = 0.0, fs = 0.0, rs = 0.0, nn = 0.0;
   if (i < n) {
     double q1 = 0.0, q2 = 0.0;
-    for (int t = 0; t < nparts; ++t) {
-      q1 += part1[t * ldpart + i];
-      q2 += part2[t * ldpart + i];
-    }
+    for (int t = 0; t < nparts; ++t) q1 += part1[t * ldpart + i];
+    for (int t = 0; t < nparts2; ++t) q2 += part2[t * ldpart + i];
     const double lv = s[i] + 0.5 * q1;
     const double lm = q2;
     const double fi = exp(A * lm + 0.5 * A * A * lv + lambda0);   // U:1138
@@ -134,11 +132,11 @@ __global__ void moments_rows_kernel(const double* __restrict__ s, const double* 
 
 int moments_rows_blocks(long n) { return cdiv(n, 256); }
 
-void moments_rows(const double* s, const double* part1, const double* part2, long ldpart, int nparts,
+void moments_rows(const double* s, const double* part1, const double* part2, long ldpart, int nparts, int nparts2,
                   const double* r, long n, double A, double lambda0, double* lam_m, double* lam_var, double* f,
                   double* u, double* v, double* blockpart, cudaStream_t st) {
   if (n <= 0) return;
-  note_launch(); moments_rows_kernel<<<moments_rows_blocks(n), 256, 0, st>>>(s, part1, part2, ldpart, nparts, r, n, A, lambda0,
+  note_launch(); moments_rows_kernel<<<moments_rows_blocks(n), 256, 0, st>>>(s, part1, part2, ldpart, nparts, nparts2, r, n, A, lambda0,
                                                               lam_m, lam_var, f, u, v, blockpart);
 }
 
@@ -746,7 +744,7 @@ void finalize(const double* scal, const int* flags, double A, double lambda0, co
 // E-step / f-param helpers
 // =====================================================================================================
 __global__ void moments_combine_kernel(const double* __restrict__ Kvec, const double* __restrict__ part1,
-                                       const double* __restrict__ part2, long ldpart, int nparts,
+                                       const double* __restrict__ part2, long ldpart, int nparts, int nparts2,
                                        const double* __restrict__ a, long lda, const double* __restrict__ K_b,
                                        long ldk, long n, int q, double* __restrict__ lam_m,
                                        double* __restrict__ lam_var) {
@@ -759,19 +757,17 @@ __global__ void moments_combine_kernel(const double* __restrict__ Kvec, const do
   d = warp_sum(d);
   if (lane == 0) {
     double q1 = 0.0, q2 = 0.0;
-    for (int t = 0; t < nparts; ++t) {
-      q1 += part1[t * ldpart + i];
-      q2 += part2[t * ldpart + i];
-    }
+    for (int t = 0; t < nparts; ++t) q1 += part1[t * ldpart + i];
+    for (int t = 0; t < nparts2; ++t) q2 += part2[t * ldpart + i];
     lam_m[i] = q2;
     lam_var[i] = Kvec[i] + (q1 - d);
   }
 }
 void moments_combine(const double* Kvec, const double* part1, const double* part2, long ldpart, int nparts,
-                     const double* a, long lda, const double* K_b, long ldk, long n, int q, double* lam_m,
+                     int nparts2, const double* a, long lda, const double* K_b, long ldk, long n, int q, double* lam_m,
                      double* lam_var, cudaStream_t st) {
   if (n <= 0) return;
-  note_launch(); moments_combine_kernel<<<cdiv(n, 8), 256, 0, st>>>(Kvec, part1, part2, ldpart, nparts, a, lda, K_b,
+  note_launch(); moments_combine_kernel<<<cdiv(n, 8), 256, 0, st>>>(Kvec, part1, part2, ldpart, nparts, nparts2, a, lda, K_b,
                                                                     ldk, n, q, lam_m, lam_var);
 }
 

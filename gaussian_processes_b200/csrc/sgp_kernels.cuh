@@ -49,10 +49,10 @@ void norms_finalize(const double* part, long ldpart, int nparts, long n, double 
                     cudaStream_t st);
 
 // ---- a5-a7: per-image moments, rate, adjoint weights ---------------------------------------
-// lam_var = s + 0.5*sum_t part1 ; lam_m = sum_t part2 ; f = exp(A lam_m + A^2 lam_var/2 + lambda0)
+// lam_var = s + 0.5*sum_{t<nparts} part1 ; lam_m = sum_{t<nparts2} part2 ; f = exp(A lam_m + A^2 lam_var/2 + lambda0)
 // u = A (r - f) ; v = -A^2 f / 2 ; blockpart[blk*4 + {0,1,2,3}] = sum r*lam_m, sum f, sum r, nan-count
 int moments_rows_blocks(long n);
-void moments_rows(const double* s, const double* part1, const double* part2, long ldpart, int nparts,
+void moments_rows(const double* s, const double* part1, const double* part2, long ldpart, int nparts, int nparts2,
                   const double* r, long n, double A, double lambda0, double* lam_m, double* lam_var, double* f,
                   double* u, double* v, double* blockpart, cudaStream_t st);
 
@@ -128,7 +128,7 @@ void finalize(const double* scal, const int* flags, double A, double lambda0, co
 // ---- E-step / f-param helpers -------------------------------------------------------------------
 // lam_m = sum_t part2 ; lam_var = Kvec + sum_t part1 - rowdot(K_b, a)        (utils.py:1090-1101)
 void moments_combine(const double* Kvec, const double* part1, const double* part2, long ldpart, int nparts,
-                     const double* a, long lda, const double* K_b, long ldk, long n, int q, double* lam_m,
+                     int nparts2, const double* a, long lda, const double* K_b, long ldk, long n, int q, double* lam_m,
                      double* lam_var, cudaStream_t st);
 // one streaming pass over (lam_m, lam_var, r): out[0..6) =
 //   sum r*lam_m, sum f, sum (lam_m + A lam_var) f, sum r, sum exp(A lam_m + A^2 lam_var/2), nan-count.
@@ -169,8 +169,9 @@ int oz_ldk(int K);                                   // row pitch (bytes) of one
 size_t oz_slice_bytes(long rows, int K, int S);      // bytes of the digit array of a rows x K operand
 cudaError_t oz_init();                               // opt-in shared memory of the kernel (once per process)
 // q: [ceil(S/2)][rows][ldk] int8 digits (slices 2j, 2j+1 interleaved per 64-byte k-block), exps[rows]: row scales
+// colvec / rowdot (optional): rowdot[r] = sum_c X[r][c] * colvec[c], taken while the row streams through
 cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
-                          cudaStream_t st);
+                          cudaStream_t st, const double* colvec = nullptr, double* rowdot = nullptr);
 // C (M x N) = A * B^T from the slices of A (M rows) and B (N rows), K columns each
 // slices of X^T (contraction over the rows of X): q is [ceil(S/2)][cols][oz_ldk(rows)], exps[cols]; mx: cols 8-byte words
 // rowsq (optional, length rows): row r is multiplied by sqrt(|rowsq[r]|) before slicing (the sign goes into alpha)
@@ -181,7 +182,8 @@ cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S,
 int oz_split(long M, int N, int K, int S, int lower_only = 0);
 inline int oz_eff_split(int K, int nz) { const int nkb = (K + 63) / 64, kbz = (nkb + nz - 1) / nz; return (nkb + kbz - 1) / kbz; }
 // optional moments epilogue: per 16-column group g, part1[g*ldpart + row] = sum_col C*aux, part2 = sum_col aux*colvec
-struct OzMoments { const double* aux; long ldaux; const double* colvec; double* part1; double* part2; long ldpart; };
+// row-sum epilogue: part1[g * ldpart + row] = sum over the 16-column group g of C[row][.] * aux[row][.]
+struct OzMoments { const double* aux; long ldaux; double* part1; long ldpart; };
 cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,
                     int S, double* C, long ldc, int nz, long zstride, int accumulate, cudaStream_t st,
                     const OzMoments* mom = nullptr, int max_ctas = 0, double alpha = 1.0, int lower_only = 0);
