@@ -10,7 +10,8 @@
 //   x^T dC_{eps_0x} x          = 4 e^{theta_beta} Amp sum_ix (lin_ix - eps_0x) rsx[ix]             (utils.py:904)
 //   x^T dC_{eps_0y} x          = 4 e^{theta_beta} Amp sum_iy (lin_iy - eps_0y) rsy[iy]             (utils.py:905)
 //   x^T dC_{-2log2beta} x      = -2 e^{theta_beta} Amp (sum (lin_ix-eps_0x)^2 rsx + sum (lin_iy-eps_0y)^2 rsy)  (U:907)
-// i.e. 8 n^3 flops per image instead of the 2 p^2 (value) + 2 p^2 (adjoint) of the dense products.
+// i.e. 8 n^3 flops per image instead of the 2 p^2 (value) + 2 p^2 (adjoint) of the dense products -- 6.4 n^3 with
+// the symmetry of Sy / Sx (only the tiles on and below the diagonal of the second product of each chain).
 //
 // One warp per image; the four n x n x n products run on the fp64 tensor pipe (DMMA m8n8k4).  The first product
 // of each chain stays in registers: its C fragments are turned into A fragments with quad shuffles.
@@ -30,12 +31,12 @@ __device__ __forceinline__ double lin_coord_dev(int i, int n) {   // torch.linsp
 }
 
 // RB row tiles (8 rows each) of one chain.  TR = false: rows are iy (Sy = M G M^T); TR = true: rows are ix
-// (Sx = M^T G M).  Adds per-lane partial sums: rs_tot += sum E, d2 += sum E o D2, a1 += sum phi*rs, a2 += sum phi^2*rs.
+// (Sx = M^T G M).  Adds the per-lane partial sums T0..T3 described at the end of the function.
 // Two row tiles share every G / M fragment of the second operand (7 fragment loads per 10 DMMAs instead of 6 per 5).
 template <int NT, bool TR, int RB>
 __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M, const double* __restrict__ G,
-                                           const double* __restrict__ lin, double center, int lane, double& rs_tot,
-                                           double& d2, double& a1, double& a2) {
+                                           const double* __restrict__ lin, const double* __restrict__ lin2, int lane,
+                                           double& T0, double& T1, double& T2, double& T3) {
   constexpr int LD = 8 * NT + 4;
   const int g = lane >> 2, t = lane & 3;
   double P[RB][NT][2];
@@ -56,6 +57,8 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
       for (int r = 0; r < RB; ++r) dmma884(P[r][j][0], P[r][j][1], af[r], bf);
     }
   }
+  // S = P M^T (resp. P M) is symmetric: only the tiles on and below the diagonal are formed (15 of 25 at n = 40);
+  // a tile below the diagonal stands for its mirror image too, through the weights of the sums further down.
   double S[RB][NT][2];
 #pragma unroll
   for (int r = 0; r < RB; ++r)
@@ -77,40 +80,50 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
       const int k = 8 * jk + 4 * h + t;
 #pragma unroll
       for (int jn = 0; jn < NT; ++jn) {
-        const double bf = TR ? M[k * LD + 8 * jn + g] : M[(8 * jn + g) * LD + k];
+        if (jn <= i0 + RB - 1) {
+          const double bf = TR ? M[k * LD + 8 * jn + g] : M[(8 * jn + g) * LD + k];
 #pragma unroll
-        for (int r = 0; r < RB; ++r) dmma884(S[r][jn][0], S[r][jn][1], af[r], bf);
+          for (int r = 0; r < RB; ++r)
+            if (jn <= i0 + r) dmma884(S[r][jn][0], S[r][jn][1], af[r], bf);
+        }
       }
     }
   }
+  // With w = 1/2 on the diagonal tiles and 1 below (a tile below the diagonal also stands for its mirror image, a
+  // diagonal tile holds both (a,b) and (b,a)) and E = S o G:
+  //   T0 += w E ; T1 += w E (l_a - l_b)^2 ; T2 += w E (l_a + l_b) ; T3 += w E (l_a^2 + l_b^2)
+  // so that over the whole matrix  sum E = 2 T0,  sum E o D2 = 2 T1,  sum_a (l_a - c) rs_a = T2 - 2 c T0,
+  // sum_a (l_a - c)^2 rs_a = T3 - 2 c T2 + 2 c^2 T0   (rs = row sums of E; c = the receptive-field centre).
 #pragma unroll
   for (int r = 0; r < RB; ++r) {
     const int a = 8 * (i0 + r) + g;
-    const double la = lin[a];
-    double rs = 0.0;
+    const double la = lin[a], la2 = lin2[a];
 #pragma unroll
     for (int jn = 0; jn < NT; ++jn) {
-      const int b = 8 * jn + 2 * t;
-      const double2 gg = *reinterpret_cast<const double2*>(G + a * LD + b);
-      const double e0 = S[r][jn][0] * gg.x, e1 = S[r][jn][1] * gg.y;
-      const double d0 = la - lin[b], d1 = la - lin[b + 1];
-      rs += e0 + e1;
-      d2 += e0 * (d0 * d0) + e1 * (d1 * d1);
+      if (jn <= i0 + r) {
+        const double w = (jn == i0 + r) ? 0.5 : 1.0;
+        const int b = 8 * jn + 2 * t;
+        const double2 gg = *reinterpret_cast<const double2*>(G + a * LD + b);
+        const double2 lb = *reinterpret_cast<const double2*>(lin + b);
+        const double2 lb2 = *reinterpret_cast<const double2*>(lin2 + b);
+        const double e0 = S[r][jn][0] * (gg.x * w), e1 = S[r][jn][1] * (gg.y * w);
+        const double d0 = la - lb.x, d1 = la - lb.y;
+        T0 += e0 + e1;
+        T1 = fma(e0 * d0, d0, fma(e1 * d1, d1, T1));
+        T2 = fma(e0, la + lb.x, fma(e1, la + lb.y, T2));
+        T3 = fma(e0, la2 + lb2.x, fma(e1, la2 + lb2.y, T3));
+      }
     }
-    const double phi = la - center;
-    rs_tot += rs;
-    a1 += phi * rs;
-    a2 += (phi * phi) * rs;
   }
 }
 
 template <int NT, bool TR>
 __device__ __forceinline__ void chain(const double* __restrict__ M, const double* __restrict__ G,
-                                      const double* __restrict__ lin, double center, int lane, double& rs_tot,
-                                      double& d2, double& a1, double& a2) {
+                                      const double* __restrict__ lin, const double* __restrict__ lin2, int lane,
+                                      double& T0, double& T1, double& T2, double& T3) {
 #pragma unroll 1
-  for (int i0 = 0; i0 + 1 < NT; i0 += 2) chain_rows<NT, TR, 2>(i0, M, G, lin, center, lane, rs_tot, d2, a1, a2);
-  if (NT & 1) chain_rows<NT, TR, 1>(NT - 1, M, G, lin, center, lane, rs_tot, d2, a1, a2);
+  for (int i0 = 0; i0 + 1 < NT; i0 += 2) chain_rows<NT, TR, 2>(i0, M, G, lin, lin2, lane, T0, T1, T2, T3);
+  if (NT & 1) chain_rows<NT, TR, 1>(NT - 1, M, G, lin, lin2, lane, T0, T1, T2, T3);
 }
 
 // pstage > 0: every warp owns a staging buffer of pstage doubles and the NEXT image's row is brought in with cp.async
@@ -120,11 +133,16 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
   constexpr int NP = 8 * NT, LD = NP + 4;
   extern __shared__ __align__(16) double sm[];
   double* sG = sm;                 // NP x LD
-  double* sLin = sG + NP * LD;     // NP
+  double* sLin = sG + NP * LD;     // NP coordinates, then NP squares
+  double* sLin2 = sLin + NP;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  double* sM = sLin + NP + (size_t)warp * NP * LD;
+  double* sM = sLin + 2 * NP + (size_t)warp * NP * LD;
 
-  for (int e = tid; e < NP; e += blockDim.x) sLin[e] = (e < a.n) ? lin_coord_dev(e, a.n) : 0.0;
+  for (int e = tid; e < NP; e += blockDim.x) {
+    const double l = (e < a.n) ? lin_coord_dev(e, a.n) : 0.0;
+    sLin[e] = l;
+    sLin2[e] = l * l;
+  }
   for (int e = tid; e < NP * LD; e += blockDim.x) {
     const int r = e / LD, c = e % LD;
     double v = 0.0;
@@ -137,7 +155,7 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
   for (int e = lane; e < NP * LD; e += 32) sM[e] = 0.0;   // pixels outside the mask / padding stay zero
   __syncthreads();
 
-  double* sStage = sLin + NP + (size_t)kSepWarps * NP * LD + (size_t)warp * pstage;
+  double* sStage = sLin + 2 * NP + (size_t)kSepWarps * NP * LD + (size_t)warp * pstage;
   const long stride = (long)gridDim.x * kSepWarps;
   auto prefetch = [&](long img) {
     const double* xr = a.X + img * a.ldx;
@@ -158,15 +176,16 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
       for (int c = lane; c < a.p; c += 32) sM[a.off[c]] = xr[c] * a.alpha[c];
     }
     __syncwarp();
-    double base = 0.0, dy = 0.0, ay1 = 0.0, ay2 = 0.0, bx = 0.0, dx = 0.0, ax1 = 0.0, ax2 = 0.0;
-    chain<NT, false>(sM, sG, sLin, a.ey, lane, base, dy, ay1, ay2);
-    chain<NT, true>(sM, sG, sLin, a.ex, lane, bx, dx, ax1, ax2);
+    double y0 = 0.0, y1 = 0.0, y2 = 0.0, y3 = 0.0, x0 = 0.0, x1 = 0.0, x2 = 0.0, x3 = 0.0;
+    chain<NT, false>(sM, sG, sLin, sLin2, lane, y0, y1, y2, y3);
+    chain<NT, true>(sM, sG, sLin, sLin2, lane, x0, x1, x2, x3);
     __syncwarp();
-    base = warp_sum(base);
-    const double dd = warp_sum(dx + dy);
-    ax1 = warp_sum(ax1);
-    ay1 = warp_sum(ay1);
-    const double a2 = warp_sum(ax2 + ay2);
+    const double base = warp_sum(2.0 * y0);
+    const double dd = warp_sum(2.0 * (x1 + y1));
+    const double ax1 = warp_sum(x2 - 2.0 * a.ex * x0);
+    const double ay1 = warp_sum(y2 - 2.0 * a.ey * y0);
+    const double a2 = warp_sum((x3 - 2.0 * a.ex * x2 + 2.0 * a.ex * a.ex * x0) +
+                               (y3 - 2.0 * a.ey * y2 + 2.0 * a.ey * a.ey * y0));
     if (lane == 0) {
       const double sq = a.amp * base;          // x^T C x
       const double s = sq + a.s02;
@@ -187,7 +206,7 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
 template <int NT>
 cudaError_t launch_sep(const SepQuadArgs& a, cudaStream_t st) {
   constexpr int NP = 8 * NT, LD = NP + 4;
-  size_t smem = (size_t)(NP * LD + NP + kSepWarps * NP * LD) * sizeof(double);
+  size_t smem = (size_t)(NP * LD + 2 * NP + kSepWarps * NP * LD) * sizeof(double);
   // staging buffers for the cp.async prefetch, if the rows are 16-byte aligned and everything fits in 227 KB
   int pstage = (a.p + 1) & ~1;
   const bool aligned = (a.ldx % 2 == 0) && (reinterpret_cast<uintptr_t>(a.X) % 16 == 0);
