@@ -168,7 +168,16 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
     if (pstage > 0) {
       cp_async_wait<0>();
       __syncwarp();
-      for (int c = lane; c < a.p; c += 32) sM[a.off[c]] = sStage[c] * a.alpha[c];
+      // scatter into the n x n layout with the receptive-field weights; five pixels per lane in flight
+      int c = lane;
+      for (; c + 128 < a.p; c += 160) {
+        int o[5]; double v[5];
+#pragma unroll
+        for (int u = 0; u < 5; ++u) { o[u] = __ldg(a.off + c + 32 * u); v[u] = sStage[c + 32 * u] * __ldg(a.alpha + c + 32 * u); }
+#pragma unroll
+        for (int u = 0; u < 5; ++u) sM[o[u]] = v[u];
+      }
+      for (; c < a.p; c += 32) sM[a.off[c]] = sStage[c] * a.alpha[c];
       __syncwarp();
       if (img + stride < a.nrows) prefetch(img + stride);
     } else {
