@@ -1121,8 +1121,16 @@ int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double
   size_t need = 0;
   auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
   acc((size_t)p * ldp); acc((size_t)n2 * ldp); acc((size_t)n2 * ldp); acc((size_t)slab * ldp); acc((size_t)slab * ldp);
-  acc((size_t)ntp_s * ldpart); acc(n2); acc(n2); acc(slab); acc(slab); acc((size_t)slab * ldn2); acc((size_t)slab * ldn2);
+  // image-sized x1: both products on the int8 tensor-core path (csrc/ozaki_i8.cu), x1's digit slices shared by them
+  const int ozS = oz_pick(h, n1, std::min<long>(n2, p), p);
+  const int ng16 = (p + 15) / 16;
+  const int nparts_max = std::max(ntp_s, ozS ? ng16 : 0);
+  acc((size_t)nparts_max * ldpart); acc(n2); acc(n2); acc(slab); acc(slab); acc((size_t)slab * ldn2); acc((size_t)slab * ldn2);
   acc(symm ? (size_t)n1 * ldn2 : 1);
+  if (ozS) {
+    acc((size_t)n2 * ldp); acc(oz_slice_bytes(slab, p, ozS) / 8 + 16); acc(oz_slice_bytes(p, p, ozS) / 8 + 16);
+    acc(oz_slice_bytes(n2, p, ozS) / 8 + 16); acc(slab / 2 + 8); acc(p); acc(n2); acc(p);
+  }
   need += 4096;
   CU(h->arena.reserve(need));
   Arena ar(h->arena.p, h->arena.bytes);
@@ -1131,11 +1139,21 @@ int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double
   double* Z2 = ar.take<double>((size_t)n2 * ldp);
   double* x1w = ar.take<double>((size_t)slab * ldp);
   double* Z1 = ar.take<double>((size_t)slab * ldp);
-  double* part = ar.take<double>((size_t)ntp_s * ldpart);
+  double* part = ar.take<double>((size_t)nparts_max * ldpart);
   double* t2 = ar.take<double>(n2); double* X2 = ar.take<double>(n2);
   double* s1 = ar.take<double>(slab); double* X1 = ar.take<double>(slab);
   double* Kw = ar.take<double>((size_t)slab * ldn2); double* cosw = ar.take<double>((size_t)slab * ldn2);
   double* Kfull = symm ? ar.take<double>((size_t)n1 * ldn2) : nullptr;
+  double* Wt = nullptr; int8_t* xq = nullptr; int8_t* cq = nullptr; int8_t* wq = nullptr;
+  int* xe = nullptr; int* ce = nullptr; int* we = nullptr; unsigned long long* cmx = nullptr;
+  if (ozS) {
+    Wt = ar.take<double>((size_t)n2 * ldp);
+    xq = (int8_t*)ar.take<double>(oz_slice_bytes(slab, p, ozS) / 8 + 16);
+    cq = (int8_t*)ar.take<double>(oz_slice_bytes(p, p, ozS) / 8 + 16);
+    wq = (int8_t*)ar.take<double>(oz_slice_bytes(n2, p, ozS) / 8 + 16);
+    xe = (int*)ar.take<double>(slab / 2 + 8); ce = (int*)ar.take<double>(p); we = (int*)ar.take<double>(n2);
+    cmx = (unsigned long long*)ar.take<double>(p);
+  }
 
   const double* Cc = C; long ldcc = ldc;
   if (!aligned2(C, ldc)) { copy_mat(C, ldc, p, p, Cw, ldp, st); Cc = Cw; ldcc = ldp; }
@@ -1148,10 +1166,27 @@ int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double
     CU(gemm(st, 0, 1, kRowdot, true, 1, g));
     norms_finalize(part, ldpart, ntp_s, n2, s02, t2, X2, st);
   }
+  if (ozS) {
+    // x1^T C x2 = x1 . (x2 C^T): the p x p product moves to the n2 side, exact for any C
+    CU(mm(st, 0, 0, x2c, ld2c, Cc, ldcc, Wt, ldp, (int)n2, p, p));
+    CU(oz_slice_rows(Wt, ldp, n2, p, ozS, wq, oz_ldk(p), we, st));
+    CU(oz_slice_cols(Cc, ldcc, p, p, ozS, cq, oz_ldk(p), ce, cmx, st));     // B operand of x1 C: rows = columns of C
+  }
   for (long i0 = 0; i0 < n1; i0 += slab) {
     const long ns = std::min(slab, n1 - i0);
     const double* xs = x1 + i0 * ld1; long lds = ld1;
     if (!aligned2(xs, ld1)) { copy_mat(xs, ld1, (int)ns, p, x1w, ldp, st); xs = x1w; lds = ldp; }
+    if (ozS) {
+      CU(oz_slice_rows(xs, lds, ns, p, ozS, xq, oz_ldk(p), xe, st));
+      const OzMoments mom{xs, lds, part, ldpart};                           // rowdot(x1 C, x1)  (U:978)
+      CU(oz_gemm(xq, xe, ns, cq, ce, p, p, oz_ldk(p), ozS, Z1, ldp, 1, 0, 0, st, &mom));
+      norms_finalize(part, ldpart, ng16, ns, s02, s1, X1, st);
+      CU(oz_gemm(xq, xe, ns, wq, we, (int)n2, p, oz_ldk(p), ozS, Kw, ldn2, 1, 0, 0, st));
+      acos_forward(Kw, cosw, ldn2, ns, (int)n2, X1, X2, s02, st);           // U:982-990
+      if (symm) copy_mat(Kw, ldn2, (int)ns, (int)n2, Kfull + i0 * ldn2, ldn2, st);
+      else copy_mat(Kw, ldn2, (int)ns, (int)n2, K + i0 * ldk, ldk, st);
+      continue;
+    }
     GemmArgs g{};
     g.A = xs; g.lda = lds; g.B = Cc; g.ldb = ldcc; g.C = Z1; g.ldc = ldp; g.M = (int)ns; g.N = p; g.K = p;
     g.aux = xs; g.ldaux = lds; g.part1 = part; g.ldpart = ldpart;
@@ -1176,11 +1211,13 @@ int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, 
   cudaStream_t st = (cudaStream_t)stream;
   const long ldp = rup(p, 16);
   const long slab = std::min<long>(h->slab_rows, rup(n1, 128));
-  const int ntp = (p + 127) / 128;
+  const int ozS = oz_pick(h, n1, p, p);      // image-sized x1: x1 C on the int8 tensor-core path
+  const int ntp = ozS ? (p + 15) / 16 : (p + 127) / 128;
   const long ldpart = rup(slab, 16);
   size_t need = 0;
   auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
   acc((size_t)p * ldp); acc((size_t)slab * ldp); acc((size_t)slab * ldp); acc((size_t)ntp * ldpart); acc(slab);
+  if (ozS) { acc(oz_slice_bytes(slab, p, ozS) / 8 + 16); acc(oz_slice_bytes(p, p, ozS) / 8 + 16); acc(slab / 2 + 8); acc(p); acc(p); }
   need += 4096;
   CU(h->arena.reserve(need));
   Arena ar(h->arena.p, h->arena.bytes);
@@ -1191,10 +1228,25 @@ int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, 
   double* nrm = ar.take<double>(slab);
   const double* Cc = C; long ldcc = ldc;
   if (!aligned2(C, ldc)) { copy_mat(C, ldc, p, p, Cw, ldp, st); Cc = Cw; ldcc = ldp; }
+  int8_t* xq = nullptr; int8_t* cq = nullptr; int* xe = nullptr; int* ce = nullptr;
+  if (ozS) {
+    xq = (int8_t*)ar.take<double>(oz_slice_bytes(slab, p, ozS) / 8 + 16);
+    cq = (int8_t*)ar.take<double>(oz_slice_bytes(p, p, ozS) / 8 + 16);
+    xe = (int*)ar.take<double>(slab / 2 + 8); ce = (int*)ar.take<double>(p);
+    unsigned long long* cmx = (unsigned long long*)ar.take<double>(p);
+    CU(oz_slice_cols(Cc, ldcc, p, p, ozS, cq, oz_ldk(p), ce, cmx, st));
+  }
   for (long i0 = 0; i0 < n1; i0 += slab) {
     const long ns = std::min(slab, n1 - i0);
     const double* xs = x1 + i0 * ld1; long lds = ld1;
     if (!aligned2(xs, ld1)) { copy_mat(xs, ld1, (int)ns, p, x1w, ldp, st); xs = x1w; lds = ldp; }
+    if (ozS) {
+      CU(oz_slice_rows(xs, lds, ns, p, ozS, xq, oz_ldk(p), xe, st));
+      const OzMoments mom{xs, lds, part, ldpart};
+      CU(oz_gemm(xq, xe, ns, cq, ce, p, p, oz_ldk(p), ozS, Z1, ldp, 1, 0, 0, st, &mom));
+      norms_finalize(part, ldpart, ntp, ns, sigma_0 * sigma_0, Kvec + i0, nrm, st);
+      continue;
+    }
     GemmArgs g{};
     g.A = xs; g.lda = lds; g.B = Cc; g.ldb = ldcc; g.C = Z1; g.ldc = ldp; g.M = (int)ns; g.N = p; g.K = p;
     g.aux = xs; g.ldaux = lds; g.part1 = part; g.ldpart = ldpart;

@@ -143,6 +143,24 @@ def test_acosker_many_rows_odd_leading_dimension(nat):
     assert rel_err(Kvec.cpu().numpy(), (((x1 @ C) * x1).sum(1) + 0.49).numpy()) < 1e-12
 
 
+@pytest.mark.parametrize("n1,n2,p,sym_c", [(6000, 70, 100, True), (9000, 96, 131, False)])
+def test_acosker_image_sized_rows_int8_path(nat, n1, n2, p, sym_c):
+    """Standalone acosker / acosker_diag above the int8 threshold (x1 C with the row-dot epilogue and x1 (x2 C^T)^T on
+    the tcgen05 int8-slice path), including a non-symmetric C, against the oracle (utils.py:978-990, 1029)."""
+    import oracle.spatial_gp_oracle as orc
+    g = torch.Generator().manual_seed(n1 + p)
+    x1 = torch.randn(n1, p, generator=g, dtype=torch.float64)
+    x2 = torch.randn(n2, p, generator=g, dtype=torch.float64)
+    A = torch.randn(p, p, generator=g, dtype=torch.float64)
+    C = A @ A.T / p + 0.1 * torch.eye(p, dtype=torch.float64)
+    if not sym_c:
+        C = C + 0.05 * torch.triu(torch.randn(p, p, generator=g, dtype=torch.float64), 1)
+    K = nat.acosker(0.7, x1.to(dev()), x2.to(dev()), C.to(dev()), False)
+    Kvec = nat.acosker_diag(0.7, x1.to(dev()), C.to(dev()))
+    assert rel_err(K.cpu().numpy(), orc.arccos_kernel({"sigma_0": 0.7}, x1, x2, C).numpy()) < 1e-11
+    assert rel_err(Kvec.cpu().numpy(), (((x1 @ C) * x1).sum(1) + 0.49).numpy()) < 1e-12
+
+
 @pytest.mark.parametrize("name", ["closure_dense_n8", "closure_local_n12", "closure_rankdef_n10", "closure_c1_dense"])
 def test_moments_estep_fparams_against_reference(nat, name):
     import oracle.spatial_gp_oracle as orc
