@@ -43,6 +43,7 @@ SIGNATURES = {
     "sgp_mask_host": (_i, [_dp, _i, C.POINTER(C.c_uint8), _ip]),
     "sgp_localker": (_i, [_p, _dp, _i, _p, _l, _p, _l, _p]),
     "sgp_acosker": (_i, [_p, _p, _l, _l, _p, _l, _l, _i, _p, _l, _d, _p, _l, _i, _p]),
+    "sgp_acosker_kvec": (_i, [_p, _p, _l, _l, _p, _l, _l, _i, _p, _l, _d, _p, _l, _i, _p, _p]),
     "sgp_acosker_diag": (_i, [_p, _p, _l, _l, _i, _p, _l, _d, _p, _p]),
     "sgp_lambda_moments": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _p, _p, _l, _p, _p, _p]),
     "sgp_fparam_eval": (_i, [_p, _p, _p, _p, _l, _d, _d, _p, _dp, _p]),

@@ -1107,8 +1107,12 @@ bool aligned2(const void* p, long ld) { return ((uintptr_t)p % 16 == 0) && (ld %
 
 extern "C" {
 
-int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double* x2, long n2, long ld2, int p,
-                const double* C, long ldc, double sigma_0, double* K, long ldk, int symm, void* stream) {
+}  // extern "C"
+
+// K (and, when Kvec_out is given, Kvec_i = x1_i^T C x1_i + sigma_0^2, which the kernel needs anyway as X1^2)
+static int acosker_impl(sgp_handle* h, const double* x1, long n1, long ld1, const double* x2, long n2, long ld2, int p,
+                        const double* C, long ldc, double sigma_0, double* K, long ldk, int symm, double* Kvec_out,
+                        void* stream) {
   if (!h || !x1 || !x2 || !C || !K) return fail(h, SGP_E_ARG, "sgp_acosker: null argument");
   if (symm && n1 != n2) return fail(h, SGP_E_ARG, "sgp_acosker: symmetrize needs n1 == n2");
   int rc = ensure_ready(h); if (rc) return rc;
@@ -1181,6 +1185,7 @@ int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double
       const OzMoments mom{xs, lds, part, ldpart};                           // rowdot(x1 C, x1)  (U:978)
       CU(oz_gemm(xq, xe, ns, cq, ce, p, p, oz_ldk(p), ozS, Z1, ldp, 1, 0, 0, st, &mom));
       norms_finalize(part, ldpart, ng16, ns, s02, s1, X1, st);
+      if (Kvec_out) CU(cudaMemcpyAsync(Kvec_out + i0, s1, sizeof(double) * ns, cudaMemcpyDeviceToDevice, st));
       CU(oz_gemm(xq, xe, ns, wq, we, (int)n2, p, oz_ldk(p), ozS, Kw, ldn2, 1, 0, 0, st));
       acos_forward(Kw, cosw, ldn2, ns, (int)n2, X1, X2, s02, st);           // U:982-990
       if (symm) copy_mat(Kw, ldn2, (int)ns, (int)n2, Kfull + i0 * ldn2, ldn2, st);
@@ -1192,6 +1197,7 @@ int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double
     g.aux = xs; g.ldaux = lds; g.part1 = part; g.ldpart = ldpart;
     CU(gemm(st, 0, 1, kRowdot, false, 1, g));
     norms_finalize(part, ldpart, ntp, ns, s02, s1, X1, st);
+    if (Kvec_out) CU(cudaMemcpyAsync(Kvec_out + i0, s1, sizeof(double) * ns, cudaMemcpyDeviceToDevice, st));
     GemmArgs a{};  // K slab into scratch (ld = ldn2, shared with the cosine scratch), then out
     a.A = Z1; a.lda = ldp; a.B = x2c; a.ldb = ld2c; a.C = Kw; a.ldc = ldn2; a.M = (int)ns; a.N = (int)n2; a.K = p;
     a.rowvec = X1; a.colvec = X2; a.C2 = cosw; a.s02 = s02;
@@ -1202,6 +1208,20 @@ int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double
   if (symm) symmetrize(Kfull, ldn2, (int)n1, K, ldk, st);   // U:1024-1025
   CU(cudaGetLastError());
   return SGP_OK;
+}
+
+extern "C" {
+
+int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double* x2, long n2, long ld2, int p,
+                const double* C, long ldc, double sigma_0, double* K, long ldk, int symm, void* stream) {
+  return acosker_impl(h, x1, n1, ld1, x2, n2, ld2, p, C, ldc, sigma_0, K, ldk, symm, nullptr, stream);
+}
+
+int sgp_acosker_kvec(sgp_handle* h, const double* x1, long n1, long ld1, const double* x2, long n2, long ld2, int p,
+                     const double* C, long ldc, double sigma_0, double* K, long ldk, int symm, double* Kvec,
+                     void* stream) {
+  if (!Kvec) return fail(h, SGP_E_ARG, "sgp_acosker_kvec: null argument");
+  return acosker_impl(h, x1, n1, ld1, x2, n2, ld2, p, C, ldc, sigma_0, K, ldk, symm, Kvec, stream);
 }
 
 int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, const double* C, long ldc,

@@ -100,6 +100,20 @@ def acosker(sigma_0: float, x1: torch.Tensor, x2: torch.Tensor, Cm: torch.Tensor
     return K
 
 
+def acosker_kvec(sigma_0: float, x1: torch.Tensor, x2: torch.Tensor, Cm: torch.Tensor, symmetrize: bool):
+    """(K, Kvec) in one pass over x1: acosker(x1, x2) and acosker(x1, diag=True) share the x1 C product."""
+    _need_cuda(x1, x2, Cm)
+    x1, x2, Cm = _c(x1), _c(x2), _c(Cm)
+    n1, p = x1.shape
+    n2 = x2.shape[0]
+    K = torch.empty((n1, n2), dtype=torch.float64, device=x1.device)
+    Kvec = torch.empty((n1,), dtype=torch.float64, device=x1.device)
+    h = _h(x1)
+    h.check(lib.sgp_acosker_kvec(h.ptr, _ptr(x1), n1, _ld(x1), _ptr(x2), n2, _ld(x2), int(p), _ptr(Cm), _ld(Cm),
+                                 float(sigma_0), _ptr(K), n2, 1 if symmetrize else 0, _ptr(Kvec), _stream(x1.device)))
+    return K, Kvec
+
+
 def acosker_diag(sigma_0: float, x1: torch.Tensor, Cm: torch.Tensor) -> torch.Tensor:
     _need_cuda(x1, Cm)
     x1, Cm = _c(x1), _c(Cm)

@@ -570,6 +570,10 @@ def _kernels_at(theta, lo, hi, n_px_side, x, xtilde, kernfun, same):
     C, mask = localker(theta=theta, theta_higher_lims=hi, theta_lower_lims=lo, n_px_side=n_px_side, grad=False)
     xm, um = x[:, mask], xtilde[:, mask]
     K_tilde = kernfun(theta, um, um, C=C, dC=None, diag=False)
+    if kernfun is acosker and not same:
+        # K and Kvec share the x C product (sgp_acosker_kvec): one pass over the images instead of two
+        K, Kvec = native.acosker_kvec(_fl(theta['sigma_0']), xm, um, C, symmetrize=(xm.shape[0] == um.shape[0]))
+        return C, mask, K_tilde, K, Kvec
     K = K_tilde if same else kernfun(theta, xm, um, C=C, dC=None, diag=False)
     Kvec = kernfun(theta, xm, x2=None, C=C, dC=None, diag=True)
     return C, mask, K_tilde, K, Kvec

@@ -89,6 +89,11 @@ SGP_API int sgp_localker(sgp_handle* h, const double* theta_host, int n_px, doub
  * K = (K + K^T)/2 (the reference does so whenever n1 == n2).                                                   */
 SGP_API int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, const double* x2, long n2, long ld2, int p,
                 const double* C, long ldc, double sigma_0, double* K, long ldk, int symmetrize, void* stream);
+/* K as above plus Kvec_i = x1_i^T C x1_i + sigma_0^2 (utils.py:1029) in the same pass: the kernel forms it anyway as
+ * X1^2 (utils.py:978), so varGP's "K, then Kvec" pair (utils.py:1677-1680, 1804-1806) costs one x1 C product.      */
+SGP_API int sgp_acosker_kvec(sgp_handle* h, const double* x1, long n1, long ld1, const double* x2, long n2, long ld2,
+                     int p, const double* C, long ldc, double sigma_0, double* K, long ldk, int symmetrize,
+                     double* Kvec, void* stream);
 /* ---- a3: acosker(theta, x1, x2=None, C, diag=True)  utils.py:1027-1030 : Kvec_i = x_i^T C x_i + sigma_0^2     */
 SGP_API int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, const double* C, long ldc,
                      double sigma_0, double* Kvec, void* stream);

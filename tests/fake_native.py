@@ -41,6 +41,10 @@ def acosker(sigma_0, x1, x2, Cm, symmetrize):
     return K
 
 
+def acosker_kvec(sigma_0, x1, x2, Cm, symmetrize):
+    return acosker(sigma_0, x1, x2, Cm, symmetrize), acosker_diag(sigma_0, x1, Cm)
+
+
 def acosker_diag(sigma_0, x1, Cm):
     return ((x1 @ Cm) * x1).sum(1) + sigma_0 * sigma_0
 

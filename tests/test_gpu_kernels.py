@@ -141,6 +141,8 @@ def test_acosker_many_rows_odd_leading_dimension(nat):
     Kvec = nat.acosker_diag(0.7, x1.to(dev()), C.to(dev()))
     assert rel_err(K.cpu().numpy(), orc.arccos_kernel({"sigma_0": 0.7}, x1, x2, C).numpy()) < 1e-11
     assert rel_err(Kvec.cpu().numpy(), (((x1 @ C) * x1).sum(1) + 0.49).numpy()) < 1e-12
+    K2, Kvec2 = nat.acosker_kvec(0.7, x1.to(dev()), x2.to(dev()), C.to(dev()), False)
+    assert torch.equal(K2, K) and rel_err(Kvec2.cpu().numpy(), Kvec.cpu().numpy()) < 1e-14
 
 
 @pytest.mark.parametrize("n1,n2,p,sym_c", [(6000, 70, 100, True), (9000, 96, 131, False)])
@@ -159,6 +161,8 @@ def test_acosker_image_sized_rows_int8_path(nat, n1, n2, p, sym_c):
     Kvec = nat.acosker_diag(0.7, x1.to(dev()), C.to(dev()))
     assert rel_err(K.cpu().numpy(), orc.arccos_kernel({"sigma_0": 0.7}, x1, x2, C).numpy()) < 1e-11
     assert rel_err(Kvec.cpu().numpy(), (((x1 @ C) * x1).sum(1) + 0.49).numpy()) < 1e-12
+    K2, Kvec2 = nat.acosker_kvec(0.7, x1.to(dev()), x2.to(dev()), C.to(dev()), False)
+    assert torch.equal(K2, K) and rel_err(Kvec2.cpu().numpy(), Kvec.cpu().numpy()) < 1e-14
 
 
 @pytest.mark.parametrize("name", ["closure_dense_n8", "closure_local_n12", "closure_rankdef_n10", "closure_c1_dense"])
