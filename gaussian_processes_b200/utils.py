@@ -746,19 +746,25 @@ def varGP(x, r, **kwargs):
             # ---- E-step (U:1861-1937) ---------------------------------------------------------------------
             t0 = time.time()
             if nEstep > 0:
+                # lambda_moments only looks at the images when Kvec is missing (U:1093-1094): no per-step gather
+                xm_e = x[:, mask] if Kvec is None else None
                 for i_estep in range(nEstep):
                     if i_estep == 0 and nMstep > 0:
-                        lambda_m, lambda_var = lambda_moments(x[:, mask], K_tilde_b, KKtilde_inv_b, Kvec, K_b, C, m_b,
+                        lambda_m, lambda_var = lambda_moments(xm_e, K_tilde_b, KKtilde_inv_b, Kvec, K_b, C, m_b,
                                                               V_b, theta, kernfun=kernfun)
                         f_params['lambda0'] = lambda0_given_logA(f_params['logA'], r, lambda_m, lambda_var)
                     f_mean = mean_f_given_lambda_moments(f_params, lambda_m, lambda_var)
                     m_b, V_b = Estep(r=r, KKtilde_inv=KKtilde_inv_b, m=m_b, f_params=f_params, f_mean=f_mean,
                                      K_tilde=K_tilde_b, K_tilde_inv=K_tilde_inv_b, update_V_inv=False, alpha=1)
-                    f_mean, lambda_m, lambda_var = mean_f(f_params=f_params, calculate_moments=True, x=x[:, mask],
+                    f_mean, lambda_m, lambda_var = mean_f(f_params=f_params, calculate_moments=True, x=xm_e,
                                                           K_tilde=K_tilde_b, KKtilde_inv=KKtilde_inv_b, Kvec=Kvec,
                                                           K=K_b, C=C, m=m_b, V=V_b, theta=theta, kernfun=kernfun)
                     t1 = time.time()
                     f_params['lambda0'] = lambda0_given_logA(f_params['logA'], r, lambda_m, lambda_var)
+                    # the optimiser's own arithmetic is a handful of scalar operations per step: it runs on a host
+                    # copy of logA (same IEEE operations, no device launches / read-backs), written back afterwards
+                    logA_dev = f_params['logA']
+                    f_params['logA'] = logA_dev.detach().cpu().clone()
                     optimizer_f_params = torch.optim.LBFGS([f_params['logA']], lr=0.1, max_iter=nFparamstep,
                                                            tolerance_change=1.e-9, tolerance_grad=1.e-7,
                                                            history_size=nFparamstep, line_search_fn='strong_wolfe')
@@ -781,7 +787,7 @@ def varGP(x, r, **kwargs):
                             res["dlogA"] = A_now * (res["r_lam"] - res["lamf"])
                             res["lambda0_closed"] = math.log(res["sum_r"]) - math.log(res["sum_exp"])
                         f_params['logA'].grad = _scalar(-res["dlogA"], like=f_params['logA'])
-                        f_params['lambda0'] = _scalar(res["lambda0_closed"], like=r)
+                        f_params['lambda0'] = res["lambda0_closed"]          # float until the optimiser returns
                         if res["nan"] > 0:
                             raise ValueError(f'Nan in f_mean during f param update in Estep, closure has been called '
                                              f'{calls[0]} times in estep {i_estep} iteration. Try substituting them '
@@ -789,9 +795,15 @@ def varGP(x, r, **kwargs):
                         if _SHARD is None and res["sum_f"] / lambda_m.shape[0] > 100:
                             print(f'f_mean mean is {res["sum_f"] / lambda_m.shape[0]} at i_step {i_estep} iteration '
                                   f'{iteration} at closure call {calls[0]}')
-                        return _scalar(-res["loglik"], like=r)
+                        return _scalar(-res["loglik"], like=f_params['logA'])
 
-                    optimizer_f_params.step(closure_f_params)
+                    try:
+                        optimizer_f_params.step(closure_f_params)
+                    finally:
+                        logA_dev.data.copy_(f_params['logA'])
+                        logA_dev.grad = (f_params['logA'].grad.to(logA_dev.device)
+                                         if f_params['logA'].grad is not None else None)
+                        f_params['logA'] = logA_dev
                     f_params['lambda0'] = lambda0_given_logA(f_params['logA'], r, lambda_m, lambda_var)
                     time_f_params_total += time.time() - t1
             else:
