@@ -169,6 +169,22 @@ __device__ __forceinline__ double pow2d(int e) {   // 2^e for -1022 <= e <= 1023
   return __longlong_as_double((long long)(1023 + e) << 52);
 }
 
+// x * 2^k, exact; the plain multiply whenever 2^k is a normal number (always, except for operands of denormal scale)
+__device__ __forceinline__ double scale_pow2(double x, int k) {
+  return (k >= -1000 && k <= 1000) ? x * pow2d(k) : scalbn(x, k);
+}
+
+// One base-128 digit of the running remainder w (|w| <= 2^(6-7s) on entry): adding 1.5 * 2^(52-7s) rounds w to the
+// nearest multiple of 2^(-7s) (ties to even) and leaves that multiple, as a two's-complement integer, in the low
+// mantissa bits; the remainder update is exact.  Three fp64 adds per digit, no float<->int conversion instructions.
+template <int s>
+__device__ __forceinline__ uint32_t take_digit(double& w) {
+  const double magic = __longlong_as_double((long long)(1023 + 52 - 7 * s) << 52) * 1.5;
+  const double u = w + magic;
+  w -= (u - magic);
+  return (uint32_t)__double2loint(u) & 0xffu;
+}
+
 __global__ void __launch_bounds__(kOzThreads, 1)
 oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const OzArgs a) {
   extern __shared__ uint8_t oz_smem_raw[];
@@ -389,20 +405,20 @@ oz_slice_rows_kernel(const double* __restrict__ X, long ldx, long rows, int cols
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int c = 4 * g + j;
-        t[j] = c < cols ? scalbn(x[c], 6 - e) : 0.0;
+        t[j] = c < cols ? scale_pow2(x[c], 6 - e) : 0.0;
       }
-      for (int s = 0; s < S; ++s) {
-        uint32_t w = 0;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const double d = rint(t[j]);
-          t[j] = (t[j] - d) * 128.0;
-          w |= ((uint32_t)(__double2int_rn(d)) & 0xffu) << (8 * j);
-        }
-        // pair s/2, row r, k-block (4g)/64: [slice 2j: 64 B][slice 2j+1: 64 B]
-        const int k = 4 * g;
-        *reinterpret_cast<uint32_t*>(q + (s >> 1) * pair_stride + r * ldk + (k >> 6) * 128 + (s & 1) * 64 + (k & 63)) = w;
-      }
+      // pair s/2, row r, k-block (4g)/64: [slice 2j: 64 B][slice 2j+1: 64 B]
+      const int k = 4 * g;
+      int8_t* o = q + r * ldk + (k >> 6) * 128 + (k & 63);
+      auto put = [&](int sl, uint32_t w) {
+        *reinterpret_cast<uint32_t*>(o + (sl >> 1) * pair_stride + (sl & 1) * 64) = w;
+      };
+#define SGP_OZ_DIGITS4(sl)                                                                                     \
+      if (sl < S) put(sl, take_digit<sl>(t[0]) | (take_digit<sl>(t[1]) << 8) | (take_digit<sl>(t[2]) << 16) |   \
+                              (take_digit<sl>(t[3]) << 24));
+      SGP_OZ_DIGITS4(0) SGP_OZ_DIGITS4(1) SGP_OZ_DIGITS4(2) SGP_OZ_DIGITS4(3)
+      SGP_OZ_DIGITS4(4) SGP_OZ_DIGITS4(5) SGP_OZ_DIGITS4(6) SGP_OZ_DIGITS4(7)
+#undef SGP_OZ_DIGITS4
     }
   }
 }
@@ -441,29 +457,40 @@ __global__ void __launch_bounds__(256)
 oz_slice_cols_kernel(const double* __restrict__ X, long ldx, long rows, int cols, int S, int8_t* __restrict__ q,
                      int ldk, long pair_stride, const int* __restrict__ exps, const double* __restrict__ rowsq) {
   __shared__ double tile[64][65];
-  const long r0 = (long)blockIdx.x * 64;
-  const int c0 = blockIdx.y * 64;
-  for (int e = threadIdx.x; e < 64 * 64; e += 256) {
-    const int i = e >> 6, c = e & 63;
-    tile[i][c] = (r0 + i < rows && c0 + c < cols) ? X[(r0 + i) * ldx + c0 + c] * (rowsq ? sqrt(fabs(rowsq[r0 + i])) : 1.0) : 0.0;
-  }
-  __syncthreads();
+  __shared__ double rsc[64];
+  // column tiles vary fastest across the grid: the blocks resident together read whole rows of X between them
+  const int c0 = blockIdx.x * 64;
   const int c = threadIdx.x & 63, quarter = threadIdx.x >> 6;
-  if (c0 + c >= cols) return;
-  const int e = exps[c0 + c];
-  double t[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) t[j] = scalbn(tile[16 * quarter + j][c], 6 - e);
-  int8_t* orow = q + (long)(c0 + c) * ldk + (long)blockIdx.x * 128 + quarter * 16;
-  for (int s = 0; s < S; ++s) {
-    uint32_t w[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const double d = rint(t[j]);
-      t[j] = (t[j] - d) * 128.0;
-      w[j >> 2] |= ((uint32_t)(__double2int_rn(d)) & 0xffu) << (8 * (j & 3));
+  const bool live = c0 + c < cols;
+  const int e = live ? exps[c0 + c] : 0;
+  for (long rt = blockIdx.y; rt * 64 < rows; rt += gridDim.y) {
+    const long r0 = rt * 64;
+    if (threadIdx.x < 64) rsc[threadIdx.x] = (rowsq && r0 + threadIdx.x < rows) ? sqrt(fabs(rowsq[r0 + threadIdx.x])) : 1.0;
+    __syncthreads();
+    for (int el = threadIdx.x; el < 64 * 64; el += 256) {
+      const int i = el >> 6, cc = el & 63;
+      tile[i][cc] = (r0 + i < rows && c0 + cc < cols) ? X[(r0 + i) * ldx + c0 + cc] * rsc[i] : 0.0;
     }
-    *reinterpret_cast<uint4*>(orow + (s >> 1) * pair_stride + (s & 1) * 64) = make_uint4(w[0], w[1], w[2], w[3]);
+    __syncthreads();
+    if (live) {
+      double t[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) t[j] = scale_pow2(tile[16 * quarter + j][c], 6 - e);
+      int8_t* orow = q + (long)(c0 + c) * ldk + rt * 128 + quarter * 16;
+#define SGP_OZ_DIGITS16(sl)                                                                                    \
+      if (sl < S) {                                                                                            \
+        uint32_t w[4];                                                                                         \
+        _Pragma("unroll") for (int j4 = 0; j4 < 4; ++j4)                                                      \
+          w[j4] = take_digit<sl>(t[4 * j4]) | (take_digit<sl>(t[4 * j4 + 1]) << 8) |                           \
+                  (take_digit<sl>(t[4 * j4 + 2]) << 16) | (take_digit<sl>(t[4 * j4 + 3]) << 24);               \
+        *reinterpret_cast<uint4*>(orow + (sl >> 1) * pair_stride + (sl & 1) * 64) =                            \
+            make_uint4(w[0], w[1], w[2], w[3]);                                                                \
+      }
+      SGP_OZ_DIGITS16(0) SGP_OZ_DIGITS16(1) SGP_OZ_DIGITS16(2) SGP_OZ_DIGITS16(3)
+      SGP_OZ_DIGITS16(4) SGP_OZ_DIGITS16(5) SGP_OZ_DIGITS16(6) SGP_OZ_DIGITS16(7)
+#undef SGP_OZ_DIGITS16
+    }
+    __syncthreads();
   }
 }
 
@@ -529,7 +556,7 @@ cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S,
   note_launch(3);
   oz_col_absmax_kernel<<<dim3((cols + 31) / 32, gy), 256, 0, st>>>(X, ldx, rows, cols, rowsq, mx);
   oz_exps_from_max_kernel<<<(cols + 255) / 256, 256, 0, st>>>(mx, cols, exps);
-  oz_slice_cols_kernel<<<dim3((unsigned)((rows + 63) / 64), (cols + 63) / 64), 256, 0, st>>>(
+  oz_slice_cols_kernel<<<dim3((cols + 63) / 64, (unsigned)std::min<long>((rows + 63) / 64, 65535)), 256, 0, st>>>(
       X, ldx, rows, cols, S, q, ldk, (long)cols * ldk, exps, rowsq);
   return cudaGetLastError();
 }
