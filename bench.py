@@ -290,6 +290,51 @@ def secondary_metrics(native, dev, X, r, xt, Cm, mask, theta, B, ev_keep, m_b, V
                          "logmarginal_track": [float(v) for v in lt]}
     except Exception as e:  # pragma: no cover
         out["em_fit"] = {"error": repr(e)}
+    # the same evaluation at the other two operating points of SURVEY 8(d): localised theta (generate_theta defaults,
+    # p = 820 of 1600 pixels inside the mask: gathered images, separable forms + int8 products) and the notebook theta
+    # (p = 68: dense-C path, m-space products on the int8 engine); fresh subspace / variational state at each theta
+    n_side = int(round(math.sqrt(X.shape[1])))
+    out["theta_variants"] = {}
+    for name, th in (("localised", synth.theta_localised(n_side)), ("notebook", dict(synth.THETA_NOTEBOOK))):
+        try:
+            Cv, mv = native.localker(th, n_side, dev)
+            uv = xt[:, mv].contiguous()
+            Ktv = native.acosker(th["sigma_0"], uv, uv, Cv, True)
+            evv, evecv = torch.linalg.eigh(Ktv, UPLO="L")
+            kp = evv > max(float(evv.max()) * 1e-4, 1e-4)
+            Bv = evecv[:, kp].contiguous()
+            mbv, Vbv = synth.make_variational_state(torch.diag(evv[kp]).cpu(), CFG)
+            mbv, Vbv = mbv.to(dev), Vbv.to(dev)
+            res = {}
+            tv = timed(lambda: res.update(native.elbo_grad(X, r, xt, n_side, th, Bv, mbv, Vbv, logA, lambda0)),
+                       reps=5, warm=2)
+            out["theta_variants"][name] = {"p": int(mv.sum()), "q": int(Bv.shape[1]), "ms": tv * 1e3,
+                                           "evals_per_sec": 1.0 / tv, "flags": int(res.get("flags", -1)),
+                                           "loglik": float(res.get("loglik", float("nan")))}
+            del Cv, Ktv, evecv, Bv
+        except Exception as e:  # pragma: no cover
+            out["theta_variants"][name] = {"error": repr(e)}
+    # precision / throughput knob of the int8-slice products: S digits of 7 bits per fp64 operand (S = 8: DGEMM error
+    # class, the default and the headline; S = 4: 27 bits, above fp32's 24).  Error = against the S = 8 result.
+    try:
+        sweep = {}
+        ref8 = native.elbo_grad(X, r, xt, n_side, theta, B, m_b, V_b, logA, lambda0)
+        g8 = torch.tensor([ref8["grad"][k] for k in KEYS], dtype=torch.float64)
+        for S_ in (4, 5, 6, 7):
+            native.set_option(dev.index or 0, "i8_slices", S_)
+            res = {}
+            ts = timed(lambda: res.update(native.elbo_grad(X, r, xt, n_side, theta, B, m_b, V_b, logA, lambda0)),
+                       reps=3, warm=2)
+            gs = torch.tensor([res["grad"][k] for k in KEYS], dtype=torch.float64)
+            sweep[str(S_)] = {"ms": ts * 1e3, "evals_per_sec": 1.0 / ts,
+                              "loglik_rel_err": abs(res["loglik"] - ref8["loglik"]) / abs(ref8["loglik"]),
+                              "grad_rel_err": float((gs - g8).abs().max() / g8.abs().max())}
+        out["i8_slices_sweep"] = sweep
+    except Exception as e:  # pragma: no cover
+        out["i8_slices_sweep"] = {"error": repr(e)}
+    finally:
+        native.set_option(dev.index or 0, "i8_slices", -1)
+        native.invalidate_cache(dev.index or 0)
     out["estep_iteration"] = {"N": N, "q": q, "ms": t * 1e3, "iters_per_sec": 1.0 / t,
                               "contract_tflops": flops / t / 1e12,
                               "what": "rate, g/G (one pass over a), (K^-1+G)^-1 by blocked Cholesky, new moments, lambda0"}

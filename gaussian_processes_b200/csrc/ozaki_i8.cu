@@ -450,6 +450,28 @@ __global__ void oz_exps_from_max_kernel(const unsigned long long* __restrict__ m
   exps[i] = (m > 0.0 && m < 1.0e300) ? ilogb(m) + 1 : 0;
 }
 
+// Column scales from per-block column maxima (written by the pass that produced the matrix): 32 columns x 8 block
+// groups per CTA.  squared: the maxima are of the squared entries; the 1e-10 margin keeps 2^e above the true maximum
+// whatever the rounding of the square / square root (a scale one bit too large costs one bit of the last digit).
+__global__ void __launch_bounds__(256)
+oz_exps_from_colmax_kernel(const double* __restrict__ part, int nblk, int cols, long ld, int squared,
+                           int* __restrict__ exps) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int g = threadIdx.x >> 5;
+  __shared__ double red[8][33];
+  double m = 0.0;
+  if (c < cols)
+    for (int b = g; b < nblk; b += 8) m = fmax(m, part[(long)b * ld + c]);
+  red[g][threadIdx.x & 31] = m;
+  __syncthreads();
+  if (g == 0 && c < cols) {
+#pragma unroll
+    for (int i = 1; i < 8; ++i) m = fmax(m, red[i][threadIdx.x]);
+    if (squared) m = sqrt(m) * (1.0 + 1.0e-10);
+    exps[c] = (m > 0.0 && m < 1.0e300) ? ilogb(m) + 1 : 0;
+  }
+}
+
 // Slices of X^T: output row = column c of X (rows x cols), K runs over the rows of X.  One block transposes a
 // 64 (rows of X) x 64 (columns) tile through shared memory; thread (quarter, c) turns 16 consecutive k of column c
 // into one 16-byte store per slice.
@@ -547,18 +569,27 @@ cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S,
 // Slices of X^T for a contraction over the ROWS of X (rows x cols): q is [pairs][cols][oz_ldk(rows)], exps[cols].
 // mx: scratch of `cols` 8-byte words.
 cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
-                          unsigned long long* mx, cudaStream_t st, const double* rowsq) {
+                          unsigned long long* mx, cudaStream_t st, const double* rowsq, bool exps_ready) {
   if (rows <= 0 || cols <= 0) return cudaSuccess;
   if (S < 1 || S > kOzMaxS || rows > (1L << 30) || ldk != oz_ldk((int)rows)) return cudaErrorInvalidValue;
-  cudaError_t e = cudaMemsetAsync(mx, 0, sizeof(unsigned long long) * cols, st);
-  if (e != cudaSuccess) return e;
-  const int gy = (int)std::min<long>((rows + 63) / 64, 148L * 4 / ((cols + 31) / 32) + 1);
-  note_launch(3);
-  oz_col_absmax_kernel<<<dim3((cols + 31) / 32, gy), 256, 0, st>>>(X, ldx, rows, cols, rowsq, mx);
-  oz_exps_from_max_kernel<<<(cols + 255) / 256, 256, 0, st>>>(mx, cols, exps);
+  if (!exps_ready) {
+    cudaError_t e = cudaMemsetAsync(mx, 0, sizeof(unsigned long long) * cols, st);
+    if (e != cudaSuccess) return e;
+    const int gy = (int)std::min<long>((rows + 63) / 64, 148L * 4 / ((cols + 31) / 32) + 1);
+    note_launch(2);
+    oz_col_absmax_kernel<<<dim3((cols + 31) / 32, gy), 256, 0, st>>>(X, ldx, rows, cols, rowsq, mx);
+    oz_exps_from_max_kernel<<<(cols + 255) / 256, 256, 0, st>>>(mx, cols, exps);
+  }
+  note_launch();
   oz_slice_cols_kernel<<<dim3((cols + 63) / 64, (unsigned)std::min<long>((rows + 63) / 64, 65535)), 256, 0, st>>>(
       X, ldx, rows, cols, S, q, ldk, (long)cols * ldk, exps, rowsq);
   return cudaGetLastError();
+}
+
+void oz_exps_from_colmax(const double* part, int nblk, int cols, long ld, int squared, int* exps, cudaStream_t st) {
+  if (cols <= 0) return;
+  note_launch();
+  oz_exps_from_colmax_kernel<<<(cols + 31) / 32, 256, 0, st>>>(part, nblk, cols, ld, squared, exps);
 }
 
 // C (M x N, ld = ldc) = A * B^T from the int8 slices of A (M rows) and B (N rows); K bytes per row, pitch ldk.

@@ -522,14 +522,17 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   if (h->path == 1) use_sep = false;
   if (h->path == 2) use_sep = sep_quad_supported(n);
   // int8-slice tensor-core products for K_lin = X (UC)^T and D = X^T R (separable path only)
-  int ozS = 0;
-  if (use_sep && h->i8_slices != 0) ozS = h->i8_slices > 0 ? h->i8_slices : (slab >= 4096 && m >= 64 ? 8 : 0);
+  // ozM: the two m-space products (T = K Mfull^T, Sig2 = K^T diag(v) K) -- on either path;  ozS: the two products with the
+  // images (separable path only: the dense path's X C / X^T Y keep the DMMA GEMM with its fused epilogues)
+  int ozM = 0;
+  if (h->i8_slices != 0) ozM = h->i8_slices > 0 ? h->i8_slices : (slab >= 4096 && m >= 64 ? 8 : 0);
+  const int ozS = use_sep ? ozM : 0;
   const int ldkP = oz_ldk(p), ldkN = oz_ldk((int)slab);
   const bool chain_overlap = use_sep && h->overlap != 0;
   const bool tail_overlap = chain_overlap && ozS > 0;
-  const int oz_pairs = (ozS + 1) / 2;
+  const int oz_pairs = (ozM + 1) / 2;
   const int nzO = ozS ? oz_split(p, m, (int)std::min(slab, N), ozS) : 1;
-  const int nzK = ozS ? oz_split(m, m, (int)std::min(slab, N), ozS, 1) : 1;
+  const int nzK = ozM ? oz_split(m, m, (int)std::min(slab, N), ozM, 1) : 1;
   std::vector<int> off; std::vector<double> alpha;
   if (use_sep) {
     const int ldq_sep = sep_quad_ld(n);
@@ -575,16 +578,16 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   for (int i = 0; i < 6; ++i) acc(slab);                              // s, X1, u, v, w (+1)
   for (int i = 0; i < 3; ++i) acc(N);                                 // lam_m, lam_var, f (when not supplied)
   const int ng16 = (m + 15) / 16;                                     // 16-column groups of the int8 moments epilogue
-  acc((size_t)std::max(std::max(ntp, ntm), ozS ? ng16 : 0) * ldpartN * 3);   // partN, pm1, pm2
-  acc((size_t)nblk_mom * 4); acc((size_t)nblk_bwd * ldm * 2); acc(nblk_bwd);
+  acc((size_t)std::max(std::max(ntp, ntm), ozM ? ng16 : 0) * ldpartN * 3);   // partN, pm1, pm2
+  acc((size_t)nblk_mom * 4); acc((size_t)nblk_bwd * ldm * 4); acc(nblk_bwd);
   acc((size_t)nblk_bwdU * ldm); acc(nblk_bwdU);
   acc((size_t)p * ldp);                                               // GCU
   acc((size_t)p * 5);                                                 // gpart
   if (streaming) { acc((size_t)slab * ldp); }                         // gathered slab when streaming from host
-  if (ozS) {                                                          // slices of UC and of R^T, exponents, col-max scratch
-    acc(oz_slice_bytes(m, p, ozS) / 8 + 16); acc((size_t)oz_pairs * m * ldkN / 8 + 16); acc(m); acc(m);
+  if (ozM) {                                                          // slices of UC and of R^T, exponents, col-max scratch
+    acc(oz_slice_bytes(m, p, ozM) / 8 + 16); acc((size_t)oz_pairs * m * ldkN / 8 + 16); acc(m); acc(m);
     acc((size_t)std::max(p, m) + 8);
-    acc(oz_slice_bytes(slab, m, ozS) / 8 + 16); acc(oz_slice_bytes(m, m, ozS) / 8 + 16); acc(slab / 2 + 8); acc(m);   // K, Mfull slices
+    acc(oz_slice_bytes(slab, m, ozM) / 8 + 16); acc(oz_slice_bytes(m, m, ozM) / 8 + 16); acc(slab / 2 + 8); acc(m);   // K, Mfull slices
   }
   need += 4096;
   CU(h->arena.reserve(need));
@@ -623,11 +626,12 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* lam_m = in.lam_m ? in.lam_m : ar.take<double>(N);
   double* lam_var = in.lam_var ? in.lam_var : ar.take<double>(N);
   double* fvec = in.f ? in.f : ar.take<double>(N);
-  const int ntmax = std::max(std::max(ntp, ntm), ozS ? ng16 : 0);
+  const int ntmax = std::max(std::max(ntp, ntm), ozM ? ng16 : 0);
   double* partN = ar.take<double>((size_t)ntmax * ldpartN); double* pm1 = ar.take<double>((size_t)ntmax * ldpartN);
   double* pm2 = ar.take<double>((size_t)ntmax * ldpartN);
   double* blockpart = ar.take<double>((size_t)nblk_mom * 4);
   double* colk = ar.take<double>((size_t)nblk_bwd * ldm); double* coly = ar.take<double>((size_t)nblk_bwd * ldm);
+  double* cmaxR = ar.take<double>((size_t)nblk_bwd * ldm); double* cmaxW = ar.take<double>((size_t)nblk_bwd * ldm);
   double* sumpartR = ar.take<double>(nblk_bwd);
   double* colkU = ar.take<double>((size_t)nblk_bwdU * ldm); double* sumpartU = ar.take<double>(nblk_bwdU);
   double* GCU = ar.take<double>((size_t)p * ldp);
@@ -635,13 +639,13 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* Xslab_stream = streaming ? ar.take<double>((size_t)slab * ldp) : nullptr;
   int8_t* kq = nullptr; int8_t* mq = nullptr; int* ke = nullptr; int* me = nullptr;
   int8_t* zuq = nullptr; int8_t* rtq = nullptr; int* zue = nullptr; int* rte = nullptr; unsigned long long* ozmx = nullptr;
-  if (ozS) {
-    zuq = (int8_t*)ar.take<double>(oz_slice_bytes(m, p, ozS) / 8 + 16);
+  if (ozM) {
+    zuq = (int8_t*)ar.take<double>(oz_slice_bytes(m, p, ozM) / 8 + 16);
     rtq = (int8_t*)ar.take<double>((size_t)oz_pairs * m * ldkN / 8 + 16);
     zue = (int*)ar.take<double>(m); rte = (int*)ar.take<double>(m);
     ozmx = (unsigned long long*)ar.take<double>((size_t)std::max(p, m) + 8);
-    kq = (int8_t*)ar.take<double>(oz_slice_bytes(slab, m, ozS) / 8 + 16);
-    mq = (int8_t*)ar.take<double>(oz_slice_bytes(m, m, ozS) / 8 + 16);
+    kq = (int8_t*)ar.take<double>(oz_slice_bytes(slab, m, ozM) / 8 + 16);
+    mq = (int8_t*)ar.take<double>(oz_slice_bytes(m, m, ozM) / 8 + 16);
     ke = (int*)ar.take<double>(slab / 2 + 8); me = (int*)ar.take<double>(m);
   }
 
@@ -769,7 +773,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     CU(mm(st, 0, 1, Bw, ldq, Mg, ldq, tmq2, ldq, m, q, q));                              // B Mg
     CU(mm(st, 0, 0, tmq2, ldq, Bw, ldq, Mfull, ldm, m, m, q));                           // Mfull = B Mg B^T
     kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, qq[12], st);   // qq[12]: free until the tail
-    if (ozS) CU(oz_slice_rows(Mfull, ldm, m, m, ozS, mq, oz_ldk(m), me, st));
+    if (ozM) CU(oz_slice_rows(Mfull, ldm, m, m, ozM, mq, oz_ldk(m), me, st));
     if (chain_overlap) CU(cudaEventRecord(h->ev_chain_join, st));
     st = st_main;
   }
@@ -861,15 +865,15 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     GemmArgs g3{};
     g3.A = Ks; g3.lda = ldm; g3.B = Mfull; g3.ldb = ldm; g3.C = Ts; g3.ldc = ldm; g3.M = (int)ns; g3.N = m; g3.K = m;
     g3.aux = Ks; g3.ldaux = ldm; g3.colvec = bb; g3.part1 = pm1; g3.part2 = pm2; g3.ldpart = ldpartN;
-    if (ozS) {
-      CU(oz_slice_rows(Ks, ldm, ns, m, ozS, kq, oz_ldk(m), ke, st, bb, pm2));   // pm2 = K bb on the way
+    if (ozM) {
+      CU(oz_slice_rows(Ks, ldm, ns, m, ozM, kq, oz_ldk(m), ke, st, bb, pm2));   // pm2 = K bb on the way
       const OzMoments mom{Ks, ldm, pm1, ldpartN};
-      CU(oz_gemm(kq, ke, ns, mq, me, m, m, oz_ldk(m), ozS, Ts, ldm, 1, 0, 0, st, &mom));
+      CU(oz_gemm(kq, ke, ns, mq, me, m, m, oz_ldk(m), ozM, Ts, ldm, 1, 0, 0, st, &mom));
     } else {
       CU(gemm(st, 0, 0, kMoments, false, 1, g3));
     }
     mark(4);
-    moments_rows(s_s, pm1, pm2, ldpartN, ozS ? ng16 : ntm, ozS ? 1 : ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
+    moments_rows(s_s, pm1, pm2, ldpartN, ozM ? ng16 : ntm, ozM ? 1 : ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
                  v_s, blockpart, st);
     const int nbm = moments_rows_blocks(ns);
     sum_to_slot(blockpart + 0, nbm, 4, 1.0, h->d_scal, kSlotRLam, acc_flag, st);
@@ -877,12 +881,31 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     sum_to_slot(blockpart + 2, nbm, 4, 1.0, h->d_scal, kSlotSumR, acc_flag, st);
     sum_to_slot(blockpart + 3, nbm, 4, 1.0, h->d_scal, kSlotNaN, acc_flag, st);
     // adjoint of the arc-cosine map: R (in place over T), row weights w, column sums kappa / y
-    acos_backward(0, Ts, cos_s, Ks, ldm, ns, m, u_s, v_s, bb, X1, X2, w_s, colk, coly, ldm, sumpartR, st);
+    // ... and, for the int8-slice products that follow, the column maxima of R and of diag(sqrt(-v)) K
+    acos_backward(0, Ts, cos_s, Ks, ldm, ns, m, u_s, v_s, bb, X1, X2, w_s, colk, coly, ldm, sumpartR, st,
+                  ozM ? cmaxR : nullptr, cmaxW);
     const int nbb = acos_backward_blocks(ns);
     col_reduce(colk, nbb, m, ldm, kappa, acc_flag, st);
     col_reduce(coly, nbb, m, ldm, yv, acc_flag, st);
     sum_to_slot(sumpartR, nbb, 1, 1.0, h->d_scal, kSlotSig, 1, st);
     sum_to_slot(w_s, ns, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+    // G6: Sig2 += K^T diag(v) K
+    auto sig2_product = [&]() -> cudaError_t {
+      if (ozM) {
+        // v_i = -A^2 f_i / 2 <= 0, so K^T diag(v) K = -W^T W with W = diag(sqrt(-v)) K: ONE transposed slicing serves
+        // both operands of the int8 product; only the tiles on and below the diagonal are computed
+        const int ldk_s = oz_ldk((int)ns);
+        oz_exps_from_colmax(cmaxW, acos_backward_blocks(ns), m, ldm, 1, rte, st);
+        cudaError_t e = oz_slice_cols(Ks, ldm, ns, m, ozM, rtq, ldk_s, rte, ozmx, st, v_s, true);
+        if (e != cudaSuccess) return e;
+        return oz_gemm(rtq, rte, m, rtq, rte, m, (int)ns, ldk_s, ozM, S2part, ldm, nzK, zS2, acc_flag, st, nullptr, 0, -1.0, 1);
+      }
+      GemmArgs g6{};
+      g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
+      g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
+      g6.lower_only = 1;   // K^T diag(v) K is symmetric: only the CTA tiles on and below the diagonal are computed
+      return gemm(st, 1, 1, kStore, false, nzS2, g6);
+    };
     mark(5);
     if (use_sep) {
       // sum_i w_i x_i^T dC_k x_i from the stored quadratic forms; D += X^T R (split-K over the images of the slab)
@@ -891,19 +914,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
         sum_to_slot(wqpart + k, wq_reduce_blocks(ns), 5, 1.0, h->d_scal, kSlotGW + k, acc_flag, st);
       mark(7);
       // G6: Sig2 += K^T diag(v) K (before X^T R: the q x q tail depends on it, not on D)
-      if (ozS) {
-        // v_i = -A^2 f_i / 2 <= 0, so K^T diag(v) K = -W^T W with W = diag(sqrt(-v)) K: ONE transposed slicing serves
-        // both operands of the int8 product; only the tiles on and below the diagonal are computed
-        const int ldk_s = oz_ldk((int)ns);
-        CU(oz_slice_cols(Ks, ldm, ns, m, ozS, rtq, ldk_s, rte, ozmx, st, v_s));
-        CU(oz_gemm(rtq, rte, m, rtq, rte, m, (int)ns, ldk_s, ozS, S2part, ldm, nzK, zS2, acc_flag, st, nullptr, 0, -1.0, 1));
-      } else {
-        GemmArgs g6{};
-        g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
-        g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
-        g6.lower_only = 1;   // K^T diag(v) K is symmetric: only the CTA tiles on and below the diagonal are computed
-        CU(gemm(st, 1, 1, kStore, false, nzS2, g6));
-      }
+      CU(sig2_product());
       const bool last = i0 + ns >= N;
       if (tail_overlap && last) {
         // the q x q tail and the inducing-point backward pass start now on the chain stream; this slab's X^T R
@@ -916,7 +927,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
         // the contraction runs over the images: slices of X^T (persistent) and of R^T (this evaluation)
         const int ldk_s = oz_ldk((int)ns);
         if (oz_reslice) CU(oz_slice_cols(Xs, ldxs, ns, p, ozS, xtq_s, ldk_s, xte_s, ozmx, st));
-        CU(oz_slice_cols(Ts, ldm, ns, m, ozS, rtq, ldk_s, rte, ozmx, st));
+        oz_exps_from_colmax(cmaxR, acos_backward_blocks(ns), m, ldm, 0, rte, st);
+        CU(oz_slice_cols(Ts, ldm, ns, m, ozS, rtq, ldk_s, rte, ozmx, st, nullptr, true));
         mark(10);
         CU(oz_gemm(xtq_s, xte_s, p, rtq, rte, m, (int)ns, ldk_s, ozS, Dpart, ldm, nzO, zD, acc_flag, st, nullptr,
                    (tail_overlap && last) ? 148 - 20 : 0));
@@ -939,12 +951,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       g5.k_chunk = (int)rup((ns + nzGC - 1) / nzGC, 16); g5.zstride = zGC; g5.accumulate = acc_flag;
       CU(gemm(st, 1, 1, kStore, false, nzGC, g5));
       mark(7);
-      // G6: Sig2 += K^T diag(v) K
-      GemmArgs g6{};
-      g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
-      g6.k_chunk = (int)rup((ns + nzS2 - 1) / nzS2, 16); g6.zstride = zS2; g6.accumulate = acc_flag; g6.kscale = v_s;
-      g6.lower_only = 1;
-      CU(gemm(st, 1, 1, kStore, false, nzS2, g6));
+      CU(sig2_product());
     }
     mark(8);
     if (streaming) CU(cudaEventRecord(h->ev_used[slab_i & 1], st));
@@ -953,7 +960,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   // ---- adjoint of K_tilde_b (q x q algebra) ---------------------------------------------------------------
   cudaStream_t st_loop = st;
   if (tail_overlap) st = h->chain_stream;     // issued after the fork above; joins before the final contraction
-  slice_reduce(S2part, ozS ? oz_eff_split((int)std::min(slab, N), nzK) : nzS2, zS2, zS2, Sig2, 0, st);
+  slice_reduce(S2part, ozM ? oz_eff_split((int)std::min(slab, N), nzK) : nzS2, zS2, zS2, Sig2, 0, st);
   mirror_lower(Sig2, ldm, m, st);
   col_weights(kappa, nullptr, nullptr, X2, m, beta, st);                                 // beta_j = kappa_j / (2 X2_j)
   sum_to_slot(beta, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);

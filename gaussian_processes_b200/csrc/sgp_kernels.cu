@@ -178,7 +178,7 @@ void acos_forward(double* K, double* cosm, long ld, long n, int m, const double*
 // CM = column slots per thread (m <= 256*CM); rows are processed RU at a time with all their loads issued first,
 // so enough memory requests are in flight per SM to approach the HBM rate (the pass reads T, cos, K and writes R).
 template <int MODE, int CM>
-__global__ void __launch_bounds__(256) acos_backward_kernel(double* __restrict__ G, const double* __restrict__ cosm,
+__global__ void __launch_bounds__(256, (CM <= 4) ? 2 : 1) acos_backward_kernel(double* __restrict__ G, const double* __restrict__ cosm,
                                                             const double* __restrict__ Kmat, long ld, long n, int m,
                                                             const double* __restrict__ u, const double* __restrict__ v,
                                                             const double* __restrict__ bb,
@@ -186,16 +186,18 @@ __global__ void __launch_bounds__(256) acos_backward_kernel(double* __restrict__
                                                             const double* __restrict__ nb, double* __restrict__ rowout,
                                                             double* __restrict__ colpart_k,
                                                             double* __restrict__ colpart_y, long ldcol,
-                                                            double* __restrict__ sumpart) {
+                                                            double* __restrict__ sumpart,
+                                                            double* __restrict__ colmax_r,
+                                                            double* __restrict__ colmax_w) {
   constexpr int RU = (CM <= 2) ? 4 : (CM == 4 ? 2 : 1);
   __shared__ double rowred[8][kBwdRows];
   __shared__ double red[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const long r0 = (long)blockIdx.x * kBwdRows;
-  double ck[CM], cy[CM], bbj[CM], nbj[CM];
+  double ck[CM], cy[CM], bbj[CM], nbj[CM], mr[CM], mw[CM];
 #pragma unroll
   for (int c = 0; c < CM; ++c) {
-    ck[c] = cy[c] = 0.0;
+    ck[c] = cy[c] = mr[c] = mw[c] = 0.0;
     const int j = tid + c * 256;
     bbj[c] = (MODE == 0 && j < m) ? bb[j] : 0.0;
     nbj[c] = (j < m) ? nb[j] : 0.0;
@@ -237,7 +239,11 @@ __global__ void __launch_bounds__(256) acos_backward_kernel(double* __restrict__
         sumR += Rv;
         rho += rq * nbj[c];
         ck[c] += rq * nai[q];
-        if (MODE == 0) cy[c] += kv[q][c] * ui[q];
+        if (MODE == 0) {
+          cy[c] += kv[q][c] * ui[q];
+          mr[c] = fmax(mr[c], fabs(Rv));
+          mw[c] = fmax(mw[c], -vi[q] * kv[q][c] * kv[q][c]);
+        }
       }
       rho = warp_sum(rho);
       if (lane == 0) rowred[warp][rr0 + q] = rho;
@@ -259,6 +265,10 @@ __global__ void __launch_bounds__(256) acos_backward_kernel(double* __restrict__
     if (j < m) {
       colpart_k[(long)blockIdx.x * ldcol + j] = ck[c];
       if (MODE == 0) colpart_y[(long)blockIdx.x * ldcol + j] = cy[c];
+      if (MODE == 0 && colmax_r) {
+        colmax_r[(long)blockIdx.x * ldcol + j] = mr[c];
+        colmax_w[(long)blockIdx.x * ldcol + j] = mw[c];
+      }
     }
   }
   sumR = block_sum(sumR, red);
@@ -271,10 +281,10 @@ template <int MODE>
 static void acos_backward_launch(int nblk, double* G, const double* cosm, const double* Kmat, long ld, long n, int m,
                                  const double* u, const double* v, const double* bb, const double* na,
                                  const double* nb, double* rowout, double* colpart_k, double* colpart_y, long ldcol,
-                                 double* sumpart, cudaStream_t st) {
+                                 double* sumpart, double* colmax_r, double* colmax_w, cudaStream_t st) {
 #define SGP_BWD(CM_)                                                                                              \
   acos_backward_kernel<MODE, CM_><<<nblk, 256, 0, st>>>(G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout,        \
-                                                        colpart_k, colpart_y, ldcol, sumpart)
+                                                        colpart_k, colpart_y, ldcol, sumpart, colmax_r, colmax_w)
   note_launch();
   if (m <= 256) SGP_BWD(1);
   else if (m <= 512) SGP_BWD(2);
@@ -286,15 +296,15 @@ static void acos_backward_launch(int nblk, double* G, const double* cosm, const 
 void acos_backward(int mode, double* G, const double* cosm, const double* Kmat, long ld, long n, int m,
                    const double* u, const double* v, const double* bb, const double* na, const double* nb,
                    double* rowout, double* colpart_k, double* colpart_y, long ldcol, double* sumpart,
-                   cudaStream_t st) {
+                   cudaStream_t st, double* colmax_r, double* colmax_w) {
   if (n <= 0) return;
   const int nblk = acos_backward_blocks(n);
   if (mode == 0)
     acos_backward_launch<0>(nblk, G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout, colpart_k, colpart_y, ldcol,
-                            sumpart, st);
+                            sumpart, colmax_r, colmax_r ? colmax_w : nullptr, st);
   else
     acos_backward_launch<1>(nblk, G, cosm, Kmat, ld, n, m, u, v, bb, na, nb, rowout, colpart_k, colpart_y, ldcol,
-                            sumpart, st);
+                            sumpart, nullptr, nullptr, st);
 }
 
 // =====================================================================================================

@@ -71,7 +71,10 @@ int acos_backward_blocks(long n);
 void acos_backward(int mode, double* G, const double* cosm, const double* Kmat, long ld, long n, int m,
                    const double* u, const double* v, const double* bb, const double* na, const double* nb,
                    double* rowout, double* colpart_k, double* colpart_y, long ldcol, double* sumpart,
-                   cudaStream_t st);
+                   cudaStream_t st, double* colmax_r = nullptr, double* colmax_w = nullptr);
+// colmax_r / colmax_w (mode 0, optional; [blk][ldcol] like colpart_k): per-block column maxima of |R_ij| and of
+// -v_i K_ij^2 -- the column scales of the two transposed int8 slicings that follow (oz_exps_from_colmax), so that
+// neither needs its own pass over the slab.
 
 // out[j] (+)= sum_b part[b*ld + j]   (fixed order -> deterministic)
 void col_reduce(const double* part, int nblk, int m, long ld, double* out, int accumulate, cudaStream_t st);
@@ -176,7 +179,10 @@ cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S,
 // slices of X^T (contraction over the rows of X): q is [ceil(S/2)][cols][oz_ldk(rows)], exps[cols]; mx: cols 8-byte words
 // rowsq (optional, length rows): row r is multiplied by sqrt(|rowsq[r]|) before slicing (the sign goes into alpha)
 cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S, int8_t* q, int ldk, int* exps,
-                          unsigned long long* mx, cudaStream_t st, const double* rowsq = nullptr);
+                          unsigned long long* mx, cudaStream_t st, const double* rowsq = nullptr,
+                          bool exps_ready = false);
+// exps[j] from per-block column maxima part[b*ld + j] (squared: the maxima are of the squared entries)
+void oz_exps_from_colmax(const double* part, int nblk, int cols, long ld, int squared, int* exps, cudaStream_t st);
 // nz > 1: split-K, slice z of the k-blocks goes to C + z * zstride (oz_split picks nz; the effective count, which
 // oz_gemm never exceeds, is ceil(nkb / ceil(nkb / nz))); accumulate: C += instead of C =
 int oz_split(long M, int N, int K, int S, int lower_only = 0);
