@@ -68,6 +68,7 @@ struct sgp_handle {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   cudaStream_t chain_stream = nullptr; cudaEvent_t ev_chain_fork = nullptr, ev_chain_join = nullptr;
   int overlap = 1;          // 1 = run the q x q inducing-point chain next to the first slab's quadratic forms
+  int projected = -1;       // moments in the projected basis (K_b = K B): -1 = when q is small enough to pay, 0 = never, 1 = always
   DevBuf hx[2], hr, small;
   cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr}, ev_small = nullptr;
   // options
@@ -243,6 +244,7 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
   else if (n == "profile") h->profile = value != 0.0;
   else if (n == "path") h->path = (int)value;
   else if (n == "overlap") h->overlap = value != 0.0;
+  else if (n == "projected") h->projected = (int)value;
   else if (n == "i8_slices") {
     if (value != -1 && value != 0 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices must be -1, 0 or 2..8");
     h->i8_slices = (int)value;
@@ -527,12 +529,16 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   int ozM = 0;
   if (h->i8_slices != 0) ozM = h->i8_slices > 0 ? h->i8_slices : (slab >= 4096 && m >= 64 ? 8 : 0);
   const int ozS = use_sep ? ozM : 0;
+  // Moments in the projected basis when the kept subspace is small (q < m): K_b = K B, T_b = K_b Mg^T, T = T_b B^T and
+  // K_b^T diag(v) K_b cost 4Nmq + 3Nq^2 flops against the 3Nm^2 of K Mfull^T and K^T diag(v) K (break-even q = 0.54 m;
+  // the extra slicing passes move it down).  Same numbers up to rounding: Mfull = B Mg B^T.
+  const bool proj = ozM > 0 && h->projected != 0 && q >= 16 && (h->projected > 0 || 5 * (long)q <= 2 * (long)m);
   const int ldkP = oz_ldk(p), ldkN = oz_ldk((int)slab);
   const bool chain_overlap = use_sep && h->overlap != 0;
   const bool tail_overlap = chain_overlap && ozS > 0;
   const int oz_pairs = (ozM + 1) / 2;
   const int nzO = ozS ? oz_split(p, m, (int)std::min(slab, N), ozS) : 1;
-  const int nzK = ozM ? oz_split(m, m, (int)std::min(slab, N), ozM, 1) : 1;
+  const int nzK = ozM ? (proj ? oz_split(q, q, (int)std::min(slab, N), ozM, 1) : oz_split(m, m, (int)std::min(slab, N), ozM, 1)) : 1;
   std::vector<int> off; std::vector<double> alpha;
   if (use_sep) {
     const int ldq_sep = sep_quad_ld(n);
@@ -588,6 +594,13 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     acc(oz_slice_bytes(m, p, ozM) / 8 + 16); acc((size_t)oz_pairs * m * ldkN / 8 + 16); acc(m); acc(m);
     acc((size_t)std::max(p, m) + 8);
     acc(oz_slice_bytes(slab, m, ozM) / 8 + 16); acc(oz_slice_bytes(m, m, ozM) / 8 + 16); acc(slab / 2 + 8); acc(m);   // K, Mfull slices
+  }
+  if (proj) {                                                         // K_b, T_b and the slices of K_b, T_b, B, B^T, Mg
+    acc((size_t)slab * ldq); acc((size_t)slab * ldq);
+    acc(oz_slice_bytes(slab, q, ozM) / 8 + 16); acc(oz_slice_bytes(slab, q, ozM) / 8 + 16);
+    acc(oz_slice_bytes(m, q, ozM) / 8 + 16); acc(oz_slice_bytes(q, m, ozM) / 8 + 16); acc(oz_slice_bytes(q, q, ozM) / 8 + 16);
+    acc((size_t)(ozM + 1) / 2 * q * ldkN / 8 + 16);
+    acc(slab / 2 + 8); acc(slab / 2 + 8); acc(m); acc(q); acc(q); acc(q);
   }
   need += 4096;
   CU(h->arena.reserve(need));
@@ -647,6 +660,23 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     kq = (int8_t*)ar.take<double>(oz_slice_bytes(slab, m, ozM) / 8 + 16);
     mq = (int8_t*)ar.take<double>(oz_slice_bytes(m, m, ozM) / 8 + 16);
     ke = (int*)ar.take<double>(slab / 2 + 8); me = (int*)ar.take<double>(m);
+  }
+
+  double* Kb = nullptr; double* Tb = nullptr;
+  int8_t* kbq = nullptr; int8_t* tbq = nullptr; int8_t* brq = nullptr; int8_t* btq = nullptr; int8_t* mgq = nullptr;
+  int8_t* kbtq = nullptr; int* kbe = nullptr; int* tbe = nullptr; int* bre = nullptr; int* bte = nullptr; int* mge = nullptr;
+  int* kbte = nullptr;
+  if (proj) {
+    Kb = ar.take<double>((size_t)slab * ldq); Tb = ar.take<double>((size_t)slab * ldq);
+    kbq = (int8_t*)ar.take<double>(oz_slice_bytes(slab, q, ozM) / 8 + 16);
+    tbq = (int8_t*)ar.take<double>(oz_slice_bytes(slab, q, ozM) / 8 + 16);
+    brq = (int8_t*)ar.take<double>(oz_slice_bytes(m, q, ozM) / 8 + 16);
+    btq = (int8_t*)ar.take<double>(oz_slice_bytes(q, m, ozM) / 8 + 16);
+    mgq = (int8_t*)ar.take<double>(oz_slice_bytes(q, q, ozM) / 8 + 16);
+    kbtq = (int8_t*)ar.take<double>((size_t)(ozM + 1) / 2 * q * ldkN / 8 + 16);
+    kbe = (int*)ar.take<double>(slab / 2 + 8); tbe = (int*)ar.take<double>(slab / 2 + 8);
+    bre = (int*)ar.take<double>(m); bte = (int*)ar.take<double>(q); mge = (int*)ar.take<double>(q);
+    kbte = (int*)ar.take<double>(q);
   }
 
   double* Ktb_raw = qq[0]; double* Ktb = qq[1]; double* Lk = qq[2]; double* Linv = qq[3]; double* Kinv_raw = qq[4];
@@ -773,7 +803,11 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     CU(mm(st, 0, 1, Bw, ldq, Mg, ldq, tmq2, ldq, m, q, q));                              // B Mg
     CU(mm(st, 0, 0, tmq2, ldq, Bw, ldq, Mfull, ldm, m, m, q));                           // Mfull = B Mg B^T
     kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, qq[12], st);   // qq[12]: free until the tail
-    if (ozM) CU(oz_slice_rows(Mfull, ldm, m, m, ozM, mq, oz_ldk(m), me, st));
+    if (proj) {
+      CU(oz_slice_rows(Mg, ldq, q, q, ozM, mgq, oz_ldk(q), mge, st));                    // B operand of T_b = K_b Mg^T
+      CU(oz_slice_rows(Bw, ldq, m, q, ozM, brq, oz_ldk(q), bre, st));                    // B operand of T = T_b B^T
+      CU(oz_slice_cols(Bw, ldq, m, q, ozM, btq, oz_ldk(m), bte, ozmx, st));              // B operand of K_b = K B
+    } else if (ozM) CU(oz_slice_rows(Mfull, ldm, m, m, ozM, mq, oz_ldk(m), me, st));
     if (chain_overlap) CU(cudaEventRecord(h->ev_chain_join, st));
     st = st_main;
   }
@@ -865,7 +899,15 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     GemmArgs g3{};
     g3.A = Ks; g3.lda = ldm; g3.B = Mfull; g3.ldb = ldm; g3.C = Ts; g3.ldc = ldm; g3.M = (int)ns; g3.N = m; g3.K = m;
     g3.aux = Ks; g3.ldaux = ldm; g3.colvec = bb; g3.part1 = pm1; g3.part2 = pm2; g3.ldpart = ldpartN;
-    if (ozM) {
+    if (proj) {
+      CU(oz_slice_rows(Ks, ldm, ns, m, ozM, kq, oz_ldk(m), ke, st));
+      CU(oz_gemm(kq, ke, ns, btq, bte, q, m, oz_ldk(m), ozM, Kb, ldq, 1, 0, 0, st));          // K_b = K B   (U:2049)
+      CU(oz_slice_rows(Kb, ldq, ns, q, ozM, kbq, oz_ldk(q), kbe, st, bq, pm2));              // pm2 = K_b b = lam_m
+      const OzMoments mom{Kb, ldq, pm1, ldpartN};
+      CU(oz_gemm(kbq, kbe, ns, mgq, mge, q, q, oz_ldk(q), ozM, Tb, ldq, 1, 0, 0, st, &mom));  // T_b = K_b Mg^T + row sums
+      CU(oz_slice_rows(Tb, ldq, ns, q, ozM, tbq, oz_ldk(q), tbe, st));
+      CU(oz_gemm(tbq, tbe, ns, brq, bre, m, q, oz_ldk(q), ozM, Ts, ldm, 1, 0, 0, st));        // T = T_b B^T
+    } else if (ozM) {
       CU(oz_slice_rows(Ks, ldm, ns, m, ozM, kq, oz_ldk(m), ke, st, bb, pm2));   // pm2 = K bb on the way
       const OzMoments mom{Ks, ldm, pm1, ldpartN};
       CU(oz_gemm(kq, ke, ns, mq, me, m, m, oz_ldk(m), ozM, Ts, ldm, 1, 0, 0, st, &mom));
@@ -873,7 +915,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       CU(gemm(st, 0, 0, kMoments, false, 1, g3));
     }
     mark(4);
-    moments_rows(s_s, pm1, pm2, ldpartN, ozM ? ng16 : ntm, ozM ? 1 : ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
+    moments_rows(s_s, pm1, pm2, ldpartN, proj ? (q + 15) / 16 : (ozM ? ng16 : ntm), ozM ? 1 : ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
                  v_s, blockpart, st);
     const int nbm = moments_rows_blocks(ns);
     sum_to_slot(blockpart + 0, nbm, 4, 1.0, h->d_scal, kSlotRLam, acc_flag, st);
@@ -883,7 +925,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     // adjoint of the arc-cosine map: R (in place over T), row weights w, column sums kappa / y
     // ... and, for the int8-slice products that follow, the column maxima of R and of diag(sqrt(-v)) K
     acos_backward(0, Ts, cos_s, Ks, ldm, ns, m, u_s, v_s, bb, X1, X2, w_s, colk, coly, ldm, sumpartR, st,
-                  ozM ? cmaxR : nullptr, cmaxW);
+                  (ozS || (ozM && !proj)) ? cmaxR : nullptr, cmaxW);
     const int nbb = acos_backward_blocks(ns);
     col_reduce(colk, nbb, m, ldm, kappa, acc_flag, st);
     col_reduce(coly, nbb, m, ldm, yv, acc_flag, st);
@@ -891,6 +933,13 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     sum_to_slot(w_s, ns, 1, 1.0, h->d_scal, kSlotSig, 1, st);
     // G6: Sig2 += K^T diag(v) K
     auto sig2_product = [&]() -> cudaError_t {
+      if (proj) {     // S2b += K_b^T diag(v) K_b directly (q x q): no B^T Sig2 B in the tail
+        const int ldk_s = oz_ldk((int)ns);
+        cudaError_t e = oz_slice_cols(Kb, ldq, ns, q, ozM, kbtq, ldk_s, kbte, ozmx, st, v_s);
+        if (e != cudaSuccess) return e;
+        return oz_gemm(kbtq, kbte, q, kbtq, kbte, q, (int)ns, ldk_s, ozM, S2part, ldq, nzK, (long)q * ldq, acc_flag, st,
+                       nullptr, 0, -1.0, 1);
+      }
       if (ozM) {
         // v_i = -A^2 f_i / 2 <= 0, so K^T diag(v) K = -W^T W with W = diag(sqrt(-v)) K: ONE transposed slicing serves
         // both operands of the int8 product; only the tiles on and below the diagonal are computed
@@ -960,13 +1009,20 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   // ---- adjoint of K_tilde_b (q x q algebra) ---------------------------------------------------------------
   cudaStream_t st_loop = st;
   if (tail_overlap) st = h->chain_stream;     // issued after the fork above; joins before the final contraction
-  slice_reduce(S2part, ozM ? oz_eff_split((int)std::min(slab, N), nzK) : nzS2, zS2, zS2, Sig2, 0, st);
-  mirror_lower(Sig2, ldm, m, st);
+  if (proj) {
+    slice_reduce(S2part, oz_eff_split((int)std::min(slab, N), nzK), (long)q * ldq, (long)q * ldq, S2b, 0, st);
+    mirror_lower(S2b, ldq, q, st);
+  } else {
+    slice_reduce(S2part, ozM ? oz_eff_split((int)std::min(slab, N), nzK) : nzS2, zS2, zS2, Sig2, 0, st);
+    mirror_lower(Sig2, ldm, m, st);
+  }
   col_weights(kappa, nullptr, nullptr, X2, m, beta, st);                                 // beta_j = kappa_j / (2 X2_j)
   sum_to_slot(beta, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);
   gemv(Bw, ldq, m, q, 1, yv, y_b, st);                                                  // y_b = B^T y
-  CU(mm(st, 0, 1, Sig2, ldm, Bw, ldq, tmq1, ldq, m, q, m));
-  CU(mm(st, 1, 1, Bw, ldq, tmq1, ldq, S2b, ldq, q, q, m));                               // B^T Sig2 B
+  if (!proj) {
+    CU(mm(st, 0, 1, Sig2, ldm, Bw, ldq, tmq1, ldq, m, q, m));
+    CU(mm(st, 1, 1, Bw, ldq, tmq1, ldq, S2b, ldq, q, q, m));                             // B^T Sig2 B
+  }
   CU(mm(st, 0, 0, Kinv, ldq, Vw, ldq, KV, ldq, q, q, q));                                // Kinv V^T
   lincomb(W2, ldq, q, q, 2.0, KV, ldq, 0.0, nullptr, 0, -1.0, st);                      // 2 Kinv V^T - I
   CU(mm(st, 0, 1, S2b, ldq, W2, ldq, inner, ldq, q, q, q));
@@ -1020,7 +1076,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   CU(cudaStreamSynchronize(st));
   if (dbg_t) fprintf(stderr, "[sgp timing] first copy issued %.3f ms after entry; all work enqueued at %.3f; done at %.3f\n",
                      t_issue - t_entry, t_enq - t_entry, now_ms() - t_entry);
-  if (out_host) std::memcpy(out_host, h->h_out, sizeof(double) * 16);
+  if (out_host) { std::memcpy(out_host, h->h_out, sizeof(double) * 16); out_host[15] = proj ? 1.0 : 0.0; }
   if (h->profile) {
     for (size_t i = 0; i + 1 < h->prof_used; ++i) {
       float ms = 0.f;

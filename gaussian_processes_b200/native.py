@@ -282,7 +282,7 @@ def rate(lam_m: torch.Tensor, lam_var: torch.Tensor, logA: float, lambda0: float
 
 
 OUT_KEYS = ("loglik", "KL", "g_sigma_0", "g_eps_0x", "g_eps_0y", "g_-2log2beta", "g_-log2rho2", "g_Amp",
-            "flags", "p", "sum_r", "sum_f", "r_lam", "logdetK", "logdetV", "_")
+            "flags", "p", "sum_r", "sum_f", "r_lam", "logdetK", "logdetV", "projected")
 
 
 def elbo_grad(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
