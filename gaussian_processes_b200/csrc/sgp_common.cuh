@@ -48,15 +48,75 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                : "d"(a), "d"(b));
 }
 
+// ---- fp64 reciprocal / square root / arc cosine without libdevice ---------------------------------------------------
+// The N x m elementwise passes of the arc-cosine kernel were ISSUE-bound on libdevice's acos / sqrt / division (ncu:
+// 181 executed instructions per element, 77 % of the issue slots, half of them moves that materialise 64-bit polynomial
+// coefficients and the slow-path guards of division / sqrt).  These versions are branch-free, take their coefficients
+// from the constant bank as DFMA operands, and are accurate to 1 ulp (acos: the rational approximation of Sun's fdlibm
+// e_acos.c -- restated, |error| <= 1 ulp against numpy.arccos on 2.4e6 points: tests/test_acos_restatement.py keeps the
+// numpy restatement honest); the parity bar of the path is 1e-9, not bit-identity.
+__device__ __forceinline__ double rcp_nr(double x) {          // x normal and nonzero
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));        // MUFU.RCP64H: ~20 bits
+  double e = fma(-x, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-x, y, 1.0);
+  return fma(y, e, y);
+}
+__device__ __forceinline__ double div_nr(double a, double b) {  // a / b, b normal and nonzero; faithfully rounded
+  const double y = rcp_nr(b);
+  const double q = a * y;
+  return fma(fma(-b, q, a), y, q);
+}
+__device__ __forceinline__ double sqrt_nr(double x) {          // x >= 0 and either 0 or normal
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));      // MUFU.RSQ64H
+  double g = x * y, h = 0.5 * y;
+  double r = fma(-g, h, 0.5);
+  g = fma(g, r, g); h = fma(h, r, h);
+  r = fma(-g, h, 0.5);
+  g = fma(g, r, g); h = fma(h, r, h);
+  g = fma(fma(-g, g, x), h, g);
+  return x > 0.0 ? g : 0.0;
+}
+
+static __constant__ double kAcosP[6] = {1.66666666666666657415e-01, -3.25565818622400915405e-01,
+                                        2.01212532134862925881e-01, -4.00555345006794114027e-02,
+                                        7.91534994289814532176e-04, 3.47933107596021167570e-05};
+static __constant__ double kAcosQ[4] = {-2.40339491173441421878e+00, 2.02094576023350569471e+00,
+                                        -6.88283971605453293030e-01, 7.70381505559019352791e-02};
+constexpr double kPio2Hi = 1.57079632679489655800e+00, kPio2Lo = 6.12323399573676603587e-17;
+constexpr double kPiTrue = 3.14159265358979311600e+00;
+constexpr double kInvPi32 = 1.0 / kPi32;
+
+// delta = acos(c) for c in [-1, 1].  |c| < 1/2: pi/2 - (c + c R(c^2));  otherwise with z = (1 - |c|)/2, s = sqrt(z):
+// 2 (s + s R(z)) for c > 0 and pi - 2 (s + s R(z)) for c < 0;  R = P/Q of degrees 6/4.
+__device__ __forceinline__ double acos_nr(double c) {
+  const double a = fabs(c);
+  const bool big = a >= 0.5;
+  const double z = big ? 0.5 * (1.0 - a) : c * c;
+  double pz = fma(z, kAcosP[5], kAcosP[4]);
+  pz = fma(z, pz, kAcosP[3]); pz = fma(z, pz, kAcosP[2]); pz = fma(z, pz, kAcosP[1]); pz = fma(z, pz, kAcosP[0]);
+  pz *= z;
+  double qz = fma(z, kAcosQ[3], kAcosQ[2]);
+  qz = fma(z, qz, kAcosQ[1]); qz = fma(z, qz, kAcosQ[0]); qz = fma(z, qz, 1.0);
+  const double r = pz * rcp_nr(qz);
+  const double s = sqrt_nr(z);
+  const double small = kPio2Hi - (c - (kPio2Lo - c * r));
+  const double bigp = 2.0 * fma(s, r, s);
+  const double bign = kPiTrue - 2.0 * (s + fma(r, s, -kPio2Lo));
+  return big ? (c > 0.0 ? bigp : bign) : small;
+}
+
 // The arc-cosine nonlinearity of acosker (utils.py:984-990) for one (lin, X1*X2) pair.
-// Returns K = X1X2 * J; optionally cos(delta).  No FMA contraction on 1 - c*c so the value
-// matches the reference's two-step evaluation bit for bit in the common case.
+// Returns K = X1X2 * J; optionally cos(delta).  1 - c*c is evaluated in the reference's two steps (no FMA contraction):
+// near c = 1 (an inducing image that is also a training image) the rounding of c*c is what the reference's sqrt sees.
 __device__ __forceinline__ double acos_kernel_value(double lin, double nn, double* cos_out) {
-  double c = lin / (nn + kCosEps);
+  double c = div_nr(lin, nn + kCosEps);
   c = fmin(fmax(c, -1.0), 1.0);
-  const double delta = acos(c);
-  const double sq = sqrt(__dsub_rn(1.0, __dmul_rn(c, c)));
-  const double J = (sq + kPi32 * c - delta * c) / kPi32;
+  const double delta = acos_nr(c);
+  const double sq = sqrt_nr(__dsub_rn(1.0, __dmul_rn(c, c)));
+  const double J = (sq + kPi32 * c - delta * c) * kInvPi32;
   if (cos_out) *cos_out = c;
   return nn * J;
 }
@@ -64,9 +124,9 @@ __device__ __forceinline__ double acos_kernel_value(double lin, double nn, doubl
 // Local partials used by every derivative in acosker (utils.py:998-1000, 1017-1021):
 // P = (pi~ - delta)/pi~ ,  Q = sqrt(1-c^2)/pi~   so that  dK = P*d(lin) + Q*d(X1X2).
 __device__ __forceinline__ void acos_partials(double c, double& P, double& Q) {
-  const double delta = acos(c);
-  P = (kPi32 - delta) / kPi32;
-  Q = sqrt(__dsub_rn(1.0, __dmul_rn(c, c))) / kPi32;
+  const double delta = acos_nr(c);
+  P = (kPi32 - delta) * kInvPi32;
+  Q = sqrt_nr(__dsub_rn(1.0, __dmul_rn(c, c))) * kInvPi32;
 }
 
 }  // namespace sgp

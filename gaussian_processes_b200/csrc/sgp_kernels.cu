@@ -148,28 +148,49 @@ void moments_rows(const double* s, const double* part1, const double* part2, lon
 __global__ void __launch_bounds__(256) acos_forward_kernel(double* __restrict__ K, double* __restrict__ cosm, long ld,
                                                            long n, int m, const double* __restrict__ na,
                                                            const double* __restrict__ nb, double s02) {
+  // Two rows per block iteration, one column pair per thread (no 64-bit index division per element); the NEXT two rows
+  // are loaded before the current ones are worked on: ncu showed 41 % of the warp samples waiting on the single 16-byte
+  // load each thread had in flight in front of ~280 dependent instructions.
   const int m2 = (m + 1) >> 1;
-  const long total = n * m2;
-  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
-    const long i = e / m2;
-    const int j = (int)(e - i * m2) * 2;
-    const long o = i * ld + j;
-    const double nai = __ldg(na + i);
-    const double2 lin = *reinterpret_cast<const double2*>(K + o);   // ld is even, padding columns are in bounds
-    double c0, c1 = 0.0;
-    const double k0 = acos_kernel_value(lin.x + s02, nai * __ldg(nb + j), &c0);
-    const double k1 = (j + 1 < m) ? acos_kernel_value(lin.y + s02, nai * __ldg(nb + j + 1), &c1) : 0.0;
-    *reinterpret_cast<double2*>(K + o) = make_double2(k0, k1);
-    *reinterpret_cast<double2*>(cosm + o) = make_double2(c0, c1);
+  const long step = 2L * gridDim.x;
+  for (int j2 = threadIdx.x; j2 < m2; j2 += blockDim.x) {
+    const int j = 2 * j2;
+    const bool two = j + 1 < m;
+    const double nb0 = __ldg(nb + j), nb1 = two ? __ldg(nb + j + 1) : 1.0;
+    long i = 2L * blockIdx.x;
+    double2 cur[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+      cur[q] = (i + q < n) ? *reinterpret_cast<const double2*>(K + (i + q) * ld + j) : make_double2(0.0, 0.0);
+    for (; i < n; i += step) {
+      double2 nxt[2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q)
+        nxt[q] = (i + step + q < n) ? *reinterpret_cast<const double2*>(K + (i + step + q) * ld + j)
+                                    : make_double2(0.0, 0.0);
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        if (i + q < n) {
+          const double nai = __ldg(na + i + q);
+          double c0, c1 = 0.0;
+          const double k0 = acos_kernel_value(cur[q].x + s02, nai * nb0, &c0);
+          const double k1 = two ? acos_kernel_value(cur[q].y + s02, nai * nb1, &c1) : 0.0;
+          const long o = (i + q) * ld + j;                              // ld is even, padding columns are in bounds
+          *reinterpret_cast<double2*>(K + o) = make_double2(k0, k1);
+          *reinterpret_cast<double2*>(cosm + o) = make_double2(c0, c1);
+        }
+      }
+      cur[0] = nxt[0]; cur[1] = nxt[1];
+    }
   }
 }
 void acos_forward(double* K, double* cosm, long ld, long n, int m, const double* na, const double* nb, double s02,
                   cudaStream_t st) {
   if (n <= 0 || m <= 0) return;
-  const long total = n * ((m + 1) >> 1);
-  long nb_ = (total + 255) / 256;
-  if (nb_ > 148L * 32) nb_ = 148L * 32;
-  note_launch(); acos_forward_kernel<<<(unsigned)nb_, 256, 0, st>>>(K, cosm, ld, n, m, na, nb, s02);
+  const int m2 = (m + 1) >> 1;
+  const int threads = m2 >= 192 ? 256 : (m2 >= 96 ? 128 : 64);
+  const long nb_ = std::min<long>((n + 1) / 2, 148L * (2048 / threads));
+  note_launch(); acos_forward_kernel<<<(unsigned)nb_, threads, 0, st>>>(K, cosm, ld, n, m, na, nb, s02);
 }
 
 // =====================================================================================================
@@ -189,7 +210,10 @@ __global__ void __launch_bounds__(256, (CM <= 4) ? 2 : 1) acos_backward_kernel(d
                                                             double* __restrict__ sumpart,
                                                             double* __restrict__ colmax_r,
                                                             double* __restrict__ colmax_w) {
-  constexpr int RU = (CM <= 2) ? 4 : (CM == 4 ? 2 : 1);
+  // RU rows per batch; the loads of batch b+1 are issued before batch b is worked on (register double buffer), so
+  // every warp keeps RU*CM*3 loads in flight all the time: the pass reads T, cos, K and writes R, and with the loads
+  // of a batch only issued after the previous batch's arithmetic, ncu showed 48 % of the samples on long-scoreboard.
+  constexpr int RU = (CM <= 2) ? 2 : 1;
   __shared__ double rowred[8][kBwdRows];
   __shared__ double red[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -203,26 +227,32 @@ __global__ void __launch_bounds__(256, (CM <= 4) ? 2 : 1) acos_backward_kernel(d
     nbj[c] = (j < m) ? nb[j] : 0.0;
   }
   double sumR = 0.0;
-  for (int rr0 = 0; rr0 < kBwdRows; rr0 += RU) {
-    if (r0 + rr0 >= n) break;
-    double gv[RU][CM], cv[RU][CM], kv[RU][CM], ui[RU], vi[RU], nai[RU];
+  double gv[RU][CM], cv[RU][CM], kv[RU][CM], ui[RU], vi[RU], nai[RU];
+  auto load_batch = [&](int rr0, double (&g_)[RU][CM], double (&c_)[RU][CM], double (&k_)[RU][CM], double (&u_)[RU],
+                        double (&v_)[RU], double (&n_)[RU]) {
 #pragma unroll
     for (int q = 0; q < RU; ++q) {
       const long i = r0 + rr0 + q;
-      const bool rv = i < n;
-      ui[q] = (MODE == 0 && rv) ? u[i] : 0.0;
-      vi[q] = (MODE == 0 && rv) ? v[i] : 0.0;
-      nai[q] = rv ? na[i] : 1.0;
+      const bool rv = rr0 + q < kBwdRows && i < n;
+      u_[q] = (MODE == 0 && rv) ? u[i] : 0.0;
+      v_[q] = (MODE == 0 && rv) ? v[i] : 0.0;
+      n_[q] = rv ? na[i] : 1.0;
 #pragma unroll
       for (int c = 0; c < CM; ++c) {
         const int j = tid + c * 256;
         const bool ok = rv && j < m;
         const long o = i * ld + j;
-        gv[q][c] = ok ? G[o] : 0.0;
-        cv[q][c] = ok ? cosm[o] : 0.0;
-        kv[q][c] = (MODE == 0 && ok) ? Kmat[o] : 0.0;
+        g_[q][c] = ok ? G[o] : 0.0;
+        c_[q][c] = ok ? cosm[o] : 0.0;
+        k_[q][c] = (MODE == 0 && ok) ? Kmat[o] : 0.0;
       }
     }
+  };
+  load_batch(0, gv, cv, kv, ui, vi, nai);
+  for (int rr0 = 0; rr0 < kBwdRows; rr0 += RU) {
+    if (r0 + rr0 >= n) break;
+    double gn[RU][CM], cn[RU][CM], kn[RU][CM], un[RU], vn[RU], nn[RU];
+    load_batch(rr0 + RU, gn, cn, kn, un, vn, nn);
 #pragma unroll
     for (int q = 0; q < RU; ++q) {
       const long i = r0 + rr0 + q;
@@ -247,6 +277,12 @@ __global__ void __launch_bounds__(256, (CM <= 4) ? 2 : 1) acos_backward_kernel(d
       }
       rho = warp_sum(rho);
       if (lane == 0) rowred[warp][rr0 + q] = rho;
+    }
+#pragma unroll
+    for (int q = 0; q < RU; ++q) {
+      ui[q] = un[q]; vi[q] = vn[q]; nai[q] = nn[q];
+#pragma unroll
+      for (int c = 0; c < CM; ++c) { gv[q][c] = gn[q][c]; cv[q][c] = cn[q][c]; kv[q][c] = kn[q][c]; }
     }
   }
   __syncthreads();
