@@ -135,13 +135,17 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
   double* sG = sm;                 // NP x LD
   double* sLin = sG + NP * LD;     // NP coordinates, then NP squares
   double* sLin2 = sLin + NP;
+  double* sAx = sLin + 2 * NP;     // separable receptive-field weights: alpha[iy][ix] = sAy[iy] * sAx[ix]
+  double* sAy = sLin + 3 * NP;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  double* sM = sLin + 2 * NP + (size_t)warp * NP * LD;
+  double* sM = sLin + 4 * NP + (size_t)warp * NP * LD;
 
   for (int e = tid; e < NP; e += blockDim.x) {
     const double l = (e < a.n) ? lin_coord_dev(e, a.n) : 0.0;
     sLin[e] = l;
     sLin2[e] = l * l;
+    sAx[e] = (e < a.n) ? exp(-a.eb * (l - a.ex) * (l - a.ex)) : 0.0;
+    sAy[e] = (e < a.n) ? exp(-a.eb * (l - a.ey) * (l - a.ey)) : 0.0;
   }
   for (int e = tid; e < NP * LD; e += blockDim.x) {
     const int r = e / LD, c = e % LD;
@@ -155,7 +159,7 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
   for (int e = lane; e < NP * LD; e += 32) sM[e] = 0.0;   // pixels outside the mask / padding stay zero
   __syncthreads();
 
-  double* sStage = sLin + 2 * NP + (size_t)kSepWarps * NP * LD + (size_t)warp * pstage;
+  double* sStage = sLin + 4 * NP + (size_t)kSepWarps * NP * LD + (size_t)warp * pstage;
   const long stride = (long)gridDim.x * kSepWarps;
   auto prefetch = [&](long img) {
     const double* xr = a.X + img * a.ldx;
@@ -168,16 +172,29 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
     if (pstage > 0) {
       cp_async_wait<0>();
       __syncwarp();
-      // scatter into the n x n layout with the receptive-field weights; five pixels per lane in flight
-      int c = a.dbg_skip ? a.p : lane;
-      for (; c + 128 < a.p; c += 160) {
-        int o[5]; double v[5];
+      if (a.full && (a.n & 1) == 0) {
+        // every pixel kept: a row-by-row copy (two pixels per lane) with the separable weights from shared memory --
+        // no per-pixel offset / weight loads from global memory (they were 15 % of the kernel's stall samples)
+        const int half = a.n >> 1;
+        for (int e = lane; e < a.n * half; e += 32) {
+          const int r = e / half, c2 = 2 * (e - r * half);
+          const double2 xv = *reinterpret_cast<const double2*>(sStage + r * a.n + c2);
+          const double2 ax = *reinterpret_cast<const double2*>(sAx + c2);
+          const double ay = sAy[r];
+          *reinterpret_cast<double2*>(sM + r * LD + c2) = make_double2(xv.x * (ay * ax.x), xv.y * (ay * ax.y));
+        }
+      } else {
+        // scatter into the n x n layout with the receptive-field weights; five pixels per lane in flight
+        int c = lane;
+        for (; c + 128 < a.p; c += 160) {
+          int o[5]; double v[5];
 #pragma unroll
-        for (int u = 0; u < 5; ++u) { o[u] = __ldg(a.off + c + 32 * u); v[u] = sStage[c + 32 * u] * __ldg(a.alpha + c + 32 * u); }
+          for (int u = 0; u < 5; ++u) { o[u] = __ldg(a.off + c + 32 * u); v[u] = sStage[c + 32 * u] * __ldg(a.alpha + c + 32 * u); }
 #pragma unroll
-        for (int u = 0; u < 5; ++u) sM[o[u]] = v[u];
+          for (int u = 0; u < 5; ++u) sM[o[u]] = v[u];
+        }
+        for (; c < a.p; c += 32) sM[a.off[c]] = sStage[c] * a.alpha[c];
       }
-      for (; c < a.p; c += 32) sM[a.off[c]] = sStage[c] * a.alpha[c];
       __syncwarp();
       if (img + stride < a.nrows) prefetch(img + stride);
     } else {
@@ -215,7 +232,7 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
 template <int NT>
 cudaError_t launch_sep(const SepQuadArgs& a, cudaStream_t st) {
   constexpr int NP = 8 * NT, LD = NP + 4;
-  size_t smem = (size_t)(NP * LD + 2 * NP + kSepWarps * NP * LD) * sizeof(double);
+  size_t smem = (size_t)(NP * LD + 4 * NP + kSepWarps * NP * LD) * sizeof(double);
   // staging buffers for the cp.async prefetch, if the rows are 16-byte aligned and everything fits in 227 KB
   int pstage = (a.p + 1) & ~1;
   const bool aligned = (a.ldx % 2 == 0) && (reinterpret_cast<uintptr_t>(a.X) % 16 == 0);
@@ -237,10 +254,7 @@ int sep_quad_tiles(int n_px) { return (n_px + 7) / 8; }
 bool sep_quad_supported(int n_px) { return n_px >= 1 && n_px <= 8 * kSepMaxTiles; }
 int sep_quad_ld(int n_px) { return 8 * sep_quad_tiles(n_px) + 4; }
 
-cudaError_t sep_quad(const SepQuadArgs& a_, cudaStream_t st) {
-  SepQuadArgs a = a_;
-  static const int dbg = getenv("SGP_SEP_SKIP") ? atoi(getenv("SGP_SEP_SKIP")) : 0;
-  a.dbg_skip = dbg;
+cudaError_t sep_quad(const SepQuadArgs& a, cudaStream_t st) {
   if (a.nrows <= 0) return cudaSuccess;
   switch (sep_quad_tiles(a.n)) {
     case 1: return launch_sep<1>(a, st);

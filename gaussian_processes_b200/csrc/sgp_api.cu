@@ -861,7 +861,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       SepQuadArgs sq{};
       sq.X = Xs; sq.ldx = ldxs; sq.nrows = ns; sq.p = p; sq.off = d_off; sq.alpha = d_alpha; sq.n = n;
       sq.er = th.er; sq.eb = th.eb; sq.ex = th.ex; sq.ey = th.ey; sq.amp = th.amp; sq.s02 = th.s02;
-      sq.s = s_s; sq.nrm = X1; sq.Q = Qs;
+      sq.s = s_s; sq.nrm = X1; sq.Q = Qs; sq.full = full_mask ? 1 : 0;
       if (chain_overlap && slab_i == 0) sq.max_ctas = 148 - 20;   // leave SMs to the inducing-point chain
       CU(sep_quad(sq, st));
       mark(2);

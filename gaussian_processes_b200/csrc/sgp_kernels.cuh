@@ -160,7 +160,7 @@ struct SepQuadArgs {
   double er, eb, ex, ey, amp, s02;
   double* s; double* nrm; double* Q;   // Q may be null (value only)
   int max_ctas = 0;                    // 0 = one CTA per SM; smaller grids leave SMs to a concurrent stream
-  int dbg_skip = 0;
+  int full = 0;                        // 1: the mask keeps every pixel and off[] is the plain n x n layout (fast scatter)
 };
 bool sep_quad_supported(int n_px);
 int sep_quad_ld(int n_px);
