@@ -738,7 +738,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   }
   copy_mat(in.B, in.ldb, m, q, Bw, ldq, st);
   copy_mat(in.V, in.ldv, q, q, Vw, ldq, st);
-  // log det V_b does not depend on theta: its Cholesky runs on a side stream next to the K_tilde_b chain
+  // log det V_b does not depend on theta: its Cholesky runs on a side stream next to the K_tilde_b chain.  Only the
+  // fork is recorded here; the ~25 launches are ENQUEUED after the main stream's first kernels (enqueue_side below):
+  // the host needs ~3 us per launch, and everything queued ahead of build_C delays the whole evaluation.
   bool side_pending = false;
   if (!in.logdetV_host) {
     if (!h->side_stream) {
@@ -747,14 +749,18 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       CU(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     }
     CU(cudaEventRecord(h->ev_fork, st));
+    side_pending = true;
+  }
+  auto enqueue_side = [&]() -> int {
+    if (!side_pending) return SGP_OK;
     CU(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
     double* Lv_side = qq[9];
     copy_mat(Vw, ldq, q, q, Lv_side, ldq, h->side_stream);
     CU(cholesky_lower(Lv_side, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, winv2, h->side_stream));
     logdet_from_chol(Lv_side, ldq, q, h->d_scal, kSlotLogdetV, h->side_stream);
     CU(cudaEventRecord(h->ev_join, h->side_stream));
-    side_pending = true;
-  }
+    return SGP_OK;
+  };
 
   // ---- a1: C(theta) ---------------------------------------------------------------------------------
   build_C(C, ldp, p, d_gx, d_gy, th, nullptr, 0, st);
@@ -777,10 +783,18 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
         CU(cudaEventCreateWithFlags(&h->ev_chain_join, cudaEventDisableTiming));
       }
       CU(cudaEventRecord(h->ev_chain_fork, st));
-      CU(cudaStreamWaitEvent(h->chain_stream, h->ev_chain_fork, 0));
     }
+  }
+  // The chain itself (~100 launches, ~0.3 ms of host enqueue time).  With chain_overlap it is enqueued from inside the
+  // image loop, AFTER the first slab's quadratic forms / K_lin product / arc-cosine map have been queued on the main
+  // stream (none of them needs it): queued first, it kept the main stream waiting for the host.
+  bool chain_enqueued = false;
+  auto enqueue_chain = [&]() -> int {
+    if (chain_enqueued) return SGP_OK;
+    chain_enqueued = true;
     cudaStream_t st_main = st;
-    st = chain_overlap ? h->chain_stream : st;      // the rest of this block is issued on the chain stream
+    cudaStream_t st = chain_overlap ? h->chain_stream : st_main;   // shadows the outer stream inside this lambda
+    if (chain_overlap) CU(cudaStreamWaitEvent(h->chain_stream, h->ev_chain_fork, 0));
     GemmArgs a{};  // K_tilde (raw) = acos-kernel(ZU Ug^T)
     a.A = ZU; a.lda = ldp; a.B = Ug; a.ldb = ldug; a.C = Kraw; a.ldc = ldm; a.M = m; a.N = m; a.K = p;
     a.rowvec = X2; a.colvec = X2; a.C2 = cosU; a.s02 = th.s02;
@@ -809,8 +823,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       CU(oz_slice_cols(Bw, ldq, m, q, ozM, btq, oz_ldk(m), bte, ozmx, st));              // B operand of K_b = K B
     } else if (ozM) CU(oz_slice_rows(Mfull, ldm, m, m, ozM, mq, oz_ldk(m), me, st));
     if (chain_overlap) CU(cudaEventRecord(h->ev_chain_join, st));
-    st = st_main;
-  }
+    return SGP_OK;
+  };
+  if (!chain_overlap) { rc = enqueue_chain(); if (rc) return rc; rc = enqueue_side(); if (rc) return rc; }
 
   // ---- split-K plans for the two reductions over images ----------------------------------------------
   const int nzGC = use_sep ? 1 : pick_split(gemm_tiles(p, p), slab), nzS2 = pick_split(gemm_tiles(m, m, true), slab);
@@ -894,7 +909,11 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     mark(9);
     acos_forward(Ks, cos_s, ldm, ns, m, X1, X2, th.s02, st);
     mark(3);
-    if (chain_overlap && slab_i == 0) CU(cudaStreamWaitEvent(st, h->ev_chain_join, 0));
+    if (chain_overlap && slab_i == 0) {
+      rc = enqueue_chain(); if (rc) return rc;
+      rc = enqueue_side(); if (rc) return rc;
+      CU(cudaStreamWaitEvent(st, h->ev_chain_join, 0));
+    }
     // G3: T = K Mfull^T ; partial lam_var / lam_m row sums                    (U:1090-1101)
     GemmArgs g3{};
     g3.A = Ks; g3.lda = ldm; g3.B = Mfull; g3.ldb = ldm; g3.C = Ts; g3.ldc = ldm; g3.M = (int)ns; g3.N = m; g3.K = m;
@@ -918,10 +937,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     moments_rows(s_s, pm1, pm2, ldpartN, proj ? (q + 15) / 16 : (ozM ? ng16 : ntm), ozM ? 1 : ntm, rdev + i0, ns, A, in.lambda0, lam_m + i0, lam_var + i0, fvec + i0, u_s,
                  v_s, blockpart, st);
     const int nbm = moments_rows_blocks(ns);
-    sum_to_slot(blockpart + 0, nbm, 4, 1.0, h->d_scal, kSlotRLam, acc_flag, st);
-    sum_to_slot(blockpart + 1, nbm, 4, 1.0, h->d_scal, kSlotSumF, acc_flag, st);
-    sum_to_slot(blockpart + 2, nbm, 4, 1.0, h->d_scal, kSlotSumR, acc_flag, st);
-    sum_to_slot(blockpart + 3, nbm, 4, 1.0, h->d_scal, kSlotNaN, acc_flag, st);
+    static_assert(kSlotSumF == kSlotRLam + 1 && kSlotSumR == kSlotRLam + 2 && kSlotNaN == kSlotRLam + 3, "slot order");
+    sum_to_slots(blockpart, nbm, 4, 4, h->d_scal, kSlotRLam, acc_flag, st);
     // adjoint of the arc-cosine map: R (in place over T), row weights w, column sums kappa / y
     // ... and, for the int8-slice products that follow, the column maxima of R and of diag(sqrt(-v)) K
     acos_backward(0, Ts, cos_s, Ks, ldm, ns, m, u_s, v_s, bb, X1, X2, w_s, colk, coly, ldm, sumpartR, st,
@@ -959,8 +976,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     if (use_sep) {
       // sum_i w_i x_i^T dC_k x_i from the stored quadratic forms; D += X^T R (split-K over the images of the slab)
       wq_reduce(w_s, Qs, ns, wqpart, st);
-      for (int k = 0; k < 5; ++k)
-        sum_to_slot(wqpart + k, wq_reduce_blocks(ns), 5, 1.0, h->d_scal, kSlotGW + k, acc_flag, st);
+      sum_to_slots(wqpart, wq_reduce_blocks(ns), 5, 5, h->d_scal, kSlotGW, acc_flag, st);
       mark(7);
       // G6: Sig2 += K^T diag(v) K (before X^T R: the q x q tail depends on it, not on D)
       CU(sig2_product());
@@ -1063,9 +1079,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   }
   if (tail_overlap) CU(cudaStreamWaitEvent(st, h->ev_chain_join, 0));
   contract_dC(GCpart, nzGC, zGC, GCU, C, ldp, p, d_gx, d_gy, th, gpart, st);
-  for (int k = 0; k < 5; ++k) sum_to_slot(gpart + k, p, 5, 1.0, h->d_scal, kSlotG + k, 0, st);
-  if (use_sep)
-    for (int k = 0; k < 5; ++k) sum_to_slot(h->d_scal + kSlotGW + k, 1, 1, 1.0, h->d_scal, kSlotG + k, 1, st);
+  sum_to_slots(gpart, p, 5, 5, h->d_scal, kSlotG, 0, st);
+  if (use_sep) sum_to_slots(h->d_scal + kSlotGW, 1, 5, 5, h->d_scal, kSlotG, 1, st);
   if (side_pending) CU(cudaStreamWaitEvent(st, h->ev_join, 0));
   finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p, in.logdetV_host ? *in.logdetV_host : 0.0,
            in.logdetV_host ? 1 : 0, h->d_out, st);

@@ -399,6 +399,21 @@ void sum_to_slot(const double* x, long n, long stride, double scale, double* sca
                  cudaStream_t st) {
   note_launch(); sum_to_slot_kernel<<<1, 1024, 0, st>>>(x, n < 0 ? 0 : n, stride, scale, scal, slot, accumulate);
 }
+// nslots interleaved columns at once: scal[slot0 + k] (+)= sum_i x[i*stride + k]; block k sums column k in the
+// same fixed order as sum_to_slot (identical results), one launch instead of nslots
+__global__ void sum_to_slots_kernel(const double* __restrict__ x, long n, long stride, double* __restrict__ scal,
+                                    int slot0, int accumulate) {
+  __shared__ double red[32];
+  const int k = blockIdx.x;
+  double a = 0.0;
+  for (long i = threadIdx.x; i < n; i += blockDim.x) a += x[i * stride + k];
+  a = block_sum(a, red);
+  if (threadIdx.x == 0) scal[slot0 + k] = (accumulate ? scal[slot0 + k] : 0.0) + a;
+}
+void sum_to_slots(const double* x, long n, long stride, int nslots, double* scal, int slot0, int accumulate,
+                  cudaStream_t st) {
+  note_launch(); sum_to_slots_kernel<<<nslots, 1024, 0, st>>>(x, n < 0 ? 0 : n, stride, scal, slot0, accumulate);
+}
 
 // =====================================================================================================
 // small dense helpers

@@ -83,6 +83,8 @@ void slice_reduce(const double* part, int nz, long zstride, long n, double* out,
 // scal[slot] (+)= scale * sum_i x[i*stride], single CTA, fixed order
 void sum_to_slot(const double* x, long n, long stride, double scale, double* scal, int slot, int accumulate,
                  cudaStream_t st);
+void sum_to_slots(const double* x, long n, long stride, int nslots, double* scal, int slot0, int accumulate,
+                  cudaStream_t st);   // nslots interleaved columns, slots slot0..
 
 // ---- small dense helpers (q x q / m x m) -----------------------------------------------------
 void symmetrize(const double* A, long lda, int n, double* out, long ldo, cudaStream_t st);   // out = (A + A^T)/2
