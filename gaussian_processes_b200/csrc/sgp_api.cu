@@ -569,7 +569,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   acc(p); acc(p); acc((size_t)(p + 1) / 2 + 8);                       // gx, gy, idx
   acc((size_t)p * ldp);                                               // C
   acc((size_t)m * ldq); acc((size_t)q * ldq);                         // Bw, Vw
-  acc((size_t)m * ldp); acc((size_t)ntp_s * ldpartU); acc(m); acc(m); // ZU/YU, partU, tU, X2
+  acc((size_t)m * ldp); acc((size_t)std::max(ntp_s, (p + 15) / 16) * ldpartU); acc(m); acc(m); // ZU/YU, partU, tU, X2
   for (int i = 0; i < 6; ++i) acc((size_t)m * ldm);                   // Kraw, Kt, cosU, Mfull, Sig2, GKt
   for (int i = 0; i < 3; ++i) acc((size_t)m * ldq);                   // tmp_mq x3
   for (int i = 0; i < 14; ++i) acc((size_t)q * ldq);                  // q x q scratch
@@ -595,6 +595,11 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     acc((size_t)std::max(p, m) + 8);
     acc(oz_slice_bytes(slab, m, ozM) / 8 + 16); acc(oz_slice_bytes(m, m, ozM) / 8 + 16); acc(slab / 2 + 8); acc(m);   // K, Mfull slices
   }
+  if (ozS) {                                                          // slices of Ug, C, Ug^T, D for ZU = Ug C and GC = D Ug
+    acc(oz_slice_bytes(m, p, ozS) / 8 + 16); acc(oz_slice_bytes(p, p, ozS) / 8 + 16);
+    acc(oz_slice_bytes(p, m, ozS) / 8 + 16); acc(oz_slice_bytes(p, m, ozS) / 8 + 16);
+    acc(m); acc(p); acc(p); acc(p);
+  }
   if (proj) {                                                         // K_b, T_b and the slices of K_b, T_b, B, B^T, Mg
     acc((size_t)slab * ldq); acc((size_t)slab * ldq);
     acc(oz_slice_bytes(slab, q, ozM) / 8 + 16); acc(oz_slice_bytes(slab, q, ozM) / 8 + 16);
@@ -611,7 +616,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   double* C = ar.take<double>((size_t)p * ldp);
   double* Bw = ar.take<double>((size_t)m * ldq); double* Vw = ar.take<double>((size_t)q * ldq);
   double* ZU = ar.take<double>((size_t)m * ldp);
-  double* partU = ar.take<double>((size_t)ntp_s * ldpartU);
+  double* partU = ar.take<double>((size_t)std::max(ntp_s, (p + 15) / 16) * ldpartU);
   double* tU = ar.take<double>(m); double* X2 = ar.take<double>(m);
   double* Kraw = ar.take<double>((size_t)m * ldm); double* Kt = ar.take<double>((size_t)m * ldm);
   double* cosU = ar.take<double>((size_t)m * ldm); double* Mfull = ar.take<double>((size_t)m * ldm);
@@ -662,6 +667,15 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     ke = (int*)ar.take<double>(slab / 2 + 8); me = (int*)ar.take<double>(m);
   }
 
+  int8_t* ugq = nullptr; int8_t* cq = nullptr; int8_t* utq = nullptr; int8_t* dq = nullptr;
+  int* uge = nullptr; int* ce = nullptr; int* ute = nullptr; int* de = nullptr;
+  if (ozS) {
+    ugq = (int8_t*)ar.take<double>(oz_slice_bytes(m, p, ozS) / 8 + 16);
+    cq = (int8_t*)ar.take<double>(oz_slice_bytes(p, p, ozS) / 8 + 16);
+    utq = (int8_t*)ar.take<double>(oz_slice_bytes(p, m, ozS) / 8 + 16);
+    dq = (int8_t*)ar.take<double>(oz_slice_bytes(p, m, ozS) / 8 + 16);
+    uge = (int*)ar.take<double>(m); ce = (int*)ar.take<double>(p); ute = (int*)ar.take<double>(p); de = (int*)ar.take<double>(p);
+  }
   double* Kb = nullptr; double* Tb = nullptr;
   int8_t* kbq = nullptr; int8_t* tbq = nullptr; int8_t* brq = nullptr; int8_t* btq = nullptr; int8_t* mgq = nullptr;
   int8_t* kbtq = nullptr; int* kbe = nullptr; int* tbe = nullptr; int* bre = nullptr; int* bte = nullptr; int* mge = nullptr;
@@ -768,11 +782,21 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const bool smallU = true;  // inducing-point GEMMs are small: 64x64 tiles
   // ---- inducing-point path: K_tilde, K_tilde_b, its inverse, and the moment matrices ------------------
   {
-    GemmArgs g{};  // ZU = Ug C ; partial row dots for t_j = u_j^T C u_j
-    g.A = Ug; g.lda = ldug; g.B = C; g.ldb = ldp; g.C = ZU; g.ldc = ldp; g.M = m; g.N = p; g.K = p;
-    g.aux = Ug; g.ldaux = ldug; g.part1 = partU; g.ldpart = ldpartU;
-    CU(gemm(st, 0, 1, kRowdot, smallU, 1, g));
-    norms_finalize(partU, ldpartU, ntp_s, m, th.s02, tU, X2, st);
+    // ZU = Ug C ; partial row dots for t_j = u_j^T C u_j.  On the critical path of every evaluation (nothing else can
+    // start before it): int8-slice engine when it is on (C is symmetric, so its rows are the B operand's rows)
+    if (ozS) {
+      CU(oz_slice_rows(Ug, ldug, m, p, ozS, ugq, ldkP, uge, st));
+      CU(oz_slice_rows(C, ldp, p, p, ozS, cq, ldkP, ce, st));
+      const OzMoments mom{Ug, ldug, partU, ldpartU};
+      CU(oz_gemm(ugq, uge, m, cq, ce, p, p, ldkP, ozS, ZU, ldp, 1, 0, 0, st, &mom));
+      norms_finalize(partU, ldpartU, (p + 15) / 16, m, th.s02, tU, X2, st);
+    } else {
+      GemmArgs g{};
+      g.A = Ug; g.lda = ldug; g.B = C; g.ldb = ldp; g.C = ZU; g.ldc = ldp; g.M = m; g.N = p; g.K = p;
+      g.aux = Ug; g.ldaux = ldug; g.part1 = partU; g.ldpart = ldpartU;
+      CU(gemm(st, 0, 1, kRowdot, smallU, 1, g));
+      norms_finalize(partU, ldpartU, ntp_s, m, th.s02, tU, X2, st);
+    }
     // Everything below only feeds the moments (Mfull, bb) and the KL scalars: a chain of ~100 small launches that
     // is latency-bound on a handful of SMs.  It runs on its own stream while the main stream starts the image pass
     // (quadratic forms of the first slab on a slightly smaller grid); they join before the first moments product.
@@ -822,6 +846,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       CU(oz_slice_rows(Bw, ldq, m, q, ozM, brq, oz_ldk(q), bre, st));                    // B operand of T = T_b B^T
       CU(oz_slice_cols(Bw, ldq, m, q, ozM, btq, oz_ldk(m), bte, ozmx, st));              // B operand of K_b = K B
     } else if (ozM) CU(oz_slice_rows(Mfull, ldm, m, m, ozM, mq, oz_ldk(m), me, st));
+    if (ozS) CU(oz_slice_cols(Ug, ldug, m, p, ozS, utq, oz_ldk(m), ute, ozmx, st));     // B operand of GC = D Ug (tail)
     if (chain_overlap) CU(cudaEventRecord(h->ev_chain_join, st));
     return SGP_OK;
   };
@@ -1075,7 +1100,12 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   // ---- <dC_k, GC> and result assembly -----------------------------------------------------------------------
   if (use_sep) {
     slice_reduce(Dpart, ozS ? oz_eff_split((int)std::min(slab, N), nzO) : nzD, zD, zD, Dm, 0, st);
-    CU(mm(st, 0, 1, Dm, ldm, Ug, ldug, GCpart, ldp, p, p, m));                           // (X^T R) U
+    if (ozS) {                                                                            // (X^T R) U
+      CU(oz_slice_rows(Dm, ldm, p, m, ozS, dq, oz_ldk(m), de, st));
+      CU(oz_gemm(dq, de, p, utq, ute, p, m, oz_ldk(m), ozS, GCpart, ldp, 1, 0, 0, st));
+    } else {
+      CU(mm(st, 0, 1, Dm, ldm, Ug, ldug, GCpart, ldp, p, p, m));
+    }
   }
   if (tail_overlap) CU(cudaStreamWaitEvent(st, h->ev_chain_join, 0));
   contract_dC(GCpart, nzGC, zGC, GCU, C, ldp, p, d_gx, d_gy, th, gpart, st);
