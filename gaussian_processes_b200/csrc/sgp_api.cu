@@ -1090,7 +1090,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     g.A = GKt; g.lda = ldm; g.B = Ug; g.ldb = ldug; g.C = ZU; g.ldc = ldp; g.M = m; g.N = p; g.K = m;
     g.rowvec = wU; g.aux = Ug; g.ldaux = ldug;
     CU(gemm(st, 0, 1, kAxpyRow, smallU, 1, g));
-    CU(mm(st, 1, 1, Ug, ldug, ZU, ldp, GCU, ldp, p, p, m));                              // Ug^T YU
+    // Ug^T YU enters only through <dC_k, .> and every dC_k is symmetric, so <dC_k, Ug^T YU> = <dC_k, YU^T Ug>: with the
+    // int8 engine on, YU^T is added to D = X^T R and ONE product (D + YU^T) Ug serves both terms
+    if (!ozS) CU(mm(st, 1, 1, Ug, ldug, ZU, ldp, GCU, ldp, p, p, m));                    // Ug^T YU
   }
   if (tail_overlap) {
     CU(cudaEventRecord(h->ev_chain_join, st));
@@ -1100,7 +1102,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   // ---- <dC_k, GC> and result assembly -----------------------------------------------------------------------
   if (use_sep) {
     slice_reduce(Dpart, ozS ? oz_eff_split((int)std::min(slab, N), nzO) : nzD, zD, zD, Dm, 0, st);
-    if (ozS) {                                                                            // (X^T R) U
+    if (ozS) {                                                                            // (X^T R + YU^T) U
+      if (tail_overlap) CU(cudaStreamWaitEvent(st, h->ev_chain_join, 0));
+      add_transposed(Dm, ldm, p, m, ZU, ldp, st);
       CU(oz_slice_rows(Dm, ldm, p, m, ozS, dq, oz_ldk(m), de, st));
       CU(oz_gemm(dq, de, p, utq, ute, p, m, oz_ldk(m), ozS, GCpart, ldp, 1, 0, 0, st));
     } else {
@@ -1108,7 +1112,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     }
   }
   if (tail_overlap) CU(cudaStreamWaitEvent(st, h->ev_chain_join, 0));
-  contract_dC(GCpart, nzGC, zGC, GCU, C, ldp, p, d_gx, d_gy, th, gpart, st);
+  contract_dC(GCpart, nzGC, zGC, ozS ? nullptr : GCU, C, ldp, p, d_gx, d_gy, th, gpart, st);
   sum_to_slots(gpart, p, 5, 5, h->d_scal, kSlotG, 0, st);
   if (use_sep) sum_to_slots(h->d_scal + kSlotGW, 1, 5, 5, h->d_scal, kSlotG, 1, st);
   if (side_pending) CU(cudaStreamWaitEvent(st, h->ev_join, 0));

@@ -427,6 +427,23 @@ void symmetrize(const double* A, long lda, int n, double* out, long ldo, cudaStr
   note_launch(); symmetrize_kernel<<<dim3(cdiv(n, 128), n), 128, 0, st>>>(A, lda, n, out, ldo);
 }
 
+// A (rows x cols) += B^T, B is cols x rows: 32 x 32 tiles through shared memory (both sides coalesced)
+__global__ void __launch_bounds__(256) add_transposed_kernel(double* __restrict__ A, long lda, int rows, int cols,
+                                                             const double* __restrict__ B, long ldb) {
+  __shared__ double tile[32][33];
+  const int i0 = blockIdx.y * 32, j0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int r = ty; r < 32; r += 8)                      // B[j0 + r][i0 + tx]
+    tile[r][tx] = (j0 + r < cols && i0 + tx < rows) ? B[(long)(j0 + r) * ldb + i0 + tx] : 0.0;
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8)
+    if (i0 + r < rows && j0 + tx < cols) A[(long)(i0 + r) * lda + j0 + tx] += tile[tx][r];
+}
+void add_transposed(double* A, long lda, int rows, int cols, const double* B, long ldb, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return;
+  note_launch(); add_transposed_kernel<<<dim3(cdiv(cols, 32), cdiv(rows, 32)), 256, 0, st>>>(A, lda, rows, cols, B, ldb);
+}
+
 // A[i][j] = A[j][i] for j > i (completes a product whose upper CTA tiles were skipped)
 __global__ void mirror_lower_kernel(double* __restrict__ A, long ld, int n) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;

@@ -88,6 +88,7 @@ void sum_to_slots(const double* x, long n, long stride, int nslots, double* scal
 
 // ---- small dense helpers (q x q / m x m) -----------------------------------------------------
 void symmetrize(const double* A, long lda, int n, double* out, long ldo, cudaStream_t st);   // out = (A + A^T)/2
+void add_transposed(double* A, long lda, int rows, int cols, const double* B, long ldb, cudaStream_t st);   // A += B^T
 void mirror_lower(double* A, long ld, int n, cudaStream_t st);                                // A[i][j] = A[j][i], j > i
 void lincomb(double* out, long ldo, int rows, int cols, double a, const double* A, long lda, double b,
              const double* B, long ldb, double diag, cudaStream_t st);                        // out = a*A + b*B + diag*I
