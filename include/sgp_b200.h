@@ -61,7 +61,10 @@ SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
  * evaluation use 0 so that the all-reduced sum counts the N-independent KL term once), "profile" (1 = record
  * CUDA events at the stage boundaries of sgp_elbo_grad), "slab_rows", "path" (0 = choose, 1 = dense C products,
  * 2 = separable quadratic forms), "i8_slices" (-1 = choose, 0 = the two N x p x m products of sgp_elbo_grad on the
- * fp64 tensor pipe, 2..8 = on tcgen05.mma.kind::i8 with that many int8 slices per operand; see sgp_gemm_i8emu).
+ * fp64 tensor pipe, 2..8 = on tcgen05.mma.kind::i8 with that many int8 slices per operand; see sgp_gemm_i8emu;
+ * 8 is the error class of a DGEMM and the default, 4 gives 27 bits per operand -- the fp32-class setting),
+ * "projected" (-1 = moments in the projected basis K_b = K B when q <= 0.4 m, 0 = never, 1 = always; same numbers
+ * up to rounding, utils.py:2047-2068), "overlap" (1 = the q x q chains run on side streams).
  * With int8 slices the library keeps a sliced copy of device-resident images across calls (same bytes as X).     */
 SGP_API int sgp_set_option(sgp_handle* h, const char* name, double value);
 /* accumulated per-stage device milliseconds of sgp_elbo_grad since the last reset:
@@ -164,7 +167,8 @@ SGP_API int sgp_gemm_i8emu(sgp_handle* h, int layout, const double* A, long M, l
  *   logdetV_host: pointer to a precomputed log det V_b, or NULL to compute it here.
  *   lam_m / lam_var / f: optional device outputs (N each).
  *   out_host[16] = { loglik, KL, g_sigma_0, g_eps_0x, g_eps_0y, g_-2log2beta, g_-log2rho2, g_Amp,
- *                    flags, p, sum r, sum f, sum r*lam_m, logdet K_tilde_b, logdet V_b, 0 }
+ *                    flags, p, sum r, sum f, sum r*lam_m, logdet K_tilde_b, logdet V_b,
+ *                    1 if the moments went through the projected basis else 0 }
  *   with g_k = d(loglik - KL)/dtheta_k (the closure hands -g_k to LBFGS, U:2099).
  * The call synchronises `stream` before returning (the caller needs the loss as a host float).                  */
 SGP_API int sgp_elbo_grad(sgp_handle* h, const double* X, long ldx, const double* r, long N, const double* xtilde, long ldu,
