@@ -33,11 +33,26 @@ __device__ __forceinline__ double lin_coord_dev(int i, int n) {   // torch.linsp
 // RB row tiles (8 rows each) of one chain.  TR = false: rows are iy (Sy = M G M^T); TR = true: rows are ix
 // (Sx = M^T G M).  Adds the per-lane partial sums T0..T3 described at the end of the function.
 // Two row tiles share every G / M fragment of the second operand (7 fragment loads per 10 DMMAs instead of 6 per 5).
-template <int NT, bool TR, int RB>
+// Image tile addressing.  SWZ = 0: padded rows (pitch 8 NT + 4 doubles: conflict-free fragment loads).  SWZ = 1 / 2: pitch
+// 8 NT with the column XOR-ed by row bits instead of padding (1: NT odd, pitch = 8 mod 16 doubles, bit 2 <- row bit 1;
+// 2: NT even, pitch = 0 mod 16, bits 2-3 <- row bits 0-1): the same conflict-free loads -- for the row-major and the
+// transposed fragment patterns alike -- from 8 % less shared memory, which is what lets a warp hold TWO image tiles and
+// have cp.async write the next image straight into its final layout (16-byte chunks stay whole: the XOR is a multiple
+// of two doubles).
+template <int NT, int SWZ>
+__device__ __forceinline__ int midx(int row, int col) {
+  if (SWZ == 0) return row * (8 * NT + 4) + col;
+  if (SWZ == 1) return row * (8 * NT) + (col ^ (((row >> 1) & 1) << 2));
+  return row * (8 * NT) + (col ^ ((row & 3) << 2));
+}
+
+// G: second operand of the first product; GW: the matrix the second product is weighted with (the same matrix when the
+// receptive-field weights are already in M; D_x G D_x / D_y G D_y when M is the raw image, see sep_quad_full_kernel).
+template <int NT, bool TR, int RB, int SWZ>
 __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M, const double* __restrict__ G,
+                                           const double* __restrict__ GW,
                                            const double* __restrict__ lin, const double* __restrict__ lin2, int lane,
                                            double& T0, double& T1, double& T2, double& T3) {
-  constexpr int LD = 8 * NT + 4;
   const int g = lane >> 2, t = lane & 3;
   double P[RB][NT][2];
 #pragma unroll
@@ -49,10 +64,11 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
     const int k = 4 * kk + t;
     double af[RB];
 #pragma unroll
-    for (int r = 0; r < RB; ++r) af[r] = TR ? M[k * LD + 8 * (i0 + r) + g] : M[(8 * (i0 + r) + g) * LD + k];
+    for (int r = 0; r < RB; ++r)
+      af[r] = TR ? M[midx<NT, SWZ>(k, 8 * (i0 + r) + g)] : M[midx<NT, SWZ>(8 * (i0 + r) + g, k)];
 #pragma unroll
     for (int j = 0; j < NT; ++j) {
-      const double bf = G[k * LD + 8 * j + g];
+      const double bf = G[midx<NT, SWZ>(k, 8 * j + g)];
 #pragma unroll
       for (int r = 0; r < RB; ++r) dmma884(P[r][j][0], P[r][j][1], af[r], bf);
     }
@@ -81,7 +97,7 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
 #pragma unroll
       for (int jn = 0; jn < NT; ++jn) {
         if (jn <= i0 + RB - 1) {
-          const double bf = TR ? M[k * LD + 8 * jn + g] : M[(8 * jn + g) * LD + k];
+          const double bf = TR ? M[midx<NT, SWZ>(k, 8 * jn + g)] : M[midx<NT, SWZ>(8 * jn + g, k)];
 #pragma unroll
           for (int r = 0; r < RB; ++r)
             if (jn <= i0 + r) dmma884(S[r][jn][0], S[r][jn][1], af[r], bf);
@@ -103,7 +119,7 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
       if (jn <= i0 + r) {
         const double w = (jn == i0 + r) ? 0.5 : 1.0;
         const int b = 8 * jn + 2 * t;
-        const double2 gg = *reinterpret_cast<const double2*>(G + a * LD + b);
+        const double2 gg = *reinterpret_cast<const double2*>(GW + midx<NT, SWZ>(a, b));
         const double2 lb = *reinterpret_cast<const double2*>(lin + b);
         const double2 lb2 = *reinterpret_cast<const double2*>(lin2 + b);
         const double e0 = S[r][jn][0] * (gg.x * w), e1 = S[r][jn][1] * (gg.y * w);
@@ -117,13 +133,39 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
   }
 }
 
-template <int NT, bool TR>
+template <int NT, bool TR, int SWZ = 0>
 __device__ __forceinline__ void chain(const double* __restrict__ M, const double* __restrict__ G,
+                                      const double* __restrict__ GW,
                                       const double* __restrict__ lin, const double* __restrict__ lin2, int lane,
                                       double& T0, double& T1, double& T2, double& T3) {
 #pragma unroll 1
-  for (int i0 = 0; i0 + 1 < NT; i0 += 2) chain_rows<NT, TR, 2>(i0, M, G, lin, lin2, lane, T0, T1, T2, T3);
-  if (NT & 1) chain_rows<NT, TR, 1>(NT - 1, M, G, lin, lin2, lane, T0, T1, T2, T3);
+  for (int i0 = 0; i0 + 1 < NT; i0 += 2) chain_rows<NT, TR, 2, SWZ>(i0, M, G, GW, lin, lin2, lane, T0, T1, T2, T3);
+  if (NT & 1) chain_rows<NT, TR, 1, SWZ>(NT - 1, M, G, GW, lin, lin2, lane, T0, T1, T2, T3);
+}
+
+// Per-image results from the eight per-lane sums of the two chains (see chain_rows).
+__device__ __forceinline__ void sep_store(const SepQuadArgs& a, long img, int lane, double y0, double y1, double y2,
+                                          double y3, double x0, double x1, double x2, double x3) {
+  const double base = warp_sum(2.0 * y0);
+  const double dd = warp_sum(2.0 * (x1 + y1));
+  const double ax1 = warp_sum(x2 - 2.0 * a.ex * x0);
+  const double ay1 = warp_sum(y2 - 2.0 * a.ey * y0);
+  const double a2 = warp_sum((x3 - 2.0 * a.ex * x2 + 2.0 * a.ex * a.ex * x0) +
+                             (y3 - 2.0 * a.ey * y2 + 2.0 * a.ey * a.ey * y0));
+  if (lane == 0) {
+    const double sq = a.amp * base;          // x^T C x
+    const double s = sq + a.s02;
+    a.s[img] = s;
+    a.nrm[img] = sqrt(s);
+    if (a.Q) {
+      double* q = a.Q + img * 5;             // units of the closure's gradient slots (see finalize_kernel)
+      q[0] = sq;                             // Amp        : <C, x x^T>
+      q[1] = -2.0 * a.eb * a.amp * a2;       // -2log2beta
+      q[2] = -a.er * a.amp * dd;             // -log2rho2
+      q[3] = 2.0 * a.amp * ax1;              // eps_0x / (2 e^{theta_beta})
+      q[4] = 2.0 * a.amp * ay1;              // eps_0y / (2 e^{theta_beta})
+    }
+  }
 }
 
 // pstage > 0: every warp owns a staging buffer of pstage doubles and the NEXT image's row is brought in with cp.async
@@ -203,35 +245,97 @@ __global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_kernel(const SepQu
     }
     __syncwarp();
     double y0 = 0.0, y1 = 0.0, y2 = 0.0, y3 = 0.0, x0 = 0.0, x1 = 0.0, x2 = 0.0, x3 = 0.0;
-    chain<NT, false>(sM, sG, sLin, sLin2, lane, y0, y1, y2, y3);
-    chain<NT, true>(sM, sG, sLin, sLin2, lane, x0, x1, x2, x3);
+    chain<NT, false>(sM, sG, sG, sLin, sLin2, lane, y0, y1, y2, y3);
+    chain<NT, true>(sM, sG, sG, sLin, sLin2, lane, x0, x1, x2, x3);
     __syncwarp();
-    const double base = warp_sum(2.0 * y0);
-    const double dd = warp_sum(2.0 * (x1 + y1));
-    const double ax1 = warp_sum(x2 - 2.0 * a.ex * x0);
-    const double ay1 = warp_sum(y2 - 2.0 * a.ey * y0);
-    const double a2 = warp_sum((x3 - 2.0 * a.ex * x2 + 2.0 * a.ex * a.ex * x0) +
-                               (y3 - 2.0 * a.ey * y2 + 2.0 * a.ey * a.ey * y0));
-    if (lane == 0) {
-      const double sq = a.amp * base;          // x^T C x
-      const double s = sq + a.s02;
-      a.s[img] = s;
-      a.nrm[img] = sqrt(s);
-      if (a.Q) {
-        double* q = a.Q + img * 5;             // units of the closure's gradient slots (see finalize_kernel)
-        q[0] = sq;                             // Amp        : <C, x x^T>
-        q[1] = -2.0 * a.eb * a.amp * a2;       // -2log2beta
-        q[2] = -a.er * a.amp * dd;             // -log2rho2
-        q[3] = 2.0 * a.amp * ax1;              // eps_0x / (2 e^{theta_beta})
-        q[4] = 2.0 * a.amp * ay1;              // eps_0y / (2 e^{theta_beta})
-      }
+    sep_store(a, img, lane, y0, y1, y2, y3, x0, x1, x2, x3);
+  }
+}
+
+// Every pixel kept (dense receptive field), n even, rows 16-byte aligned: the receptive-field weights are separable,
+// alpha[iy][ix] = ay[iy] ax[ix], so they move out of the image and into the two Gaussian matrices:
+//   Sy o G = (X Gx' X^T) o Gy',  Sx o G = (X^T Gy' X) o Gx',   Gx' = D_ax G D_ax,  Gy' = D_ay G D_ay
+// and M is the RAW image.  cp.async writes it straight into the swizzled tile (no staging buffer, no scatter pass: the
+// scatter and its offset / weight loads were 13 % of the other kernel), two tiles per warp so that the next image
+// streams in under the whole of the current image's 800 DMMAs.
+template <int NT, int SWZ>
+__global__ void __launch_bounds__(kSepWarps * 32, 1) sep_quad_full_kernel(const SepQuadArgs a) {
+  constexpr int NP = 8 * NT;
+  extern __shared__ __align__(16) double sm[];
+  double* sGx = sm;                // NP x NP each, same swizzled layout as the image tiles
+  double* sGy = sGx + NP * NP;
+  double* sLin = sGy + NP * NP;
+  double* sLin2 = sLin + NP;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* sMw = sLin + 2 * NP + (size_t)warp * 2 * NP * NP;    // two NP x NP tiles
+
+  for (int e = tid; e < NP; e += blockDim.x) {
+    const double l = (e < a.n) ? lin_coord_dev(e, a.n) : 0.0;
+    sLin[e] = l;
+    sLin2[e] = l * l;
+  }
+  for (int e = tid; e < NP * NP; e += blockDim.x) {
+    const int r = e / NP, c = e % NP;
+    double vx = 0.0, vy = 0.0;
+    if (r < a.n && c < a.n) {
+      const double lr = lin_coord_dev(r, a.n), lc = lin_coord_dev(c, a.n);
+      const double d = lc - lr;
+      const double gv = exp(-a.er * (d * d));
+      vx = gv * (exp(-a.eb * (lr - a.ex) * (lr - a.ex)) * exp(-a.eb * (lc - a.ex) * (lc - a.ex)));
+      vy = gv * (exp(-a.eb * (lr - a.ey) * (lr - a.ey)) * exp(-a.eb * (lc - a.ey) * (lc - a.ey)));
     }
+    sGx[midx<NT, SWZ>(r, c)] = vx;
+    sGy[midx<NT, SWZ>(r, c)] = vy;
+  }
+  for (int e = lane; e < 2 * NP * NP; e += 32) sMw[e] = 0.0;   // padding rows / columns stay zero
+  __syncthreads();
+
+  const long stride = (long)gridDim.x * kSepWarps;
+  const int half = a.n >> 1;
+  auto prefetch = [&](long img, double* dst) {
+    const double* xr = a.X + img * a.ldx;
+    int r = lane / half, c = lane - r * half;                  // 16-byte chunk c of row r
+    for (int e = lane; e < a.n * half; e += 32) {
+      cp_async16(dst + midx<NT, SWZ>(r, 2 * c), xr + 2 * e, 16);
+      c += 32;
+      while (c >= half) { c -= half; ++r; }
+    }
+    cp_async_commit();
+  };
+  long img = (long)blockIdx.x * kSepWarps + warp;
+  int buf = 0;
+  if (img < a.nrows) prefetch(img, sMw);
+  for (; img < a.nrows; img += stride, buf ^= 1) {
+    cp_async_wait<0>();
+    __syncwarp();
+    if (img + stride < a.nrows) prefetch(img + stride, sMw + (buf ^ 1) * NP * NP);
+    const double* sM = sMw + buf * NP * NP;
+    double y0 = 0.0, y1 = 0.0, y2 = 0.0, y3 = 0.0, x0 = 0.0, x1 = 0.0, x2 = 0.0, x3 = 0.0;
+    chain<NT, false, SWZ>(sM, sGx, sGy, sLin, sLin2, lane, y0, y1, y2, y3);
+    chain<NT, true, SWZ>(sM, sGy, sGx, sLin, sLin2, lane, x0, x1, x2, x3);
+    __syncwarp();
+    sep_store(a, img, lane, y0, y1, y2, y3, x0, x1, x2, x3);
   }
 }
 
 template <int NT>
 cudaError_t launch_sep(const SepQuadArgs& a, cudaStream_t st) {
   constexpr int NP = 8 * NT, LD = NP + 4;
+  if (a.full && a.p == a.n * a.n && (a.n & 1) == 0 && (a.ldx % 2 == 0) && (reinterpret_cast<uintptr_t>(a.X) % 16 == 0)) {
+    constexpr int SWZ = (NT & 1) ? 1 : 2;
+    const size_t smem_f = (size_t)(2 * NP * NP + 2 * NP + kSepWarps * 2 * NP * NP) * sizeof(double);
+    if (smem_f <= 232448) {
+      cudaError_t e = cudaFuncSetAttribute(sep_quad_full_kernel<NT, SWZ>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)smem_f);
+      if (e != cudaSuccess) return e;
+      long nb = (a.nrows + kSepWarps - 1) / kSepWarps;
+      const long cap = a.max_ctas > 0 ? a.max_ctas : 148;
+      if (nb > cap) nb = cap;
+      note_launch();
+      sep_quad_full_kernel<NT, SWZ><<<(unsigned)nb, kSepWarps * 32, smem_f, st>>>(a);
+      return cudaGetLastError();
+    }
+  }
   size_t smem = (size_t)(NP * LD + 4 * NP + kSepWarps * NP * LD) * sizeof(double);
   // staging buffers for the cp.async prefetch, if the rows are 16-byte aligned and everything fits in 227 KB
   int pstage = (a.p + 1) & ~1;
