@@ -48,11 +48,18 @@ __device__ __forceinline__ int midx(int row, int col) {
 
 // G: second operand of the first product; GW: the matrix the second product is weighted with (the same matrix when the
 // receptive-field weights are already in M; D_x G D_x / D_y G D_y when M is the raw image, see sep_quad_full_kernel).
-template <int NT, bool TR, int RB, int SWZ>
-__device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M, const double* __restrict__ G,
+// I0 (first row tile of the group) is a template parameter: which tiles of the symmetric second product are live is
+// then known at compile time, and groups with few live tiles (<= 5: the first pair and a trailing single row tile)
+// split their accumulators by k-half (h) -- twice as many independent DMMA chains of half the length where the
+// dependency latency of the chain, not the pipe, was the limiter (ncu: 44 % of the samples on fixed-latency waits).
+template <int NT, bool TR, int RB, int SWZ, int I0>
+__device__ __forceinline__ void chain_rows(const double* __restrict__ M, const double* __restrict__ G,
                                            const double* __restrict__ GW,
                                            const double* __restrict__ lin, const double* __restrict__ lin2, int lane,
                                            double& T0, double& T1, double& T2, double& T3) {
+  constexpr int i0 = I0;
+  constexpr int LIVE = (RB == 2) ? (2 * I0 + 3) : (I0 + 1);
+  constexpr int NS = (LIVE <= 3) ? 4 : ((LIVE <= 7) ? 2 : 1);
   const int g = lane >> 2, t = lane & 3;
   double P[RB][NT][2];
 #pragma unroll
@@ -75,11 +82,13 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
   }
   // S = P M^T (resp. P M) is symmetric: only the tiles on and below the diagonal are formed (15 of 25 at n = 40);
   // a tile below the diagonal stands for its mirror image too, through the weights of the sums further down.
-  double S[RB][NT][2];
+  double S[NS][RB][NT][2];
 #pragma unroll
-  for (int r = 0; r < RB; ++r)
+  for (int z = 0; z < NS; ++z)
 #pragma unroll
-    for (int j = 0; j < NT; ++j) S[r][j][0] = S[r][j][1] = 0.0;
+    for (int r = 0; r < RB; ++r)
+#pragma unroll
+      for (int j = 0; j < NT; ++j) S[z][r][j][0] = S[z][r][j][1] = 0.0;
 #pragma unroll
   for (int jk = 0; jk < NT; ++jk) {
 #pragma unroll
@@ -100,7 +109,7 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
           const double bf = TR ? M[midx<NT, SWZ>(k, 8 * jn + g)] : M[midx<NT, SWZ>(8 * jn + g, k)];
 #pragma unroll
           for (int r = 0; r < RB; ++r)
-            if (jn <= i0 + r) dmma884(S[r][jn][0], S[r][jn][1], af[r], bf);
+            if (jn <= i0 + r) dmma884(S[(2 * jk + h) % NS][r][jn][0], S[(2 * jk + h) % NS][r][jn][1], af[r], bf);
         }
       }
     }
@@ -122,7 +131,10 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
         const double2 gg = *reinterpret_cast<const double2*>(GW + midx<NT, SWZ>(a, b));
         const double2 lb = *reinterpret_cast<const double2*>(lin + b);
         const double2 lb2 = *reinterpret_cast<const double2*>(lin2 + b);
-        const double e0 = S[r][jn][0] * (gg.x * w), e1 = S[r][jn][1] * (gg.y * w);
+        double s0 = S[0][r][jn][0], s1 = S[0][r][jn][1];
+#pragma unroll
+        for (int z = 1; z < NS; ++z) { s0 += S[z][r][jn][0]; s1 += S[z][r][jn][1]; }
+        const double e0 = s0 * (gg.x * w), e1 = s1 * (gg.y * w);
         const double d0 = la - lb.x, d1 = la - lb.y;
         T0 += e0 + e1;
         T1 = fma(e0 * d0, d0, fma(e1 * d1, d1, T1));
@@ -133,14 +145,25 @@ __device__ __forceinline__ void chain_rows(int i0, const double* __restrict__ M,
   }
 }
 
+template <int NT, bool TR, int SWZ, int I0>
+__device__ __forceinline__ void chain_from(const double* __restrict__ M, const double* __restrict__ G,
+                                           const double* __restrict__ GW, const double* __restrict__ lin,
+                                           const double* __restrict__ lin2, int lane, double& T0, double& T1,
+                                           double& T2, double& T3) {
+  if constexpr (I0 + 1 < NT) {
+    chain_rows<NT, TR, 2, SWZ, I0>(M, G, GW, lin, lin2, lane, T0, T1, T2, T3);
+    chain_from<NT, TR, SWZ, I0 + 2>(M, G, GW, lin, lin2, lane, T0, T1, T2, T3);
+  } else if constexpr (I0 < NT) {
+    chain_rows<NT, TR, 1, SWZ, I0>(M, G, GW, lin, lin2, lane, T0, T1, T2, T3);
+  }
+}
+
 template <int NT, bool TR, int SWZ = 0>
 __device__ __forceinline__ void chain(const double* __restrict__ M, const double* __restrict__ G,
                                       const double* __restrict__ GW,
                                       const double* __restrict__ lin, const double* __restrict__ lin2, int lane,
                                       double& T0, double& T1, double& T2, double& T3) {
-#pragma unroll 1
-  for (int i0 = 0; i0 + 1 < NT; i0 += 2) chain_rows<NT, TR, 2, SWZ>(i0, M, G, GW, lin, lin2, lane, T0, T1, T2, T3);
-  if (NT & 1) chain_rows<NT, TR, 1, SWZ>(NT - 1, M, G, GW, lin, lin2, lane, T0, T1, T2, T3);
+  chain_from<NT, TR, SWZ, 0>(M, G, GW, lin, lin2, lane, T0, T1, T2, T3);
 }
 
 // Per-image results from the eight per-lane sums of the two chains (see chain_rows).
