@@ -217,7 +217,11 @@ __global__ void __launch_bounds__(256, (CM <= 4) ? 2 : 1) acos_backward_kernel(d
   __shared__ double rowred[8][kBwdRows];
   __shared__ double red[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const long r0 = (long)blockIdx.x * kBwdRows;
+  // persistent blocks: each walks row chunks blockIdx.x, blockIdx.x + gridDim.x, ... and keeps its column sums / maxima
+  // in registers across them, so the per-block column partials that the follow-up reductions read are <= 296 rows
+  // instead of one per 64 images (those reductions were ~20 us each, eight per evaluation)
+  const long nchunks = (n + kBwdRows - 1) / kBwdRows;
+  long r0 = (long)blockIdx.x * kBwdRows;
   double ck[CM], cy[CM], bbj[CM], nbj[CM], mr[CM], mw[CM];
 #pragma unroll
   for (int c = 0; c < CM; ++c) {
@@ -248,6 +252,8 @@ __global__ void __launch_bounds__(256, (CM <= 4) ? 2 : 1) acos_backward_kernel(d
       }
     }
   };
+  for (long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+  r0 = chunk * kBwdRows;
   load_batch(0, gv, cv, kv, ui, vi, nai);
   for (int rr0 = 0; rr0 < kBwdRows; rr0 += RU) {
     if (r0 + rr0 >= n) break;
@@ -295,6 +301,8 @@ __global__ void __launch_bounds__(256, (CM <= 4) ? 2 : 1) acos_backward_kernel(d
       rowout[i] = ((MODE == 0) ? v[i] : 0.0) + 0.5 * rho / na[i];
     }
   }
+  __syncthreads();    // rowred is reused by the next chunk
+  }
 #pragma unroll
   for (int c = 0; c < CM; ++c) {
     const int j = tid + c * 256;
@@ -311,7 +319,7 @@ __global__ void __launch_bounds__(256, (CM <= 4) ? 2 : 1) acos_backward_kernel(d
   if (tid == 0) sumpart[blockIdx.x] = sumR;
 }
 
-int acos_backward_blocks(long n) { return cdiv(n, kBwdRows); }
+int acos_backward_blocks(long n) { const long c = cdiv(n, kBwdRows); return (int)(c < 296 ? c : 296); }
 
 template <int MODE>
 static void acos_backward_launch(int nblk, double* G, const double* cosm, const double* Kmat, long ld, long n, int m,
