@@ -65,7 +65,7 @@ void acos_forward(double* K, double* cosm, long ld, long n, int m, const double*
 // G is overwritten with R = GK*P.  rowout_i = (mode0 ? v_i : 0) + 0.5*rho_i/na_i,
 // colpart_k[blk][j] = sum_{i in blk} GK_ij Q_ij na_i ; colpart_y[blk][j] = sum_i Kmat_ij u_i (mode 0)
 // sumpart[blk] = sum R.   Requires m <= kBwdMaxCols.
-constexpr int kBwdRows = 64;
+constexpr int kBwdRows = 32;
 constexpr int kBwdMaxCols = 2048;
 int acos_backward_blocks(long n);
 void acos_backward(int mode, double* G, const double* cosm, const double* Kmat, long ld, long n, int m,
