@@ -475,7 +475,9 @@ oz_exps_from_colmax_kernel(const double* __restrict__ part, int nblk, int cols, 
 // Slices of X^T: output row = column c of X (rows x cols), K runs over the rows of X.  One block transposes a
 // 64 (rows of X) x 64 (columns) tile through shared memory; thread (quarter, c) turns 16 consecutive k of column c
 // into one 16-byte store per slice.
-__global__ void __launch_bounds__(256)
+// 4 blocks per SM (64 registers): the kernel is latency-bound between its two barriers per tile; at 78 registers / 3
+// blocks the two transposed slicings of a slab took 180 us each, with 4 blocks 165 (stage times 0.71 -> 0.69, 0.31 -> 0.29 ms)
+__global__ void __launch_bounds__(256, 4)
 oz_slice_cols_kernel(const double* __restrict__ X, long ldx, long rows, int cols, int S, int8_t* __restrict__ q,
                      int ldk, long pair_stride, const int* __restrict__ exps, const double* __restrict__ rowsq) {
   __shared__ double tile[64][65];
