@@ -107,6 +107,23 @@ def test_closure_projected_basis_moments(name, path, slab):
     check(fx, out)
 
 
+@pytest.mark.parametrize("name", ["closure_c1_dense", "closure_c1_local", "closure_dense_n8"])
+def test_closure_four_slices_fp32_class(name):
+    """i8_slices = 4 (27 bits per operand, above fp32's 24; 10 slice pairs instead of 36): the reduced-precision setting.
+    north_star's bar for fp32 arithmetic is 1e-4 relative; checked here on the well-conditioned fixtures."""
+    fx, out = run_case(name, path=2, i8=4)
+    tol = 1e-4
+    assert out["flags"] == 0
+    assert abs(out["loglik"] - float(fx["loglik"])) <= tol * abs(float(fx["loglik"]))
+    keys = [str(k) for k in fx["theta_keys"]]
+    ref = fx["dloglik"] - fx["dKL"]
+    got = np.array([out["grad"][k] for k in keys])
+    scale = max(np.abs(fx["dloglik"]).max(), np.abs(fx["dKL"]).max())
+    assert np.abs(got - ref).max() <= tol * scale, (got, ref)
+    assert np.allclose(out["lam_m"].cpu().numpy(), fx["lam_m"], rtol=tol, atol=1e-6)
+    assert np.allclose(out["f"].cpu().numpy(), fx["f"], rtol=tol, atol=0)
+
+
 def test_closure_int8_slices_cached_and_invalidate():
     """The persistent slices of the images are reused across calls and rebuilt after sgp_invalidate_cache."""
     from gaussian_processes_b200 import native
