@@ -927,7 +927,20 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       xtq_s = (int8_t*)h->xtq.p + (size_t)oz_si * oz_pairs * p * ldkN;
       xte_s = (int*)h->xte.p + oz_si * p;
       if (oz_reslice) CU(oz_slice_rows(Xs, ldxs, ns, p, ozS, xq_s, ldkP, xe_s, st));
-      CU(oz_gemm(xq_s, xe_s, ns, zuq, zue, m, p, ldkP, ozS, Ks, ldm, 1, 0, 0, st));
+      // The persistent product leaves no room for the chain's kernels on an SM it occupies, so when the chain is longer
+      // than the quadratic forms it hides behind (large q: its q x q x m GEMMs grow as q^2 m; or a short first slab) the
+      // product of the first slab leaves the same 20 SMs free: +15 % on this launch instead of a stall of the whole
+      // main stream at the join.  Estimates from the measured config-2 times (chain 1.3 ms at q = m = 500, quadratic
+      // forms 1.3 ms per 65 536 images of 40 x 40).  m = 1000, N = 50 000: 11.06 -> 10.15 ms per evaluation.
+      // SGP_CHAIN_XUC=0/1 overrides (A/B measurements).
+      static const int env_xuc = getenv("SGP_CHAIN_XUC") ? atoi(getenv("SGP_CHAIN_XUC")) : -1;
+      bool reserve = false;
+      if (chain_overlap && slab_i == 0) {
+        const double chain_ms = 1.3 * (q / 500.0) * (q / 500.0) * (m / 500.0);
+        const double quad_ms = 1.3 * ((double)ns / 65536.0) * (n / 40.0) * (n / 40.0) * (n / 40.0);
+        reserve = env_xuc >= 0 ? env_xuc != 0 : chain_ms > 1.15 * quad_ms;
+      }
+      CU(oz_gemm(xq_s, xe_s, ns, zuq, zue, m, p, ldkP, ozS, Ks, ldm, 1, 0, 0, st, nullptr, reserve ? 148 - 20 : 0));
     } else {
       CU(gemm(st, 0, 0, kStore, false, 1, g2));
     }
