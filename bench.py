@@ -314,6 +314,26 @@ def secondary_metrics(native, dev, X, r, xt, Cm, mask, theta, B, ev_keep, m_b, V
             del Cv, Ktv, evecv, Bv
         except Exception as e:  # pragma: no cover
             out["theta_variants"][name] = {"error": repr(e)}
+    # config-3-sized evaluation (BASELINE configs[2]: N = 50 000, inducing set grown to m = 1000): the q x q chain is 8x
+    # the config-2 one and no longer hides behind the quadratic forms (long chains)
+    try:
+        n3, m3 = min(50000, X.shape[0]), min(1000, X.shape[0])
+        X3, r3, xt3 = X[:n3], r[:n3], X[:m3].contiguous()
+        Kt3 = native.acosker(theta["sigma_0"], xt3, xt3, Cm, True)
+        ev3, evec3 = torch.linalg.eigh(Kt3, UPLO="L")
+        kp3 = ev3 > max(float(ev3.max()) * 1e-4, 1e-4)
+        B3 = evec3[:, kp3].contiguous()
+        mb3, Vb3 = synth.make_variational_state(torch.diag(ev3[kp3]).cpu(), CFG + 1)
+        mb3, Vb3 = mb3.to(dev), Vb3.to(dev)
+        res3 = {}
+        t3 = timed(lambda: res3.update(native.elbo_grad(X3, r3, xt3, n_side, theta, B3, mb3, Vb3, logA, lambda0)),
+                   reps=5, warm=2)
+        out["config3_size"] = {"N": n3, "m": m3, "q": int(B3.shape[1]), "ms": t3 * 1e3, "evals_per_sec": 1.0 / t3,
+                               "flags": int(res3.get("flags", -1))}
+        del Kt3, evec3, B3, Vb3
+        native.invalidate_cache(dev.index or 0)
+    except Exception as e:  # pragma: no cover
+        out["config3_size"] = {"error": repr(e)}
     # precision / throughput knob of the int8-slice products: S digits of 7 bits per fp64 operand (S = 8: DGEMM error
     # class, the default and the headline; S = 4: 27 bits, above fp32's 24).  Error = against the S = 8 result.
     try:
