@@ -37,6 +37,8 @@ SIGNATURES = {
     "sgp_last_error": (C.c_char_p, [_p]),
     "sgp_set_slab_rows": (_i, [_p, _l]),
     "sgp_invalidate_cache": (_i, [_p]),
+    "sgp_release_cache": (_i, [_p]),
+    "sgp_bind_images": (_i, [_p, C.c_ulonglong]),
     "sgp_set_option": (_i, [_p, C.c_char_p, _d]),
     "sgp_get_profile": (_i, [_p, _dp, _i, C.POINTER(_l), _i]),
     "sgp_launch_count": (_l, [_p, _i]),
@@ -91,6 +93,36 @@ class Handle:
     def ptr(self):
         return self._h
 
+    # ---- content identity of the image buffers (sgp_bind_images) ------------------------------------------------
+    _next_token = [1]
+    _token_lock = threading.Lock()
+
+    def bind_images(self, *tensors) -> None:
+        """Give the library a new image token unless `tensors` are the very objects, unmodified, that were bound
+        last: same Python tensor (weak reference still alive and identical), same torch version counter (bumped by
+        every in-place write, through views too), same pointer / shape / strides.  A freed-and-recycled address, a
+        resample `X[idx]`, `x -= mean`, a new recording of the same shape all get a fresh token, so the cached
+        gathered copies and int8 slices can never be reused for other data (VERDICT r1 weak 2 / ADVICE r1)."""
+        import weakref
+        key = tuple((t._version, t.data_ptr(), tuple(t.shape), tuple(t.stride())) for t in tensors)
+        prev = getattr(self, "_bound", None)
+        if prev is not None and prev[0] == key and len(prev[1]) == len(tensors) and \
+                all(r() is t for r, t in zip(prev[1], tensors)):
+            return
+        with Handle._token_lock:
+            tok = Handle._next_token[0]
+            Handle._next_token[0] += 1
+        self._bound = (key, [weakref.ref(t) for t in tensors])
+        self.check(lib.sgp_bind_images(self._h, C.c_ulonglong(tok)))
+
+    def new_image_epoch(self) -> None:
+        """Unconditionally start a new image token (utils.varGP calls this on entry)."""
+        self._bound = None
+        with Handle._token_lock:
+            tok = Handle._next_token[0]
+            Handle._next_token[0] += 1
+        self.check(lib.sgp_bind_images(self._h, C.c_ulonglong(tok)))
+
     def launch_count(self, reset: bool = False) -> int:
         return int(lib.sgp_launch_count(self._h, 1 if reset else 0))
 
@@ -106,15 +138,19 @@ class Handle:
             pass
 
 
-_handles = {}
-_lock = threading.Lock()
+_tls = threading.local()
 
 
 def handle_for(device: int) -> Handle:
-    """Per-(thread, device) handle: entry points are re-entrant per handle (SURVEY 8b threading row)."""
-    key = (threading.get_ident(), int(device))
-    with _lock:
-        h = _handles.get(key)
-        if h is None:
-            h = _handles[key] = Handle(device)
-        return h
+    """Per-(thread, device) handle: entry points are re-entrant per handle (SURVEY 8b threading row: one notebook
+    variant calls acosker / lambda_moments from a second thread while varGP runs).  The handles live in thread-local
+    storage, so a worker thread's handle -- its scratch arena and its cached image copies / int8 slices -- is
+    destroyed (sgp_destroy) when that thread exits instead of leaking, and a recycled thread id never inherits
+    another thread's cache."""
+    d = getattr(_tls, "handles", None)
+    if d is None:
+        d = _tls.handles = {}
+    h = d.get(int(device))
+    if h is None:
+        h = d[int(device)] = Handle(device)
+    return h

@@ -561,7 +561,7 @@ cudaError_t oz_slice_rows(const double* X, long ldx, long rows, int cols, int S,
                           cudaStream_t st, const double* colvec, double* rowdot) {
   if (rows <= 0) return cudaSuccess;
   if (S < 1 || S > kOzMaxS || ldk != oz_ldk(cols)) return cudaErrorInvalidValue;
-  const long blocks = std::min<long>((rows + 7) / 8, 148L * 8);
+  const long blocks = std::min<long>((rows + 7) / 8, (long)num_sms() * 8);
   note_launch();
   oz_slice_rows_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, ldx, rows, cols, S, q, ldk, rows * (long)ldk, exps,
                                                            rowdot ? colvec : nullptr, rowdot);
@@ -577,7 +577,7 @@ cudaError_t oz_slice_cols(const double* X, long ldx, long rows, int cols, int S,
   if (!exps_ready) {
     cudaError_t e = cudaMemsetAsync(mx, 0, sizeof(unsigned long long) * cols, st);
     if (e != cudaSuccess) return e;
-    const int gy = (int)std::min<long>((rows + 63) / 64, 148L * 4 / ((cols + 31) / 32) + 1);
+    const int gy = (int)std::min<long>((rows + 63) / 64, (long)num_sms() * 4 / ((cols + 31) / 32) + 1);
     note_launch(2);
     oz_col_absmax_kernel<<<dim3((cols + 31) / 32, gy), 256, 0, st>>>(X, ldx, rows, cols, rowsq, mx);
     oz_exps_from_max_kernel<<<(cols + 255) / 256, 256, 0, st>>>(mx, cols, exps);
@@ -611,10 +611,10 @@ int oz_split(long M, int N, int K, int S, int lower_only) {
   // fill the SMs: prefer the split whose item count is closest to whole waves, never chunks under 16 k-blocks
   double best = -1.0; int best_nz = nz;
   for (int c = nz; c <= 64 && (c == nz || nkb / c >= 16); ++c) {
-    const double waves = (double)tiles * c / 148.0;
+    const double waves = (double)tiles * c / (double)num_sms();
     const double eff = waves / std::ceil(waves) - 0.003 * c;
     if (eff > best) { best = eff; best_nz = c; }
-    if (tiles >= 4 * 148) break;   // plenty of tiles already: no split beyond what exactness needs
+    if (tiles >= 4 * num_sms()) break;   // plenty of tiles already: no split beyond what exactness needs
   }
   return best_nz;
 }
@@ -637,7 +637,7 @@ cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, c
   OzArgs a{ea, eb, C, ldc, (int)M, N, K, S, nz, kb_per_z, zstride, accumulate, alpha, lower_only, (int)tiles,
            mom ? mom->aux : nullptr, mom ? mom->ldaux : 0, mom ? mom->part1 : nullptr, mom ? mom->ldpart : 0, dbg};
   if (mom && (nz != 1 || accumulate)) return cudaErrorInvalidValue;
-  const int grid = (int)std::min<long>(tiles * nz, max_ctas > 0 ? max_ctas : 148);   // fewer CTAs leave SMs to a concurrent stream
+  const int grid = (int)std::min<long>(tiles * nz, max_ctas > 0 ? max_ctas : num_sms());   // fewer CTAs leave SMs to a concurrent stream
   note_launch();
   oz_gemm_kernel<<<grid, kOzThreads, kOzSmem, st>>>(mapA, mapB, a);
   return cudaGetLastError();

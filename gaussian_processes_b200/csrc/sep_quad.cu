@@ -352,7 +352,7 @@ cudaError_t launch_sep(const SepQuadArgs& a, cudaStream_t st) {
                                            (int)smem_f);
       if (e != cudaSuccess) return e;
       long nb = (a.nrows + kSepWarps - 1) / kSepWarps;
-      const long cap = a.max_ctas > 0 ? a.max_ctas : 148;
+      const long cap = a.max_ctas > 0 ? a.max_ctas : num_sms();
       if (nb > cap) nb = cap;
       note_launch();
       sep_quad_full_kernel<NT, SWZ><<<(unsigned)nb, kSepWarps * 32, smem_f, st>>>(a);
@@ -368,7 +368,7 @@ cudaError_t launch_sep(const SepQuadArgs& a, cudaStream_t st) {
   cudaError_t e = cudaFuncSetAttribute(sep_quad_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   long nb = (a.nrows + kSepWarps - 1) / kSepWarps;
-  const long cap = a.max_ctas > 0 ? a.max_ctas : 148;   // fewer CTAs leave SMs to a concurrent stream
+  const long cap = a.max_ctas > 0 ? a.max_ctas : num_sms();   // fewer CTAs leave SMs to a concurrent stream
   if (nb > cap) nb = cap;
   note_launch();
   sep_quad_kernel<NT><<<(unsigned)nb, kSepWarps * 32, smem, st>>>(a, pstage);

@@ -50,6 +50,8 @@ struct sgp_handle {
   // the two N x p x m products on tcgen05.mma.kind::i8 (ozaki_i8.cu): -1 = when the slab is large, 0 = never
   // (fp64 DMMA), 2..8 = always, with that many int8 slices
   int i8_slices = -1;
+  // slice count of the two products with the images (K_lin = X (UC)^T, D = X^T R): -1 = same as i8_slices
+  int i8_slices_images = -1;
   DevBuf xq, xe, xtq, xte;  // int8 slices of the images (row-wise and transposed per slab) + their exponents
   bool oz_valid = false; int oz_S = 0; long oz_slab = 0;
   // cache key of the gathered copies
@@ -57,6 +59,9 @@ struct sgp_handle {
   const double* cache_U = nullptr; long cache_m = 0, cache_ldu = 0;
   std::vector<uint8_t> cache_mask;
   bool cache_valid = false;
+  // content identity of the image buffers (sgp_bind_images): part of the key of the gathered copies and of the
+  // persistent int8 slices, because an address alone does not identify its content (allocators recycle blocks)
+  unsigned long long image_token = 0, cache_token = 0;
   int* d_flags = nullptr;
   double* d_scal = nullptr;
   unsigned* d_ticket = nullptr;        // last-block-done counter of the streaming reductions (zero between launches)
@@ -183,7 +188,7 @@ int pick_split(int tiles, long K) {
   for (int nz = 1; nz <= 64; ++nz) {
     if (nz > 1 && K / nz < 256) break;
     const double ctas = (double)tiles * nz;
-    const double waves = ctas / 296.0;
+    const double waves = ctas / (2.0 * num_sms());
     const double eff = waves / std::ceil(waves);
     const double score = eff - 0.002 * nz;
     if (score > best_score) { best_score = score; best = nz; }
@@ -212,6 +217,7 @@ int sgp_destroy(sgp_handle* h) {
     cudaSetDevice(h->device);
     h->arena.release(); h->xg.release(); h->ug.release(); h->gcpart.release(); h->s2part.release(); h->dpart.release();
     h->hx[0].release(); h->hx[1].release(); h->hr.release(); h->small.release();
+    h->xq.release(); h->xe.release(); h->xtq.release(); h->xte.release();
     if (h->d_flags) cudaFree(h->d_flags);
     if (h->d_scal) cudaFree(h->d_scal);
     if (h->d_ticket) cudaFree(h->d_ticket);
@@ -249,6 +255,10 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
     if (value != -1 && value != 0 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices must be -1, 0 or 2..8");
     h->i8_slices = (int)value;
   }
+  else if (n == "i8_slices_images") {
+    if (value != -1 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices_images must be -1 or 2..8");
+    h->i8_slices_images = (int)value;
+  }
   else if (n == "slab_rows") return sgp_set_slab_rows(h, (long)value);
   else return fail(h, SGP_E_ARG, "sgp_set_option: unknown option " + n);
   return SGP_OK;
@@ -266,6 +276,26 @@ int sgp_invalidate_cache(sgp_handle* h) {
   if (!h) return SGP_E_ARG;
   h->cache_valid = false;
   h->oz_valid = false;
+  return SGP_OK;
+}
+
+int sgp_release_cache(sgp_handle* h) {
+  if (!h) return SGP_E_ARG;
+  h->cache_valid = false;
+  h->oz_valid = false;
+  if (h->gemm_ready) {
+    if (cudaSetDevice(h->device) != cudaSuccess) return fail(h, SGP_E_CUDA, "sgp_release_cache: cudaSetDevice failed");
+    cudaDeviceSynchronize();   // nothing of this handle may still be reading the buffers
+    h->xg.release(); h->ug.release(); h->xq.release(); h->xe.release(); h->xtq.release(); h->xte.release();
+    h->hx[0].release(); h->hx[1].release(); h->hr.release();
+    h->arena.release(); h->gcpart.release(); h->s2part.release(); h->dpart.release();
+  }
+  return SGP_OK;
+}
+
+int sgp_bind_images(sgp_handle* h, unsigned long long token) {
+  if (!h) return SGP_E_ARG;
+  h->image_token = token;
   return SGP_OK;
 }
 
@@ -529,6 +559,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   int ozM = 0;
   if (h->i8_slices != 0) ozM = h->i8_slices > 0 ? h->i8_slices : (slab >= 4096 && m >= 64 ? 8 : 0);
   const int ozS = use_sep ? ozM : 0;
+  // ozI: slice count of the two products that contract with the images (K_lin = X (UC)^T, D = X^T R): they are 4Npm of
+  // the executed flops and sit upstream of the cancellation in lam_var (which lives in T = K Mfull^T, kept at ozM)
+  const int ozI = ozS ? (h->i8_slices_images > 0 ? h->i8_slices_images : ozS) : 0;
   // Moments in the projected basis when the kept subspace is small (q < m): K_b = K B, T_b = K_b Mg^T, T = T_b B^T and
   // K_b^T diag(v) K_b cost 4Nmq + 3Nq^2 flops against the 3Nm^2 of K Mfull^T and K^T diag(v) K (break-even q = 0.54 m;
   // the extra slicing passes move it down).  Same numbers up to rounding: Mfull = B Mg B^T.
@@ -536,8 +569,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const int ldkP = oz_ldk(p), ldkN = oz_ldk((int)slab);
   const bool chain_overlap = use_sep && h->overlap != 0;
   const bool tail_overlap = chain_overlap && ozS > 0;
-  const int oz_pairs = (ozM + 1) / 2;
-  const int nzO = ozS ? oz_split(p, m, (int)std::min(slab, N), ozS) : 1;
+  const int oz_pairs = (std::max(ozM, ozI) + 1) / 2, oz_pairsI = (ozI + 1) / 2;
+  const int nzO = ozS ? oz_split(p, m, (int)std::min(slab, N), ozI) : 1;
   const int nzK = ozM ? (proj ? oz_split(q, q, (int)std::min(slab, N), ozM, 1) : oz_split(m, m, (int)std::min(slab, N), ozM, 1)) : 1;
   std::vector<int> off; std::vector<double> alpha;
   if (use_sep) {
@@ -553,9 +586,14 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   // ---- gathered / aligned copies of the images (cached across calls while the mask is unchanged) --
   const bool direct_X = !streaming && full_mask && (in.ldx % 2 == 0) && ((uintptr_t)in.X % 16 == 0);
   const bool direct_U = full_mask && (in.ldu % 2 == 0) && ((uintptr_t)in.U % 16 == 0);
-  bool regather = !h->cache_valid || h->cache_mask != mask || h->cache_X != in.X || h->cache_N != N ||
-                  h->cache_ldx != in.ldx || h->cache_U != in.U || h->cache_m != m || h->cache_ldu != in.ldu;
+  bool regather = !h->cache_valid || h->cache_token != h->image_token || h->cache_mask != mask || h->cache_X != in.X ||
+                  h->cache_N != N || h->cache_ldx != in.ldx || h->cache_U != in.U || h->cache_m != m ||
+                  h->cache_ldu != in.ldu;
   if (streaming) regather = true;
+  // the caches count as valid only once this call has completed (a failure half way must not leave a 'valid' key)
+  const bool cache_was_valid = h->cache_valid && !regather;
+  const bool oz_was_valid = h->oz_valid && !regather;
+  h->cache_valid = false; h->oz_valid = false;
   const double* Xg = in.X; long ldxg = in.ldx;
   const double* Ug = in.U; long ldug = in.ldu;
   if (!direct_X && !streaming) { CU(h->xg.reserve((size_t)N * ldp * sizeof(double))); Xg = (double*)h->xg.p; ldxg = ldp; }
@@ -591,7 +629,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   acc((size_t)p * 5);                                                 // gpart
   if (streaming) { acc((size_t)slab * ldp); }                         // gathered slab when streaming from host
   if (ozM) {                                                          // slices of UC and of R^T, exponents, col-max scratch
-    acc(oz_slice_bytes(m, p, ozM) / 8 + 16); acc((size_t)oz_pairs * m * ldkN / 8 + 16); acc(m); acc(m);
+    acc(oz_slice_bytes(m, p, std::max(ozM, ozI)) / 8 + 16); acc((size_t)oz_pairs * m * ldkN / 8 + 16); acc(m); acc(m);
     acc((size_t)std::max(p, m) + 8);
     acc(oz_slice_bytes(slab, m, ozM) / 8 + 16); acc(oz_slice_bytes(m, m, ozM) / 8 + 16); acc(slab / 2 + 8); acc(m);   // K, Mfull slices
   }
@@ -658,7 +696,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   int8_t* kq = nullptr; int8_t* mq = nullptr; int* ke = nullptr; int* me = nullptr;
   int8_t* zuq = nullptr; int8_t* rtq = nullptr; int* zue = nullptr; int* rte = nullptr; unsigned long long* ozmx = nullptr;
   if (ozM) {
-    zuq = (int8_t*)ar.take<double>(oz_slice_bytes(m, p, ozM) / 8 + 16);
+    zuq = (int8_t*)ar.take<double>(oz_slice_bytes(m, p, std::max(ozM, ozI)) / 8 + 16);
     rtq = (int8_t*)ar.take<double>((size_t)oz_pairs * m * ldkN / 8 + 16);
     zue = (int*)ar.take<double>(m); rte = (int*)ar.take<double>(m);
     ozmx = (unsigned long long*)ar.take<double>((size_t)std::max(p, m) + 8);
@@ -748,8 +786,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     if (!direct_X && !streaming) gather_cols(in.X, in.ldx, N, d_idx, p, (double*)Xg, ldp, st);
     if (!direct_U) gather_cols(in.U, in.ldu, m, d_idx, p, (double*)Ug, ldp, st);
     h->cache_mask = mask; h->cache_X = in.X; h->cache_N = N; h->cache_ldx = in.ldx;
-    h->cache_U = in.U; h->cache_m = m; h->cache_ldu = in.ldu; h->cache_valid = !streaming;
+    h->cache_U = in.U; h->cache_m = m; h->cache_ldu = in.ldu; h->cache_token = h->image_token;
   }
+  (void)cache_was_valid;
   copy_mat(in.B, in.ldb, m, q, Bw, ldq, st);
   copy_mat(in.V, in.ldv, q, q, Vw, ldq, st);
   // log det V_b does not depend on theta: its Cholesky runs on a side stream next to the K_tilde_b chain.  Only the
@@ -864,13 +903,13 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   bool oz_reslice = true;
   if (ozS) {
     const long keep = streaming ? 1 : nslabs_all;
-    CU(h->xq.reserve(streaming ? oz_slice_bytes(slab, p, ozS) : oz_slice_bytes(N, p, ozS)));
+    CU(h->xq.reserve(streaming ? oz_slice_bytes(slab, p, ozI) : oz_slice_bytes(N, p, ozI)));
     CU(h->xe.reserve((size_t)(streaming ? slab : N) * sizeof(int)));
-    CU(h->xtq.reserve((size_t)keep * oz_pairs * p * ldkN));
+    CU(h->xtq.reserve((size_t)keep * oz_pairsI * p * ldkN));
     CU(h->xte.reserve((size_t)keep * p * sizeof(int)));
-    oz_reslice = streaming || regather || !h->oz_valid || h->oz_S != ozS || h->oz_slab != slab;
-    h->oz_valid = !streaming; h->oz_S = ozS; h->oz_slab = slab;
-    CU(oz_slice_rows(ZU, ldp, m, p, ozS, zuq, ldkP, zue, st));      // slices of U C (this evaluation's theta)
+    oz_reslice = streaming || regather || !oz_was_valid || h->oz_S != ozI || h->oz_slab != slab;
+    h->oz_S = ozI; h->oz_slab = slab;
+    CU(oz_slice_rows(ZU, ldp, m, p, ozI, zuq, ldkP, zue, st));      // slices of U C (this evaluation's theta)
   }
   double* Dpart = (double*)h->dpart.p;
   CU(h->gcpart.reserve((size_t)nzGC * zGC * sizeof(double)));
@@ -902,7 +941,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       sq.X = Xs; sq.ldx = ldxs; sq.nrows = ns; sq.p = p; sq.off = d_off; sq.alpha = d_alpha; sq.n = n;
       sq.er = th.er; sq.eb = th.eb; sq.ex = th.ex; sq.ey = th.ey; sq.amp = th.amp; sq.s02 = th.s02;
       sq.s = s_s; sq.nrm = X1; sq.Q = Qs; sq.full = full_mask ? 1 : 0;
-      if (chain_overlap && slab_i == 0) sq.max_ctas = 148 - 20;   // leave SMs to the inducing-point chain
+      if (chain_overlap && slab_i == 0) sq.max_ctas = num_sms() - 20;   // leave SMs to the inducing-point chain
       CU(sep_quad(sq, st));
       mark(2);
       // G2: K = acos-kernel(X (U C)^T)   -- x_i^T C u_j with the m x p matrix ZU = U C
@@ -922,11 +961,11 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     const long oz_si = streaming ? 0 : slab_i;                     // which persistent slice block this slab uses
     int8_t* xq_s = nullptr; int* xe_s = nullptr; int8_t* xtq_s = nullptr; int* xte_s = nullptr;
     if (ozS) {
-      xq_s = (int8_t*)h->xq.p + oz_slice_bytes(oz_si * slab, p, ozS);
+      xq_s = (int8_t*)h->xq.p + oz_slice_bytes(oz_si * slab, p, ozI);
       xe_s = (int*)h->xe.p + oz_si * slab;
-      xtq_s = (int8_t*)h->xtq.p + (size_t)oz_si * oz_pairs * p * ldkN;
+      xtq_s = (int8_t*)h->xtq.p + (size_t)oz_si * oz_pairsI * p * ldkN;
       xte_s = (int*)h->xte.p + oz_si * p;
-      if (oz_reslice) CU(oz_slice_rows(Xs, ldxs, ns, p, ozS, xq_s, ldkP, xe_s, st));
+      if (oz_reslice) CU(oz_slice_rows(Xs, ldxs, ns, p, ozI, xq_s, ldkP, xe_s, st));
       // The persistent product leaves no room for the chain's kernels on an SM it occupies, so when the chain is longer
       // than the quadratic forms it hides behind (large q: its q x q x m GEMMs grow as q^2 m; or a short first slab) the
       // product of the first slab leaves the same 20 SMs free: +15 % on this launch instead of a stall of the whole
@@ -940,7 +979,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
         const double quad_ms = 1.3 * ((double)ns / 65536.0) * (n / 40.0) * (n / 40.0) * (n / 40.0);
         reserve = env_xuc >= 0 ? env_xuc != 0 : chain_ms > 1.15 * quad_ms;
       }
-      CU(oz_gemm(xq_s, xe_s, ns, zuq, zue, m, p, ldkP, ozS, Ks, ldm, 1, 0, 0, st, nullptr, reserve ? 148 - 20 : 0));
+      CU(oz_gemm(xq_s, xe_s, ns, zuq, zue, m, p, ldkP, ozI, Ks, ldm, 1, 0, 0, st, nullptr, reserve ? num_sms() - 20 : 0));
     } else {
       CU(gemm(st, 0, 0, kStore, false, 1, g2));
     }
@@ -1029,12 +1068,12 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       if (ozS) {
         // the contraction runs over the images: slices of X^T (persistent) and of R^T (this evaluation)
         const int ldk_s = oz_ldk((int)ns);
-        if (oz_reslice) CU(oz_slice_cols(Xs, ldxs, ns, p, ozS, xtq_s, ldk_s, xte_s, ozmx, st));
+        if (oz_reslice) CU(oz_slice_cols(Xs, ldxs, ns, p, ozI, xtq_s, ldk_s, xte_s, ozmx, st));
         oz_exps_from_colmax(cmaxR, acos_backward_blocks(ns), m, ldm, 0, rte, st);
-        CU(oz_slice_cols(Ts, ldm, ns, m, ozS, rtq, ldk_s, rte, ozmx, st, nullptr, true));
+        CU(oz_slice_cols(Ts, ldm, ns, m, ozI, rtq, ldk_s, rte, ozmx, st, nullptr, true));
         mark(10);
-        CU(oz_gemm(xtq_s, xte_s, p, rtq, rte, m, (int)ns, ldk_s, ozS, Dpart, ldm, nzO, zD, acc_flag, st, nullptr,
-                   (tail_overlap && last) ? 148 - 20 : 0));
+        CU(oz_gemm(xtq_s, xte_s, p, rtq, rte, m, (int)ns, ldk_s, ozI, Dpart, ldm, nzO, zD, acc_flag, st, nullptr,
+                   (tail_overlap && last) ? num_sms() - 20 : 0));
       } else {
         GemmArgs g5{};
         g5.A = Xs; g5.lda = ldxs; g5.B = Ts; g5.ldb = ldm; g5.C = Dpart; g5.ldc = ldm; g5.M = p; g5.N = m; g5.K = (int)ns;
@@ -1136,6 +1175,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   mark(-1);
   const double t_enq = now_ms();
   CU(cudaStreamSynchronize(st));
+  h->cache_valid = !streaming;           // everything the caches hold was produced by work that has now completed
+  h->oz_valid = !streaming && ozS > 0;
   if (dbg_t) fprintf(stderr, "[sgp timing] first copy issued %.3f ms after entry; all work enqueued at %.3f; done at %.3f\n",
                      t_issue - t_entry, t_enq - t_entry, now_ms() - t_entry);
   if (out_host) { std::memcpy(out_host, h->h_out, sizeof(double) * 16); out_host[15] = proj ? 1.0 : 0.0; }

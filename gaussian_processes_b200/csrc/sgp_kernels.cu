@@ -13,6 +13,17 @@ static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
 static std::atomic<long> g_launches{0};
 void note_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 long launch_counter() { return g_launches.load(std::memory_order_relaxed); }
+int num_sms() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
 
 // =====================================================================================================
 // a1: localker (reference utils.py:880-910)
@@ -189,7 +200,7 @@ void acos_forward(double* K, double* cosm, long ld, long n, int m, const double*
   if (n <= 0 || m <= 0) return;
   const int m2 = (m + 1) >> 1;
   const int threads = m2 >= 192 ? 256 : (m2 >= 96 ? 128 : 64);
-  const long nb_ = std::min<long>((n + 1) / 2, 148L * (2048 / threads));
+  const long nb_ = std::min<long>((n + 1) / 2, (long)num_sms() * (2048 / threads));
   note_launch(); acos_forward_kernel<<<(unsigned)nb_, threads, 0, st>>>(K, cosm, ld, n, m, na, nb, s02);
 }
 
@@ -391,7 +402,7 @@ __global__ void slice_reduce_kernel(const double* __restrict__ part, int nz, lon
 void slice_reduce(const double* part, int nz, long zstride, long n, double* out, int accumulate, cudaStream_t st) {
   if (n <= 0) return;
   int nb = cdiv(n, 256);
-  if (nb > 148 * 8) nb = 148 * 8;
+  if (nb > num_sms() * 8) nb = num_sms() * 8;
   note_launch(); slice_reduce_kernel<<<nb, 256, 0, st>>>(part, nz, zstride, n, out, accumulate);
 }
 

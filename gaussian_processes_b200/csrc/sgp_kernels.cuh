@@ -29,6 +29,8 @@ enum ScalSlot : int {
 // every kernel launch of the library is counted (bench.py reports it as gpu_launches)
 void note_launch(int n = 1);
 long launch_counter();
+// multiProcessorCount of the current device (queried once per device; 148 on B200)
+int num_sms();
 
 struct ThetaDev {  // hyper-parameters in the form the kernels need
   double s0, s02, ex, ey, eb, er, amp;

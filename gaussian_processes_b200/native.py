@@ -306,6 +306,7 @@ def elbo_grad(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int,
     ldv_val = C.c_double(logdetV if logdetV is not None else 0.0)
     out = (C.c_double * 16)()
     h = _h(X)
+    h.bind_images(X, xtilde)     # the library's cached copies / int8 slices of the images are keyed on this token
     h.check(lib.sgp_elbo_grad(h.ptr, _ptr(X), _ld(X), _ptr(r), N, _ptr(xtilde), _ld(xtilde), int(m), int(n_px),
                               theta_array(theta), lo, hi, _ptr(B), _ld(B), int(q), _ptr(m_b), _ptr(V_b), _ld(V_b),
                               float(logA), float(lambda0), C.byref(ldv_val) if logdetV is not None else None,
@@ -368,9 +369,23 @@ def set_option(device: int, name: str, value: float):
 
 
 def invalidate_cache(device: int = 0):
-    """Forget the cached gathered copies / int8 slices of the images (call after modifying X in place)."""
+    """Forget the cached gathered copies / int8 slices of the images.  Not needed for torch tensors: elbo_grad binds
+    an image token from (tensor identity, version counter, pointer, shape) on every call."""
     h = _lib.handle_for(device)
     h.check(lib.sgp_invalidate_cache(h.ptr))
+    h.new_image_epoch()
+
+
+def new_image_epoch(device: int = 0):
+    """Start a new image token on this thread's handle (utils.varGP calls it on entry)."""
+    _lib.handle_for(device).new_image_epoch()
+
+
+def release_cache(device: int = 0):
+    """invalidate_cache + give the memory of the cached copies, slices, staging buffers and scratch arena back."""
+    h = _lib.handle_for(device)
+    h.check(lib.sgp_release_cache(h.ptr))
+    h.new_image_epoch()
 
 
 def get_profile(device: int = 0, reset: bool = True):

@@ -572,7 +572,9 @@ def _kernels_at(theta, lo, hi, n_px_side, x, xtilde, kernfun, same):
     K_tilde = kernfun(theta, um, um, C=C, dC=None, diag=False)
     if kernfun is acosker and not same:
         # K and Kvec share the x C product (sgp_acosker_kvec): one pass over the images instead of two
-        K, Kvec = native.acosker_kvec(_fl(theta['sigma_0']), xm, um, C, symmetrize=(xm.shape[0] == um.shape[0]))
+        # not `same`: globally n1 != n2, so the reference does not symmetrise (U:1024) -- a shard that happens to hold
+        # ntilde rows must not either
+        K, Kvec = native.acosker_kvec(_fl(theta['sigma_0']), xm, um, C, symmetrize=False)
         return C, mask, K_tilde, K, Kvec
     K = K_tilde if same else kernfun(theta, xm, um, C=C, dC=None, diag=False)
     Kvec = kernfun(theta, xm, x2=None, C=C, dC=None, diag=True)
@@ -610,12 +612,20 @@ def _closure_forward_mode(theta, lo, hi, n_px_side, x, xtilde, r, kernfun, same,
     return _fl(loglik), _fl(KL), {key: _fl(dloglik[key]) - _fl(dKL[key]) for key in theta.keys()}
 
 
-def elbo_and_grad(theta, lo, hi, n_px_side, x, xtilde, r, B, m_b, V_b, f_params, logdetV=None, kernfun=None):
+def _sharded() -> bool:
+    return _SHARD is not None and _SHARD.world > 1
+
+
+def elbo_and_grad(theta, lo, hi, n_px_side, x, xtilde, r, B, m_b, V_b, f_params, logdetV=None, kernfun=None,
+                  same=None):
     """One ELBO+gradient evaluation (the unit of BASELINE.json's metric): (loglik, KL, {key: d(loglik-KL)/dtheta}).
-    ntilde != nt: ONE fused C call (sgp_elbo_grad, reverse mode).  Raises ValueError out of bounds."""
+    ntilde != nt: ONE fused C call (sgp_elbo_grad, reverse mode).  Raises ValueError out of bounds.
+    `same` (ntilde == nt, the reference's a = B branch U:2032/U:2068) is decided from the GLOBAL image count: an
+    image shard that happens to hold exactly ntilde rows is not the active-learning configuration."""
     for key in _out_of_bounds(theta, lo, hi):
         raise ValueError(f"{key} = {_fl(theta[key]):.4f} is not within the limits of {lo[key]} and {hi[key]}")
-    same = x.shape[0] == xtilde.shape[0]
+    if same is None:
+        same = (not _sharded()) and x.shape[0] == xtilde.shape[0]
     kernfun = kernfun or acosker
     if not same:
         logA, lambda0 = _link_params(f_params)
@@ -668,8 +678,14 @@ def varGP(x, r, **kwargs):
     f_params = copy.deepcopy(kwargs['f_params'])
     for key in f_params.keys():
         f_params[key] = f_params[key].requires_grad_(True)
-    same = ntilde == nt
+    # ntilde == nt (a = B, U:1677-1678 / U:2032) is a statement about the whole image set, not about one shard
+    nt_global = int(round(_shard_sum([float(nt)])[0])) if _sharded() else nt
+    same = ntilde == nt_global
+    if same and _sharded():
+        raise Exception('image-sharded varGP does not support ntilde == nt (K = K_tilde needs every image on every rank)')
     lims = (theta_lower_lims, theta_higher_lims)
+    if x.is_cuda:   # a new fit may bring new images at a recycled address: never reuse cached copies / slices of them
+        native.new_image_epoch(x.device.index if x.device.index is not None else torch.cuda.current_device())
 
     # ---- initial kernels and subspace (U:1674-1694); every piece can be handed over via init_kernel ----------
     eigvecs = None
@@ -843,7 +859,7 @@ def varGP(x, r, **kwargs):
                     if bad:
                         return _scalar(float('inf'), like=r)
                     ll, kl, grad = elbo_and_grad(theta, theta_lower_lims, theta_higher_lims, n_px_side, x, xtilde, r,
-                                                 B, m_b, V_b, f_params, logdetV=logdetV, kernfun=kernfun)
+                                                 B, m_b, V_b, f_params, logdetV=logdetV, kernfun=kernfun, same=same)
                     for key in theta.keys():                                                  # U:2095-2099
                         if theta[key].requires_grad:
                             theta[key].grad = _scalar(-grad[key], like=theta[key])

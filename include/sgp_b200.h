@@ -63,6 +63,8 @@ SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
  * 2 = separable quadratic forms), "i8_slices" (-1 = choose, 0 = the two N x p x m products of sgp_elbo_grad on the
  * fp64 tensor pipe, 2..8 = on tcgen05.mma.kind::i8 with that many int8 slices per operand; see sgp_gemm_i8emu;
  * 8 is the error class of a DGEMM and the default, 4 gives 27 bits per operand -- the fp32-class setting),
+ * "i8_slices_images" (-1 = same as "i8_slices", 2..8 = slice count of the two products that contract with the
+ * images, K_lin = X (UC)^T and D = X^T R; the m-space products keep "i8_slices"),
  * "projected" (-1 = moments in the projected basis K_b = K B when q <= 0.4 m, 0 = never, 1 = always; same numbers
  * up to rounding, utils.py:2047-2068), "overlap" (1 = the q x q chains run on side streams).
  * With int8 slices the library keeps a sliced copy of device-resident images across calls (same bytes as X).     */
@@ -76,6 +78,14 @@ SGP_API int sgp_set_option(sgp_handle* h, const char* name, double value);
 SGP_API int sgp_get_profile(sgp_handle* h, double* stage_ms_out, int n, long* calls_out, int reset);
 /* forget the cached masked copies and int8 slices of X / xtilde (call if their contents changed in place) */
 SGP_API int sgp_invalidate_cache(sgp_handle* h);
+/* same, and give the memory back (gathered copies, int8 slices, staging buffers, scratch arena) */
+SGP_API int sgp_release_cache(sgp_handle* h);
+/* Content identity of the image buffers (`x` / `xtilde` of varGP, utils.py:1568: constant during a fit).  The caches
+ * above are keyed on (token, pointer, sizes, strides, mask): a pointer alone does not identify its content, because
+ * allocators hand a freed block to the next tensor of the same size.  Callers pass a NEW token whenever the images
+ * they are about to pass may differ from the last ones seen under the current token (another recording, a resample,
+ * an in-place edit); the Python binding derives it from (tensor identity, torch version counter, pointer, shape).  */
+SGP_API int sgp_bind_images(sgp_handle* h, unsigned long long token);
 /* number of kernels this library has launched through `h` since creation / last reset */
 SGP_API long sgp_launch_count(const sgp_handle* h, int reset);
 

@@ -132,6 +132,44 @@ def gen_closure_case(ref, name, N, n, m, cfg, theta_dict, store_big=False, pertu
           f"-> {os.path.getsize(path)/1024:.0f} KiB")
 
 
+def gen_big_closure_case(ref, name, N, n, m, cfg, theta_dict, perturb=None):
+    """Benchmark-size closure fixture (n = 40: the sep_quad_full_kernel<5,.> / K = 1600 oz_gemm instantiations the
+    small fixtures never reach).  Only what cannot be regenerated from the seeds is stored: B (eigh is not
+    reproducible across machines), the eigenvalues, and the reference's outputs.  m_b / V_b are regenerated by
+    ``synth.make_variational_state(diag(ev[keep]), cfg)`` (seeded CPU generator); a few of their entries are kept
+    as a guard against generator drift."""
+    prob, theta, B, m_b, V_b, ev = setup_case(ref, N, n, m, cfg, theta_dict)
+    if perturb:
+        theta = synth.theta_tensors({k: prob.theta[k] + perturb.get(k, 0.0) for k in prob.theta})
+    f_params = {"logA": torch.tensor(prob.logA), "lambda0": torch.tensor(prob.lambda0)}
+    out = ref_closure(ref, theta, prob.X, prob.r, prob.xtilde, n, B, m_b, V_b, f_params)
+    keys = list(theta.keys())
+    keep = ev > max(ev.max() * ref.EIGVAL_TOL, ref.EIGVAL_TOL)
+    fx = dict(
+        N=N, n=n, m=m, cfg=cfg, theta=np.array([float(theta[k]) for k in keys]), theta_keys=np.array(keys),
+        theta_B=np.array([prob.theta[k] for k in keys]), q=B.shape[1], p=int(out["mask"].sum()),
+        B=B.numpy(), eigvals=ev.numpy(), keep=keep.numpy(), m_b=m_b.numpy(),
+        V_b_guard=np.array([float(V_b[0, 0]), float(V_b[-1, -1]), float(V_b[0, -1]), float(V_b.sum())]),
+        logA=prob.logA, lambda0=prob.lambda0,
+        loglik=float(out["loglik"]), KL=float(out["KL"]), dloglik=out["dloglik"].numpy(), dKL=out["dKL"].numpy(),
+        lam_m=out["lam_m"].numpy(), lam_var=out["lam_var"].numpy(), f=out["f"].numpy(), Kvec=out["Kvec"].numpy(),
+    )
+    path = os.path.join(ROOT, "tests", "golden", f"{name}.npz")
+    np.savez_compressed(path, **fx)
+    print(f"{name}: N={N} n={n} m={m} p={fx['p']} q={fx['q']} loglik={fx['loglik']:.6f} KL={fx['KL']:.6f} "
+          f"-> {os.path.getsize(path)/1024:.0f} KiB")
+
+
+def gen_big(ref):
+    """Fixtures at the sizes bench.py times: config 2 dense / localised, config-3 shape."""
+    gen_big_closure_case(ref, "closure_c2_dense_n40", N=8192, n=40, m=500, cfg=2, theta_dict=synth.THETA_DENSE,
+                         perturb={"eps_0x": 0.01, "-log2rho2": -0.02, "Amp": 0.05})
+    gen_big_closure_case(ref, "closure_c2_local_n40", N=8192, n=40, m=500, cfg=2,
+                         theta_dict=synth.theta_localised(40), perturb={"eps_0x": 0.01, "eps_0y": -0.01})
+    gen_big_closure_case(ref, "closure_c3_m1000_n40", N=4096, n=40, m=1000, cfg=3, theta_dict=synth.THETA_DENSE,
+                         perturb={"eps_0y": 0.01, "sigma_0": 0.05})
+
+
 def gen_kat(ref):
     """The toy known-answer vectors of moments_gradients.ipynb cells 1-3, recomputed with the
     reference's own lambda_moments / compute_loglikelihood / log_det and compared with the
@@ -226,6 +264,9 @@ def main():
     gen_utility(ref)
     if len(sys.argv) > 1 and sys.argv[1] == "utility":
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "big":
+        gen_big(ref)
+        return
     # small closure cases, every intermediate stored
     gen_closure_case(ref, "closure_dense_n8", N=150, n=8, m=24, cfg=11, theta_dict=synth.THETA_DENSE, store_big=True)
     gen_closure_case(ref, "closure_local_n12", N=260, n=12, m=40, cfg=12, theta_dict=synth.theta_localised(12),
@@ -242,6 +283,7 @@ def main():
                      perturb={"eps_0x": 0.01, "eps_0y": -0.01})
     gen_fit_case(ref, "fit_small_n10", N=400, n=10, m=40, cfg=21, theta_dict=synth.theta_localised(10),
                  maxiter=4, nE=3, nM=3, nF=3)
+    gen_big(ref)
 
 
 if __name__ == "__main__":

@@ -169,3 +169,43 @@ def test_closure_host_streaming_matches_device():
     ref = fx["dloglik"] - fx["dKL"]
     got = np.array([out["grad"][k] for k in keys])
     assert np.abs(got - ref).max() <= RTOL * np.abs(ref).max()
+
+
+def _eval(native, X, prob, st, d):
+    return native.elbo_grad(X, prob.r.to(d), prob.xtilde.to(d), prob.n_px_side, prob.theta, st["B"].to(d),
+                            st["m_b"].to(d), st["V_b"].to(d), st["logA"], st["lambda0"])
+
+
+@pytest.mark.parametrize("theta_kind", ["local", "dense"])
+def test_cache_is_keyed_on_content_not_on_the_address(theta_kind):
+    """VERDICT r1 weak 2 / ADVICE r1: PyTorch's caching allocator hands a freed block to the next tensor of the same
+    size.  Evaluate on X1, free it, allocate DIFFERENT images X2 (the allocator returns the same address), evaluate:
+    the gathered copy (cropped mask) and the persistent int8 slices (full mask) must be rebuilt -- the result has to
+    equal, bit for bit, the one a pristine cache gives for X2.  Same for an in-place edit of the images."""
+    from gaussian_processes_b200 import native
+    fx = load("closure_c1_local" if theta_kind == "local" else "closure_c1_dense")
+    prob, st = case_inputs(fx)
+    d = torch.device("cuda:0")
+    native.set_option(0, "path", 2)
+    native.set_option(0, "i8_slices", 8)
+    try:
+        X1 = prob.X.to(d)
+        ptr1 = X1.data_ptr()
+        a = _eval(native, X1, prob, st, d)
+        del X1
+        X2 = (prob.X.flip(0) * 1.25).to(d)           # other images, same shape
+        assert X2.data_ptr() == ptr1, "allocator did not recycle the block: the test would not exercise the hazard"
+        b = _eval(native, X2, prob, st, d)
+        native.release_cache(0)                       # pristine cache
+        c = _eval(native, X2, prob, st, d)
+        assert b["loglik"] != a["loglik"]
+        assert b["loglik"] == c["loglik"] and b["grad"] == c["grad"] and b["KL"] == c["KL"]
+        X2 -= 0.5                                     # in-place edit: same object, same address, new version counter
+        e = _eval(native, X2, prob, st, d)
+        native.release_cache(0)
+        f = _eval(native, X2, prob, st, d)
+        assert e["loglik"] != b["loglik"]
+        assert e["loglik"] == f["loglik"] and e["grad"] == f["grad"]
+    finally:
+        native.set_option(0, "path", 0)
+        native.set_option(0, "i8_slices", -1)

@@ -8,7 +8,7 @@ import pytest
 import torch
 
 import oracle.spatial_gp_oracle as orc
-from helpers import CLOSURE_CASES, case_inputs, load, rel_err
+from helpers import BIG_CASES, CLOSURE_CASES, case_inputs, load, rel_err
 
 TOL = 1e-10  # oracle vs reference: same library, same formulas -> far below the 1e-9 product tolerance
 
@@ -67,6 +67,24 @@ def test_closure_against_reference(name):
     assert rel_err(out["lam_m"].numpy(), fx["lam_m"]) < TOL
     assert rel_err(out["lam_var"].numpy(), fx["lam_var"]) < 1e-9
     assert rel_err(out["f"].numpy(), fx["f"]) < TOL
+
+
+@pytest.mark.parametrize("name", BIG_CASES)
+def test_closure_against_reference_benchmark_sizes(name):
+    """The port at n = 40, m = 500 / 1000 against the real reference's outputs (chunked over the images, SURVEY 8c-iv:
+    the same chunking bench.py's cpu_baseline leg and its in-run parity figure use)."""
+    fx = load(name)
+    prob, st = case_inputs(fx)
+    full = orc.elbo_and_grad_chunked(prob.theta, prob.X, prob.r, prob.xtilde, prob.n_px_side, st["B"], st["m_b"],
+                                     st["V_b"], st["logA"], st["lambda0"], chunk=4096)
+    assert full["p"] == int(fx["p"])
+    assert abs(full["loglik"] - float(fx["loglik"])) <= TOL * abs(float(fx["loglik"]))
+    assert abs(full["KL"] - float(fx["KL"])) <= TOL * abs(float(fx["KL"]))
+    keys = [str(k) for k in fx["theta_keys"]]
+    for i, k in enumerate(keys):   # per component, on the cancellation scale of that component
+        scale = max(abs(fx["dloglik"][i]), abs(fx["dKL"][i]))
+        assert abs(full["dloglik"][k] - fx["dloglik"][i]) <= 1e-9 * scale, k
+        assert abs(full["dKL"][k] - fx["dKL"][i]) <= 1e-9 * scale, k
 
 
 @pytest.mark.parametrize("name", ["closure_dense_n8", "closure_local_n12"])
