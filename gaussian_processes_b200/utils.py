@@ -483,12 +483,19 @@ def get_utility(xstar, xtilde, C, mask, theta, m, V, K_tilde, K_tilde_inv, kernf
 
 
 # ---- inference (U:1476-1541, U:326-412) -------------------------------------------------------------------
-def lambda_moments_star(xstar, xtilde, C, theta, K_tilde, K_tilde_inv, m, V, B, kernfun):
+def lambda_moments_star(xstar, xtilde, C, theta, K_tilde, K_tilde_inv, m, V, B, kernfun, _batched=False):
+    """Predictive moments of lambda at test images (U:1476-1500): mu = a m, sigma2 = K** + diag(a (V - K_tilde) a^T)
+    with a = K(x*, xtilde) B K_tilde^-1.  `_batched` (used by test()): xstar holds many independent test images, which
+    the reference pushes through one at a time -- so K(x*, xtilde) is never symmetrised, whatever their number."""
     if kernfun == 'acosker':
         kernfun = acosker
     elif kernfun is not acosker:
         raise Exception('Kernel function not recognized')
-    Kvec_star = kernfun(theta, xstar, xtilde, C=C, dC=None, diag=False) @ B
+    if _batched:
+        Kstar = native.acosker(_fl(theta['sigma_0']), xstar, xtilde, C, symmetrize=False)
+    else:
+        Kstar = kernfun(theta, xstar, xtilde, C=C, dC=None, diag=False)
+    Kvec_star = Kstar @ B
     KKtilde_inv = Kvec_star @ K_tilde_inv
     mu_star = KKtilde_inv @ m
     K_star = kernfun(theta, xstar, x2=None, C=C, dC=None, diag=True)
@@ -556,7 +563,7 @@ def test(X_test, R_test, xtilde, X_train=None, at_iteration=None, **kwargs):
     A = torch.exp(logA)
     xs = torch.reshape(X_test, (X_test.shape[0], -1))
     mu_star, sigma_star2 = lambda_moments_star(xs[:, mask], xtilde[:, mask], C, theta, K_tilde, K_tilde_inv, m, V, B,
-                                               'acosker')
+                                               'acosker', _batched=True)
     R_predicted = torch.exp(A * mu_star + 0.5 * A * A * sigma_star2 + lambda0)                # U:395
     r2, sigma_r2 = explained_variance(R_test[:, :, cellid], R_predicted, sigma=True)
     print(f"\n\n Pietro's model: R2 = {r2:.2f} ± {sigma_r2:.2f} Cell: {cellid} maxiter = {maxiter}, "
@@ -937,41 +944,122 @@ def varGP(x, r, **kwargs):
 
 # ---- persistence (U:46-109, U:312-324, U:689-703): host I/O, same on-disk layout ---------------------------
 def save_model(model, directory, additional_description=None):
+    """Pickle of the result dict + a text `metadata` file, in the reference's on-disk layout (U:46-109): refuses an
+    existing directory, stores the description under model['description'], writes the same description text as
+    metadata.  tests/test_gpu_utils.py compares the text with a model written by the reference's own save_model."""
     if os.path.exists(directory):
         raise ValueError(f"Directory {directory} already exists")
     os.makedirs(directory)
     fp, vt = model['fit_parameters'], model['values_track']
-    lines = ["", "        Model Description:"]
+    pad = " " * 8
+
+    def row(label, first, last, width=12):
+        return f"{pad}{label + ':':<{width}} {_fl(first):>8.4f} -> {_fl(last):>8.4f}"
+
+    lines = ["", f"{pad}Model Description:"]
     for label, key in (("Cell ID", 'cellid'), ("ntilde", 'ntilde'), ("maxiter", 'maxiter'), ("nMstep", 'nMstep'),
                        ("nEstep", 'nEstep')):
-        lines.append(f"        {label + ':':<14} {fp.get(key)!s:>8}")
-    lines.append(f"        MIN_TOLERANCE: {fp['min_tolerance']:>8.12f}")
-    lines.append(f"        EIGVAL_TOL:    {fp['eigval_tol']:>8.4f}")
-    lines += ["", "        Hyperparameters results:", "        Start                 ->   End"]
+        lines.append(f"{pad}{label + ':':<14} {fp[key]:>8}")
+    lines.append(f"{pad}MIN_TOLERANCE: {fp['min_tolerance']:>8.12f}")
+    lines.append(f"{pad}EIGVAL_TOL:    {fp['eigval_tol']:>8.4f}")
+    lines += [pad, f"{pad}Hyperparameters results:", f"{pad}Start                 ->   End"]
     for key in ('sigma_0', 'eps_0x', 'eps_0y', 'Amp', '-2log2beta', '-log2rho2'):
-        tr = vt['theta_track'][key]
-        lines.append(f"        {key + ':':<12} {_fl(tr[0]):>8.4f} -> {_fl(tr[-1]):>8.4f}")
+        lines.append(row(key, vt['theta_track'][key][0], vt['theta_track'][key][-1]))
     bt, rt = vt['theta_track']['-2log2beta'], vt['theta_track']['-log2rho2']
-    lines.append(f"        beta:        {_fl(logbetaexpr_to_beta(bt[0])):>8.4f} -> {_fl(logbetaexpr_to_beta(bt[-1])):>8.4f}")
-    lines.append(f"        rho:         {_fl(logrhoexpr_to_rho(rt[0])):>8.4f} -> {_fl(logrhoexpr_to_rho(rt[-1])):>8.4f}")
-    lines += ["", "        Link function results [f_params]:", ""]
-    for key, tr in vt['f_par_track'].items():
-        lines.append(f"        {key + ':':<12} {_fl(tr[0]):>8.4f} -> {_fl(tr[-1]):>8.4f}")
+    lines += ["", row("beta", logbetaexpr_to_beta(bt[0]), logbetaexpr_to_beta(bt[-1])),
+              row("rho", logrhoexpr_to_rho(rt[0]), logrhoexpr_to_rho(rt[-1])), "",
+              f"{pad}Link function results [f_params]:", ""]
     la = vt['f_par_track']['logA']
-    lines.append(f"        A:           {math.exp(_fl(la[0])):>8.4f} -> {math.exp(_fl(la[-1])):>8.4f}")
-    description = "\n".join(lines) + "\n"
+    lines += [row("logA", la[0], la[-1]), "", row("A", math.exp(_fl(la[0])), math.exp(_fl(la[-1])))]
+    if 'lambda0' in vt['f_par_track']:
+        l0 = (_fl(vt['f_par_track']['lambda0'][0]), _fl(vt['f_par_track']['lambda0'][-1]))
+    else:   # the reference raises KeyError here (U:91); the loglambda0 parametrisation is reported as lambda0
+        l0 = tuple(math.exp(_fl(vt['f_par_track']['loglambda0'][i])) for i in (0, -1))
+    lines += [f"{pad}{'lambda0:':<12} {l0[0]:>8.4f} ->...", f"{pad}  {l0[1]:>8.4f}",
+              f"{pad}We are optimising a negative lambda0", pad]
+    description = "\n".join(lines)
     if additional_description is not None:
         description += f"\n\n{additional_description}"
     model['description'] = description
     with open(os.path.join(directory, 'model'), 'wb') as f:
         pickle.dump(model, f)
     with open(os.path.join(directory, 'metadata'), 'w') as f:
-        f.write(f"{datetime.now().strftime('%Y-%m-%d %H:%M:%S')}\n{description}")
+        f.write(description)
 
 
 def load_model(directory):
     with open(f'{directory}/model', 'rb') as f:
         return pickle.load(f)
+
+
+# ---- plotting entry points of the call surface (U:111-310, U:1543-1563) --------------------------------------
+# Visualisation is outside the hot path (SURVEY section 2 #15); the notebooks call these after every fit, so the names
+# exist with the reference's signatures.  matplotlib is imported lazily: a headless box without it gets a warning
+# and None instead of an ImportError at `import utils` (the reference imports it at module level, U:21-22).
+def _pyplot():
+    try:
+        import matplotlib.pyplot as plt
+        return plt
+    except Exception as e:                                   # pragma: no cover - depends on the host
+        warnings.warn(f'matplotlib is not available ({type(e).__name__}): nothing plotted')
+        return None
+
+
+def plot_loss_and_theta_notebook(model, linestyle='-', marker='o', figsize=(10, 10), xlim=None, ylim_logmarg=None,
+                                 ylim_lambda0=None, ylim_eigvals=None):
+    """Tracks of one fit: -ELBO / loglik / KL, the six hyper-parameters, logA and lambda0, eigenvalues of V_b."""
+    plt = _pyplot()
+    if plt is None:
+        return None
+    vt = model['values_track']
+
+    def arr(t):
+        return t.detach().cpu().numpy() if torch.is_tensor(t) else t
+
+    fig, axes = plt.subplots(3, 3, figsize=figsize)
+    axes = axes.ravel()
+    lt = vt['loss_track']
+    axes[0].plot(-arr(lt['logmarginal']), linestyle=linestyle, marker=marker)
+    axes[0].set_title('-ELBO')
+    if ylim_logmarg is not None:
+        axes[0].set_ylim(ylim_logmarg)
+    axes[1].plot(arr(lt['loglikelihood']), linestyle=linestyle, marker=marker, label='loglikelihood')
+    axes[1].plot(arr(lt['KL']), linestyle=linestyle, marker=marker, label='KL')
+    axes[1].legend()
+    for ax, key in zip(axes[2:8], vt['theta_track'].keys()):
+        ax.plot(arr(vt['theta_track'][key]), linestyle=linestyle, marker=marker)
+        ax.set_title(key)
+    for key, tr in vt['f_par_track'].items():
+        axes[8].plot(arr(tr), linestyle=linestyle, marker=marker, label=key)
+    if ylim_lambda0 is not None:
+        axes[8].set_ylim(ylim_lambda0)
+    axes[8].legend()
+    if xlim is not None:
+        for ax in axes:
+            ax.set_xlim(xlim)
+    fp = model['fit_parameters']
+    fig.suptitle(f"cell {fp.get('cellid')}  ntilde={fp.get('ntilde')}  maxiter={fp.get('maxiter')}  "
+                 f"nEstep={fp.get('nEstep')}  nMstep={fp.get('nMstep')}")
+    return fig
+
+
+def plot_fit(R_predicted, rtst, r2, sigma_r2, cellid):
+    """Predicted rate over the trial-averaged test response (U:1543-1563)."""
+    plt = _pyplot()
+    if plt is None:
+        return None
+
+    def arr(t):
+        return t.detach().cpu().numpy() if torch.is_tensor(t) else t
+
+    fig = plt.figure(figsize=(12, 8))
+    ax = fig.add_subplot(1, 1, 1)
+    R_predicted, rtst = arr(R_predicted), arr(rtst)
+    tvals = 0.05 * torch.arange(len(R_predicted)).numpy()
+    ax.plot(tvals, rtst.mean(axis=0), 'k', linewidth=1)
+    ax.plot(tvals, R_predicted, color='red', label='GP')
+    ax.set_title(f'Pietro adjusted r^2 = {float(r2):.2f} ± {float(sigma_r2):.2f} Cell: {cellid}')
+    return fig
 
 
 def save_pickle(filename, **kwargs):

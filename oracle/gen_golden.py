@@ -230,6 +230,47 @@ def gen_fit_case(ref, name, N, n, m, cfg, theta_dict, maxiter, nE, nM, nF):
     path = os.path.join(ROOT, "tests", "golden", f"{name}.npz")
     np.savez_compressed(path, **fx)
     print(f"{name}: logmarginal track {fx['logmarginal']}")
+    return prob, fit
+
+
+def gen_test_and_checkpoint(ref, prob, fit, name):
+    """the reference's own test() / lambda_moments_star / explained_variance(sigma=False) on
+    seeded test images for the model `fit` (the reference's varGP result of gen_fit_case), and that model written by
+    the reference's own save_model (pickle + metadata) -- the on-disk format the replacement must read and write."""
+    import shutil
+    n = prob.n_px_side
+    g = torch.Generator().manual_seed(5021)
+    ntest, ntrials, ncells = 30, 10, 3
+    X_test = torch.randn(ntest, n, n, 1, generator=g, dtype=torch.float64)
+    R_test = torch.poisson(torch.full((ntrials, ntest, ncells), 1.5, dtype=torch.float64), generator=g)
+    # give the cell of interest a stimulus-driven part so that the correlations of explained_variance are not ~0
+    drive = torch.exp(0.5 * X_test.reshape(ntest, -1)[:, : n].sum(1))
+    R_test[:, :, 0] = torch.poisson(drive.expand(ntrials, ntest).contiguous(), generator=g)
+    with contextlib.redirect_stdout(io.StringIO()):
+        R_cell, R_pred, r2, sr2 = ref.test(X_test, R_test, X_train=prob.X, at_iteration=None, **fit)   # as the notebooks call it
+    mask = fit["mask"]
+    xs = X_test.reshape(ntest, -1)
+    theta = fit["hyperparams_tuple"][0]
+    mu, s2 = [], []
+    for i in range(ntest):   # the reference's per-image call (n1 = 1: never symmetrised)
+        a, b = ref.lambda_moments_star(xs[i:i + 1, mask], prob.xtilde[:, mask], fit["C"], theta, fit["K_tilde_b"],
+                                       fit["K_tilde_inv_b"], fit["m_b"], fit["V_b"], fit["B"], "acosker")
+        mu.append(a); s2.append(b)
+    r2_ns, _ = ref.explained_variance(R_test[:, :, 0], R_pred, sigma=False)
+    keys = list(theta.keys())
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", f"{name}.npz"),
+                        X_test=X_test.numpy(), R_test=R_test.numpy(), R_pred=R_pred.numpy(), mu_star=torch.cat(mu).numpy(),
+                        sigma_star2=torch.cat(s2).numpy(), r2_nosigma=float(r2_ns), r2_boot=float(r2), sr2_boot=float(sr2),
+                        theta=np.array([float(theta[k]) for k in keys]), theta_keys=np.array(keys),
+                        mask=mask.numpy(), C=fit["C"].numpy(), B=fit["B"].numpy(), m_b=fit["m_b"].numpy(),
+                        V_b=fit["V_b"].numpy(), K_tilde_b=fit["K_tilde_b"].numpy(),
+                        K_tilde_inv_b=fit["K_tilde_inv_b"].numpy(), logA=float(fit["f_params"]["logA"]),
+                        lambda0=float(fit["f_params"]["lambda0"]), N=prob.N, n=n, m=prob.m, cfg=prob.cfg)
+    d = os.path.join(ROOT, "tests", "golden", f"{name}_saved_by_reference")
+    shutil.rmtree(d, ignore_errors=True)
+    ref.save_model(fit, d, additional_description="written by the reference's save_model (oracle/gen_golden.py)")
+    print(f"{name}: R_pred[:4] = {R_pred[:4].numpy()}, r2(sigma=False) = {float(r2_ns):.6f}; model pickled to {d} "
+          f"({os.path.getsize(os.path.join(d, 'model'))/1024:.0f} KiB)")
 
 
 def gen_utility(ref):
@@ -267,6 +308,11 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "big":
         gen_big(ref)
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "fit":
+        prob_f, fit_f = gen_fit_case(ref, "fit_small_n10", N=400, n=10, m=40, cfg=21,
+                                     theta_dict=synth.theta_localised(10), maxiter=4, nE=3, nM=3, nF=3)
+        gen_test_and_checkpoint(ref, prob_f, fit_f, "test_small_n10")
+        return
     # small closure cases, every intermediate stored
     gen_closure_case(ref, "closure_dense_n8", N=150, n=8, m=24, cfg=11, theta_dict=synth.THETA_DENSE, store_big=True)
     gen_closure_case(ref, "closure_local_n12", N=260, n=12, m=40, cfg=12, theta_dict=synth.theta_localised(12),
@@ -281,8 +327,9 @@ def main():
     gen_closure_case(ref, "closure_c1_dense", N=2000, n=20, m=100, cfg=1, theta_dict=synth.THETA_DENSE)
     gen_closure_case(ref, "closure_c1_local", N=2000, n=20, m=100, cfg=1, theta_dict=synth.theta_localised(20),
                      perturb={"eps_0x": 0.01, "eps_0y": -0.01})
-    gen_fit_case(ref, "fit_small_n10", N=400, n=10, m=40, cfg=21, theta_dict=synth.theta_localised(10),
-                 maxiter=4, nE=3, nM=3, nF=3)
+    prob_f, fit_f = gen_fit_case(ref, "fit_small_n10", N=400, n=10, m=40, cfg=21, theta_dict=synth.theta_localised(10),
+                                 maxiter=4, nE=3, nM=3, nF=3)
+    gen_test_and_checkpoint(ref, prob_f, fit_f, "test_small_n10")
     gen_big(ref)
 
 

@@ -40,3 +40,34 @@ def rel_err(a, b):
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
     return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+def record(name, **values):
+    """Append measured errors to gpurun_out/parity_report.jsonl (scratch; read back after a GPU run to see how far
+    below the asserted tolerance each comparison actually is)."""
+    import json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    try:
+        os.makedirs(os.path.join(root, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(root, "gpurun_out", "parity_report.jsonl"), "a") as f:
+            f.write(json.dumps({"test": name, **{k: float(v) for k, v in values.items()}}) + "\n")
+    except Exception:
+        pass
+
+
+def to_device(obj, dev):
+    """Recursively move the tensors of a (nested) fit_model dict / tuple / list to `dev` (requires_grad preserved)."""
+    if torch.is_tensor(obj):
+        t = obj.detach().to(dev)
+        return t.requires_grad_(True) if obj.requires_grad else t
+    if isinstance(obj, dict):
+        return {k: to_device(v, dev) for k, v in obj.items()}
+    if isinstance(obj, tuple):
+        return tuple(to_device(v, dev) for v in obj)
+    if isinstance(obj, list):
+        return [to_device(v, dev) for v in obj]
+    return obj
+
+
+def reference_saved_model_dir():
+    return os.path.join(GOLDEN, "test_small_n10_saved_by_reference")

@@ -9,7 +9,7 @@ import pytest
 import torch
 
 from gaussian_processes_b200 import synth
-from helpers import case_inputs, load
+from helpers import case_inputs, load, record, rel_err
 
 pytestmark = pytest.mark.gpu
 D = "cuda:0"
@@ -49,7 +49,14 @@ def test_vargp_tracks_match_reference_on_gpu(U):
     assert not err["is_error"], err
     assert native.launch_count(0) > 100          # the CUDA library did the work
     vt = fit["values_track"]
-    tol = 1e-6
+    got_t = np.stack([vt["theta_track"][k].cpu().numpy() for k in keys])
+    record("vargp_tracks", logmarginal=rel_err(vt["loss_track"]["logmarginal"].cpu().numpy(), fx["logmarginal"]),
+           loglik=rel_err(vt["loss_track"]["loglikelihood"].cpu().numpy(), fx["loglikelihood"]),
+           KL=rel_err(vt["loss_track"]["KL"].cpu().numpy(), fx["KL"]), theta=rel_err(got_t, fx["theta_track"]),
+           logA=rel_err(vt["f_par_track"]["logA"].cpu().numpy(), fx["logA_track"]))
+    # 3 EM iterations x (3 E-steps with an LBFGS on logA + 3 LBFGS M-step iterations with strong-Wolfe line searches):
+    # an evaluation that agrees to 1e-11 is amplified by the optimisers' own conditioning; measured 1e-9..1e-8
+    tol = 1e-7
     assert np.allclose(vt["loss_track"]["logmarginal"].cpu().numpy(), fx["logmarginal"], rtol=tol)
     assert np.allclose(vt["loss_track"]["loglikelihood"].cpu().numpy(), fx["loglikelihood"], rtol=tol)
     assert np.allclose(vt["loss_track"]["KL"].cpu().numpy(), fx["KL"], rtol=tol, atol=1e-8)
@@ -116,13 +123,18 @@ def test_function_level_surface_on_gpu(U):
     assert np.allclose(lv.cpu().numpy(), fx["lam_var"], rtol=1e-9, atol=1e-10)
     m_new, V_new = U.Estep(r=r, KKtilde_inv=a, m=st["m_b"].to(D), f_params=fp, f_mean=torch.from_numpy(fx["f"]).to(D),
                            K_tilde=Kt_b, K_tilde_inv=Kinv)
-    assert np.allclose(m_new.cpu().numpy(), fx["estep_m"], rtol=1e-8, atol=1e-11)
-    assert np.allclose(V_new.cpu().numpy(), fx["estep_V"], rtol=1e-8, atol=1e-11)
+    # (K^-1 + G)^-1 by blocked Cholesky instead of solve(I + K G, K) (U:1430): with the exact G the two routes agree
+    # to 2e-15 on every fixture (cond(K^-1 + G) <= 6e3 even on the rank-deficient one), so the 1e-9
+    # bar applies
+    record("estep", m=rel_err(m_new.cpu().numpy(), fx["estep_m"]), V=rel_err(V_new.cpu().numpy(), fx["estep_V"]))
+    assert np.allclose(m_new.cpu().numpy(), fx["estep_m"], rtol=1e-9, atol=1e-9 * np.abs(fx["estep_m"]).max())
+    assert np.allclose(V_new.cpu().numpy(), fx["estep_V"], rtol=1e-9, atol=1e-9 * np.abs(fx["estep_V"]).max())
     KL, dKL = U.compute_KL_div(st["m_b"].to(D), st["V_b"].to(D), Kt_b, Kinv,
                                dK_tilde={k: B.T @ dKt[k] @ B for k in dKt})
     assert abs(float(KL) - float(fx["KL"])) <= 1e-9 * abs(float(fx["KL"]))
     keys = [str(k) for k in fx["theta_keys"]]
-    assert np.allclose(np.array([float(dKL[k]) for k in keys]), fx["dKL"], rtol=1e-8, atol=1e-10)
+    record("dKL", err=rel_err(np.array([float(dKL[k]) for k in keys]), fx["dKL"]))
+    assert np.allclose(np.array([float(dKL[k]) for k in keys]), fx["dKL"], rtol=1e-9, atol=1e-9 * np.abs(fx["dKL"]).max())
 
 
 def test_cpu_tensors_raise(U):
@@ -145,3 +157,92 @@ def test_utility_family_on_gpu(U):
     assert np.array_equal(r2d.cpu().numpy(), fx["r2d"])
     j = int(fx["single_index"])
     assert abs(float(U.utility(s2[j], mu[j], r)) - float(fx["U1"])) <= 1e-9 * abs(float(fx["U1"]))
+
+
+# ---- SURVEY 8(f) ranks 3 and 4 on the CUDA library -------------------------------------------------------------
+def test_test_function_matches_reference_on_gpu(U):
+    """utils.test / lambda_moments_star on a model fitted and pickled by the REFERENCE (moved to the GPU): all test
+    images in one batch through sgp_acosker / sgp_acosker_diag; predicted rates and the deterministic r2 at 1e-9."""
+    from helpers import reference_saved_model_dir, to_device
+    fx = load("test_small_n10")
+    model = to_device(U.load_model(reference_saved_model_dir()), D)
+    X_test, R_test = torch.from_numpy(fx["X_test"]).to(D), torch.from_numpy(fx["R_test"]).to(D)
+    with contextlib.redirect_stdout(io.StringIO()):
+        R_cell, R_pred, r2, s2 = U.test(X_test, R_test, X_train=None, at_iteration=None, **model)
+    assert R_pred.is_cuda
+    record("test_fn", R_pred=rel_err(R_pred.cpu().numpy(), fx["R_pred"]))
+    assert np.allclose(R_pred.cpu().numpy(), fx["R_pred"], rtol=1e-9, atol=0)
+    assert np.isfinite(float(r2)) and np.isfinite(float(s2))
+    r2_ns, _ = U.explained_variance(R_test[:, :, 0], R_pred, sigma=False)
+    assert abs(float(r2_ns) - float(fx["r2_nosigma"])) <= 1e-9 * abs(float(fx["r2_nosigma"]))
+    theta, mask = model["hyperparams_tuple"][0], model["mask"]
+    xs = X_test.reshape(X_test.shape[0], -1)
+    mu, s2s = U.lambda_moments_star(xs[:, mask], model["xtilde"][:, mask], model["C"], theta, model["K_tilde_b"],
+                                    model["K_tilde_inv_b"], model["m_b"], model["V_b"], model["B"], "acosker")
+    assert np.allclose(mu.cpu().numpy(), fx["mu_star"], rtol=1e-9, atol=1e-12)
+    assert np.allclose(s2s.cpu().numpy(), fx["sigma_star2"], rtol=1e-9, atol=1e-12)
+
+
+def test_test_function_at_iteration_on_gpu(U):
+    """test(at_iteration=k, X_train=X) rebuilds C / K_tilde / the subspace at the tracked theta of iteration k
+    (U:358-386); at the last iteration it must reproduce the plain call on the same fit."""
+    fx = load("fit_small_n10")
+    keys = [str(k) for k in fx["theta_keys"]]
+    prob = synth.make_problem(int(fx["N"]), int(fx["n"]), int(fx["m"]), cfg=int(fx["cfg"]),
+                              theta=dict(zip(keys, fx["theta0"].tolist())))
+    tx = load("test_small_n10")
+    X_test, R_test = torch.from_numpy(tx["X_test"]).to(D), torch.from_numpy(tx["R_test"]).to(D)
+    with contextlib.redirect_stdout(io.StringIO()):
+        fit, err = U.varGP(prob.X.to(D), prob.r.to(D), **fit_args(fx, prob, D))
+        _, plain, _, _ = U.test(X_test, R_test, X_train=prob.X.to(D), at_iteration=None, **fit)
+        last = int(fit["fit_parameters"]["maxiter"]) - 1
+        _, at_last, _, _ = U.test(X_test, R_test, X_train=prob.X.to(D), at_iteration=last, **fit)
+    assert not err["is_error"]
+    assert np.allclose(at_last.cpu().numpy(), plain.cpu().numpy(), rtol=1e-8, atol=0)
+    # and the GPU fit predicts what the reference's fit predicts (tracks agree to ~1e-8, see the track test)
+    assert np.allclose(plain.cpu().numpy(), tx["R_pred"], rtol=1e-6, atol=0)
+
+
+def test_checkpoint_round_trip_and_warm_start_on_gpu(U, tmp_path):
+    """save_model -> load_model -> varGP(**model) on the GPU: a CUDA model pickles and reloads onto the device, the
+    warm start (m, V lifted with B as notebook cell 17 does) begins at the loss the saved fit ended at; a checkpoint
+    written by the reference's save_model warm-starts the same way."""
+    from helpers import reference_saved_model_dir, to_device
+    fx = load("fit_small_n10")
+    keys = [str(k) for k in fx["theta_keys"]]
+    prob = synth.make_problem(int(fx["N"]), int(fx["n"]), int(fx["m"]), cfg=int(fx["cfg"]),
+                              theta=dict(zip(keys, fx["theta0"].tolist())))
+    X, r = prob.X.to(D), prob.r.to(D)
+    with contextlib.redirect_stdout(io.StringIO()):
+        fit, err = U.varGP(X, r, **fit_args(fx, prob, D))
+    assert not err["is_error"]
+    U.save_model(fit, str(tmp_path / "ckpt"))
+    for src in (str(tmp_path / "ckpt"), reference_saved_model_dir()):
+        model = to_device(U.load_model(src), D)
+        B = model["B"]
+        model["m"] = B @ model["m_b"]
+        model["V"] = B @ model["V_b"] @ B.T
+        last = float(model["values_track"]["loss_track"]["logmarginal"][-1])
+        model["fit_parameters"] = dict(model["fit_parameters"], maxiter=2, nEstep=1, nMstep=0)
+        with contextlib.redirect_stdout(io.StringIO()):
+            fit2, err2 = U.varGP(X, r, **model)
+        assert not err2["is_error"], err2
+        first = float(fit2["values_track"]["loss_track"]["logmarginal"][0])
+        record("warm_start", rel=abs(first - last) / abs(last))
+        assert abs(first - last) <= 1e-8 * abs(last)
+
+
+def test_plot_entry_points_exist(U):
+    """The notebooks call utils.plot_loss_and_theta_notebook after every fit (11 call sites): the names exist and
+    degrade to a warning + None on a box without matplotlib instead of an AttributeError."""
+    import warnings
+    model = U.load_model(__import__("helpers").reference_saved_model_dir())
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        fig = U.plot_loss_and_theta_notebook(model, xlim=None, ylim_logmarg=None)
+        fig2 = U.plot_fit(torch.ones(5), torch.ones(3, 5), 0.5, 0.1, 0)
+    try:
+        import matplotlib  # noqa: F401
+        assert fig is not None and fig2 is not None
+    except ImportError:
+        assert fig is None and fig2 is None

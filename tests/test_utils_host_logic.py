@@ -210,3 +210,82 @@ def test_utility_family_surface(U):
     # the single-candidate variants DROP overflowing counts instead of zeroing them (U:551-553)
     lam0, keep0 = U.lambda_r_mean(r, s2[0], mu[0])
     assert lam0.numel() == int(keep0.sum()) < 100
+
+
+# ---- test() / lambda_moments_star / explained_variance and the checkpoint format ----------
+def test_checkpoint_written_by_the_reference_loads_and_text_matches(U, tmp_path):
+    """load_model reads a model pickled by the reference's own save_model; save_model writes the same description /
+    metadata text for it, and refuses an existing directory (U:46-109, U:312-324)."""
+    from helpers import reference_saved_model_dir
+    d = reference_saved_model_dir()
+    model = U.load_model(d)
+    assert {"fit_parameters", "final_kernel", "values_track", "m_b", "V_b", "B", "description"} <= set(model)
+    ref_text = open(f"{d}/metadata").read()
+    assert model["description"] == ref_text
+    model.pop("description")
+    out = tmp_path / "resaved"
+    U.save_model(model, str(out), additional_description="written by the reference's save_model (oracle/gen_golden.py)")
+    assert (out / "metadata").read_text() == ref_text
+    back = U.load_model(str(out))
+    assert torch.equal(back["V_b"], model["V_b"]) and back["description"] == ref_text
+    with pytest.raises(ValueError):
+        U.save_model(model, str(out))
+
+
+def test_test_function_matches_reference(U):
+    """utils.test as the notebooks call it (`test(X_test, R_test, X_train=X, at_iteration=None, **fit_model)`) on a
+    model fitted AND pickled by the reference: predicted rates at 1e-9, the deterministic r2 at 1e-9."""
+    from helpers import reference_saved_model_dir
+    fx = load("test_small_n10")
+    model = U.load_model(reference_saved_model_dir())
+    X_test, R_test = torch.from_numpy(fx["X_test"]), torch.from_numpy(fx["R_test"])
+    with contextlib.redirect_stdout(io.StringIO()):
+        R_cell, R_pred, r2, s2 = U.test(X_test, R_test, X_train=None, at_iteration=None, **model)
+    assert np.allclose(R_pred.numpy(), fx["R_pred"], rtol=1e-9, atol=0)
+    assert torch.equal(R_cell, R_test[:, :, 0]) and math.isfinite(float(r2)) and math.isfinite(float(s2))
+    r2_ns, none = U.explained_variance(R_test[:, :, 0], R_pred, sigma=False)
+    assert none is None and abs(float(r2_ns) - float(fx["r2_nosigma"])) <= 1e-9 * abs(float(fx["r2_nosigma"]))
+    theta = model["hyperparams_tuple"][0]
+    mask = model["mask"]
+    xs = X_test.reshape(X_test.shape[0], -1)
+    mu, s2s = U.lambda_moments_star(xs[:7, mask], model["xtilde"][:, mask], model["C"], theta, model["K_tilde_b"],
+                                    model["K_tilde_inv_b"], model["m_b"], model["V_b"], model["B"], "acosker")
+    assert np.allclose(mu.numpy(), fx["mu_star"][:7], rtol=1e-9, atol=1e-12)
+    assert np.allclose(s2s.numpy(), fx["sigma_star2"][:7], rtol=1e-9, atol=1e-12)
+
+
+def test_warm_start_from_a_reloaded_checkpoint(U, tmp_path):
+    """save_model -> load_model -> varGP(**model) with (m, V) lifted back as the active loop does (notebook cell 17):
+    the warm-started fit begins exactly where the saved one ended."""
+    fx, keys, prob, args, fit, err = run_fit(U)
+    assert not err["is_error"]
+    U.save_model(fit, str(tmp_path / "ckpt"))
+    model = U.load_model(str(tmp_path / "ckpt"))
+    B = model["B"]
+    model["m"] = B @ model["m_b"]
+    model["V"] = B @ model["V_b"] @ B.T
+    model["fit_parameters"] = dict(model["fit_parameters"], maxiter=2, nEstep=1, nMstep=0)
+    with contextlib.redirect_stdout(io.StringIO()):
+        fit2, err2 = U.varGP(prob.X, prob.r, **model)      # extra keys of the result dict are tolerated (SURVEY 8b)
+    assert not err2["is_error"], err2
+    last = float(fit["values_track"]["loss_track"]["logmarginal"][-1])
+    first = float(fit2["values_track"]["loss_track"]["logmarginal"][0])
+    assert abs(first - last) <= 1e-8 * abs(last)
+
+
+def test_plot_entry_points_exist(U):
+    """plot_loss_and_theta_notebook / plot_fit exist with the reference's signatures (U:111, U:1543) and return None
+    with a warning when matplotlib is absent (it is, in this image) instead of failing at `import utils`."""
+    import warnings
+    from helpers import reference_saved_model_dir
+    model = U.load_model(reference_saved_model_dir())
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        fig = U.plot_loss_and_theta_notebook(model, linestyle='-', marker='o', figsize=(10, 10), xlim=None,
+                                             ylim_logmarg=None, ylim_lambda0=None, ylim_eigvals=None)
+        fig2 = U.plot_fit(torch.ones(5), torch.ones(3, 5), 0.5, 0.1, 0)
+    try:
+        import matplotlib  # noqa: F401
+        assert fig is not None and fig2 is not None
+    except ImportError:
+        assert fig is None and fig2 is None
