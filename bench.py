@@ -96,16 +96,39 @@ def build_state_cpu(prob, orc):
     return B, m_b, V_b
 
 
-def cpu_eval_time(orc, prob, B, m_b, V_b, chunk, reps, warm=1):
-    """Seconds per oracle closure evaluation on the first `chunk` images (all host threads)."""
+def cpu_eval_time(orc, prob, B, m_b, V_b, chunk, reps, warm=1, keep=None):
+    """Seconds per oracle closure evaluation on the first `chunk` images (all host threads).
+    `keep` (dict): receives the last evaluation's result (with lam_m / lam_var / f) for the parity figure."""
     Xc, rc = prob.X[:chunk], prob.r[:chunk]
     ts = []
     for i in range(warm + reps):
         t0 = time.perf_counter()
-        orc.elbo_and_grad(prob.theta, Xc, rc, prob.xtilde, prob.n_px_side, B, m_b, V_b, prob.logA, prob.lambda0)
+        o = orc.elbo_and_grad(prob.theta, Xc, rc, prob.xtilde, prob.n_px_side, B, m_b, V_b, prob.logA, prob.lambda0,
+                              return_moments=keep is not None)
         if i >= warm:
             ts.append(time.perf_counter() - t0)
+    if keep is not None:
+        keep.update(o)
     return ts
+
+
+def parity_figure(native, orc_out, X, r, xt, n, theta, B, m_b, V_b, logA, lambda0, chunk):
+    """GPU path against the CPU port on the very images the cpu_baseline leg timed (the first `chunk` of the benchmark's
+    own problem, default path / default engine: sep_quad_full_kernel<5,.> and oz_gemm_kernel at K = 1600).  Relative
+    errors; gradients per component on that component's cancellation scale max(|dloglik_k|, |dKL_k|)."""
+    out = native.elbo_grad(X[:chunk], r[:chunk], xt, n, theta, B, m_b, V_b, logA, lambda0, want_moments=True)
+    g = max(abs(out["grad"][k] - orc_out["grad"][k]) / max(abs(orc_out["dloglik"][k]), abs(orc_out["dKL"][k]))
+            for k in KEYS)
+
+    def vrel(a, b):
+        b = b.to(a.device)
+        return float((a - b).abs().max() / b.abs().max())
+    return {"sample": f"first {chunk} images of the benchmark problem, GPU default path vs CPU port (oracle)",
+            "loglik_rel": abs(out["loglik"] - orc_out["loglik"]) / abs(orc_out["loglik"]),
+            "KL_rel": abs(out["KL"] - orc_out["KL"]) / abs(orc_out["KL"]),
+            "grad_rel_max": g, "lam_m_rel_max": vrel(out["lam_m"], orc_out["lam_m"]),
+            "lam_var_rel_max": vrel(out["lam_var"], orc_out["lam_var"]), "f_rel_max": vrel(out["f"], orc_out["f"]),
+            "flags": out["flags"], "tolerance": 1e-9}
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
@@ -311,6 +334,24 @@ def secondary_metrics(native, dev, X, r, xt, Cm, mask, theta, B, ev_keep, m_b, V
             out["theta_variants"][name] = {"p": int(mv.sum()), "q": int(Bv.shape[1]), "ms": tv * 1e3,
                                            "evals_per_sec": 1.0 / tv, "flags": int(res.get("flags", -1)),
                                            "loglik": float(res.get("loglik", float("nan")))}
+            if name == "localised":
+                # The same evaluation when the receptive-field mask changes at EVERY call, as it does inside an LBFGS
+                # line search over eps_0 / beta (U:2030: the mask is recomputed from theta in every closure; parity
+                # trap 5): theta alternates between two centres whose masks differ, so no call finds its own mask cached.
+                th_b = dict(th)
+                th_b["eps_0x"] = th["eps_0x"] + 0.03
+                th_b["eps_0y"] = th["eps_0y"] - 0.02
+                p_b = int(native.mask_host(th_b, n_side).sum())
+                flip = [0]
+
+                def alt():
+                    flip[0] ^= 1
+                    res.update(native.elbo_grad(X, r, xt, n_side, th_b if flip[0] else th, Bv, mbv, Vbv, logA, lambda0))
+                tf_ = timed(alt, reps=6, warm=2)
+                out["mask_flip"] = {"theta": "localised (generate_theta defaults), eps_0 alternating between two centres",
+                                    "p": [int(mv.sum()), p_b], "ms_mask_cached": tv * 1e3, "ms_mask_changes_every_call": tf_ * 1e3,
+                                    "note": "best of 6 alternating calls; includes whatever re-gathering / re-slicing of "
+                                            "the images the new mask costs"}
             del Cv, Ktv, evecv, Bv
         except Exception as e:  # pragma: no cover
             out["theta_variants"][name] = {"error": repr(e)}
@@ -359,6 +400,80 @@ def secondary_metrics(native, dev, X, r, xt, Cm, mask, theta, B, ev_keep, m_b, V
                               "contract_tflops": flops / t / 1e12,
                               "what": "rate, g/G (one pass over a), (K^-1+G)^-1 by blocked Cholesky, new moments, lambda0"}
     return out
+
+
+def library_gpu_baseline(orc, prob, X, r, xt, B, m_b, V_b, chunk=20000, reps=2):
+    """The reference-shaped computation on the B200 itself: the port of the reference's formulas (forward-mode dK per
+    hyper-parameter, U:2030-2099) with its tensors on cuda:0, i.e. cuBLAS DGEMM + cuSOLVER + ATen pointwise kernels --
+    what `utils.py` executes when the notebook selects the GPU (U:41).  SURVEY 2a / 8(d): "the number the hand-written
+    kernels must beat".  The whole N is evaluated (row chunks of 20 000, SURVEY 8c-iv: the reference's N x m x 7
+    temporaries do not fit otherwise); CUDA events around the full evaluation."""
+    def one():
+        return orc.elbo_and_grad_chunked(prob.theta, X, r, xt, prob.n_px_side, B, m_b, V_b, prob.logA, prob.lambda0,
+                                         chunk=chunk)
+    one()
+    torch.cuda.synchronize()
+    best, res = float("inf"), None
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        res = one()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1) * 1e-3)
+    torch.cuda.empty_cache()
+    return {"evals_per_sec": 1.0 / best, "ms": best * 1e3, "chunk": chunk,
+            "what": "oracle port (the reference's forward-mode formulas) on cuda:0: cuBLAS DGEMM + cuSOLVER + ATen, whole N "
+                    "in row chunks, best of %d" % reps,
+            "loglik": res["loglik"], "grad": [res["grad"][k] for k in KEYS]}
+
+
+def config5_leg(native, sharded, dist, dev, world, rank, n, xt, theta, B, m_b, V_b, logA, lambda0, sg, steps=3, warm=2):
+    """BASELINE configs[4] / north_star's target: ONE cell, N = 1 000 000 images of 40 x 40, m = 500, the images sharded
+    over the ranks (strong scaling: the total is fixed), one all-reduce per evaluation.  Images are drawn on the device
+    (12.8 GB at one GPU).  Returns evaluations/s of the 1M-image problem, timed on the device, max over ranks."""
+    total = int(os.environ.get("SGP_BENCH_C5_N", 1000000))
+    N5 = total // world
+    local = dev.index or 0
+    native.release_cache(local)
+    torch.cuda.empty_cache()
+    g = torch.Generator(device=dev).manual_seed(5000 + rank)
+    X5 = torch.randn(N5, n * n, generator=g, dtype=torch.float64, device=dev)
+    lin = torch.linspace(-1, 1, n, dtype=torch.float64, device=dev)
+    yc, xc = torch.meshgrid(lin, lin, indexing="ij")
+    w = torch.exp(-((xc.flatten() - 0.2) ** 2 + (yc.flatten() + 0.1) ** 2) / (2 * 0.15 ** 2))
+    drive = X5 @ w
+    r5 = torch.poisson(torch.exp(0.8 * drive / drive.std() - 0.5), generator=g)
+    del drive
+
+    def step():
+        return sharded.elbo_grad(X5, r5, xt, n, theta, B, m_b, V_b, logA, lambda0, sg=sg)
+    for _ in range(warm):
+        out = step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = step()
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) * 1e-3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    el = float(t.item())
+    mem = torch.cuda.max_memory_allocated(dev)
+    del X5, r5
+    native.release_cache(local)
+    torch.cuda.empty_cache()
+    return {"workload": "config5: single cell, 40x40 px, N=%d images in total sharded over %d GPU(s), m=%d, dense theta" %
+                        (N5 * world, world, xt.shape[0]),
+            "images_total": N5 * world, "images_per_gpu": N5, "gpus": world, "steps": steps, "warmup": warm,
+            "ms": 1e3 * el / steps, "evals_per_sec": steps / el, "scaling": "strong",
+            "loglik": out["loglik"], "flags": int(out["flags"]), "torch_max_allocated_gb": mem / 1e9}
 
 
 def run_ours(args):
@@ -457,6 +572,13 @@ def run_ours(args):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = world * e2e_steps / float(te.item())
     h2d = Xh.numel() * 8 + rh.numel() * 8 + (xth.numel() + Bh.numel() + Vh.numel() + mh.numel()) * 8
+    # ---- config 5 (north_star's target) on the same ranks: 1M images in total, strong scaling
+    c5 = None
+    if os.environ.get("SGP_BENCH_CONFIG5", "1") != "0" and not args.no_config5 and n == 40:
+        try:
+            c5 = config5_leg(native, sharded, dist, dev, world, rank, n, xt, theta, B, m_b, V_b, prob.logA, prob.lambda0, sg)
+        except Exception as e:  # pragma: no cover
+            c5 = {"error": repr(e)}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -505,6 +627,10 @@ def run_ours(args):
                                 "issues at twice the bf16 rate on sm_100a" if mp_bf16 else
                                 "nominal 4.5 POP/s (MEASURED_PEAKS.json missing)"),
                 "library_int8_gemm_tops_measured": peak_i8_lib,
+                "frac_vs_2x_bf16_burst": (ach / peak) if ach else None,
+                "frac_vs_library_int8_gemm": (ach / peak_i8_lib) if (ach and peak_i8_lib) else None,
+                "ncu_sm__pipe_tc_cycles_active_pct": "79-84 on the K = 1600 launches, 57.8 on K = 500 (profiles/r1_ncu_v30_summary.md; "
+                                                     "ncu replays are cold-cache, quoted beside the live figure, not instead of it)",
                 "fp64_equivalent_tflops": 2.0 * (2.0 * N * p * m) / t_i8 / 1e12 if t_i8 > 0 else None,
                 "fp64_dmma_peak_tflops_measured": peak_f64}
     else:
@@ -544,19 +670,41 @@ def run_ours(args):
         except Exception as e:  # pragma: no cover  (secondary numbers must never take the headline down)
             secondary = {"error": repr(e)}
 
-    # ---- CPU baseline beside it (rank 0, N=1 only): oracle port on a bounded sample
+    # ---- CPU baseline beside it (rank 0, N=1 only): oracle port on a bounded sample, and the parity figure on the
+    #      same sample: the GPU's default path against the port, printed in every bench line (exit 3 above 1e-9)
     cpu = None
+    parity = None
     if world == 1 and not args.no_cpu_baseline:
         import oracle.spatial_gp_oracle as orc
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
         chunk = int(os.environ.get("SGP_BENCH_CPU_CHUNK", min(10000, N)))
         Bc, mc, Vc = B.cpu(), m_b.cpu(), V_b.cpu()
-        ts = cpu_eval_time(orc, prob, Bc, mc, Vc, chunk, reps=5, warm=1)
+        kept = {}
+        ts = cpu_eval_time(orc, prob, Bc, mc, Vc, chunk, reps=5, warm=1, keep=kept)
         tmed = statistics.median(ts)
         cpu = {"value": 1.0 / (tmed * N / chunk), "unit": "evals/s", "cores": cores, "kind": "port",
                "sample": f"oracle port on the first {chunk} of {N} images, median of 5, scaled linearly to N "
                          f"(extrapolated); {tmed:.3f} s per {chunk}-image evaluation"}
+        try:
+            native.set_option(local, "i8_slices", args.i8_slices)
+            parity = parity_figure(native, kept, X, r, xt, n, theta, B, m_b, V_b, prob.logA, prob.lambda0, chunk)
+        except Exception as e:  # pragma: no cover
+            parity = {"error": repr(e)}
+        # the reference-shaped computation on this very GPU through the libraries (cuBLAS / cuSOLVER / ATen)
+        try:
+            roof["library_gpu_baseline"] = library_gpu_baseline(orc, prob, X, r, xt, B, m_b, V_b)
+            roof["library_gpu_baseline_evals_per_sec"] = roof["library_gpu_baseline"]["evals_per_sec"]
+            roof["speedup_vs_library_gpu_baseline"] = sharded_evals_per_sec / roof["library_gpu_baseline_evals_per_sec"]
+        except Exception as e:  # pragma: no cover
+            roof["library_gpu_baseline"] = {"error": repr(e)}
+    # the driver's record keeps `roofline` and drops `secondary`: the figures north_star names live in both
+    if secondary:
+        for k in ("logA_closure_pass", "estep_iteration", "mask_flip", "config3_size", "theta_variants"):
+            if k in secondary:
+                roof[k] = secondary[k]
+    if c5 is not None:
+        roof["config5"] = c5
 
     line = {"metric": "elbo_grad_evals_per_sec", "value": value, "unit": "evals/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps,
@@ -575,11 +723,18 @@ def run_ours(args):
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 128,
                     "steps": e2e_steps, "api": "sgp_elbo_grad_host (pinned host images streamed slab by slab)"},
-            "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "secondary": secondary,
+            "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "parity": parity,
+            "secondary": secondary,
             "result": {"loglik": float(vec[0]), "KL": out["KL"], "grad": [float(v) for v in vec[1:7]]}}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    if parity and "error" not in parity:
+        worst = max(parity[k] for k in ("loglik_rel", "KL_rel", "grad_rel_max", "lam_m_rel_max", "lam_var_rel_max",
+                                        "f_rel_max"))
+        if not (worst <= parity["tolerance"]) or parity["flags"] != 0:
+            print(f"bench.py: parity against the CPU port FAILED ({worst:.3e} > 1e-9)", file=sys.stderr)
+            sys.exit(3)
 
 
 def main():
@@ -590,6 +745,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--no-config5", action="store_true")
     ap.add_argument("--i8-slices", type=int, default=-1,
                     help="-1: library's choice (8 int8 slices on tcgen05 at this size), 0: fp64 DMMA products, 2..8")
     args = ap.parse_args()

@@ -51,20 +51,22 @@ def check_bounds(theta, lo, hi) -> Optional[str]:
 
 
 # --------------------------------------------------------------------------- a1: localker
-def pixel_grid(n: int) -> Tuple[torch.Tensor, torch.Tensor]:
-    """U:876-879: linspace(-1,1,n) grid, 'ij' indexing, flattened row-major: k = iy*n + ix."""
-    lin = torch.linspace(-1, 1, n, dtype=F64)
+def pixel_grid(n: int, device=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """U:876-879: linspace(-1,1,n) grid, 'ij' indexing, flattened row-major: k = iy*n + ix.
+    `device`: the reference builds everything on torch's default device (U:41); None = CPU.  bench.py passes the
+    GPU to time the reference-shaped computation on cuBLAS / cuSOLVER / ATen (the "library GPU baseline")."""
+    lin = torch.linspace(-1, 1, n, dtype=F64, device=device)
     gy, gx = torch.meshgrid(lin, lin, indexing="ij")
     return gx.reshape(-1), gy.reshape(-1)
 
 
-def build_C(theta, n: int, grad: bool = False):
+def build_C(theta, n: int, grad: bool = False, device=None):
     """Pixel-space covariance C(theta), RF mask, and dC for 5 hyper-parameters (U:861-914)."""
     eb = math.exp(_f(theta["-2log2beta"]))
     er = math.exp(_f(theta["-log2rho2"]))
     ex, ey = _f(theta["eps_0x"]), _f(theta["eps_0y"])
     amp = _f(theta["Amp"])
-    gx, gy = pixel_grid(n)
+    gx, gy = pixel_grid(n, device)
     log_alpha = -eb * ((gx - ex) ** 2 + (gy - ey) ** 2)          # U:880
     alpha = torch.exp(log_alpha)
     mask = alpha >= MASK_THRESHOLD                                # U:883
@@ -225,7 +227,7 @@ def estep_update(a, r, f, m_b, Kt_b, logA: float):
     """Newton update of (m_b, V_b), alpha = 1 branch (U:1428-1439)."""
     g, G = estep_terms(a, r, f, logA)
     q = Kt_b.shape[0]
-    V_new = torch.linalg.solve(torch.eye(q, dtype=F64) + Kt_b @ G, Kt_b)
+    V_new = torch.linalg.solve(torch.eye(q, dtype=F64, device=Kt_b.device) + Kt_b @ G, Kt_b)
     m_new = V_new @ (G @ m_b + g)
     return m_new, (V_new + V_new.T) / 2
 
@@ -246,7 +248,7 @@ def elbo_and_grad(theta, X, r, xtilde, n_px: int, B, m_b, V_b, logA: float, lamb
     Returns dict with loglik, KL, elbo (= loglik - KL), grad[key] = d(loglik - KL)/dtheta_key
     (the closure hands -elbo / -grad to LBFGS), and optionally lam_m / lam_var / f.
     """
-    C, mask, dC = build_C(theta, n_px, grad=True)                                   # U:2030
+    C, mask, dC = build_C(theta, n_px, grad=True, device=X.device)                  # U:2030
     xm, um = X[:, mask], xtilde[:, mask]
     same = X.shape[0] == xtilde.shape[0]                                            # ntilde == nt, U:2032
     Kt, dKt = arccos_kernel(theta, um, um, C, dC)                                   # U:2031
@@ -257,7 +259,7 @@ def elbo_and_grad(theta, X, r, xtilde, n_px: int, B, m_b, V_b, logA: float, lamb
     K_b = K @ B                                                                     # U:2049
     dKt_b = {k: B.T @ dKt[k] @ B for k in dKt}                                      # U:2061
     dK_b = {k: dK[k] @ B for k in dK}                                               # U:2062
-    Kt_inv_b = torch.linalg.solve(Kt_b, torch.eye(Kt_b.shape[0], dtype=F64))        # U:2067
+    Kt_inv_b = torch.linalg.solve(Kt_b, torch.eye(Kt_b.shape[0], dtype=F64, device=Kt_b.device))   # U:2067
     a = B if same else K_b @ Kt_inv_b                                               # U:2068
     lam_m, lam_var, dlam_m, dlam_var = moments(a, K_b, Kvec, m_b, V_b, dK_b, dKt_b, dKvec, Kt_inv_b)
     f = rate_mean(logA, lambda0, lam_m, lam_var)                                    # U:2070 (lambda0 not re-estimated)

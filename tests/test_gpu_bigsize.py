@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import BIG_CASES, case_inputs, load
+from helpers import BIG_CASES, case_inputs, load, record
 
 pytestmark = pytest.mark.gpu
 RTOL = 1e-9
@@ -29,7 +29,16 @@ def inputs(name):
     return _cache[name]
 
 
-def check(fx, out, moments=True):
+def check(fx, out, moments=True, tag=""):
+    keys_ = [str(k) for k in fx["theta_keys"]]
+    gerr = max(abs(out["grad"][k] - (fx["dloglik"][i] - fx["dKL"][i])) / max(abs(fx["dloglik"][i]), abs(fx["dKL"][i]))
+               for i, k in enumerate(keys_))
+    rec = dict(loglik=abs(out["loglik"] - float(fx["loglik"])) / abs(float(fx["loglik"])),
+               KL=abs(out["KL"] - float(fx["KL"])) / abs(float(fx["KL"])), grad_comp=gerr)
+    if moments:
+        rec["lam_var"] = np.abs(out["lam_var"].cpu().numpy() - fx["lam_var"]).max() / np.abs(fx["lam_var"]).max()
+        rec["lam_m"] = np.abs(out["lam_m"].cpu().numpy() - fx["lam_m"]).max() / np.abs(fx["lam_m"]).max()
+    record("big:" + tag, **rec)
     assert out["flags"] == 0
     assert out["p"] == int(fx["p"])
     assert abs(out["loglik"] - float(fx["loglik"])) <= RTOL * abs(float(fx["loglik"]))
@@ -76,7 +85,7 @@ def test_benchmark_size_int8_engine(name, path, projected):
     """8 int8 slices on tcgen05 (the benchmarked engine), multi-slab, separable and dense-C routes, projected on/off."""
     fx, out = run(name, SLAB[name], path, 8, projected)
     assert out["projected"] == float(projected)
-    check(fx, out)
+    check(fx, out, tag=f"{name}/i8/path{path}/proj{projected}")
 
 
 @pytest.mark.parametrize("path", [1, 2])
@@ -84,14 +93,14 @@ def test_benchmark_size_int8_engine(name, path, projected):
 def test_benchmark_size_dmma_engine(name, path):
     """Same cases with every product on the fp64 DMMA GEMM (i8_slices = 0)."""
     fx, out = run(name, SLAB[name], path, 0)
-    check(fx, out)
+    check(fx, out, tag=f"{name}/dmma/path{path}")
 
 
 @pytest.mark.parametrize("name", BIG_CASES)
 def test_benchmark_size_library_defaults(name):
     """No options at all: whatever bench.py's default path picks at this size (one slab of N rows)."""
     fx, out = run(name, 0, 0, -1)
-    check(fx, out)
+    check(fx, out, tag=f"{name}/defaults")
 
 
 @pytest.mark.parametrize("name", BIG_CASES)
@@ -105,4 +114,13 @@ def test_benchmark_size_host_buffers(name):
                                     st["m_b"], st["V_b"], st["logA"], st["lambda0"])
     finally:
         native.set_slab_rows(0, 0)
-    check(fx, out, moments=False)
+    check(fx, out, moments=False, tag=f"{name}/host")
+
+
+@pytest.mark.parametrize("name", BIG_CASES)
+def test_benchmark_size_seven_slices_for_the_image_products(name):
+    """i8_slices_images = 7: the two products that contract with the images (K_lin = X (UC)^T, D = X^T R: 4Npm of the
+    executed flops) on 28 slice pairs instead of 36, the m-space products (where lam_var's cancellation lives) on 8.
+    Must hold the same 1e-9 bar to be eligible as the default."""
+    fx, out = run(name, SLAB[name], 2, 8, i8_images=7)
+    check(fx, out, tag=f"{name}/images7")

@@ -209,3 +209,16 @@ def test_cache_is_keyed_on_content_not_on_the_address(theta_kind):
     finally:
         native.set_option(0, "path", 0)
         native.set_option(0, "i8_slices", -1)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_closure_seven_slices_for_the_image_products_only(name):
+    """i8_slices_images = 7 with the m-space products at 8 slices: unlike 7 slices everywhere (test above), this keeps
+    the rank-deficient fixture inside 1e-9 -- lam_var's cancellation lives in T = K Mfull^T, not in K_lin."""
+    from gaussian_processes_b200 import native
+    native.set_option(0, "i8_slices_images", 7)
+    try:
+        fx, out = run_case(name, slab=128, path=2, i8=8)
+    finally:
+        native.set_option(0, "i8_slices_images", -1)
+    check(fx, out)
