@@ -73,6 +73,7 @@ struct sgp_handle {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   cudaStream_t chain_stream = nullptr; cudaEvent_t ev_chain_fork = nullptr, ev_chain_join = nullptr;
   int overlap = 1;          // 1 = run the q x q inducing-point chain next to the first slab's quadratic forms
+  int support = -1;         // pixel set of the cached image copies: -1 = mask grown by 2 px, reused while the mask stays inside; 0 = the mask itself; 1 = whole grid
   int projected = -1;       // moments in the projected basis (K_b = K B): -1 = when q is small enough to pay, 0 = never, 1 = always
   DevBuf hx[2], hr, small;
   cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr}, ev_small = nullptr;
@@ -251,6 +252,7 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
   else if (n == "path") h->path = (int)value;
   else if (n == "overlap") h->overlap = value != 0.0;
   else if (n == "projected") h->projected = (int)value;
+  else if (n == "support") h->support = (int)value;
   else if (n == "i8_slices") {
     if (value != -1 && value != 0 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices must be -1, 0 or 2..8");
     h->i8_slices = (int)value;
@@ -539,8 +541,60 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
 
   // ---- host: mask / coordinates (U:880-887) ------------------------------------------------------
   std::vector<uint8_t> mask; std::vector<int> idx; std::vector<double> gx, gy;
-  const int p = compute_mask(in.theta, n, mask, idx, gx, gy);
-  if (p == 0) return fail(h, SGP_E_ARG, "sgp_elbo_grad: empty receptive-field mask");
+  const int p_true = compute_mask(in.theta, n, mask, idx, gx, gy);
+  if (p_true == 0) return fail(h, SGP_E_ARG, "sgp_elbo_grad: empty receptive-field mask");
+  // ---- support: the pixel set the evaluation runs on, a SUPERSET of the mask ------------------------------
+  // The mask is recomputed from theta in every closure (U:2030) and flips pixels inside an LBFGS line search (parity
+  // trap 5).  Gathering X[:, mask] and slicing it again at every flip costs more than a few extra columns, so the
+  // gathered copy / int8 slices are built on a support S >= mask (the mask grown by two pixels, or the whole grid) and
+  // kept while the mask stays inside S.  Pixels of S outside the mask get C = 0 rows / columns (coordinates at 1e30:
+  // alpha = exp(-e^beta * 1e60) = 0 exactly, so C, every dC_k and the separable weights vanish there): they add exact
+  // zeros to every product, and the result is the one the reference computes on x[:, mask].
+  std::vector<uint8_t> support = mask;
+  if (p_true < (int)P && !streaming && h->support != 0) {
+    const bool same_images = h->cache_valid && h->cache_token == h->image_token && h->cache_X == in.X && h->cache_N == N &&
+                             h->cache_ldx == in.ldx && h->cache_U == in.U && h->cache_m == m && h->cache_ldu == in.ldu &&
+                             h->cache_mask.size() == (size_t)P;
+    bool reuse = false;
+    if (same_images && h->support < 0) {
+      long cs = 0; bool inside = true;
+      for (long k = 0; k < P; ++k) { cs += h->cache_mask[k]; if (mask[k] && !h->cache_mask[k]) inside = false; }
+      reuse = inside && 10L * p_true >= 6L * cs;     // and the support has not become wastefully large for this mask
+    }
+    if (reuse) support = h->cache_mask;
+    else if (h->support > 0) support.assign((size_t)P, 1);
+    else {
+      for (int pass = 0; pass < 2; ++pass) {         // grow by one pixel ring per pass (8-neighbourhood)
+        std::vector<uint8_t> g = support;
+        for (int iy = 0; iy < n; ++iy)
+          for (int ix = 0; ix < n; ++ix) {
+            if (support[(size_t)iy * n + ix]) continue;
+            bool near = false;
+            for (int dy = -1; dy <= 1 && !near; ++dy)
+              for (int dx = -1; dx <= 1; ++dx) {
+                const int y = iy + dy, x = ix + dx;
+                if (y >= 0 && y < n && x >= 0 && x < n && support[(size_t)y * n + x]) { near = true; break; }
+              }
+            if (near) g[(size_t)iy * n + ix] = 1;
+          }
+        support.swap(g);
+      }
+      long cs = 0; for (long k = 0; k < P; ++k) cs += support[k];
+      if (10 * cs >= 9 * P) support.assign((size_t)P, 1);   // nearly everything: read the images in place instead
+    }
+  }
+  if (support != mask) {      // index / coordinate lists over the support; 1e30 marks the pixels outside the mask
+    idx.clear(); gx.clear(); gy.clear();
+    for (int iy = 0; iy < n; ++iy)
+      for (int ix = 0; ix < n; ++ix) {
+        const size_t k = (size_t)iy * n + ix;
+        if (!support[k]) continue;
+        idx.push_back((int)k);
+        gx.push_back(mask[k] ? lin_coord(ix, n) : 1.0e30);
+        gy.push_back(mask[k] ? lin_coord(iy, n) : 1.0e30);
+      }
+  }
+  const int p = (int)idx.size();     // from here on "p" is the size of the support; p_true is what the reference calls p
   const ThetaDev th = make_theta(in.theta);
   const double A = std::exp(in.logA);
   const long ldp = rup(p, 16), ldm = rup(m, 16), ldq = rup(q, 16);
@@ -548,7 +602,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const long ldpartN = rup(slab, 16), ldpartU = ldm;
   const int ntp = (int)((p + 127) / 128), ntm = (int)((m + 127) / 128);
   const int ntp_s = (int)((p + 63) / 64);
-  const bool full_mask = (p == P);
+  const bool full_mask = (p == P);            // of the SUPPORT: the images are read in place, no gathered copy
   // separable path (sep_quad.cu): 8 n^3 flops per image for the quadratic forms instead of 4 p^2 dense ones
   bool use_sep = sep_quad_supported(n) && (12.0 * n * n * n < 4.0 * (double)p * p);
   if (h->path == 1) use_sep = false;
@@ -561,7 +615,10 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const int ozS = use_sep ? ozM : 0;
   // ozI: slice count of the two products that contract with the images (K_lin = X (UC)^T, D = X^T R): they are 4Npm of
   // the executed flops and sit upstream of the cancellation in lam_var (which lives in T = K Mfull^T, kept at ozM)
-  const int ozI = ozS ? (h->i8_slices_images > 0 ? h->i8_slices_images : ozS) : 0;
+  // Default (both options on auto): 7 slices = 28 slice pairs instead of 36.  Measured against the real reference at
+  // n = 40, m = 500 / 1000 (tests/test_gpu_bigsize.py, profiles/r2_parity_report_v1.jsonl): gradients 3e-11 of their
+  // cancellation scale, lam_m 4e-12 -- the same class as 8 slices, because the moments' cancellation is downstream.
+  const int ozI = ozS ? (h->i8_slices_images > 0 ? h->i8_slices_images : (h->i8_slices < 0 ? 7 : ozS)) : 0;
   // Moments in the projected basis when the kept subspace is small (q < m): K_b = K B, T_b = K_b Mg^T, T = T_b B^T and
   // K_b^T diag(v) K_b cost 4Nmq + 3Nq^2 flops against the 3Nm^2 of K Mfull^T and K^T diag(v) K (break-even q = 0.54 m;
   // the extra slicing passes move it down).  Same numbers up to rounding: Mfull = B Mg B^T.
@@ -579,14 +636,15 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     for (int c = 0; c < p; ++c) {
       const int iy = idx[c] / n, ix = idx[c] % n;
       off[c] = iy * ldq_sep + ix;
-      alpha[c] = std::exp(-th.eb * ((gx[c] - th.ex) * (gx[c] - th.ex) + (gy[c] - th.ey) * (gy[c] - th.ey)));
+      alpha[c] = mask[idx[c]] ? std::exp(-th.eb * ((gx[c] - th.ex) * (gx[c] - th.ex) + (gy[c] - th.ey) * (gy[c] - th.ey)))
+                              : 0.0;
     }
   }
 
   // ---- gathered / aligned copies of the images (cached across calls while the mask is unchanged) --
   const bool direct_X = !streaming && full_mask && (in.ldx % 2 == 0) && ((uintptr_t)in.X % 16 == 0);
   const bool direct_U = full_mask && (in.ldu % 2 == 0) && ((uintptr_t)in.U % 16 == 0);
-  bool regather = !h->cache_valid || h->cache_token != h->image_token || h->cache_mask != mask || h->cache_X != in.X ||
+  bool regather = !h->cache_valid || h->cache_token != h->image_token || h->cache_mask != support || h->cache_X != in.X ||
                   h->cache_N != N || h->cache_ldx != in.ldx || h->cache_U != in.U || h->cache_m != m ||
                   h->cache_ldu != in.ldu;
   if (streaming) regather = true;
@@ -785,7 +843,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   if (regather) {
     if (!direct_X && !streaming) gather_cols(in.X, in.ldx, N, d_idx, p, (double*)Xg, ldp, st);
     if (!direct_U) gather_cols(in.U, in.ldu, m, d_idx, p, (double*)Ug, ldp, st);
-    h->cache_mask = mask; h->cache_X = in.X; h->cache_N = N; h->cache_ldx = in.ldx;
+    h->cache_mask = support; h->cache_X = in.X; h->cache_N = N; h->cache_ldx = in.ldx;
     h->cache_U = in.U; h->cache_m = m; h->cache_ldu = in.ldu; h->cache_token = h->image_token;
   }
   (void)cache_was_valid;
@@ -940,7 +998,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
       SepQuadArgs sq{};
       sq.X = Xs; sq.ldx = ldxs; sq.nrows = ns; sq.p = p; sq.off = d_off; sq.alpha = d_alpha; sq.n = n;
       sq.er = th.er; sq.eb = th.eb; sq.ex = th.ex; sq.ey = th.ey; sq.amp = th.amp; sq.s02 = th.s02;
-      sq.s = s_s; sq.nrm = X1; sq.Q = Qs; sq.full = full_mask ? 1 : 0;
+      sq.s = s_s; sq.nrm = X1; sq.Q = Qs; sq.full = (p_true == (int)P) ? 1 : 0;
       if (chain_overlap && slab_i == 0) sq.max_ctas = num_sms() - 20;   // leave SMs to the inducing-point chain
       CU(sep_quad(sq, st));
       mark(2);
@@ -1168,7 +1226,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   sum_to_slots(gpart, p, 5, 5, h->d_scal, kSlotG, 0, st);
   if (use_sep) sum_to_slots(h->d_scal + kSlotGW, 1, 5, 5, h->d_scal, kSlotG, 1, st);
   if (side_pending) CU(cudaStreamWaitEvent(st, h->ev_join, 0));
-  finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p, in.logdetV_host ? *in.logdetV_host : 0.0,
+  finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p_true, in.logdetV_host ? *in.logdetV_host : 0.0,
            in.logdetV_host ? 1 : 0, h->d_out, st);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(double) * 16, cudaMemcpyDeviceToHost, st));

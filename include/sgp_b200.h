@@ -65,6 +65,10 @@ SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
  * 8 is the error class of a DGEMM and the default, 4 gives 27 bits per operand -- the fp32-class setting),
  * "i8_slices_images" (-1 = same as "i8_slices", 2..8 = slice count of the two products that contract with the
  * images, K_lin = X (UC)^T and D = X^T R; the m-space products keep "i8_slices"),
+ * "support" (pixel set the cached copies / int8 slices of the images are built on: -1 = the receptive-field mask grown
+ * by two pixels, kept while later masks stay inside it -- the mask is recomputed from theta in every closure
+ * (utils.py:2030) and flips pixels during a line search; 0 = exactly the mask, as the reference gathers x[:, mask];
+ * 1 = the whole grid, images read in place.  Pixels of the support outside the mask carry C = 0, i.e. exact zeros),
  * "projected" (-1 = moments in the projected basis K_b = K B when q <= 0.4 m, 0 = never, 1 = always; same numbers
  * up to rounding, utils.py:2047-2068), "overlap" (1 = the q x q chains run on side streams).
  * With int8 slices the library keeps a sliced copy of device-resident images across calls (same bytes as X).     */

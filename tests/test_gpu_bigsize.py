@@ -54,9 +54,10 @@ def check(fx, out, moments=True, tag=""):
         assert np.allclose(out["f"].cpu().numpy(), fx["f"], rtol=RTOL, atol=0)
 
 
-def run(name, slab, path, i8, projected=-1, i8_images=None):
+def run(name, slab, path, i8, projected=-1, i8_images=None, support=-1):
     from gaussian_processes_b200 import native
     fx, prob, st, dv = inputs(name)
+    native.set_option(0, "support", support)
     native.set_slab_rows(0, slab)
     native.set_option(0, "path", path)
     native.set_option(0, "i8_slices", i8)
@@ -72,6 +73,7 @@ def run(name, slab, path, i8, projected=-1, i8_images=None):
         native.set_option(0, "i8_slices", -1)
         native.set_option(0, "projected", -1)
         native.set_option(0, "i8_slices_images", -1)
+        native.set_option(0, "support", -1)
     return fx, out
 
 
@@ -124,3 +126,56 @@ def test_benchmark_size_seven_slices_for_the_image_products(name):
     Must hold the same 1e-9 bar to be eligible as the default."""
     fx, out = run(name, SLAB[name], 2, 8, i8_images=7)
     check(fx, out, tag=f"{name}/images7")
+
+
+@pytest.mark.parametrize("support", [0, 1])
+@pytest.mark.parametrize("path,i8", [(2, 8), (2, 0), (1, 8)])
+def test_benchmark_size_support_variants(path, i8, support):
+    """Localised theta at n = 40 (p = 821 of 1600 pixels): the evaluation on exactly the mask (support 0, the
+    reference's x[:, mask]) and on the whole grid with C = 0 outside the mask (support 1: images read in place, int8
+    slices shared by every mask) -- the default (mask grown by two pixels) is covered by the tests above."""
+    from gaussian_processes_b200 import native
+    native.invalidate_cache(0)
+    fx, out = run("closure_c2_local_n40", 4096, path, i8, support=support)
+    check(fx, out, tag=f"local/support{support}/path{path}/i8_{i8}")
+
+
+def test_mask_flips_reuse_the_cached_support():
+    """A line search moves eps_0 / beta, the 1e-3 mask flips pixels (parity trap 5; p = 821, 820, 811, 804, 796 here):
+    evaluations whose mask stays inside the cached support must not re-gather / re-slice the images, and must agree
+    with a pristine evaluation at the same theta."""
+    from gaussian_processes_b200 import native
+    fx, prob, st, dv = inputs("closure_c2_local_n40")
+
+    def ev(theta):
+        return native.elbo_grad(dv["X"], dv["r"], dv["xt"], prob.n_px_side, theta, dv["B"], dv["m_b"], dv["V_b"],
+                                st["logA"], st["lambda0"])
+    native.invalidate_cache(0)
+    thetas = []
+    for k in range(5):
+        th = dict(prob.theta)
+        th["eps_0x"] += 0.013 * k
+        th["-2log2beta"] += 0.01 * k
+        thetas.append(th)
+    ps = [int(native.mask_host(t, prob.n_px_side).sum()) for t in thetas]
+    assert len(set(ps)) > 2, ps                       # the masks really differ
+    try:
+        ev(thetas[0])
+        native.launch_count(0, reset=True)
+        seq = [ev(t) for t in thetas[1:]]
+        n_seq = native.launch_count(0)
+        fresh, n_fresh = [], 0
+        for t in thetas[1:]:
+            native.invalidate_cache(0)
+            native.launch_count(0, reset=True)
+            fresh.append(ev(t))
+            n_fresh += native.launch_count(0)
+        assert n_seq < n_fresh                        # no gather / slicing launches while the support holds
+        for a, b, pp in zip(seq, fresh, ps[1:]):
+            assert a["p"] == pp == b["p"] and a["flags"] == 0
+            assert abs(a["loglik"] - b["loglik"]) <= 1e-12 * abs(b["loglik"])
+            gmax = max(abs(v) for v in b["grad"].values())
+            for k in a["grad"]:
+                assert abs(a["grad"][k] - b["grad"][k]) <= 1e-10 * gmax
+    finally:
+        native.invalidate_cache(0)

@@ -222,3 +222,20 @@ def test_closure_seven_slices_for_the_image_products_only(name):
     finally:
         native.set_option(0, "i8_slices_images", -1)
     check(fx, out)
+
+
+@pytest.mark.parametrize("support", [-1, 0, 1])
+@pytest.mark.parametrize("path,i8", [(1, 0), (2, 0), (2, 8), (1, 8)])
+@pytest.mark.parametrize("name", ["closure_rankdef_n10", "closure_c1_local"])   # p = 24 of 100 pixels / full mask
+def test_closure_on_a_support_larger_than_the_mask(name, path, i8, support):
+    """Option "support": the evaluation runs on a pixel set S >= mask (mask grown by two pixels / whole grid) with C = 0
+    outside the mask, so that cached image copies and int8 slices survive mask flips.  Same 1e-9 bar against the
+    reference, which gathers x[:, mask] exactly (U:2031-2033)."""
+    from gaussian_processes_b200 import native
+    native.set_option(0, "support", support)
+    native.invalidate_cache(0)
+    try:
+        fx, out = run_case(name, slab=128 if i8 else None, path=path, i8=i8)
+    finally:
+        native.set_option(0, "support", -1)
+    check(fx, out)

@@ -54,14 +54,14 @@ def test_vargp_tracks_match_reference_on_gpu(U):
            loglik=rel_err(vt["loss_track"]["loglikelihood"].cpu().numpy(), fx["loglikelihood"]),
            KL=rel_err(vt["loss_track"]["KL"].cpu().numpy(), fx["KL"]), theta=rel_err(got_t, fx["theta_track"]),
            logA=rel_err(vt["f_par_track"]["logA"].cpu().numpy(), fx["logA_track"]))
-    # 3 EM iterations x (3 E-steps with an LBFGS on logA + 3 LBFGS M-step iterations with strong-Wolfe line searches):
-    # an evaluation that agrees to 1e-11 is amplified by the optimisers' own conditioning; measured 1e-9..1e-8
-    tol = 1e-7
+    # 3 EM iterations x (3 E-steps with an LBFGS on logA + 3 LBFGS M-step iterations with strong-Wolfe line searches);
+    # measured on the B200: 2e-13 (loss tracks) .. 4e-12 (theta tracks), profiles/r2_parity_report_v1.jsonl
+    tol = 1e-9
     assert np.allclose(vt["loss_track"]["logmarginal"].cpu().numpy(), fx["logmarginal"], rtol=tol)
     assert np.allclose(vt["loss_track"]["loglikelihood"].cpu().numpy(), fx["loglikelihood"], rtol=tol)
-    assert np.allclose(vt["loss_track"]["KL"].cpu().numpy(), fx["KL"], rtol=tol, atol=1e-8)
+    assert np.allclose(vt["loss_track"]["KL"].cpu().numpy(), fx["KL"], rtol=tol, atol=1e-10)
     got = np.stack([vt["theta_track"][k].cpu().numpy() for k in keys])
-    assert np.allclose(got, fx["theta_track"], rtol=tol, atol=1e-8)
+    assert np.allclose(got, fx["theta_track"], rtol=tol, atol=1e-10)
     assert np.allclose(vt["f_par_track"]["logA"].cpu().numpy(), fx["logA_track"], rtol=tol)
     assert np.allclose(vt["f_par_track"]["lambda0"].cpu().numpy(), fx["lambda0_track"], rtol=tol)
     assert fit["V_b"].is_cuda and fit["K_b"].is_cuda
