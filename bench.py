@@ -476,6 +476,79 @@ def config5_leg(native, sharded, dist, dev, world, rank, n, xt, theta, B, m_b, V
             "loglik": out["loglik"], "flags": int(out["flags"]), "torch_max_allocated_gb": mem / 1e9}
 
 
+def config4_leg(native, dist, dev, world, rank, n, m, logA, lambda0, steps=2, warm=1):
+    """BASELINE configs[3]: population fit -- 256 independent cells sharing N = 200 000 stimuli of 40 x 40, the cells
+    sharded across the GPUs (32 per GPU at 8; every rank times 32 cells, the per-GPU load of that configuration, so the
+    1-GPU run is a bounded sample of the population and the 8-GPU run is the whole of it).  Receptive-field centres drawn
+    uniformly in [-0.5, 0.5]^2 (seed 4000), dense theta otherwise; own spikes, own subspace and variational
+    state per cell.  No data-path collective.  One "step" = every cell of every rank evaluated once."""
+    from gaussian_processes_b200 import population
+    N4 = int(os.environ.get("SGP_BENCH_C4_N", 200000))
+    ncells_total = int(os.environ.get("SGP_BENCH_C4_CELLS", 256))
+    per_gpu = int(os.environ.get("SGP_BENCH_C4_CELLS_PER_GPU", 32))
+    local = dev.index or 0
+    native.release_cache(local)
+    torch.cuda.empty_cache()
+    g = torch.Generator(device=dev).manual_seed(4100)              # the stimuli are shared: same seed on every rank
+    X4 = torch.randn(N4, n * n, generator=g, dtype=torch.float64, device=dev)
+    xt = X4[:m].clone()
+    ge = torch.Generator().manual_seed(4000)
+    eps_all = torch.rand(ncells_total, 2, generator=ge, dtype=torch.float64) - 0.5
+    first = (rank * per_gpu) % ncells_total
+    lin = torch.linspace(-1, 1, n, dtype=torch.float64, device=dev)
+    yc, xc = torch.meshgrid(lin, lin, indexing="ij")
+    gc = torch.Generator(device=dev).manual_seed(4200 + rank)
+    cells = []
+    for j in range(per_gpu):
+        ex, ey = (float(v) for v in eps_all[(first + j) % ncells_total])
+        th = dict(synth.THETA_DENSE)
+        th["eps_0x"], th["eps_0y"] = ex, ey
+        Cm, mask = native.localker(th, n, dev)
+        um = xt if bool(mask.all()) else xt[:, mask].contiguous()
+        Kt = native.acosker(th["sigma_0"], um, um, Cm, True)
+        ev, evec = torch.linalg.eigh(Kt, UPLO="L")
+        keep = ev > max(float(ev.max()) * 1e-4, 1e-4)
+        mb, Vb = synth.make_variational_state(torch.diag(ev[keep]).cpu(), 400 + first + j)
+        w = torch.exp(-((xc.flatten() - ex) ** 2 + (yc.flatten() - ey) ** 2) / (2 * 0.15 ** 2))
+        drive = X4 @ w
+        r = torch.poisson(torch.exp(0.8 * drive / drive.std() - 0.5), generator=gc)
+        cells.append(dict(theta=th, r=r, B=evec[:, keep].contiguous(), m_b=mb.to(dev), V_b=Vb.to(dev), logA=logA,
+                          lambda0=lambda0, p=int(mask.sum())))
+        del Kt, evec, drive
+    for _ in range(warm):
+        res = population.evaluate_cells(X4, xt, n, cells)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    native.launch_count(local, reset=True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        res = population.evaluate_cells(X4, xt, n, cells)
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    launches = native.launch_count(local)
+    t = torch.tensor([e0.elapsed_time(e1) * 1e-3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    el = float(t.item())
+    out = {"workload": "config4: %d cells per GPU of a %d-cell population sharing N=%d stimuli of %dx%d px, m=%d, cells "
+                       "sharded over %d GPU(s), no collective" % (per_gpu, ncells_total, N4, n, n, m, world),
+           "cells_per_gpu": per_gpu, "cells_evaluated": per_gpu * world, "population": ncells_total, "N": N4, "gpus": world,
+           "steps": steps, "ms_per_cell": 1e3 * el / (steps * per_gpu),
+           "cell_evals_per_sec": steps * per_gpu * world / el,
+           "population_evals_per_sec": steps * per_gpu * world / el / ncells_total,
+           "p_range": [min(c["p"] for c in cells), max(c["p"] for c in cells)],
+           "flags_any": int(any(x["flags"] for x in res)), "gpu_launches_per_cell": launches / (steps * per_gpu),
+           "fp64_equivalent_tflops_per_gpu": (4.0 * N4 * (n * n) * m + 3.0 * N4 * m * m + 6.4 * N4 * n ** 3) * steps * per_gpu / el / 1e12}
+    del X4, cells
+    native.release_cache(local)
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(args):
     import torch.distributed as dist
     from gaussian_processes_b200 import native, sharded
@@ -579,6 +652,12 @@ def run_ours(args):
             c5 = config5_leg(native, sharded, dist, dev, world, rank, n, xt, theta, B, m_b, V_b, prob.logA, prob.lambda0, sg)
         except Exception as e:  # pragma: no cover
             c5 = {"error": repr(e)}
+    c4 = None
+    if os.environ.get("SGP_BENCH_CONFIG4", "1") != "0" and not args.no_config4 and n == 40:
+        try:
+            c4 = config4_leg(native, dist, dev, world, rank, n, m, prob.logA, prob.lambda0)
+        except Exception as e:  # pragma: no cover
+            c4 = {"error": repr(e)}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -705,6 +784,8 @@ def run_ours(args):
                 roof[k] = secondary[k]
     if c5 is not None:
         roof["config5"] = c5
+    if c4 is not None:
+        roof["config4"] = c4
 
     line = {"metric": "elbo_grad_evals_per_sec", "value": value, "unit": "evals/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps,
@@ -746,6 +827,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true")
     ap.add_argument("--no-config5", action="store_true")
+    ap.add_argument("--no-config4", action="store_true")
     ap.add_argument("--i8-slices", type=int, default=-1,
                     help="-1: library's choice (8 int8 slices on tcgen05 at this size), 0: fp64 DMMA products, 2..8")
     args = ap.parse_args()

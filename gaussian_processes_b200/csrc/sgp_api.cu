@@ -67,6 +67,12 @@ struct sgp_handle {
   unsigned* d_ticket = nullptr;        // last-block-done counter of the streaming reductions (zero between launches)
   double* d_out = nullptr;
   double* h_out = nullptr;  // pinned
+  // pinned staging ring for the small per-evaluation uploads (pixel lists of the support): uploads from PAGEABLE memory
+  // synchronise the stream first, which would serialise back-to-back evaluations (cells, asynchronous calls)
+  static constexpr int kPinSlots = 4;
+  char* pin_base = nullptr; size_t pin_slot_bytes = 0; int pin_next = 0;
+  cudaEvent_t pin_ev[kPinSlots] = {nullptr, nullptr, nullptr, nullptr}; bool pin_used[kPinSlots] = {false, false, false, false};
+  DevBuf cells_out;
   std::map<std::string, DebugEntry> dbg;
   // second stream + events for the host-streaming variant
   cudaStream_t copy_stream = nullptr, compute_stream = nullptr, side_stream = nullptr;
@@ -224,6 +230,9 @@ int sgp_destroy(sgp_handle* h) {
     if (h->d_ticket) cudaFree(h->d_ticket);
     if (h->d_out) cudaFree(h->d_out);
     if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->pin_base) cudaFreeHost(h->pin_base);
+    for (int i = 0; i < sgp_handle::kPinSlots; ++i) if (h->pin_ev[i]) cudaEventDestroy(h->pin_ev[i]);
+    h->cells_out.release();
     for (int i = 0; i < 2; ++i) {
       if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]);
       if (h->ev_used[i]) cudaEventDestroy(h->ev_used[i]);
@@ -518,7 +527,31 @@ struct ClosureIn {
   // host streaming (X_host != nullptr): X / r above are ignored
   const double* X_host = nullptr; const double* r_host = nullptr;
   bool first_copy_issued = false;   // the caller already started the H2D copy of slab 0 into hx[0]
+  // asynchronous mode: the 16 result doubles go to out_dev (device memory) and the call returns without waiting for the
+  // stream -- the caller reads / reduces them in stream order (cells loop, device-side all-reduce of the image shards)
+  double* out_dev = nullptr;
+  int force_support = -2;           // -2: the handle's option; otherwise overrides it for this call
 };
+
+// one slot of the pinned upload ring, at least `bytes` large; waits until the copies last issued from it are done
+int pin_acquire(sgp_handle* h, size_t bytes, char** out, int* slot_out) {
+  if (bytes > h->pin_slot_bytes) {
+    CU(cudaDeviceSynchronize());
+    if (h->pin_base) cudaFreeHost(h->pin_base);
+    h->pin_base = nullptr; h->pin_slot_bytes = 0;
+    const size_t sb = (bytes + 65535) & ~size_t(65535);
+    CU(cudaMallocHost((void**)&h->pin_base, sb * sgp_handle::kPinSlots));
+    h->pin_slot_bytes = sb;
+    for (int i = 0; i < sgp_handle::kPinSlots; ++i) h->pin_used[i] = false;
+  }
+  const int sl = h->pin_next;
+  h->pin_next = (h->pin_next + 1) % sgp_handle::kPinSlots;
+  if (!h->pin_ev[sl]) CU(cudaEventCreateWithFlags(&h->pin_ev[sl], cudaEventDisableTiming));
+  if (h->pin_used[sl]) CU(cudaEventSynchronize(h->pin_ev[sl]));
+  *out = h->pin_base + (size_t)sl * h->pin_slot_bytes;
+  *slot_out = sl;
+  return SGP_OK;
+}
 
 int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream_t st) {
   const double t_entry = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -551,18 +584,19 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   // alpha = exp(-e^beta * 1e60) = 0 exactly, so C, every dC_k and the separable weights vanish there): they add exact
   // zeros to every product, and the result is the one the reference computes on x[:, mask].
   std::vector<uint8_t> support = mask;
-  if (p_true < (int)P && !streaming && h->support != 0) {
+  const int support_opt = in.force_support != -2 ? in.force_support : h->support;
+  if (p_true < (int)P && !streaming && support_opt != 0) {
     const bool same_images = h->cache_valid && h->cache_token == h->image_token && h->cache_X == in.X && h->cache_N == N &&
                              h->cache_ldx == in.ldx && h->cache_U == in.U && h->cache_m == m && h->cache_ldu == in.ldu &&
                              h->cache_mask.size() == (size_t)P;
     bool reuse = false;
-    if (same_images && h->support < 0) {
+    if (same_images && support_opt < 0) {
       long cs = 0; bool inside = true;
       for (long k = 0; k < P; ++k) { cs += h->cache_mask[k]; if (mask[k] && !h->cache_mask[k]) inside = false; }
       reuse = inside && 10L * p_true >= 6L * cs;     // and the support has not become wastefully large for this mask
     }
     if (reuse) support = h->cache_mask;
-    else if (h->support > 0) support.assign((size_t)P, 1);
+    else if (support_opt > 0) support.assign((size_t)P, 1);
     else {
       for (int pass = 0; pass < 2; ++pass) {         // grow by one pixel ring per pass (8-neighbourhood)
         std::vector<uint8_t> g = support;
@@ -802,15 +836,24 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   // stream for the slab's whole duration.
   if (streaming) CU(ensure_copy_stream(h));
   cudaStream_t up = streaming ? h->copy_stream : st;
-  CU(cudaMemcpyAsync(d_gx, gx.data(), sizeof(double) * p, cudaMemcpyHostToDevice, up));
-  CU(cudaMemcpyAsync(d_gy, gy.data(), sizeof(double) * p, cudaMemcpyHostToDevice, up));
-  CU(cudaMemcpyAsync(d_idx, idx.data(), sizeof(int) * p, cudaMemcpyHostToDevice, up));
+  {
+    char* pin = nullptr; int pslot = 0;
+    const size_t pb = (size_t)p * 8;
+    rc = pin_acquire(h, 5 * pb + 64, &pin, &pslot); if (rc) return rc;
+    std::memcpy(pin, gx.data(), pb); std::memcpy(pin + pb, gy.data(), pb); std::memcpy(pin + 2 * pb, idx.data(), (size_t)p * 4);
+    CU(cudaMemcpyAsync(d_gx, pin, pb, cudaMemcpyHostToDevice, up));
+    CU(cudaMemcpyAsync(d_gy, pin + pb, pb, cudaMemcpyHostToDevice, up));
+    CU(cudaMemcpyAsync(d_idx, pin + 2 * pb, (size_t)p * 4, cudaMemcpyHostToDevice, up));
+    if (use_sep) {
+      std::memcpy(pin + 3 * pb, off.data(), (size_t)p * 4); std::memcpy(pin + 4 * pb, alpha.data(), pb);
+      CU(cudaMemcpyAsync(d_off, pin + 3 * pb, (size_t)p * 4, cudaMemcpyHostToDevice, up));
+      CU(cudaMemcpyAsync(d_alpha, pin + 4 * pb, pb, cudaMemcpyHostToDevice, up));
+    }
+    CU(cudaEventRecord(h->pin_ev[pslot], up));
+    h->pin_used[pslot] = true;
+  }
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
   CU(cudaMemsetAsync(h->d_scal, 0, sizeof(double) * kNumSlots, st));
-  if (use_sep) {
-    CU(cudaMemcpyAsync(d_off, off.data(), sizeof(int) * p, cudaMemcpyHostToDevice, up));
-    CU(cudaMemcpyAsync(d_alpha, alpha.data(), sizeof(double) * p, cudaMemcpyHostToDevice, up));
-  }
   // ---- host streaming resources ------------------------------------------------------------------------
   if (streaming) {
     for (int i = 0; i < 2; ++i) CU(h->hx[i].reserve((size_t)slab * P * sizeof(double)));
@@ -1226,18 +1269,21 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   sum_to_slots(gpart, p, 5, 5, h->d_scal, kSlotG, 0, st);
   if (use_sep) sum_to_slots(h->d_scal + kSlotGW, 1, 5, 5, h->d_scal, kSlotG, 1, st);
   if (side_pending) CU(cudaStreamWaitEvent(st, h->ev_join, 0));
+  const bool async_out = in.out_dev != nullptr;
   finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p_true, in.logdetV_host ? *in.logdetV_host : 0.0,
-           in.logdetV_host ? 1 : 0, h->d_out, st);
+           in.logdetV_host ? 1 : 0, async_out ? in.out_dev : h->d_out, proj ? 1.0 : 0.0, st);
   CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(double) * 16, cudaMemcpyDeviceToHost, st));
+  if (!async_out) CU(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(double) * 16, cudaMemcpyDeviceToHost, st));
   mark(-1);
   const double t_enq = now_ms();
-  CU(cudaStreamSynchronize(st));
-  h->cache_valid = !streaming;           // everything the caches hold was produced by work that has now completed
+  // asynchronous calls return here: everything is enqueued in stream order, the caches are valid for later work on this
+  // stream.  (With option "profile" the stage events have to be read, so profiled calls always wait.)
+  if (!async_out || h->profile) CU(cudaStreamSynchronize(st));
+  h->cache_valid = !streaming;           // everything the caches hold is produced by work enqueued (or completed) on st
   h->oz_valid = !streaming && ozS > 0;
   if (dbg_t) fprintf(stderr, "[sgp timing] first copy issued %.3f ms after entry; all work enqueued at %.3f; done at %.3f\n",
                      t_issue - t_entry, t_enq - t_entry, now_ms() - t_entry);
-  if (out_host) { std::memcpy(out_host, h->h_out, sizeof(double) * 16); out_host[15] = proj ? 1.0 : 0.0; }
+  if (out_host && !async_out) std::memcpy(out_host, h->h_out, sizeof(double) * 16);
   if (h->profile) {
     for (size_t i = 0; i + 1 < h->prof_used; ++i) {
       float ms = 0.f;
@@ -1283,6 +1329,57 @@ int sgp_elbo_grad(sgp_handle* h, const double* X, long ldx, const double* r, lon
   in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = logdetV_host;
   in.lam_m = lam_m; in.lam_var = lam_var; in.f = f;
   return run_closure(h, in, out_host, (cudaStream_t)stream);
+}
+
+int sgp_elbo_grad_dev(sgp_handle* h, const double* X, long ldx, const double* r, long N, const double* xtilde, long ldu,
+                      int m, int n_px, const double* theta, const double* B, long ldb, int q, const double* m_b,
+                      const double* V_b, long ldv, double logA, double lambda0, const double* logdetV_host,
+                      double* lam_m, double* lam_var, double* f, double* out_dev, void* stream) {
+  if (!h || !X || !r || !xtilde || !theta || !B || !m_b || !V_b || !out_dev)
+    return fail(h, SGP_E_ARG, "sgp_elbo_grad_dev: null argument");
+  ClosureIn in{};
+  in.X = X; in.ldx = ldx; in.r = r; in.N = N; in.U = xtilde; in.ldu = ldu; in.m = m; in.n_px = n_px;
+  in.theta = theta; in.B = B; in.ldb = ldb; in.q = q; in.m_b = m_b; in.V = V_b; in.ldv = ldv;
+  in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = logdetV_host;
+  in.lam_m = lam_m; in.lam_var = lam_var; in.f = f; in.out_dev = out_dev;
+  return run_closure(h, in, nullptr, (cudaStream_t)stream);
+}
+
+int sgp_elbo_grad_cells(sgp_handle* h, const double* X, long ldx, long N, const double* xtilde, long ldu, int m,
+                        int n_px, int ncells, const double* const* r, const double* theta, const double* const* B,
+                        const long* ldb, const int* q, const double* const* m_b, const double* const* V_b,
+                        const long* ldv, const double* logA, const double* lambda0, const double* logdetV,
+                        double* out_host, void* stream) {
+  if (!h || !X || !xtilde || !r || !theta || !B || !ldb || !q || !m_b || !V_b || !ldv || !logA || !lambda0 || !out_host)
+    return fail(h, SGP_E_ARG, "sgp_elbo_grad_cells: null argument");
+  if (ncells <= 0) return fail(h, SGP_E_ARG, "sgp_elbo_grad_cells: ncells <= 0");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  CU(h->cells_out.reserve((size_t)ncells * 16 * sizeof(double)));
+  double* d_out = (double*)h->cells_out.p;
+  // every cell has its own receptive field, hence its own mask; they all run on the whole pixel grid (C = 0 outside a
+  // cell's mask) so that ONE resident copy of the images and ONE set of int8 slices serves the population
+  const long P = (long)n_px * n_px;
+  bool any_cropped = false;
+  for (int c = 0; c < ncells && !any_cropped; ++c) {
+    int pc = 0;
+    sgp_mask_host(theta + 6 * c, n_px, nullptr, &pc);
+    any_cropped = pc < P;
+  }
+  for (int c = 0; c < ncells; ++c) {
+    if (!r[c] || !B[c] || !m_b[c] || !V_b[c]) return fail(h, SGP_E_ARG, "sgp_elbo_grad_cells: null per-cell pointer");
+    ClosureIn in{};
+    in.X = X; in.ldx = ldx; in.r = r[c]; in.N = N; in.U = xtilde; in.ldu = ldu; in.m = m; in.n_px = n_px;
+    in.theta = theta + 6 * c; in.B = B[c]; in.ldb = ldb[c]; in.q = q[c]; in.m_b = m_b[c]; in.V = V_b[c]; in.ldv = ldv[c];
+    in.logA = logA[c]; in.lambda0 = lambda0[c]; in.logdetV_host = logdetV ? logdetV + c : nullptr;
+    in.out_dev = d_out + 16 * c;
+    in.force_support = any_cropped ? 1 : -2;
+    rc = run_closure(h, in, nullptr, st);
+    if (rc) return rc;
+  }
+  CU(cudaMemcpyAsync(out_host, d_out, (size_t)ncells * 16 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return SGP_OK;
 }
 
 int sgp_elbo_grad_host(sgp_handle* h, const double* X_host, long ldx, const double* r_host, long N,

@@ -805,7 +805,7 @@ void contract_dC(const double* GCpart, int nz, long zstride, const double* GCext
 
 __global__ void finalize_kernel(const double* __restrict__ scal, const int* __restrict__ flags, double A,
                                 double lambda0, ThetaDev th, int p, double logdetV_override, int use_override,
-                                double* __restrict__ out) {
+                                double* __restrict__ out, double out15) {
   const double s0 = th.s0, amp = th.amp, eb = th.eb;
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   const double logdetV = use_override ? logdetV_override : scal[kSlotLogdetV];
@@ -828,12 +828,12 @@ __global__ void finalize_kernel(const double* __restrict__ scal, const int* __re
   out[12] = scal[kSlotRLam];
   out[13] = scal[kSlotLogdetK];
   out[14] = logdetV;
-  out[15] = 0.0;
+  out[15] = out15;
 }
 
 void finalize(const double* scal, const int* flags, double A, double lambda0, const ThetaDev& th, int p,
-              double logdetV_override, int use_override, double* out, cudaStream_t st) {
-  note_launch(); finalize_kernel<<<1, 32, 0, st>>>(scal, flags, A, lambda0, th, p, logdetV_override, use_override, out);
+              double logdetV_override, int use_override, double* out, double out15, cudaStream_t st) {
+  note_launch(); finalize_kernel<<<1, 32, 0, st>>>(scal, flags, A, lambda0, th, p, logdetV_override, use_override, out, out15);
 }
 
 

@@ -128,9 +128,9 @@ void contract_dC(const double* GCpart, int nz, long zstride, const double* GCext
                  const double* gx, const double* gy, const ThetaDev& th, double* gpart, cudaStream_t st);
 
 // out[0] loglik, [1] KL, [2..7] d(loglik-KL)/d(sigma_0, eps_0x, eps_0y, -2log2beta, -log2rho2, Amp),
-// [8] flags, [9] p, [10] sum r, [11] sum f, [12] sum r*lam_m, [13] logdet K_tilde_b, [14] logdet V_b, [15] 0
+// [8] flags, [9] p, [10] sum r, [11] sum f, [12] sum r*lam_m, [13] logdet K_tilde_b, [14] logdet V_b, [15] out15 (1 = moments in the projected basis)
 void finalize(const double* scal, const int* flags, double A, double lambda0, const ThetaDev& th, int p,
-              double logdetV_override, int use_override, double* out, cudaStream_t st);
+              double logdetV_override, int use_override, double* out, double out15, cudaStream_t st);
 
 
 // ---- E-step / f-param helpers -------------------------------------------------------------------

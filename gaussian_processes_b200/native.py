@@ -320,6 +320,75 @@ def elbo_grad(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int,
     return res
 
 
+def elbo_grad_dev(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
+                  m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float,
+                  logdetV: Optional[float] = None, kl_weight: float = 1.0,
+                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Asynchronous fused closure (sgp_elbo_grad_dev): returns the 16 result doubles as a DEVICE tensor (layout
+    OUT_KEYS) without synchronising the host; the caller reduces / reads them in stream order."""
+    _need_cuda(X, r, xtilde, B, m_b, V_b)
+    set_option(X.device.index if X.device.index is not None else torch.cuda.current_device(), "kl_weight", kl_weight)
+    X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
+    r, m_b = r.contiguous(), m_b.contiguous()
+    N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]
+    if out is None:
+        out = torch.empty(16, dtype=torch.float64, device=X.device)
+    ldv_val = C.c_double(logdetV if logdetV is not None else 0.0)
+    h = _h(X)
+    h.bind_images(X, xtilde)
+    h.check(lib.sgp_elbo_grad_dev(h.ptr, _ptr(X), _ld(X), _ptr(r), N, _ptr(xtilde), _ld(xtilde), int(m), int(n_px),
+                                  theta_array(theta), _ptr(B), _ld(B), int(q), _ptr(m_b), _ptr(V_b), _ld(V_b),
+                                  float(logA), float(lambda0), C.byref(ldv_val) if logdetV is not None else None,
+                                  None, None, None, _ptr(out), _stream(X.device)))
+    return out
+
+
+def result_dict(vals) -> Dict:
+    """OUT_KEYS dict (+ grad / int flags) from 16 doubles."""
+    res = dict(zip(OUT_KEYS, [float(v) for v in vals]))
+    res["grad"] = {k: res["g_" + k] for k in THETA_KEYS}
+    res["flags"] = int(res["flags"])
+    res["p"] = int(res["p"])
+    return res
+
+
+def elbo_grad_cells(X: torch.Tensor, r: Sequence[torch.Tensor], xtilde: torch.Tensor, n_px: int, thetas: Sequence,
+                    B: Sequence[torch.Tensor], m_b: Sequence[torch.Tensor], V_b: Sequence[torch.Tensor],
+                    logA: Sequence[float], lambda0: Sequence[float],
+                    logdetV: Optional[Sequence[float]] = None) -> list:
+    """Population fit (sgp_elbo_grad_cells): one fused closure per cell, back to back on the current stream, all cells
+    on the same resident images and the same int8 slices of them.  Returns one result dict per cell."""
+    nc = len(thetas)
+    if not (len(r) == len(B) == len(m_b) == len(V_b) == len(logA) == len(lambda0) == nc):
+        raise ValueError("elbo_grad_cells: per-cell argument lists differ in length")
+    _need_cuda(X, xtilde, *r, *B, *m_b, *V_b)
+    X, xtilde = _c(X), _c(xtilde)
+    r = [t.contiguous() for t in r]
+    B = [_c(t) for t in B]
+    V_b = [_c(t) for t in V_b]
+    m_b = [t.contiguous() for t in m_b]
+    N, m = X.shape[0], xtilde.shape[0]
+    th = (C.c_double * (6 * nc))(*[float(t[k]) if isinstance(t, dict) else float(t[i])
+                                    for t in thetas for i, k in enumerate(THETA_KEYS)])
+
+    def parr(ts):
+        return (C.c_void_p * nc)(*[t.data_ptr() for t in ts])
+    ldb = (C.c_long * nc)(*[_ld(t) for t in B])
+    ldv = (C.c_long * nc)(*[_ld(t) for t in V_b])
+    qs = (C.c_int * nc)(*[t.shape[1] for t in B])
+    la = (C.c_double * nc)(*[float(v) for v in logA])
+    l0 = (C.c_double * nc)(*[float(v) for v in lambda0])
+    ldvv = (C.c_double * nc)(*[float(v) for v in logdetV]) if logdetV is not None else None
+    out = (C.c_double * (16 * nc))()
+    h = _h(X)
+    h.bind_images(X, xtilde)
+    h.check(lib.sgp_elbo_grad_cells(h.ptr, _ptr(X), _ld(X), N, _ptr(xtilde), _ld(xtilde), int(m), int(n_px), nc, parr(r),
+                                    th, parr(B), ldb, qs, parr(m_b), parr(V_b), ldv, la, l0, ldvv, out,
+                                    _stream(X.device)))
+    vals = list(out)
+    return [result_dict(vals[16 * c:16 * c + 16]) for c in range(nc)]
+
+
 def elbo_grad_host(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
                    m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float, device: int = 0) -> Dict:
     """Same evaluation with every operand in HOST memory (pinned preferred); H2D streamed slab by slab."""

@@ -48,6 +48,22 @@ class ShardGroup:
         self.calls += 1
         return t
 
+    def reduce_result_(self, out_dev: torch.Tensor):
+        """The one exchange step of an image-sharded evaluation, on the DEVICE and in stream order: the 16 result doubles
+        of sgp_elbo_grad_dev stay where the kernel wrote them, entries [0..8] (loglik, KL, 6 gradients, flags) are
+        all-reduced in place over NCCL on the launching stream, and the host reads them back ONCE.  KL is identical on
+        every rank and must count once: ranks > 0 zero their copy first (the KL part of their gradient is already
+        weighted by kl_weight = 0)."""
+        if self.rank != 0:
+            out_dev[1:2].zero_()
+        # status bits do not survive a sum; what the callers need is "K_tilde_b was not positive definite on some rank"
+        # (bits 1 | 2): reduce that as a count
+        fl = out_dev[8:9]
+        fl.copy_(torch.remainder(fl, 4.0).gt(0.0))
+        dist.all_reduce(out_dev[:9], op=dist.ReduceOp.SUM, group=self.group)
+        self.calls += 1
+        return out_dev.cpu().tolist()          # the only host synchronisation of the evaluation
+
 
 def enable(group=None, device=None) -> ShardGroup:
     """Make ``utils`` treat its ``x`` / ``r`` arguments as this rank's block of the images."""
@@ -77,6 +93,12 @@ def elbo_grad(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0,
         from . import native as native_mod
     keys = native_mod.THETA_KEYS
     rank = sg.rank if sg is not None else 0
+    if sg is not None and sg.world > 1 and X_local.is_cuda and hasattr(native_mod, "elbo_grad_dev"):
+        dev = native_mod.elbo_grad_dev(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0,
+                                       logdetV=logdetV, kl_weight=1.0 if rank == 0 else 0.0)
+        v = sg.reduce_result_(dev)
+        return {"loglik": v[0], "KL": v[1], "grad": dict(zip(keys, v[2:8])), "flags": int(v[8] > 0),
+                "any_flag": v[8] > 0, "p": int(v[9])}
     out = native_mod.elbo_grad(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0, logdetV=logdetV,
                                kl_weight=1.0 if rank == 0 else 0.0)
     vec = [out["loglik"]] + [out["grad"][k] for k in keys] + [float(out["flags"] != 0)]

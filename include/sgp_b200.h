@@ -191,6 +191,28 @@ SGP_API int sgp_elbo_grad(sgp_handle* h, const double* X, long ldx, const double
                   double lambda0, const double* logdetV_host, double* lam_m, double* lam_var, double* f,
                   double* out_host, void* stream);
 
+/* Same evaluation, ASYNCHRONOUS: the 16 result doubles are written to `out_dev` (device memory) and the call returns
+ * once everything is enqueued on `stream`, without a host synchronisation.  For callers that post-process the result
+ * on the device in stream order: an image-sharded evaluation all-reduces out_dev[0..8] across the GPUs and reads it back
+ * once (the one exchange step per evaluation).                                                 */
+SGP_API int sgp_elbo_grad_dev(sgp_handle* h, const double* X, long ldx, const double* r, long N, const double* xtilde,
+                              long ldu, int m, int n_px, const double* theta, const double* B, long ldb, int q,
+                              const double* m_b, const double* V_b, long ldv, double logA, double lambda0,
+                              const double* logdetV_host, double* lam_m, double* lam_var, double* f, double* out_dev,
+                              void* stream);
+/* Population fit (BASELINE.json configs[3]; the reference fits one cell per varGP call, utils.py:1568 / `cellid`
+ * utils.py:1636-1643): `ncells` independent cells that share the stimuli X (N x n_px^2, device) and the inducing images
+ * xtilde.  Cell c has its own theta (theta + 6c), spike counts r[c] (N), basis B[c] (m x q[c], ld ldb[c]), variational
+ * state m_b[c] / V_b[c] (ld ldv[c]), link parameters logA[c] / lambda0[c] and optionally logdetV[c] (nullable array).
+ * r, B, m_b, V_b are HOST arrays of DEVICE pointers.  One pass of the fused closure per cell, back to back on `stream`
+ * with no host synchronisation in between; every cell runs on the same resident images and the same int8 slices of
+ * them (cells whose receptive-field mask crops the grid get C = 0 outside it).  out_host: ncells x 16 doubles, the
+ * layout of sgp_elbo_grad.  No collective: cells are independent (last row).                   */
+SGP_API int sgp_elbo_grad_cells(sgp_handle* h, const double* X, long ldx, long N, const double* xtilde, long ldu, int m,
+                                int n_px, int ncells, const double* const* r, const double* theta,
+                                const double* const* B, const long* ldb, const int* q, const double* const* m_b,
+                                const double* const* V_b, const long* ldv, const double* logA, const double* lambda0,
+                                const double* logdetV, double* out_host, void* stream);
 /* Same evaluation with X / r in HOST memory (pinned or pageable): the images are streamed to the device slab by
  * slab on a copy stream that overlaps the compute stream.  Used for the end-to-end measurement.                  */
 SGP_API int sgp_elbo_grad_host(sgp_handle* h, const double* X_host, long ldx, const double* r_host, long N,

@@ -1,0 +1,95 @@
+"""GPU: population fit (BASELINE configs[3]) -- sgp_elbo_grad_cells evaluates several independent cells that share the
+stimuli in one call, all on the same resident images / int8 slices; it must give what per-cell calls of the fused
+closure give (which tests/test_gpu_closure.py / test_gpu_bigsize.py pin to the reference)."""
+import numpy as np
+import pytest
+import torch
+
+from gaussian_processes_b200 import synth
+from helpers import record
+
+pytestmark = pytest.mark.gpu
+D = torch.device("cuda:0")
+
+
+def make_cells(N, n, m, ncells, base_theta, eps, seed=4000):
+    """`ncells` cells on shared images: own receptive-field centre (eps[c]), own spikes, own subspace / variational state."""
+    from gaussian_processes_b200 import native
+    prob = synth.make_problem(N, n, m, cfg=40, theta=base_theta)
+    X, xt = prob.X.to(D), prob.xtilde.to(D)
+    g = torch.Generator().manual_seed(seed)
+    cells = []
+    for c in range(ncells):
+        th = dict(base_theta)
+        th["eps_0x"], th["eps_0y"] = eps[c]
+        Cm, mask = native.localker(th, n, D)
+        um = xt[:, mask].contiguous()
+        Kt = native.acosker(th["sigma_0"], um, um, Cm, True)
+        ev, evec = torch.linalg.eigh(Kt, UPLO="L")
+        keep = ev > max(float(ev.max()) * 1e-4, 1e-4)
+        B = evec[:, keep].contiguous()
+        m_b, V_b = synth.make_variational_state(torch.diag(ev[keep]).cpu(), 40 + c)
+        r = torch.poisson(torch.full((N,), 0.6 + 0.2 * c, dtype=torch.float64), generator=g)
+        # evaluate away from the theta the subspace was built at (frozen B)
+        th_eval = dict(th)
+        th_eval["-log2rho2"] += 0.02 * (c + 1)
+        cells.append(dict(theta=th_eval, B=B, m_b=m_b.to(D), V_b=V_b.to(D), r=r.to(D), logA=np.log(0.05) + 0.01 * c,
+                          lambda0=-0.5 - 0.05 * c, p=int(native.mask_host(th_eval, n).sum())))
+    return prob, X, xt, cells
+
+
+@pytest.mark.parametrize("cfg", [dict(N=2000, n=20, m=100, i8=8, slab=512), dict(N=8192, n=40, m=200, i8=-1, slab=4096),
+                                 dict(N=1500, n=20, m=64, i8=0, slab=0)])
+def test_cells_equal_single_cell_calls(cfg):
+    from gaussian_processes_b200 import native
+    # a narrower RF than THETA_DENSE so that off-centre cells crop the grid (p < P) while the central one keeps it
+    base = dict(synth.THETA_DENSE)
+    base["-2log2beta"] = 1.9
+    eps = [(0.0, 0.0), (0.45, -0.4), (-0.5, 0.5), (0.2, 0.3)]
+    prob, X, xt, cells = make_cells(cfg["N"], cfg["n"], cfg["m"], 4, base, eps)
+    P = cfg["n"] ** 2
+    assert any(c["p"] < P for c in cells) and len({c["p"] for c in cells}) > 1, [c["p"] for c in cells]
+    native.set_option(0, "i8_slices", cfg["i8"])
+    native.set_option(0, "path", 2)
+    native.set_slab_rows(0, cfg["slab"])
+    try:
+        native.invalidate_cache(0)
+        singles = [native.elbo_grad(X, c["r"], xt, cfg["n"], c["theta"], c["B"], c["m_b"], c["V_b"], c["logA"],
+                                    c["lambda0"]) for c in cells]
+        native.invalidate_cache(0)
+        native.launch_count(0, reset=True)
+        batch = native.elbo_grad_cells(X, [c["r"] for c in cells], xt, cfg["n"], [c["theta"] for c in cells],
+                                       [c["B"] for c in cells], [c["m_b"] for c in cells], [c["V_b"] for c in cells],
+                                       [c["logA"] for c in cells], [c["lambda0"] for c in cells])
+        again = native.elbo_grad_cells(X, [c["r"] for c in cells], xt, cfg["n"], [c["theta"] for c in cells],
+                                       [c["B"] for c in cells], [c["m_b"] for c in cells], [c["V_b"] for c in cells],
+                                       [c["logA"] for c in cells], [c["lambda0"] for c in cells])
+    finally:
+        native.set_option(0, "i8_slices", -1)
+        native.set_option(0, "path", 0)
+        native.set_slab_rows(0, 0)
+        native.invalidate_cache(0)
+    worst_ll = worst_g = 0.0
+    for c, s, b, a in zip(cells, singles, batch, again):
+        assert b["flags"] == 0 and s["flags"] == 0
+        assert b["p"] == c["p"] == s["p"]
+        assert b["loglik"] == a["loglik"] and b["grad"] == a["grad"]        # back-to-back cells are deterministic
+        worst_ll = max(worst_ll, abs(b["loglik"] - s["loglik"]) / abs(s["loglik"]))
+        assert abs(b["KL"] - s["KL"]) <= 1e-12 * abs(s["KL"])
+        gmax = max(abs(v) for v in s["grad"].values())
+        worst_g = max(worst_g, max(abs(b["grad"][k] - s["grad"][k]) for k in s["grad"]) / gmax)
+    record(f"cells_vs_single/n{cfg['n']}_i8_{cfg['i8']}", loglik=worst_ll, grad=worst_g)
+    assert worst_ll <= 1e-12 and worst_g <= 1e-12     # measured: 6e-16 / 7e-13 (different zero padding of the support)
+
+
+def test_cells_argument_checks():
+    from gaussian_processes_b200 import native
+    base = dict(synth.THETA_DENSE)
+    prob, X, xt, cells = make_cells(600, 12, 32, 2, base, [(0.0, 0.0), (0.1, 0.1)])
+    with pytest.raises(ValueError):
+        native.elbo_grad_cells(X, [cells[0]["r"]], xt, 12, [c["theta"] for c in cells], [c["B"] for c in cells],
+                               [c["m_b"] for c in cells], [c["V_b"] for c in cells], [0.0, 0.0], [0.0, 0.0])
+    with pytest.raises(RuntimeError):
+        native.elbo_grad_cells(X.cpu(), [c["r"] for c in cells], xt, 12, [c["theta"] for c in cells],
+                               [c["B"] for c in cells], [c["m_b"] for c in cells], [c["V_b"] for c in cells],
+                               [0.0, 0.0], [0.0, 0.0])
