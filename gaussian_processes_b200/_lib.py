@@ -62,6 +62,8 @@ SIGNATURES = {
                                _p]),
     "sgp_elbo_grad_cells": (_i, [_p, _p, _l, _l, _p, _l, _i, _i, _i, _p, _dp, _p, C.POINTER(_l), _ip, _p, _p,
                                  C.POINTER(_l), _dp, _dp, _dp, _dp, _p]),
+    "sgp_upload_images": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i]),
+    "sgp_elbo_grad_resident": (_i, [_p, _dp, _dp, _dp, _p, _l, _i, _p, _p, _l, _d, _d, _dp]),
     "sgp_elbo_grad_host": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i, _dp, _p, _l, _i, _p, _p, _l, _d, _d, _dp]),
     "sgp_debug_get": (_i, [_p, C.c_char_p, _p, _l, C.POINTER(_l), C.POINTER(_l), C.POINTER(_l)]),
 }

@@ -73,6 +73,8 @@ struct sgp_handle {
   char* pin_base = nullptr; size_t pin_slot_bytes = 0; int pin_next = 0;
   cudaEvent_t pin_ev[kPinSlots] = {nullptr, nullptr, nullptr, nullptr}; bool pin_used[kPinSlots] = {false, false, false, false};
   DevBuf cells_out;
+  // resident-image protocol (sgp_upload_images / sgp_elbo_grad_resident): the fit's constant operands live here
+  DevBuf res_x, res_r, res_u; long res_N = 0, res_m = 0; int res_npx = 0;
   std::map<std::string, DebugEntry> dbg;
   // second stream + events for the host-streaming variant
   cudaStream_t copy_stream = nullptr, compute_stream = nullptr, side_stream = nullptr;
@@ -232,7 +234,7 @@ int sgp_destroy(sgp_handle* h) {
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->pin_base) cudaFreeHost(h->pin_base);
     for (int i = 0; i < sgp_handle::kPinSlots; ++i) if (h->pin_ev[i]) cudaEventDestroy(h->pin_ev[i]);
-    h->cells_out.release();
+    h->cells_out.release(); h->res_x.release(); h->res_r.release(); h->res_u.release();
     for (int i = 0; i < 2; ++i) {
       if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]);
       if (h->ev_used[i]) cudaEventDestroy(h->ev_used[i]);
@@ -1412,6 +1414,61 @@ int sgp_elbo_grad_host(sgp_handle* h, const double* X_host, long ldx, const doub
   in.theta = theta; in.B = dB; in.ldb = q; in.q = q; in.m_b = dm; in.V = dV; in.ldv = q;
   in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = nullptr;
   in.X_host = X_host; in.r_host = r_host;
+  return run_closure(h, in, out_host, st);
+}
+
+int sgp_upload_images(sgp_handle* h, const double* X_host, long ldx, const double* r_host, long N,
+                      const double* xtilde_host, long ldu, int m, int n_px) {
+  if (!h || !X_host || !r_host || !xtilde_host) return fail(h, SGP_E_ARG, "sgp_upload_images: null argument");
+  if (N <= 0 || m <= 0 || n_px <= 0) return fail(h, SGP_E_ARG, "sgp_upload_images: bad sizes");
+  int rc = ensure_ready(h); if (rc) return rc;
+  if (!h->compute_stream) CU(cudaStreamCreateWithFlags(&h->compute_stream, cudaStreamNonBlocking));
+  cudaStream_t st = h->compute_stream;
+  const long P = (long)n_px * n_px;
+  CU(h->res_x.reserve((size_t)N * P * sizeof(double)));
+  CU(h->res_r.reserve((size_t)N * sizeof(double)));
+  CU(h->res_u.reserve((size_t)m * P * sizeof(double)));
+  CU(cudaMemcpy2DAsync(h->res_x.p, P * sizeof(double), X_host, ldx * sizeof(double), P * sizeof(double), N,
+                       cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(h->res_r.p, r_host, (size_t)N * sizeof(double), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpy2DAsync(h->res_u.p, P * sizeof(double), xtilde_host, ldu * sizeof(double), P * sizeof(double), m,
+                       cudaMemcpyHostToDevice, st));
+  CU(cudaStreamSynchronize(st));
+  h->res_N = N; h->res_m = m; h->res_npx = n_px;
+  h->cache_valid = false; h->oz_valid = false;      // new content at (possibly) the same addresses
+  h->image_token = h->image_token * 2654435761ULL + 0x9e3779b97f4a7c15ULL;   // and a token nobody else has handed out
+  return SGP_OK;
+}
+
+int sgp_elbo_grad_resident(sgp_handle* h, const double* theta, const double* lo, const double* hi,
+                           const double* B_host, long ldb, int q, const double* m_b_host, const double* V_b_host,
+                           long ldv, double logA, double lambda0, double* out_host) {
+  if (!h || !theta || !B_host || !m_b_host || !V_b_host || !out_host)
+    return fail(h, SGP_E_ARG, "sgp_elbo_grad_resident: null argument");
+  if (h->res_N <= 0) return fail(h, SGP_E_ARG, "sgp_elbo_grad_resident: call sgp_upload_images first");
+  if (lo && hi)
+    for (int k = 0; k < 6; ++k)
+      if (!(lo[k] <= theta[k] && theta[k] <= hi[k]))
+        return fail(h, SGP_E_BOUNDS, "sgp_elbo_grad_resident: theta[" + std::to_string(k) + "] outside its limits");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = h->compute_stream;
+  const int m = (int)h->res_m;
+  const long P = (long)h->res_npx * h->res_npx;
+  if (q <= 0 || q > m) return fail(h, SGP_E_ARG, "sgp_elbo_grad_resident: bad q");
+  const size_t nB = (size_t)m * q, nV = (size_t)q * q;
+  CU(h->small.reserve((nB + nV + q + 64) * sizeof(double)));
+  double* dB = (double*)h->small.p; double* dV = dB + ((nB + 1) & ~size_t(1)); double* dm = dV + ((nV + 1) & ~size_t(1));
+  // the per-evaluation state: B (m x q), V_b (q x q), m_b (q) -- a few MB; the images stay where sgp_upload_images put them
+  CU(cudaMemcpy2DAsync(dB, q * sizeof(double), B_host, ldb * sizeof(double), q * sizeof(double), m,
+                       cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpy2DAsync(dV, q * sizeof(double), V_b_host, ldv * sizeof(double), q * sizeof(double), q,
+                       cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(dm, m_b_host, q * sizeof(double), cudaMemcpyHostToDevice, st));
+  ClosureIn in{};
+  in.X = (const double*)h->res_x.p; in.ldx = P; in.r = (const double*)h->res_r.p; in.N = h->res_N;
+  in.U = (const double*)h->res_u.p; in.ldu = P; in.m = m; in.n_px = h->res_npx;
+  in.theta = theta; in.B = dB; in.ldb = q; in.q = q; in.m_b = dm; in.V = dV; in.ldv = q;
+  in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = nullptr;
   return run_closure(h, in, out_host, st);
 }
 

@@ -409,6 +409,38 @@ def elbo_grad_host(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px:
     return res
 
 
+def upload_images(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, device: int = 0) -> None:
+    """Resident-image protocol, step 1 (once per fit): host images / spike counts / inducing images -> device buffers owned
+    by this thread's handle (sgp_upload_images)."""
+    for t in (X, r, xtilde):
+        if t.is_cuda or t.dtype != torch.float64:
+            raise TypeError("upload_images expects CPU fp64 tensors")
+    X, xtilde, r = _c(X), _c(xtilde), r.contiguous()
+    h = _lib.handle_for(device)
+    h.check(lib.sgp_upload_images(h.ptr, _ptr(X), _ld(X), _ptr(r), X.shape[0], _ptr(xtilde), _ld(xtilde),
+                                  int(xtilde.shape[0]), int(n_px)))
+    h._bound = None
+
+
+def elbo_grad_resident(theta, B: torch.Tensor, m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float,
+                       lims=None, device: int = 0) -> Dict:
+    """Resident-image protocol, step 2 (per closure evaluation): theta by value, B / m_b / V_b from HOST memory (pinned
+    preferred); the images uploaded by upload_images are reused (sgp_elbo_grad_resident)."""
+    for t in (B, m_b, V_b):
+        if t.is_cuda or t.dtype != torch.float64:
+            raise TypeError("elbo_grad_resident expects CPU fp64 tensors")
+    B, V_b, m_b = _c(B), _c(V_b), m_b.contiguous()
+    lo = hi = None
+    if lims is not None:
+        lo = (C.c_double * 6)(*[float(lims[0][k]) for k in THETA_KEYS])
+        hi = (C.c_double * 6)(*[float(lims[1][k]) for k in THETA_KEYS])
+    out = (C.c_double * 16)()
+    h = _lib.handle_for(device)
+    h.check(lib.sgp_elbo_grad_resident(h.ptr, theta_array(theta), lo, hi, _ptr(B), _ld(B), int(B.shape[1]), _ptr(m_b),
+                                       _ptr(V_b), _ld(V_b), float(logA), float(lambda0), out))
+    return result_dict(list(out))
+
+
 def debug_get(device, name: str) -> torch.Tensor:
     h = _lib.handle_for(device.index if isinstance(device, torch.device) else int(device))
     rows, cols, ld = C.c_long(0), C.c_long(0), C.c_long(0)

@@ -213,6 +213,17 @@ SGP_API int sgp_elbo_grad_cells(sgp_handle* h, const double* X, long ldx, long N
                                 const double* const* B, const long* ldb, const int* q, const double* const* m_b,
                                 const double* const* V_b, const long* ldv, const double* logA, const double* lambda0,
                                 const double* logdetV, double* out_host, void* stream);
+/* Resident-image protocol for HOST callers.  `x`, `r` and `xtilde` are constant during a fit (varGP never modifies
+ * them, utils.py:1568-2316), only theta and the projected variational state change between closure evaluations.
+ * sgp_upload_images copies the three to device buffers owned by the handle ONCE (the int8 slices of the images are
+ * made by the first evaluation and kept); sgp_elbo_grad_resident then sends theta (by value), B (m x q), m_b (q) and
+ * V_b (q x q) from host memory per evaluation -- a few MB instead of the N x n_px^2 images -- runs the fused closure
+ * and returns the 16 doubles of sgp_elbo_grad in out_host.  lo / hi: nullable theta limits (SGP_E_BOUNDS outside).   */
+SGP_API int sgp_upload_images(sgp_handle* h, const double* X_host, long ldx, const double* r_host, long N,
+                              const double* xtilde_host, long ldu, int m, int n_px);
+SGP_API int sgp_elbo_grad_resident(sgp_handle* h, const double* theta, const double* lo, const double* hi,
+                                   const double* B_host, long ldb, int q, const double* m_b_host,
+                                   const double* V_b_host, long ldv, double logA, double lambda0, double* out_host);
 /* Same evaluation with X / r in HOST memory (pinned or pageable): the images are streamed to the device slab by
  * slab on a copy stream that overlaps the compute stream.  Used for the end-to-end measurement.                  */
 SGP_API int sgp_elbo_grad_host(sgp_handle* h, const double* X_host, long ldx, const double* r_host, long N,

@@ -179,3 +179,25 @@ def test_mask_flips_reuse_the_cached_support():
                 assert abs(a["grad"][k] - b["grad"][k]) <= 1e-10 * gmax
     finally:
         native.invalidate_cache(0)
+
+
+@pytest.mark.parametrize("name", ["closure_c2_dense_n40", "closure_c2_local_n40"])
+def test_benchmark_size_resident_protocol(name):
+    """sgp_upload_images once + sgp_elbo_grad_resident per evaluation (theta, B, m_b, V_b from host memory): the e2e entry
+    points of bench.py.  Two thetas in a row on the same uploaded images; the second must not see anything stale."""
+    from gaussian_processes_b200 import native, synth
+    fx, prob, st, dv = inputs(name)
+    native.upload_images(prob.X.pin_memory(), prob.r, prob.xtilde, prob.n_px_side)
+    try:
+        th2 = dict(prob.theta)
+        th2["eps_0x"] += 0.05
+        other = native.elbo_grad_resident(th2, st["B"], st["m_b"], st["V_b"], st["logA"], st["lambda0"])
+        out = native.elbo_grad_resident(prob.theta, st["B"], st["m_b"], st["V_b"], st["logA"], st["lambda0"],
+                                        lims=(synth.THETA_LIMS_LO, synth.THETA_LIMS_HI))
+        assert other["loglik"] != out["loglik"]
+        check(fx, out, moments=False, tag=f"{name}/resident")
+        ref2 = native.elbo_grad(dv["X"], dv["r"], dv["xt"], prob.n_px_side, th2, dv["B"], dv["m_b"], dv["V_b"],
+                                st["logA"], st["lambda0"])
+        assert abs(other["loglik"] - ref2["loglik"]) <= 1e-12 * abs(ref2["loglik"])
+    finally:
+        native.release_cache(0)
