@@ -588,6 +588,17 @@ def run_ours(args):
     native.set_option(local, "i8_slices", args.i8_slices)
     native.set_option(local, "i8_slices_images", args.i8_slices_images)
     sg = sharded.ShardGroup(device=dev) if world > 1 else None
+    # exchange step of the image-sharded evaluation: fused into the result-assembly kernel over peer memory (default);
+    # SGP_BENCH_EXCHANGE=nccl keeps the device-side NCCL all-reduce of the 9 leading result doubles
+    exchange = "none"
+    if sg is not None:
+        exchange = "nccl_device"
+        if os.environ.get("SGP_BENCH_EXCHANGE", "peer") == "peer":
+            try:
+                if sg.enable_peer_exchange():
+                    exchange = "peer_memory (finalize_exchange_kernel: P2P stores + epoch flags over NVLink)"
+            except Exception as e:  # pragma: no cover
+                exchange = "nccl_device (peer exchange unavailable: %r)" % (e,)
 
     def step():
         # fused closure on the local block of images + (N > 1) the one exchange step: all-reduce of 8 doubles
@@ -823,6 +834,7 @@ def run_ours(args):
                                                           "the masked gather" % (S_img, S)) if i8 else "fp64 DMMA",
                                              "images_per_sec": sharded_evals_per_sec * N * world,
                                              "sharded_problem_evals_per_sec": sharded_evals_per_sec,
+                                             "exchange": exchange,
                                              "unit_of_work": "one ELBO+grad evaluation over N images x m inducing "
                                                              "(the config-2 problem); an image-sharded evaluation "
                                                              "over gpus x N images counts as `gpus` units"}),

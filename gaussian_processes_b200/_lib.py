@@ -20,7 +20,7 @@ if not os.path.exists(LIB_PATH):
 lib = C.CDLL(LIB_PATH)
 
 SGP_OK, SGP_E_CUDA, SGP_E_ARG, SGP_E_BOUNDS, SGP_E_UNSUPPORTED, SGP_E_NOMEM = range(6)
-FLAG_KT_NOT_PD, FLAG_KT_SMALL_PIVOT, FLAG_V_NOT_PD, FLAG_V_SMALL_PIVOT, FLAG_NAN = 1, 2, 4, 8, 16
+FLAG_KT_NOT_PD, FLAG_KT_SMALL_PIVOT, FLAG_V_NOT_PD, FLAG_V_SMALL_PIVOT, FLAG_NAN, FLAG_COMM_TIMEOUT = 1, 2, 4, 8, 16, 32
 
 _p = C.c_void_p
 _d = C.c_double
@@ -62,6 +62,9 @@ SIGNATURES = {
                                _p]),
     "sgp_elbo_grad_cells": (_i, [_p, _p, _l, _l, _p, _l, _i, _i, _i, _p, _dp, _p, C.POINTER(_l), _ip, _p, _p,
                                  C.POINTER(_l), _dp, _dp, _dp, _dp, _p]),
+    "sgp_comm_export": (_i, [_p, _i, _p]),
+    "sgp_comm_import": (_i, [_p, _i, _i, _p]),
+    "sgp_comm_close": (_i, [_p]),
     "sgp_upload_images": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i]),
     "sgp_elbo_grad_resident": (_i, [_p, _dp, _dp, _dp, _p, _l, _i, _p, _p, _l, _d, _d, _dp]),
     "sgp_elbo_grad_host": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i, _dp, _p, _l, _i, _p, _p, _l, _d, _d, _dp]),

@@ -73,6 +73,8 @@ struct sgp_handle {
   char* pin_base = nullptr; size_t pin_slot_bytes = 0; int pin_next = 0;
   cudaEvent_t pin_ev[kPinSlots] = {nullptr, nullptr, nullptr, nullptr}; bool pin_used[kPinSlots] = {false, false, false, false};
   DevBuf cells_out;
+  // image-sharded exchange over peer memory (sgp_comm_*): my buffer, the peers' mappings, the lock-step epoch
+  DevBuf comm_buf; CommDev comm; bool comm_on = false; void* comm_peer[kCommMaxRanks] = {nullptr};
   // resident-image protocol (sgp_upload_images / sgp_elbo_grad_resident): the fit's constant operands live here
   DevBuf res_x, res_r, res_u; long res_N = 0, res_m = 0; int res_npx = 0;
   std::map<std::string, DebugEntry> dbg;
@@ -234,6 +236,8 @@ int sgp_destroy(sgp_handle* h) {
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->pin_base) cudaFreeHost(h->pin_base);
     for (int i = 0; i < sgp_handle::kPinSlots; ++i) if (h->pin_ev[i]) cudaEventDestroy(h->pin_ev[i]);
+    for (int i = 0; i < kCommMaxRanks; ++i) if (h->comm_peer[i]) cudaIpcCloseMemHandle(h->comm_peer[i]);
+    h->comm_buf.release();
     h->cells_out.release(); h->res_x.release(); h->res_r.release(); h->res_u.release();
     for (int i = 0; i < 2; ++i) {
       if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]);
@@ -533,6 +537,7 @@ struct ClosureIn {
   // stream -- the caller reads / reduces them in stream order (cells loop, device-side all-reduce of the image shards)
   double* out_dev = nullptr;
   int force_support = -2;           // -2: the handle's option; otherwise overrides it for this call
+  bool exchange = false;            // image shard of a larger evaluation: reduce the result with the peers (sgp_comm_*)
 };
 
 // one slot of the pinned upload ring, at least `bytes` large; waits until the copies last issued from it are done
@@ -1272,8 +1277,14 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   if (use_sep) sum_to_slots(h->d_scal + kSlotGW, 1, 5, 5, h->d_scal, kSlotG, 1, st);
   if (side_pending) CU(cudaStreamWaitEvent(st, h->ev_join, 0));
   const bool async_out = in.out_dev != nullptr;
-  finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p_true, in.logdetV_host ? *in.logdetV_host : 0.0,
-           in.logdetV_host ? 1 : 0, async_out ? in.out_dev : h->d_out, proj ? 1.0 : 0.0, st);
+  if (h->comm_on && in.exchange) {
+    h->comm.epoch += 1;           // every rank issues its evaluations in the same order: the epochs agree
+    finalize_exchange(h->d_scal, h->d_flags, A, in.lambda0, th, p_true, in.logdetV_host ? *in.logdetV_host : 0.0,
+                      in.logdetV_host ? 1 : 0, async_out ? in.out_dev : h->d_out, proj ? 1.0 : 0.0, h->comm, st);
+  } else {
+    finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p_true, in.logdetV_host ? *in.logdetV_host : 0.0,
+             in.logdetV_host ? 1 : 0, async_out ? in.out_dev : h->d_out, proj ? 1.0 : 0.0, st);
+  }
   CU(cudaGetLastError());
   if (!async_out) CU(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(double) * 16, cudaMemcpyDeviceToHost, st));
   mark(-1);
@@ -1330,6 +1341,7 @@ int sgp_elbo_grad(sgp_handle* h, const double* X, long ldx, const double* r, lon
   in.theta = theta; in.B = B; in.ldb = ldb; in.q = q; in.m_b = m_b; in.V = V_b; in.ldv = ldv;
   in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = logdetV_host;
   in.lam_m = lam_m; in.lam_var = lam_var; in.f = f;
+  in.exchange = true;       // no-op unless sgp_comm_import made this handle one shard of an image-sharded evaluation
   return run_closure(h, in, out_host, (cudaStream_t)stream);
 }
 
@@ -1344,6 +1356,7 @@ int sgp_elbo_grad_dev(sgp_handle* h, const double* X, long ldx, const double* r,
   in.theta = theta; in.B = B; in.ldb = ldb; in.q = q; in.m_b = m_b; in.V = V_b; in.ldv = ldv;
   in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = logdetV_host;
   in.lam_m = lam_m; in.lam_var = lam_var; in.f = f; in.out_dev = out_dev;
+  in.exchange = true;
   return run_closure(h, in, nullptr, (cudaStream_t)stream);
 }
 
@@ -1415,6 +1428,55 @@ int sgp_elbo_grad_host(sgp_handle* h, const double* X_host, long ldx, const doub
   in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = nullptr;
   in.X_host = X_host; in.r_host = r_host;
   return run_closure(h, in, out_host, st);
+}
+
+int sgp_comm_export(sgp_handle* h, int world, unsigned char* handle_out) {
+  if (!h || !handle_out) return fail(h, SGP_E_ARG, "sgp_comm_export: null argument");
+  if (world < 2 || world > kCommMaxRanks) return fail(h, SGP_E_ARG, "sgp_comm_export: world must be 2..16");
+  int rc = ensure_ready(h); if (rc) return rc;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  h->comm_on = false;
+  CU(h->comm_buf.reserve(comm_buffer_bytes(world)));
+  CU(cudaMemset(h->comm_buf.p, 0, comm_buffer_bytes(world)));
+  cudaIpcMemHandle_t ih;
+  CU(cudaIpcGetMemHandle(&ih, h->comm_buf.p));
+  std::memcpy(handle_out, &ih, 64);
+  return SGP_OK;
+}
+
+int sgp_comm_import(sgp_handle* h, int rank, int world, const unsigned char* handles) {
+  if (!h || !handles) return fail(h, SGP_E_ARG, "sgp_comm_import: null argument");
+  if (world < 2 || world > kCommMaxRanks || rank < 0 || rank >= world) return fail(h, SGP_E_ARG, "sgp_comm_import: bad rank / world");
+  if (!h->comm_buf.p) return fail(h, SGP_E_ARG, "sgp_comm_import: call sgp_comm_export first");
+  CU(cudaSetDevice(h->device));
+  CommDev c;
+  c.rank = rank; c.world = world; c.epoch = 0;
+  for (int i = 0; i < world; ++i) {
+    void* base = h->comm_buf.p;
+    if (i != rank) {
+      cudaIpcMemHandle_t ih;
+      std::memcpy(&ih, handles + 64 * i, 64);
+      if (h->comm_peer[i]) { cudaIpcCloseMemHandle(h->comm_peer[i]); h->comm_peer[i] = nullptr; }
+      CU(cudaIpcOpenMemHandle(&base, ih, cudaIpcMemLazyEnablePeerAccess));
+      h->comm_peer[i] = base;
+    }
+    c.slots[i] = (double*)base;
+    c.flags[i] = (unsigned long long*)((char*)base + (size_t)2 * world * 16 * sizeof(double));
+  }
+  h->comm = c;
+  h->comm_on = true;
+  return SGP_OK;
+}
+
+int sgp_comm_close(sgp_handle* h) {
+  if (!h) return SGP_E_ARG;
+  h->comm_on = false;
+  if (h->gemm_ready) {
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    for (int i = 0; i < kCommMaxRanks; ++i) if (h->comm_peer[i]) { cudaIpcCloseMemHandle(h->comm_peer[i]); h->comm_peer[i] = nullptr; }
+  }
+  return SGP_OK;
 }
 
 int sgp_upload_images(sgp_handle* h, const double* X_host, long ldx, const double* r_host, long N,

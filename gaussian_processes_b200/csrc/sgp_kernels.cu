@@ -803,37 +803,118 @@ void contract_dC(const double* GCpart, int nz, long zstride, const double* GCext
   note_launch(); contract_dC_kernel<<<p, 256, 0, st>>>(GCpart, nz, zstride, GCextra, C, ld, p, gx, gy, th, gpart);
 }
 
-__global__ void finalize_kernel(const double* __restrict__ scal, const int* __restrict__ flags, double A,
-                                double lambda0, ThetaDev th, int p, double logdetV_override, int use_override,
-                                double* __restrict__ out, double out15) {
+__device__ __forceinline__ void assemble_result(const double* __restrict__ scal, const int* __restrict__ flags, double A,
+                                                double lambda0, const ThetaDev& th, int p, double logdetV_override,
+                                                int use_override, double out15, double* v) {
   const double s0 = th.s0, amp = th.amp, eb = th.eb;
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
   const double logdetV = use_override ? logdetV_override : scal[kSlotLogdetV];
   const double loglik = A * scal[kSlotRLam] + lambda0 * scal[kSlotSumR] - scal[kSlotSumF];      // U:1243
   const double KL = -0.5 * logdetV + 0.5 * scal[kSlotLogdetK] + 0.5 * scal[kSlotMb] + 0.5 * scal[kSlotTrVK];  // U:1326
   int fl = flags[0];
   if (scal[kSlotNaN] > 0.0) fl |= kFlagNaN;
-  out[0] = loglik;
-  out[1] = KL;
-  out[2] = 2.0 * s0 * scal[kSlotSig];          // sigma_0
-  out[3] = 2.0 * eb * scal[kSlotG + 3];        // eps_0x
-  out[4] = 2.0 * eb * scal[kSlotG + 4];        // eps_0y
-  out[5] = scal[kSlotG + 1];                   // -2log2beta
-  out[6] = scal[kSlotG + 2];                   // -log2rho2
-  out[7] = scal[kSlotG + 0] / amp;             // Amp
-  out[8] = (double)fl;
-  out[9] = (double)p;
-  out[10] = scal[kSlotSumR];
-  out[11] = scal[kSlotSumF];
-  out[12] = scal[kSlotRLam];
-  out[13] = scal[kSlotLogdetK];
-  out[14] = logdetV;
-  out[15] = out15;
+  v[0] = loglik;
+  v[1] = KL;
+  v[2] = 2.0 * s0 * scal[kSlotSig];          // sigma_0
+  v[3] = 2.0 * eb * scal[kSlotG + 3];        // eps_0x
+  v[4] = 2.0 * eb * scal[kSlotG + 4];        // eps_0y
+  v[5] = scal[kSlotG + 1];                   // -2log2beta
+  v[6] = scal[kSlotG + 2];                   // -log2rho2
+  v[7] = scal[kSlotG + 0] / amp;             // Amp
+  v[8] = (double)fl;
+  v[9] = (double)p;
+  v[10] = scal[kSlotSumR];
+  v[11] = scal[kSlotSumF];
+  v[12] = scal[kSlotRLam];
+  v[13] = scal[kSlotLogdetK];
+  v[14] = logdetV;
+  v[15] = out15;
+}
+
+__global__ void finalize_kernel(const double* __restrict__ scal, const int* __restrict__ flags, double A,
+                                double lambda0, ThetaDev th, int p, double logdetV_override, int use_override,
+                                double* __restrict__ out, double out15) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double v[16];
+  assemble_result(scal, flags, A, lambda0, th, p, logdetV_override, use_override, out15, v);
+#pragma unroll
+  for (int k = 0; k < 16; ++k) out[k] = v[k];
 }
 
 void finalize(const double* scal, const int* flags, double A, double lambda0, const ThetaDev& th, int p,
               double logdetV_override, int use_override, double* out, double out15, cudaStream_t st) {
   note_launch(); finalize_kernel<<<1, 32, 0, st>>>(scal, flags, A, lambda0, th, p, logdetV_override, use_override, out, out15);
+}
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// One warp.  Lane k < 16 owns result element k; lane i < world polls rank i's flag.
+__global__ void finalize_exchange_kernel(const double* __restrict__ scal, const int* __restrict__ flags, double A,
+                                         double lambda0, ThetaDev th, int p, double logdetV_override, int use_override,
+                                         double* __restrict__ out, double out15, CommDev comm) {
+  __shared__ double v[16];
+  __shared__ int timed_out;
+  const int lane = threadIdx.x;
+  if (lane == 0) {
+    double t[16];
+    assemble_result(scal, flags, A, lambda0, th, p, logdetV_override, use_override, out15, t);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = t[k];
+    timed_out = 0;
+  }
+  __syncwarp();
+  const int par = (int)(comm.epoch & 1ULL), W = comm.world;
+  // 1. my 16 doubles into slot [par][my rank] of every rank's buffer (my own included)
+  if (lane < 16)
+    for (int j = 0; j < W; ++j) comm.slots[j][((size_t)par * W + comm.rank) * 16 + lane] = v[lane];
+  __threadfence_system();
+  __syncwarp();
+  // 2. publish: flag [par][my rank] of every rank = epoch (release: the slot stores above are visible before it)
+  if (lane < W) st_release_sys(comm.flags[lane] + (size_t)par * W + comm.rank, comm.epoch);
+  // 3. wait for every rank's flag in MY buffer
+  if (lane < W) {
+    const unsigned long long* f = comm.flags[comm.rank] + (size_t)par * W + lane;
+    const unsigned long long t0 = global_ns();
+    while (ld_acquire_sys(f) != comm.epoch) {
+      if (global_ns() - t0 > 3000000000ULL) { atomicExch(&timed_out, 1); break; }   // 3 s: a peer never arrived
+      __nanosleep(200);
+    }
+  }
+  __threadfence_system();
+  __syncwarp();
+  // 4. reduce in rank order (identical bits on every rank): sums for loglik / gradients / the image sums, OR for flags
+  if (lane < 16) {
+    const volatile double* mine = comm.slots[comm.rank] + (size_t)par * W * 16;   // written by the peers: no cached copy
+    double r = v[lane];
+    if (lane == 0 || (lane >= 2 && lane <= 7) || (lane >= 10 && lane <= 12)) {
+      r = 0.0;
+      for (int i = 0; i < W; ++i) r += mine[i * 16 + lane];
+    } else if (lane == 8) {
+      int fl = timed_out ? kFlagCommTimeout : 0;
+      for (int i = 0; i < W; ++i) fl |= (int)mine[i * 16 + 8];
+      r = (double)fl;
+    }
+    out[lane] = r;
+  }
+}
+
+void finalize_exchange(const double* scal, const int* flags, double A, double lambda0, const ThetaDev& th, int p,
+                       double logdetV_override, int use_override, double* out, double out15, const CommDev& comm,
+                       cudaStream_t st) {
+  note_launch();
+  finalize_exchange_kernel<<<1, 32, 0, st>>>(scal, flags, A, lambda0, th, p, logdetV_override, use_override, out, out15,
+                                             comm);
 }
 
 

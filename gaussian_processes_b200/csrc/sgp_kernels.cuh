@@ -13,6 +13,7 @@ enum StatusBits : int {
   kFlagVNotPD = 4,         // same for V_b
   kFlagVSmallPivot = 8,
   kFlagNaN = 16,           // NaN in f (reference raises in the f-param closure, U:1923)
+  kFlagCommTimeout = 32,   // image-sharded exchange: a peer's partial result did not arrive within the time limit
 };
 
 // slots of the small device scalar buffer the closure accumulates into
@@ -131,6 +132,24 @@ void contract_dC(const double* GCpart, int nz, long zstride, const double* GCext
 // [8] flags, [9] p, [10] sum r, [11] sum f, [12] sum r*lam_m, [13] logdet K_tilde_b, [14] logdet V_b, [15] out15 (1 = moments in the projected basis)
 void finalize(const double* scal, const int* flags, double A, double lambda0, const ThetaDev& th, int p,
               double logdetV_override, int use_override, double* out, double out15, cudaStream_t st);
+
+// ---- image-sharded evaluation: the exchange step fused into the result assembly ----------------------------------
+// Every rank's finalize kernel writes its 16 result doubles straight into a slot of EVERY peer's exchange buffer
+// (peer-to-peer stores over NVLink / NVSwitch; the buffers are cudaMalloc'ed and opened through CUDA IPC), publishes a
+// per-rank epoch flag with release semantics, waits for the flags of all ranks (acquire loads, bounded by a time limit),
+// and sums the slots in rank order -- so every rank ends with bit-identical reduced numbers, without a collective
+// launch, a second kernel or a host round trip.  Slots / flags are double-buffered by epoch parity.
+constexpr int kCommMaxRanks = 16;
+struct CommDev {
+  int rank = 0, world = 1;
+  unsigned long long epoch = 0;                       // same on every rank: evaluations are issued in lock step
+  double* slots[kCommMaxRanks] = {nullptr};           // base of rank i's buffer: [2][world][16] doubles
+  unsigned long long* flags[kCommMaxRanks] = {nullptr};   // rank i's flags: [2][world]
+};
+inline size_t comm_buffer_bytes(int world) { return (size_t)2 * world * 16 * sizeof(double) + (size_t)2 * world * 8 + 256; }
+void finalize_exchange(const double* scal, const int* flags, double A, double lambda0, const ThetaDev& th, int p,
+                       double logdetV_override, int use_override, double* out, double out15, const CommDev& comm,
+                       cudaStream_t st);
 
 
 // ---- E-step / f-param helpers -------------------------------------------------------------------

@@ -409,6 +409,29 @@ def elbo_grad_host(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px:
     return res
 
 
+def comm_export(device: int, world: int) -> bytes:
+    """Allocate this rank's exchange buffer and return its 64-byte CUDA IPC handle (sgp_comm_export)."""
+    h = _lib.handle_for(device)
+    buf = (C.c_ubyte * 64)()
+    h.check(lib.sgp_comm_export(h.ptr, int(world), buf))
+    return bytes(buf)
+
+
+def comm_import(device: int, rank: int, world: int, handles: bytes) -> None:
+    """Map every peer's exchange buffer (handles: world x 64 bytes, in rank order); from now on sgp_elbo_grad /
+    sgp_elbo_grad_dev on this thread's handle return results already reduced over the image shards."""
+    if len(handles) != 64 * world:
+        raise ValueError("comm_import: need world x 64 bytes of IPC handles")
+    h = _lib.handle_for(device)
+    buf = (C.c_ubyte * len(handles)).from_buffer_copy(handles)
+    h.check(lib.sgp_comm_import(h.ptr, int(rank), int(world), buf))
+
+
+def comm_close(device: int) -> None:
+    h = _lib.handle_for(device)
+    h.check(lib.sgp_comm_close(h.ptr))
+
+
 def upload_images(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, device: int = 0) -> None:
     """Resident-image protocol, step 1 (once per fit): host images / spike counts / inducing images -> device buffers owned
     by this thread's handle (sgp_upload_images)."""

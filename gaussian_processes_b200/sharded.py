@@ -36,6 +36,34 @@ class ShardGroup:
             device = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
         self.device = torch.device(device)
         self.calls = 0
+        self.peer_exchange = False
+
+    def enable_peer_exchange(self, native_mod=None) -> bool:
+        """Fuse the exchange step of the M-step closure into its result-assembly kernel: every rank's exchange buffer is
+        mapped into every other rank (CUDA IPC over NVLink / NVSwitch peer access; the 64-byte handles travel through
+        this process group once), after which `native.elbo_grad` returns numbers already summed over the image shards --
+        no NCCL launch and a single host read-back per evaluation.  NCCL stays for the E-step's q x q all-reduce."""
+        if self.world == 1 or self.device.type != "cuda":
+            return False
+        if native_mod is None:
+            from . import native as native_mod
+        dev = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        mine = native_mod.comm_export(dev, self.world)
+        allh = [None] * self.world
+        dist.all_gather_object(allh, mine, group=self.group)
+        native_mod.comm_import(dev, self.rank, self.world, b"".join(allh))
+        dist.barrier(group=self.group)
+        self.peer_exchange = True
+        return True
+
+    def disable_peer_exchange(self, native_mod=None) -> None:
+        if not self.peer_exchange:
+            return
+        if native_mod is None:
+            from . import native as native_mod
+        dist.barrier(group=self.group)
+        native_mod.comm_close(self.device.index if self.device.index is not None else torch.cuda.current_device())
+        self.peer_exchange = False
 
     def sum_floats(self, vals: Sequence[float]):
         t = torch.tensor([float(v) for v in vals], dtype=torch.float64, device=self.device)
@@ -93,6 +121,12 @@ def elbo_grad(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0,
         from . import native as native_mod
     keys = native_mod.THETA_KEYS
     rank = sg.rank if sg is not None else 0
+    if sg is not None and sg.world > 1 and getattr(sg, "peer_exchange", False):
+        # the exchange happened inside the evaluation's last kernel: the 16 doubles read back are already reduced
+        out = native_mod.elbo_grad(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0, logdetV=logdetV,
+                                   kl_weight=1.0 if rank == 0 else 0.0)
+        return {"loglik": out["loglik"], "KL": out["KL"], "grad": out["grad"], "flags": out["flags"],
+                "any_flag": out["flags"] != 0, "p": out["p"]}
     if sg is not None and sg.world > 1 and X_local.is_cuda and hasattr(native_mod, "elbo_grad_dev"):
         dev = native_mod.elbo_grad_dev(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0,
                                        logdetV=logdetV, kl_weight=1.0 if rank == 0 else 0.0)

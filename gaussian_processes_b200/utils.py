@@ -636,6 +636,15 @@ def elbo_and_grad(theta, lo, hi, n_px_side, x, xtilde, r, B, m_b, V_b, f_params,
     kernfun = kernfun or acosker
     if not same:
         logA, lambda0 = _link_params(f_params)
+        if _sharded() and getattr(_SHARD, "peer_exchange", False):
+            # image shards with the exchange fused into the evaluation's last kernel (peer memory): already reduced
+            out = native.elbo_grad(x, r, xtilde, int(n_px_side), _theta_floats(theta), B, m_b, V_b, logA, lambda0,
+                                   logdetV=logdetV, kl_weight=1.0 if _shard_rank() == 0 else 0.0)
+            if out["flags"] & 32:
+                raise RuntimeError("image-sharded evaluation: a peer's partial result did not arrive (exchange timeout)")
+            if not out["flags"] & (FLAG_KT_NOT_PD | FLAG_KT_SMALL_PIVOT):
+                return out["loglik"], out["KL"], out["grad"]
+            return _closure_forward_mode(theta, lo, hi, n_px_side, x, xtilde, r, kernfun, same, B, m_b, V_b, f_params)
         if _sharded() and x.is_cuda and hasattr(native, "elbo_grad_dev"):
             # image shards: asynchronous fused call, device-side all-reduce of the 9 leading result doubles, ONE read-back
             dev_out = native.elbo_grad_dev(x, r, xtilde, int(n_px_side), _theta_floats(theta), B, m_b, V_b, logA, lambda0,

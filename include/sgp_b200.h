@@ -213,6 +213,20 @@ SGP_API int sgp_elbo_grad_cells(sgp_handle* h, const double* X, long ldx, long N
                                 const double* const* B, const long* ldb, const int* q, const double* const* m_b,
                                 const double* const* V_b, const long* ldv, const double* logA, const double* lambda0,
                                 const double* logdetV, double* out_host, void* stream);
+/* ---- image-sharded evaluation: exchange over peer memory (north_star item 4) ---------------
+ * One process per GPU; rank k holds a block of the images and calls sgp_elbo_grad / sgp_elbo_grad_dev on it.  After
+ *   sgp_comm_export(h, world, handle64)            -- allocate this rank's exchange buffer, get its CUDA IPC handle
+ *   <all-gather the 64-byte handles over any host channel>
+ *   sgp_comm_import(h, rank, world, handles)       -- map every peer's buffer (NVLink / NVSwitch peer access)
+ * the result-assembly kernel of every evaluation ALSO does the exchange step: each rank stores its 16 doubles into a
+ * slot of every peer's buffer, publishes an epoch flag (release), waits for all ranks' flags (acquire, 3 s limit ->
+ * status bit 32), and sums loglik, the 6 gradients and the image sums in rank order.  Every rank returns identical,
+ * already reduced numbers from ONE kernel: no collective launch, no extra host round trip.  KL is replicated and
+ * returned once; the KL part of the gradient must be counted once (option "kl_weight" = 0 on ranks > 0).  All ranks must
+ * issue the same sequence of evaluations.  sgp_comm_close ends the mode.  Cells / host-streaming calls never exchange. */
+SGP_API int sgp_comm_export(sgp_handle* h, int world, unsigned char* handle_out /* 64 bytes */);
+SGP_API int sgp_comm_import(sgp_handle* h, int rank, int world, const unsigned char* handles /* world x 64 bytes */);
+SGP_API int sgp_comm_close(sgp_handle* h);
 /* Resident-image protocol for HOST callers.  `x`, `r` and `xtilde` are constant during a fit (varGP never modifies
  * them, utils.py:1568-2316), only theta and the projected variational state change between closure evaluations.
  * sgp_upload_images copies the three to device buffers owned by the handle ONCE (the int8 slices of the images are
