@@ -52,6 +52,7 @@ SIGNATURES = {
     "sgp_loglik_sums": (_i, [_p, _p, _p, _p, _p, _l, _d, _dp, _p]),
     "sgp_estep_terms": (_i, [_p, _p, _l, _p, _p, _l, _i, _d, _p, _p, _l, _p]),
     "sgp_cholesky": (_i, [_p, _p, _l, _i, _ip, _p]),
+    "sgp_cholesky_noalloc": (_i, [_p, _l, _i, _p, _p, C.c_char_p, _i]),
     "sgp_spd_inverse": (_i, [_p, _p, _l, _i, _p, _l, _dp, _ip, _p]),
     "sgp_gemm_f64": (_i, [_p, _i, _i, _p, _l, _p, _l, _p, _l, _i, _i, _i, _d, _i, _i, _p]),
     "sgp_nd_utility": (_i, [_p, _p, _p, _l, _p, _i, _p, _p, _p, _p, _p, _p]),

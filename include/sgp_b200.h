@@ -156,6 +156,20 @@ SGP_API int sgp_nd_utility(sgp_handle* h, const double* sigma2, const double* mu
 SGP_API int sgp_cholesky(sgp_handle* h, double* A, long ld, int n, int* flags_host, void* stream);
 SGP_API int sgp_spd_inverse(sgp_handle* h, const double* A, long lda, int n, double* Ainv, long ldi, double* logdet_host,
                     int* flags_host, void* stream);
+/* sgp_cholesky_noalloc -- NO counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The in-place lower Cholesky of sgp_cholesky (same kernels, same result) for n <= 1024, with its scratch (the inverses of
+ * the 64 x 64 diagonal blocks of L + one status word: 512.25 KiB) in a file-scope `static __device__` array that every
+ * GPU loading the library holds until the process exits.  Takes no handle; calls no cudaMalloc / cudaFree / allocating
+ * library routine; does not synchronise: all work is enqueued on `stream` of the CURRENT device.
+ *   A          device, n x n row-major, ld even and >= n, 16-byte aligned; lower triangle in, L out
+ *   flags_dev  device int, nullable: receives the status bits (1 = pivot <= 0, 2 = pivot < 1e-10) in stream order
+ *   errbuf     nullable host buffer (errbuf_len bytes) for the error message
+ * n > 1024 returns SGP_E_UNSUPPORTED with a message naming the limit.  Every call on a device shares the one array and it
+ * keeps the last call's contents (the status word is cleared at the start of each call): calls that OVERLAP on the GPU
+ * (two streams / two threads on one device) race -- serialise them.  The first call on a device does the one-time
+ * set-up (cudaGetSymbolAddress + kernel attributes): make it outside a graph capture.                              */
+SGP_API int sgp_cholesky_noalloc(double* A, long ld, int n, int* flags_dev, void* stream, char* errbuf, int errbuf_len);
 
 /* ---- generic fp64 tensor-core GEMM (exposed for tests and for the roofline measurement) -----------------------
  * C[M x N] = alpha * A * B^T-style contraction with selectable operand layouts:
