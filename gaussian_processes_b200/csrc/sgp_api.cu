@@ -84,6 +84,9 @@ struct sgp_handle {
   cudaStream_t chain_stream = nullptr; cudaEvent_t ev_chain_fork = nullptr, ev_chain_join = nullptr;
   int overlap = 1;          // 1 = run the q x q inducing-point chain next to the first slab's quadratic forms
   int support = -1;         // pixel set of the cached image copies: -1 = mask grown by 2 px, reused while the mask stays inside; 0 = the mask itself; 1 = whole grid
+  // N == m: 1 = the reference's ntilde == nt branch (K = K_tilde, a = B); 0 = treat it as any other N (an image SHARD
+  // that happens to hold m rows is not the active-learning configuration)
+  int square_is_same = 1;
   int projected = -1;       // moments in the projected basis (K_b = K B): -1 = when q is small enough to pay, 0 = never, 1 = always
   DevBuf hx[2], hr, small;
   cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr}, ev_small = nullptr;
@@ -268,6 +271,7 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
   else if (n == "overlap") h->overlap = value != 0.0;
   else if (n == "projected") h->projected = (int)value;
   else if (n == "support") h->support = (int)value;
+  else if (n == "square_is_same") h->square_is_same = value != 0.0;
   else if (n == "i8_slices") {
     if (value != -1 && value != 0 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices must be -1, 0 or 2..8");
     h->i8_slices = (int)value;
@@ -560,6 +564,8 @@ int pin_acquire(sgp_handle* h, size_t bytes, char** out, int* slot_out) {
   return SGP_OK;
 }
 
+int run_closure_same(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream_t st);
+
 int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream_t st) {
   const double t_entry = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
   int rc = ensure_ready(h); if (rc) return rc;
@@ -577,7 +583,12 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const long N = in.N; const int m = in.m, q = in.q, n = in.n_px; const long P = (long)n * n;
   if (N <= 0 || m <= 0 || q <= 0 || q > m) return fail(h, SGP_E_ARG, "sgp_elbo_grad: bad sizes");
   if (m > kBwdMaxCols) return fail(h, SGP_E_UNSUPPORTED, "sgp_elbo_grad: m > 2048 not supported");
-  if (N == m) return fail(h, SGP_E_UNSUPPORTED, "sgp_elbo_grad: ntilde == nt (a = B) path not implemented");
+  // ntilde == nt: the reference's a = B branch (U:2032, U:2068) -- the configuration its active-learning notebook
+  // always runs (m == N: every image in use is an inducing image).  Small problem, own routine.
+  if (N == m && h->square_is_same) {
+    if (streaming) return fail(h, SGP_E_UNSUPPORTED, "sgp_elbo_grad_host: ntilde == nt needs device-resident images");
+    return run_closure_same(h, in, out_host, st);
+  }
 
   // ---- host: mask / coordinates (U:880-887) ------------------------------------------------------
   std::vector<uint8_t> mask; std::vector<int> idx; std::vector<double> gx, gy;
@@ -1321,6 +1332,184 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   return SGP_OK;
 }
 
+// =====================================================================================================
+// ntilde == nt: the closure as the reference evaluates it when every training image is an inducing image
+// (U:2032 `K = K_tilde`, U:2068 `a = B`; one_cell_active_training.ipynb cell 17 always runs this way).
+//   K = K_tilde (symmetrised, from xtilde), K_b = K B, a = B (frozen), Kvec_i = x_i^T C x_i + sigma_0^2 (from x),
+//   lam_m = B m_b, lam_var = Kvec + rowsum(a o (a V_b) - K_b o a), f, loglik, KL as in the general case.
+// The gradient is the reference's FORMULA (lambda_moments, U:1113-1120, applied with a = B):
+//   da = (dK_b - a dK_tilde_b) K_tilde_b^-1, dlam_m = da m_b,
+//   dlam_var = dKvec + 2 rowdot(da, a V_b) - rowdot(dK_b, a) - rowdot(K_b, da)
+// (da vanishes only when q = m).  Reverse mode of exactly that, with u = A(r - f), v = -A^2 f / 2:
+//   Ga = u m_b^T + v o (2 a V_b - K_b)                      (adjoint of da)
+//   H = Ga K_tilde_b^-1;   Gq = -a^T H - kl_weight * dKL/dK_tilde_b       (adjoint of dK_tilde_b)
+//   G_Ktilde = (H - diag(v) a + B Gq) B^T                   (dK_b = dK B, dK_tilde_b = B^T dK B, and dK = dK_tilde)
+//   then the inducing-point backward pass of the general case on G_Ktilde, plus the dKvec term: X^T diag(v) X against
+//   dC_k and 2 sigma_0 sum(v).  Everything is m x m / m x p: dense kernels, one stream.
+// =====================================================================================================
+int run_closure_same(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream_t st) {
+  int rc = ensure_ready(h); if (rc) return rc;
+  const int m = in.m, q = in.q, n = in.n_px;
+  if (in.N != m) return fail(h, SGP_E_ARG, "run_closure_same: N != m");
+  std::vector<uint8_t> mask; std::vector<int> idx; std::vector<double> gx, gy;
+  const int p = compute_mask(in.theta, n, mask, idx, gx, gy);       // exactly the reference's x[:, mask]
+  if (p == 0) return fail(h, SGP_E_ARG, "sgp_elbo_grad: empty receptive-field mask");
+  const ThetaDev th = make_theta(in.theta);
+  const double A = std::exp(in.logA);
+  const long ldp = rup(p, 16), ldm = rup(m, 16), ldq = rup(q, 16);
+  const int ntp_s = (p + 63) / 64, ntq = (q + 127) / 128;
+  const long ldpart = ldm;
+  const int nblk_bwd = acos_backward_blocks(m), nbm = moments_rows_blocks(m);
+  size_t need = 0;
+  auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
+  acc(p); acc(p); acc((size_t)(p + 1) / 2 + 8); acc((size_t)p * ldp);
+  for (int i = 0; i < 5; ++i) acc((size_t)m * ldp);                   // Xg, Ug, ZU, ZX, YX
+  for (int i = 0; i < 4; ++i) acc((size_t)m * ldm);                   // Kraw, Kt, cosU, GKt
+  for (int i = 0; i < 8; ++i) acc((size_t)m * ldq);                   // Bw, Kb, aV, Ga, H, BGq, E, spare
+  for (int i = 0; i < 10; ++i) acc((size_t)q * ldq);
+  acc(64 * ldq); acc(chol_winv_elems(q)); acc(chol_winv_elems(q));
+  for (int i = 0; i < 16; ++i) acc(ldm);
+  acc((size_t)std::max(ntp_s, ntq) * ldpart * 2);
+  acc((size_t)nbm * 4); acc((size_t)nblk_bwd * ldm); acc(nblk_bwd);
+  acc((size_t)p * ldp); acc((size_t)p * ldp); acc((size_t)p * 5);
+  for (int i = 0; i < 3; ++i) acc(m);
+  need += 4096;
+  CU(h->arena.reserve(need));
+  Arena ar(h->arena.p, h->arena.bytes);
+  double* d_gx = ar.take<double>(p); double* d_gy = ar.take<double>(p);
+  int* d_idx = (int*)ar.take<double>((size_t)(p + 1) / 2 + 8);
+  double* C = ar.take<double>((size_t)p * ldp);
+  double* Xg = ar.take<double>((size_t)m * ldp); double* Ug = ar.take<double>((size_t)m * ldp);
+  double* ZU = ar.take<double>((size_t)m * ldp); double* ZX = ar.take<double>((size_t)m * ldp);
+  double* YX = ar.take<double>((size_t)m * ldp);
+  double* Kraw = ar.take<double>((size_t)m * ldm); double* Kt = ar.take<double>((size_t)m * ldm);
+  double* cosU = ar.take<double>((size_t)m * ldm); double* GKt = ar.take<double>((size_t)m * ldm);
+  double* Bw = ar.take<double>((size_t)m * ldq); double* Kb = ar.take<double>((size_t)m * ldq);
+  double* aV = ar.take<double>((size_t)m * ldq); double* Ga = ar.take<double>((size_t)m * ldq);
+  double* Hm = ar.take<double>((size_t)m * ldq); double* BGq = ar.take<double>((size_t)m * ldq);
+  double* Em = ar.take<double>((size_t)m * ldq); (void)ar.take<double>((size_t)m * ldq);
+  double* qq[10]; for (int i = 0; i < 10; ++i) qq[i] = ar.take<double>((size_t)q * ldq);
+  double* tri_tmp = ar.take<double>(64 * ldq);
+  double* winv = ar.take<double>(chol_winv_elems(q)); double* winv2 = ar.take<double>(chol_winv_elems(q));
+  double* vecs[16]; for (int i = 0; i < 16; ++i) vecs[i] = ar.take<double>(ldm);
+  double* part1 = ar.take<double>((size_t)std::max(ntp_s, ntq) * ldpart);
+  double* part2 = ar.take<double>((size_t)std::max(ntp_s, ntq) * ldpart);
+  double* blockpart = ar.take<double>((size_t)nbm * 4);
+  double* colkU = ar.take<double>((size_t)nblk_bwd * ldm); double* sumpartU = ar.take<double>(nblk_bwd);
+  double* GCU = ar.take<double>((size_t)p * ldp); double* GCX = ar.take<double>((size_t)p * ldp);
+  double* gpart = ar.take<double>((size_t)p * 5);
+  double* lam_m = in.lam_m ? in.lam_m : ar.take<double>(m);
+  double* lam_var = in.lam_var ? in.lam_var : ar.take<double>(m);
+  double* fvec = in.f ? in.f : ar.take<double>(m);
+  double* Vw = qq[0]; double* Ktb_raw = qq[1]; double* Ktb = qq[2]; double* Lk = qq[3]; double* Linv = qq[4];
+  double* Kinv_raw = qq[5]; double* Kinv = qq[6]; double* KV = qq[7]; double* KVK = qq[8]; double* Gq = qq[9];
+  double* tU = vecs[0]; double* X2 = vecs[1]; double* sX = vecs[2]; double* nX = vecs[3]; double* bq = vecs[4];
+  double* lm_t = vecs[5]; double* lv_t = vecs[6]; double* u_s = vecs[7]; double* v_s = vecs[8]; double* wr = vecs[9];
+  double* kappaU = vecs[10]; double* wc = vecs[11]; double* wU = vecs[12]; double* Lv = Ktb_raw;   // reused after K_tilde_b
+
+  {   // small uploads through the pinned ring (pageable uploads would synchronise the stream)
+    char* pin = nullptr; int pslot = 0;
+    const size_t pb = (size_t)p * 8;
+    rc = pin_acquire(h, 3 * pb + 64, &pin, &pslot); if (rc) return rc;
+    std::memcpy(pin, gx.data(), pb); std::memcpy(pin + pb, gy.data(), pb); std::memcpy(pin + 2 * pb, idx.data(), (size_t)p * 4);
+    CU(cudaMemcpyAsync(d_gx, pin, pb, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_gy, pin + pb, pb, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_idx, pin + 2 * pb, (size_t)p * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaEventRecord(h->pin_ev[pslot], st));
+    h->pin_used[pslot] = true;
+  }
+  CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
+  CU(cudaMemsetAsync(h->d_scal, 0, sizeof(double) * kNumSlots, st));
+  gather_cols(in.X, in.ldx, m, d_idx, p, Xg, ldp, st);
+  gather_cols(in.U, in.ldu, m, d_idx, p, Ug, ldp, st);
+  copy_mat(in.B, in.ldb, m, q, Bw, ldq, st);
+  copy_mat(in.V, in.ldv, q, q, Vw, ldq, st);
+  build_C(C, ldp, p, d_gx, d_gy, th, nullptr, 0, st);
+
+  // ---- forward ------------------------------------------------------------------------------------------
+  auto rowdot_gemm = [&](const double* Xm, double* Z, double* s_out, double* n_out) -> int {   // Z = Xm C, s = rowdot + s0^2
+    GemmArgs g{};
+    g.A = Xm; g.lda = ldp; g.B = C; g.ldb = ldp; g.C = Z; g.ldc = ldp; g.M = m; g.N = p; g.K = p;
+    g.aux = Xm; g.ldaux = ldp; g.part1 = part1; g.ldpart = ldpart;
+    CU(gemm(st, 0, 1, kRowdot, true, 1, g));
+    norms_finalize(part1, ldpart, ntp_s, m, th.s02, s_out, n_out, st);
+    return SGP_OK;
+  };
+  rc = rowdot_gemm(Ug, ZU, tU, X2); if (rc) return rc;                                      // U:978-979 on xtilde
+  rc = rowdot_gemm(Xg, ZX, sX, nX); if (rc) return rc;                                      // Kvec from x (U:2033)
+  {
+    GemmArgs a{};   // K_tilde (raw) = acos-kernel(ZU Ug^T), cos kept for the backward pass
+    a.A = ZU; a.lda = ldp; a.B = Ug; a.ldb = ldp; a.C = Kraw; a.ldc = ldm; a.M = m; a.N = m; a.K = p;
+    a.rowvec = X2; a.colvec = X2; a.C2 = cosU; a.s02 = th.s02;
+    CU(gemm(st, 0, 0, kAcos, true, 1, a));
+  }
+  symmetrize(Kraw, ldm, m, Kt, ldm, st);                                                    // U:1024-1025
+  CU(mm(st, 0, 1, Kt, ldm, Bw, ldq, Kb, ldq, m, q, m));                                      // K_b = K B, K = K_tilde (U:2032, 2049)
+  CU(mm(st, 1, 1, Bw, ldq, Kb, ldq, Ktb_raw, ldq, q, q, m));                                 // B^T K_tilde B (U:2047)
+  symmetrize(Ktb_raw, ldq, q, Ktb, ldq, st);                                                // U:2048
+  copy_mat(Ktb, ldq, q, q, Lk, ldq, st);
+  CU(cholesky_lower(Lk, ldq, q, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, winv, st));
+  logdet_from_chol(Lk, ldq, q, h->d_scal, kSlotLogdetK, st);
+  CU(tri_inverse_lower(Lk, ldq, q, Linv, tri_tmp, winv, st));
+  CU(mm(st, 1, 1, Linv, ldq, Linv, ldq, Kinv_raw, ldq, q, q, q));                            // K_tilde_b^-1 (U:2067)
+  symmetrize(Kinv_raw, ldq, q, Kinv, ldq, st);
+  gemv(Kinv, ldq, q, q, 0, in.m_b, bq, st);
+  CU(mm(st, 0, 1, Kinv, ldq, Vw, ldq, KV, ldq, q, q, q));
+  CU(mm(st, 0, 1, KV, ldq, Kinv, ldq, KVK, ldq, q, q, q));
+  kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, Gq, st);      // Gq: scratch until the backward pass
+  if (!in.logdetV_host) {
+    copy_mat(Vw, ldq, q, q, Lv, ldq, st);
+    CU(cholesky_lower(Lv, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, winv2, st));
+    logdet_from_chol(Lv, ldq, q, h->d_scal, kSlotLogdetV, st);
+  }
+  {
+    GemmArgs g{};   // aV = a V^T with a = B; part1 = rowdot(aV, a), part2 = a m_b   (U:1090-1101)
+    g.A = Bw; g.lda = ldq; g.B = Vw; g.ldb = ldq; g.C = aV; g.ldc = ldq; g.M = m; g.N = q; g.K = q;
+    g.aux = Bw; g.ldaux = ldq; g.colvec = in.m_b; g.part1 = part1; g.part2 = part2; g.ldpart = ldpart;
+    CU(gemm(st, 0, 0, kMoments, false, 1, g));
+  }
+  moments_combine(sX, part1, part2, ldpart, ntq, ntq, Bw, ldq, Kb, ldq, m, q, lm_t, lv_t, st);
+  moments_rows(lv_t, part1, lm_t, ldpart, 0, 1, in.r, m, A, in.lambda0, lam_m, lam_var, fvec, u_s, v_s, blockpart, st);
+  sum_to_slots(blockpart, nbm, 4, 4, h->d_scal, kSlotRLam, 0, st);
+  // ---- backward -----------------------------------------------------------------------------------------
+  same_ga(Ga, ldq, m, q, u_s, v_s, in.m_b, aV, Kb, st);
+  CU(mm(st, 0, 1, Ga, ldq, Kinv, ldq, Hm, ldq, m, q, q));                                    // H = Ga K_tilde_b^-1
+  CU(mm(st, 1, 1, Bw, ldq, Hm, ldq, Gq, ldq, q, q, m, -1.0));                                // -a^T H
+  gkt_assemble(Gq, ldq, q, Kinv, KVK, bq, h->kl_weight, st);                                // - kl_weight * dKL/dK_tilde_b (U:1333)
+  CU(mm(st, 0, 1, Bw, ldq, Gq, ldq, BGq, ldq, m, q, q));
+  same_combine(Em, ldq, m, q, Hm, v_s, Bw, BGq, st);
+  CU(mm(st, 0, 0, Em, ldq, Bw, ldq, GKt, ldm, m, m, q));                                     // adjoint of the m x m dK_tilde
+  acos_backward(1, GKt, cosU, nullptr, ldm, m, m, nullptr, nullptr, nullptr, X2, X2, wr, colkU, nullptr, ldm, sumpartU,
+                st);
+  col_reduce(colkU, nblk_bwd, m, ldm, kappaU, 0, st);
+  col_weights(kappaU, nullptr, nullptr, X2, m, wc, st);
+  sum_to_slot(sumpartU, nblk_bwd, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+  sum_to_slot(wr, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+  sum_to_slot(wc, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);
+  sum_to_slot(v_s, m, 1, 1.0, h->d_scal, kSlotSig, 1, st);                                  // dKvec[sigma_0] = 2 sigma_0 (U:1036)
+  lincomb(wU, ldm, 1, m, 1.0, wr, ldm, 1.0, wc, ldm, 0.0, st);
+  {
+    GemmArgs g{};   // YU = R Ug + diag(wU) Ug  (into ZU), then Ug^T YU
+    g.A = GKt; g.lda = ldm; g.B = Ug; g.ldb = ldp; g.C = ZU; g.ldc = ldp; g.M = m; g.N = p; g.K = m;
+    g.rowvec = wU; g.aux = Ug; g.ldaux = ldp;
+    CU(gemm(st, 0, 1, kAxpyRow, true, 1, g));
+  }
+  CU(mm(st, 1, 1, Ug, ldp, ZU, ldp, GCU, ldp, p, p, m));
+  scale_rows(YX, Xg, ldp, m, v_s, st);                                                      // dKvec[k] = x_i^T dC_k x_i (U:1042)
+  CU(mm(st, 1, 1, Xg, ldp, YX, ldp, GCX, ldp, p, p, m));                                     // X^T diag(v) X
+  contract_dC(GCX, 1, (long)p * ldp, GCU, C, ldp, p, d_gx, d_gy, th, gpart, st);
+  sum_to_slots(gpart, p, 5, 5, h->d_scal, kSlotG, 0, st);
+  const bool async_out = in.out_dev != nullptr;
+  finalize(h->d_scal, h->d_flags, A, in.lambda0, th, p, in.logdetV_host ? *in.logdetV_host : 0.0,
+           in.logdetV_host ? 1 : 0, async_out ? in.out_dev : h->d_out, 0.0, st);
+  CU(cudaGetLastError());
+  if (async_out) return SGP_OK;
+  CU(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(double) * 16, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (out_host) std::memcpy(out_host, h->h_out, sizeof(double) * 16);
+  h->dbg.clear();
+  return SGP_OK;
+}
 }  // namespace
 
 extern "C" {

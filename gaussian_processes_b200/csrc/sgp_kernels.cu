@@ -1117,4 +1117,46 @@ void scale_vec(double* x, long n, double alpha, cudaStream_t st) {
   note_launch(); scale_vec_kernel<<<cdiv(n, 256), 256, 0, st>>>(x, n, alpha);
 }
 
+// =====================================================================================================
+// ntilde == nt closure (a = B, utils.py:2032 / 2068): the three elementwise pieces of its adjoint (m x q, small)
+// =====================================================================================================
+// Ga_ij = u_i m_b[j] + v_i (2 aV_ij - Kb_ij): adjoint of `da` in dlam_m = da m, dlam_var = ... + 2 rowdot(da, aV) - rowdot(K_b, da)
+__global__ void same_ga_kernel(double* __restrict__ Ga, long ld, int rows, int cols, const double* __restrict__ u,
+                               const double* __restrict__ v, const double* __restrict__ m_b,
+                               const double* __restrict__ aV, const double* __restrict__ Kb) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i >= rows || j >= ld) return;
+  const long o = (long)i * ld + j;
+  Ga[o] = j < cols ? u[i] * m_b[j] + v[i] * (2.0 * aV[o] - Kb[o]) : 0.0;
+}
+void same_ga(double* Ga, long ld, int rows, int cols, const double* u, const double* v, const double* m_b,
+             const double* aV, const double* Kb, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return;
+  note_launch(); same_ga_kernel<<<dim3(cdiv(ld, 128), rows), 128, 0, st>>>(Ga, ld, rows, cols, u, v, m_b, aV, Kb);
+}
+// E_ij = H_ij - v_i a_ij + BG_ij  (H = Ga K^-1: via da -> dK_b; -v a: the -rowdot(dK_b, a) term; BG: via dK_tilde_b)
+__global__ void same_combine_kernel(double* __restrict__ E, long ld, int rows, int cols, const double* __restrict__ H,
+                                    const double* __restrict__ v, const double* __restrict__ a,
+                                    const double* __restrict__ BG) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i >= rows || j >= ld) return;
+  const long o = (long)i * ld + j;
+  E[o] = j < cols ? H[o] - v[i] * a[o] + BG[o] : 0.0;
+}
+void same_combine(double* E, long ld, int rows, int cols, const double* H, const double* v, const double* a,
+                  const double* BG, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return;
+  note_launch(); same_combine_kernel<<<dim3(cdiv(ld, 128), rows), 128, 0, st>>>(E, ld, rows, cols, H, v, a, BG);
+}
+// out_ij = w_i in_ij (row scaling; padding columns up to ld copied scaled as well: they are zero)
+__global__ void scale_rows_kernel(double* __restrict__ out, const double* __restrict__ in, long ld, int rows,
+                                  const double* __restrict__ w) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (i < rows && j < ld) out[(long)i * ld + j] = w[i] * in[(long)i * ld + j];
+}
+void scale_rows(double* out, const double* in, long ld, int rows, const double* w, cudaStream_t st) {
+  if (rows <= 0) return;
+  note_launch(); scale_rows_kernel<<<dim3(cdiv(ld, 128), rows), 128, 0, st>>>(out, in, ld, rows, w);
+}
+
 }  // namespace sgp

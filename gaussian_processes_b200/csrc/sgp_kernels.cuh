@@ -122,6 +122,13 @@ void logdet_from_chol(const double* L, long ld, int n, double* scal, int slot, c
 void kl_scalars(const double* m_b, const double* b, const double* V, long ldv, const double* Kinv, long ldk, int q,
                 double* scal, int slot_mb, int slot_tr, double* scratch, cudaStream_t st);
 
+// ---- ntilde == nt closure (a = B): elementwise pieces of the adjoint, m x q each (definitions: sgp_kernels.cu) ----
+void same_ga(double* Ga, long ld, int rows, int cols, const double* u, const double* v, const double* m_b,
+             const double* aV, const double* Kb, cudaStream_t st);                   // u m^T + v o (2 aV - Kb)
+void same_combine(double* E, long ld, int rows, int cols, const double* H, const double* v, const double* a,
+                  const double* BG, cudaStream_t st);                                // H - diag(v) a + BG
+void scale_rows(double* out, const double* in, long ld, int rows, const double* w, cudaStream_t st);   // diag(w) in
+
 // ---- final contraction with dC_k and result assembly -----------------------------------------
 // GC = sum_z GCpart[z] + GCextra ; gpart[blk*5 + k] = sum_ab GC_ab * dC_k,ab  (k: Amp, beta, rho, ex, ey)
 int contract_blocks(int p);

@@ -287,11 +287,16 @@ OUT_KEYS = ("loglik", "KL", "g_sigma_0", "g_eps_0x", "g_eps_0y", "g_-2log2beta",
 
 def elbo_grad(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
               m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float, lims=None,
-              logdetV: Optional[float] = None, want_moments: bool = False, kl_weight: float = 1.0) -> Dict:
+              logdetV: Optional[float] = None, want_moments: bool = False, kl_weight: float = 1.0,
+              same: Optional[bool] = None) -> Dict:
     """Fused M-step closure body (utils.py:2030-2099): one C call, one 16-double read-back.
-    kl_weight scales the KL part of the returned gradient (image shards other than the first pass 0)."""
+    kl_weight scales the KL part of the returned gradient (image shards other than the first pass 0).
+    same: None = as the reference decides (ntilde == nt by the row counts: K = K_tilde, a = B); False = never (callers
+    whose X is a shard of the images)."""
     _need_cuda(X, r, xtilde, B, m_b, V_b)
-    set_option(X.device.index if X.device.index is not None else torch.cuda.current_device(), "kl_weight", kl_weight)
+    _dev = X.device.index if X.device.index is not None else torch.cuda.current_device()
+    set_option(_dev, "kl_weight", kl_weight)
+    set_option(_dev, "square_is_same", 0.0 if same is False else 1.0)
     X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
     r, m_b = r.contiguous(), m_b.contiguous()
     N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]
@@ -327,7 +332,9 @@ def elbo_grad_dev(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: 
     """Asynchronous fused closure (sgp_elbo_grad_dev): returns the 16 result doubles as a DEVICE tensor (layout
     OUT_KEYS) without synchronising the host; the caller reduces / reads them in stream order."""
     _need_cuda(X, r, xtilde, B, m_b, V_b)
-    set_option(X.device.index if X.device.index is not None else torch.cuda.current_device(), "kl_weight", kl_weight)
+    _dev = X.device.index if X.device.index is not None else torch.cuda.current_device()
+    set_option(_dev, "kl_weight", kl_weight)
+    set_option(_dev, "square_is_same", 0.0)       # image shards: the local row count says nothing about ntilde == nt
     X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
     r, m_b = r.contiguous(), m_b.contiguous()
     N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]

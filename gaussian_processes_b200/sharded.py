@@ -124,7 +124,7 @@ def elbo_grad(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0,
     if sg is not None and sg.world > 1 and getattr(sg, "peer_exchange", False):
         # the exchange happened inside the evaluation's last kernel: the 16 doubles read back are already reduced
         out = native_mod.elbo_grad(X_local, r_local, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0, logdetV=logdetV,
-                                   kl_weight=1.0 if rank == 0 else 0.0)
+                                   kl_weight=1.0 if rank == 0 else 0.0, same=False)
         return {"loglik": out["loglik"], "KL": out["KL"], "grad": out["grad"], "flags": out["flags"],
                 "any_flag": out["flags"] != 0, "p": out["p"]}
     if sg is not None and sg.world > 1 and X_local.is_cuda and hasattr(native_mod, "elbo_grad_dev"):

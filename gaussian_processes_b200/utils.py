@@ -634,12 +634,19 @@ def elbo_and_grad(theta, lo, hi, n_px_side, x, xtilde, r, B, m_b, V_b, f_params,
     if same is None:
         same = (not _sharded()) and x.shape[0] == xtilde.shape[0]
     kernfun = kernfun or acosker
+    if same and x.is_cuda and kernfun is acosker:
+        # ntilde == nt (K = K_tilde, a = B: the active-learning configuration): the fused call's own routine for it
+        logA, lambda0 = _link_params(f_params)
+        out = native.elbo_grad(x, r, xtilde, int(n_px_side), _theta_floats(theta), B, m_b, V_b, logA, lambda0,
+                               logdetV=logdetV, same=True)
+        if not out["flags"] & (FLAG_KT_NOT_PD | FLAG_KT_SMALL_PIVOT):
+            return out["loglik"], out["KL"], out["grad"]
     if not same:
         logA, lambda0 = _link_params(f_params)
         if _sharded() and getattr(_SHARD, "peer_exchange", False):
             # image shards with the exchange fused into the evaluation's last kernel (peer memory): already reduced
             out = native.elbo_grad(x, r, xtilde, int(n_px_side), _theta_floats(theta), B, m_b, V_b, logA, lambda0,
-                                   logdetV=logdetV, kl_weight=1.0 if _shard_rank() == 0 else 0.0)
+                                   logdetV=logdetV, kl_weight=1.0 if _shard_rank() == 0 else 0.0, same=False)
             if out["flags"] & 32:
                 raise RuntimeError("image-sharded evaluation: a peer's partial result did not arrive (exchange timeout)")
             if not out["flags"] & (FLAG_KT_NOT_PD | FLAG_KT_SMALL_PIVOT):
@@ -654,7 +661,8 @@ def elbo_and_grad(theta, lo, hi, n_px_side, x, xtilde, r, B, m_b, V_b, f_params,
                 return v[0], v[1], dict(zip(THETA_KEYS, v[2:8]))
             return _closure_forward_mode(theta, lo, hi, n_px_side, x, xtilde, r, kernfun, same, B, m_b, V_b, f_params)
         out = native.elbo_grad(x, r, xtilde, int(n_px_side), _theta_floats(theta), B, m_b, V_b, logA, lambda0,
-                               logdetV=logdetV, kl_weight=1.0 if _shard_rank() == 0 else 0.0)
+                               logdetV=logdetV, kl_weight=1.0 if _shard_rank() == 0 else 0.0,
+                               same=False if _sharded() else None)
         bad = float(bool(out["flags"] & (FLAG_KT_NOT_PD | FLAG_KT_SMALL_PIVOT)))
         vec = _shard_sum([out["loglik"]] + [out["grad"][k] for k in THETA_KEYS] + [bad])   # the one exchange step
         if vec[7] == 0:

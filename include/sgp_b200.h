@@ -69,6 +69,9 @@ SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
  * by two pixels, kept while later masks stay inside it -- the mask is recomputed from theta in every closure
  * (utils.py:2030) and flips pixels during a line search; 0 = exactly the mask, as the reference gathers x[:, mask];
  * 1 = the whole grid, images read in place.  Pixels of the support outside the mask carry C = 0, i.e. exact zeros),
+ * "square_is_same" (1 = a call with N == m is the reference's ntilde == nt branch, K = K_tilde and a = B,
+ * utils.py:2032 / 2068 -- the default, as the reference decides by the row counts alone; 0 = N == m is treated like
+ * any other N: set by image-sharded callers, whose local row count says nothing about the global one),
  * "projected" (-1 = moments in the projected basis K_b = K B when q <= 0.4 m, 0 = never, 1 = always; same numbers
  * up to rounding, utils.py:2047-2068), "overlap" (1 = the q x q chains run on side streams).
  * With int8 slices the library keeps a sliced copy of device-resident images across calls (same bytes as X).     */

@@ -170,6 +170,18 @@ def gen_big(ref):
                          perturb={"eps_0y": 0.01, "sigma_0": 0.05})
 
 
+def gen_square_cases(ref):
+    """ntilde == nt (K = K_tilde, a = B) beyond the full-rank toy case: a rank-deficient one (q < m, so the reference's
+    `da` formula does not vanish), a perturbed-theta one, and one at the active-learning notebook's scale (m = N = 300)."""
+    rd = {**synth.THETA_NOTEBOOK, "-2log2beta": 3.0, "-log2rho2": 3.5}
+    gen_closure_case(ref, "closure_square_rankdef_n10", N=90, n=10, m=90, cfg=15, theta_dict=rd, store_big=False,
+                     perturb={"eps_0y": -0.02, "-log2rho2": 0.1, "sigma_0": 0.05})
+    gen_closure_case(ref, "closure_square_local_n12", N=70, n=12, m=70, cfg=16, theta_dict=synth.theta_localised(12),
+                     store_big=False, perturb={"eps_0x": 0.03, "Amp": 0.2, "-2log2beta": -0.05})
+    gen_closure_case(ref, "closure_square_n20_m300", N=300, n=20, m=300, cfg=17, theta_dict=synth.theta_localised(20),
+                     store_big=False, perturb={"eps_0x": 0.01, "eps_0y": -0.01})
+
+
 def gen_kat(ref):
     """The toy known-answer vectors of moments_gradients.ipynb cells 1-3, recomputed with the
     reference's own lambda_moments / compute_loglikelihood / log_det and compared with the
@@ -305,6 +317,9 @@ def main():
     gen_utility(ref)
     if len(sys.argv) > 1 and sys.argv[1] == "utility":
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "square":
+        gen_square_cases(ref)
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "big":
         gen_big(ref)
         return
@@ -323,6 +338,7 @@ def main():
                      perturb={"eps_0y": -0.02, "-log2rho2": 0.1})
     # ntilde == nt (active-learning configuration: K = K_tilde, a = B)
     gen_closure_case(ref, "closure_square_n8", N=48, n=8, m=48, cfg=14, theta_dict=synth.THETA_DENSE, store_big=False)
+    gen_square_cases(ref)
     # BASELINE config 1 (20x20, N=2000, m=100), dense and localised theta
     gen_closure_case(ref, "closure_c1_dense", N=2000, n=20, m=100, cfg=1, theta_dict=synth.THETA_DENSE)
     gen_closure_case(ref, "closure_c1_local", N=2000, n=20, m=100, cfg=1, theta_dict=synth.theta_localised(20),

@@ -113,7 +113,7 @@ def matmul_tn(At, B):
 
 
 def elbo_grad(X, r, xtilde, n_px, theta, B, m_b, V_b, logA, lambda0, lims=None, logdetV=None, want_moments=False,
-              kl_weight=1.0):
+              kl_weight=1.0, same=None):
     calls["elbo_grad"] += 1
     out = adjoint_model.elbo_and_grad(_th(theta), X, r, xtilde, n_px, B, m_b, V_b, logA, lambda0, kl_weight=kl_weight)
     KL = out["KL"]

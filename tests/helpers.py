@@ -8,7 +8,10 @@ from gaussian_processes_b200 import synth
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CLOSURE_CASES = ["closure_dense_n8", "closure_local_n12", "closure_rankdef_n10", "closure_square_n8",
-                 "closure_c1_dense", "closure_c1_local"]
+                 "closure_c1_dense", "closure_c1_local", "closure_square_rankdef_n10", "closure_square_local_n12",
+                 "closure_square_n20_m300"]
+# ntilde == nt (K = K_tilde, a = B: the configuration the reference's active-learning notebook always runs)
+SQUARE_CASES = ["closure_square_n8", "closure_square_rankdef_n10", "closure_square_local_n12", "closure_square_n20_m300"]
 # fixtures at the sizes bench.py times (n = 40; m = 500 / 1000): outputs of the real reference, B stored, V_b regenerated
 BIG_CASES = ["closure_c2_dense_n40", "closure_c2_local_n40", "closure_c3_m1000_n40"]
 

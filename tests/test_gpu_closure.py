@@ -239,3 +239,46 @@ def test_closure_on_a_support_larger_than_the_mask(name, path, i8, support):
     finally:
         native.set_option(0, "support", -1)
     check(fx, out)
+
+
+@pytest.mark.parametrize("i8", [-1, 0, 8])
+@pytest.mark.parametrize("name", ["closure_square_n8", "closure_square_rankdef_n10", "closure_square_local_n12",
+                                  "closure_square_n20_m300"])
+def test_closure_ntilde_equals_nt_fused(name, i8):
+    """ntilde == nt inside the fused call (run_closure_same: K = K_tilde, a = B, U:2032 / U:2068; the reference's own
+    `da` formula, which only vanishes when q = m -- the rank-deficient fixture has q = 71 < m = 90).  Same 1e-9 bar,
+    gradients per component; the engine option must not matter (the routine is dense fp64)."""
+    from helpers import record
+    fx, out = run_case(name, i8=i8)
+    check(fx, out)
+    keys = [str(k) for k in fx["theta_keys"]]
+    worst = 0.0
+    for i, k in enumerate(keys):
+        sc = max(abs(fx["dloglik"][i]), abs(fx["dKL"][i]))
+        err = abs(out["grad"][k] - (fx["dloglik"][i] - fx["dKL"][i])) / sc
+        worst = max(worst, err)
+        assert err <= RTOL, (k, err)
+    record(f"same/{name}/i8_{i8}", grad_comp=worst, loglik=abs(out["loglik"] - float(fx["loglik"])) / abs(float(fx["loglik"])))
+
+
+def test_square_shard_is_not_the_same_case():
+    """An image SHARD that happens to hold m rows must not take the a = B branch: with same=False the
+    N == m call runs the general path, i.e. it equals the sum of two half-shards evaluated the general way."""
+    from gaussian_processes_b200 import native
+    fx = load("closure_square_local_n12")
+    prob, st = case_inputs(fx)
+    d = torch.device("cuda:0")
+    X, r, xt = prob.X.to(d), prob.r.to(d), prob.xtilde.flip(0).contiguous().to(d)    # other inducing images than X's
+    B, m_b, V_b = st["B"].to(d), st["m_b"].to(d), st["V_b"].to(d)
+
+    def ev(Xs, rs, klw, **kw):
+        return native.elbo_grad(Xs, rs, xt, prob.n_px_side, prob.theta, B, m_b, V_b, st["logA"], st["lambda0"],
+                                kl_weight=klw, **kw)
+    whole = ev(X, r, 1.0, same=False)
+    h = X.shape[0] // 2
+    a, b = ev(X[:h], r[:h], 1.0), ev(X[h:], r[h:], 0.0)
+    as_same = ev(X, r, 1.0)                                    # the reference's reading of N == m
+    assert abs(whole["loglik"] - (a["loglik"] + b["loglik"])) <= 1e-12 * abs(whole["loglik"])
+    for k in whole["grad"]:
+        assert abs(whole["grad"][k] - (a["grad"][k] + b["grad"][k])) <= 1e-10 * max(abs(v) for v in whole["grad"].values())
+    assert abs(as_same["loglik"] - whole["loglik"]) > 1e-6 * abs(whole["loglik"])

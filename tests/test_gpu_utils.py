@@ -70,7 +70,8 @@ def test_vargp_tracks_match_reference_on_gpu(U):
     assert np.allclose(np.linalg.eigvalsh(fit["V_b"].cpu().numpy()), np.linalg.eigvalsh(fx["V_b"]), rtol=1e-6)
 
 
-@pytest.mark.parametrize("name", ["closure_square_n8", "closure_local_n12", "closure_c1_dense"])
+@pytest.mark.parametrize("name", ["closure_square_n8", "closure_square_rankdef_n10", "closure_square_n20_m300",
+                                  "closure_local_n12", "closure_c1_dense"])
 def test_elbo_and_grad_surface(U, name):
     """utils.elbo_and_grad: fused reverse-mode call when ntilde != nt, reference-sequenced closure when ntilde == nt."""
     fx = load(name)
