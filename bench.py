@@ -375,6 +375,51 @@ def secondary_metrics(native, dev, X, r, xt, Cm, mask, theta, B, ev_keep, m_b, V
         native.invalidate_cache(dev.index or 0)
     except Exception as e:  # pragma: no cover
         out["config3_size"] = {"error": repr(e)}
+    # BASELINE configs[2] as a WORKLOAD (one_cell_active_training.ipynb cell 17): a fixed training set of
+    # N = 50 000 images, the inducing set grown from 980 to 1000 one image at a time.  Per added image: one new column of
+    # K_tilde (sgp_acosker on one image) and of K (N x 1), padded (m, V), eigh(K_tilde) (library), K_b = K B,
+    # and the warm-started varGP(init_kernel=...) -- here 2 EM iterations of 3 E-steps (3 logA steps) + 3 LBFGS M-steps.
+    try:
+        import contextlib
+        import io
+        from gaussian_processes_b200 import active, utils as U
+        na, m_a0 = min(50000, X.shape[0]), int(os.environ.get("SGP_BENCH_ACTIVE_M0", 980))
+        n_add = int(os.environ.get("SGP_BENCH_ACTIVE_STEPS", 20))
+        Xa, ra = X[:na], r[:na]
+        with contextlib.redirect_stdout(io.StringIO()):
+            fit_kw = dict(
+                fit_parameters=dict(ntilde=m_a0, maxiter=2, nEstep=2, nMstep=0, nFparamstep=3, kernfun="acosker",
+                                    cellid=0, n_px_side=n_side, display_hyper=False),
+                xtilde=X[:m_a0].clone(),
+                hyperparams_tuple=(synth.theta_tensors(theta, device=dev, requires_grad=True),
+                                   dict(synth.THETA_LIMS_LO), dict(synth.THETA_LIMS_HI)),
+                f_params={"logA": torch.tensor(logA, device=dev), "lambda0": torch.tensor(lambda0, device=dev)})
+            model, err = U.varGP(Xa, ra, **fit_kw)
+            assert not err["is_error"], err
+            model["fit_parameters"] = dict(model["fit_parameters"], maxiter=3, nEstep=3, nMstep=3, nFparamstep=3)
+            tm = {}
+            native.launch_count(dev.index or 0, reset=True)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            losses = []
+            for j in range(n_add):
+                model, err = active.add_image_and_refit(U, model, Xa, ra, X[:m_a0 + j + 1].clone(), tm)
+                assert not err["is_error"], err
+                losses.append(float(model["values_track"]["loss_track"]["logmarginal"][-1]))
+            torch.cuda.synchronize()
+            tot = time.perf_counter() - t0
+        out["active_loop"] = {"what": "add inducing image -> new K_tilde / K column -> eigh -> K_b = K B -> varGP(init_kernel): "
+                                      "2 EM iterations x (3 E-steps + 3 LBFGS M-step iterations)",
+                              "N": na, "m_from": m_a0, "m_to": m_a0 + n_add, "additions": n_add, "q_last": int(model["B"].shape[1]),
+                              "ms_per_addition": 1e3 * tot / n_add, "additions_per_sec": n_add / tot,
+                              "ms_per_addition_by_stage": {k: 1e3 * v / n_add for k, v in tm.items()},
+                              "gpu_launches_per_addition": native.launch_count(dev.index or 0) / n_add,
+                              "logmarginal_first_last": [losses[0], losses[-1]]}
+        del model, Xa
+        native.release_cache(dev.index or 0)
+        torch.cuda.empty_cache()
+    except Exception as e:  # pragma: no cover
+        out["active_loop"] = {"error": repr(e)}
     # precision / throughput knob of the int8-slice products: S digits of 7 bits per fp64 operand (S = 8: DGEMM error
     # class, the default and the headline; S = 4: 27 bits, above fp32's 24).  Error = against the S = 8 result.
     try:
@@ -815,7 +860,7 @@ def run_ours(args):
             roof["library_gpu_baseline"] = {"error": repr(e)}
     # the driver's record keeps `roofline` and drops `secondary`: the figures north_star names live in both
     if secondary:
-        for k in ("logA_closure_pass", "estep_iteration", "mask_flip", "config3_size", "theta_variants"):
+        for k in ("logA_closure_pass", "estep_iteration", "mask_flip", "config3_size", "theta_variants", "active_loop"):
             if k in secondary:
                 roof[k] = secondary[k]
     if c5 is not None:

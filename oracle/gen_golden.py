@@ -182,6 +182,59 @@ def gen_square_cases(ref):
                      store_big=False, perturb={"eps_0x": 0.01, "eps_0y": -0.01})
 
 
+def gen_active_case(ref, name, n, m0, n_add, same, N_fixed=None, cfg=31, fit=(3, 2, 2, 2)):
+    """Active-learning cycles (one_cell_active_training.ipynb cell 17) run by the REAL reference: a start fit with m0
+    inducing images, then `n_add` times: append one image, grow K_tilde (and K) by one column, eigh, and the
+    warm-started `varGP(X_in_use, R_in_use, **active_model)` with `m`, `V`, `init_kernel`.  The cell is notebook code;
+    `gaussian_processes_b200.active.grow_model` restates it and is driven here with U = the reference module.
+    same: ntilde == nt (the notebook's case: every image in use is an inducing image); otherwise the training set is the
+    fixed first N_fixed images and only the inducing set grows.  Stored: the tracks of every warm-started fit."""
+    from gaussian_processes_b200 import active
+    maxiter, nE, nM, nF = fit
+    npool = m0 + n_add if same else N_fixed
+    prob = synth.make_problem(max(npool, m0 + n_add), n, m0, cfg=cfg, theta=synth.theta_localised(n))
+    X, R = prob.X, prob.r
+    theta = synth.theta_tensors(prob.theta, requires_grad=True)
+    X_in_use, R_in_use = (X[:m0], R[:m0]) if same else (X[:N_fixed], R[:N_fixed])
+    args = dict(
+        fit_parameters=dict(ntilde=m0, maxiter=maxiter, nEstep=nE, nMstep=nM, nFparamstep=nF, kernfun="acosker", cellid=0,
+                            n_px_side=n, display_hyper=False),
+        xtilde=X[:m0].clone(), hyperparams_tuple=(theta, dict(synth.THETA_LIMS_LO), dict(synth.THETA_LIMS_HI)),
+        f_params={"logA": torch.tensor(prob.logA), "lambda0": torch.tensor(prob.lambda0)})
+    with contextlib.redirect_stdout(io.StringIO()):
+        model, err = ref.varGP(X_in_use, R_in_use, **args)
+    assert not err["is_error"], err
+    keys = list(model["hyperparams_tuple"][0].keys())
+    fx = dict(n=n, m0=m0, n_add=n_add, same=int(same), N_fixed=N_fixed or 0, cfg=cfg, maxiter=maxiter, nEstep=nE, nMstep=nM,
+              nFparamstep=nF, theta_keys=np.array(keys), logA0=prob.logA, lambda00=prob.lambda0,
+              start_logmarginal=model["values_track"]["loss_track"]["logmarginal"].numpy())
+    for j in range(n_add):
+        xt_new = X[:m0 + j + 1].clone()
+        if same:
+            X_in_use, R_in_use = X[:m0 + j + 1], R[:m0 + j + 1]
+        with contextlib.redirect_stdout(io.StringIO()):
+            model, err = active.add_image_and_refit(ref, model, X_in_use, R_in_use, xt_new)
+        assert not err["is_error"], err
+        vt = model["values_track"]
+        fx[f"logmarginal_{j}"] = vt["loss_track"]["logmarginal"].numpy()
+        fx[f"loglikelihood_{j}"] = vt["loss_track"]["loglikelihood"].numpy()
+        fx[f"KL_{j}"] = vt["loss_track"]["KL"].numpy()
+        fx[f"theta_track_{j}"] = np.stack([vt["theta_track"][k].numpy() for k in keys])
+        fx[f"logA_track_{j}"] = vt["f_par_track"]["logA"].numpy()
+        fx[f"lambda0_track_{j}"] = vt["f_par_track"]["lambda0"].numpy()
+        fx[f"q_{j}"] = model["B"].shape[1]
+    path = os.path.join(ROOT, "tests", "golden", f"{name}.npz")
+    np.savez_compressed(path, **fx)
+    print(f"{name}: start {fx['start_logmarginal'][-1]:.4f}; " +
+          ", ".join(f"step {j}: {fx['logmarginal_%d' % j][0]:.4f} -> {fx['logmarginal_%d' % j][-1]:.4f} (q={fx['q_%d' % j]})"
+                    for j in range(n_add)))
+
+
+def gen_active(ref):
+    gen_active_case(ref, "active_same_n10", n=10, m0=40, n_add=3, same=True)
+    gen_active_case(ref, "active_fixedN_n10", n=10, m0=40, n_add=3, same=False, N_fixed=400, cfg=32)
+
+
 def gen_kat(ref):
     """The toy known-answer vectors of moments_gradients.ipynb cells 1-3, recomputed with the
     reference's own lambda_moments / compute_loglikelihood / log_det and compared with the
@@ -317,6 +370,9 @@ def main():
     gen_utility(ref)
     if len(sys.argv) > 1 and sys.argv[1] == "utility":
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "active":
+        gen_active(ref)
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "square":
         gen_square_cases(ref)
         return
@@ -346,6 +402,7 @@ def main():
     prob_f, fit_f = gen_fit_case(ref, "fit_small_n10", N=400, n=10, m=40, cfg=21, theta_dict=synth.theta_localised(10),
                                  maxiter=4, nE=3, nM=3, nF=3)
     gen_test_and_checkpoint(ref, prob_f, fit_f, "test_small_n10")
+    gen_active(ref)
     gen_big(ref)
 
 

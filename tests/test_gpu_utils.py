@@ -247,3 +247,17 @@ def test_plot_entry_points_exist(U):
         assert fig is not None and fig2 is not None
     except ImportError:
         assert fig is None and fig2 is None
+
+
+@pytest.mark.parametrize("name", ["active_same_n10", "active_fixedN_n10"])
+def test_active_learning_cycles_match_reference_on_gpu(U, name):
+    """The active-learning cycle on the CUDA library: incremental K_tilde / K columns through sgp_acosker on one image,
+    eigh, warm start through init_kernel; ntilde == nt runs the fused a = B closure.  Tracks of every warm-started fit
+    against the REAL reference's (driven through the same gaussian_processes_b200.active.grow_model)."""
+    from active_flow import run_active_fixture
+    from gaussian_processes_b200 import native
+    native.launch_count(0, reset=True)
+    worst = run_active_fixture(U, name, dev=D)
+    assert native.launch_count(0) > 100
+    record("active/" + name, **worst)
+    assert max(worst.values()) <= 1e-9, worst      # measured 2e-15 (ntilde == nt) and 5e-12 (fixed N)

@@ -289,3 +289,12 @@ def test_plot_entry_points_exist(U):
         assert fig is not None and fig2 is not None
     except ImportError:
         assert fig is None and fig2 is None
+
+
+@pytest.mark.parametrize("name", ["active_same_n10", "active_fixedN_n10"])
+def test_active_learning_cycles_match_reference(U, name):
+    """three add-one-image cycles (K_tilde grown by one column, eigh, warm start through `m`, `V`,
+    `init_kernel`) against the tracks of the REAL reference run through the same driver (oracle/gen_golden.py)."""
+    from active_flow import run_active_fixture
+    worst = run_active_fixture(U, name)
+    assert max(worst.values()) <= 1e-6, worst
