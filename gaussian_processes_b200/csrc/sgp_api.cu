@@ -52,6 +52,9 @@ struct sgp_handle {
   int i8_slices = -1;
   // slice count of the two products with the images (K_lin = X (UC)^T, D = X^T R): -1 = same as i8_slices
   int i8_slices_images = -1;
+  // slice counts of the two products that feed ONLY the gradient: D = X^T R (<= the images' count: it reads the leading
+  // slices of the persistent X^T digits) and Sigma2 = K^T diag(v) K (<= i8_slices); -1 = same as the parent option
+  int i8_slices_xtr = -1, i8_slices_sig2 = -1;
   DevBuf xq, xe, xtq, xte;  // int8 slices of the images (row-wise and transposed per slab) + their exponents
   bool oz_valid = false; int oz_S = 0; long oz_slab = 0;
   // cache key of the gathered copies
@@ -275,6 +278,10 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
   else if (n == "i8_slices") {
     if (value != -1 && value != 0 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices must be -1, 0 or 2..8");
     h->i8_slices = (int)value;
+  }
+  else if (n == "i8_slices_xtr" || n == "i8_slices_sig2") {
+    if (value != -1 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: " + n + " must be -1 or 2..8");
+    (n == "i8_slices_xtr" ? h->i8_slices_xtr : h->i8_slices_sig2) = (int)value;
   }
   else if (n == "i8_slices_images") {
     if (value != -1 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices_images must be -1 or 2..8");
@@ -678,6 +685,12 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const int ldkP = oz_ldk(p), ldkN = oz_ldk((int)slab);
   const bool chain_overlap = use_sep && h->overlap != 0;
   const bool tail_overlap = chain_overlap && ozS > 0;
+  const int ozX = ozI ? (h->i8_slices_xtr > 0 ? std::min(h->i8_slices_xtr, ozI) : ozI) : 0;      // D = X^T R
+  // Sigma2 enters only the gradient (through S2b), not lam_var: with everything on auto it takes 7 slices as well.
+  // Measured against the real reference (scripts/probe_gradslices.py, round 2): gradients <= 5e-11 of their
+  // cancellation scale on every fixture (8 slices: 3e-11).  X^T R at 6 slices would save another 0.33 ms but leaves
+  // only a 3x margin (3e-10 at m = 1000), so it keeps the images' count.
+  const int ozW = ozM ? (h->i8_slices_sig2 > 0 ? std::min(h->i8_slices_sig2, ozM) : (h->i8_slices < 0 ? std::min(7, ozM) : ozM)) : 0;
   const int oz_pairs = (std::max(ozM, ozI) + 1) / 2, oz_pairsI = (ozI + 1) / 2;
   const int nzO = ozS ? oz_split(p, m, (int)std::min(slab, N), ozI) : 1;
   const int nzK = ozM ? (proj ? oz_split(q, q, (int)std::min(slab, N), ozM, 1) : oz_split(m, m, (int)std::min(slab, N), ozM, 1)) : 1;
@@ -1158,9 +1171,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
         // both operands of the int8 product; only the tiles on and below the diagonal are computed
         const int ldk_s = oz_ldk((int)ns);
         oz_exps_from_colmax(cmaxW, acos_backward_blocks(ns), m, ldm, 1, rte, st);
-        cudaError_t e = oz_slice_cols(Ks, ldm, ns, m, ozM, rtq, ldk_s, rte, ozmx, st, v_s, true);
+        cudaError_t e = oz_slice_cols(Ks, ldm, ns, m, ozW, rtq, ldk_s, rte, ozmx, st, v_s, true);
         if (e != cudaSuccess) return e;
-        return oz_gemm(rtq, rte, m, rtq, rte, m, (int)ns, ldk_s, ozM, S2part, ldm, nzK, zS2, acc_flag, st, nullptr, 0, -1.0, 1);
+        return oz_gemm(rtq, rte, m, rtq, rte, m, (int)ns, ldk_s, ozW, S2part, ldm, nzK, zS2, acc_flag, st, nullptr, 0, -1.0, 1);
       }
       GemmArgs g6{};
       g6.A = Ks; g6.lda = ldm; g6.B = Ks; g6.ldb = ldm; g6.C = S2part; g6.ldc = ldm; g6.M = m; g6.N = m; g6.K = (int)ns;
@@ -1189,9 +1202,9 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
         const int ldk_s = oz_ldk((int)ns);
         if (oz_reslice) CU(oz_slice_cols(Xs, ldxs, ns, p, ozI, xtq_s, ldk_s, xte_s, ozmx, st));
         oz_exps_from_colmax(cmaxR, acos_backward_blocks(ns), m, ldm, 0, rte, st);
-        CU(oz_slice_cols(Ts, ldm, ns, m, ozI, rtq, ldk_s, rte, ozmx, st, nullptr, true));
+        CU(oz_slice_cols(Ts, ldm, ns, m, ozX, rtq, ldk_s, rte, ozmx, st, nullptr, true));
         mark(10);
-        CU(oz_gemm(xtq_s, xte_s, p, rtq, rte, m, (int)ns, ldk_s, ozI, Dpart, ldm, nzO, zD, acc_flag, st, nullptr,
+        CU(oz_gemm(xtq_s, xte_s, p, rtq, rte, m, (int)ns, ldk_s, ozX, Dpart, ldm, nzO, zD, acc_flag, st, nullptr,
                    (tail_overlap && last) ? num_sms() - 20 : 0));
       } else {
         GemmArgs g5{};

@@ -65,6 +65,8 @@ SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
  * 8 is the error class of a DGEMM and the default, 4 gives 27 bits per operand -- the fp32-class setting),
  * "i8_slices_images" (-1 = same as "i8_slices", 2..8 = slice count of the two products that contract with the
  * images, K_lin = X (UC)^T and D = X^T R; the m-space products keep "i8_slices"),
+ * "i8_slices_xtr" / "i8_slices_sig2" (-1 = default, 2..8: slice counts of the two products that feed only the gradient,
+ * D = X^T R (at most the images' count) and Sigma2 = K^T diag(v) K (default 7 when "i8_slices" is on auto)),
  * "support" (pixel set the cached copies / int8 slices of the images are built on: -1 = the receptive-field mask grown
  * by two pixels, kept while later masks stay inside it -- the mask is recomputed from theta in every closure
  * (utils.py:2030) and flips pixels during a line search; 0 = exactly the mask, as the reference gathers x[:, mask];

@@ -201,3 +201,20 @@ def test_benchmark_size_resident_protocol(name):
         assert abs(other["loglik"] - ref2["loglik"]) <= 1e-12 * abs(ref2["loglik"])
     finally:
         native.release_cache(0)
+
+
+@pytest.mark.parametrize("name", BIG_CASES)
+def test_benchmark_size_gradient_only_products_slice_counts(name):
+    """Slice counts of the two products that feed only the gradient.  Sigma2 = K^T diag(v) K at 7 slices (the default) and
+    at 8 both hold the 1e-9 bar with a wide margin; D = X^T R at 6 slices still passes but with a 3x margin only
+    (3e-10 at m = 1000, scripts/probe_gradslices.py) -- which is why it is an option and not the default."""
+    from gaussian_processes_b200 import native
+    for xtr, sig2 in ((-1, 8), (-1, 7), (6, 7)):
+        native.set_option(0, "i8_slices_xtr", xtr)
+        native.set_option(0, "i8_slices_sig2", sig2)
+        try:
+            fx, out = run(name, SLAB[name], 2, -1)
+        finally:
+            native.set_option(0, "i8_slices_xtr", -1)
+            native.set_option(0, "i8_slices_sig2", -1)
+        check(fx, out, tag=f"{name}/xtr{xtr}_sig{sig2}")
