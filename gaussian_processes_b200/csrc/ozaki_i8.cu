@@ -94,12 +94,13 @@ __device__ __forceinline__ void mma_i8(uint32_t d_tmem, uint64_t adesc, uint64_t
       ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
       : "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr));
+// 16 lanes x 16 columns in the accumulator-fragment layout (cute SM100_TMEM_LOAD_16dp256b2x): thread t of the warp
+// holds, for lane rows r = t/4 and r + 8 of the 16 addressed lanes and column pairs 2(t%4), 2(t%4)+1 (+8):
+//   v[0..1] = (r, 2c..2c+1)  v[2..3] = (r+8, 2c..)  v[4..5] = (r, 8+2c..)  v[6..7] = (r+8, 8+2c..)
+__device__ __forceinline__ void tmem_ld_frag16(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr));
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
@@ -138,6 +139,11 @@ __device__ __forceinline__ void issue_stage(uint64_t dA, uint64_t dB, uint32_t t
     }
   }
 }
+
+// SGP_OZ_DEBUG & 64: CTA 0 writes where its MMA-issuing thread and its first epilogue warp spent their cycles
+// [0] MMA: waiting for TMEM to be released  [1] MMA: waiting for operand stages  [2] MMA: whole loop
+// [3] epilogue: waiting for the tile's MMAs  [4] epilogue: TMEM drain  [5] epilogue: scale + store  [6] tiles of CTA 0
+__device__ double g_oz_prof[8];
 
 struct OzArgs {
   const int* ea; const int* eb;   // row exponents of A and of B
@@ -241,13 +247,19 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     // ===== MMA issuer (one thread) =====
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0, tphase = 0;
+      const bool prof = (a.dbg & 64) && blockIdx.x == 0;
+      long long c_te = 0, c_full = 0, c_all = prof ? clock64() : 0, ntile = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
         const int z = item / num_tiles;
         const int kb0 = z * a.kb_per_z, kb1 = min(nkb_all, kb0 + a.kb_per_z);
+        long long c0 = prof ? clock64() : 0;
         mbar_wait(bar_tempty, tphase ^ 1);
+        if (prof) { c_te += clock64() - c0; ++ntile; }
         tc_fence_after();
         for (int kb = kb0; kb < kb1; ++kb) {
+          c0 = prof ? clock64() : 0;
           mbar_wait(bar_full + 8 * stage, phase);
+          if (prof) c_full += clock64() - c0;
           tc_fence_after();
           const uint32_t sA = base + stage * (kOzStageA + kOzStageB), sB = sA + kOzStageA;
           if (!(a.dbg & 16)) {
@@ -269,105 +281,138 @@ oz_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         }
         tphase ^= 1;
       }
+      if (prof) { g_oz_prof[0] = (double)c_te; g_oz_prof[1] = (double)c_full; g_oz_prof[2] = (double)(clock64() - c_all); g_oz_prof[6] = (double)ntile; }
     }
   } else {
-    // ===== epilogue (8 warps): TMEM -> fp64 Horner sum over the diagonals in registers -> release TMEM ->
-    //       scale, transpose through shared memory, coalesced store (overlaps the next tile's MMAs) =====
+    // ===== epilogue (8 warps): TMEM -> fp64 Horner sum over the diagonals in registers -> release TMEM -> scale and
+    //       store (overlaps the next tile's MMAs).  The accumulators are read in the FRAGMENT layout (16x256b): a thread
+    //       holds 4 rows x (2 + 2) adjacent columns of each 16-column group, so the output goes out as 16-byte stores,
+    //       64 contiguous bytes per row and instruction, straight from registers -- no shared-memory transpose, no warp
+    //       barriers.  (Round 2: with the row-per-thread layout the staging round trips of the store phase competed with
+    //       the tensor core's operand reads for shared-memory bandwidth: MMAs and epilogue needed ~13.5 us per tile each
+    //       but 20 us together at K = 500, profiles/r2_ncu_summary.md.) =====
     const int q = warp & 3;                       // TMEM lane quarter this warp may read
     const int h = (warp - 2) >> 2;                // column half of the tile this warp owns
-    double* stg = reinterpret_cast<double*>(oz_smem_raw + (bars + 64 - raw)) + (warp - 2) * (32 * 16);
+    const int rq = lane >> 2, cq = lane & 3;
+    const bool mom = a.part1 != nullptr;
+    const bool vecC = ((a.ldc & 1) == 0) && ((reinterpret_cast<uintptr_t>(a.C) & 15) == 0) && ((a.zstride & 1) == 0);
+    const bool vecA = mom && ((a.ldaux & 1) == 0) && ((reinterpret_cast<uintptr_t>(a.aux) & 15) == 0);
     uint32_t tphase = 0;
+    const bool eprof = (a.dbg & 64) && blockIdx.x == 0 && warp == 2;
+    long long e_wait = 0, e_drain = 0, e_store = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
       const int tile = item % num_tiles;
       double* Cz = a.C + (long)(item / num_tiles) * a.zstride;
       int m0, n0;
       tile_origin(a.lower_only, tile, num_nt, m0, n0);
       n0 += 32 * h;
-      const long row = m0 + 32 * q + lane;
-      const double sa = row < a.M ? pow2d(a.ea[row] - 12) * a.alpha : 0.0;
+      const long long e0 = eprof ? clock64() : 0;
+      const long row0 = m0 + 32 * q + rq;         // this thread's rows: row0 + 8 * ai, ai = 0..3
+      double sa[4];
+#pragma unroll
+      for (int ai = 0; ai < 4; ++ai) sa[ai] = (row0 + 8 * ai < a.M) ? pow2d(a.ea[row0 + 8 * ai] - 12) * a.alpha : 0.0;
       mbar_wait(bar_tfull, tphase);
+      const long long e1 = eprof ? clock64() : 0;
       tc_fence_after();
       const uint32_t tl = tmem + ((uint32_t)(32 * q) << 16) + 32 * h;
-      double acc[2][16];
+      double acc[2][16];                          // [cg][4 * ai + 2 * j + e]: row row0 + 8 ai, column 8 j + 2 cq + e
 #pragma unroll
       for (int cg = 0; cg < 2; ++cg) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) acc[cg][j] = 0.0;
         if (a.dbg & 8) continue;
 #pragma unroll
-        for (int dh = 4; dh >= 0; dh -= 4) {      // diagonals dh+3 .. dh, four TMEM loads in flight
-          uint32_t v[4][16];
+        for (int dh = 6; dh >= 0; dh -= 2) {      // diagonals dh+1, dh: four TMEM loads (2 lane halves each) in flight
+          uint32_t v[2][2][8];
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            if (dh + 3 - i < S) tmem_ld16(tl + (uint32_t)(kOzBN * diag_pos(dh + 3 - i) + 16 * cg), v[i]);
+          for (int i = 0; i < 2; ++i)
+            if (dh + 1 - i < S) {
+#pragma unroll
+              for (int h2 = 0; h2 < 2; ++h2)
+                tmem_ld_frag16(tl + ((uint32_t)(16 * h2) << 16) + (uint32_t)(kOzBN * diag_pos(dh + 1 - i) + 16 * cg), v[i][h2]);
+            }
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            if (dh + 3 - i < S) {
+          for (int i = 0; i < 2; ++i)
+            if (dh + 1 - i < S) {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                // int32 -> double through the 2^52 + 2^31 offset (exact; keeps the conversion off the I2F path)
-                const double dv = __hiloint2double(0x43300000, (int)(v[i][j] ^ 0x80000000u)) - 4503601774854144.0;
-                acc[cg][j] = fma(acc[cg][j], 0.0078125, dv);
-              }
+              for (int h2 = 0; h2 < 2; ++h2)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                  // register k of the fragment: column block j = k >> 2, second row (+8) = (k >> 1) & 1, parity e = k & 1
+                  const int idx = 4 * (2 * h2 + ((k >> 1) & 1)) + 2 * (k >> 2) + (k & 1);
+                  // int32 -> double through the 2^52 + 2^31 offset (exact; keeps the conversion off the I2F path)
+                  const double dv = __hiloint2double(0x43300000, (int)(v[i][h2][k] ^ 0x80000000u)) - 4503601774854144.0;
+                  acc[cg][idx] = fma(acc[cg][idx], 0.0078125, dv);
+                }
             }
         }
       }
       tc_fence_before();
       mbar_arrive(bar_tempty);                    // TMEM is free: the next tile's MMAs may start
       tphase ^= 1;
-      // Phase 1 (thread = row): row scale, staging store.  Phase 2 (lane & 15 = column, two rows per pass): column
-      // scale, coalesced store of C; with the moments epilogue the product with aux (read coalesced) goes back into
-      // the staging tile.  Phase 3 (thread = row): this row's sum over the 16-column group.
-      const bool mom = a.part1 != nullptr;
-      const int cc = lane & 15;
+      const long long e2 = eprof ? clock64() : 0;
 #pragma unroll
       for (int cg = 0; cg < 2; ++cg) {
         if (a.dbg & 32) break;
         const int c0 = n0 + 16 * cg;
-        const int colc = c0 + cc;
-        const double sbc = colc < a.N ? pow2d(a.eb[colc]) : 0.0;
-        // aux is read one 4-row batch ahead of its use (first batch before the staging stores)
-        auto load_aux = [&](double (&dst)[4], int rb) {
+        double sb[2][2];
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const long grow = m0 + 32 * q + 2 * (rb + u) + (lane >> 4);
-            dst[u] = (grow < a.M && colc < a.N) ? __ldg(a.aux + grow * a.ldaux + colc) : 0.0;
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int col = c0 + 8 * j + 2 * cq + e;
+            sb[j][e] = col < a.N ? pow2d(a.eb[col]) : 0.0;
           }
-        };
-        double ax[4] = {0.0, 0.0, 0.0, 0.0}, axn[4] = {0.0, 0.0, 0.0, 0.0};
-        if (mom) load_aux(ax, 0);
-        __syncwarp();
+        double ax[16];
+        if (mom) {                                // aux (= K) for the whole group, requested before the stores
 #pragma unroll
-        for (int j = 0; j < 16; ++j) stg[lane * 16 + (j ^ cc)] = acc[cg][j] * sa;
-        __syncwarp();
-#pragma unroll 1
-        for (int rb = 0; rb < 16; rb += 4) {
-          if (mom && rb + 4 < 16) load_aux(axn, rb + 4);
+          for (int ai = 0; ai < 4; ++ai)
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int rr = 2 * (rb + u) + (lane >> 4);
-            const long grow = m0 + 32 * q + rr;
-            const int si = rr * 16 + (cc ^ (rr & 15));
-            const double val = stg[si] * sbc;
-            if (grow < a.M && colc < a.N) {
-              double* dst = Cz + grow * a.ldc + colc;
-              *dst = a.accumulate ? *dst + val : val;
+            for (int j = 0; j < 2; ++j) {
+              const long grow = row0 + 8 * ai;
+              const int col = c0 + 8 * j + 2 * cq;
+              const double* src = a.aux + grow * a.ldaux + col;
+              double x0 = 0.0, x1 = 0.0;
+              if (grow < a.M) {
+                if (vecA && col + 1 < a.N) { const double2 t = __ldg(reinterpret_cast<const double2*>(src)); x0 = t.x; x1 = t.y; }
+                else { if (col < a.N) x0 = __ldg(src); if (col + 1 < a.N) x1 = __ldg(src + 1); }
+              }
+              ax[4 * ai + 2 * j] = x0; ax[4 * ai + 2 * j + 1] = x1;
             }
-            if (mom) stg[si] = val * ax[u];
-          }
-#pragma unroll
-          for (int u = 0; u < 4; ++u) ax[u] = axn[u];
         }
-        if (mom) {
-          __syncwarp();
+#pragma unroll
+        for (int ai = 0; ai < 4; ++ai) {
+          const long grow = row0 + 8 * ai;
           double t1 = 0.0;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) t1 += stg[lane * 16 + (j ^ cc)];
-          if (row < a.M && c0 < a.N) a.part1[(long)(c0 >> 4) * a.ldpart + row] = t1;
+          for (int j = 0; j < 2; ++j) {
+            const int col = c0 + 8 * j + 2 * cq;
+            const double v0 = acc[cg][4 * ai + 2 * j] * sa[ai] * sb[j][0];
+            const double v1 = acc[cg][4 * ai + 2 * j + 1] * sa[ai] * sb[j][1];
+            if (grow < a.M) {
+              double* dst = Cz + grow * a.ldc + col;
+              if (vecC && col + 1 < a.N) {
+                double2* d2 = reinterpret_cast<double2*>(dst);
+                if (a.accumulate) { const double2 o = *d2; *d2 = make_double2(o.x + v0, o.y + v1); }
+                else *d2 = make_double2(v0, v1);
+              } else {
+                if (col < a.N) dst[0] = a.accumulate ? dst[0] + v0 : v0;
+                if (col + 1 < a.N) dst[1] = a.accumulate ? dst[1] + v1 : v1;
+              }
+            }
+            if (mom) t1 = fma(v1, ax[4 * ai + 2 * j + 1], fma(v0, ax[4 * ai + 2 * j], t1));
+          }
+          if (mom) {                              // row sum over the 16-column group: the 4 threads that share the row
+            t1 += __shfl_xor_sync(0xffffffffu, t1, 1);
+            t1 += __shfl_xor_sync(0xffffffffu, t1, 2);
+            if (cq == 0 && grow < a.M && c0 < a.N) a.part1[(long)(c0 >> 4) * a.ldpart + grow] = t1;
+          }
         }
       }
+      if (eprof) { const long long e3 = clock64(); e_wait += e1 - e0; e_drain += e2 - e1; e_store += e3 - e2; }
     }
+    if (eprof && lane == 0) { g_oz_prof[3] = (double)e_wait; g_oz_prof[4] = (double)e_drain; g_oz_prof[5] = (double)e_store; }
   }
 
   tc_fence_before();
@@ -617,6 +662,11 @@ int oz_split(long M, int N, int K, int S, int lower_only) {
     if (tiles >= 4 * num_sms()) break;   // plenty of tiles already: no split beyond what exactness needs
   }
   return best_nz;
+}
+
+double* oz_prof_ptr() {
+  double* p = nullptr;
+  return cudaGetSymbolAddress((void**)&p, g_oz_prof) == cudaSuccess ? p : nullptr;
 }
 
 cudaError_t oz_gemm(const int8_t* qa, const int* ea, long M, const int8_t* qb, const int* eb, int N, int K, int ldk,

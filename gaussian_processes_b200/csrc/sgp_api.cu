@@ -503,6 +503,16 @@ int sgp_spd_inverse(sgp_handle* h, const double* A, long lda, int n, double* Ain
 
 int sgp_debug_get(sgp_handle* h, const char* name, double* dst, long capacity, long* rows, long* cols, long* ld) {
   if (!h || !name) return SGP_E_ARG;
+  if (std::string(name) == "oz_prof") {   // cycle counters of the last int8 GEMM launch (SGP_OZ_DEBUG & 64)
+    if (rows) *rows = 1;
+    if (cols) *cols = 8;
+    if (ld) *ld = 8;
+    if (dst) {
+      if (capacity < 8 || !oz_prof_ptr()) return fail(h, SGP_E_ARG, "sgp_debug_get: oz_prof unavailable");
+      CU(cudaMemcpy(dst, oz_prof_ptr(), sizeof(double) * 8, cudaMemcpyDeviceToDevice));
+    }
+    return SGP_OK;
+  }
   auto it = h->dbg.find(name);
   if (it == h->dbg.end()) return fail(h, SGP_E_ARG, std::string("sgp_debug_get: unknown name ") + name);
   const DebugEntry& e = it->second;

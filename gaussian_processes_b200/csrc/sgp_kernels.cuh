@@ -218,6 +218,7 @@ void oz_exps_from_colmax(const double* part, int nblk, int cols, long ld, int sq
 // nz > 1: split-K, slice z of the k-blocks goes to C + z * zstride (oz_split picks nz; the effective count, which
 // oz_gemm never exceeds, is ceil(nkb / ceil(nkb / nz))); accumulate: C += instead of C =
 int oz_split(long M, int N, int K, int S, int lower_only = 0);
+double* oz_prof_ptr();   // 8 doubles written by CTA 0 of the last oz_gemm launch when SGP_OZ_DEBUG & 64 (cycle counts)
 inline int oz_eff_split(int K, int nz) { const int nkb = (K + 63) / 64, kbz = (nkb + nz - 1) / nz; return (nkb + kbz - 1) / kbz; }
 // optional moments epilogue: per 16-column group g, part1[g*ldpart + row] = sum_col C*aux, part2 = sum_col aux*colvec
 // row-sum epilogue: part1[g * ldpart + row] = sum over the 16-column group g of C[row][.] * aux[row][.]
