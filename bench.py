@@ -420,6 +420,35 @@ def secondary_metrics(native, dev, X, r, xt, Cm, mask, theta, B, ev_keep, m_b, V
         torch.cuda.empty_cache()
     except Exception as e:  # pragma: no cover
         out["active_loop"] = {"error": repr(e)}
+    # the shape of the reference's REAL data (one_cell_fit.ipynb cell 4 / cell 10: 108 x 108 images, 3160 of them, ntilde = 200,
+    # notebook theta -> p = 500 of 11 664 pixels, q < m).  BASELINE.md section 2 derives 0.17-0.21 s per closure evaluation
+    # (5-6 evaluations/s) for the reference on its authors' GPU from the notebook's stored timings -- context, not a
+    # published benchmark, so vs_baseline stays null.
+    try:
+        n_r, N_r, m_r = 108, 3160, 200
+        pr = synth.make_problem(N_r, n_r, m_r, cfg=108, theta=synth.THETA_NOTEBOOK)
+        Xr, rr_, xtr_ = pr.X.to(dev), pr.r.to(dev), pr.xtilde.to(dev)
+        Cr, mr = native.localker(pr.theta, n_r, dev)
+        ur = xtr_[:, mr].contiguous()
+        evr, evecr = torch.linalg.eigh(native.acosker(pr.theta["sigma_0"], ur, ur, Cr, True), UPLO="L")
+        kpr = evr > max(float(evr.max()) * 1e-4, 1e-4)
+        Br = evecr[:, kpr].contiguous()
+        mbr, Vbr = synth.make_variational_state(torch.diag(evr[kpr]).cpu(), 108)
+        mbr, Vbr = mbr.to(dev), Vbr.to(dev)
+        resr = {}
+        native.launch_count(dev.index or 0, reset=True)
+        tr_ = timed(lambda: resr.update(native.elbo_grad(Xr, rr_, xtr_, n_r, pr.theta, Br, mbr, Vbr, logA, lambda0)),
+                    reps=20, warm=3)
+        out["real_data_shape"] = {"what": "108x108 images, N=3160, ntilde=200, notebook theta (the reference's own data shape)",
+                                  "p": int(mr.sum()), "q": int(Br.shape[1]), "ms": tr_ * 1e3, "evals_per_sec": 1.0 / tr_,
+                                  "gpu_launches_per_eval": native.launch_count(dev.index or 0) / 23,
+                                  "flags": int(resr.get("flags", -1)),
+                                  "reference_context": "5-6 evaluations/s derived from the notebook's stored M-step timings on the "
+                                                       "authors' (unnamed) GPU, BASELINE.md section 2"}
+        del Xr, pr
+        native.release_cache(dev.index or 0)
+    except Exception as e:  # pragma: no cover
+        out["real_data_shape"] = {"error": repr(e)}
     # precision / throughput knob of the int8-slice products: S digits of 7 bits per fp64 operand (S = 8: DGEMM error
     # class, the default and the headline; S = 4: 27 bits, above fp32's 24).  Error = against the S = 8 result.
     try:
@@ -860,7 +889,8 @@ def run_ours(args):
             roof["library_gpu_baseline"] = {"error": repr(e)}
     # the driver's record keeps `roofline` and drops `secondary`: the figures north_star names live in both
     if secondary:
-        for k in ("logA_closure_pass", "estep_iteration", "mask_flip", "config3_size", "theta_variants", "active_loop"):
+        for k in ("logA_closure_pass", "estep_iteration", "mask_flip", "config3_size", "theta_variants", "active_loop",
+                  "real_data_shape"):
             if k in secondary:
                 roof[k] = secondary[k]
     if c5 is not None:
