@@ -449,6 +449,26 @@ def secondary_metrics(native, dev, X, r, xt, Cm, mask, theta, B, ev_keep, m_b, V
         native.release_cache(dev.index or 0)
     except Exception as e:  # pragma: no cover
         out["real_data_shape"] = {"error": repr(e)}
+    # fp32 mode (north_star: 1e-4 in fp32): float32 images through sgp_elbo_grad_f32 -- fp32-class engine (5 int8 slices for every
+    # product), fp64 elementwise passes; error against the fp64 evaluation of the same (fp32-valued) images
+    try:
+        X32, xt32 = X.float(), xt.float()
+        ref64 = native.elbo_grad(X32.double(), r, xt32.double(), n_side, theta, B, m_b, V_b, logA, lambda0)
+        res32 = {}
+        t32 = timed(lambda: res32.update(native.elbo_grad_f32(X32, r, xt32, n_side, theta, B, m_b, V_b, logA, lambda0)),
+                    reps=5, warm=3)
+        g64 = torch.tensor([ref64["grad"][k] for k in KEYS], dtype=torch.float64)
+        g32 = torch.tensor([res32["grad"][k] for k in KEYS], dtype=torch.float64)
+        out["fp32_mode"] = {"what": "float32 images, 5 int8 slices for every product (35-bit operands), fp64 elementwise",
+                            "ms": t32 * 1e3, "evals_per_sec": 1.0 / t32, "tolerance": 1e-4,
+                            "loglik_rel_err_vs_fp64": abs(res32["loglik"] - ref64["loglik"]) / abs(ref64["loglik"]),
+                            "grad_rel_err_vs_fp64": float(((g32 - g64).abs() / g64.abs()).max()),
+                            "flags": int(res32.get("flags", -1))}
+        del X32, xt32
+        native.release_cache(dev.index or 0)
+        torch.cuda.empty_cache()
+    except Exception as e:  # pragma: no cover
+        out["fp32_mode"] = {"error": repr(e)}
     # precision / throughput knob of the int8-slice products: S digits of 7 bits per fp64 operand (S = 8: DGEMM error
     # class, the default and the headline; S = 4: 27 bits, above fp32's 24).  Error = against the S = 8 result.
     try:
@@ -890,7 +910,7 @@ def run_ours(args):
     # the driver's record keeps `roofline` and drops `secondary`: the figures north_star names live in both
     if secondary:
         for k in ("logA_closure_pass", "estep_iteration", "mask_flip", "config3_size", "theta_variants", "active_loop",
-                  "real_data_shape"):
+                  "real_data_shape", "fp32_mode"):
             if k in secondary:
                 roof[k] = secondary[k]
     if c5 is not None:

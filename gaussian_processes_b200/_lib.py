@@ -59,6 +59,8 @@ SIGNATURES = {
     "sgp_gemm_i8emu": (_i, [_p, _i, _p, _l, _l, _p, _i, _l, _l, _i, _p, _l, _p]),
     "sgp_elbo_grad": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i, _dp, _dp, _dp, _p, _l, _i, _p, _p, _l, _d, _d,
                            _dp, _p, _p, _p, _dp, _p]),
+    "sgp_elbo_grad_f32": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i, _dp, _dp, _dp, _p, _l, _i, _p, _p, _l, _d, _d,
+                               _dp, _p, _p, _p, _dp, _p]),
     "sgp_elbo_grad_dev": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _i, _dp, _p, _l, _i, _p, _p, _l, _d, _d, _dp, _p, _p, _p, _p,
                                _p]),
     "sgp_elbo_grad_cells": (_i, [_p, _p, _l, _l, _p, _l, _i, _i, _i, _p, _dp, _p, C.POINTER(_l), _ip, _p, _p,

@@ -558,6 +558,9 @@ struct ClosureIn {
   // stream -- the caller reads / reduces them in stream order (cells loop, device-side all-reduce of the image shards)
   double* out_dev = nullptr;
   int force_support = -2;           // -2: the handle's option; otherwise overrides it for this call
+  // float32 images (sgp_elbo_grad_f32): X / U above then hold the same addresses (cache key only) and every read of the
+  // images goes through the fp64 working copy that the gather makes once per image set
+  const float* X32 = nullptr; const float* U32 = nullptr;
   bool exchange = false;            // image shard of a larger evaluation: reduce the result with the peers (sgp_comm_*)
 };
 
@@ -717,8 +720,8 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   }
 
   // ---- gathered / aligned copies of the images (cached across calls while the mask is unchanged) --
-  const bool direct_X = !streaming && full_mask && (in.ldx % 2 == 0) && ((uintptr_t)in.X % 16 == 0);
-  const bool direct_U = full_mask && (in.ldu % 2 == 0) && ((uintptr_t)in.U % 16 == 0);
+  const bool direct_X = !streaming && !in.X32 && full_mask && (in.ldx % 2 == 0) && ((uintptr_t)in.X % 16 == 0);
+  const bool direct_U = !in.U32 && full_mask && (in.ldu % 2 == 0) && ((uintptr_t)in.U % 16 == 0);
   bool regather = !h->cache_valid || h->cache_token != h->image_token || h->cache_mask != support || h->cache_X != in.X ||
                   h->cache_N != N || h->cache_ldx != in.ldx || h->cache_U != in.U || h->cache_m != m ||
                   h->cache_ldu != in.ldu;
@@ -925,8 +928,14 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   if (streaming && !in.first_copy_issued) CU(issue_copy(0));
 
   if (regather) {
-    if (!direct_X && !streaming) gather_cols(in.X, in.ldx, N, d_idx, p, (double*)Xg, ldp, st);
-    if (!direct_U) gather_cols(in.U, in.ldu, m, d_idx, p, (double*)Ug, ldp, st);
+    if (!direct_X && !streaming) {
+      if (in.X32) gather_cols_f32(in.X32, in.ldx, N, d_idx, p, (double*)Xg, ldp, st);
+      else gather_cols(in.X, in.ldx, N, d_idx, p, (double*)Xg, ldp, st);
+    }
+    if (!direct_U) {
+      if (in.U32) gather_cols_f32(in.U32, in.ldu, m, d_idx, p, (double*)Ug, ldp, st);
+      else gather_cols(in.U, in.ldu, m, d_idx, p, (double*)Ug, ldp, st);
+    }
     h->cache_mask = support; h->cache_X = in.X; h->cache_N = N; h->cache_ldx = in.ldx;
     h->cache_U = in.U; h->cache_m = m; h->cache_ldu = in.ldu; h->cache_token = h->image_token;
   }
@@ -1443,8 +1452,10 @@ int run_closure_same(sgp_handle* h, const ClosureIn& in, double* out_host, cudaS
   }
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
   CU(cudaMemsetAsync(h->d_scal, 0, sizeof(double) * kNumSlots, st));
-  gather_cols(in.X, in.ldx, m, d_idx, p, Xg, ldp, st);
-  gather_cols(in.U, in.ldu, m, d_idx, p, Ug, ldp, st);
+  if (in.X32) gather_cols_f32(in.X32, in.ldx, m, d_idx, p, Xg, ldp, st);
+  else gather_cols(in.X, in.ldx, m, d_idx, p, Xg, ldp, st);
+  if (in.U32) gather_cols_f32(in.U32, in.ldu, m, d_idx, p, Ug, ldp, st);
+  else gather_cols(in.U, in.ldu, m, d_idx, p, Ug, ldp, st);
   copy_mat(in.B, in.ldb, m, q, Bw, ldq, st);
   copy_mat(in.V, in.ldv, q, q, Vw, ldq, st);
   build_C(C, ldp, p, d_gx, d_gy, th, nullptr, 0, st);
@@ -1555,6 +1566,33 @@ int sgp_elbo_grad(sgp_handle* h, const double* X, long ldx, const double* r, lon
   in.lam_m = lam_m; in.lam_var = lam_var; in.f = f;
   in.exchange = true;       // no-op unless sgp_comm_import made this handle one shard of an image-sharded evaluation
   return run_closure(h, in, out_host, (cudaStream_t)stream);
+}
+
+int sgp_elbo_grad_f32(sgp_handle* h, const float* X, long ldx, const double* r, long N, const float* xtilde, long ldu,
+                      int m, int n_px, const double* theta, const double* lo, const double* hi, const double* B, long ldb,
+                      int q, const double* m_b, const double* V_b, long ldv, double logA, double lambda0,
+                      const double* logdetV_host, double* lam_m, double* lam_var, double* f, double* out_host,
+                      void* stream) {
+  if (!h || !X || !r || !xtilde || !theta || !B || !m_b || !V_b)
+    return fail(h, SGP_E_ARG, "sgp_elbo_grad_f32: null argument");
+  if (lo && hi)
+    for (int k = 0; k < 6; ++k)
+      if (!(lo[k] <= theta[k] && theta[k] <= hi[k]))
+        return fail(h, SGP_E_BOUNDS, "sgp_elbo_grad_f32: theta[" + std::to_string(k) + "] outside its limits");
+  ClosureIn in{};
+  in.X32 = X; in.U32 = xtilde;
+  in.X = reinterpret_cast<const double*>(X); in.U = reinterpret_cast<const double*>(xtilde);   // cache key only
+  in.ldx = ldx; in.r = r; in.N = N; in.ldu = ldu; in.m = m; in.n_px = n_px;
+  in.theta = theta; in.B = B; in.ldb = ldb; in.q = q; in.m_b = m_b; in.V = V_b; in.ldv = ldv;
+  in.logA = logA; in.lambda0 = lambda0; in.logdetV_host = logdetV_host;
+  in.lam_m = lam_m; in.lam_var = lam_var; in.f = f;
+  in.exchange = true;
+  // fp32-class engine unless the caller chose one: 5 int8 slices (35 bits per operand >= the 24 of the inputs)
+  const int keep = h->i8_slices, keep_i = h->i8_slices_images, keep_w = h->i8_slices_sig2;
+  if (h->i8_slices < 0) { h->i8_slices = 5; h->i8_slices_images = 5; h->i8_slices_sig2 = 5; }
+  const int rc = run_closure(h, in, out_host, (cudaStream_t)stream);
+  h->i8_slices = keep; h->i8_slices_images = keep_i; h->i8_slices_sig2 = keep_w;
+  return rc;
 }
 
 int sgp_elbo_grad_dev(sgp_handle* h, const double* X, long ldx, const double* r, long N, const double* xtilde, long ldu,

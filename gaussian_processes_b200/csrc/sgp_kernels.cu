@@ -75,6 +75,25 @@ __global__ void gather_cols_kernel(const double* __restrict__ X, long ldx, long 
     out[row * ldo + c] = (c < p) ? X[row * ldx + idx[c]] : 0.0;
 }
 
+// same gather from FLOAT32 images (sgp_elbo_grad_f32): the fp64 working copy is made here, once per image set
+__global__ void gather_cols_f32_kernel(const float* __restrict__ X, long ldx, long nrows, const int* __restrict__ idx,
+                                       int p, double* __restrict__ out, long ldo) {
+  const long row = blockIdx.y;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < ldo; c += gridDim.x * blockDim.x)
+    out[row * ldo + c] = (c < p) ? (double)X[row * ldx + idx[c]] : 0.0;
+}
+
+void gather_cols_f32(const float* X, long ldx, long nrows, const int* idx, int p, double* out, long ldo,
+                     cudaStream_t st) {
+  if (nrows <= 0) return;
+  const int gx = cdiv(ldo, 256) > 8 ? 8 : (int)cdiv(ldo, 256);
+  for (long r0 = 0; r0 < nrows; r0 += 65535) {
+    const long nr = (nrows - r0) < 65535 ? (nrows - r0) : 65535;
+    note_launch();
+    gather_cols_f32_kernel<<<dim3(gx, (unsigned)nr), 256, 0, st>>>(X + r0 * ldx, ldx, nr, idx, p, out + r0 * ldo, ldo);
+  }
+}
+
 void gather_cols(const double* X, long ldx, long nrows, const int* idx, int p, double* out, long ldo,
                  cudaStream_t st) {
   if (nrows <= 0) return;

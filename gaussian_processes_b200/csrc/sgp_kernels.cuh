@@ -46,6 +46,8 @@ void build_C(double* C, long ldc, int p, const double* gx, const double* gy, con
 // out[i][c] = X[i][idx[c]] (c < p), 0 for p <= c < ldo
 void gather_cols(const double* X, long ldx, long nrows, const int* idx, int p, double* out, long ldo,
                  cudaStream_t st);
+void gather_cols_f32(const float* X, long ldx, long nrows, const int* idx, int p, double* out, long ldo,
+                     cudaStream_t st);     // same, from float32 images
 
 // s[i] = s02 + sum_t part[t*ldpart + i] ; nrm[i] = sqrt(s[i])
 void norms_finalize(const double* part, long ldpart, int nparts, long n, double s02, double* s, double* nrm,

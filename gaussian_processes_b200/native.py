@@ -325,6 +325,45 @@ def elbo_grad(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int,
     return res
 
 
+def elbo_grad_f32(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
+                  m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float, lims=None,
+                  logdetV: Optional[float] = None, want_moments: bool = False, kl_weight: float = 1.0,
+                  same: Optional[bool] = None) -> Dict:
+    """fp32 mode (sgp_elbo_grad_f32): the images X / xtilde are float32 CUDA tensors, everything else fp64.  The library
+    keeps its own fp64 working copy + int8 slices of the images; products run on the fp32-class engine (5 int8 slices)
+    unless option "i8_slices" says otherwise.  Same result dict as elbo_grad."""
+    for t in (X, xtilde):
+        if not t.is_cuda or t.dtype != torch.float32:
+            raise TypeError("elbo_grad_f32 expects float32 CUDA images")
+    _need_cuda(r, B, m_b, V_b)
+    _dev = X.device.index if X.device.index is not None else torch.cuda.current_device()
+    set_option(_dev, "kl_weight", kl_weight)
+    set_option(_dev, "square_is_same", 0.0 if same is False else 1.0)
+    X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
+    r, m_b = r.contiguous(), m_b.contiguous()
+    N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]
+    lam_m = lam_var = f = None
+    if want_moments:
+        lam_m = torch.empty((N,), dtype=torch.float64, device=X.device)
+        lam_var, f = torch.empty_like(lam_m), torch.empty_like(lam_m)
+    lo = hi = None
+    if lims is not None:
+        lo = (C.c_double * 6)(*[float(lims[0][k]) for k in THETA_KEYS])
+        hi = (C.c_double * 6)(*[float(lims[1][k]) for k in THETA_KEYS])
+    ldv_val = C.c_double(logdetV if logdetV is not None else 0.0)
+    out = (C.c_double * 16)()
+    h = _h(X)
+    h.bind_images(X, xtilde)
+    h.check(lib.sgp_elbo_grad_f32(h.ptr, _ptr(X), _ld(X), _ptr(r), N, _ptr(xtilde), _ld(xtilde), int(m), int(n_px),
+                                  theta_array(theta), lo, hi, _ptr(B), _ld(B), int(q), _ptr(m_b), _ptr(V_b), _ld(V_b),
+                                  float(logA), float(lambda0), C.byref(ldv_val) if logdetV is not None else None,
+                                  _ptr(lam_m), _ptr(lam_var), _ptr(f), out, _stream(X.device)))
+    res = result_dict(list(out))
+    if want_moments:
+        res.update(lam_m=lam_m, lam_var=lam_var, f=f)
+    return res
+
+
 def elbo_grad_dev(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
                   m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float,
                   logdetV: Optional[float] = None, kl_weight: float = 1.0,

@@ -210,6 +210,17 @@ SGP_API int sgp_elbo_grad(sgp_handle* h, const double* X, long ldx, const double
                   double lambda0, const double* logdetV_host, double* lam_m, double* lam_var, double* f,
                   double* out_host, void* stream);
 
+/* fp32 mode (north_star: "1e-4 in fp32"; the reference itself is fp64 only, utils.py:31-33).  Same evaluation with the
+ * images `X` / `xtilde` in FLOAT32 (device, row-major, ld in floats).  The library makes its fp64 working copy (and
+ * the int8 slices) of them once per image set; with "i8_slices" on auto the products run on 5 int8 slices (35 bits per
+ * operand -- the fp32-class engine; the slice threshold N >= 4096 still applies), the elementwise passes and the
+ * quadratic forms stay fp64.  Results agree with the fp64 evaluation of the same (fp32-valued) images to 1e-4 or
+ * better (tests/test_gpu_f32.py); everything else (r, B, m_b, V_b, outputs) is fp64 as in sgp_elbo_grad.            */
+SGP_API int sgp_elbo_grad_f32(sgp_handle* h, const float* X, long ldx, const double* r, long N, const float* xtilde,
+                              long ldu, int m, int n_px, const double* theta, const double* lo, const double* hi,
+                              const double* B, long ldb, int q, const double* m_b, const double* V_b, long ldv,
+                              double logA, double lambda0, const double* logdetV_host, double* lam_m, double* lam_var,
+                              double* f, double* out_host, void* stream);
 /* Same evaluation, ASYNCHRONOUS: the 16 result doubles are written to `out_dev` (device memory) and the call returns
  * once everything is enqueued on `stream`, without a host synchronisation.  For callers that post-process the result
  * on the device in stream order: an image-sharded evaluation all-reduces out_dev[0..8] across the GPUs and reads it back
