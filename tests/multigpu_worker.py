@@ -87,6 +87,38 @@ def main():
     rep["peer_memory_identical_on_all_ranks"] = bool(torch.equal(lo, hi))
     rep["local_after_close_differs"] = after["loglik"] != res["peer_memory"]["loglik"]
     ok = ok and rep["peer_memory_identical_on_all_ranks"] and rep["local_after_close_differs"]
+    # ---- the whole EM fit, SPMD over the image shards (utils.varGP with sharded.enable): tracks must equal the fit of
+    #      ALL the images on one GPU.  M-step closures reduce inside the evaluation's last kernel (peer memory), the
+    #      E-step's g / G and the logA-closure sums go through NCCL.
+    if os.environ.get("MG_FIT", "1") != "0":
+        import contextlib
+        import io
+        with contextlib.redirect_stdout(io.StringIO()):
+            from gaussian_processes_b200 import utils as U
+
+            def fit_kw():
+                return dict(fit_parameters=dict(ntilde=m, maxiter=3, nEstep=2, nMstep=3, nFparamstep=3, kernfun="acosker",
+                                                cellid=0, n_px_side=n, display_hyper=False),
+                            xtilde=xt, hyperparams_tuple=(synth.theta_tensors(prob.theta, device=dev, requires_grad=True),
+                                                          dict(synth.THETA_LIMS_LO), dict(synth.THETA_LIMS_HI)),
+                            f_params={"logA": torch.tensor(prob.logA, device=dev),
+                                      "lambda0": torch.tensor(prob.lambda0, device=dev)})
+            single, e1 = U.varGP(Xall, rall, **fit_kw())                  # every rank: all images, no sharding
+            sgf = sharded.enable(device=dev)
+            sgf.enable_peer_exchange()
+            shard, e2 = U.varGP(X, r, **fit_kw())
+            sgf.disable_peer_exchange()
+            sharded.disable()
+        fit_ok = not e1["is_error"] and not e2["is_error"]
+        errs = {}
+        for key in ("logmarginal", "loglikelihood", "KL"):
+            a_, b_ = shard["values_track"]["loss_track"][key], single["values_track"]["loss_track"][key]
+            errs[key] = float((a_ - b_).abs().max() / b_.abs().max())
+        ta = torch.stack([shard["values_track"]["theta_track"][k] for k in native.THETA_KEYS])
+        tb = torch.stack([single["values_track"]["theta_track"][k] for k in native.THETA_KEYS])
+        errs["theta"] = float((ta - tb).abs().max() / tb.abs().max())
+        rep["sharded_fit_vs_single_gpu"] = errs
+        ok = ok and fit_ok and max(errs.values()) < 1e-9
     okt = torch.tensor([1.0 if ok else 0.0], device=dev)
     dist.all_reduce(okt, op=dist.ReduceOp.MIN)
     if rank == 0:
