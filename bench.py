@@ -810,7 +810,7 @@ def run_ours(args):
                     "gemm_XtR": gemm_nm + " (D = X^T R)", "gemm_XtR_i8": gemm_nm + " (D = X^T R)",
                     "gemm_KtvK": "gemm_f64_kernel<64,128,MN-major,MN-major,kscale,split-K> (K^T diag(v) K)"}
     traffic = None
-    tf = os.path.join(ROOT, "profiles", "r1_top_kernel_traffic.json")
+    tf = os.path.join(ROOT, "profiles", "r2_top_kernel_traffic.json")
     tj = json.load(open(tf)) if os.path.exists(tf) else {}
     if i8:
         # dominant kernel: oz_gemm_kernel, launched for both N x p x m products of every slab.  Algorithmic work of a
