@@ -1,0 +1,102 @@
+"""GPU: edge shapes of the fused closure against the CPU oracle (pinned to the real reference): one training image, a
+receptive-field mask of a handful of pixels, more inducing images than pixels in the mask, tiny ntilde == nt, an image
+count that is not a multiple of any tile, and theta exactly on its limits."""
+import pytest
+import torch
+
+import oracle.spatial_gp_oracle as orc
+from gaussian_processes_b200 import synth
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9
+D = torch.device("cuda:0")
+
+
+def run(N, n, m, theta0, dtheta=None, cfg=60, i8=-1, slab=0, xt_rows=None):
+    from gaussian_processes_b200 import native
+    prob = synth.make_problem(max(N, m), n, m, cfg=cfg, theta=theta0)
+    X, r = prob.X[:N], prob.r[:N]
+    xt = prob.xtilde if xt_rows is None else prob.X[xt_rows]
+    C, mask = orc.build_C(theta0, n)
+    um = xt[:, mask]
+    B, Kt_b, _ = orc.eig_projection(orc.arccos_kernel(theta0, um, um, C))
+    m_b, V_b = synth.make_variational_state(Kt_b, cfg)
+    theta = dict(theta0)
+    theta.update(dtheta or {})
+    ref = orc.elbo_and_grad(theta, X, r, xt, n, B, m_b, V_b, prob.logA, prob.lambda0, return_moments=True)
+    native.set_option(0, "i8_slices", i8)
+    native.set_slab_rows(0, slab)
+    native.invalidate_cache(0)
+    try:
+        out = native.elbo_grad(X.to(D), r.to(D), xt.to(D), n, theta, B.to(D), m_b.to(D), V_b.to(D), prob.logA,
+                               prob.lambda0, want_moments=True, lims=(synth.THETA_LIMS_LO, synth.THETA_LIMS_HI))
+    finally:
+        native.set_option(0, "i8_slices", -1)
+        native.set_slab_rows(0, 0)
+    assert out["flags"] == 0 and out["p"] == ref["p"], (out["flags"], out["p"], ref["p"])
+    assert abs(out["loglik"] - ref["loglik"]) <= RTOL * max(abs(ref["loglik"]), 1e-300)
+    assert abs(out["KL"] - ref["KL"]) <= RTOL * abs(ref["KL"])
+    for k in orc.KEYS:
+        sc = max(abs(ref["dloglik"][k]), abs(ref["dKL"][k]), 1e-300)
+        assert abs(out["grad"][k] - ref["grad"][k]) <= RTOL * sc, (k, out["grad"][k], ref["grad"][k], sc)
+    assert torch.allclose(out["lam_m"].cpu(), ref["lam_m"], rtol=RTOL, atol=1e-12)
+    assert torch.allclose(out["lam_var"].cpu(), ref["lam_var"], rtol=RTOL, atol=1e-10)
+    return out, ref, B.shape[1]
+
+
+def test_single_training_image():
+    run(1, 8, 6, synth.THETA_DENSE, {"eps_0x": 0.02})
+
+
+def test_two_inducing_images():
+    run(37, 8, 2, synth.THETA_DENSE, {"Amp": 0.3})
+
+
+@pytest.mark.parametrize("i8", [0, 8])
+def test_mask_of_a_few_pixels(i8):
+    """A very narrow receptive field: p = 5 pixels of 144 (and m = 30 > p: K_tilde is far from full rank in the pixel
+    space, the arc-cosine nonlinearity keeps q well above p)."""
+    th = {**synth.THETA_NOTEBOOK, "-2log2beta": 6.9, "-log2rho2": 5.0, "eps_0x": 0.09, "eps_0y": -0.09}
+    out, ref, q = run(333, 12, 30, th, {"eps_0x": 0.094}, i8=i8, slab=128)
+    assert out["p"] <= 9 and q <= 30
+
+
+def test_empty_mask_is_refused():
+    """No pixel reaches alpha >= 1e-3: the reference would index with an empty mask and fail inside the kernel function;
+    the library refuses the evaluation with SGP_E_ARG and says why."""
+    from gaussian_processes_b200 import _lib, native
+    th = {**synth.THETA_NOTEBOOK, "-2log2beta": 6.9, "-log2rho2": 5.0, "eps_0x": 0.004, "eps_0y": -0.09}
+    assert int(native.mask_host(th, 12).sum()) == 0
+    prob = synth.make_problem(64, 12, 8, cfg=62, theta=synth.theta_localised(12))
+    e8 = torch.eye(8, dtype=torch.float64, device=D)
+    with pytest.raises(_lib.SgpError) as e:
+        native.elbo_grad(prob.X.to(D), prob.r.to(D), prob.xtilde.to(D), 12, th, e8, e8[0].contiguous(), e8, 0.0, 0.0)
+    assert "empty" in str(e.value)
+
+
+def test_tiny_ntilde_equals_nt():
+    run(5, 8, 5, synth.theta_localised(8), {"sigma_0": 0.1})
+
+
+def test_ragged_image_count_multi_slab():
+    """N = 1001 with 128-row slabs: 7 full slabs and a ragged one of 105 rows, int8 engine forced."""
+    run(1001, 12, 40, synth.theta_localised(12), {"eps_0y": 0.01}, i8=8, slab=128)
+
+
+def test_theta_on_its_limits_is_inside():
+    """The reference's bounds check is inclusive (`lo <= value <= hi`, U:866): eps_0 = 1 and Amp at a tiny positive value
+    are evaluated, not rejected."""
+    th = dict(synth.THETA_DENSE)
+    th.update({"eps_0x": 1.0, "eps_0y": -1.0})
+    run(200, 8, 10, th)
+
+
+def test_more_inducing_images_than_the_backward_kernel_supports_is_refused():
+    from gaussian_processes_b200 import _lib, native
+    prob = synth.make_problem(2100, 8, 2100, cfg=61, theta=synth.THETA_DENSE)
+    X = prob.X.to(D)
+    B = torch.eye(2100, dtype=torch.float64, device=D)[:, :8].contiguous()
+    with pytest.raises(_lib.SgpError) as e:
+        native.elbo_grad(X[:50], prob.r[:50].to(D), X, 8, prob.theta, B, torch.zeros(8, dtype=torch.float64, device=D),
+                         torch.eye(8, dtype=torch.float64, device=D), 0.0, 0.0)
+    assert e.value.code == _lib.SGP_E_UNSUPPORTED
