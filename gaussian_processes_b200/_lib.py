@@ -47,6 +47,7 @@ SIGNATURES = {
     "sgp_acosker": (_i, [_p, _p, _l, _l, _p, _l, _l, _i, _p, _l, _d, _p, _l, _i, _p]),
     "sgp_acosker_kvec": (_i, [_p, _p, _l, _l, _p, _l, _l, _i, _p, _l, _d, _p, _l, _i, _p, _p]),
     "sgp_acosker_diag": (_i, [_p, _p, _l, _l, _i, _p, _l, _d, _p, _p]),
+    "sgp_acosker_known": (_i, [_p, _p, _l, _l, _p, _p, _l, _l, _i, _p, _l, _d, _p, _l, _p]),
     "sgp_lambda_moments": (_i, [_p, _p, _l, _p, _l, _p, _l, _i, _p, _p, _l, _p, _p, _p]),
     "sgp_fparam_eval": (_i, [_p, _p, _p, _p, _l, _d, _d, _p, _dp, _p]),
     "sgp_loglik_sums": (_i, [_p, _p, _p, _p, _p, _l, _d, _dp, _p]),

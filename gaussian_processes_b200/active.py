@@ -78,7 +78,12 @@ def grow_model(U, model: dict, X_in_use: torch.Tensor, xtilde_updated: torch.Ten
     else:
         if fk['K'].shape[0] != nt:
             raise ValueError('the training set changed: the cached K does not match it')
-        kcol = U.acosker(theta, X_in_use[:, mask], x_new, C=C, dC=None, diag=False)   # (nt, 1)
+        Xm = X_in_use if bool(mask.all()) else X_in_use[:, mask]
+        known = getattr(U, 'acosker_known_norms', None)       # ours: the images' norms are the model's Kvec (same theta)
+        if known is not None and Xm.is_cuda:
+            kcol = known(theta, Xm, fk['Kvec'], x_new, C)                              # (nt, 1), one pass over X
+        else:
+            kcol = U.acosker(theta, Xm, x_new, C=C, dC=None, diag=False)
         K = torch.cat((fk['K'], kcol), dim=1)
         Kvec = fk['Kvec']                                                         # same images, same theta
     tick('new_kernel_columns', t0)

@@ -1914,6 +1914,64 @@ int sgp_acosker_kvec(sgp_handle* h, const double* x1, long n1, long ld1, const d
   return acosker_impl(h, x1, n1, ld1, x2, n2, ld2, p, C, ldc, sigma_0, K, ldk, symm, Kvec, stream);
 }
 
+// New columns of K against images whose squared norms are already known: kvec1_i = x1_i^T C x1_i + sigma_0^2 is what
+// acosker(x1, diag=True) returned at this theta (the model's 'Kvec').  The n1 x p x p product x1 C -- all of the cost of
+// sgp_acosker when n2 is a handful of images -- is not repeated: K_lin = x1 (x2 C)^T + sigma_0^2 moves C to the n2 side
+// (x2 C is n2 x p x p), the arc-cosine map is the same epilogue.  One pass over x1: 8 n1 p bytes.
+int sgp_acosker_known(sgp_handle* h, const double* x1, long n1, long ld1, const double* kvec1, const double* x2, long n2,
+                      long ld2, int p, const double* C, long ldc, double sigma_0, double* K, long ldk, void* stream) {
+  if (!h || !x1 || !kvec1 || !x2 || !C || !K) return fail(h, SGP_E_ARG, "sgp_acosker_known: null argument");
+  if (n1 <= 0 || n2 <= 0 || p <= 0 || ldk < n2) return fail(h, SGP_E_ARG, "sgp_acosker_known: bad shape");
+  int rc = ensure_ready(h); if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long ldp = rup(p, 16), ldn2 = rup(n2, 16);
+  const long slab = std::min<long>(h->slab_rows, rup(n1, 128));
+  const int ntp_s = (p + 63) / 64;
+  const long ldpart = rup(std::max<long>(slab, n2), 16);
+  const double s02 = sigma_0 * sigma_0;
+  size_t need = 0;
+  auto acc = [&](size_t nelem) { need = ((need + 255) & ~size_t(255)) + nelem * sizeof(double); };
+  acc((size_t)p * ldp); acc((size_t)n2 * ldp); acc((size_t)n2 * ldp); acc((size_t)n2 * ldp); acc((size_t)slab * ldp);
+  acc((size_t)ntp_s * ldpart); acc(n2); acc(n2); acc(slab); acc(slab); acc((size_t)slab * ldn2); acc((size_t)slab * ldn2);
+  need += 4096;
+  CU(h->arena.reserve(need));
+  Arena ar(h->arena.p, h->arena.bytes);
+  double* Cw = ar.take<double>((size_t)p * ldp);
+  double* x2w = ar.take<double>((size_t)n2 * ldp);
+  double* Z2 = ar.take<double>((size_t)n2 * ldp);
+  double* Wt = ar.take<double>((size_t)n2 * ldp);
+  double* x1w = ar.take<double>((size_t)slab * ldp);
+  double* part = ar.take<double>((size_t)ntp_s * ldpart);
+  double* t2 = ar.take<double>(n2); double* X2 = ar.take<double>(n2);
+  double* s1 = ar.take<double>(slab); double* X1 = ar.take<double>(slab);
+  double* Kw = ar.take<double>((size_t)slab * ldn2); double* cosw = ar.take<double>((size_t)slab * ldn2);
+  const double* Cc = C; long ldcc = ldc;
+  if (!aligned2(C, ldc)) { copy_mat(C, ldc, p, p, Cw, ldp, st); Cc = Cw; ldcc = ldp; }
+  const double* x2c = x2; long ld2c = ld2;
+  if (!aligned2(x2, ld2)) { copy_mat(x2, ld2, (int)n2, p, x2w, ldp, st); x2c = x2w; ld2c = ldp; }
+  {
+    GemmArgs g{};                                                            // X2^2 = rowdot(x2 C, x2) + sigma_0^2  (U:979)
+    g.A = x2c; g.lda = ld2c; g.B = Cc; g.ldb = ldcc; g.C = Z2; g.ldc = ldp; g.M = (int)n2; g.N = p; g.K = p;
+    g.aux = x2c; g.ldaux = ld2c; g.part1 = part; g.ldpart = ldpart;
+    CU(gemm(st, 0, 1, kRowdot, true, 1, g));
+    norms_finalize(part, ldpart, ntp_s, n2, s02, t2, X2, st);
+  }
+  CU(mm(st, 0, 0, x2c, ld2c, Cc, ldcc, Wt, ldp, (int)n2, p, p));             // x1^T C x2 = x1 . (x2 C^T)
+  for (long i0 = 0; i0 < n1; i0 += slab) {
+    const long ns = std::min(slab, n1 - i0);
+    const double* xs = x1 + i0 * ld1; long lds = ld1;
+    if (!aligned2(xs, ld1)) { copy_mat(xs, ld1, (int)ns, p, x1w, ldp, st); xs = x1w; lds = ldp; }
+    norms_finalize(kvec1 + i0, ldpart, 1, ns, 0.0, s1, X1, st);             // X1 = sqrt(kvec1)  (U:978)
+    GemmArgs a{};
+    a.A = xs; a.lda = lds; a.B = Wt; a.ldb = ldp; a.C = Kw; a.ldc = ldn2; a.M = (int)ns; a.N = (int)n2; a.K = p;
+    a.rowvec = X1; a.colvec = X2; a.C2 = cosw; a.s02 = s02;
+    CU(gemm(st, 0, 0, kAcos, false, 1, a));                                  // U:982-990
+    copy_mat(Kw, ldn2, (int)ns, (int)n2, K + i0 * ldk, ldk, st);
+  }
+  CU(cudaGetLastError());
+  return SGP_OK;
+}
+
 int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, const double* C, long ldc,
                      double sigma_0, double* Kvec, void* stream) {
   if (!h || !x1 || !C || !Kvec) return fail(h, SGP_E_ARG, "sgp_acosker_diag: null argument");

@@ -114,6 +114,21 @@ def acosker_kvec(sigma_0: float, x1: torch.Tensor, x2: torch.Tensor, Cm: torch.T
     return K, Kvec
 
 
+def acosker_known(sigma_0: float, x1: torch.Tensor, kvec1: torch.Tensor, x2: torch.Tensor, Cm: torch.Tensor) -> torch.Tensor:
+    """acosker(x1, x2) for images whose Kvec at this theta is known (sgp_acosker_known): one pass over x1."""
+    _need_cuda(x1, kvec1, x2, Cm)
+    x1, x2, Cm, kvec1 = _c(x1), _c(x2), _c(Cm), kvec1.contiguous()
+    n1, p = x1.shape
+    n2 = x2.shape[0]
+    if kvec1.shape != (n1,) or kvec1.dtype != torch.float64:
+        raise ValueError("acosker_known: kvec1 must be a float64 vector with one entry per row of x1")
+    K = torch.empty((n1, n2), dtype=torch.float64, device=x1.device)
+    h = _h(x1)
+    h.check(lib.sgp_acosker_known(h.ptr, _ptr(x1), n1, _ld(x1), _ptr(kvec1), _ptr(x2), n2, _ld(x2), int(p), _ptr(Cm),
+                                  _ld(Cm), float(sigma_0), _ptr(K), n2, _stream(x1.device)))
+    return K
+
+
 def acosker_diag(sigma_0: float, x1: torch.Tensor, Cm: torch.Tensor) -> torch.Tensor:
     _need_cuda(x1, Cm)
     x1, Cm = _c(x1), _c(Cm)

@@ -264,6 +264,13 @@ def acosker(theta, x1, x2=None, C=None, dC=None, diag=False):
     return K, dK
 
 
+def acosker_known_norms(theta, x1, Kvec1, x2, C):
+    """`acosker(theta, x1, x2, C=C)` when `Kvec1 = acosker(theta, x1, C=C, diag=True)` is at hand (a fitted model keeps it
+    as 'Kvec'): the x1 C product, which is all of the cost for a handful of new images x2, is not repeated.  No
+    counterpart in the reference (it recomputes; one_cell_active_training.ipynb cell 17) -- same values."""
+    return native.acosker_known(_fl(theta['sigma_0']), x1, Kvec1, x2, C)
+
+
 # ---- a5: lambda_moments (U:1072-1124) ---------------------------------------------------------------------
 @torch.no_grad()
 def lambda_moments(x, K_tilde, KKtilde_inv, Kvec, K, C, m, V, theta, kernfun=None, dK=None, dK_tilde=None,

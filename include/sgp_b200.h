@@ -116,6 +116,13 @@ SGP_API int sgp_acosker(sgp_handle* h, const double* x1, long n1, long ld1, cons
 SGP_API int sgp_acosker_kvec(sgp_handle* h, const double* x1, long n1, long ld1, const double* x2, long n2, long ld2,
                      int p, const double* C, long ldc, double sigma_0, double* K, long ldk, int symmetrize,
                      double* Kvec, void* stream);
+/* acosker(theta, x1, x2, C) for images x1 whose Kvec (= x1_i^T C x1_i + sigma_0^2, the `diag=True` result at THIS theta:
+ * the fitted model's 'Kvec') is already known: the x1 C product is not repeated, one pass over x1.  The active-learning
+ * cycle's "one new column of K" (one_cell_active_training.ipynb cell 17; same values as sgp_acosker, never symmetrised:
+ * n1 != n2 there).                                                                                                 */
+SGP_API int sgp_acosker_known(sgp_handle* h, const double* x1, long n1, long ld1, const double* kvec1, const double* x2,
+                      long n2, long ld2, int p, const double* C, long ldc, double sigma_0, double* K, long ldk,
+                      void* stream);
 /* ---- a3: acosker(theta, x1, x2=None, C, diag=True)  utils.py:1027-1030 : Kvec_i = x_i^T C x_i + sigma_0^2     */
 SGP_API int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, const double* C, long ldc,
                      double sigma_0, double* Kvec, void* stream);

@@ -165,6 +165,28 @@ def test_acosker_image_sized_rows_int8_path(nat, n1, n2, p, sym_c):
     assert torch.equal(K2, K) and rel_err(Kvec2.cpu().numpy(), Kvec.cpu().numpy()) < 1e-14
 
 
+@pytest.mark.parametrize("n1,n2,p", [(50, 1, 37), (3000, 1, 400), (9000, 3, 131), (70000, 2, 64)])
+def test_acosker_known_norms_new_columns(nat, n1, n2, p):
+    """sgp_acosker_known: new columns of K for images whose Kvec is at hand (the active-learning cycle's one new column):
+    the oracle's acosker on the same inputs, and sgp_acosker itself; odd leading dimensions and several slabs included."""
+    import oracle.spatial_gp_oracle as orc
+    g = torch.Generator().manual_seed(n1 + p)
+    x1 = torch.randn(n1, p, generator=g, dtype=torch.float64)
+    x2 = torch.randn(n2, p, generator=g, dtype=torch.float64)
+    A = torch.randn(p, p, generator=g, dtype=torch.float64)
+    C = A @ A.T / p + 0.1 * torch.eye(p, dtype=torch.float64)
+    d = dev()
+    Kvec = nat.acosker_diag(0.7, x1.to(d), C.to(d))
+    K = nat.acosker_known(0.7, x1.to(d), Kvec, x2.to(d), C.to(d))
+    assert K.shape == (n1, n2)
+    if n1 <= 9000:
+        assert rel_err(K.cpu().numpy(), orc.arccos_kernel({"sigma_0": 0.7}, x1, x2, C).numpy()) < 1e-11
+    Kfull = nat.acosker(0.7, x1.to(d), x2.to(d), C.to(d), False)
+    assert rel_err(K.cpu().numpy(), Kfull.cpu().numpy()) < 1e-12
+    with pytest.raises(ValueError):
+        nat.acosker_known(0.7, x1.to(d), Kvec[:-1], x2.to(d), C.to(d))
+
+
 @pytest.mark.parametrize("name", ["closure_dense_n8", "closure_local_n12", "closure_rankdef_n10", "closure_c1_dense"])
 def test_moments_estep_fparams_against_reference(nat, name):
     import oracle.spatial_gp_oracle as orc

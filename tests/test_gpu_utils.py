@@ -251,7 +251,7 @@ def test_plot_entry_points_exist(U):
 
 @pytest.mark.parametrize("name", ["active_same_n10", "active_fixedN_n10"])
 def test_active_learning_cycles_match_reference_on_gpu(U, name):
-    """The active-learning cycle on the CUDA library: incremental K_tilde / K columns through sgp_acosker on one image,
+    """The active-learning cycle on the CUDA library: incremental K_tilde / K columns (sgp_acosker on one image; sgp_acosker_known for the column of K),
     eigh, warm start through init_kernel; ntilde == nt runs the fused a = B closure.  Tracks of every warm-started fit
     against the REAL reference's (driven through the same gaussian_processes_b200.active.grow_model)."""
     from active_flow import run_active_fixture
