@@ -8,6 +8,7 @@
 #include <cstring>
 #include <map>
 #include <string>
+#include <initializer_list>
 #include <vector>
 
 #include "gemm_f64.cuh"
@@ -249,8 +250,10 @@ int sgp_destroy(sgp_handle* h) {
       if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]);
       if (h->ev_used[i]) cudaEventDestroy(h->ev_used[i]);
     }
-    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
-    if (h->compute_stream) cudaStreamDestroy(h->compute_stream);
+    if (h->ev_small) cudaEventDestroy(h->ev_small);
+    for (cudaEvent_t e : {h->ev_fork, h->ev_join, h->ev_chain_fork, h->ev_chain_join}) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->prof_ev) if (e) cudaEventDestroy(e);
+    for (cudaStream_t s : {h->copy_stream, h->compute_stream, h->side_stream, h->chain_stream}) if (s) cudaStreamDestroy(s);
   }
   delete h;
   return SGP_OK;

@@ -1,0 +1,100 @@
+"""GPU: handle lifecycle and re-entrancy (SURVEY 8b "Threading / device" and "Ownership" rows).
+
+* one notebook variant (one_cell_active_training.ipynb cell 19) calls acosker / lambda_moments / compute_loglikelihood from
+  a second Python thread while varGP runs: entry points are re-entrant per handle, handles are per (thread, device);
+* the .so owns only scratch: creating, using and destroying handles returns every byte to the driver."""
+import threading
+
+import pytest
+import torch
+
+from gaussian_processes_b200 import synth
+
+pytestmark = pytest.mark.gpu
+D = torch.device("cuda:0")
+
+
+def problem(N=6000, n=20, m=120, cfg=70):
+    from gaussian_processes_b200 import native
+    prob = synth.make_problem(N, n, m, cfg=cfg, theta=synth.theta_localised(n))
+    X, r, xt = prob.X.to(D), prob.r.to(D), prob.xtilde.to(D)
+    Cm, mask = native.localker(prob.theta, n, D)
+    um = xt[:, mask].contiguous()
+    Kt = native.acosker(prob.theta["sigma_0"], um, um, Cm, True)
+    ev, evec = torch.linalg.eigh(Kt, UPLO="L")
+    keep = ev > max(float(ev.max()) * 1e-4, 1e-4)
+    B = evec[:, keep].contiguous()
+    m_b, V_b = synth.make_variational_state(torch.diag(ev[keep]).cpu(), cfg)
+    return prob, X, r, xt, Cm, mask, B, m_b.to(D), V_b.to(D)
+
+
+def test_second_thread_calls_function_level_entry_points_while_the_closure_runs():
+    from gaussian_processes_b200 import _lib, native
+    prob, X, r, xt, Cm, mask, B, m_b, V_b = problem()
+    xm, um = X[:, mask].contiguous(), xt[:, mask].contiguous()
+    s0 = prob.theta["sigma_0"]
+
+    def closure(k):
+        th = dict(prob.theta)
+        th["eps_0x"] += 0.01 * (k % 3)
+        return native.elbo_grad(X, r, xt, prob.n_px_side, th, B, m_b, V_b, prob.logA, prob.lambda0)
+
+    def side(k):
+        K, Kvec = native.acosker_kvec(s0, xm[: 2000 + 100 * (k % 3)], um, Cm, False)
+        return float(K.sum()), float(Kvec.sum())
+    ref_main = [closure(k) for k in range(3)]
+    ref_side = [side(k) for k in range(3)]
+    torch.cuda.synchronize()
+    errors, got_side, handles = [], [], []
+
+    def worker():
+        try:
+            torch.cuda.set_device(0)
+            handles.append(_lib.handle_for(0))
+            for k in range(30):
+                got_side.append((k % 3, side(k)))
+        except Exception as e:  # pragma: no cover
+            errors.append(e)
+    t = threading.Thread(target=worker)
+    t.start()
+    got_main = [(k % 3, closure(k)) for k in range(30)]
+    t.join()
+    assert not errors, errors
+    assert handles[0] is not _lib.handle_for(0)            # its own handle: own scratch, own caches
+    for k, o in got_main:                                  # deterministic kernels: the interleaving changes nothing
+        assert o["loglik"] == ref_main[k]["loglik"] and o["KL"] == ref_main[k]["KL"] and o["flags"] == 0
+        assert all(o["grad"][key] == ref_main[k]["grad"][key] for key in o["grad"])
+    for k, v in got_side:
+        assert v == ref_side[k]
+
+
+def test_handles_return_their_memory():
+    """create -> evaluate (work areas, cached image copies, int8 slices) -> destroy, 12 times: free device memory comes back
+    to where it started, and a destroyed handle's caches are not inherited by the next one."""
+    from gaussian_processes_b200 import _lib
+    from gaussian_processes_b200.native import THETA_KEYS  # noqa: F401  (package import builds the default handle first)
+    prob, X, r, xt, Cm, mask, B, m_b, V_b = problem(N=9000, n=20, m=100, cfg=71)
+    import ctypes as C
+    lib = _lib.lib
+    theta = (C.c_double * 6)(*[float(prob.theta[k]) for k in THETA_KEYS])
+    q = B.shape[1]
+
+    def one_cycle():
+        h = _lib.Handle(0)
+        out = (C.c_double * 16)()
+        rc = lib.sgp_elbo_grad(h.ptr, C.c_void_p(X.data_ptr()), X.stride(0), C.c_void_p(r.data_ptr()), X.shape[0],
+                               C.c_void_p(xt.data_ptr()), xt.stride(0), xt.shape[0], prob.n_px_side, theta, None, None,
+                               C.c_void_p(B.data_ptr()), B.stride(0), q, C.c_void_p(m_b.data_ptr()),
+                               C.c_void_p(V_b.data_ptr()), V_b.stride(0), float(prob.logA), float(prob.lambda0), None,
+                               None, None, None, out, C.c_void_p(torch.cuda.current_stream(D).cuda_stream))
+        h.check(rc)
+        h.close()
+        return out[0]
+    first = one_cycle()
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info(0)
+    vals = [one_cycle() for _ in range(12)]
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info(0)
+    assert all(v == first for v in vals)
+    assert free0 - free1 < (8 << 20), (free0, free1)        # nothing accumulates (driver bookkeeping aside)
