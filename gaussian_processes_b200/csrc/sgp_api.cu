@@ -27,10 +27,25 @@ struct DevBuf {
     p = nullptr; bytes = 0;
     cudaError_t e = cudaMalloc(&p, need);
     if (e == cudaSuccess) bytes = need;
+    if (e == cudaSuccess && poison_new()) e = cudaMemset(p, 0xFF, need);   // SGP_POISON: fresh memory is not zero either
     return e;
   }
+  static bool poison_new() { static const bool on = getenv("SGP_POISON") && atoi(getenv("SGP_POISON")) != 0; return on; }
   void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
 };
+
+// SGP_POISON=1 (testing only): every entry point fills its work area with 0xFF bytes (NaN as a double, -1 as a digit or
+// an exponent) before using it, so a kernel that reads scratch it did not write in THIS call -- stale values from an
+// earlier call, unwritten padding multiplied by zero -- shows up as NaN / wrong results in the parity tests.
+const int g_poison = getenv("SGP_POISON") ? atoi(getenv("SGP_POISON")) : 0;
+#define RESERVE_ARENA(need)                                                                   \
+  do {                                                                                        \
+    CU(h->arena.reserve(need));                                                               \
+    if (g_poison) {   /* synchronised: uploads on the copy stream must not race with the fill */ \
+      CU(cudaMemsetAsync(h->arena.p, 0xFF, h->arena.bytes, st));                              \
+      CU(cudaStreamSynchronize(st));                                                          \
+    }                                                                                         \
+  } while (0)
 
 struct DebugEntry { const double* ptr; long rows, cols, ld; };
 
@@ -355,7 +370,7 @@ int sgp_localker(sgp_handle* h, const double* theta, int n_px, double* C, long l
   std::vector<uint8_t> mask; std::vector<int> idx; std::vector<double> gx, gy;
   const int p = compute_mask(theta, n_px, mask, idx, gx, gy);
   if (ldc < p) return fail(h, SGP_E_ARG, "sgp_localker: ldc < p");
-  CU(h->arena.reserve((size_t)(2 * p + 64) * sizeof(double)));
+  RESERVE_ARENA((size_t)(2 * p + 64) * sizeof(double));
   double* dgx = (double*)h->arena.p; double* dgy = dgx + p;
   CU(cudaMemcpyAsync(dgx, gx.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
   CU(cudaMemcpyAsync(dgy, gy.data(), sizeof(double) * p, cudaMemcpyHostToDevice, st));
@@ -389,7 +404,7 @@ static int oz_mm(sgp_handle* h, cudaStream_t st, int al, int bl, const double* A
   acc(oz_slice_bytes(M, K, S)); acc(oz_slice_bytes(N, K, S));
   acc((size_t)M * sizeof(int)); acc((size_t)N * sizeof(int)); acc((size_t)std::max<long>(M, N) * 8);
   need += 4096;
-  CU(h->arena.reserve(need));
+  RESERVE_ARENA(need);
   Arena ar(h->arena.p, h->arena.bytes);
   int8_t* qa = ar.take<int8_t>(oz_slice_bytes(M, K, S));
   int8_t* qb = ar.take<int8_t>(oz_slice_bytes(N, K, S));
@@ -437,7 +452,7 @@ int sgp_gemm_i8emu(sgp_handle* h, int layout, const double* A, long M, long lda,
   acc((size_t)M * sizeof(int)); acc((size_t)N * sizeof(int)); acc((size_t)std::max<long>(M, N) * 8);
   acc(nz > 1 ? (size_t)nz * zs * sizeof(double) : 8);
   need += 4096;
-  CU(h->arena.reserve(need));
+  RESERVE_ARENA(need);
   Arena ar(h->arena.p, h->arena.bytes);
   int8_t* qa = ar.take<int8_t>(oz_slice_bytes(M, (int)K, slices));
   int8_t* qb = ar.take<int8_t>(oz_slice_bytes(N, (int)K, slices));
@@ -468,7 +483,7 @@ int sgp_cholesky(sgp_handle* h, double* A, long ld, int n, int* flags_host, void
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
-  CU(h->arena.reserve((size_t)chol_winv_elems(n) * sizeof(double) + 4096));
+  RESERVE_ARENA((size_t)chol_winv_elems(n) * sizeof(double) + 4096);
   CU(cholesky_lower(A, ld, n, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, (double*)h->arena.p, st));
   if (flags_host) {
     CU(cudaMemcpyAsync(flags_host, h->d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -483,7 +498,7 @@ int sgp_spd_inverse(sgp_handle* h, const double* A, long lda, int n, double* Ain
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const long ld = rup(n, 16);
-  CU(h->arena.reserve((size_t)(3 * ld * ld + 64 * ld + chol_winv_elems(n) + 1024) * sizeof(double)));
+  RESERVE_ARENA((size_t)(3 * ld * ld + 64 * ld + chol_winv_elems(n) + 1024) * sizeof(double));
   Arena ar(h->arena.p, h->arena.bytes);
   double* L = ar.take<double>(ld * ld);
   double* X = ar.take<double>(ld * ld);
@@ -785,7 +800,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     acc(slab / 2 + 8); acc(slab / 2 + 8); acc(m); acc(q); acc(q); acc(q);
   }
   need += 4096;
-  CU(h->arena.reserve(need));
+  RESERVE_ARENA(need);
   Arena ar(h->arena.p, h->arena.bytes);
 
   double* d_gx = ar.take<double>(p); double* d_gy = ar.take<double>(p);
@@ -1409,7 +1424,7 @@ int run_closure_same(sgp_handle* h, const ClosureIn& in, double* out_host, cudaS
   acc((size_t)p * ldp); acc((size_t)p * ldp); acc((size_t)p * 5);
   for (int i = 0; i < 3; ++i) acc(m);
   need += 4096;
-  CU(h->arena.reserve(need));
+  RESERVE_ARENA(need);
   Arena ar(h->arena.p, h->arena.bytes);
   double* d_gx = ar.take<double>(p); double* d_gy = ar.take<double>(p);
   int* d_idx = (int*)ar.take<double>((size_t)(p + 1) / 2 + 8);
@@ -1829,7 +1844,7 @@ static int acosker_impl(sgp_handle* h, const double* x1, long n1, long ld1, cons
     acc(oz_slice_bytes(n2, p, ozS) / 8 + 16); acc(slab / 2 + 8); acc(p); acc(n2); acc(p);
   }
   need += 4096;
-  CU(h->arena.reserve(need));
+  RESERVE_ARENA(need);
   Arena ar(h->arena.p, h->arena.bytes);
   double* Cw = ar.take<double>((size_t)p * ldp);
   double* x2w = ar.take<double>((size_t)n2 * ldp);
@@ -1937,7 +1952,7 @@ int sgp_acosker_known(sgp_handle* h, const double* x1, long n1, long ld1, const 
   acc((size_t)p * ldp); acc((size_t)n2 * ldp); acc((size_t)n2 * ldp); acc((size_t)n2 * ldp); acc((size_t)slab * ldp);
   acc((size_t)ntp_s * ldpart); acc(n2); acc(n2); acc(slab); acc(slab); acc((size_t)slab * ldn2); acc((size_t)slab * ldn2);
   need += 4096;
-  CU(h->arena.reserve(need));
+  RESERVE_ARENA(need);
   Arena ar(h->arena.p, h->arena.bytes);
   double* Cw = ar.take<double>((size_t)p * ldp);
   double* x2w = ar.take<double>((size_t)n2 * ldp);
@@ -1990,7 +2005,7 @@ int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, 
   acc((size_t)p * ldp); acc((size_t)slab * ldp); acc((size_t)slab * ldp); acc((size_t)ntp * ldpart); acc(slab);
   if (ozS) { acc(oz_slice_bytes(slab, p, ozS) / 8 + 16); acc(oz_slice_bytes(p, p, ozS) / 8 + 16); acc(slab / 2 + 8); acc(p); acc(p); }
   need += 4096;
-  CU(h->arena.reserve(need));
+  RESERVE_ARENA(need);
   Arena ar(h->arena.p, h->arena.bytes);
   double* Cw = ar.take<double>((size_t)p * ldp);
   double* x1w = ar.take<double>((size_t)slab * ldp);
@@ -2055,7 +2070,7 @@ int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K
   acc((size_t)q * ldq); acc((size_t)slab * ldq); acc((size_t)slab * ldq); acc((size_t)ntq * ldpart * 2);
   if (ozS) { acc(oz_slice_bytes(slab, q, ozS) / 8 + 16); acc(oz_slice_bytes(q, q, ozS) / 8 + 16); acc(slab / 2 + 8); acc(q); }
   need += 4096;
-  CU(h->arena.reserve(need));
+  RESERVE_ARENA(need);
   Arena ar(h->arena.p, h->arena.bytes);
   double* Vw = ar.take<double>((size_t)q * ldq);
   double* aw = ar.take<double>((size_t)slab * ldq);
@@ -2097,7 +2112,7 @@ int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, c
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = fparam_blocks(N);
-  CU(h->arena.reserve((size_t)nb * 8 * sizeof(double) + 4096));
+  RESERVE_ARENA((size_t)nb * 8 * sizeof(double) + 4096);
   double* bp = (double*)h->arena.p;
   const double A = std::exp(logA);
   fparam_pass(lam_m, lam_var, r, N, A, lambda0, f, bp, h->d_ticket, h->d_scal + kSlotAux0, st);
@@ -2120,7 +2135,7 @@ int sgp_loglik_sums(sgp_handle* h, const double* r, const double* f, const doubl
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = fparam_blocks(N);
-  CU(h->arena.reserve((size_t)nb * 8 * sizeof(double) + 4096));
+  RESERVE_ARENA((size_t)nb * 8 * sizeof(double) + 4096);
   double* bp = (double*)h->arena.p;
   loglik_sums_pass(r, f, lam_m, lam_var, N, std::exp(logA), bp, h->d_ticket, h->d_scal + kSlotAux0, st);
   CU(cudaGetLastError());
@@ -2148,7 +2163,7 @@ int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, c
   acc((size_t)slab * ldq); acc((size_t)nz * zs); acc((size_t)ncb * ldq); acc((size_t)q * ldq);
   if (ozS) { acc((size_t)((ozS + 1) / 2) * q * ldkN / 8 + 16); acc(q); acc(q); }
   need += 4096;
-  CU(h->arena.reserve(need));
+  RESERVE_ARENA(need);
   Arena ar(h->arena.p, h->arena.bytes);
   double* aw = ar.take<double>((size_t)slab * ldq);
   double* Gpart = ar.take<double>((size_t)nz * zs);

@@ -98,3 +98,19 @@ def test_handles_return_their_memory():
     free1, _ = torch.cuda.mem_get_info(0)
     assert all(v == first for v in vals)
     assert free0 - free1 < (8 << 20), (free0, free1)        # nothing accumulates (driver bookkeeping aside)
+
+
+def test_no_kernel_depends_on_stale_scratch():
+    """SGP_POISON=1 fills every work area (and every fresh allocation) with 0xFF bytes -- NaN as a double, -1 as an int8
+    digit or an exponent -- before each entry point uses it.  The closure / edge / cells parity tests must pass unchanged in
+    a process started that way: no kernel reads scratch it did not write in the same call (compute-sanitizer's initcheck
+    is not available on the GPU pool; this is the library's own version of it)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, SGP_POISON="1")
+    files = ["tests/test_gpu_edges.py", "tests/test_gpu_closure.py", "tests/test_gpu_cells.py", "tests/test_gpu_f32.py"]
+    res = subprocess.run([sys.executable, "-m", "pytest", *files, "-m", "gpu", "-x", "-q", "-p", "no:cacheprovider"],
+                         cwd=root, env=env, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-2000:]
