@@ -621,6 +621,10 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   const long N = in.N; const int m = in.m, q = in.q, n = in.n_px; const long P = (long)n * n;
   if (N <= 0 || m <= 0 || q <= 0 || q > m) return fail(h, SGP_E_ARG, "sgp_elbo_grad: bad sizes");
   if (m > kBwdMaxCols) return fail(h, SGP_E_UNSUPPORTED, "sgp_elbo_grad: m > 2048 not supported");
+  // a row of images must hold n_px^2 pixels: a smaller leading dimension means the caller's n_px does not match its images
+  // (the reference fails on the shape mismatch in x[:, mask], U:2031); reading on would run past the buffers
+  if (n <= 0 || in.ldx < P || in.ldu < P || in.ldb < q || in.ldv < q)
+    return fail(h, SGP_E_ARG, "sgp_elbo_grad: leading dimension smaller than the row length (n_px^2 pixels per image)");
   // ntilde == nt: the reference's a = B branch (U:2032, U:2068) -- the configuration its active-learning notebook
   // always runs (m == N: every image in use is an inducing image).  Small problem, own routine.
   if (N == m && h->square_is_same) {

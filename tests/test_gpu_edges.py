@@ -100,3 +100,69 @@ def test_more_inducing_images_than_the_backward_kernel_supports_is_refused():
         native.elbo_grad(X[:50], prob.r[:50].to(D), X, 8, prob.theta, B, torch.zeros(8, dtype=torch.float64, device=D),
                          torch.eye(8, dtype=torch.float64, device=D), 0.0, 0.0)
     assert e.value.code == _lib.SGP_E_UNSUPPORTED
+
+
+def _state(prob, theta0, n):
+    C, mask = orc.build_C(theta0, n)
+    um = prob.xtilde[:, mask]
+    B, Kt_b, _ = orc.eig_projection(orc.arccos_kernel(theta0, um, um, C))
+    m_b, V_b = synth.make_variational_state(Kt_b, 63)
+    return B.to(D), m_b.to(D), V_b.to(D)
+
+
+@pytest.mark.parametrize("N,slab,i8", [(700, 0, 0), (9000, 4096, 8)])
+def test_nan_in_the_images_is_flagged_and_does_not_outlive_the_call(N, slab, i8):
+    """One NaN pixel: the evaluation comes back (no hang, no exception from the library) with the NaN status bit -- the
+    reference raises on NaN in f_mean (U:1923), utils maps the bit to that -- and the NEXT call, on clean images of the same
+    shape at the same address, is exactly what a fresh process computes: nothing of the poisoned call survives in the
+    cached copies, the int8 slices or the work areas."""
+    from gaussian_processes_b200 import _lib, native
+    n, m = 12, 40
+    th = synth.theta_localised(n)
+    prob = synth.make_problem(N, n, m, cfg=63, theta=th)
+    B, m_b, V_b = _state(prob, th, n)
+    X, r, xt = prob.X.to(D), prob.r.to(D), prob.xtilde.to(D)
+    native.set_option(0, "i8_slices", i8)
+    native.set_slab_rows(0, slab)
+    try:
+        native.invalidate_cache(0)
+        clean = native.elbo_grad(X, r, xt, n, th, B, m_b, V_b, prob.logA, prob.lambda0)
+        assert clean["flags"] == 0
+        mask = native.mask_host(th, n)
+        px = int(torch.nonzero(mask)[3])
+        X[N // 2, px] = float("nan")
+        bad = native.elbo_grad(X, r, xt, n, th, B, m_b, V_b, prob.logA, prob.lambda0)
+        assert bad["flags"] & _lib.FLAG_NAN
+        X[N // 2, px] = prob.X[N // 2, px]
+        again = native.elbo_grad(X, r, xt, n, th, B, m_b, V_b, prob.logA, prob.lambda0)
+        assert again["flags"] == 0 and again["loglik"] == clean["loglik"] and again["KL"] == clean["KL"]
+        assert all(again["grad"][k] == clean["grad"][k] for k in clean["grad"])
+    finally:
+        native.set_option(0, "i8_slices", -1)
+        native.set_slab_rows(0, 0)
+        native.invalidate_cache(0)
+
+
+def test_the_handle_survives_refused_calls():
+    """Out-of-bounds theta (the reference's ValueError, U:865-867), an empty mask and a bad argument are refused with their
+    codes; the same handle then evaluates correctly."""
+    from gaussian_processes_b200 import _lib, native
+    n, m, N = 12, 30, 500
+    th = synth.theta_localised(n)
+    prob = synth.make_problem(N, n, m, cfg=64, theta=th)
+    B, m_b, V_b = _state(prob, th, n)
+    X, r, xt = prob.X.to(D), prob.r.to(D), prob.xtilde.to(D)
+    lims = (synth.THETA_LIMS_LO, synth.THETA_LIMS_HI)
+    ref = native.elbo_grad(X, r, xt, n, th, B, m_b, V_b, prob.logA, prob.lambda0, lims=lims)
+    out_of_bounds = dict(th, eps_0x=1.5)
+    with pytest.raises(_lib.SgpError) as e:
+        native.elbo_grad(X, r, xt, n, out_of_bounds, B, m_b, V_b, prob.logA, prob.lambda0, lims=lims)
+    assert e.value.code == _lib.SGP_E_BOUNDS
+    empty = {**synth.THETA_NOTEBOOK, "-2log2beta": 6.9, "-log2rho2": 5.0, "eps_0x": 0.004, "eps_0y": -0.09}
+    with pytest.raises(_lib.SgpError):
+        native.elbo_grad(X, r, xt, n, empty, B, m_b, V_b, prob.logA, prob.lambda0)
+    with pytest.raises(_lib.SgpError):
+        native.elbo_grad(X, r, xt, n + 1, th, B, m_b, V_b, prob.logA, prob.lambda0)       # P != n_px^2
+    out = native.elbo_grad(X, r, xt, n, th, B, m_b, V_b, prob.logA, prob.lambda0, lims=lims)
+    assert out["flags"] == 0 and out["loglik"] == ref["loglik"]
+    assert all(out["grad"][k] == ref["grad"][k] for k in ref["grad"])
