@@ -365,6 +365,7 @@ int sgp_mask_host(const double* theta, int n_px, uint8_t* mask_host, int* p_out)
 int sgp_localker(sgp_handle* h, const double* theta, int n_px, double* C, long ldc, double* dC, long dc_stride,
                  void* stream) {
   if (!h || !theta || !C) return fail(h, SGP_E_ARG, "sgp_localker: null argument");
+  if (n_px <= 0) return fail(h, SGP_E_ARG, "sgp_localker: n_px must be positive");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   std::vector<uint8_t> mask; std::vector<int> idx; std::vector<double> gx, gy;
@@ -423,6 +424,10 @@ static int oz_mm(sgp_handle* h, cudaStream_t st, int al, int bl, const double* A
 int sgp_gemm_f64(sgp_handle* h, int al, int bl, const double* A, long lda, const double* B, long ldb, double* C,
                  long ldc, int M, int N, int K, double alpha, int accumulate, int small_tile, void* stream) {
   if (!h || !A || !B || !C) return fail(h, SGP_E_ARG, "sgp_gemm_f64: null argument");
+  if (M <= 0 || N <= 0 || K <= 0) return fail(h, SGP_E_ARG, "sgp_gemm_f64: sizes must be positive");
+  // layouts: A is M x K (al == 0) or K x M (al == 1); B is N x K (bl == 0) or K x N (bl == 1)
+  if (lda < (al ? M : K) || ldb < (bl ? N : K) || ldc < N)
+    return fail(h, SGP_E_ARG, "sgp_gemm_f64: leading dimension smaller than the row length");
   int rc = ensure_ready(h); if (rc) return rc;
   // image-sized products (K_b = K B, a = K_b K_tilde_b^-1: utils.py:1693-1694) go to the int8 tensor-core path
   if (al == 0 && !small_tile && h->i8_slices != 0 && M >= 4096 && N >= 64 && K >= 64 &&
@@ -441,6 +446,8 @@ int sgp_gemm_i8emu(sgp_handle* h, int layout, const double* A, long M, long lda,
   if (!h || !A || !B || !C) return fail(h, SGP_E_ARG, "sgp_gemm_i8emu: null argument");
   if (slices < 2 || slices > 8) return fail(h, SGP_E_ARG, "sgp_gemm_i8emu: slices must be in 2..8");
   if (M <= 0 || N <= 0 || K <= 0 || K > (1L << 30)) return fail(h, SGP_E_ARG, "sgp_gemm_i8emu: bad sizes");
+  if (ldc < N || lda < (layout ? M : K) || ldb < (layout ? N : K))
+    return fail(h, SGP_E_ARG, "sgp_gemm_i8emu: leading dimension smaller than the row length");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int ldk = oz_ldk((int)K);
@@ -480,6 +487,7 @@ int sgp_gemm_i8emu(sgp_handle* h, int layout, const double* A, long M, long lda,
 
 int sgp_cholesky(sgp_handle* h, double* A, long ld, int n, int* flags_host, void* stream) {
   if (!h || !A) return fail(h, SGP_E_ARG, "sgp_cholesky: null argument");
+  if (n <= 0 || ld < n) return fail(h, SGP_E_ARG, "sgp_cholesky: need n > 0 and ld >= n");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
@@ -495,6 +503,7 @@ int sgp_cholesky(sgp_handle* h, double* A, long ld, int n, int* flags_host, void
 int sgp_spd_inverse(sgp_handle* h, const double* A, long lda, int n, double* Ainv, long ldi, double* logdet_host,
                     int* flags_host, void* stream) {
   if (!h || !A || !Ainv) return fail(h, SGP_E_ARG, "sgp_spd_inverse: null argument");
+  if (n <= 0 || lda < n || ldi < n) return fail(h, SGP_E_ARG, "sgp_spd_inverse: need n > 0 and leading dimensions >= n");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const long ld = rup(n, 16);
@@ -1827,6 +1836,9 @@ static int acosker_impl(sgp_handle* h, const double* x1, long n1, long ld1, cons
                         void* stream) {
   if (!h || !x1 || !x2 || !C || !K) return fail(h, SGP_E_ARG, "sgp_acosker: null argument");
   if (symm && n1 != n2) return fail(h, SGP_E_ARG, "sgp_acosker: symmetrize needs n1 == n2");
+  if (n1 <= 0 || n2 <= 0 || p <= 0) return fail(h, SGP_E_ARG, "sgp_acosker: sizes must be positive");
+  if (ld1 < p || ld2 < p || ldc < p || ldk < n2)
+    return fail(h, SGP_E_ARG, "sgp_acosker: leading dimension smaller than the row length");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const long ldp = rup(p, 16), ldn2 = rup(n2, 16);
@@ -1944,6 +1956,8 @@ int sgp_acosker_known(sgp_handle* h, const double* x1, long n1, long ld1, const 
                       long ld2, int p, const double* C, long ldc, double sigma_0, double* K, long ldk, void* stream) {
   if (!h || !x1 || !kvec1 || !x2 || !C || !K) return fail(h, SGP_E_ARG, "sgp_acosker_known: null argument");
   if (n1 <= 0 || n2 <= 0 || p <= 0 || ldk < n2) return fail(h, SGP_E_ARG, "sgp_acosker_known: bad shape");
+  if (ld1 < p || ld2 < p || ldc < p)
+    return fail(h, SGP_E_ARG, "sgp_acosker_known: leading dimension smaller than the row length");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const long ldp = rup(p, 16), ldn2 = rup(n2, 16);
@@ -1997,6 +2011,7 @@ int sgp_acosker_known(sgp_handle* h, const double* x1, long n1, long ld1, const 
 int sgp_acosker_diag(sgp_handle* h, const double* x1, long n1, long ld1, int p, const double* C, long ldc,
                      double sigma_0, double* Kvec, void* stream) {
   if (!h || !x1 || !C || !Kvec) return fail(h, SGP_E_ARG, "sgp_acosker_diag: null argument");
+  if (n1 <= 0 || p <= 0 || ld1 < p || ldc < p) return fail(h, SGP_E_ARG, "sgp_acosker_diag: bad sizes / leading dimensions");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const long ldp = rup(p, 16);
@@ -2062,6 +2077,8 @@ int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K
                        void* stream) {
   if (!h || !a || !K_b || !Kvec || !m_b || !V_b || !lam_m || !lam_var)
     return fail(h, SGP_E_ARG, "sgp_lambda_moments: null argument");
+  if (N <= 0 || q <= 0 || lda < q || ldk < q || ldv < q)
+    return fail(h, SGP_E_ARG, "sgp_lambda_moments: bad sizes / leading dimensions");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const long ldq = rup(q, 16);
@@ -2113,6 +2130,7 @@ int sgp_lambda_moments(sgp_handle* h, const double* a, long lda, const double* K
 int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, const double* r, long N, double logA,
                     double lambda0, double* f, double* out_host, void* stream) {
   if (!h || !lam_m || !lam_var || !r || !out_host) return fail(h, SGP_E_ARG, "sgp_fparam_eval: null argument");
+  if (N <= 0) return fail(h, SGP_E_ARG, "sgp_fparam_eval: N must be positive");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = fparam_blocks(N);
@@ -2136,6 +2154,7 @@ int sgp_fparam_eval(sgp_handle* h, const double* lam_m, const double* lam_var, c
 int sgp_loglik_sums(sgp_handle* h, const double* r, const double* f, const double* lam_m, const double* lam_var, long N,
                     double logA, double* out_host, void* stream) {
   if (!h || !r || !f || !lam_m || !out_host) return fail(h, SGP_E_ARG, "sgp_loglik_sums: null argument");
+  if (N <= 0) return fail(h, SGP_E_ARG, "sgp_loglik_sums: N must be positive");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = fparam_blocks(N);
@@ -2152,6 +2171,7 @@ int sgp_loglik_sums(sgp_handle* h, const double* r, const double* f, const doubl
 int sgp_estep_terms(sgp_handle* h, const double* a, long lda, const double* r, const double* f, long N, int q,
                     double logA, double* g, double* G, long ldg, void* stream) {
   if (!h || !a || !r || !f || !g || !G) return fail(h, SGP_E_ARG, "sgp_estep_terms: null argument");
+  if (N <= 0 || q <= 0 || lda < q || ldg < q) return fail(h, SGP_E_ARG, "sgp_estep_terms: bad sizes / leading dimensions");
   int rc = ensure_ready(h); if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const double A = std::exp(logA);

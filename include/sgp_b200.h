@@ -8,6 +8,8 @@
  *
  * Conventions
  *   - every function returns an int status (SGP_OK == 0); sgp_last_error(h) gives the message;
+ *   - sizes must be positive and every leading dimension at least the row length it strides over: anything else is
+ *     refused with SGP_E_ARG before a kernel is launched (the library cannot know the size of the caller's buffers);
  *   - all matrices are fp64, row-major, caller-allocated DEVICE memory unless the name ends in _host;
  *   - `ld*` are leading dimensions in elements; `stream` is a cudaStream_t passed as void*;
  *   - the library never owns user-visible memory; the handle owns scratch workspace only;

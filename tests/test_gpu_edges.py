@@ -166,3 +166,38 @@ def test_the_handle_survives_refused_calls():
     out = native.elbo_grad(X, r, xt, n, th, B, m_b, V_b, prob.logA, prob.lambda0, lims=lims)
     assert out["flags"] == 0 and out["loglik"] == ref["loglik"]
     assert all(out["grad"][k] == ref["grad"][k] for k in ref["grad"])
+
+
+def test_function_level_entry_points_refuse_bad_shapes():
+    """Sizes <= 0 and leading dimensions smaller than the row length come back as SGP_E_ARG with a message, through the C
+    ABI, before any kernel is launched (the buffers below would be overrun otherwise)."""
+    import ctypes as C
+    from gaussian_processes_b200 import _lib
+    lib, h = _lib.lib, _lib.handle_for(0)
+    a = torch.ones(64, 8, dtype=torch.float64, device=D)
+    v = torch.ones(64, dtype=torch.float64, device=D)
+    P = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    st = C.c_void_p(torch.cuda.current_stream(D).cuda_stream)
+    out = (C.c_double * 16)()
+    calls = [
+        lambda: lib.sgp_gemm_f64(h.ptr, 0, 0, P(a), 4, P(a), 8, P(a), 8, 8, 8, 8, 1.0, 0, 0, st),          # lda < K
+        lambda: lib.sgp_gemm_f64(h.ptr, 0, 0, P(a), 8, P(a), 8, P(a), 8, 0, 8, 8, 1.0, 0, 0, st),          # M == 0
+        lambda: lib.sgp_gemm_i8emu(h.ptr, 0, P(a), 8, 8, P(a), 8, 8, 8, 8, P(a), 4, st),                    # ldc < N
+        lambda: lib.sgp_cholesky(h.ptr, P(a), 4, 8, None, st),                                              # ld < n
+        lambda: lib.sgp_spd_inverse(h.ptr, P(a), 8, 8, P(a), 4, None, None, st),                            # ldi < n
+        lambda: lib.sgp_acosker(h.ptr, P(a), 8, 4, P(a), 8, 8, 8, P(a), 8, 1.0, P(a), 8, 0, st),            # ld1 < p
+        lambda: lib.sgp_acosker(h.ptr, P(a), 8, 8, P(a), 8, 8, 8, P(a), 8, 1.0, P(a), 4, 0, st),            # ldk < n2
+        lambda: lib.sgp_acosker_diag(h.ptr, P(a), -1, 8, 8, P(a), 8, 1.0, P(v), st),                        # n1 < 0
+        lambda: lib.sgp_acosker_known(h.ptr, P(a), 8, 8, P(v), P(a), 1, 4, 8, P(a), 8, 1.0, P(a), 8, st),   # ld2 < p
+        lambda: lib.sgp_lambda_moments(h.ptr, P(a), 4, P(a), 8, P(v), 8, 8, P(v), P(a), 8, P(v), P(v), st),  # lda < q
+        lambda: lib.sgp_estep_terms(h.ptr, P(a), 8, P(v), P(v), 8, 8, 0.0, P(v), P(a), 4, st),              # ldg < q
+        lambda: lib.sgp_fparam_eval(h.ptr, P(v), P(v), P(v), 0, 0.0, 0.0, None, out, st),                   # N == 0
+        lambda: lib.sgp_localker(h.ptr, (C.c_double * 6)(1, 0, 0, 1, 1, 1), 0, P(a), 8, None, 0, st),       # n_px == 0
+    ]
+    before = a.clone()
+    for i, call in enumerate(calls):
+        rc = call()
+        assert rc == _lib.SGP_E_ARG, (i, rc)
+        assert lib.sgp_last_error(h.ptr)
+    torch.cuda.synchronize()
+    assert torch.equal(a, before)
