@@ -300,6 +300,23 @@ OUT_KEYS = ("loglik", "KL", "g_sigma_0", "g_eps_0x", "g_eps_0y", "g_-2log2beta",
             "flags", "p", "sum_r", "sum_f", "r_lam", "logdetK", "logdetV", "projected")
 
 
+def _check_closure_shapes(X, r, xtilde, n_px, B, m_b, V_b):
+    """The C ABI sees pointers and leading dimensions only: the shapes are checked here, where they are known (the
+    reference fails on these mismatches inside x[:, mask] / its matmuls)."""
+    P = int(n_px) * int(n_px)
+    if X.dim() != 2 or xtilde.dim() != 2 or X.shape[1] != P or xtilde.shape[1] != P:
+        raise ValueError(f"images must be (N, {P}) and (ntilde, {P}) for n_px_side = {n_px}: got {tuple(X.shape)} and "
+                         f"{tuple(xtilde.shape)}")
+    N, m = X.shape[0], xtilde.shape[0]
+    if r.shape != (N,):
+        raise ValueError(f"r must have one spike count per image: got {tuple(r.shape)} for {N} images")
+    if B.dim() != 2 or B.shape[0] != m or B.shape[1] < 1 or B.shape[1] > m:
+        raise ValueError(f"B must be (ntilde, q) with 1 <= q <= ntilde = {m}: got {tuple(B.shape)}")
+    q = B.shape[1]
+    if m_b.shape != (q,) or V_b.shape != (q, q):
+        raise ValueError(f"m_b must be ({q},) and V_b ({q}, {q}): got {tuple(m_b.shape)} and {tuple(V_b.shape)}")
+
+
 def elbo_grad(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int, theta, B: torch.Tensor,
               m_b: torch.Tensor, V_b: torch.Tensor, logA: float, lambda0: float, lims=None,
               logdetV: Optional[float] = None, want_moments: bool = False, kl_weight: float = 1.0,
@@ -314,6 +331,7 @@ def elbo_grad(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: int,
     set_option(_dev, "square_is_same", 0.0 if same is False else 1.0)
     X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
     r, m_b = r.contiguous(), m_b.contiguous()
+    _check_closure_shapes(X, r, xtilde, n_px, B, m_b, V_b)
     N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]
     lam_m = lam_var = f = None
     if want_moments:
@@ -356,6 +374,7 @@ def elbo_grad_f32(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: 
     set_option(_dev, "square_is_same", 0.0 if same is False else 1.0)
     X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
     r, m_b = r.contiguous(), m_b.contiguous()
+    _check_closure_shapes(X, r, xtilde, n_px, B, m_b, V_b)
     N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]
     lam_m = lam_var = f = None
     if want_moments:
@@ -391,6 +410,7 @@ def elbo_grad_dev(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px: 
     set_option(_dev, "square_is_same", 0.0)       # image shards: the local row count says nothing about ntilde == nt
     X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
     r, m_b = r.contiguous(), m_b.contiguous()
+    _check_closure_shapes(X, r, xtilde, n_px, B, m_b, V_b)
     N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]
     if out is None:
         out = torch.empty(16, dtype=torch.float64, device=X.device)
@@ -458,6 +478,7 @@ def elbo_grad_host(X: torch.Tensor, r: torch.Tensor, xtilde: torch.Tensor, n_px:
             raise TypeError("elbo_grad_host expects CPU fp64 tensors")
     X, xtilde, B, V_b = _c(X), _c(xtilde), _c(B), _c(V_b)
     r, m_b = r.contiguous(), m_b.contiguous()
+    _check_closure_shapes(X, r, xtilde, n_px, B, m_b, V_b)
     N, m, q = X.shape[0], xtilde.shape[0], B.shape[1]
     out = (C.c_double * 16)()
     h = _lib.handle_for(device)

@@ -161,8 +161,22 @@ def test_the_handle_survives_refused_calls():
     empty = {**synth.THETA_NOTEBOOK, "-2log2beta": 6.9, "-log2rho2": 5.0, "eps_0x": 0.004, "eps_0y": -0.09}
     with pytest.raises(_lib.SgpError):
         native.elbo_grad(X, r, xt, n, empty, B, m_b, V_b, prob.logA, prob.lambda0)
-    with pytest.raises(_lib.SgpError):
-        native.elbo_grad(X, r, xt, n + 1, th, B, m_b, V_b, prob.logA, prob.lambda0)       # P != n_px^2
+    with pytest.raises(ValueError):
+        native.elbo_grad(X, r, xt, n + 1, th, B, m_b, V_b, prob.logA, prob.lambda0)       # P != n_px^2: Python-side check
+    with pytest.raises(ValueError):
+        native.elbo_grad(X, r[:-1], xt, n, th, B, m_b, V_b, prob.logA, prob.lambda0)      # one spike count short
+    with pytest.raises(ValueError):
+        native.elbo_grad(X, r, xt, n, th, B, m_b[:-1], V_b, prob.logA, prob.lambda0)
+    with pytest.raises(_lib.SgpError) as e:                                                # and the C ABI's own check
+        import ctypes as C
+        h = _lib.handle_for(0)
+        out = (C.c_double * 16)()
+        P_ = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+        h.check(_lib.lib.sgp_elbo_grad(h.ptr, P_(X), X.stride(0), P_(r), N, P_(xt), xt.stride(0), m, n + 1,
+                                       native.theta_array(th), None, None, P_(B), B.stride(0), B.shape[1], P_(m_b), P_(V_b),
+                                       V_b.stride(0), float(prob.logA), float(prob.lambda0), None, None, None, None, out,
+                                       C.c_void_p(torch.cuda.current_stream(D).cuda_stream)))
+    assert e.value.code == _lib.SGP_E_ARG
     out = native.elbo_grad(X, r, xt, n, th, B, m_b, V_b, prob.logA, prob.lambda0, lims=lims)
     assert out["flags"] == 0 and out["loglik"] == ref["loglik"]
     assert all(out["grad"][k] == ref["grad"][k] for k in ref["grad"])
