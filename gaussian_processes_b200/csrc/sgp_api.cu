@@ -1684,6 +1684,9 @@ int sgp_elbo_grad_host(sgp_handle* h, const double* X_host, long ldx, const doub
                        long ldv, double logA, double lambda0, double* out_host) {
   if (!h || !X_host || !r_host || !xtilde_host || !theta || !B_host || !m_b_host || !V_b_host)
     return fail(h, SGP_E_ARG, "sgp_elbo_grad_host: null argument");
+  if (N <= 0 || m <= 0 || n_px <= 0 || q <= 0 || q > m) return fail(h, SGP_E_ARG, "sgp_elbo_grad_host: bad sizes");
+  if (ldx < (long)n_px * n_px || ldu < (long)n_px * n_px || ldb < q || ldv < q)
+    return fail(h, SGP_E_ARG, "sgp_elbo_grad_host: leading dimension smaller than the row length");
   int rc = ensure_ready(h); if (rc) return rc;
   if (!h->compute_stream) CU(cudaStreamCreateWithFlags(&h->compute_stream, cudaStreamNonBlocking));
   cudaStream_t st = h->compute_stream;
@@ -1764,6 +1767,8 @@ int sgp_upload_images(sgp_handle* h, const double* X_host, long ldx, const doubl
                       const double* xtilde_host, long ldu, int m, int n_px) {
   if (!h || !X_host || !r_host || !xtilde_host) return fail(h, SGP_E_ARG, "sgp_upload_images: null argument");
   if (N <= 0 || m <= 0 || n_px <= 0) return fail(h, SGP_E_ARG, "sgp_upload_images: bad sizes");
+  if (ldx < (long)n_px * n_px || ldu < (long)n_px * n_px)
+    return fail(h, SGP_E_ARG, "sgp_upload_images: leading dimension smaller than the row length (n_px^2 pixels per image)");
   int rc = ensure_ready(h); if (rc) return rc;
   if (!h->compute_stream) CU(cudaStreamCreateWithFlags(&h->compute_stream, cudaStreamNonBlocking));
   cudaStream_t st = h->compute_stream;
@@ -1797,7 +1802,7 @@ int sgp_elbo_grad_resident(sgp_handle* h, const double* theta, const double* lo,
   cudaStream_t st = h->compute_stream;
   const int m = (int)h->res_m;
   const long P = (long)h->res_npx * h->res_npx;
-  if (q <= 0 || q > m) return fail(h, SGP_E_ARG, "sgp_elbo_grad_resident: bad q");
+  if (q <= 0 || q > m || ldb < q || ldv < q) return fail(h, SGP_E_ARG, "sgp_elbo_grad_resident: bad q / leading dimensions");
   const size_t nB = (size_t)m * q, nV = (size_t)q * q;
   CU(h->small.reserve((nB + nV + q + 64) * sizeof(double)));
   double* dB = (double*)h->small.p; double* dV = dB + ((nB + 1) & ~size_t(1)); double* dm = dV + ((nV + 1) & ~size_t(1));
