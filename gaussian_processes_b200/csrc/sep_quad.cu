@@ -394,6 +394,89 @@ cudaError_t sep_quad(const SepQuadArgs& a, cudaStream_t st) {
   }
 }
 
+// ZU = U C and t_j = u_j^T C u_j + sigma_0^2 for the m inducing images through the same Kronecker structure, without C:
+//   (C u)_a = Amp a_a [G (u o a as an n x n image) G]_a        (C = Amp D_a (G (x) G) D_a, G symmetric)
+// -- 4 n^3 flops per image instead of the 2 p^2 of the dense product, and, more to the point, ONE launch in front of the
+// image pass instead of build_C -> slices of U -> slices of C -> U C product -> norms (five dependent launches, ~0.15 ms of
+// every evaluation's critical path; C itself is only needed again by the tail's <dC, G_C> contraction and is built on the
+// chain stream).  One block per inducing image, plain fp64 FMAs (m images: ~0.1 GFLOP in all).
+__global__ void __launch_bounds__(256) sep_apply_C_kernel(const double* __restrict__ U, long ldu, int m, int p,
+                                                          const int* __restrict__ off, int off_ld,
+                                                          const double* __restrict__ alpha, int n, double er, double amp,
+                                                          double s02, double* __restrict__ ZU, long ldz,
+                                                          double* __restrict__ t_out, double* __restrict__ nrm_out) {
+  extern __shared__ double sm_apply[];
+  const int pitch = n + 1;
+  double* G = sm_apply;                 // n x n Gaussian matrix of the grid coordinates
+  double* M = G + n * pitch;            // the weighted image, later Z = G T
+  double* T = M + n * pitch;            // T = M G
+  __shared__ double red[8];
+  const int j = blockIdx.x;
+  const double* u = U + (long)j * ldu;
+  for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+    const int a = e / n, b = e % n;
+    const double d = lin_coord_dev(a, n) - lin_coord_dev(b, n);
+    G[a * pitch + b] = exp(-er * d * d);
+    M[a * pitch + b] = 0.0;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < p; k += blockDim.x) {
+    const int o = off[k], iy = o / off_ld, ix = o % off_ld;
+    M[iy * pitch + ix] = alpha[k] * u[k];
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < n * n; e += blockDim.x) {      // T = M G
+    const int iy = e / n, jx = e % n;
+    double acc = 0.0;
+    for (int k = 0; k < n; ++k) acc = fma(M[iy * pitch + k], G[k * pitch + jx], acc);
+    T[iy * pitch + jx] = acc;
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < n * n; e += blockDim.x) {      // Z = G T  (into M)
+    const int iy = e / n, jx = e % n;
+    double acc = 0.0;
+    for (int k = 0; k < n; ++k) acc = fma(G[iy * pitch + k], T[k * pitch + jx], acc);
+    M[iy * pitch + jx] = acc;
+  }
+  __syncthreads();
+  double t = 0.0;
+  for (int k = threadIdx.x; k < ldz; k += blockDim.x) {
+    double z = 0.0;
+    if (k < p) {
+      const int o = off[k], iy = o / off_ld, ix = o % off_ld;
+      z = amp * alpha[k] * M[iy * pitch + ix];
+      t = fma(u[k], z, t);
+    }
+    ZU[(long)j * ldz + k] = z;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = t;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w];
+    s += s02;
+    t_out[j] = s;
+    nrm_out[j] = sqrt(s);
+  }
+}
+
+cudaError_t sep_apply_C(const double* U, long ldu, int m, int p, const int* off, const double* alpha, int n, double er,
+                        double amp, double s02, double* ZU, long ldz, double* t_out, double* nrm_out, cudaStream_t st) {
+  if (m <= 0) return cudaSuccess;
+  if (!sep_quad_supported(n)) return cudaErrorInvalidValue;
+  const size_t smem = (size_t)3 * n * (n + 1) * sizeof(double);
+  if (smem > 48 * 1024) {            // 3 * 48 * 49 * 8 = 56 KB at the largest n: above the default limit (per device)
+    cudaError_t e = cudaFuncSetAttribute(sep_apply_C_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  note_launch();
+  sep_apply_C_kernel<<<m, 256, smem, st>>>(U, ldu, m, p, off, sep_quad_ld(n), alpha, n, er, amp, s02, ZU, ldz, t_out,
+                                            nrm_out);
+  return cudaGetLastError();
+}
+
 // blockpart[blk*5 + k] = sum_{i in blk} w_i Q[i][k]
 __global__ void __launch_bounds__(256) wq_reduce_kernel(const double* __restrict__ w, const double* __restrict__ Q,
                                                         long n, double* __restrict__ blockpart) {

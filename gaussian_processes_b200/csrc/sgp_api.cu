@@ -106,6 +106,7 @@ struct sgp_handle {
   // N == m: 1 = the reference's ntilde == nt branch (K = K_tilde, a = B); 0 = treat it as any other N (an image SHARD
   // that happens to hold m rows is not the active-learning configuration)
   int square_is_same = 1;
+  int sep_uc = getenv("SGP_SEP_UC") ? atoi(getenv("SGP_SEP_UC")) : 1;   // U C from the separable structure of C (one launch)
   int projected = -1;       // moments in the projected basis (K_b = K B): -1 = when q is small enough to pay, 0 = never, 1 = always
   DevBuf hx[2], hr, small;
   cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr}, ev_small = nullptr;
@@ -293,6 +294,7 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
   else if (n == "projected") h->projected = (int)value;
   else if (n == "support") h->support = (int)value;
   else if (n == "square_is_same") h->square_is_same = value != 0.0;
+  else if (n == "sep_uc") h->sep_uc = value != 0.0;
   else if (n == "i8_slices") {
     if (value != -1 && value != 0 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices must be -1, 0 or 2..8");
     h->i8_slices = (int)value;
@@ -998,14 +1000,20 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
   };
 
   // ---- a1: C(theta) ---------------------------------------------------------------------------------
-  build_C(C, ldp, p, d_gx, d_gy, th, nullptr, 0, st);
+  // Separable path: nothing in front of the tail needs C itself (the image pass takes its quadratic forms and U C from the
+  // Kronecker structure), so C is built at the head of the inducing-point chain, off the critical path.
+  const bool sep_uc = use_sep && h->sep_uc != 0;
+  if (!sep_uc) build_C(C, ldp, p, d_gx, d_gy, th, nullptr, 0, st);
 
   const bool smallU = true;  // inducing-point GEMMs are small: 64x64 tiles
   // ---- inducing-point path: K_tilde, K_tilde_b, its inverse, and the moment matrices ------------------
   {
     // ZU = Ug C ; partial row dots for t_j = u_j^T C u_j.  On the critical path of every evaluation (nothing else can
     // start before it): int8-slice engine when it is on (C is symmetric, so its rows are the B operand's rows)
-    if (ozS) {
+    if (sep_uc) {
+      // ZU = U C, t_j = u_j^T C u_j + sigma_0^2, X2 = sqrt(t): one launch (sep_quad.cu) instead of five dependent ones
+      CU(sep_apply_C(Ug, ldug, m, p, d_off, d_alpha, n, th.er, th.amp, th.s02, ZU, ldp, tU, X2, st));
+    } else if (ozS) {
       CU(oz_slice_rows(Ug, ldug, m, p, ozS, ugq, ldkP, uge, st));
       CU(oz_slice_rows(C, ldp, p, p, ozS, cq, ldkP, ce, st));
       const OzMoments mom{Ug, ldug, partU, ldpartU};
@@ -1040,6 +1048,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     cudaStream_t st_main = st;
     cudaStream_t st = chain_overlap ? h->chain_stream : st_main;   // shadows the outer stream inside this lambda
     if (chain_overlap) CU(cudaStreamWaitEvent(h->chain_stream, h->ev_chain_fork, 0));
+    if (sep_uc) build_C(C, ldp, p, d_gx, d_gy, th, nullptr, 0, st);     // for the tail's <dC_k, G_C> contraction only
     GemmArgs a{};  // K_tilde (raw) = acos-kernel(ZU Ug^T)
     a.A = ZU; a.lda = ldp; a.B = Ug; a.ldb = ldug; a.C = Kraw; a.ldc = ldm; a.M = m; a.N = m; a.K = p;
     a.rowvec = X2; a.colvec = X2; a.C2 = cosU; a.s02 = th.s02;

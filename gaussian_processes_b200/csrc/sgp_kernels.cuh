@@ -198,6 +198,10 @@ struct SepQuadArgs {
 bool sep_quad_supported(int n_px);
 int sep_quad_ld(int n_px);
 cudaError_t sep_quad(const SepQuadArgs& a, cudaStream_t st);
+// ZU (m x ldz, padding zeroed) = U C, t_out[j] = u_j^T C u_j + s02, nrm_out[j] = sqrt(t_out[j]) from the separable structure
+// of C (off / alpha as in SepQuadArgs); U: the gathered inducing images (m x p, ld = ldu)
+cudaError_t sep_apply_C(const double* U, long ldu, int m, int p, const int* off, const double* alpha, int n, double er,
+                        double amp, double s02, double* ZU, long ldz, double* t_out, double* nrm_out, cudaStream_t st);
 int wq_reduce_blocks(long n);
 void wq_reduce(const double* w, const double* Q, long n, double* blockpart, cudaStream_t st);
 
