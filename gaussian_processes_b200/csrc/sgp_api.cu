@@ -106,6 +106,7 @@ struct sgp_handle {
   // N == m: 1 = the reference's ntilde == nt branch (K = K_tilde, a = B); 0 = treat it as any other N (an image SHARD
   // that happens to hold m rows is not the active-learning configuration)
   int square_is_same = 1;
+  int chol_fused = getenv("SGP_CHOL_FUSED") ? atoi(getenv("SGP_CHOL_FUSED")) : 320;   // one-launch Cholesky / inverse up to this order
   int sep_uc = getenv("SGP_SEP_UC") ? atoi(getenv("SGP_SEP_UC")) : 1;   // U C from the separable structure of C (one launch)
   int projected = -1;       // moments in the projected basis (K_b = K B): -1 = when q is small enough to pay, 0 = never, 1 = always
   DevBuf hx[2], hr, small;
@@ -187,6 +188,19 @@ cudaError_t mm(cudaStream_t st, int al, int bl, const double* A, long lda, const
   GemmArgs g{};
   g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K; g.alpha = alpha;
   return gemm(st, al, bl, kStore, small, 1, g);
+}
+
+// Cholesky factor (in place, lower), optionally L^-1 (X) and log det (scal[slot], slot >= 0): ONE launch of the cluster
+// kernel (chol_fused.cu) up to option "chol_fused" rows (default 320: beyond that the trailing updates want more than the
+// cluster's 8 SMs and the launch-per-step path is faster), else cholesky_lower / logdet_from_chol / tri_inverse_lower.
+cudaError_t factor_any(sgp_handle* h, double* L, long ld, int n, double* X, double* tri_tmp, double* winv, int bit_notpd,
+                       int bit_small, int slot, cudaStream_t st) {
+  if (n <= h->chol_fused && chol_inv_fused_supported(n))
+    return chol_inv_fused(L, ld, n, X, ld, winv, h->d_flags, bit_notpd, bit_small, h->d_scal, slot, st);
+  cudaError_t e = cholesky_lower(L, ld, n, h->d_flags, bit_notpd, bit_small, winv, st);
+  if (e != cudaSuccess) return e;
+  if (slot >= 0) logdet_from_chol(L, ld, n, h->d_scal, slot, st);
+  return X ? tri_inverse_lower(L, ld, n, X, tri_tmp, winv, st) : cudaSuccess;
 }
 
 int ensure_ready(sgp_handle* h) {
@@ -294,6 +308,7 @@ int sgp_set_option(sgp_handle* h, const char* name, double value) {
   else if (n == "projected") h->projected = (int)value;
   else if (n == "support") h->support = (int)value;
   else if (n == "square_is_same") h->square_is_same = value != 0.0;
+  else if (n == "chol_fused") h->chol_fused = (int)value;
   else if (n == "sep_uc") h->sep_uc = value != 0.0;
   else if (n == "i8_slices") {
     if (value != -1 && value != 0 && (value < 2 || value > 8)) return fail(h, SGP_E_ARG, "sgp_set_option: i8_slices must be -1, 0 or 2..8");
@@ -494,7 +509,7 @@ int sgp_cholesky(sgp_handle* h, double* A, long ld, int n, int* flags_host, void
   cudaStream_t st = (cudaStream_t)stream;
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
   RESERVE_ARENA((size_t)chol_winv_elems(n) * sizeof(double) + 4096);
-  CU(cholesky_lower(A, ld, n, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, (double*)h->arena.p, st));
+  CU(factor_any(h, A, ld, n, nullptr, nullptr, (double*)h->arena.p, kFlagKtNotPD, kFlagKtSmallPivot, -1, st));
   if (flags_host) {
     CU(cudaMemcpyAsync(flags_host, h->d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -518,9 +533,7 @@ int sgp_spd_inverse(sgp_handle* h, const double* A, long lda, int n, double* Ain
   double* winv = ar.take<double>(chol_winv_elems(n));
   CU(cudaMemsetAsync(h->d_flags, 0, sizeof(int) * 4, st));
   copy_mat(A, lda, n, n, L, ld, st);
-  CU(cholesky_lower(L, ld, n, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, winv, st));
-  logdet_from_chol(L, ld, n, h->d_scal, kSlotLogdetK, st);
-  CU(tri_inverse_lower(L, ld, n, X, tmp, winv, st));
+  CU(factor_any(h, L, ld, n, X, tmp, winv, kFlagKtNotPD, kFlagKtSmallPivot, kSlotLogdetK, st));
   CU(mm(st, 1, 1, X, ld, X, ld, R, ld, n, n, n));
   symmetrize(R, ld, n, Ainv, ldi, st);
   CU(cudaGetLastError());
@@ -993,8 +1006,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     CU(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
     double* Lv_side = qq[9];
     copy_mat(Vw, ldq, q, q, Lv_side, ldq, h->side_stream);
-    CU(cholesky_lower(Lv_side, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, winv2, h->side_stream));
-    logdet_from_chol(Lv_side, ldq, q, h->d_scal, kSlotLogdetV, h->side_stream);
+    CU(factor_any(h, Lv_side, ldq, q, nullptr, nullptr, winv2, kFlagVNotPD, kFlagVSmallPivot, kSlotLogdetV, h->side_stream));
     CU(cudaEventRecord(h->ev_join, h->side_stream));
     return SGP_OK;
   };
@@ -1058,9 +1070,7 @@ int run_closure(sgp_handle* h, const ClosureIn& in, double* out_host, cudaStream
     CU(mm(st, 1, 1, Bw, ldq, tmq1, ldq, Ktb_raw, ldq, q, q, m));                         // B^T Kt B   U:2047
     symmetrize(Ktb_raw, ldq, q, Ktb, ldq, st);                                          // U:2048
     copy_mat(Ktb, ldq, q, q, Lk, ldq, st);
-    CU(cholesky_lower(Lk, ldq, q, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, winv, st));
-    logdet_from_chol(Lk, ldq, q, h->d_scal, kSlotLogdetK, st);
-    CU(tri_inverse_lower(Lk, ldq, q, Linv, tri_tmp, winv, st));
+    CU(factor_any(h, Lk, ldq, q, Linv, tri_tmp, winv, kFlagKtNotPD, kFlagKtSmallPivot, kSlotLogdetK, st));
     CU(mm(st, 1, 1, Linv, ldq, Linv, ldq, Kinv_raw, ldq, q, q, q));                      // K_tilde_b^-1  (U:2067)
     symmetrize(Kinv_raw, ldq, q, Kinv, ldq, st);
     gemv(Kinv, ldq, q, q, 0, in.m_b, bq, st);                                           // b = Kinv m_b
@@ -1522,9 +1532,7 @@ int run_closure_same(sgp_handle* h, const ClosureIn& in, double* out_host, cudaS
   CU(mm(st, 1, 1, Bw, ldq, Kb, ldq, Ktb_raw, ldq, q, q, m));                                 // B^T K_tilde B (U:2047)
   symmetrize(Ktb_raw, ldq, q, Ktb, ldq, st);                                                // U:2048
   copy_mat(Ktb, ldq, q, q, Lk, ldq, st);
-  CU(cholesky_lower(Lk, ldq, q, h->d_flags, kFlagKtNotPD, kFlagKtSmallPivot, winv, st));
-  logdet_from_chol(Lk, ldq, q, h->d_scal, kSlotLogdetK, st);
-  CU(tri_inverse_lower(Lk, ldq, q, Linv, tri_tmp, winv, st));
+  CU(factor_any(h, Lk, ldq, q, Linv, tri_tmp, winv, kFlagKtNotPD, kFlagKtSmallPivot, kSlotLogdetK, st));
   CU(mm(st, 1, 1, Linv, ldq, Linv, ldq, Kinv_raw, ldq, q, q, q));                            // K_tilde_b^-1 (U:2067)
   symmetrize(Kinv_raw, ldq, q, Kinv, ldq, st);
   gemv(Kinv, ldq, q, q, 0, in.m_b, bq, st);
@@ -1533,8 +1541,7 @@ int run_closure_same(sgp_handle* h, const ClosureIn& in, double* out_host, cudaS
   kl_scalars(in.m_b, bq, Vw, ldq, Kinv, ldq, q, h->d_scal, kSlotMb, kSlotTrVK, Gq, st);      // Gq: scratch until the backward pass
   if (!in.logdetV_host) {
     copy_mat(Vw, ldq, q, q, Lv, ldq, st);
-    CU(cholesky_lower(Lv, ldq, q, h->d_flags, kFlagVNotPD, kFlagVSmallPivot, winv2, st));
-    logdet_from_chol(Lv, ldq, q, h->d_scal, kSlotLogdetV, st);
+    CU(factor_any(h, Lv, ldq, q, nullptr, nullptr, winv2, kFlagVNotPD, kFlagVSmallPivot, kSlotLogdetV, st));
   }
   {
     GemmArgs g{};   // aV = a V^T with a = B; part1 = rowdot(aV, a), part2 = a m_b   (U:1090-1101)

@@ -1,5 +1,6 @@
 // Non-GEMM kernels of the Spatial_GP ELBO+gradient pass (sm_100a).  See sgp_kernels.cuh.
 #include "sgp_kernels.cuh"
+#include "chol_diag.cuh"
 
 #include <atomic>
 
@@ -581,106 +582,42 @@ void col_weights(const double* ka, const double* kb, const double* extra, const 
 // =====================================================================================================
 constexpr int kNB = 64;
 
-// One CTA factors a 64 x 64 diagonal block D = L L^T and inverts the factor, W = L^-1, in the same sweep.
-// 256 threads as a 16 x 16 grid, each holding a 4 x 4 sub-block of D (-> L) and of W in registers.  Step k: the
-// owners publish column k of D and row k of the running W through double-buffered shared memory, ONE barrier,
-// then every thread scales by 1/sqrt(d_kk) and applies the rank-1 updates to its registers (right-looking):
-//   D_ij -= l_ik l_jk (k < j <= i),   W_ij -= l_ik w_kj (i > k),   w_k. = (e_k - sum_{l<k} l_kl w_l.) / l_kk.
-// W turns the panel solve below the block and the triangular inverse into plain DMMA GEMMs.
+// One CTA factors a 64 x 64 diagonal block D = L L^T and inverts the factor, W = L^-1 (chol_diag.cuh: the block is itself
+// blocked 8 x 8, the pivot chain runs inside one warp).  W turns the panel solve below the block and the triangular
+// inverse into plain DMMA GEMMs.
 constexpr int kCholThreads = 256;
+constexpr int kCholPitch = 65;
+constexpr size_t kCholSmem = (size_t)(2 * kNB * kCholPitch + 512 + 512) * sizeof(double);   // 74 752 bytes
 __global__ void __launch_bounds__(kCholThreads) chol_diag_kernel(double* __restrict__ A, long ld, int nb,
                                                                  double* __restrict__ Wout, int* __restrict__ flags,
                                                                  int bit_notpd, int bit_small) {
-  __shared__ double colL[2][kNB], rowW[2][kNB];
-  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-  double a[4][4], w[4][4];
-#pragma unroll
-  for (int ri = 0; ri < 4; ++ri)
-#pragma unroll
-    for (int cj = 0; cj < 4; ++cj) {
-      const int r = 4 * ty + ri, c = 4 * tx + cj;
-      double v = (r == c) ? 1.0 : 0.0;                      // identity padding beyond nb
-      if (r < nb && c < nb) v = (c <= r) ? A[(long)r * ld + c] : 0.0;
-      a[ri][cj] = v;
-      w[ri][cj] = (r == c) ? 1.0 : 0.0;
-    }
-  int bad = 0;
-  // the 4 steps of one register column are unrolled (register indices must be compile-time); the 16 column groups
-  // loop, so the body stays resident in the instruction cache
-#pragma unroll 1
-  for (int kb = 0; kb < kNB / 4; ++kb)
-#pragma unroll
-  for (int kc = 0; kc < 4; ++kc) {
-    const int k = 4 * kb + kc, buf = kc & 1;
-    if (tx == kb) {
-#pragma unroll
-      for (int ri = 0; ri < 4; ++ri) colL[buf][4 * ty + ri] = a[ri][kc];
-    }
-    if (ty == kb) {
-#pragma unroll
-      for (int cj = 0; cj < 4; ++cj) rowW[buf][4 * tx + cj] = w[kc][cj];
-    }
-    __syncthreads();
-    const double d = colL[buf][k];
-    const double ds = d > 0.0 ? d : 1.0;          // keep going with a harmless pivot; the flag tells the host
-    const double inv = rsqrt(ds);
-    const double lkk = ds * inv;
-    if (k < nb) {
-      if (!(d > 0.0)) bad |= bit_notpd;
-      else if (lkk < 1e-10) bad |= bit_small;
-    }
-    double lr[4], lc[4], wk[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      lr[q] = colL[buf][4 * ty + q] * inv;
-      lc[q] = colL[buf][4 * tx + q] * inv;
-      wk[q] = rowW[buf][4 * tx + q] * inv;
-    }
-    if (tx == kb) {
-#pragma unroll
-      for (int ri = 0; ri < 4; ++ri) {
-        const int r = 4 * ty + ri;
-        if (r > k) a[ri][kc] = lr[ri];
-        else if (r == k) a[ri][kc] = lkk;
-      }
-    }
-    if (ty == kb) {
-#pragma unroll
-      for (int cj = 0; cj < 4; ++cj) w[kc][cj] = wk[cj];
-    }
-#pragma unroll
-    for (int ri = 0; ri < 4; ++ri) {
-      const int r = 4 * ty + ri;
-      if (r > k) {
-#pragma unroll
-        for (int cj = 0; cj < 4; ++cj) {
-          const int c = 4 * tx + cj;
-          if (c > k && c <= r) a[ri][cj] -= lr[ri] * lc[cj];
-          w[ri][cj] -= lr[ri] * wk[cj];
-        }
-      }
-    }
+  extern __shared__ double chol_sm[];
+  double* D = chol_sm;
+  double* Wm = D + kNB * kCholPitch;
+  double* Ti = Wm + kNB * kCholPitch;
+  double* pan = Ti + 512;
+  const int bad = diag_factor_inv<kCholPitch>(A, ld, nb, D, Wm, Ti, pan, bit_notpd, bit_small);
+  if (threadIdx.x == 0 && bad) atomicOr(flags, bad);
+  for (int e = threadIdx.x; e < kNB * kNB; e += kCholThreads) {
+    const int r = e >> 6, c = e & 63;
+    if (r < nb && c < nb) A[(long)r * ld + c] = D[r * kCholPitch + c];
+    Wout[e] = Wm[r * kCholPitch + c];
   }
-  if (tid == 0 && bad) atomicOr(flags, bad);
-#pragma unroll
-  for (int ri = 0; ri < 4; ++ri)
-#pragma unroll
-    for (int cj = 0; cj < 4; ++cj) {
-      const int r = 4 * ty + ri, c = 4 * tx + cj;
-      if (r < nb && c < nb) A[(long)r * ld + c] = (c <= r) ? a[ri][cj] : 0.0;
-      Wout[r * kNB + c] = (c <= r) ? w[ri][cj] : 0.0;
-    }
 }
 
 // In-place blocked Cholesky; Winv (cdiv(n,64) blocks of 64 x 64) receives the inverses of the diagonal blocks of L.
 cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, double* Winv,
                            cudaStream_t st) {
+  {   // 73 KB of shared memory: above the default limit (per device; not a stream operation)
+    cudaError_t e = cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholSmem);
+    if (e != cudaSuccess) return e;
+  }
   for (int j0 = 0; j0 < n; j0 += kNB) {
     const int nb = (n - j0) < kNB ? (n - j0) : kNB;
     const int rem = n - j0 - nb;
     double* W = Winv + (long)(j0 / kNB) * kNB * kNB;
     note_launch();
-    chol_diag_kernel<<<1, kCholThreads, 0, st>>>(A + (long)j0 * ld + j0, ld, nb, W, flags, bit_notpd, bit_small);
+    chol_diag_kernel<<<1, kCholThreads, kCholSmem, st>>>(A + (long)j0 * ld + j0, ld, nb, W, flags, bit_notpd, bit_small);
     if (rem > 0) {
       const int j1 = j0 + nb;
       GemmArgs t{};   // panel below the block, in place: L21 = A21 W^T   (one n-tile: a CTA reads only the rows it writes)

@@ -115,6 +115,11 @@ void col_weights(const double* kap_a, const double* kap_b, const double* extra, 
 inline long chol_winv_elems(int n) { return (long)((n + 63) / 64) * 64 * 64; }
 cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, double* Winv,
                            cudaStream_t st);
+// One-launch version of cholesky_lower + tri_inverse_lower + logdet_from_chol for n <= 1024 (chol_fused.cu: a cluster of
+// 8 CTAs, cluster barriers instead of kernel boundaries).  X (optional) = L^-1; slot < 0: no log det.
+bool chol_inv_fused_supported(int n);
+cudaError_t chol_inv_fused(double* A, long ld, int n, double* X, long ldx, double* Winv, int* flags, int bit_notpd,
+                           int bit_small, double* scal, int slot, cudaStream_t st);
 // X = L^{-1} (lower, strict upper zero). X must not alias L. tmp: scratch >= 64*ld doubles; Winv from cholesky_lower.
 cudaError_t tri_inverse_lower(const double* L, long ld, int n, double* X, double* tmp, const double* Winv,
                               cudaStream_t st);

@@ -77,7 +77,11 @@ SGP_API int sgp_set_slab_rows(sgp_handle* h, long rows);
  * utils.py:2032 / 2068 -- the default, as the reference decides by the row counts alone; 0 = N == m is treated like
  * any other N: set by image-sharded callers, whose local row count says nothing about the global one),
  * "projected" (-1 = moments in the projected basis K_b = K B when q <= 0.4 m, 0 = never, 1 = always; same numbers
- * up to rounding, utils.py:2047-2068), "overlap" (1 = the q x q chains run on side streams).
+ * up to rounding, utils.py:2047-2068), "overlap" (1 = the q x q chains run on side streams),
+ * "chol_fused" (largest matrix order whose Cholesky factor / inverse / log det run as ONE launch of a thread-block
+ * cluster, csrc/chol_fused.cu; default 320, at most 1024, 0 = always one launch per block step),
+ * "sep_uc" (1, the default = on the separable path U C and the inducing norms come from the Kronecker structure of C in
+ * one launch; 0 = build C, slice, multiply).
  * With int8 slices the library keeps a sliced copy of device-resident images across calls (same bytes as X).     */
 SGP_API int sgp_set_option(sgp_handle* h, const char* name, double value);
 /* accumulated per-stage device milliseconds of sgp_elbo_grad since the last reset:

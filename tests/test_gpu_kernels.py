@@ -80,8 +80,19 @@ def test_gemm_alpha_accumulate(nat):
     assert (out - (C0 - A @ B.T)).abs().max().item() < 1e-11
 
 
-@pytest.mark.parametrize("n", [1, 5, 64, 65, 100, 257, 500])
-def test_cholesky_and_spd_inverse(nat, n):
+@pytest.mark.parametrize("fused", [1024, 0])
+@pytest.mark.parametrize("n", [1, 5, 64, 65, 100, 128, 257, 500, 513, 1000, 1024, 1100])
+def test_cholesky_and_spd_inverse(nat, n, fused):
+    """Option "chol_fused" = largest order that takes chol_fused.cu (one launch: a cluster of 8 CTAs; at most 1024, so 1100
+    falls back; the default is 320); 0: always the launch-per-step path."""
+    nat.set_option(0, "chol_fused", fused)
+    try:
+        _cholesky_and_spd_inverse(nat, n)
+    finally:
+        nat.set_option(0, "chol_fused", 320)
+
+
+def _cholesky_and_spd_inverse(nat, n):
     g = torch.Generator(device="cpu").manual_seed(n)
     W = torch.randn(n, n + 3, generator=g, dtype=torch.float64)
     A = (W @ W.T + 0.5 * torch.eye(n, dtype=torch.float64))
@@ -97,11 +108,43 @@ def test_cholesky_and_spd_inverse(nat, n):
     assert abs(logdet - torch.logdet(A).item()) < 1e-10 * max(1.0, abs(torch.logdet(A).item()))
 
 
-def test_cholesky_flags_indefinite(nat):
-    A = torch.eye(70, dtype=torch.float64)
-    A[40, 40] = -1.0
-    _, fl = nat.cholesky(A.to(dev()))
-    assert fl & 1
+@pytest.mark.parametrize("fused", [1024, 0])
+def test_cholesky_flags_indefinite(nat, fused):
+    nat.set_option(0, "chol_fused", fused)
+    try:
+        A = torch.eye(70, dtype=torch.float64)
+        A[40, 40] = -1.0
+        _, fl = nat.cholesky(A.to(dev()))
+        assert fl & 1
+        A = torch.eye(300, dtype=torch.float64)
+        A[250, 250] = 1e-22                           # pivot 1e-11 < 1e-10: the reference's safe_log raises (U:670)
+        _, fl = nat.cholesky(A.to(dev()))
+        assert fl == 2
+    finally:
+        nat.set_option(0, "chol_fused", 320)
+
+
+def test_fused_and_stepwise_factorisations_agree(nat):
+    """Same blocked algorithm, same tile products: the factor, the inverse and log det agree to rounding (the trailing
+    update sums in a different tile order), on a matrix shaped like K_tilde_b + G (E-step, utils.py:1430)."""
+    g = torch.Generator(device="cpu").manual_seed(9)
+    n = 500
+    W = torch.randn(n, 2 * n, generator=g, dtype=torch.float64)
+    A = (W @ W.T / n + torch.diag(torch.logspace(-3, 2, n, dtype=torch.float64))).to(dev())
+    res = {}
+    for fused in (1024, 0):
+        nat.set_option(0, "chol_fused", fused)
+        try:
+            res[fused] = (nat.cholesky(A)[0], *nat.spd_inverse(A))
+        finally:
+            nat.set_option(0, "chol_fused", 320)
+    L1, I1, ld1, f1 = res[1024]
+    L0, I0, ld0, f0 = res[0]
+    assert f1 == f0 == 0
+    assert (torch.tril(L1) - torch.tril(L0)).abs().max().item() < 1e-12 * L0.abs().max().item()
+    assert (I1 - I0).abs().max().item() < 1e-11 * I0.abs().max().item()
+    assert abs(ld1 - ld0) < 1e-12 * abs(ld0)
+    assert torch.equal(I1, I1.T)
 
 
 @pytest.mark.parametrize("name", ["closure_dense_n8", "closure_local_n12"])
