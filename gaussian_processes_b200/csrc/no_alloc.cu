@@ -70,6 +70,8 @@ extern "C" int sgp_cholesky_noalloc(double* A, long ld, int n, int* flags_dev, v
         return fail(errbuf, errbuf_len, SGP_E_CUDA, "cudaGetSymbolAddress", cudaGetErrorString(e));
       e = sgp::gemm_f64_init();
       if (e != cudaSuccess) return fail(errbuf, errbuf_len, SGP_E_CUDA, "gemm_f64_init", cudaGetErrorString(e));
+      e = sgp::chol_init();
+      if (e != cudaSuccess) return fail(errbuf, errbuf_len, SGP_E_CUDA, "chol_init", cudaGetErrorString(e));
       g_scratch_ptr[dev] = p;
     }
     scratch = g_scratch_ptr[dev];

@@ -207,6 +207,7 @@ int ensure_ready(sgp_handle* h) {
   CU(cudaSetDevice(h->device));
   if (!h->gemm_ready) {
     CU(gemm_f64_init());
+    CU(chol_init());
     CU(oz_init());
     CU(cudaMalloc(&h->d_flags, sizeof(int) * 4));
     CU(cudaMalloc(&h->d_scal, sizeof(double) * kNumSlots));

@@ -605,13 +605,14 @@ __global__ void __launch_bounds__(kCholThreads) chol_diag_kernel(double* __restr
   }
 }
 
+// once per device, before the first factorisation: the diagonal-block kernel's 73 KB of shared memory are above the default
+cudaError_t chol_init() {
+  return cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholSmem);
+}
+
 // In-place blocked Cholesky; Winv (cdiv(n,64) blocks of 64 x 64) receives the inverses of the diagonal blocks of L.
 cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, double* Winv,
                            cudaStream_t st) {
-  {   // 73 KB of shared memory: above the default limit (per device; not a stream operation)
-    cudaError_t e = cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholSmem);
-    if (e != cudaSuccess) return e;
-  }
   for (int j0 = 0; j0 < n; j0 += kNB) {
     const int nb = (n - j0) < kNB ? (n - j0) : kNB;
     const int rem = n - j0 - nb;

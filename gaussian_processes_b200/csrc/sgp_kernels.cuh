@@ -113,6 +113,7 @@ void col_weights(const double* kap_a, const double* kap_b, const double* extra, 
 // blocks is zeroed). flags |= notpd/small bits.  Winv: workspace of chol_winv_elems(n) doubles, receives the
 // inverses of the 64 x 64 diagonal blocks of L.  Panel solve and trailing update run on the DMMA GEMM.
 inline long chol_winv_elems(int n) { return (long)((n + 63) / 64) * 64 * 64; }
+cudaError_t chol_init();     // once per device (kernel attribute), before the first cholesky_lower
 cudaError_t cholesky_lower(double* A, long ld, int n, int* flags, int bit_notpd, int bit_small, double* Winv,
                            cudaStream_t st);
 // One-launch version of cholesky_lower + tri_inverse_lower + logdet_from_chol for n <= 1024 (chol_fused.cu: a cluster of
