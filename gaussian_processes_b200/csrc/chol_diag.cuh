@@ -1,8 +1,8 @@
 // Cholesky factor L and inverse factor W = L^-1 of one 64 x 64 diagonal block, by one CTA of 256 threads, in shared memory.
 //
-// Round 1 did this as 64 rank-1 steps over register tiles with one block barrier per step: ~1 us per step (every thread
-// waits for the barrier, the published column, an fp64 rsqrt and 32 FMAs), 65 us per block -- 0.5 of the 0.51 ms of a
-// q = 500 factorisation, whatever is done about launches.  Here the block is itself blocked 8 x 8:
+// Round 1 did this as 64 rank-1 steps over register tiles with one block barrier per step (every thread waits for the
+// barrier, the published column, an fp64 rsqrt and 32 FMAs): 40 us per block as a call, most of a q = 500 factorisation
+// whatever is done about launches.  Here the block is itself blocked 8 x 8 (30 us per block, 500 -> 407 us at q = 500):
 //   per 8-column sub-block s:  warp 0 factors the 8 x 8 diagonal sub-block in registers with shuffles (no block barrier
 //   inside the pivot chain) and inverts it;  all threads solve the panel below (times Ti^T) and apply the rank-8 update;
 //   then W is built block row by block row from the eight 8 x 8 inverses:  W_IJ = -Ti_I sum_{J<=K<I} L_IK W_KJ.

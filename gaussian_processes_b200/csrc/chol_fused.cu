@@ -1,6 +1,7 @@
 // Cholesky factor, its inverse and log det of a q x q matrix (q <= 1024) in ONE launch: a thread-block cluster of 8 CTAs
 // walks the blocked algorithm with cluster barriers where cholesky_lower / tri_inverse_lower (sgp_kernels.cu) launch a
-// kernel -- 40 dependent launches at q = 500, ~0.6 ms of pure launch latency on a problem of 0.1 GFLOP.
+// kernel (40 dependent launches at q = 500).  Measured (scripts/probe_chol.py): a few per cent faster than the stepwise path up
+// to q ~ 320 and slower beyond (the trailing updates want more than 8 SMs) -- hence the "chol_fused" threshold in sgp_api.cu.
 //
 // The K_tilde_b factorisation sits on every evaluation's inducing-point chain (utils.py:2047-2067: solve(K_tilde_b, I),
 // log_det) and in every E-step iteration (utils.py:1420-1439); north_star item 2 / SURVEY 7.1-5 ask for a blocked on-chip

@@ -1,5 +1,5 @@
 """Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list of `bench.py`: kernels of the LAST
-ELBO+grad evaluation (from the last build_C_kernel launch of the fused closure to the end of that evaluation),
+ELBO+grad evaluation (from one sep_apply_C_kernel / build_C_kernel launch of the fused closure to the next),
 grouped by kernel, with each kernel's share of the evaluation.
 
 usage: python scripts/summarize_launches.py gpurun_out/launches.csv [launches_per_eval [first_launch]] > profiles/rN_launches_summary.txt
@@ -28,7 +28,10 @@ def main():
     for rec in csv.DictReader(lines):
         if rec["Metric Name"] == "gpu__time_duration.sum":
             rows.append((rec["Kernel Name"], float(rec["Metric Value"].replace(",", "")) * 1e-6))
-    starts = [i for i, (k, _) in enumerate(rows) if "build_C_kernel" in k]
+    # one launch per evaluation marks its start: sep_apply_C_kernel on the separable path (C itself is built later, at the
+    # head of the inducing-point chain), build_C_kernel otherwise
+    marker = "sep_apply_C_kernel" if any("sep_apply_C_kernel" in k for k, _ in rows) else "build_C_kernel"
+    starts = [i for i, (k, _) in enumerate(rows) if marker in k]
     if len(starts) < 2:
         raise SystemExit("need at least two evaluations in the launch list")
     per_eval = int(sys.argv[2]) if len(sys.argv) > 2 else starts[-1] - starts[-2]
