@@ -298,6 +298,15 @@ def gen_fit_case(ref, name, N, n, m, cfg, theta_dict, maxiter, nE, nM, nF):
     return prob, fit
 
 
+def gen_fit_big(ref):
+    """Loop-level fixtures at sizes that reach the production kernels: BASELINE config 1 itself (separable quadratic forms,
+    cluster Cholesky), and an N = 8192 / 40 x 40 / m = 200 fit whose image-sized products run on the int8-slice engine."""
+    gen_fit_case(ref, "fit_c1_n20", N=2000, n=20, m=100, cfg=1, theta_dict=synth.theta_localised(20),
+                 maxiter=3, nE=3, nM=3, nF=3)
+    gen_fit_case(ref, "fit_n40_N8192_m200", N=8192, n=40, m=200, cfg=22, theta_dict=synth.THETA_DENSE,
+                 maxiter=3, nE=2, nM=3, nF=3)      # maxiter = 3: the reference's first M-step runs in iteration 1
+
+
 def gen_test_and_checkpoint(ref, prob, fit, name):
     """the reference's own test() / lambda_moments_star / explained_variance(sigma=False) on
     seeded test images for the model `fit` (the reference's varGP result of gen_fit_case), and that model written by
@@ -379,6 +388,9 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "big":
         gen_big(ref)
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "fitbig":
+        gen_fit_big(ref)
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "fit":
         prob_f, fit_f = gen_fit_case(ref, "fit_small_n10", N=400, n=10, m=40, cfg=21,
                                      theta_dict=synth.theta_localised(10), maxiter=4, nE=3, nM=3, nF=3)
@@ -404,6 +416,7 @@ def main():
     gen_test_and_checkpoint(ref, prob_f, fit_f, "test_small_n10")
     gen_active(ref)
     gen_big(ref)
+    gen_fit_big(ref)
 
 
 if __name__ == "__main__":

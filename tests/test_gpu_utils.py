@@ -37,9 +37,12 @@ def fit_args(fx, prob, dev):
         f_params={"logA": torch.tensor(prob.logA, device=dev), "lambda0": torch.tensor(prob.lambda0, device=dev)})
 
 
-def test_vargp_tracks_match_reference_on_gpu(U):
+@pytest.mark.parametrize("name", ["fit_small_n10", "fit_c1_n20", "fit_n40_N8192_m200"])
+def test_vargp_tracks_match_reference_on_gpu(U, name):
+    """The whole EM loop against the REAL reference's varGP: the small case, BASELINE config 1 itself (separable quadratic
+    forms, cluster Cholesky), and N = 8192 / 40 x 40 / m = 200, whose image-sized products run on the int8-slice engine."""
     from gaussian_processes_b200 import native
-    fx = load("fit_small_n10")
+    fx = load(name)
     keys = [str(k) for k in fx["theta_keys"]]
     prob = synth.make_problem(int(fx["N"]), int(fx["n"]), int(fx["m"]), cfg=int(fx["cfg"]),
                               theta=dict(zip(keys, fx["theta0"].tolist())))
@@ -50,7 +53,7 @@ def test_vargp_tracks_match_reference_on_gpu(U):
     assert native.launch_count(0) > 100          # the CUDA library did the work
     vt = fit["values_track"]
     got_t = np.stack([vt["theta_track"][k].cpu().numpy() for k in keys])
-    record("vargp_tracks", logmarginal=rel_err(vt["loss_track"]["logmarginal"].cpu().numpy(), fx["logmarginal"]),
+    record("vargp_tracks/" + name, logmarginal=rel_err(vt["loss_track"]["logmarginal"].cpu().numpy(), fx["logmarginal"]),
            loglik=rel_err(vt["loss_track"]["loglikelihood"].cpu().numpy(), fx["loglikelihood"]),
            KL=rel_err(vt["loss_track"]["KL"].cpu().numpy(), fx["KL"]), theta=rel_err(got_t, fx["theta_track"]),
            logA=rel_err(vt["f_par_track"]["logA"].cpu().numpy(), fx["logA_track"]))

@@ -45,9 +45,11 @@ def run_fit(U, name="fit_small_n10", **over):
     return fx, keys, prob, args, fit, err
 
 
-def test_vargp_tracks_match_reference(U):
-    """Loop-level parity: loss / theta / f-param tracks of the reference's own varGP."""
-    fx, keys, prob, args, fit, err = run_fit(U)
+@pytest.mark.parametrize("name", ["fit_small_n10", "fit_c1_n20"])
+def test_vargp_tracks_match_reference(U, name):
+    """Loop-level parity: loss / theta / f-param tracks of the reference's own varGP (the small case and
+    BASELINE config 1: N = 2000, 20 x 20, m = 100)."""
+    fx, keys, prob, args, fit, err = run_fit(U, name)
     assert not err["is_error"], err
     vt = fit["values_track"]
     tol = 1e-6   # LBFGS line searches amplify round-off differences of the adjoint vs forward-mode gradients
