@@ -388,6 +388,11 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "big":
         gen_big(ref)
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "fitc2":
+        # BASELINE config 2 itself (N = 100 000, 40 x 40, m = 500, dense theta): ~10 minutes and ~15 GB on 8 host cores
+        gen_fit_case(ref, "fit_c2_n40_N100000_m500", N=100000, n=40, m=500, cfg=2, theta_dict=synth.THETA_DENSE,
+                     maxiter=3, nE=2, nM=2, nF=2)
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "fitbig":
         gen_fit_big(ref)
         return

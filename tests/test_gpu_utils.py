@@ -37,10 +37,12 @@ def fit_args(fx, prob, dev):
         f_params={"logA": torch.tensor(prob.logA, device=dev), "lambda0": torch.tensor(prob.lambda0, device=dev)})
 
 
-@pytest.mark.parametrize("name", ["fit_small_n10", "fit_c1_n20", "fit_n40_N8192_m200"])
+@pytest.mark.parametrize("name", ["fit_small_n10", "fit_c1_n20", "fit_n40_N8192_m200", "fit_c2_n40_N100000_m500"])
 def test_vargp_tracks_match_reference_on_gpu(U, name):
     """The whole EM loop against the REAL reference's varGP: the small case, BASELINE config 1 itself (separable quadratic
-    forms, cluster Cholesky), and N = 8192 / 40 x 40 / m = 200, whose image-sized products run on the int8-slice engine."""
+    forms, cluster Cholesky), N = 8192 / 40 x 40 / m = 200, whose image-sized products run on the int8-slice engine, and
+    BASELINE config 2 itself (N = 100 000, 40 x 40, m = 500: the size bench.py times; ten minutes of the reference on 8 host
+    cores, oracle/gen_golden.py fitc2)."""
     from gaussian_processes_b200 import native
     fx = load(name)
     keys = [str(k) for k in fx["theta_keys"]]
