@@ -388,6 +388,16 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "big":
         gen_big(ref)
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "bigfull":
+        # the closure at BASELINE's full sizes: config 2 (N = 100 000, m = 500), dense and localised theta, and config 3's
+        # end point (N = 50 000, m = 1000).  Minutes each and up to ~25 GB on the host.
+        gen_big_closure_case(ref, "closure_c2_full_dense", N=100000, n=40, m=500, cfg=2, theta_dict=synth.THETA_DENSE,
+                             perturb={"eps_0x": 0.01, "-log2rho2": -0.02, "Amp": 0.05})
+        gen_big_closure_case(ref, "closure_c2_full_local", N=100000, n=40, m=500, cfg=2,
+                             theta_dict=synth.theta_localised(40), perturb={"eps_0x": 0.01, "eps_0y": -0.01})
+        gen_big_closure_case(ref, "closure_c3_full_m1000", N=50000, n=40, m=1000, cfg=3, theta_dict=synth.THETA_DENSE,
+                             perturb={"eps_0y": 0.01, "sigma_0": 0.05})
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "fitc2":
         # BASELINE config 2 itself (N = 100 000, 40 x 40, m = 500, dense theta): ~10 minutes and ~15 GB on 8 host cores
         gen_fit_case(ref, "fit_c2_n40_N100000_m500", N=100000, n=40, m=500, cfg=2, theta_dict=synth.THETA_DENSE,
