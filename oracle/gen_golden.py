@@ -160,6 +160,40 @@ def gen_big_closure_case(ref, name, N, n, m, cfg, theta_dict, perturb=None):
           f"-> {os.path.getsize(path)/1024:.0f} KiB")
 
 
+def gen_config5(ref, total=1000000, chunk=100000):
+    """BASELINE config 5 (10^6 images of 40 x 40, m = 500) through the real reference, on row chunks (the
+    likelihood part of the ELBO and its gradient are sums over images, KL does not depend on them): the reference's closure
+    on ten blocks of 100 000 images with the same q x q state, partial loglik / dloglik added.  ~25 minutes, ~30 GB."""
+    n, m, cfg = 40, 500, 5
+    prob, theta, B, m_b, V_b, ev = setup_case(ref, total, n, m, cfg, synth.THETA_DENSE)
+    theta = synth.theta_tensors({k: prob.theta[k] + {"eps_0x": 0.01, "-2log2beta": 0.02}.get(k, 0.0) for k in prob.theta})
+    f_params = {"logA": torch.tensor(prob.logA), "lambda0": torch.tensor(prob.lambda0)}
+    keys = list(theta.keys())
+    loglik, dloglik, KL, dKL = 0.0, None, None, None
+    sample_m, sample_v, sample_f = [], [], []
+    for c0 in range(0, total, chunk):
+        out = ref_closure(ref, theta, prob.X[c0:c0 + chunk], prob.r[c0:c0 + chunk], prob.xtilde, n, B, m_b, V_b, f_params)
+        loglik += float(out["loglik"])
+        dloglik = out["dloglik"].clone() if dloglik is None else dloglik + out["dloglik"]
+        if KL is None:
+            KL, dKL = float(out["KL"]), out["dKL"].clone()
+        sample_m.append(out["lam_m"][::1000].clone()); sample_v.append(out["lam_var"][::1000].clone())
+        sample_f.append(out["f"][::1000].clone())
+        print(f"  chunk at {c0}: partial loglik {float(out['loglik']):.6f}", flush=True)
+        del out
+    keep = ev > max(ev.max() * ref.EIGVAL_TOL, ref.EIGVAL_TOL)
+    fx = dict(N=total, n=n, m=m, cfg=cfg, chunk=chunk, theta=np.array([float(theta[k]) for k in keys]), theta_keys=np.array(keys),
+              theta_B=np.array([prob.theta[k] for k in keys]), q=B.shape[1], p=n * n, B=B.numpy(), eigvals=ev.numpy(),
+              keep=keep.numpy(), m_b=m_b.numpy(),
+              V_b_guard=np.array([float(V_b[0, 0]), float(V_b[-1, -1]), float(V_b[0, -1]), float(V_b.sum())]),
+              logA=prob.logA, lambda0=prob.lambda0, loglik=loglik, KL=KL, dloglik=dloglik.numpy(), dKL=dKL.numpy(),
+              lam_m_every_1000=torch.cat(sample_m).numpy(), lam_var_every_1000=torch.cat(sample_v).numpy(),
+              f_every_1000=torch.cat(sample_f).numpy())
+    path = os.path.join(ROOT, "tests", "golden", "closure_c5_full_1M.npz")
+    np.savez_compressed(path, **fx)
+    print(f"closure_c5_full_1M: loglik={loglik:.6f} KL={KL:.6f} -> {os.path.getsize(path)/1024:.0f} KiB")
+
+
 def gen_big(ref):
     """Fixtures at the sizes bench.py times: config 2 dense / localised, config-3 shape."""
     gen_big_closure_case(ref, "closure_c2_dense_n40", N=8192, n=40, m=500, cfg=2, theta_dict=synth.THETA_DENSE,
@@ -387,6 +421,9 @@ def main():
         return
     if len(sys.argv) > 1 and sys.argv[1] == "big":
         gen_big(ref)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "config5":
+        gen_config5(ref)
         return
     if len(sys.argv) > 1 and sys.argv[1] == "bigfull":
         # the closure at BASELINE's full sizes: config 2 (N = 100 000, m = 500), dense and localised theta, and config 3's
