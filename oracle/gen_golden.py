@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import io
 import contextlib
+import math
 import os
 import sys
 import types
@@ -192,6 +193,55 @@ def gen_config5(ref, total=1000000, chunk=100000):
     path = os.path.join(ROOT, "tests", "golden", "closure_c5_full_1M.npz")
     np.savez_compressed(path, **fx)
     print(f"closure_c5_full_1M: loglik={loglik:.6f} KL={KL:.6f} -> {os.path.getsize(path)/1024:.0f} KiB")
+
+
+def gen_config4_cells(ref, N=200000, chunk=100000):
+    """BASELINE config 4's shape through the real reference: three cells of a population that share N = 200 000 stimuli of
+    40 x 40 (m = 500), each with its own receptive-field centre (all crop the grid: p < P), spikes, subspace and variational
+    state.  The reference's closure per cell, on two blocks of 100 000 images (partial loglik / dloglik added)."""
+    n, m = 40, 500
+    base = dict(synth.THETA_DENSE)
+    base["-2log2beta"] = 1.9
+    eps = [(0.0, 0.0), (0.45, -0.4), (-0.5, 0.5)]
+    prob = synth.make_problem(N, n, m, cfg=4, theta=base)
+    g = torch.Generator().manual_seed(4000)
+    lo, hi = synth.THETA_LIMS_LO, synth.THETA_LIMS_HI
+    fx = dict(N=N, n=n, m=m, cfg=4, ncells=len(eps), theta_keys=np.array(list(synth.THETA_KEYS)), spike_seed=4000)
+    for c, (ex, ey) in enumerate(eps):
+        th = dict(base, eps_0x=ex, eps_0y=ey)
+        theta_B = synth.theta_tensors(th)
+        C, mask = ref.localker(theta=theta_B, theta_higher_lims=hi, theta_lower_lims=lo, n_px_side=n, grad=False)
+        Kt = ref.acosker(theta_B, prob.xtilde[:, mask], prob.xtilde[:, mask], C=C, dC=None, diag=False)
+        ev, evec = torch.linalg.eigh(Kt, UPLO="L")
+        keep = ev > max(ev.max() * ref.EIGVAL_TOL, ref.EIGVAL_TOL)
+        B = evec[:, keep]
+        m_b, V_b = synth.make_variational_state(torch.diag(ev[keep]), 40 + c)
+        r = torch.poisson(torch.full((N,), 0.6 + 0.2 * c, dtype=torch.float64), generator=g)
+        th_eval = dict(th)
+        th_eval["-log2rho2"] += 0.02 * (c + 1)                      # evaluate away from the theta B was built at
+        theta = synth.theta_tensors(th_eval)
+        f_params = {"logA": torch.tensor(math.log(0.05) + 0.01 * c), "lambda0": torch.tensor(-0.5 - 0.05 * c)}
+        loglik, dloglik, KL, dKL, sm, sv = 0.0, None, None, None, [], []
+        for c0 in range(0, N, chunk):
+            out = ref_closure(ref, theta, prob.X[c0:c0 + chunk], r[c0:c0 + chunk], prob.xtilde, n, B, m_b, V_b, f_params)
+            loglik += float(out["loglik"])
+            dloglik = out["dloglik"].clone() if dloglik is None else dloglik + out["dloglik"]
+            if KL is None:
+                KL, dKL, p = float(out["KL"]), out["dKL"].clone(), int(out["mask"].sum())
+            sm.append(out["lam_m"][::200].clone()); sv.append(out["lam_var"][::200].clone())
+            del out
+        keys = list(theta.keys())
+        fx.update({f"theta_{c}": np.array([float(theta[k]) for k in keys]), f"B_{c}": B.numpy(), f"eigvals_{c}": ev.numpy(),
+                   f"keep_{c}": keep.numpy(), f"m_b_{c}": m_b.numpy(),
+                   f"V_b_guard_{c}": np.array([float(V_b[0, 0]), float(V_b[-1, -1]), float(V_b[0, -1]), float(V_b.sum())]),
+                   f"logA_{c}": float(f_params["logA"]), f"lambda0_{c}": float(f_params["lambda0"]), f"p_{c}": p,
+                   f"r_sum_{c}": float(r.sum()), f"loglik_{c}": loglik, f"KL_{c}": KL, f"dloglik_{c}": dloglik.numpy(),
+                   f"dKL_{c}": dKL.numpy(), f"lam_m_every_200_{c}": torch.cat(sm).numpy(),
+                   f"lam_var_every_200_{c}": torch.cat(sv).numpy()})
+        print(f"  cell {c}: eps=({ex},{ey}) p={p} q={B.shape[1]} loglik={loglik:.6f} KL={KL:.6f}", flush=True)
+    path = os.path.join(ROOT, "tests", "golden", "cells_c4_full.npz")
+    np.savez_compressed(path, **fx)
+    print(f"cells_c4_full -> {os.path.getsize(path)/1024:.0f} KiB")
 
 
 def gen_big(ref):
@@ -421,6 +471,9 @@ def main():
         return
     if len(sys.argv) > 1 and sys.argv[1] == "big":
         gen_big(ref)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "config4":
+        gen_config4_cells(ref)
         return
     if len(sys.argv) > 1 and sys.argv[1] == "config5":
         gen_config5(ref)

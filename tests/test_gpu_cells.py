@@ -95,3 +95,60 @@ def test_cells_argument_checks():
         native.elbo_grad_cells(X.cpu(), [c["r"] for c in cells], xt, 12, [c["theta"] for c in cells],
                                [c["B"] for c in cells], [c["m_b"] for c in cells], [c["V_b"] for c in cells],
                                [0.0, 0.0], [0.0, 0.0])
+
+
+def test_cells_at_config4_size_against_the_reference():
+    """BASELINE config 4's shape against the REAL reference (oracle/gen_golden.py config4): three cells of a population on
+    N = 200 000 shared stimuli of 40 x 40, m = 500 -- own receptive-field centre (all three crop the grid: p = 1240 /
+    883 / 802), spikes, subspace and state each; the reference's closure per cell on two 100 000-image blocks.  One sgp_elbo_grad_cells call."""
+    from gaussian_processes_b200 import native
+    from helpers import load
+    fx = load("cells_c4_full")
+    N, n, m, nc = int(fx["N"]), int(fx["n"]), int(fx["m"]), int(fx["ncells"])
+    keys = [str(k) for k in fx["theta_keys"]]
+    prob = synth.make_problem(N, n, m, cfg=int(fx["cfg"]), theta=synth.THETA_DENSE)
+    X, xt = prob.X.to(D), prob.xtilde.to(D)
+    g = torch.Generator().manual_seed(int(fx["spike_seed"]))
+    cells = []
+    for c in range(nc):
+        ev = torch.from_numpy(fx[f"eigvals_{c}"])[torch.from_numpy(fx[f"keep_{c}"])]
+        m_b, V_b = synth.make_variational_state(torch.diag(ev), 40 + c)
+        got = np.array([float(V_b[0, 0]), float(V_b[-1, -1]), float(V_b[0, -1]), float(V_b.sum())])
+        assert np.allclose(got, fx[f"V_b_guard_{c}"], rtol=1e-13, atol=0) and np.array_equal(m_b.numpy(), fx[f"m_b_{c}"])
+        r = torch.poisson(torch.full((N,), 0.6 + 0.2 * c, dtype=torch.float64), generator=g)
+        assert float(r.sum()) == float(fx[f"r_sum_{c}"])          # the seeded spike trains are the reference's
+        cells.append(dict(theta=dict(zip(keys, fx[f"theta_{c}"].tolist())), B=torch.from_numpy(fx[f"B_{c}"]).to(D),
+                          m_b=m_b.to(D), V_b=V_b.to(D), r=r.to(D), logA=float(fx[f"logA_{c}"]),
+                          lambda0=float(fx[f"lambda0_{c}"])))
+    native.invalidate_cache(0)
+    try:
+        outs = native.elbo_grad_cells(X, [c["r"] for c in cells], xt, n, [c["theta"] for c in cells],
+                                      [c["B"] for c in cells], [c["m_b"] for c in cells], [c["V_b"] for c in cells],
+                                      [c["logA"] for c in cells], [c["lambda0"] for c in cells])
+        ps = []
+        for c, o in enumerate(outs):
+            dl, dk = fx[f"dloglik_{c}"], fx[f"dKL_{c}"]
+            gerr = max(abs(o["grad"][k] - (dl[i] - dk[i])) / max(abs(dl[i]), abs(dk[i])) for i, k in enumerate(keys))
+            e_ll = abs(o["loglik"] - float(fx[f"loglik_{c}"])) / abs(float(fx[f"loglik_{c}"]))
+            e_kl = abs(o["KL"] - float(fx[f"KL_{c}"])) / abs(float(fx[f"KL_{c}"]))
+            record(f"cells_c4_full/cell{c}", loglik=e_ll, KL=e_kl, grad_comp=gerr, p=o["p"])
+            assert o["flags"] == 0 and o["p"] == int(fx[f"p_{c}"])
+            # measured 1e-10 .. 7e-10 per gradient component: the largest is eps_0x of the cell centred at (0, 0), a sum over
+            # 200 000 images that cancels to ~10 by symmetry (spike trains independent of the stimuli); fixed-order
+            # reductions make the figure reproducible
+            assert e_ll <= 1e-9 and e_kl <= 1e-9 and gerr <= 1e-9, (c, e_ll, e_kl, gerr)
+            ps.append(o["p"])
+        assert min(ps) < n * n                                     # at least one cell's mask crops the grid
+        # the same cells one by one, with the per-image moments (every 200th image is in the fixture)
+        for c, cell in enumerate(cells):
+            o = native.elbo_grad(X, cell["r"], xt, n, cell["theta"], cell["B"], cell["m_b"], cell["V_b"], cell["logA"],
+                                 cell["lambda0"], want_moments=True)
+            lm, lv = o["lam_m"][::200].cpu().numpy(), o["lam_var"][::200].cpu().numpy()
+            rm, rv = fx[f"lam_m_every_200_{c}"], fx[f"lam_var_every_200_{c}"]
+            assert np.allclose(lm, rm, rtol=1e-9, atol=1e-11 * np.abs(rm).max())
+            assert np.allclose(lv, rv, rtol=1e-9, atol=1e-10)
+            assert abs(o["loglik"] - outs[c]["loglik"]) <= 1e-12 * abs(o["loglik"])
+    finally:
+        del X
+        native.release_cache(0)
+        torch.cuda.empty_cache()
