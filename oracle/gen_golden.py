@@ -317,6 +317,10 @@ def gen_active_case(ref, name, n, m0, n_add, same, N_fixed=None, cfg=31, fit=(3,
 def gen_active(ref):
     gen_active_case(ref, "active_same_n10", n=10, m0=40, n_add=3, same=True)
     gen_active_case(ref, "active_fixedN_n10", n=10, m0=40, n_add=3, same=False, N_fixed=400, cfg=32)
+    # larger cycles: 20 x 20 pixels, a fixed training set above the int8 threshold (N = 5000) with m = 100 -> 103, and the
+    # notebook's ntilde == nt configuration at m = 150 -> 153
+    gen_active_case(ref, "active_fixedN_n20_N5000", n=20, m0=100, n_add=3, same=False, N_fixed=5000, cfg=33)
+    gen_active_case(ref, "active_same_n20_m150", n=20, m0=150, n_add=3, same=True, cfg=34)
 
 
 def gen_kat(ref):

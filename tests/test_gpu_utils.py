@@ -254,7 +254,7 @@ def test_plot_entry_points_exist(U):
         assert fig is None and fig2 is None
 
 
-@pytest.mark.parametrize("name", ["active_same_n10", "active_fixedN_n10"])
+@pytest.mark.parametrize("name", ["active_same_n10", "active_fixedN_n10", "active_fixedN_n20_N5000", "active_same_n20_m150"])
 def test_active_learning_cycles_match_reference_on_gpu(U, name):
     """The active-learning cycle on the CUDA library: incremental K_tilde / K columns (sgp_acosker on one image; sgp_acosker_known for the column of K),
     eigh, warm start through init_kernel; ntilde == nt runs the fused a = B closure.  Tracks of every warm-started fit
