@@ -131,6 +131,39 @@ def parity_figure(native, orc_out, X, r, xt, n, theta, B, m_b, V_b, logA, lambda
             "flags": out["flags"], "tolerance": 1e-9}
 
 
+def reference_fixture_parity(native, X, r, xt, n):
+    """The WHOLE benchmark problem against the real reference: tests/golden/closure_c2_full_dense.npz holds the outputs of
+    the reference's own closure on these very N = 100 000 images (same seeds; oracle/gen_golden.py bigfull, minutes of the
+    reference on 8 host cores) at a theta and a subspace of its own.  One more evaluation, at that theta / state; default
+    path, default engine.  Only a fixture is read: nothing of the reference or of the oracle runs here."""
+    import numpy as np
+    path = os.path.join(ROOT, "tests", "golden", "closure_c2_full_dense.npz")
+    if not os.path.exists(path):
+        return {"unavailable": "tests/golden/closure_c2_full_dense.npz not found"}
+    fx = np.load(path)
+    if int(fx["N"]) != X.shape[0] or int(fx["n"]) != n or int(fx["m"]) != xt.shape[0] or int(fx["cfg"]) != CFG:
+        return {"unavailable": "the workload is not the fixture's (config 2: N = 100000, 40 x 40, m = 500)"}
+    keys = [str(k) for k in fx["theta_keys"]]
+    theta = dict(zip(keys, fx["theta"].tolist()))
+    ev = torch.from_numpy(fx["eigvals"])[torch.from_numpy(fx["keep"])]
+    m_b, V_b = synth.make_variational_state(torch.diag(ev), CFG)      # seeded: the state the reference was given
+    dev = X.device
+    out = native.elbo_grad(X, r, xt, n, theta, torch.from_numpy(fx["B"]).to(dev), m_b.to(dev), V_b.to(dev), float(fx["logA"]),
+                           float(fx["lambda0"]), want_moments=True)
+    g = max(abs(out["grad"][k] - (fx["dloglik"][i] - fx["dKL"][i])) / max(abs(fx["dloglik"][i]), abs(fx["dKL"][i]))
+            for i, k in enumerate(keys))
+
+    def vrel(a, b):
+        b = torch.from_numpy(b).to(a.device)
+        return float((a - b).abs().max() / b.abs().max())
+    return {"what": "all N images of the benchmark problem, GPU default path vs the REAL reference's closure (fixture "
+                    "closure_c2_full_dense, oracle/gen_golden.py bigfull)",
+            "loglik_rel": abs(out["loglik"] - float(fx["loglik"])) / abs(float(fx["loglik"])),
+            "KL_rel": abs(out["KL"] - float(fx["KL"])) / abs(float(fx["KL"])), "grad_rel_max": g,
+            "lam_m_rel_max": vrel(out["lam_m"], fx["lam_m"]), "lam_var_rel_max": vrel(out["lam_var"], fx["lam_var"]),
+            "f_rel_max": vrel(out["f"], fx["f"]), "flags": out["flags"], "tolerance": 1e-9}
+
+
 # ------------------------------------------------------------------------------------------------ reference arm
 def run_reference(args):
     """The reference's own algorithm on the host cores (oracle port: the Python reference cannot travel to the
@@ -900,6 +933,10 @@ def run_ours(args):
             parity = parity_figure(native, kept, X, r, xt, n, theta, B, m_b, V_b, prob.logA, prob.lambda0, chunk)
         except Exception as e:  # pragma: no cover
             parity = {"error": repr(e)}
+        try:
+            parity["reference_full_size"] = reference_fixture_parity(native, X, r, xt, n)
+        except Exception as e:  # pragma: no cover
+            parity["reference_full_size"] = {"error": repr(e)}
         # the reference-shaped computation on this very GPU through the libraries (cuBLAS / cuSOLVER / ATen)
         try:
             roof["library_gpu_baseline"] = library_gpu_baseline(orc, prob, X, r, xt, B, m_b, V_b)
@@ -959,6 +996,13 @@ def run_ours(args):
         if not (worst <= parity["tolerance"]) or parity["flags"] != 0:
             print(f"bench.py: parity against the CPU port FAILED ({worst:.3e} > 1e-9)", file=sys.stderr)
             sys.exit(3)
+        full = parity.get("reference_full_size") or {}
+        if "loglik_rel" in full:
+            worst = max(full[k] for k in ("loglik_rel", "KL_rel", "grad_rel_max", "lam_m_rel_max", "lam_var_rel_max",
+                                          "f_rel_max"))
+            if not (worst <= full["tolerance"]) or full["flags"] != 0:
+                print(f"bench.py: parity against the reference's full-size fixture FAILED ({worst:.3e} > 1e-9)", file=sys.stderr)
+                sys.exit(3)
 
 
 def main():
