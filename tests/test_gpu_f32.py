@@ -63,3 +63,34 @@ def test_fp32_entry_rejects_fp64_images():
     with pytest.raises(TypeError):
         native.elbo_grad_f32(prob.X.to(d), prob.r.to(d), prob.xtilde.to(d), prob.n_px_side, prob.theta, st["B"].to(d),
                              st["m_b"].to(d), st["V_b"].to(d), st["logA"], st["lambda0"])
+
+
+@pytest.mark.parametrize("name", ["closure_c2_full_dense", "closure_c3_full_m1000"])
+def test_fp32_mode_at_full_size_against_the_real_reference(name):
+    """fp32 mode at BASELINE's full sizes (config 2: N = 100 000, m = 500; config 3's end point: N = 50 000, m = 1000) against
+    the REAL reference's fp64 closure on the fp64 images (oracle/gen_golden.py bigfull): rounding the images to float32 and
+    running the products on five int8 slices must stay inside north_star's fp32 bar, 1e-4, on every output."""
+    from gaussian_processes_b200 import native
+    fx = load(name)
+    prob, st = case_inputs(fx)
+    d = torch.device("cuda:0")
+    X32, U32 = prob.X.float().to(d), prob.xtilde.float().to(d)
+    del prob.X
+    native.invalidate_cache(0)
+    try:
+        out = native.elbo_grad_f32(X32, prob.r.to(d), U32, prob.n_px_side, prob.theta, st["B"].to(d), st["m_b"].to(d),
+                                   st["V_b"].to(d), st["logA"], st["lambda0"], want_moments=True)
+    finally:
+        del X32
+        native.release_cache(0)
+        torch.cuda.empty_cache()
+    keys = [str(k) for k in fx["theta_keys"]]
+    e_ll = abs(out["loglik"] - float(fx["loglik"])) / abs(float(fx["loglik"]))
+    e_kl = abs(out["KL"] - float(fx["KL"])) / abs(float(fx["KL"]))
+    e_g = max(abs(out["grad"][k] - (fx["dloglik"][i] - fx["dKL"][i])) / max(abs(fx["dloglik"][i]), abs(fx["dKL"][i]))
+              for i, k in enumerate(keys))
+    e_m = float(np.abs(out["lam_m"].cpu().numpy() - fx["lam_m"]).max() / np.abs(fx["lam_m"]).max())
+    e_v = float(np.abs(out["lam_var"].cpu().numpy() - fx["lam_var"]).max() / np.abs(fx["lam_var"]).max())
+    record(f"f32_full/{name}", loglik=e_ll, KL=e_kl, grad_comp=e_g, lam_m=e_m, lam_var=e_v)
+    assert out["flags"] == 0 and out["p"] == int(fx["p"])
+    assert max(e_ll, e_kl, e_g, e_m, e_v) <= TOL, (e_ll, e_kl, e_g, e_m, e_v)
