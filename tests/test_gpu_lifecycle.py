@@ -114,3 +114,51 @@ def test_no_kernel_depends_on_stale_scratch():
     res = subprocess.run([sys.executable, "-m", "pytest", *files, "-m", "gpu", "-x", "-q", "-p", "no:cacheprovider"],
                          cwd=root, env=env, capture_output=True, text=True, timeout=900)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-2000:]
+
+
+def test_evaluations_are_bitwise_reproducible():
+    """Every reduction in the library runs in a fixed order (split-K partials summed by slice_reduce, per-block partials by
+    tickets, column scales by atomicMax -- order-independent): the same call gives the same bits, call after call, with cold
+    and warm caches, from a fresh handle in another thread, and on the int8 and the DMMA engine each."""
+    from gaussian_processes_b200 import native
+    n, m, N = 40, 200, 20000
+    prob = synth.make_problem(N, n, m, cfg=72, theta=synth.THETA_DENSE)
+    X, r, xt = prob.X.to(D), prob.r.to(D), prob.xtilde.to(D)
+    Cm, mask = native.localker(prob.theta, n, D)
+    Kt = native.acosker(prob.theta["sigma_0"], xt, xt, Cm, True)
+    ev, evec = torch.linalg.eigh(Kt, UPLO="L")
+    keep = ev > max(float(ev.max()) * 1e-4, 1e-4)
+    B = evec[:, keep].contiguous()
+    m_b, V_b = synth.make_variational_state(torch.diag(ev[keep]).cpu(), 72)
+    m_b, V_b = m_b.to(D), V_b.to(D)
+    theta = dict(prob.theta, eps_0x=0.07)
+
+    def ev_():
+        o = native.elbo_grad(X, r, xt, n, theta, B, m_b, V_b, prob.logA, prob.lambda0, want_moments=True)
+        return (o["loglik"], o["KL"], tuple(o["grad"][k] for k in native.THETA_KEYS), o["flags"]), o["lam_var"].clone()
+    for i8 in (-1, 0):
+        native.set_option(0, "i8_slices", i8)
+        native.set_slab_rows(0, 8192)                          # three slabs, a ragged last one
+        try:
+            native.invalidate_cache(0)
+            first, lv0 = ev_()                                 # cold caches
+            assert first[3] == 0
+            for rep in range(25):
+                if rep == 10:
+                    native.invalidate_cache(0)
+                got, lv = ev_()
+                assert got == first and torch.equal(lv, lv0), (i8, rep)
+            res = []
+
+            def other_thread():
+                torch.cuda.set_device(0)
+                native.set_option(0, "i8_slices", i8)          # this thread's own handle
+                native.set_slab_rows(0, 8192)
+                res.append(ev_())
+            t = threading.Thread(target=other_thread)
+            t.start(); t.join()
+            assert res and res[0][0] == first and torch.equal(res[0][1], lv0)
+        finally:
+            native.set_option(0, "i8_slices", -1)
+            native.set_slab_rows(0, 0)
+            native.invalidate_cache(0)
